@@ -1,0 +1,189 @@
+/*
+ * ghr.h -- C ABI of the B200-native GauHuman render hot path (libghr.so).
+ *
+ * Plain pointers and sizes only: no torch types, no C++ types, never throws.
+ * Every entry point returns 0 (GHR_OK) or a negative ghr_status; all work is
+ * enqueued on the caller's cudaStream_t (passed as void*), nothing is
+ * allocated behind the caller's back, no global state is kept between calls.
+ *
+ * Each entry point names the reference interface it replaces (paths relative
+ * to /root/reference/).  `dgr/` = submodules/diff-gaussian-rasterization/.
+ */
+#ifndef GHR_H_INCLUDED
+#define GHR_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GHR_VERSION 1
+#define GHR_TILE 16 /* dgr/cuda_rasterizer/config.h:16-17 BLOCK_X/BLOCK_Y */
+
+typedef enum ghr_status {
+    GHR_OK = 0,
+    GHR_ERR_BAD_ARG = -1,   /* null/misaligned pointer, negative size, bad shape */
+    GHR_ERR_BUFFER = -2,    /* a state/workspace buffer is smaller than required */
+    GHR_ERR_CUDA = -3,      /* a CUDA runtime call or (debug) a kernel failed    */
+    GHR_ERR_CAPACITY = -4,  /* num_rendered exceeded the binning capacity         */
+    GHR_ERR_PREFILTER = -5  /* prefiltered=1 but a Gaussian was culled            */
+} ghr_status;
+
+/*
+ * Per-call rasteriser configuration + inputs.  Mirrors the 19 positional
+ * arguments of _C.rasterize_gaussians (dgr/rasterize_points.h:19-39,
+ * dgr/rasterize_points.cu:36-120) and the fields of
+ * GaussianRasterizationSettings (dgr/diff_gaussian_rasterization/__init__.py:160-172).
+ * Absent optional inputs are NULL (the reference passes 0-element tensors and
+ * tests ptr==nullptr: forward.cu:205,241).  All pointers are device pointers
+ * to contiguous fp32 unless noted.  Matrices are the reference's transposed
+ * (column-major-as-read) 4x4s, dgr/cuda_rasterizer/auxiliary.h:58-77.
+ */
+typedef struct ghr_raster_params {
+    int32_t P;                /* number of Gaussians                              */
+    int32_t D;                /* active SH degree (0..3)                          */
+    int32_t M;                /* SH coefficients per channel in `shs` (0 if none) */
+    int32_t W, H;             /* image size in pixels                             */
+    float scale_modifier;
+    float tan_fovx, tan_fovy;
+    int32_t prefiltered;
+    int32_t debug;            /* 1: synchronise + check after every stage         */
+    const float* background;  /* [3]                                              */
+    const float* means3D;     /* [P,3]                                            */
+    const float* shs;         /* [P,M,3] or NULL                                  */
+    const float* colors_precomp; /* [P,3] or NULL                                 */
+    const float* opacities;   /* [P]                                              */
+    const float* scales;      /* [P,3] or NULL                                    */
+    const float* rotations;   /* [P,4] or NULL (not normalised, forward.cu:127)   */
+    const float* cov3D_precomp; /* [P,6] or NULL                                  */
+    const float* viewmatrix;  /* [16]                                             */
+    const float* projmatrix;  /* [16]                                             */
+    const float* campos;      /* [3]                                              */
+} ghr_raster_params;
+
+/*
+ * Byte offsets of the arrays inside the three opaque state buffers (the
+ * reference's geomBuffer / binningBuffer / imgBuffer, carved by fromChunk,
+ * dgr/cuda_rasterizer/rasterizer_impl.cu:155-194).  Layout is ours; exposed so
+ * parity tests can read tiles_touched / point_offsets / keys / ranges /
+ * n_contrib.  Sorted keys/ids live in buffer A or B depending on the device
+ * word `sorted_sel` (0 = A, 1 = B).
+ */
+typedef struct ghr_layout {
+    /* geom buffer */
+    size_t geom_bytes;
+    size_t g_header;        /* ghr_geom_header                                    */
+    size_t g_rec;           /* float4[P][3]: {px,py,depth,_} {conic xyz,opacity} {rgb,_} */
+    size_t g_tiles_touched; /* uint32[P]                                          */
+    size_t g_point_offsets; /* uint32[P] inclusive scan                           */
+    size_t g_cov3D;         /* float[P][6] (only when computed from scale/rot)    */
+    size_t g_clamped;       /* uint8[P] bit c set = channel c clamped             */
+    size_t g_scan_status;   /* uint64[ceil(P/256)+1] look-back words              */
+    /* img buffer */
+    size_t img_bytes;
+    size_t i_final_T;       /* float[W*H]                                         */
+    size_t i_n_contrib;     /* uint32[W*H]                                        */
+    size_t i_ranges;        /* uint2[tiles]                                       */
+    /* binning buffer */
+    size_t binning_bytes;
+    size_t b_header;        /* ghr_sort_header                                    */
+    size_t b_keys_a;        /* uint64[cap]  (unsorted keys are emitted here)      */
+    size_t b_keys_b;        /* uint64[cap]                                        */
+    size_t b_vals_a;        /* uint32[cap]                                        */
+    size_t b_vals_b;        /* uint32[cap]                                        */
+    size_t b_status;        /* uint32[passes][tiles_per_pass][256] look-back      */
+    int64_t capacity;       /* pairs the binning buffer holds                     */
+    int32_t sort_bits;      /* 32 + getHigherMsb(tiles), rasterizer_impl.cu:302   */
+    int32_t sort_passes;
+} ghr_layout;
+
+/* First bytes of the geom buffer (device memory). */
+typedef struct ghr_geom_header {
+    uint32_t num_rendered;  /* N = sum of tiles_touched (rasterizer_impl.cu:283)  */
+    uint32_t error;         /* 0 or -(ghr_status) raised on the device            */
+    uint32_t scan_ticket;   /* work counter of the fused preprocess+scan kernel   */
+    uint32_t reserved[61];
+} ghr_geom_header;
+
+int ghr_version(void);
+const char* ghr_error_string(int status);
+
+/* Sizes of the three state buffers.  `capacity` = max (Gaussian,tile) pairs
+ * the binning buffer can hold (the reference sizes it exactly from a blocking
+ * D2H read of num_rendered, rasterizer_impl.cu:283-287).                     */
+int ghr_state_layout(int32_t P, int64_t capacity, int32_t W, int32_t H, ghr_layout* out);
+
+/*
+ * Stage 1 of Rasterizer::forward (dgr/cuda_rasterizer/rasterizer_impl.cu:198-283):
+ * preprocessCUDA (forward.cu:156-256) fused with the InclusiveSum
+ * (rasterizer_impl.cu:279).  Writes radii[P] (int32), the packed geometry
+ * records, tiles_touched, point_offsets and num_rendered (into the geom header
+ * and, if non-NULL, into *num_rendered_host, which must be pinned/mapped host
+ * memory the device can write).
+ */
+int ghr_forward_preprocess(const ghr_raster_params* prm, int32_t* radii, void* geom, size_t geom_bytes,
+                           int32_t* num_rendered_host, void* stream);
+
+/*
+ * Stage 2 of Rasterizer::forward (rasterizer_impl.cu:285-341): duplicateWithKeys
+ * (:70-111), the depth|tile radix sort (:305-310, here a hand-written onesweep),
+ * identifyTileRanges (:116-138) and renderCUDA (forward.cu:261-383).
+ * num_rendered is read on the device; if it exceeds `capacity` nothing is
+ * rendered and GHR_ERR_CAPACITY is latched in the geom header.
+ * out_color [3,H,W], out_depth [H,W], out_alpha [H,W].
+ */
+int ghr_forward_render(const ghr_raster_params* prm, void* geom, size_t geom_bytes, void* binning,
+                       size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
+                       float* out_depth, float* out_alpha, void* stream);
+
+/*
+ * Rasterizer::backward (rasterizer_impl.cu:345-446): renderCUDA bwd
+ * (backward.cu:399-587), computeCov2DCUDA (:144-274) and preprocessCUDA bwd
+ * (:346-396) for _C.rasterize_gaussians_backward (dgr/rasterize_points.cu:122-207).
+ * `accum` is a float[P*12] workspace the caller zeroes (the packed per-Gaussian
+ * accumulator of the blend backward: dL_dcolor 0-2, dL_dmean2D 3-4, dL_dconic
+ * 5-7, dL_dopacity 8).  Every output is fully written for all P Gaussians
+ * (the reference instead zero-fills 75 floats per Gaussian first,
+ * rasterize_points.cu:159-167).  dL_dmeans2D [P,3], dL_dcolors [P,3],
+ * dL_dopacity [P], dL_dmeans3D [P,3], dL_dcov3D [P,6]; dL_dsh [P,M,3],
+ * dL_dscales [P,3], dL_drotations [P,4] may be NULL when the matching input is
+ * absent.
+ */
+int ghr_backward(const ghr_raster_params* prm, const int32_t* radii, const void* geom, size_t geom_bytes,
+                 const void* binning, size_t binning_bytes, int64_t capacity, const void* img, size_t img_bytes,
+                 const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha, float* accum,
+                 float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                 float* dL_dsh, float* dL_dscales, float* dL_drotations, void* stream);
+
+/* Rasterizer::markVisible / checkFrustum (rasterizer_impl.cu:54-66,141-153)
+ * for _C.mark_visible (dgr/rasterize_points.cu:209-228).  present: uint8[P]. */
+int ghr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream);
+
+/*
+ * The sort of rasterizer_impl.cu:305-310 in isolation (bench hook, Mkeys/s):
+ * stable LSD radix sort of N (uint64 key, uint32 value) pairs on key bits
+ * [0,bits).  keys_a/vals_a hold the input; the result is in A or B as
+ * reported through *sorted_sel_dev (device uint32).  workspace from
+ * ghr_sort_workspace_bytes.
+ */
+size_t ghr_sort_workspace_bytes(int64_t N);
+int ghr_sort_pairs_u64(int64_t N, int32_t bits, uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a,
+                       uint32_t* vals_b, void* workspace, size_t workspace_bytes, uint32_t* sorted_sel_dev,
+                       void* stream);
+
+/*
+ * distCUDA2 (submodules/simple-knn/spatial.cu:15-26 -> SimpleKNN::knn,
+ * simple_knn.cu:185-221): out[i] = mean of the 3 smallest squared distances
+ * from point i to the other points.
+ */
+size_t ghr_knn_workspace_bytes(int32_t P);
+int ghr_dist2_knn3(int32_t P, const float* points, float* out, void* workspace, size_t workspace_bytes,
+                   void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GHR_H_INCLUDED */

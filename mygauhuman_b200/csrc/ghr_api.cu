@@ -1,0 +1,244 @@
+// extern "C" entry points of libghr.so (declared in include/ghr.h).
+// Host side only: argument validation, buffer layout, stage sequencing.
+#include <stdio.h>
+#include <string.h>
+#include "ghr_common.cuh"
+#include "ghr_internal.h"
+
+using namespace ghr;
+
+namespace {
+
+inline bool misaligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) != 0; }
+
+int check_cuda(cudaError_t e, const char* what)
+{
+    if (e == cudaSuccess) return GHR_OK;
+    fprintf(stderr, "[libghr] CUDA error in %s: %s\n", what, cudaGetErrorString(e));
+    return GHR_ERR_CUDA;
+}
+
+// debug=1 mirrors the reference's CHECK_CUDA(.., debug): sync + check after each stage
+int stage_done(const ghr_raster_params* prm, cudaError_t launch_err, cudaStream_t s, const char* what)
+{
+    int r = check_cuda(launch_err, what);
+    if (r != GHR_OK) return r;
+    if (prm && prm->debug) return check_cuda(cudaStreamSynchronize(s), what);
+    return GHR_OK;
+}
+
+int validate(const ghr_raster_params* p)
+{
+    if (!p) return GHR_ERR_BAD_ARG;
+    if (p->P < 0 || p->W <= 0 || p->H <= 0 || p->M < 0 || p->D < 0 || p->D > 3) return GHR_ERR_BAD_ARG;
+    if (p->P == 0) return GHR_OK;
+    if (!p->means3D || !p->opacities || !p->viewmatrix || !p->projmatrix || !p->background) return GHR_ERR_BAD_ARG;
+    if (!p->shs && !p->colors_precomp) return GHR_ERR_BAD_ARG;
+    if (p->shs && (p->M <= 0 || !p->campos || (p->D + 1) * (p->D + 1) > p->M || p->M > 16)) return GHR_ERR_BAD_ARG;
+    if (!p->cov3D_precomp && (!p->scales || !p->rotations)) return GHR_ERR_BAD_ARG;
+    if (misaligned(p->means3D, 4) || misaligned(p->cov3D_precomp, 8) || misaligned(p->rotations, 16) ||
+        misaligned(p->shs, 16))
+        return GHR_ERR_BAD_ARG;
+    return GHR_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ghr_version(void) { return GHR_VERSION; }
+
+const char* ghr_error_string(int status)
+{
+    switch (status) {
+        case GHR_OK: return "ok";
+        case GHR_ERR_BAD_ARG: return "bad argument (null/misaligned pointer or bad size)";
+        case GHR_ERR_BUFFER: return "state/workspace buffer too small";
+        case GHR_ERR_CUDA: return "CUDA runtime or kernel error";
+        case GHR_ERR_CAPACITY: return "num_rendered exceeded the binning capacity";
+        case GHR_ERR_PREFILTER: return "Point is filtered although prefiltered is set";
+        default: return "unknown status";
+    }
+}
+
+int ghr_state_layout(int32_t P, int64_t capacity, int32_t W, int32_t H, ghr_layout* L)
+{
+    if (!L || P < 0 || capacity < 0 || W <= 0 || H <= 0 || capacity >= (int64_t(1) << 30)) return GHR_ERR_BAD_ARG;
+    memset(L, 0, sizeof(*L));
+    const size_t Ps = (size_t)P;
+    size_t o = 0;
+    L->g_header = o; o += align_up(sizeof(ghr_geom_header));
+    L->g_scan_status = o; o += align_up(sizeof(uint64_t) * ((Ps + GHR_BLOCK - 1) / GHR_BLOCK + 1));
+    L->g_rec = o; o += align_up(sizeof(float4) * 3 * Ps);
+    L->g_tiles_touched = o; o += align_up(sizeof(uint32_t) * Ps);
+    L->g_point_offsets = o; o += align_up(sizeof(uint32_t) * Ps);
+    L->g_cov3D = o; o += align_up(sizeof(float) * 6 * Ps);
+    L->g_clamped = o; o += align_up(Ps);
+    L->geom_bytes = o;
+
+    const size_t X = (size_t)W * H;
+    const size_t tiles = (size_t)((W + GHR_TILE - 1) / GHR_TILE) * ((H + GHR_TILE - 1) / GHR_TILE);
+    o = 0;
+    L->i_final_T = o; o += align_up(sizeof(float) * X);
+    L->i_n_contrib = o; o += align_up(sizeof(uint32_t) * X);
+    L->i_ranges = o; o += align_up(sizeof(uint2) * tiles);
+    L->img_bytes = o;
+
+    L->capacity = capacity;
+    L->sort_bits = 32 + (int32_t)higher_msb((uint32_t)tiles);
+    L->sort_passes = (L->sort_bits + kRadixBits - 1) / kRadixBits;
+    const size_t cap = (size_t)capacity;
+    o = 0;
+    L->b_header = o; o += align_up(sizeof(SortHeader));
+    L->b_status = o; o += align_up(sizeof(uint32_t) * (size_t)L->sort_passes * (size_t)sort_tiles(capacity) * kRadix);
+    L->b_keys_a = o; o += align_up(sizeof(uint64_t) * cap);
+    L->b_keys_b = o; o += align_up(sizeof(uint64_t) * cap);
+    L->b_vals_a = o; o += align_up(sizeof(uint32_t) * cap);
+    L->b_vals_b = o; o += align_up(sizeof(uint32_t) * cap);
+    L->binning_bytes = o;
+    return GHR_OK;
+}
+
+int ghr_forward_preprocess(const ghr_raster_params* prm, int32_t* radii, void* geom, size_t geom_bytes,
+                           int32_t* num_rendered_host, void* stream)
+{
+    int r = validate(prm);
+    if (r != GHR_OK) return r;
+    cudaStream_t s = (cudaStream_t)stream;
+    ghr_layout L;
+    if (ghr_state_layout(prm->P, 0, prm->W, prm->H, &L) != GHR_OK) return GHR_ERR_BAD_ARG;
+    if (!geom || geom_bytes < L.geom_bytes || misaligned(geom, 256)) return GHR_ERR_BUFFER;
+    if (prm->P == 0) {
+        r = check_cuda(cudaMemsetAsync(geom, 0, sizeof(ghr_geom_header), s), "preprocess(P=0)");
+        if (num_rendered_host) *num_rendered_host = 0;
+        return r;
+    }
+    if (!radii) return GHR_ERR_BAD_ARG;
+    return stage_done(prm, launch_preprocess(*prm, radii, (char*)geom, L, num_rendered_host, s), s, "preprocess");
+}
+
+int ghr_forward_render(const ghr_raster_params* prm, void* geom, size_t geom_bytes, void* binning,
+                       size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
+                       float* out_depth, float* out_alpha, void* stream)
+{
+    int r = validate(prm);
+    if (r != GHR_OK) return r;
+    if (!out_color || !out_depth || !out_alpha) return GHR_ERR_BAD_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    ghr_layout L;
+    if (ghr_state_layout(prm->P, capacity, prm->W, prm->H, &L) != GHR_OK) return GHR_ERR_BAD_ARG;
+    if (!geom || geom_bytes < L.geom_bytes || !img || img_bytes < L.img_bytes || misaligned(img, 256))
+        return GHR_ERR_BUFFER;
+    if (!binning || binning_bytes < L.binning_bytes || misaligned(binning, 256)) return GHR_ERR_BUFFER;
+    char* g = (char*)geom; char* b = (char*)binning; char* im = (char*)img;
+    if (prm->P == 0) {
+        // rasterize_points.cu:83: with no Gaussians the reference returns its zero-filled outputs untouched
+        const size_t X = (size_t)prm->W * prm->H;
+        r = check_cuda(cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * X, s), "P=0 memset");
+        if (r == GHR_OK) r = check_cuda(cudaMemsetAsync(out_depth, 0, sizeof(float) * X, s), "P=0 memset");
+        if (r == GHR_OK) r = check_cuda(cudaMemsetAsync(out_alpha, 0, sizeof(float) * X, s), "P=0 memset");
+        return r;
+    }
+    // one memset clears the sort header (tickets, histograms) and every pass's look-back words
+    r = check_cuda(cudaMemsetAsync(b + L.b_header, 0, L.b_keys_a - L.b_header, s), "binning memset");
+    if (r != GHR_OK) return r;
+    const uint32_t* n_dev = reinterpret_cast<const uint32_t*>(g + L.g_header);
+    if (capacity > 0 && prm->P > 0) {
+        r = stage_done(prm, launch_emit_keys(*prm, g, b, L, capacity, s), s, "emit_keys");
+        if (r != GHR_OK) return r;
+        r = stage_done(prm,
+                       launch_sort(reinterpret_cast<SortHeader*>(b + L.b_header), reinterpret_cast<uint32_t*>(b + L.b_status),
+                                   n_dev, capacity, L.sort_bits, reinterpret_cast<uint64_t*>(b + L.b_keys_a),
+                                   reinterpret_cast<uint64_t*>(b + L.b_keys_b), reinterpret_cast<uint32_t*>(b + L.b_vals_a),
+                                   reinterpret_cast<uint32_t*>(b + L.b_vals_b), s),
+                       s, "sort");
+        if (r != GHR_OK) return r;
+    }
+    r = stage_done(prm, launch_tile_ranges(*prm, g, b, im, L, capacity, s), s, "tile_ranges");
+    if (r != GHR_OK) return r;
+    return stage_done(prm, launch_blend_forward(*prm, g, b, im, L, out_color, out_depth, out_alpha, s), s, "blend_forward");
+}
+
+int ghr_backward(const ghr_raster_params* prm, const int32_t* radii, const void* geom, size_t geom_bytes,
+                 const void* binning, size_t binning_bytes, int64_t capacity, const void* img, size_t img_bytes,
+                 const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha, float* accum,
+                 float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                 float* dL_dsh, float* dL_dscales, float* dL_drotations, void* stream)
+{
+    int r = validate(prm);
+    if (r != GHR_OK) return r;
+    if (prm->P == 0) return GHR_OK;
+    if (!radii || !dL_dout_color || !dL_dout_depth || !dL_dout_alpha || !accum || !dL_dmeans2D || !dL_dcolors ||
+        !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || misaligned(accum, 16) || misaligned(dL_drotations, 16))
+        return GHR_ERR_BAD_ARG;
+    if (prm->shs && !dL_dsh) return GHR_ERR_BAD_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    ghr_layout L;
+    if (ghr_state_layout(prm->P, capacity, prm->W, prm->H, &L) != GHR_OK) return GHR_ERR_BAD_ARG;
+    if (!geom || geom_bytes < L.geom_bytes || !img || img_bytes < L.img_bytes || !binning ||
+        binning_bytes < L.binning_bytes)
+        return GHR_ERR_BUFFER;
+    r = stage_done(prm,
+                   launch_blend_backward(*prm, (const char*)geom, (const char*)binning, (const char*)img, L,
+                                         dL_dout_color, dL_dout_depth, dL_dout_alpha, accum, s),
+                   s, "blend_backward");
+    if (r != GHR_OK) return r;
+    return stage_done(prm,
+                      launch_preprocess_backward(*prm, radii, (const char*)geom, L, accum, dL_dmeans2D, dL_dcolors,
+                                                 dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, s),
+                      s, "preprocess_backward");
+}
+
+int ghr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream)
+{
+    (void)projmatrix;
+    if (P < 0) return GHR_ERR_BAD_ARG;
+    if (P == 0) return GHR_OK;
+    if (!means3D || !viewmatrix || !present) return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream), "mark_visible");
+}
+
+size_t ghr_sort_workspace_bytes(int64_t N)
+{
+    if (N < 0 || N >= (int64_t(1) << 30)) return 0;
+    return align_up(sizeof(SortHeader)) + align_up(sizeof(uint32_t) * (size_t)kMaxPasses * (size_t)sort_tiles(N) * kRadix) + 256;
+}
+
+int ghr_sort_pairs_u64(int64_t N, int32_t bits, uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a,
+                       uint32_t* vals_b, void* workspace, size_t workspace_bytes, uint32_t* sorted_sel_dev,
+                       void* stream)
+{
+    if (N < 0 || N >= (int64_t(1) << 30) || bits <= 0 || bits > 64) return GHR_ERR_BAD_ARG;
+    if (!workspace || workspace_bytes < ghr_sort_workspace_bytes(N) || misaligned(workspace, 256)) return GHR_ERR_BUFFER;
+    if (N > 0 && (!keys_a || !keys_b || !vals_a || !vals_b)) return GHR_ERR_BAD_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    char* w = (char*)workspace;
+    SortHeader* hdr = reinterpret_cast<SortHeader*>(w);
+    uint32_t* status = reinterpret_cast<uint32_t*>(w + align_up(sizeof(SortHeader)));
+    uint32_t* n_dev = reinterpret_cast<uint32_t*>(w + workspace_bytes - 256);  // last 256 B hold N
+    int r = check_cuda(cudaMemsetAsync(w, 0, workspace_bytes, s), "sort memset");
+    if (r != GHR_OK) return r;
+    const uint32_t n32 = (uint32_t)N;
+    r = check_cuda(cudaMemcpyAsync(n_dev, &n32, sizeof(n32), cudaMemcpyHostToDevice, s), "sort N upload");
+    if (r != GHR_OK) return r;
+    r = check_cuda(launch_sort(hdr, status, n_dev, N, bits, keys_a, keys_b, vals_a, vals_b, s), "sort");
+    if (r != GHR_OK) return r;
+    if (sorted_sel_dev)
+        r = check_cuda(cudaMemcpyAsync(sorted_sel_dev, &hdr->sorted_sel, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s),
+                       "sort sel copy");
+    return r;
+}
+
+size_t ghr_knn_workspace_bytes(int32_t P) { return knn_workspace_bytes(P); }
+
+int ghr_dist2_knn3(int32_t P, const float* points, float* out, void* workspace, size_t workspace_bytes, void* stream)
+{
+    if (P < 0) return GHR_ERR_BAD_ARG;
+    if (P == 0) return GHR_OK;
+    if (!points || !out) return GHR_ERR_BAD_ARG;
+    if (!workspace || workspace_bytes < knn_workspace_bytes(P) || misaligned(workspace, 256)) return GHR_ERR_BUFFER;
+    return check_cuda(launch_knn(P, points, out, (char*)workspace, workspace_bytes, (cudaStream_t)stream), "knn");
+}
+
+}  // extern "C"

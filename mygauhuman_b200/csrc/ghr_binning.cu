@@ -1,0 +1,113 @@
+// Key emission (reference rasterizer_impl.cu:70-111 duplicateWithKeys) and
+// tile range detection (rasterizer_impl.cu:116-138 identifyTileRanges).
+// HBM-stream kernels: emission 8*P + 12*V + 12*N bytes, ranges 8*N + 8*tiles.
+#include "ghr_common.cuh"
+#include "ghr_internal.h"
+
+namespace ghr {
+
+// One warp handles 32 Gaussians.  Gaussians touching few tiles are emitted by
+// their own lane; a Gaussian touching >= 32 tiles is emitted cooperatively by
+// the whole warp (lane-contiguous 8-B/4-B stores) so a screen-filling splat
+// does not serialise on one thread.  The emitted order (y-major, then x,
+// starting at point_offsets[idx-1]) is the reference's.
+__global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int H,
+                                                              const uint32_t* __restrict__ tiles_touched,
+                                                              const float4* __restrict__ rec,
+                                                              const uint32_t* __restrict__ point_offsets,
+                                                              const ghr_geom_header* __restrict__ hdr,
+                                                              int64_t capacity, uint64_t* __restrict__ keys,
+                                                              uint32_t* __restrict__ vals)
+{
+    if ((int64_t)hdr->num_rendered > capacity) return;  // overflow is latched by the ranges kernel
+    const int idx = blockIdx.x * GHR_BLOCK + threadIdx.x;
+    const uint32_t lane = lane_id();
+    const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE, gy = (H + GHR_TILE - 1) / GHR_TILE;
+    uint32_t minx = 0, miny = 0, maxx = 0, maxy = 0, off = 0, dbits = 0;
+    // tiles_touched > 0  <=>  radii > 0 (preprocess stores both or neither)
+    const bool visible = idx < P && tiles_touched[idx] > 0;
+    if (visible) {
+        const float4 r0 = rec[3 * (size_t)idx];
+        get_rect(r0.x, r0.y, __float_as_int(r0.w), gx, gy, minx, miny, maxx, maxy);
+        off = idx == 0 ? 0u : point_offsets[idx - 1];
+        dbits = __float_as_uint(r0.z);
+    }
+    const uint32_t w = maxx - minx;
+    const uint32_t cnt = w * (maxy - miny);
+    uint32_t big = __ballot_sync(0xffffffffu, cnt >= 32u);
+    if (cnt > 0 && cnt < 32u) {
+        for (uint32_t ty = miny; ty < maxy; ty++)
+            for (uint32_t tx = minx; tx < maxx; tx++) {
+                keys[off] = ((uint64_t)(ty * gx + tx) << 32) | dbits;
+                vals[off] = (uint32_t)idx;
+                off++;
+            }
+    }
+    while (big) {
+        const int src = __ffs(big) - 1;
+        big &= big - 1;
+        const uint32_t b_minx = __shfl_sync(0xffffffffu, minx, src), b_miny = __shfl_sync(0xffffffffu, miny, src);
+        const uint32_t b_w = __shfl_sync(0xffffffffu, w, src), b_cnt = __shfl_sync(0xffffffffu, cnt, src);
+        const uint32_t b_off = __shfl_sync(0xffffffffu, off, src), b_d = __shfl_sync(0xffffffffu, dbits, src);
+        const uint32_t b_idx = (uint32_t)(idx - (int)lane + src);
+        for (uint32_t k = lane; k < b_cnt; k += 32) {
+            const uint32_t ty = b_miny + k / b_w, tx = b_minx + k % b_w;
+            keys[b_off + k] = ((uint64_t)(ty * gx + tx) << 32) | b_d;
+            vals[b_off + k] = b_idx;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_kernel(ghr_geom_header* hdr, int64_t capacity,
+                                                                const SortHeader* __restrict__ sh,
+                                                                const uint64_t* __restrict__ keys_a,
+                                                                const uint64_t* __restrict__ keys_b, uint2* ranges)
+{
+    const int64_t L = hdr->num_rendered;
+    if (L > capacity) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicMax(&hdr->error, (uint32_t)(-GHR_ERR_CAPACITY));
+        return;
+    }
+    const uint64_t* __restrict__ keys = sh->sorted_sel ? keys_b : keys_a;
+    for (int64_t idx = (int64_t)blockIdx.x * GHR_BLOCK + threadIdx.x; idx < L; idx += (int64_t)gridDim.x * GHR_BLOCK) {
+        const uint32_t cur = (uint32_t)(keys[idx] >> 32);
+        if (idx == 0) ranges[cur].x = 0;
+        else {
+            const uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
+            if (cur != prev) { ranges[prev].y = (uint32_t)idx; ranges[cur].x = (uint32_t)idx; }
+        }
+        if (idx == L - 1) ranges[cur].y = (uint32_t)L;
+    }
+}
+
+cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binning,
+                             const ghr_layout& L, int64_t capacity, cudaStream_t s)
+{
+    if (p.P == 0) return cudaSuccess;
+    emit_keys_kernel<<<(p.P + GHR_BLOCK - 1) / GHR_BLOCK, GHR_BLOCK, 0, s>>>(
+        p.P, p.W, p.H, reinterpret_cast<const uint32_t*>(geom + L.g_tiles_touched),
+        reinterpret_cast<const float4*>(geom + L.g_rec),
+        reinterpret_cast<const uint32_t*>(geom + L.g_point_offsets),
+        reinterpret_cast<const ghr_geom_header*>(geom + L.g_header), capacity,
+        reinterpret_cast<uint64_t*>(binning + L.b_keys_a), reinterpret_cast<uint32_t*>(binning + L.b_vals_a));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, char* binning, char* img,
+                               const ghr_layout& L, int64_t capacity, cudaStream_t s)
+{
+    const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
+    cudaError_t e = cudaMemsetAsync(img + L.i_ranges, 0, sizeof(uint2) * (size_t)tiles, s);
+    if (e != cudaSuccess) return e;
+    int64_t grid = (capacity + GHR_BLOCK - 1) / GHR_BLOCK;
+    if (grid > 148 * 16) grid = 148 * 16;
+    if (grid < 1) grid = 1;
+    tile_ranges_kernel<<<(unsigned)grid, GHR_BLOCK, 0, s>>>(
+        reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header), capacity,
+        reinterpret_cast<const SortHeader*>(binning + L.b_header),
+        reinterpret_cast<const uint64_t*>(binning + L.b_keys_a),
+        reinterpret_cast<const uint64_t*>(binning + L.b_keys_b), reinterpret_cast<uint2*>(img + L.i_ranges));
+    return cudaGetLastError();
+}
+
+}  // namespace ghr

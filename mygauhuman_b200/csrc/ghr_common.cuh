@@ -1,0 +1,182 @@
+// Shared device helpers for libghr (sm_100a).
+//
+// Bit-exactness note: radii / tiles_touched / keys depend on the exact fp32
+// operation sequence of the reference kernels *as compiled* (which mul/add
+// pairs nvcc+ptxas fused into FFMA).  That sequence was read off the
+// reference's sm_100 SASS; here it is spelled with __fmaf_rn/__fmul_rn/
+// __fadd_rn/__fsub_rn/__frcp_rn/__fdiv_rn/__fsqrt_rn, which the compiler never
+// contracts or reorders, so the result does not depend on our own compiler's
+// fusion choices.  oracle/raster_oracle.c spells the same sequence with fmaf.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/ghr.h"
+
+#define GHR_BLOCK 256
+
+namespace ghr {
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ uint32_t lanemask_lt()
+{
+    uint32_t m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// m0*x + m4*y + m8*z + m12 as the reference compiles it
+// (auxiliary.h:58-77): t = y*m4; t = fma(x,m0,t); t = fma(z,m8,t); t = m12 + t
+__device__ __forceinline__ float affine_row(float x, float y, float z, float m0, float m4, float m8, float m12)
+{
+    float t = __fmul_rn(y, m4);
+    t = __fmaf_rn(x, m0, t);
+    t = __fmaf_rn(z, m8, t);
+    return __fadd_rn(m12, t);
+}
+
+// a0*b0 + a1*b1 + a2*b2 as the reference compiles a GLM mat3 product element
+__device__ __forceinline__ float dot3_glm(float a0, float b0, float a1, float b1, float a2, float b2)
+{
+    float t = __fmul_rn(a1, b1);
+    t = __fmaf_rn(a0, b0, t);
+    t = __fmaf_rn(a2, b2, t);
+    return t;
+}
+
+// auxiliary.h:41-44, evaluated in fp64 with one DFMA
+__device__ __forceinline__ float ndc2pix(float v, int S)
+{
+    double d = __dadd_rn((double)v, 1.0);
+    d = __fma_rn(d, (double)S, -1.0);
+    d = __dmul_rn(d, 0.5);
+    return (float)d;
+}
+
+// auxiliary.h:45-55
+__device__ __forceinline__ void get_rect(float px, float py, int max_radius, uint32_t gx, uint32_t gy, uint32_t& minx,
+                                         uint32_t& miny, uint32_t& maxx, uint32_t& maxy)
+{
+    const float rf = (float)max_radius;
+    minx = min(gx, (uint32_t)max(0, __float2int_rz(__fmul_rn(__fsub_rn(px, rf), 0.0625f))));
+    miny = min(gy, (uint32_t)max(0, __float2int_rz(__fmul_rn(__fsub_rn(py, rf), 0.0625f))));
+    maxx = min(gx, (uint32_t)max(0, __float2int_rz(__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(px, rf), 16.0f), -1.0f), 0.0625f))));
+    maxy = min(gy, (uint32_t)max(0, __float2int_rz(__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(py, rf), 16.0f), -1.0f), 0.0625f))));
+}
+
+// T = W*J of computeCov2D (forward.cu:74-113), shared by forward and backward.
+struct Cov2DCtx {
+    float T00, T01, T02, T10, T11, T12;  // T[c][r]; third column is zero
+    float tx, ty, tz;                    // clamped view-space mean
+    float txtz, tytz, limx, limy;
+};
+
+__device__ __forceinline__ void cov2d_T(float mx, float my, float mz, float fx, float fy, float tan_fovx,
+                                        float tan_fovy, const float* __restrict__ V, Cov2DCtx& c)
+{
+    const float tx = affine_row(mx, my, mz, V[0], V[4], V[8], V[12]);
+    const float ty = affine_row(mx, my, mz, V[1], V[5], V[9], V[13]);
+    const float tz = affine_row(mx, my, mz, V[2], V[6], V[10], V[14]);
+    const float limx = __fmul_rn(1.3f, tan_fovx), limy = __fmul_rn(1.3f, tan_fovy);
+    const float txtz = __fdiv_rn(tx, tz), tytz = __fdiv_rn(ty, tz);
+    const float clx = fminf(limx, fmaxf(-limx, txtz));
+    const float cly = fminf(limy, fmaxf(-limy, tytz));
+    const float tz2 = __fmul_rn(tz, tz);
+    const float J00 = __fdiv_rn(fx, tz);
+    const float J02 = __fdiv_rn(__fmul_rn(fx, __fmul_rn(clx, -tz)), tz2);
+    const float J11 = __fdiv_rn(fy, tz);
+    const float J12 = __fdiv_rn(__fmul_rn(fy, __fmul_rn(cly, -tz)), tz2);
+    c.T00 = __fmaf_rn(V[2], J02, __fmul_rn(V[0], J00));
+    c.T01 = __fmaf_rn(V[6], J02, __fmul_rn(V[4], J00));
+    c.T02 = __fmaf_rn(V[10], J02, __fmul_rn(V[8], J00));
+    c.T10 = __fmaf_rn(V[2], J12, __fmul_rn(J11, V[1]));
+    c.T11 = __fmaf_rn(V[6], J12, __fmul_rn(J11, V[5]));
+    c.T12 = __fmaf_rn(V[10], J12, __fmul_rn(J11, V[9]));
+    c.tx = __fmul_rn(clx, tz);
+    c.ty = __fmul_rn(cly, tz);
+    c.tz = tz;
+    c.txtz = txtz; c.tytz = tytz; c.limx = limx; c.limy = limy;
+}
+
+// cov = T^T * Vrk^T * T, + 0.3 low-pass (forward.cu:107-112)
+__device__ __forceinline__ void cov2d(const Cov2DCtx& c, const float* v, float& c00, float& c01, float& c11)
+{
+    const float A00 = dot3_glm(c.T00, v[0], c.T01, v[1], c.T02, v[2]);
+    const float A01 = dot3_glm(c.T10, v[0], c.T11, v[1], c.T12, v[2]);
+    const float A10 = dot3_glm(c.T00, v[1], c.T01, v[3], c.T02, v[4]);
+    const float A11 = dot3_glm(c.T10, v[1], c.T11, v[3], c.T12, v[4]);
+    const float A20 = dot3_glm(c.T00, v[2], c.T01, v[4], c.T02, v[5]);
+    const float A21 = dot3_glm(c.T10, v[2], c.T11, v[4], c.T12, v[5]);
+    c00 = __fadd_rn(dot3_glm(c.T00, A00, c.T01, A10, c.T02, A20), 0.3f);
+    c01 = dot3_glm(c.T00, A01, c.T01, A11, c.T02, A21);
+    c11 = __fadd_rn(dot3_glm(c.T10, A01, c.T11, A11, c.T12, A21), 0.3f);
+}
+
+// computeCov3D (forward.cu:118-152), FMA placement from the reference SASS.
+__device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s2, float mod, float r, float x,
+                                                     float y, float z, float* cov6)
+{
+    const float sx = __fmul_rn(s0, mod), sy = __fmul_rn(s1, mod), sz = __fmul_rn(s2, mod);
+    const float xz = __fmul_rn(x, z), rx = __fmul_rn(r, x), rz = __fmul_rn(r, z);
+    const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+    const float xz_p_ry = __fmaf_rn(r, y, xz), xz_m_ry = __fmaf_rn(-r, y, xz);
+    const float yz_m_rx = __fmaf_rn(y, z, -rx), yz_p_rx = __fmaf_rn(y, z, rx);
+    const float xy_m_rz = __fmaf_rn(x, y, -rz), xy_p_rz = __fmaf_rn(x, y, rz);
+    const float xx_p_yy = __fmaf_rn(x, x, yy), xx_p_zz = __fmaf_rn(x, x, zz);
+    const float yy_p_zz = __fadd_rn(yy, zz);
+    const float R00 = __fsub_rn(1.0f, __fadd_rn(yy_p_zz, yy_p_zz)), R01 = __fadd_rn(xy_m_rz, xy_m_rz),
+                R02 = __fadd_rn(xz_p_ry, xz_p_ry);
+    const float R10 = __fadd_rn(xy_p_rz, xy_p_rz), R11 = __fsub_rn(1.0f, __fadd_rn(xx_p_zz, xx_p_zz)),
+                R12 = __fadd_rn(yz_m_rx, yz_m_rx);
+    const float R20 = __fadd_rn(xz_m_ry, xz_m_ry), R21 = __fadd_rn(yz_p_rx, yz_p_rx),
+                R22 = __fsub_rn(1.0f, __fadd_rn(xx_p_yy, xx_p_yy));
+    const float M00 = __fmul_rn(sx, R00), M01 = __fmul_rn(sy, R01), M02 = __fmul_rn(sz, R02);
+    const float M10 = __fmul_rn(sx, R10), M11 = __fmul_rn(sy, R11), M12 = __fmul_rn(sz, R12);
+    const float M20 = __fmul_rn(sx, R20), M21 = __fmul_rn(sy, R21), M22 = __fmul_rn(sz, R22);
+    cov6[0] = dot3_glm(M00, M00, M01, M01, M02, M02);
+    cov6[1] = dot3_glm(M10, M00, M11, M01, M12, M02);
+    cov6[2] = dot3_glm(M20, M00, M21, M01, M22, M02);
+    cov6[3] = dot3_glm(M10, M10, M11, M11, M12, M12);
+    cov6[4] = dot3_glm(M20, M10, M21, M11, M22, M12);
+    cov6[5] = dot3_glm(M20, M20, M21, M21, M22, M22);
+}
+
+// SH constants, auxiliary.h:22-39
+#define GHR_SH_C0 0.28209479177387814f
+#define GHR_SH_C1 0.4886025119029199f
+__device__ __constant__ const float kSH_C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                                 -1.0925484305920792f, 0.5462742152960396f};
+__device__ __constant__ const float kSH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                                 0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
+                                                 -0.5900435899266435f};
+
+// power / alpha of one (pixel, Gaussian) pair exactly as renderCUDA compiles
+// (forward.cu:336-347): s = fma(dx, dx*a, dy*(dy*c)); power = fma(s,-0.5,-(dy*(dx*b)))
+__device__ __forceinline__ float pair_power(float dx, float dy, float ca, float cb, float cc)
+{
+    const float s = __fmaf_rn(dx, __fmul_rn(dx, ca), __fmul_rn(dy, __fmul_rn(dy, cc)));
+    return __fmaf_rn(s, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, cb)));
+}
+
+// ---- decoupled look-back status words -------------------------------------
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v)
+{
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t* p)
+{
+    uint64_t v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(uint64_t* p, uint64_t v)
+{
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+}  // namespace ghr

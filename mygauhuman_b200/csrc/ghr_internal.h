@@ -1,0 +1,72 @@
+// Host-side internals of libghr: buffer layouts and per-stage launchers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/ghr.h"
+
+namespace ghr {
+
+constexpr int kMaxPasses = 8;
+constexpr int kRadixBits = 8;
+constexpr int kRadix = 1 << kRadixBits;
+constexpr int kSortThreads = 256;
+
+// Control block at the start of the binning buffer (device memory).
+struct SortHeader {
+    uint32_t sorted_sel;              // buffer holding the sorted result: 0 = A, 1 = B
+    uint32_t num_passes;
+    uint32_t pad[2];
+    uint32_t pass_trivial[kMaxPasses];  // 1: all keys share this digit -> pass skipped
+    uint32_t pass_src[kMaxPasses];      // buffer a pass reads from
+    uint32_t ticket[kMaxPasses];        // dynamic tile counters (one per pass)
+    uint32_t hist[kMaxPasses][kRadix];  // global digit histograms
+    uint32_t bin_base[kMaxPasses][kRadix];  // exclusive scan of hist
+};
+
+// keys per onesweep tile for a given capacity (must match between layout and launch)
+inline int sort_items_per_thread(int64_t capacity) { return capacity <= (int64_t(1) << 20) ? 4 : 16; }
+inline int64_t sort_tiles(int64_t capacity)
+{
+    const int64_t tile = int64_t(kSortThreads) * sort_items_per_thread(capacity);
+    return (capacity + tile - 1) / tile;
+}
+
+inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// rasterizer_impl.cu:35-50 getHigherMsb
+inline uint32_t higher_msb(uint32_t n)
+{
+    uint32_t msb = sizeof(n) * 4, step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step; else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+// ---- stage launchers (each enqueues on `s`, returns the launch error) -----
+cudaError_t launch_preprocess(const ghr_raster_params& p, int32_t* radii, char* geom, const ghr_layout& L,
+                              int32_t* n_host, cudaStream_t s);
+cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binning,
+                             const ghr_layout& L, int64_t capacity, cudaStream_t s);
+// Sort N (device word) pairs held in A; header/status must be zeroed beforehand.
+cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev, int64_t capacity, int bits,
+                        uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, cudaStream_t s);
+cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, char* binning, char* img,
+                               const ghr_layout& L, int64_t capacity, cudaStream_t s);
+cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, const char* binning, char* img,
+                                 const ghr_layout& L, float* out_color, float* out_depth, float* out_alpha,
+                                 cudaStream_t s);
+cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, const char* binning, const char* img,
+                                  const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
+                                  const float* dL_dalpha, float* accum, cudaStream_t s);
+cudaError_t launch_preprocess_backward(const ghr_raster_params& p, const int32_t* radii, const char* geom,
+                                       const ghr_layout& L, const float* accum, float* dL_dmean2D, float* dL_dcolor,
+                                       float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                                       float* dL_dscale, float* dL_drot, cudaStream_t s);
+cudaError_t launch_mark_visible(int P, const float* means3D, const float* V, uint8_t* present, cudaStream_t s);
+size_t knn_workspace_bytes(int P);
+cudaError_t launch_knn(int P, const float* points, float* out, char* ws, size_t ws_bytes, cudaStream_t s);
+
+}  // namespace ghr

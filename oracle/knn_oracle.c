@@ -9,7 +9,7 @@
  * accelerate the search -- the result is the exact 3-NN value -- so the oracle
  * is the brute-force definition.  dist = dx*dx + dy*dy + dz*dz is evaluated
  * with the FMA placement nvcc uses for updateKBest (simple_knn.cu:134-135):
- * t = dx*dx; t = fma(dy,dy,t); t = fma(dz,dz,t).
+ * t = dy*dy; t = fma(dx,dx,t); t = fma(dz,dz,t)  (read off the reference PTX).
  * "best" slots that are never filled stay FLT_MAX as in the reference
  * (P < 4), so the mean overflows to +inf exactly as the reference does.
  */
@@ -25,7 +25,7 @@ void ora_dist2_knn3(int P, const float* pts, float* out)
         for (int j = 0; j < P; j++) {
             if (j == i) continue;
             float dx = pts[3 * j] - px, dy = pts[3 * j + 1] - py, dz = pts[3 * j + 2] - pz;
-            float d = dx * dx; d = fmaf(dy, dy, d); d = fmaf(dz, dz, d);
+            float d = dy * dy; d = fmaf(dx, dx, d); d = fmaf(dz, dz, d);
             for (int k = 0; k < 3; k++)
                 if (best[k] > d) { float t = best[k]; best[k] = d; d = t; }
         }
