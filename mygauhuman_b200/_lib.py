@@ -1,0 +1,102 @@
+"""ctypes binding of libghr.so (the C ABI declared in include/ghr.h).
+
+There is no CPU fallback: if the CUDA library is missing, import of the
+operators fails loudly (build it with ``python -c "import __graft_entry__ as g; g.build()"``
+or ``mygauhuman_b200/csrc/build.sh``).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libghr.so")
+
+GHR_OK = 0
+GHR_ERR_BAD_ARG, GHR_ERR_BUFFER, GHR_ERR_CUDA, GHR_ERR_CAPACITY, GHR_ERR_PREFILTER = -1, -2, -3, -4, -5
+
+c_f32p = C.c_void_p  # device pointers travel as integers
+
+
+class RasterParams(C.Structure):
+    """ghr_raster_params (include/ghr.h)."""
+    _fields_ = [
+        ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("W", C.c_int32), ("H", C.c_int32),
+        ("scale_modifier", C.c_float), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
+        ("prefiltered", C.c_int32), ("debug", C.c_int32),
+        ("background", c_f32p), ("means3D", c_f32p), ("shs", c_f32p), ("colors_precomp", c_f32p),
+        ("opacities", c_f32p), ("scales", c_f32p), ("rotations", c_f32p), ("cov3D_precomp", c_f32p),
+        ("viewmatrix", c_f32p), ("projmatrix", c_f32p), ("campos", c_f32p),
+    ]
+
+
+class Layout(C.Structure):
+    """ghr_layout (include/ghr.h)."""
+    _fields_ = [
+        ("geom_bytes", C.c_size_t), ("g_header", C.c_size_t), ("g_rec", C.c_size_t),
+        ("g_tiles_touched", C.c_size_t), ("g_point_offsets", C.c_size_t), ("g_cov3D", C.c_size_t),
+        ("g_clamped", C.c_size_t), ("g_scan_status", C.c_size_t),
+        ("img_bytes", C.c_size_t), ("i_final_T", C.c_size_t), ("i_n_contrib", C.c_size_t), ("i_ranges", C.c_size_t),
+        ("binning_bytes", C.c_size_t), ("b_header", C.c_size_t), ("b_keys_a", C.c_size_t), ("b_keys_b", C.c_size_t),
+        ("b_vals_a", C.c_size_t), ("b_vals_b", C.c_size_t), ("b_status", C.c_size_t),
+        ("capacity", C.c_int64), ("sort_bits", C.c_int32), ("sort_passes", C.c_int32),
+    ]
+
+
+# name -> (restype, argtypes); kept in one table so tests can check every
+# symbol include/ghr.h declares is exported.
+SIGNATURES = {
+    "ghr_version": (C.c_int, []),
+    "ghr_error_string": (C.c_char_p, [C.c_int]),
+    "ghr_state_layout": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.POINTER(Layout)]),
+    "ghr_forward_preprocess": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                         C.c_void_p]),
+    "ghr_forward_render": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                     C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p]),
+    "ghr_backward": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                               C.c_int64, C.c_void_p, C.c_size_t] + [C.c_void_p] * 13),
+    "ghr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ghr_sort_workspace_bytes": (C.c_size_t, [C.c_int64]),
+    "ghr_sort_pairs_u64": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_size_t, C.c_void_p, C.c_void_p]),
+    "ghr_knn_workspace_bytes": (C.c_size_t, [C.c_int32]),
+    "ghr_dist2_knn3": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+}
+
+_lib = None
+
+
+class GhrError(RuntimeError):
+    def __init__(self, status, where):
+        self.status = status
+        super().__init__(f"libghr {where}: {error_string(status)} (status {status})")
+
+
+def lib():
+    """Load libghr.so once; raise (never fall back) if it is not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: the CUDA library has not been built "
+                "(run mygauhuman_b200/csrc/build.sh). There is no CPU fallback.")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def error_string(status):
+    return lib().ghr_error_string(int(status)).decode()
+
+
+def check(status, where):
+    if status != GHR_OK:
+        raise GhrError(status, where)
+
+
+def state_layout(P, capacity, W, H):
+    L = Layout()
+    check(lib().ghr_state_layout(int(P), int(capacity), int(W), int(H), C.byref(L)), "ghr_state_layout")
+    return L

@@ -1,0 +1,229 @@
+"""Drop-in for the reference's compiled extension ``diff_gaussian_rasterization._C``
+(/root/reference/submodules/diff-gaussian-rasterization/ext.cpp:15-19,
+rasterize_points.cu:36-228): same three functions, same positional arguments,
+same return tuples -- implemented on the C ABI of libghr.so through ctypes.
+
+Differences that are deliberate and invisible to callers:
+* kernels run on torch's *current* stream (the reference uses the legacy
+  default stream);
+* the three opaque uint8 state tensors use libghr's layout (see
+  ``state_views``), not the reference's ``fromChunk`` layout;
+* ``prefiltered=True`` with a culled point raises instead of ``__trap()``-ing
+  the context (only checked when ``debug`` is set, as it needs a sync).
+"""
+import ctypes as C
+
+import torch
+
+from .. import _lib
+from .._lib import RasterParams, check, lib, state_layout
+
+# Sync-free mode: when set to an int, forward() does not read num_rendered back
+# to the host; the binning buffer is sized for that many (Gaussian, tile) pairs
+# and the returned "num_rendered" is that capacity.  Overflow is latched on the
+# device (see ``read_status``).  None = the reference's exact-size behaviour
+# (one 4-byte host read after the first kernel).
+_capacity = None
+_pinned = {}
+
+
+def set_sync_free_capacity(capacity):
+    global _capacity
+    _capacity = None if capacity is None else int(capacity)
+
+
+def _ptr(t, align=4):
+    if t is None or t.numel() == 0:
+        return None, t
+    if not t.is_cuda:
+        raise RuntimeError("libghr: tensor arguments must live on a CUDA device")
+    if t.dtype != torch.float32:
+        t = t.float()
+    t = t.contiguous()
+    if t.data_ptr() % align:
+        t = t.clone()
+    return t.data_ptr(), t
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _params(keep, background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+            projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug):
+    p = RasterParams()
+    p.P = means3D.size(0)
+    p.D = int(degree)
+    p.M = sh.size(1) if sh.numel() != 0 else 0
+    p.W, p.H = int(W), int(H)
+    p.scale_modifier = float(scale_modifier)
+    p.tan_fovx, p.tan_fovy = float(tan_fovx), float(tan_fovy)
+    p.prefiltered, p.debug = int(bool(prefiltered)), int(bool(debug))
+    for name, t, al in (("background", background, 4), ("means3D", means3D, 4), ("shs", sh, 16),
+                        ("colors_precomp", colors, 4), ("opacities", opacity, 4), ("scales", scales, 4),
+                        ("rotations", rotations, 16), ("cov3D_precomp", cov3D_precomp, 8),
+                        ("viewmatrix", viewmatrix, 4), ("projmatrix", projmatrix, 4), ("campos", campos, 4)):
+        ptr, t = _ptr(t, al)
+        keep.append(t)
+        setattr(p, name, ptr)
+    return p
+
+
+def _pinned_counter(device):
+    buf = _pinned.get(device)
+    if buf is None:
+        buf = torch.zeros(1, dtype=torch.int32).pin_memory()
+        _pinned[device] = buf
+    return buf
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, debug):
+    """RasterizeGaussiansCUDA, rasterize_points.cu:36-120."""
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    dev = means3D.device
+    if not means3D.is_cuda:
+        raise RuntimeError("libghr: tensor arguments must live on a CUDA device (there is no CPU fallback)")
+    f32 = dict(dtype=torch.float32, device=dev)
+    if P == 0:
+        u8 = dict(dtype=torch.uint8, device=dev)
+        return (0, torch.zeros(3, H, W, **f32), torch.zeros(1, H, W, **f32), torch.zeros(1, H, W, **f32),
+                torch.zeros(0, dtype=torch.int32, device=dev), torch.empty(0, **u8), torch.empty(0, **u8),
+                torch.empty(0, **u8))
+    with torch.cuda.device(dev):
+        keep = []
+        p = _params(keep, background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                    viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug)
+        L0 = state_layout(P, 0, W, H)
+        geom = torch.empty(L0.geom_bytes, dtype=torch.uint8, device=dev)
+        img = torch.empty(L0.img_bytes, dtype=torch.uint8, device=dev)
+        radii = torch.empty(P, dtype=torch.int32, device=dev)
+        out_color = torch.empty(3, H, W, **f32)
+        out_depth = torch.empty(1, H, W, **f32)
+        out_alpha = torch.empty(1, H, W, **f32)
+        l = lib()
+        s = _stream()
+        if _capacity is None:
+            counter = _pinned_counter(dev)
+            check(l.ghr_forward_preprocess(C.byref(p), radii.data_ptr(), geom.data_ptr(), geom.numel(),
+                                           counter.data_ptr(), s), "ghr_forward_preprocess")
+            torch.cuda.current_stream().synchronize()  # the reference's blocking D2H read, rasterizer_impl.cu:283
+            capacity = num_rendered = int(counter[0])
+        else:
+            check(l.ghr_forward_preprocess(C.byref(p), radii.data_ptr(), geom.data_ptr(), geom.numel(), None, s),
+                  "ghr_forward_preprocess")
+            capacity = num_rendered = _capacity
+        L = state_layout(P, capacity, W, H)
+        binning = torch.empty(L.binning_bytes, dtype=torch.uint8, device=dev)
+        check(l.ghr_forward_render(C.byref(p), geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(),
+                                   capacity, img.data_ptr(), img.numel(), out_color.data_ptr(), out_depth.data_ptr(),
+                                   out_alpha.data_ptr(), s), "ghr_forward_render")
+        if debug:
+            read_status(geom, raise_on_error=True)
+    return num_rendered, out_color, out_depth, out_alpha, radii, geom, binning, img
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                                 viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth,
+                                 dL_dout_alpha, sh, degree, campos, geomBuffer, R, binningBuffer, imageBuffer, alphas,
+                                 debug):
+    """RasterizeGaussiansBackwardCUDA, rasterize_points.cu:122-207."""
+    P = means3D.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    dev = means3D.device
+    if P == 0:
+        z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
+        return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
+    with torch.cuda.device(dev):
+        keep = []
+        # opacities are not an input of the reference backward (they live in the saved geometry state)
+        p = _params(keep, background, means3D, colors, means3D, scales, rotations, scale_modifier, cov3D_precomp,
+                    viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, False, debug)
+        # one allocation for the accumulator and every gradient; only the accumulator is zeroed
+        sizes = [12, 4, 3, 3, 1, 3, 6, 3, 3 * M]  # accum, drot, dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dscales, dsh
+        flat = torch.empty(P * sum(sizes), dtype=torch.float32, device=dev)
+        views, o = [], 0
+        for n in sizes:
+            views.append(flat[o:o + P * n])
+            o += P * n
+        accum, drot, dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dscales, dsh = views
+        accum.zero_()
+        g = [t.contiguous() if t.dtype == torch.float32 else t.float().contiguous()
+             for t in (dL_dout_color, dL_dout_depth, dL_dout_alpha)]
+        radii = radii.contiguous()
+        check(lib().ghr_backward(C.byref(p), radii.data_ptr(), geomBuffer.data_ptr(), geomBuffer.numel(),
+                                 binningBuffer.data_ptr(), binningBuffer.numel(), int(R), imageBuffer.data_ptr(),
+                                 imageBuffer.numel(), g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(),
+                                 accum.data_ptr(), dmeans2D.data_ptr(), dcolors.data_ptr(), dopacity.data_ptr(),
+                                 dmeans3D.data_ptr(), dcov3D.data_ptr(), dsh.data_ptr() if M else None,
+                                 dscales.data_ptr(), drot.data_ptr(), _stream()), "ghr_backward")
+    return (dmeans2D.view(P, 3), dcolors.view(P, 3), dopacity.view(P, 1), dmeans3D.view(P, 3), dcov3D.view(P, 6),
+            dsh.view(P, M, 3), dscales.view(P, 3), drot.view(P, 4))
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """markVisible, rasterize_points.cu:209-228."""
+    P = means3D.size(0)
+    present = torch.zeros(P, dtype=torch.bool, device=means3D.device)
+    if P:
+        with torch.cuda.device(means3D.device):
+            keep = []
+            ptrs = []
+            for t in (means3D, viewmatrix, projmatrix):
+                ptr, t = _ptr(t)
+                keep.append(t)
+                ptrs.append(ptr)
+            check(lib().ghr_mark_visible(P, ptrs[0], ptrs[1], ptrs[2], present.data_ptr(), _stream()),
+                  "ghr_mark_visible")
+    return present
+
+
+# ---- inspection helpers (parity tests, debugging) ---------------------------
+
+def read_status(geomBuffer, raise_on_error=False):
+    """(num_rendered, error) from the geometry header; synchronises."""
+    hdr = geomBuffer[:8].view(torch.int32).cpu()
+    n, err = int(hdr[0]), int(hdr[1])
+    if raise_on_error and err:
+        raise _lib.GhrError(-err, "device status")
+    return n, err
+
+
+def state_views(P, capacity, W, H, geomBuffer, binningBuffer, imageBuffer):
+    """Typed views of the internal state the reference keeps in its three buffers."""
+    L = state_layout(P, capacity, W, H)
+    X = W * H
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    g, b, im = geomBuffer, binningBuffer, imageBuffer
+
+    def view(buf, off, count, dtype, itemsize):
+        return buf[off:off + count * itemsize].view(dtype)
+
+    rec = view(g, L.g_rec, P * 12, torch.float32, 4).view(P, 3, 4)
+    out = {
+        "means2D": rec[:, 0, 0:2], "depths": rec[:, 0, 2], "conic_opacity": rec[:, 1, :], "rgb": rec[:, 2, 0:3],
+        "tiles_touched": view(g, L.g_tiles_touched, P, torch.int32, 4),
+        "point_offsets": view(g, L.g_point_offsets, P, torch.int32, 4),
+        "cov3D": view(g, L.g_cov3D, P * 6, torch.float32, 4).view(P, 6),
+        "clamped": view(g, L.g_clamped, P, torch.uint8, 1),
+        "final_T": view(im, L.i_final_T, X, torch.float32, 4).view(H, W),
+        "n_contrib": view(im, L.i_n_contrib, X, torch.int32, 4).view(H, W),
+        "ranges": view(im, L.i_ranges, tiles * 2, torch.int32, 4).view(tiles, 2),
+    }
+    if capacity > 0:
+        hdr = view(b, L.b_header, 4, torch.int32, 4)
+        sel = int(hdr[0])
+        n = min(read_status(g)[0], capacity)
+        ka = view(b, L.b_keys_a, capacity, torch.int64, 8)
+        kb = view(b, L.b_keys_b, capacity, torch.int64, 8)
+        va = view(b, L.b_vals_a, capacity, torch.int32, 4)
+        vb = view(b, L.b_vals_b, capacity, torch.int32, 4)
+        out["point_list_keys"] = (kb if sel else ka)[:n]
+        out["point_list"] = (vb if sel else va)[:n]
+        out["sorted_sel"] = sel
+        out["pass_trivial"] = view(b, L.b_header + 16, 8, torch.int32, 4)
+    return out

@@ -1,0 +1,105 @@
+"""CPU checks of the drop-in boundary: libghr.so loads and exports every
+symbol include/ghr.h declares; argument validation and layout (no compute)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from mygauhuman_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "ghr.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ghr_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    l = _lib.lib()
+    syms = declared_symbols()
+    assert len(syms) >= 11
+    for s in syms:
+        assert hasattr(l, s), f"{s} declared in include/ghr.h but not exported"
+        assert s in _lib.SIGNATURES, f"{s} has no ctypes signature"
+    assert l.ghr_version() == 1
+
+
+def test_error_strings():
+    assert _lib.error_string(0) == "ok"
+    for code in (-1, -2, -3, -4, -5):
+        assert _lib.error_string(code) not in ("ok", "unknown status")
+    assert "prefiltered" in _lib.error_string(-5)
+
+
+def test_layout_is_aligned_and_monotone():
+    L = _lib.state_layout(50000, 180000, 512, 512)
+    assert L.sort_bits == 43 and L.sort_passes == 6          # ZJU 512^2 -> 1024 tiles
+    assert _lib.state_layout(10, 10, 1024, 1024).sort_bits == 45
+    assert _lib.state_layout(10, 10, 1920, 1080).sort_bits == 45
+    offs = [L.g_header, L.g_scan_status, L.g_rec, L.g_tiles_touched, L.g_point_offsets, L.g_cov3D, L.g_clamped]
+    assert offs == sorted(offs) and all(o % 256 == 0 for o in offs) and L.geom_bytes > offs[-1]
+    b = [L.b_header, L.b_status, L.b_keys_a, L.b_keys_b, L.b_vals_a, L.b_vals_b]
+    assert b == sorted(b) and all(o % 256 == 0 for o in b)
+    assert L.b_keys_b - L.b_keys_a >= 8 * 180000 and L.binning_bytes - L.b_vals_b >= 4 * 180000
+    assert L.img_bytes >= 512 * 512 * 8 + 1024 * 8
+    assert L.capacity == 180000
+
+
+def test_bad_arguments_are_rejected_without_touching_the_gpu():
+    l = _lib.lib()
+    L = _lib.Layout()
+    assert l.ghr_state_layout(-1, 0, 16, 16, C.byref(L)) == _lib.GHR_ERR_BAD_ARG
+    assert l.ghr_state_layout(1, 1 << 30, 16, 16, C.byref(L)) == _lib.GHR_ERR_BAD_ARG
+    assert l.ghr_state_layout(1, 0, 0, 16, C.byref(L)) == _lib.GHR_ERR_BAD_ARG
+    p = _lib.RasterParams()
+    p.P, p.W, p.H = 4, 16, 16
+    assert l.ghr_forward_preprocess(C.byref(p), None, None, 0, None, None) == _lib.GHR_ERR_BAD_ARG  # null inputs
+    assert l.ghr_forward_preprocess(None, None, None, 0, None, None) == _lib.GHR_ERR_BAD_ARG
+    p.D = 7
+    assert l.ghr_forward_render(C.byref(p), None, 0, None, 0, 0, None, 0, None, None, None, None) == _lib.GHR_ERR_BAD_ARG
+    assert l.ghr_mark_visible(-1, None, None, None, None, None) == _lib.GHR_ERR_BAD_ARG
+    assert l.ghr_mark_visible(3, None, None, None, None, None) == _lib.GHR_ERR_BAD_ARG
+    assert l.ghr_sort_pairs_u64(-1, 32, None, None, None, None, None, 0, None, None) == _lib.GHR_ERR_BAD_ARG
+    assert l.ghr_sort_pairs_u64(10, 0, None, None, None, None, None, 0, None, None) == _lib.GHR_ERR_BAD_ARG
+    assert l.ghr_sort_pairs_u64(10, 40, None, None, None, None, None, 0, None, None) == _lib.GHR_ERR_BUFFER
+    assert l.ghr_dist2_knn3(-5, None, None, None, 0, None) == _lib.GHR_ERR_BAD_ARG
+    assert l.ghr_dist2_knn3(5, None, None, None, 0, None) == _lib.GHR_ERR_BAD_ARG
+    assert l.ghr_sort_workspace_bytes(1000) > 0 and l.ghr_knn_workspace_bytes(6890) > 0
+
+
+def test_operator_api_surface_and_argument_errors():
+    import torch
+    import mygauhuman_b200
+    from mygauhuman_b200.diff_gaussian_rasterization import (GaussianRasterizationSettings, GaussianRasterizer,
+                                                             rasterize_gaussians, _C)
+    assert GaussianRasterizationSettings._fields == (
+        "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
+        "sh_degree", "campos", "prefiltered", "debug")
+    for f in ("rasterize_gaussians", "rasterize_gaussians_backward", "mark_visible"):
+        assert callable(getattr(_C, f))
+    rs = GaussianRasterizationSettings(16, 16, 1.0, 1.0, torch.zeros(3), 1.0, torch.eye(4), torch.eye(4), 0,
+                                       torch.zeros(3), False, False)
+    r = GaussianRasterizer(rs)
+    x = torch.zeros(4, 3)
+    with pytest.raises(Exception, match="SHs or precomputed colors"):
+        r(means3D=x, means2D=x, opacities=x[:, :1])
+    with pytest.raises(Exception, match="SHs or precomputed colors"):
+        r(means3D=x, means2D=x, opacities=x[:, :1], shs=torch.zeros(4, 1, 3), colors_precomp=x)
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(means3D=x, means2D=x, opacities=x[:, :1], colors_precomp=x)
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(means3D=x, means2D=x, opacities=x[:, :1], colors_precomp=x, scales=x, rotations=torch.zeros(4, 4),
+          cov3D_precomp=torch.zeros(4, 6))
+    with pytest.raises(RuntimeError, match="num_points, 3"):
+        _C.rasterize_gaussians(torch.zeros(3), torch.zeros(4, 2), x, x[:, :1], x, x, 1.0, x, torch.eye(4), torch.eye(4),
+                               1.0, 1.0, 16, 16, x, 0, torch.zeros(3), False, False)
+    with pytest.raises(RuntimeError, match="CUDA"):  # no CPU fallback
+        _C.rasterize_gaussians(torch.zeros(3), x, x, x[:, :1], x, torch.zeros(4, 4), 1.0, torch.Tensor([]),
+                               torch.eye(4), torch.eye(4), 1.0, 1.0, 16, 16, torch.Tensor([]), 0, torch.zeros(3),
+                               False, False)
+    dgr, sknn = mygauhuman_b200.install()
+    import diff_gaussian_rasterization, simple_knn._C
+    assert diff_gaussian_rasterization is dgr and callable(simple_knn._C.distCUDA2)
