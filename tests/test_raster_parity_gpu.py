@@ -157,7 +157,7 @@ def test_mark_visible_matches_reference():
     from mygauhuman_b200.diff_gaussian_rasterization import _C
     from oracle import ref_cuda
     import oracle as O
-    case = Cm.raster_case(5000, 64, 64, seed=9, radius=0.6)
+    case = Cm.raster_case(5000, 64, 64, seed=9, radius=0.05)  # camera inside the body
     tc = Cm.to_torch(case, "cuda")
     ours = _C.mark_visible(tc["means3D"], tc["view"], tc["proj"])
     assert np.array_equal(_np(ours), O.mark_visible(case["means3D"], case["view"], case["proj"]))
