@@ -183,6 +183,35 @@ size_t ghr_knn_workspace_bytes(int32_t P);
 int ghr_dist2_knn3(int32_t P, const float* points, float* out, void* workspace, size_t workspace_bytes,
                    void* stream);
 
+/*
+ * Measurement hooks (no reference counterpart; the reference has no profiling
+ * facility beyond wall-clock prints, train.py:209).  Process-wide, off by
+ * default, the only state the library keeps between calls.
+ *  - ghr_launch_count: kernels this library has launched since it was loaded.
+ *  - ghr_profile_enable(1): every entry point brackets each stage with CUDA
+ *    events on the caller's stream.  ghr_profile_read synchronises those
+ *    events, returns the summed device milliseconds and the span count per
+ *    stage (arrays of GHR_STAGE_COUNT) and clears the record.
+ */
+enum ghr_stage {
+    GHR_STAGE_PREPROCESS = 0,   /* fused preprocess + scan                       */
+    GHR_STAGE_EMIT_KEYS = 1,
+    GHR_STAGE_SORT = 2,         /* histogram + plan + onesweep passes            */
+    GHR_STAGE_TILE_RANGES = 3,
+    GHR_STAGE_BLEND_FWD = 4,
+    GHR_STAGE_BLEND_BWD = 5,
+    GHR_STAGE_PREPROCESS_BWD = 6,
+    GHR_STAGE_KNN = 7,
+    GHR_STAGE_LBS_JOINTS = 8,
+    GHR_STAGE_LBS_FWD = 9,
+    GHR_STAGE_LBS_BWD = 10,
+    GHR_STAGE_MISC = 11,
+    GHR_STAGE_COUNT = 12
+};
+uint64_t ghr_launch_count(void);
+int ghr_profile_enable(int on);
+int ghr_profile_read(double* ms_out, int64_t* count_out);
+
 #ifdef __cplusplus
 }
 #endif

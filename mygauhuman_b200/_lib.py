@@ -59,7 +59,13 @@ SIGNATURES = {
     "ghr_sort_pairs_u64": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_size_t, C.c_void_p, C.c_void_p]),
     "ghr_knn_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "ghr_dist2_knn3": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "ghr_launch_count": (C.c_uint64, []),
+    "ghr_profile_enable": (C.c_int, [C.c_int]),
+    "ghr_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
 }
+
+STAGES = ("preprocess", "emit_keys", "sort", "tile_ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "knn",
+          "lbs_joints", "lbs_fwd", "lbs_bwd", "misc")
 
 _lib = None
 
@@ -94,6 +100,23 @@ def error_string(status):
 def check(status, where):
     if status != GHR_OK:
         raise GhrError(status, where)
+
+
+def launch_count():
+    """Kernels launched by libghr since it was loaded."""
+    return int(lib().ghr_launch_count())
+
+
+def profile_enable(on=True):
+    check(lib().ghr_profile_enable(int(bool(on))), "ghr_profile_enable")
+
+
+def profile_read():
+    """{stage: (device ms summed over spans, span count)} since the last read; synchronises."""
+    ms = (C.c_double * len(STAGES))()
+    cnt = (C.c_int64 * len(STAGES))()
+    check(lib().ghr_profile_read(ms, cnt), "ghr_profile_read")
+    return {name: (ms[i], cnt[i]) for i, name in enumerate(STAGES)}
 
 
 def state_layout(P, capacity, W, H):

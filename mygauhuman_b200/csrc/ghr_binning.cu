@@ -84,6 +84,8 @@ cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binni
                              const ghr_layout& L, int64_t capacity, cudaStream_t s)
 {
     if (p.P == 0) return cudaSuccess;
+    StageTimer timer(GHR_STAGE_EMIT_KEYS, s);
+    count_launch();
     emit_keys_kernel<<<(p.P + GHR_BLOCK - 1) / GHR_BLOCK, GHR_BLOCK, 0, s>>>(
         p.P, p.W, p.H, reinterpret_cast<const uint32_t*>(geom + L.g_tiles_touched),
         reinterpret_cast<const float4*>(geom + L.g_rec),
@@ -96,6 +98,8 @@ cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binni
 cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, char* binning, char* img,
                                const ghr_layout& L, int64_t capacity, cudaStream_t s)
 {
+    StageTimer timer(GHR_STAGE_TILE_RANGES, s);
+    count_launch();
     const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
     cudaError_t e = cudaMemsetAsync(img + L.i_ranges, 0, sizeof(uint2) * (size_t)tiles, s);
     if (e != cudaSuccess) return e;

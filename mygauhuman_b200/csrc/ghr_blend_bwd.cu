@@ -19,8 +19,6 @@
 
 namespace ghr {
 
-constexpr int kBatchB = 256;
-
 __device__ __forceinline__ void cp_async16b(void* smem, const void* gmem)
 {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
@@ -69,32 +67,53 @@ __device__ __forceinline__ int reduce_slot(uint32_t lane)
     return local < 5 ? local : 99;
 }
 
-__global__ void __launch_bounds__(256) blend_backward_kernel(
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) blend_backward_kernel(
     int W, int H, const uint2* __restrict__ ranges, const SortHeader* __restrict__ sh,
     const uint32_t* __restrict__ vals_a, const uint32_t* __restrict__ vals_b, const float4* __restrict__ rec,
     const ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
     const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
     const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas, float* __restrict__ accum)
 {
-    __shared__ __align__(16) float4 s_rec[2][kBatchB * 3];
-    __shared__ uint32_t s_id[2][kBatchB];
+    constexpr int THREADS = WARPS * 32;
+    constexpr int SUBS = 8 / WARPS;
+    constexpr int BATCH = 128;
+    constexpr int PER_THREAD = BATCH / THREADS;
+    static_assert(BATCH % THREADS == 0, "batch/threads");
+    __shared__ __align__(16) float4 s_rec[2][BATCH * 3];
+    __shared__ uint32_t s_id[2][BATCH];
 
-    const uint32_t tx = threadIdx.x & 15, ty = threadIdx.x >> 4, lane = threadIdx.x & 31;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
-    const uint32_t pixx = blockIdx.x * GHR_TILE + tx, pixy = blockIdx.y * GHR_TILE + ty;
+    const uint32_t tile_x = blockIdx.x / SUBS, sub = blockIdx.x % SUBS, tile_y = blockIdx.y;
+    const uint32_t wb = sub * WARPS + warp;  // same 8x4 pixel blocks as the forward
+    const uint32_t bx0 = tile_x * GHR_TILE + (wb & 1u) * 8u, by0 = tile_y * GHR_TILE + (wb >> 1) * 4u;
+    const uint32_t pixx = bx0 + (lane & 7u), pixy = by0 + (lane >> 3);
     const bool inside = pixx < (uint32_t)W && pixy < (uint32_t)H;
     const float pxf = (float)pixx, pyf = (float)pixy;
+    const float rx0 = (float)bx0, rx1 = (float)(bx0 + 7u), ry0 = (float)by0, ry1 = (float)(by0 + 3u);
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
-    const uint2 range = overflow ? make_uint2(0, 0) : ranges[blockIdx.y * gx + blockIdx.x];
+    const uint2 range = overflow ? make_uint2(0, 0) : ranges[tile_y * gx + tile_x];
     const uint32_t* __restrict__ point_list = sh->sorted_sel ? vals_b : vals_a;
     const int todo_total = (int)(range.y - range.x);
-    const int rounds = (todo_total + kBatchB - 1) / kBatchB;
-    if (rounds == 0) return;
 
     const size_t pix = (size_t)pixy * W + pixx, HW = (size_t)H * W;
     const float T_final = inside ? final_Ts[pix] : 0.0f;
     float T = T_final;
     const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+    // the CTA only walks the part of the list some pixel of it still needs
+    __shared__ int s_cta_last[WARPS];
+    const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0) s_cta_last[warp] = warp_last;
+    __syncthreads();
+    int cta_last = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) cta_last = max(cta_last, s_cta_last[w]);
+    // list positions [0, cta_last) are needed; walk them back to front
+    const int walk = min(todo_total, cta_last);
+    const int rounds = (walk + BATCH - 1) / BATCH;
+    if (rounds == 0) return;
+
     float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, dL_ddepth = 0.f, dL_dalpha = 0.f;
     if (inside) {
         dpix0 = dL_dpixels[pix]; dpix1 = dL_dpixels[HW + pix]; dpix2 = dL_dpixels[2 * HW + pix];
@@ -104,83 +123,112 @@ __global__ void __launch_bounds__(256) blend_backward_kernel(
     float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
     float accum_depth_rec = 0.f, accum_alpha_rec = 0.f, last_alpha = 0.f, last_depth = 0.f;
     const float ddelx_dx = (float)(0.5 * W), ddely_dy = (float)(0.5 * H);
-    // highest list position any pixel of this warp still needs
-    const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
     const int slot = reduce_slot(lane);
     const bool writer = slot < 9 && !(lane & 1);
 
+    // round r stages list positions walk-1-r*BATCH-slot (back to front)
     auto stage = [&](int round, int buf) {
-        const int progress = round * kBatchB + (int)threadIdx.x;
-        if (progress < todo_total) {
-            const uint32_t id = point_list[range.y - 1 - (uint32_t)progress];  // back to front
-            s_id[buf][threadIdx.x] = id;
-            const float4* src = rec + 3 * (size_t)id;
-            float4* dst = &s_rec[buf][threadIdx.x * 3];
-            cp_async16b(dst, src);
-            cp_async16b(dst + 1, src + 1);
-            cp_async16b(dst + 2, src + 2);
+#pragma unroll
+        for (int u = 0; u < PER_THREAD; u++) {
+            const int sl = (int)threadIdx.x + u * THREADS;
+            const int progress = round * BATCH + sl;
+            if (progress < walk) {
+                const uint32_t id = point_list[range.x + (uint32_t)(walk - 1 - progress)];
+                s_id[buf][sl] = id;
+                const float4* src = rec + 3 * (size_t)id;
+                float4* dst = &s_rec[buf][sl * 3];
+                cp_async16b(dst, src);
+                cp_async16b(dst + 1, src + 1);
+                cp_async16b(dst + 2, src + 2);
+            }
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
     stage(0, 0);
-    int contributor = todo_total;
-    int toDo = todo_total;
-    for (int i = 0; i < rounds; i++, toDo -= kBatchB) {
+    int toDo = walk;
+    for (int i = 0; i < rounds; i++, toDo -= BATCH) {
         const int buf = i & 1;
         if (i + 1 < rounds) { stage(i + 1, buf ^ 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
         else asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
-        const int n = min(kBatchB, toDo);
+        const int n = min(BATCH, toDo);
         const float4* r = s_rec[buf];
-        // entries with contributor-1 >= warp_last are beyond every pixel's last contributor
-        int j0 = contributor - warp_last;
-        j0 = j0 < 0 ? 0 : (j0 > n ? n : j0);
-        contributor -= j0;
-        for (int j = j0; j < n; j++) {
-            contributor--;
-            const float4 r0 = r[3 * j], r1 = r[3 * j + 1];
-            const float dx = __fsub_rn(r0.x, pxf), dy = __fsub_rn(r0.y, pyf);
-            const float power = pair_power(dx, dy, r1.x, r1.y, r1.z);
-            const float G = expf(power);
-            const float alpha = fminf(0.99f, __fmul_rn(r1.w, G));
-            const bool valid = (contributor < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-            if (!__any_sync(0xffffffffu, valid)) continue;
-            float v[9];
-#pragma unroll
-            for (int k = 0; k < 9; k++) v[k] = 0.0f;
-            if (valid) {
-                const float4 r2 = r[3 * j + 2];
-                T = T / (1.0f - alpha);
-                const float dchannel_dcolor = alpha * T;
-                float dL_dopa = 0.0f;
-                acc0 = last_alpha * lc0 + (1.0f - last_alpha) * acc0; lc0 = r2.x;
-                dL_dopa += (r2.x - acc0) * dpix0; v[0] = dchannel_dcolor * dpix0;
-                acc1 = last_alpha * lc1 + (1.0f - last_alpha) * acc1; lc1 = r2.y;
-                dL_dopa += (r2.y - acc1) * dpix1; v[1] = dchannel_dcolor * dpix1;
-                acc2 = last_alpha * lc2 + (1.0f - last_alpha) * acc2; lc2 = r2.z;
-                dL_dopa += (r2.z - acc2) * dpix2; v[2] = dchannel_dcolor * dpix2;
-                accum_depth_rec = last_alpha * last_depth + (1.0f - last_alpha) * accum_depth_rec;
-                last_depth = r0.z;
-                dL_dopa += (r0.z - accum_depth_rec) * dL_ddepth;
-                accum_alpha_rec = last_alpha + (1.0f - last_alpha) * accum_alpha_rec;
-                dL_dopa += (1.0f - accum_alpha_rec) * dL_dalpha;
-                dL_dopa *= T;
-                last_alpha = alpha;
-                dL_dopa += (-T_final / (1.0f - alpha)) * bg_dot;
-                const float dL_dG = r1.w * dL_dopa;
-                const float gdx = G * dx, gdy = G * dy;
-                const float dG_ddelx = -gdx * r1.x - gdy * r1.y;
-                const float dG_ddely = -gdy * r1.z - gdx * r1.y;
-                v[3] = dL_dG * dG_ddelx * ddelx_dx;
-                v[4] = dL_dG * dG_ddely * ddely_dy;
-                v[5] = -0.5f * gdx * dx * dL_dG;
-                v[6] = -0.5f * gdx * dy * dL_dG;
-                v[7] = -0.5f * gdy * dy * dL_dG;
-                v[8] = G * dL_dopa;
+        // entry j of this round sits at list position pos(j) = walk-1-(i*BATCH+j); the reference's
+        // `contributor` for it equals pos(j) (backward.cu:499-501: skip if contributor >= last_contributor)
+        const int pos0 = walk - 1 - i * BATCH;
+        // first j this warp needs: pos(j) < warp_last
+        int j0 = pos0 - warp_last + 1;
+        j0 = j0 < 0 ? 0 : j0;
+        for (int g = (j0 & ~31); g < n; g += 32) {
+            const int jj = g + (int)lane;
+            bool keep = false;
+            if (jj >= j0 && jj < n) {
+                const float4 c0 = r[3 * jj];
+                float ex, ey;
+                unpack_cull_extent(__float_as_uint(r[3 * jj + 2].w), ex, ey);
+                const float ddx = fmaxf(fmaxf(rx0 - c0.x, c0.x - rx1), 0.0f);
+                const float ddy = fmaxf(fmaxf(ry0 - c0.y, c0.y - ry1), 0.0f);
+                keep = !(ddx > ex) && !(ddy > ey);
             }
-            const float total = warp_reduce9(v, lane);
-            if (writer) atomicAdd(accum + 12 * (size_t)s_id[buf][j] + slot, total);
+            uint32_t mask = __ballot_sync(0xffffffffu, keep);
+            while (mask) {
+                const int j = g + __ffs(mask) - 1;
+                mask &= mask - 1;
+                const int contributor = pos0 - j;
+                const float4 r0 = r[3 * j], r1 = r[3 * j + 1];
+                const float dx = __fsub_rn(r0.x, pxf), dy = __fsub_rn(r0.y, pyf);
+                const float power = pair_power(dx, dy, r1.x, r1.y, r1.z);
+                const float G = expf(power);
+                const float alpha = fminf(0.99f, __fmul_rn(r1.w, G));
+                const bool valid = (contributor < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+                if (vmask == 0) continue;
+                float v[9];
+#pragma unroll
+                for (int k = 0; k < 9; k++) v[k] = 0.0f;
+                if (valid) {
+                    const float4 r2 = r[3 * j + 2];
+                    T = T / (1.0f - alpha);
+                    const float dchannel_dcolor = alpha * T;
+                    float dL_dopa = 0.0f;
+                    acc0 = last_alpha * lc0 + (1.0f - last_alpha) * acc0; lc0 = r2.x;
+                    dL_dopa += (r2.x - acc0) * dpix0; v[0] = dchannel_dcolor * dpix0;
+                    acc1 = last_alpha * lc1 + (1.0f - last_alpha) * acc1; lc1 = r2.y;
+                    dL_dopa += (r2.y - acc1) * dpix1; v[1] = dchannel_dcolor * dpix1;
+                    acc2 = last_alpha * lc2 + (1.0f - last_alpha) * acc2; lc2 = r2.z;
+                    dL_dopa += (r2.z - acc2) * dpix2; v[2] = dchannel_dcolor * dpix2;
+                    accum_depth_rec = last_alpha * last_depth + (1.0f - last_alpha) * accum_depth_rec;
+                    last_depth = r0.z;
+                    dL_dopa += (r0.z - accum_depth_rec) * dL_ddepth;
+                    accum_alpha_rec = last_alpha + (1.0f - last_alpha) * accum_alpha_rec;
+                    dL_dopa += (1.0f - accum_alpha_rec) * dL_dalpha;
+                    dL_dopa *= T;
+                    last_alpha = alpha;
+                    dL_dopa += (-T_final / (1.0f - alpha)) * bg_dot;
+                    const float dL_dG = r1.w * dL_dopa;
+                    const float gdx = G * dx, gdy = G * dy;
+                    const float dG_ddelx = -gdx * r1.x - gdy * r1.y;
+                    const float dG_ddely = -gdy * r1.z - gdx * r1.y;
+                    v[3] = dL_dG * dG_ddelx * ddelx_dx;
+                    v[4] = dL_dG * dG_ddely * ddely_dy;
+                    v[5] = -0.5f * gdx * dx * dL_dG;
+                    v[6] = -0.5f * gdx * dy * dL_dG;
+                    v[7] = -0.5f * gdy * dy * dL_dG;
+                    v[8] = G * dL_dopa;
+                }
+                float* dst = accum + 12 * (size_t)s_id[buf][j];
+                if (__popc(vmask) <= 2) {
+                    // one or two pixels: cheaper to let them add directly than to reduce
+                    if (valid) {
+#pragma unroll
+                        for (int k = 0; k < 9; k++) atomicAdd(dst + k, v[k]);
+                    }
+                } else {
+                    const float total = warp_reduce9(v, lane);
+                    if (writer) atomicAdd(dst + slot, total);
+                }
+            }
         }
         __syncthreads();
     }
@@ -190,8 +238,11 @@ cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, 
                                   const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
                                   const float* dL_dalpha, float* accum, cudaStream_t s)
 {
-    dim3 grid((p.W + GHR_TILE - 1) / GHR_TILE, (p.H + GHR_TILE - 1) / GHR_TILE);
-    blend_backward_kernel<<<grid, 256, 0, s>>>(
+    StageTimer timer(GHR_STAGE_BLEND_BWD, s);
+    count_launch();
+    constexpr int WARPS = 2;
+    dim3 grid(((p.W + GHR_TILE - 1) / GHR_TILE) * (8 / WARPS), (p.H + GHR_TILE - 1) / GHR_TILE);
+    blend_backward_kernel<WARPS><<<grid, WARPS * 32, 0, s>>>(
         p.W, p.H, reinterpret_cast<const uint2*>(img + L.i_ranges),
         reinterpret_cast<const SortHeader*>(binning + L.b_header),
         reinterpret_cast<const uint32_t*>(binning + L.b_vals_a), reinterpret_cast<const uint32_t*>(binning + L.b_vals_b),

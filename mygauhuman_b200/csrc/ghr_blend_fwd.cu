@@ -1,22 +1,30 @@
 // Per-tile front-to-back alpha blending with depth and alpha-mask outputs
 // (reference forward.cu:261-383 renderCUDA).
 //
-// One CTA per 16x16 tile, one thread per pixel (thread_rank = ty*16+tx as in
-// the reference).  Gaussians are staged in batches of 256 packed 48-byte
-// records {px,py,depth,_ | conic.xyz,opacity | r,g,b,_} with cp.async
-// (LDGSTS) into a double-buffered shared-memory ring, so the inner loop never
-// touches global memory (the reference gathers colour and depth from global
-// per contributing pair, forward.cu:360,362).
+// Work decomposition (ours): a 16x16 tile is covered by 8 warps, each owning an
+// 8x4 pixel block; a CTA holds WARPS of them (2 by default, so a heavy tile is
+// spread over 4 CTAs / SMs instead of serialising on one).  Per CTA, Gaussians
+// are staged in batches of packed 48-byte records
+//   {px,py,depth,radius | conic.xyz,opacity | r,g,b,cull-extent}
+// with cp.async (LDGSTS) into a double-buffered shared-memory ring, so the
+// inner loop never touches global memory (the reference gathers colour and
+// depth from global per contributing pair, forward.cu:360,362).
 //
-// Bound: fp32 issue + MUFU.EX2, not HBM (algorithmic bytes 44*N + 28*X).
-// The arithmetic sequence per pair is the reference's compiled sequence
-// (pair_power, expf, fma accumulation) so final_T/n_contrib are bit-exact.
+// Per warp and batch: (1) each lane tests one Gaussian's conservative bounding
+// box (pack_cull_extent) against the warp's 8x4 block; a ballot yields the
+// survivors.  (2) Survivors are evaluated four at a time: the power/exp/alpha
+// of the four are independent (ILP), only the transmittance recurrence is
+// sequential.  Skipped Gaussians are exactly those the reference's per-pixel
+// tests (power > 0, alpha < 1/255) would skip for every pixel of the block, and
+// the per-pair arithmetic is the reference's compiled sequence (pair_power,
+// expf, fma accumulation), so final_T / n_contrib are bit-exact.
+//
+// Bound: fp32 issue + MUFU.EX2 along the longest per-pixel list, not HBM
+// (algorithmic bytes 44*N + 28*X).
 #include "ghr_common.cuh"
 #include "ghr_internal.h"
 
 namespace ghr {
-
-constexpr int kBatch = 256;
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
 {
@@ -30,76 +38,125 @@ __device__ __forceinline__ void cp_async_wait()
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-__global__ void __launch_bounds__(256) blend_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
-                                                            const SortHeader* __restrict__ sh,
-                                                            const uint32_t* __restrict__ vals_a,
-                                                            const uint32_t* __restrict__ vals_b,
-                                                            const float4* __restrict__ rec,
-                                                            const ghr_geom_header* __restrict__ hdr, int64_t capacity,
-                                                            const float* __restrict__ bg, float* __restrict__ out_color,
-                                                            float* __restrict__ out_depth, float* __restrict__ out_alpha,
-                                                            float* __restrict__ final_T, uint32_t* __restrict__ n_contrib)
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
+    int W, int H, const uint2* __restrict__ ranges, const SortHeader* __restrict__ sh,
+    const uint32_t* __restrict__ vals_a, const uint32_t* __restrict__ vals_b, const float4* __restrict__ rec,
+    const ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
+    float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha,
+    float* __restrict__ final_T, uint32_t* __restrict__ n_contrib)
 {
-    __shared__ __align__(16) float4 s_rec[2][kBatch * 3];
+    constexpr int THREADS = WARPS * 32;
+    constexpr int SUBS = 8 / WARPS;     // CTAs per tile
+    constexpr int BATCH = 128;          // Gaussians staged per round
+    constexpr int PER_THREAD = BATCH / THREADS > 0 ? BATCH / THREADS : 1;
+    static_assert(BATCH % THREADS == 0 || THREADS > BATCH, "batch/threads");
+    __shared__ __align__(16) float4 s_rec[2][BATCH * 3];
 
-    const uint32_t tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
-    const uint32_t pixx = blockIdx.x * GHR_TILE + tx, pixy = blockIdx.y * GHR_TILE + ty;
+    const uint32_t tile_x = blockIdx.x / SUBS, sub = blockIdx.x % SUBS, tile_y = blockIdx.y;
+    const uint32_t wb = sub * WARPS + warp;  // which of the tile's eight 8x4 blocks
+    const uint32_t bx0 = tile_x * GHR_TILE + (wb & 1u) * 8u, by0 = tile_y * GHR_TILE + (wb >> 1) * 4u;
+    const uint32_t pixx = bx0 + (lane & 7u), pixy = by0 + (lane >> 3);
     const bool inside = pixx < (uint32_t)W && pixy < (uint32_t)H;
     const float pxf = (float)pixx, pyf = (float)pixy;
+    const float rx0 = (float)bx0, rx1 = (float)(bx0 + 7u), ry0 = (float)by0, ry1 = (float)(by0 + 3u);
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
-    uint2 range = overflow ? make_uint2(0, 0) : ranges[blockIdx.y * gx + blockIdx.x];
+    const uint2 range = overflow ? make_uint2(0, 0) : ranges[tile_y * gx + tile_x];
     const uint32_t* __restrict__ point_list = sh->sorted_sel ? vals_b : vals_a;
 
     const int todo_total = (int)(range.y - range.x);
-    const int rounds = (todo_total + kBatch - 1) / kBatch;
+    const int rounds = (todo_total + BATCH - 1) / BATCH;
 
     auto stage = [&](int round, int buf) {
-        const uint32_t k = range.x + (uint32_t)round * kBatch + threadIdx.x;
-        if (k < range.y) {
-            const uint32_t id = point_list[k];
-            const float4* src = rec + 3 * (size_t)id;
-            float4* dst = &s_rec[buf][threadIdx.x * 3];
-            cp_async16(dst, src);
-            cp_async16(dst + 1, src + 1);
-            cp_async16(dst + 2, src + 2);
+#pragma unroll
+        for (int u = 0; u < PER_THREAD; u++) {
+            const uint32_t slot = threadIdx.x + u * THREADS;
+            const uint32_t k = range.x + (uint32_t)round * BATCH + slot;
+            if (slot < (uint32_t)BATCH && k < range.y) {
+                const uint32_t id = point_list[k];
+                const float4* src = rec + 3 * (size_t)id;
+                float4* dst = &s_rec[buf][slot * 3];
+                cp_async16(dst, src);
+                cp_async16(dst + 1, src + 1);
+                cp_async16(dst + 2, src + 2);
+            }
         }
         cp_async_commit();
     };
 
     bool done = !inside;
     float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, wsum = 0.f, Dacc = 0.f;
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0;
 
     if (rounds > 0) stage(0, 0);
     int toDo = todo_total;
-    for (int i = 0; i < rounds; i++, toDo -= kBatch) {
+    for (int i = 0; i < rounds; i++, toDo -= BATCH) {
         const int buf = i & 1;
         if (i + 1 < rounds) { stage(i + 1, buf ^ 1); cp_async_wait<1>(); }
         else cp_async_wait<0>();
-        // barrier doubles as the "whole tile done" vote (forward.cu:313-315)
+        // barrier doubles as the "whole CTA done" vote (forward.cu:313-315)
         const int num_done = __syncthreads_count(done);
-        if (num_done == 256) break;
-        const int n = min(kBatch, toDo);
+        if (num_done == THREADS) break;
+        const int n = min(BATCH, toDo);
         const float4* r = s_rec[buf];
-        for (int j = 0; !done && j < n; j++) {
-            contributor++;
-            const float4 r0 = r[3 * j], r1 = r[3 * j + 1];
-            const float dx = __fsub_rn(r0.x, pxf), dy = __fsub_rn(r0.y, pyf);
-            const float power = pair_power(dx, dy, r1.x, r1.y, r1.z);
-            if (power > 0.0f) continue;
-            const float alpha = fminf(0.99f, __fmul_rn(r1.w, expf(power)));
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-            if (test_T < 0.0001f) { done = true; continue; }
-            const float4 r2 = r[3 * j + 2];
-            C0 = __fmaf_rn(T, __fmul_rn(alpha, r2.x), C0);
-            C1 = __fmaf_rn(T, __fmul_rn(alpha, r2.y), C1);
-            C2 = __fmaf_rn(T, __fmul_rn(alpha, r2.z), C2);
-            wsum = __fmaf_rn(T, alpha, wsum);
-            Dacc = __fmaf_rn(T, __fmul_rn(alpha, r0.z), Dacc);
-            T = test_T;
-            last_contributor = contributor;
+        const uint32_t base = (uint32_t)i * BATCH;  // list position of r[0]
+        if (!__all_sync(0xffffffffu, done)) {
+            for (int g = 0; g < n; g += 32) {
+                // (1) conservative bounding-box cull, one Gaussian per lane
+                const int jj = g + (int)lane;
+                bool keep = false;
+                if (jj < n) {
+                    const float4 c0 = r[3 * jj];
+                    float ex, ey;
+                    unpack_cull_extent(__float_as_uint(r[3 * jj + 2].w), ex, ey);
+                    const float ddx = fmaxf(fmaxf(rx0 - c0.x, c0.x - rx1), 0.0f);
+                    const float ddy = fmaxf(fmaxf(ry0 - c0.y, c0.y - ry1), 0.0f);
+                    keep = !(ddx > ex) && !(ddy > ey);
+                }
+                uint32_t mask = __ballot_sync(0xffffffffu, keep);
+                // (2) survivors, four at a time
+                while (mask) {
+                    int j[4];
+                    bool v[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        v[u] = mask != 0;
+                        j[u] = v[u] ? g + __ffs(mask) - 1 : j[0];
+                        mask &= mask - 1;
+                    }
+                    float alpha[4], depth[4], c0[4], c1[4], c2[4];
+                    bool ok[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const float4 r0 = r[3 * j[u]], r1 = r[3 * j[u] + 1], r2 = r[3 * j[u] + 2];
+                        const float dx = __fsub_rn(r0.x, pxf), dy = __fsub_rn(r0.y, pyf);
+                        const float power = pair_power(dx, dy, r1.x, r1.y, r1.z);
+                        alpha[u] = fminf(0.99f, __fmul_rn(r1.w, expf(power)));
+                        ok[u] = v[u] && !(power > 0.0f) && !(alpha[u] < 1.0f / 255.0f);
+                        depth[u] = r0.z; c0[u] = r2.x; c1[u] = r2.y; c2[u] = r2.z;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        if (ok[u] && !done) {
+                            const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha[u]));
+                            if (test_T < 0.0001f) {
+                                done = true;
+                            } else {
+                                C0 = __fmaf_rn(T, __fmul_rn(alpha[u], c0[u]), C0);
+                                C1 = __fmaf_rn(T, __fmul_rn(alpha[u], c1[u]), C1);
+                                C2 = __fmaf_rn(T, __fmul_rn(alpha[u], c2[u]), C2);
+                                wsum = __fmaf_rn(T, alpha[u], wsum);
+                                Dacc = __fmaf_rn(T, __fmul_rn(alpha[u], depth[u]), Dacc);
+                                T = test_T;
+                                last_contributor = base + (uint32_t)j[u] + 1u;
+                            }
+                        }
+                    }
+                    if (__all_sync(0xffffffffu, done)) { mask = 0; g = n; }
+                }
+            }
         }
         __syncthreads();  // buffer `buf` is re-filled two rounds later by stage(i+2)
     }
@@ -121,9 +178,12 @@ cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, c
                                  const ghr_layout& L, float* out_color, float* out_depth, float* out_alpha,
                                  cudaStream_t s)
 {
-    dim3 grid((p.W + GHR_TILE - 1) / GHR_TILE, (p.H + GHR_TILE - 1) / GHR_TILE);
+    StageTimer timer(GHR_STAGE_BLEND_FWD, s);
+    count_launch();
+    constexpr int WARPS = 2;
+    dim3 grid(((p.W + GHR_TILE - 1) / GHR_TILE) * (8 / WARPS), (p.H + GHR_TILE - 1) / GHR_TILE);
     const int64_t capacity = L.capacity;
-    blend_forward_kernel<<<grid, 256, 0, s>>>(
+    blend_forward_kernel<WARPS><<<grid, WARPS * 32, 0, s>>>(
         p.W, p.H, reinterpret_cast<const uint2*>(img + L.i_ranges),
         reinterpret_cast<const SortHeader*>(binning + L.b_header),
         reinterpret_cast<const uint32_t*>(binning + L.b_vals_a), reinterpret_cast<const uint32_t*>(binning + L.b_vals_b),

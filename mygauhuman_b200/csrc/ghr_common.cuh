@@ -9,6 +9,7 @@
 // fusion choices.  oracle/raster_oracle.c spells the same sequence with fmaf.
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include "../../include/ghr.h"
 
@@ -155,6 +156,45 @@ __device__ __forceinline__ float pair_power(float dx, float dy, float ca, float 
 {
     const float s = __fmaf_rn(dx, __fmul_rn(dx, ca), __fmul_rn(dy, __fmul_rn(dy, cc)));
     return __fmaf_rn(s, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, cb)));
+}
+
+
+// ---- conservative screen-space extent of a splat (blend culling) ----------
+// A (pixel, Gaussian) pair contributes only if alpha = min(0.99, o*exp(power))
+// >= 1/255 (forward.cu:343-347), i.e. only inside the ellipse
+// q(d) = a dx^2 + 2b dx dy + c dy^2 <= 2 ln(255 o).  Its axis-aligned bounding
+// box has half-extents sqrt(2t * c/det), sqrt(2t * a/det) with det = ac - b^2.
+// We store both, rounded UP to fp16 with a safety margin that swallows the fp32
+// rounding of power/expf in the blend, packed in one 32-bit word.  A warp skips
+// a Gaussian whose box misses its pixel block; the skip is conservative, so
+// final_T / n_contrib stay bit-exact.  -1 = never contributes, +inf = unknown
+// (NaN / indefinite conic): never skipped.
+__device__ __forceinline__ uint32_t pack_cull_extent(float con_a, float con_b, float con_c, float opacity)
+{
+    const float t = 2.0f * (logf(255.0f * opacity) + 0.05f);
+    float ex, ey;
+    if (t > 0.0f) {
+        const double det = (double)con_a * (double)con_c - (double)con_b * (double)con_b;
+        if (det > 0.0) {
+            ex = (float)sqrt((double)t * (double)con_c / det) * 1.01f + 0.02f;
+            ey = (float)sqrt((double)t * (double)con_a / det) * 1.01f + 0.02f;
+            if (!(ex >= 0.0f)) ex = __int_as_float(0x7f800000);
+            if (!(ey >= 0.0f)) ey = __int_as_float(0x7f800000);
+        } else {
+            ex = ey = __int_as_float(0x7f800000);
+        }
+    } else if (t <= 0.0f) {
+        ex = ey = -1.0f;  // o <= exp(-0.05)/255: alpha < 1/255 everywhere
+    } else {
+        ex = ey = __int_as_float(0x7f800000);  // NaN opacity: fminf(0.99, NaN) = 0.99 contributes
+    }
+    const uint32_t hx = __half_as_ushort(__float2half_ru(ex)), hy = __half_as_ushort(__float2half_ru(ey));
+    return hx | (hy << 16);
+}
+__device__ __forceinline__ void unpack_cull_extent(uint32_t w, float& ex, float& ey)
+{
+    ex = __half2float(__ushort_as_half((unsigned short)(w & 0xFFFFu)));
+    ey = __half2float(__ushort_as_half((unsigned short)(w >> 16)));
 }
 
 // ---- decoupled look-back status words -------------------------------------

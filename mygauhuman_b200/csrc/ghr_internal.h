@@ -2,9 +2,26 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 #include "../../include/ghr.h"
 
 namespace ghr {
+
+// ---- measurement hooks (ghr_profile.cu) ------------------------------------
+extern std::atomic<uint64_t> g_launches;
+inline void count_launch(uint64_t n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+// RAII stage span: records CUDA events on `s` when profiling is enabled.
+class StageTimer {
+public:
+    StageTimer(int stage, cudaStream_t s);
+    ~StageTimer();
+    StageTimer(const StageTimer&) = delete;
+    StageTimer& operator=(const StageTimer&) = delete;
+private:
+    int stage_;
+    cudaStream_t stream_;
+    cudaEvent_t beg_;
+};
 
 constexpr int kMaxPasses = 8;
 constexpr int kRadixBits = 8;

@@ -235,11 +235,14 @@ size_t knn_workspace_bytes(int P)
 cudaError_t launch_knn(int P, const float* points, float* out, char* ws, size_t ws_bytes, cudaStream_t s)
 {
     if (P <= 0) return cudaSuccess;
+    StageTimer timer(GHR_STAGE_KNN, s);
     if (P <= kBruteMax) {
+        count_launch();
         knn_brute_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, points, out);
         return cudaGetLastError();
     }
     (void)ws_bytes;
+    count_launch(6);
     float* aabb = reinterpret_cast<float*>(ws);
     KnnGrid* grid = reinterpret_cast<KnnGrid*>(ws + 64);
     uint32_t* counts = reinterpret_cast<uint32_t*>(ws + 256);

@@ -190,8 +190,9 @@ __global__ void __launch_bounds__(GHR_BLOCK) preprocess_kernel(const PreArgs a)
                     tiles = cnt;
                     float4* r = a.rec + 3 * (size_t)idx;
                     r[0] = make_float4(px, py, pvz, __int_as_float(ri));
-                    r[1] = make_float4(con0, con1, con2, a.opacities[idx]);
-                    r[2] = make_float4(rgb[0], rgb[1], rgb[2], 0.0f);
+                    const float opac = a.opacities[idx];
+                    r[1] = make_float4(con0, con1, con2, opac);
+                    r[2] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(pack_cull_extent(con0, con1, con2, opac)));
                 }
             }
         }
@@ -245,6 +246,7 @@ __global__ void __launch_bounds__(GHR_BLOCK) mark_visible_kernel(int P, const fl
 cudaError_t launch_preprocess(const ghr_raster_params& p, int32_t* radii, char* geom, const ghr_layout& L,
                               int32_t* n_host, cudaStream_t s)
 {
+    StageTimer timer(GHR_STAGE_PREPROCESS, s);
     PreArgs a;
     a.P = p.P; a.D = p.D; a.M = p.M; a.W = p.W; a.H = p.H;
     a.scale_modifier = p.scale_modifier; a.tan_fovx = p.tan_fovx; a.tan_fovy = p.tan_fovy;
@@ -268,11 +270,14 @@ cudaError_t launch_preprocess(const ghr_raster_params& p, int32_t* radii, char* 
     cudaError_t e = cudaMemsetAsync(geom + L.g_header, 0, L.g_rec - L.g_header, s);
     if (e != cudaSuccess) return e;
     preprocess_kernel<<<a.nblocks, GHR_BLOCK, 0, s>>>(a);
+    count_launch();
     return cudaGetLastError();
 }
 
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* V, uint8_t* present, cudaStream_t s)
 {
+    StageTimer timer(GHR_STAGE_MISC, s);
+    count_launch();
     mark_visible_kernel<<<(P + GHR_BLOCK - 1) / GHR_BLOCK, GHR_BLOCK, 0, s>>>(P, means3D, V, present);
     return cudaGetLastError();
 }

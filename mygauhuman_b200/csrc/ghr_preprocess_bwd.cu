@@ -226,6 +226,8 @@ cudaError_t launch_preprocess_backward(const ghr_raster_params& p, const int32_t
                                        float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                                        float* dL_dscale, float* dL_drot, cudaStream_t s)
 {
+    StageTimer timer(GHR_STAGE_PREPROCESS_BWD, s);
+    count_launch();
     PreBwdArgs a;
     a.P = p.P; a.D = p.D; a.M = p.M; a.W = p.W; a.H = p.H;
     a.scale_modifier = p.scale_modifier; a.tan_fovx = p.tan_fovx; a.tan_fovy = p.tan_fovy;

@@ -189,6 +189,7 @@ cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev
                         uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, cudaStream_t s)
 {
     if (capacity <= 0) return cudaSuccess;
+    StageTimer timer(GHR_STAGE_SORT, s);
     const int passes = (bits + kRadixBits - 1) / kRadixBits;
     const int items = sort_items_per_thread(capacity);
     const int64_t tiles = sort_tiles(capacity);
@@ -196,6 +197,7 @@ cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev
     const int hgrid = (int)(hg < 148 * 8 ? hg : 148 * 8);
     sort_histogram_kernel<<<hgrid, 256, 0, s>>>(keys_a, n_dev, capacity, bits, passes, hdr);
     sort_plan_kernel<<<1, 256, 0, s>>>(n_dev, capacity, passes, hdr);
+    count_launch(2 + passes);
     for (int p = 0; p < passes; p++) {
         const int rem = bits - p * kRadixBits;
         const uint32_t mask = rem >= kRadixBits ? 0xFFu : ((1u << rem) - 1u);
