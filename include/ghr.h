@@ -183,6 +183,120 @@ size_t ghr_knn_workspace_bytes(int32_t P);
 int ghr_dist2_knn3(int32_t P, const float* points, float* out, void* workspace, size_t workspace_bytes,
                    void* stream);
 
+/* ======================================================================== *
+ *  LBS deformation of SMPL-initialised Gaussians
+ *  (reference scene/gaussian_model.py:768-872 coarse_deform_c2source,
+ *   :894-980 batch_rodrigues_torch / get_rigid_transformation_torch /
+ *   get_transform_params_torch, :35-42 build_covariance_from_scaling_rotation,
+ *   utils/sh_utils.py:135-190 eval_sh, smplx/lbs.py:156-405)
+ * ======================================================================== */
+#define GHR_LBS_JOINTS 24
+#define GHR_LBS_POSE_DIM 207 /* (24-1)*9 pose-feature entries */
+
+/* Body model in device memory (keys of SMPL_to_tensor, gaussian_model.py:880-892). */
+typedef struct ghr_lbs_model {
+    int32_t V;                    /* vertices (6890)                                    */
+    int32_t NB;                   /* shape coefficients used (10)                       */
+    const float* weights;         /* [V,24]   skinning weights                          */
+    const float* posedirs;        /* [V*3,207]                                          */
+    const float* shapedirs;       /* [V,3,NB]                                           */
+    const float* joint_template;  /* [24,3]    J_regressor . v_template   (ghr_lbs_prepare) */
+    const float* joint_shapedirs; /* [24,3,NB] J_regressor . shapedirs    (ghr_lbs_prepare) */
+    const int32_t* parents;       /* [24] kintree_table[0]; parents[0] ignored           */
+} ghr_lbs_model;
+
+/* Layout (float offsets) of a "pose buffer", the output of ghr_lbs_pose. */
+#define GHR_POSE_A 0        /* [24][12] rows 0-2 of A_j (rigid transform relative to the rest pose) */
+#define GHR_POSE_ROT 288    /* [24][9]  joint rotations (after correct_Rs)               */
+#define GHR_POSE_PF 504     /* [207]    pose feature (rot[1:] - I)                       */
+#define GHR_POSE_JOINTS 720 /* [24][3]  rest joints                                      */
+#define GHR_POSE_RGINV 800  /* [9]      inverse of the global rotation params['R']       */
+#define GHR_POSE_RG 816     /* [9]      params['R']                                      */
+#define GHR_POSE_TH 832     /* [3]      params['Th']                                     */
+#define GHR_POSE_G 848      /* [24][12] world chain G_j (before removing the rest joint) */
+#define GHR_POSE_ROD 1136   /* [24][9]  Rodrigues rotations before correct_Rs            */
+#define GHR_POSE_FLOATS 1536
+
+/* One-time model preparation: because joints = J_regressor (v_template + shapedirs beta)
+ * is linear in beta (gaussian_model.py:951-970), the regressor is folded into the template
+ * and shape directions once.  J_regressor [24,V], v_template [V,3]. */
+int ghr_lbs_prepare(int32_t V, int32_t NB, const float* v_template, const float* shapedirs, const float* J_regressor,
+                    float* joint_template, float* joint_shapedirs, void* stream);
+
+/* get_transform_params_torch (gaussian_model.py:947-980): Rodrigues (:894-912), optional
+ * correct_Rs right-multiplication (:833-836,964-967), rest joints, the 24-joint chain
+ * (:914-944), pose feature (:811,838) and inverse of the global R (:863).
+ * poses [72], shapes [NB], correct_Rs [23,3,3] or NULL, R [3,3], Th [3] (all device). */
+int ghr_lbs_pose(const ghr_lbs_model* model, const float* poses, const float* shapes, const float* correct_Rs,
+                 const float* R, const float* Th, float* pose_out, void* stream);
+
+/* Per-vertex blend-shape displacement applied between the two skinning steps
+ * (gaussian_model.py:805-844): off[v] = shapedirs[v].beta + posedirs[v].(pf_target - pf_big). */
+int ghr_lbs_vertex_offsets(const ghr_lbs_model* model, const float* pose_big, const float* pose_target,
+                           const float* shapes, float* offsets /*[V,3]*/, void* stream);
+
+/* Nearest SMPL vertex (the reference's knn_cuda KNN(k=1), gaussian_model.py:775).
+ * build: bins t_vertices [V,3] into a uniform grid inside `workspace`;
+ * query: exact nearest vertex (lowest index on ties) for P points -> vert_ids [P] int32. */
+size_t ghr_vertex_grid_workspace_bytes(int32_t V);
+int ghr_vertex_grid_build(int32_t V, const float* t_vertices, void* workspace, size_t workspace_bytes, void* stream);
+int ghr_nearest_vertex(int32_t P, const float* query, const void* workspace, int32_t* vert_ids, void* stream);
+
+/* Fused per-Gaussian deformation: skinning-weight blend (optionally
+ * softmax(log(w+1e-9)+offset), :776-781), big pose -> T pose (:785-799), blend-shape
+ * offsets, T pose -> target pose (:847-860), SMPL -> world (:863-870); then, if
+ * requested, the world-space covariance T Sigma T^T (gaussian_model.py:35-42,
+ * general_utils.py:60-117) and the view-dependent colour clamp_min(eval_sh+0.5,0)
+ * (gaussian_renderer/__init__.py:124-125,191-195).  NULL outputs are skipped. */
+typedef struct ghr_deform_params {
+    int32_t P;
+    int32_t V;
+    int32_t sh_degree;           /* active degree 0..3                                  */
+    int32_t M;                   /* SH coefficients per channel in shs (0: no colours)  */
+    float scale_modifier;
+    const float* xyz;            /* [P,3] canonical (big-pose) means                    */
+    const float* normals;        /* [P,3] or NULL                                       */
+    const int32_t* vert_ids;     /* [P]                                                 */
+    const float* weights;        /* [V,24] model skinning weights                       */
+    const float* lbs_offsets;    /* logit offsets, element (p,j) at p*stride_p + j*stride_j, or NULL */
+    int64_t lbs_stride_p, lbs_stride_j;
+    const float* vertex_offsets; /* [V,3] from ghr_lbs_vertex_offsets                   */
+    const float* pose_big;       /* pose buffer of the big pose                         */
+    const float* pose_target;    /* pose buffer of the target pose                      */
+    const float* scales;         /* [P,3] activated scales or NULL (no covariance)      */
+    const float* rotations;      /* [P,4] raw quaternions (normalised inside)           */
+    const float* shs;            /* [P,M,3] or NULL                                     */
+    const float* campos;         /* [3]                                                 */
+} ghr_deform_params;
+
+int ghr_lbs_deform_forward(const ghr_deform_params* prm, float* smpl_pts /*[P,3]|NULL*/, float* world_pts /*[P,3]*/,
+                           float* bweights /*[P,24]|NULL*/, float* transforms /*[P,3,3]*/,
+                           float* translation /*[P,3]|NULL*/, float* world_normals /*[P,3]|NULL*/,
+                           float* cov3D /*[P,6]|NULL*/, float* colors /*[P,3]|NULL*/, uint8_t* clamped /*[P]|NULL*/,
+                           void* stream);
+
+/* Backward of ghr_lbs_deform_forward.  Incoming gradients may be NULL (= zero).
+ * dL_dA_target [24*12] and dL_dvertex_offsets [V*3] are ACCUMULATED (caller zeroes
+ * them) and may be NULL when the pose branch needs no gradient. */
+int ghr_lbs_deform_backward(const ghr_deform_params* prm, const uint8_t* clamped, const float* dL_dworld_pts,
+                            const float* dL_dtransforms, const float* dL_dworld_normals, const float* dL_dcov3D,
+                            const float* dL_dcolors, float* dL_dxyz, float* dL_dnormals,
+                            float* dL_dlbs_offsets /*[P,24]*/, float* dL_dscales, float* dL_drotations,
+                            float* dL_dshs, float* dL_dA_target, float* dL_dvertex_offsets, void* stream);
+
+/* Pose-branch backward: dL/dA_target [24,12] and dL/dvertex_offsets [V,3] (or NULL) -> dL/dcorrect_Rs
+ * [23,3,3] (the only learnable input of the pose branch, nets/mlp_delta_body_pose.py).
+ * dL_dcorrect_Rs must hold 23*9 + 207 floats: the tail is scratch for the pose-feature gradient. */
+int ghr_lbs_pose_backward(const ghr_lbs_model* model, const float* pose_target, const float* correct_Rs,
+                          const float* dL_dA_target, const float* dL_dvertex_offsets, float* dL_dcorrect_Rs,
+                          void* stream);
+
+/* smplx/lbs.py:156-252 lbs() for batch size 1 over the model's own V vertices
+ * (BASELINE.json config 1): v = T (v_template + shapedirs beta + posedirs pf), T = W A. */
+int ghr_smpl_lbs_vertices(const ghr_lbs_model* model, const float* v_template, const float* pose_buf,
+                          const float* vertex_offsets /*[V,3] from ghr_lbs_vertex_offsets(pose_big=NULL)*/,
+                          float* verts /*[V,3]*/, float* T_out /*[V,12]|NULL*/, void* stream);
+
 /*
  * Measurement hooks (no reference counterpart; the reference has no profiling
  * facility beyond wall-clock prints, train.py:209).  Process-wide, off by

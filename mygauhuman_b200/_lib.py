@@ -41,6 +41,24 @@ class Layout(C.Structure):
     ]
 
 
+class LbsModel(C.Structure):
+    """ghr_lbs_model (include/ghr.h)."""
+    _fields_ = [("V", C.c_int32), ("NB", C.c_int32), ("weights", c_f32p), ("posedirs", c_f32p), ("shapedirs", c_f32p),
+                ("joint_template", c_f32p), ("joint_shapedirs", c_f32p), ("parents", C.c_void_p)]
+
+
+class DeformParams(C.Structure):
+    """ghr_deform_params (include/ghr.h)."""
+    _fields_ = [("P", C.c_int32), ("V", C.c_int32), ("sh_degree", C.c_int32), ("M", C.c_int32),
+                ("scale_modifier", C.c_float), ("xyz", c_f32p), ("normals", c_f32p), ("vert_ids", C.c_void_p),
+                ("weights", c_f32p), ("lbs_offsets", c_f32p), ("lbs_stride_p", C.c_int64), ("lbs_stride_j", C.c_int64),
+                ("vertex_offsets", c_f32p), ("pose_big", c_f32p), ("pose_target", c_f32p), ("scales", c_f32p),
+                ("rotations", c_f32p), ("shs", c_f32p), ("campos", c_f32p)]
+
+
+POSE_FLOATS = 1536
+POSE_A, POSE_ROT, POSE_PF, POSE_JOINTS, POSE_RGINV, POSE_RG, POSE_TH, POSE_G, POSE_ROD = 0, 288, 504, 720, 800, 816, 832, 848, 1136
+
 # name -> (restype, argtypes); kept in one table so tests can check every
 # symbol include/ghr.h declares is exported.
 SIGNATURES = {
@@ -59,6 +77,16 @@ SIGNATURES = {
     "ghr_sort_pairs_u64": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_size_t, C.c_void_p, C.c_void_p]),
     "ghr_knn_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "ghr_dist2_knn3": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "ghr_lbs_prepare": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 6),
+    "ghr_lbs_pose": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 7),
+    "ghr_lbs_vertex_offsets": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 5),
+    "ghr_vertex_grid_workspace_bytes": (C.c_size_t, [C.c_int32]),
+    "ghr_vertex_grid_build": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "ghr_nearest_vertex": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ghr_lbs_deform_forward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 10),
+    "ghr_lbs_deform_backward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 15),
+    "ghr_lbs_pose_backward": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
+    "ghr_smpl_lbs_vertices": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
     "ghr_launch_count": (C.c_uint64, []),
     "ghr_profile_enable": (C.c_int, [C.c_int]),
     "ghr_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64)]),

@@ -242,3 +242,134 @@ int ghr_dist2_knn3(int32_t P, const float* points, float* out, void* workspace, 
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// LBS deformation entry points
+// ---------------------------------------------------------------------------
+namespace {
+int validate_model(const ghr_lbs_model* m)
+{
+    if (!m || m->V <= 0 || m->NB < 0 || m->NB > 32 || !m->weights || !m->posedirs || !m->joint_template || !m->parents)
+        return GHR_ERR_BAD_ARG;
+    if (m->NB > 0 && (!m->shapedirs || !m->joint_shapedirs)) return GHR_ERR_BAD_ARG;
+    if (misaligned(m->weights, 16)) return GHR_ERR_BAD_ARG;
+    return GHR_OK;
+}
+int validate_deform(const ghr_deform_params* p)
+{
+    if (!p || p->P < 0 || p->V <= 0 || p->M < 0 || p->M > 16 || p->sh_degree < 0 || p->sh_degree > 3) return GHR_ERR_BAD_ARG;
+    if (p->P == 0) return GHR_OK;
+    if (!p->xyz || !p->vert_ids || !p->weights || !p->vertex_offsets || !p->pose_big || !p->pose_target)
+        return GHR_ERR_BAD_ARG;
+    if (p->shs && (p->M <= 0 || !p->campos || (p->sh_degree + 1) * (p->sh_degree + 1) > p->M)) return GHR_ERR_BAD_ARG;
+    if (p->scales && !p->rotations) return GHR_ERR_BAD_ARG;
+    if (misaligned(p->weights, 16) || misaligned(p->rotations, 16)) return GHR_ERR_BAD_ARG;
+    return GHR_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ghr_lbs_prepare(int32_t V, int32_t NB, const float* v_template, const float* shapedirs, const float* J_regressor,
+                    float* joint_template, float* joint_shapedirs, void* stream)
+{
+    if (V <= 0 || NB < 0 || NB > 32 || !v_template || !J_regressor || !joint_template) return GHR_ERR_BAD_ARG;
+    if (NB > 0 && (!shapedirs || !joint_shapedirs)) return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_lbs_prepare(V, NB, v_template, shapedirs, J_regressor, joint_template, joint_shapedirs,
+                                         (cudaStream_t)stream), "lbs_prepare");
+}
+
+int ghr_lbs_pose(const ghr_lbs_model* model, const float* poses, const float* shapes, const float* correct_Rs,
+                 const float* R, const float* Th, float* pose_out, void* stream)
+{
+    int r = validate_model(model);
+    if (r != GHR_OK) return r;
+    if (!poses || !R || !Th || !pose_out || (model->NB > 0 && !shapes)) return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_lbs_pose(*model, poses, shapes, correct_Rs, R, Th, pose_out, (cudaStream_t)stream), "lbs_pose");
+}
+
+int ghr_lbs_vertex_offsets(const ghr_lbs_model* model, const float* pose_big, const float* pose_target,
+                           const float* shapes, float* offsets, void* stream)
+{
+    int r = validate_model(model);
+    if (r != GHR_OK) return r;
+    if (!pose_target || !offsets) return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_lbs_vertex_offsets(*model, pose_big, pose_target, shapes, offsets, (cudaStream_t)stream),
+                      "lbs_vertex_offsets");
+}
+
+size_t ghr_vertex_grid_workspace_bytes(int32_t V) { return vertex_grid_workspace_bytes(V); }
+
+int ghr_vertex_grid_build(int32_t V, const float* t_vertices, void* workspace, size_t workspace_bytes, void* stream)
+{
+    if (V <= 0 || !t_vertices) return GHR_ERR_BAD_ARG;
+    if (!workspace || workspace_bytes < vertex_grid_workspace_bytes(V) || misaligned(workspace, 256)) return GHR_ERR_BUFFER;
+    return check_cuda(launch_vertex_grid_build(V, t_vertices, (char*)workspace, (cudaStream_t)stream), "vertex_grid_build");
+}
+
+int ghr_nearest_vertex(int32_t P, const float* query, const void* workspace, int32_t* vert_ids, void* stream)
+{
+    if (P < 0) return GHR_ERR_BAD_ARG;
+    if (P == 0) return GHR_OK;
+    if (!query || !workspace || !vert_ids) return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_nearest_vertex(P, query, (const char*)workspace, vert_ids, (cudaStream_t)stream), "nearest_vertex");
+}
+
+int ghr_lbs_deform_forward(const ghr_deform_params* prm, float* smpl_pts, float* world_pts, float* bweights,
+                           float* transforms, float* translation, float* world_normals, float* cov3D, float* colors,
+                           uint8_t* clamped, void* stream)
+{
+    int r = validate_deform(prm);
+    if (r != GHR_OK) return r;
+    if (prm->P == 0) return GHR_OK;
+    if (!world_pts || !transforms) return GHR_ERR_BAD_ARG;
+    if (world_normals && !prm->normals) return GHR_ERR_BAD_ARG;
+    if (cov3D && !prm->scales) return GHR_ERR_BAD_ARG;
+    if (colors && !prm->shs) return GHR_ERR_BAD_ARG;
+    DeformOut o{smpl_pts, world_pts, bweights, transforms, translation, world_normals, cov3D, colors, clamped};
+    return check_cuda(launch_lbs_deform_forward(*prm, o, (cudaStream_t)stream), "lbs_deform_forward");
+}
+
+int ghr_lbs_deform_backward(const ghr_deform_params* prm, const uint8_t* clamped, const float* dL_dworld_pts,
+                            const float* dL_dtransforms, const float* dL_dworld_normals, const float* dL_dcov3D,
+                            const float* dL_dcolors, float* dL_dxyz, float* dL_dnormals, float* dL_dlbs_offsets,
+                            float* dL_dscales, float* dL_drotations, float* dL_dshs, float* dL_dA_target,
+                            float* dL_dvertex_offsets, void* stream)
+{
+    int r = validate_deform(prm);
+    if (r != GHR_OK) return r;
+    if (prm->P == 0) return GHR_OK;
+    if (!dL_dxyz) return GHR_ERR_BAD_ARG;
+    if (dL_dscales && (!prm->scales || !dL_drotations)) return GHR_ERR_BAD_ARG;
+    if (dL_dshs && !prm->shs) return GHR_ERR_BAD_ARG;
+    if (misaligned(dL_drotations, 16)) return GHR_ERR_BAD_ARG;
+    DeformGrads g{clamped, dL_dworld_pts, dL_dtransforms, dL_dworld_normals, dL_dcov3D, dL_dcolors, dL_dxyz, dL_dnormals,
+                  dL_dlbs_offsets, dL_dscales, dL_drotations, dL_dshs, dL_dA_target, dL_dvertex_offsets};
+    return check_cuda(launch_lbs_deform_backward(*prm, g, (cudaStream_t)stream), "lbs_deform_backward");
+}
+
+int ghr_lbs_pose_backward(const ghr_lbs_model* model, const float* pose_target, const float* correct_Rs,
+                          const float* dL_dA_target, const float* dL_dvertex_offsets, float* dL_dcorrect_Rs, void* stream)
+{
+    (void)correct_Rs;
+    int r = validate_model(model);
+    if (r != GHR_OK) return r;
+    if (!pose_target || !dL_dA_target || !dL_dcorrect_Rs) return GHR_ERR_BAD_ARG;
+    // the 207-float pose-feature gradient is staged in the tail of dL_dcorrect_Rs' own buffer: callers pass
+    // a buffer of 23*9 + 207 floats (documented in include/ghr.h)
+    float* scratch = dL_dcorrect_Rs + 23 * 9;
+    return check_cuda(launch_lbs_pose_backward(*model, pose_target, dL_dA_target, dL_dvertex_offsets, dL_dcorrect_Rs,
+                                               scratch, (cudaStream_t)stream), "lbs_pose_backward");
+}
+
+int ghr_smpl_lbs_vertices(const ghr_lbs_model* model, const float* v_template, const float* pose_buf,
+                          const float* offsets, float* verts, float* T_out, void* stream)
+{
+    int r = validate_model(model);
+    if (r != GHR_OK) return r;
+    if (!v_template || !pose_buf || !offsets || !verts) return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_smpl_lbs_vertices(*model, v_template, pose_buf, offsets, verts, T_out, (cudaStream_t)stream),
+                      "smpl_lbs_vertices");
+}
+
+}  // extern "C"

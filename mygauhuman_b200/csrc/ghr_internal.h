@@ -83,6 +83,32 @@ cudaError_t launch_preprocess_backward(const ghr_raster_params& p, const int32_t
                                        float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                                        float* dL_dscale, float* dL_drot, cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* V, uint8_t* present, cudaStream_t s);
+// ---- LBS (ghr_lbs_pose.cu, ghr_lbs_deform.cu, ghr_knn.cu) -------------------
+struct DeformOut {
+    float *smpl_pts, *world_pts, *bweights, *transforms, *translation, *world_normals, *cov3D, *colors;
+    uint8_t* clamped;
+};
+struct DeformGrads {
+    const uint8_t* clamped;
+    const float *g_world, *g_transforms, *g_normals, *g_cov, *g_colors;  // incoming (may be NULL)
+    float *d_xyz, *d_normals, *d_offsets, *d_scales, *d_rot, *d_shs;     // per-Gaussian outputs
+    float *d_A_target, *d_vertex_offsets;                                 // accumulated (may be NULL)
+};
+cudaError_t launch_lbs_prepare(int V, int NB, const float* vt, const float* sd, const float* Jreg, float* jt, float* jsd,
+                               cudaStream_t s);
+cudaError_t launch_lbs_pose(const ghr_lbs_model& m, const float* poses, const float* shapes, const float* correct_Rs,
+                            const float* R, const float* Th, float* out, cudaStream_t s);
+cudaError_t launch_lbs_vertex_offsets(const ghr_lbs_model& m, const float* pose_big, const float* pose_tgt,
+                                      const float* shapes, float* off, cudaStream_t s);
+cudaError_t launch_lbs_pose_backward(const ghr_lbs_model& m, const float* pose_tgt, const float* dA, const float* doff,
+                                     float* dC, float* dpf_scratch, cudaStream_t s);
+cudaError_t launch_smpl_lbs_vertices(const ghr_lbs_model& m, const float* vt, const float* pose, const float* offsets,
+                                     float* verts, float* T_out, cudaStream_t s);
+cudaError_t launch_lbs_deform_forward(const ghr_deform_params& p, const DeformOut& o, cudaStream_t s);
+cudaError_t launch_lbs_deform_backward(const ghr_deform_params& p, const DeformGrads& g, cudaStream_t s);
+size_t vertex_grid_workspace_bytes(int V);
+cudaError_t launch_vertex_grid_build(int V, const float* verts, char* ws, cudaStream_t s);
+cudaError_t launch_nearest_vertex(int P, const float* query, const char* ws, int32_t* vid, cudaStream_t s);
 size_t knn_workspace_bytes(int P);
 cudaError_t launch_knn(int P, const float* points, float* out, char* ws, size_t ws_bytes, cudaStream_t s);
 

@@ -221,6 +221,68 @@ __global__ void __launch_bounds__(128) knn_grid_search_kernel(int P, const KnnGr
     out[self] = __fdiv_rn(__fadd_rn(__fadd_rn(b0, b1), b2), 3.0f);
 }
 
+// ---- nearest model vertex for arbitrary query points (LBS, knn_cuda KNN(k=1)) ----
+// Exact: rings of cells are searched until the best distance is provably final;
+// lowest vertex index wins ties.  Faces of the searched block that lie on or
+// beyond the grid boundary hide no unexamined cell and are ignored, so queries
+// outside the vertex AABB terminate as quickly as interior ones.
+__global__ void __launch_bounds__(128) nearest_vertex_kernel(int P, const float* __restrict__ query, const KnnGrid* gp,
+                                                             const uint32_t* __restrict__ starts,
+                                                             const float4* __restrict__ sorted, int32_t* __restrict__ vid)
+{
+    const KnnGrid g = *gp;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const float qx = query[3 * i], qy = query[3 * i + 1], qz = query[3 * i + 2];
+    const int3 c = cell_of(g, qx, qy, qz);
+    float best = FLT_MAX;
+    int best_id = 0x7FFFFFFF;
+    const int maxr = max(g.nx, max(g.ny, g.nz));
+    const float inf = __int_as_float(0x7f800000);
+    for (int r = 0; r <= maxr; r++) {
+        if (r > 0) {
+            float lo = inf;
+            if (c.x - r + 1 > 0) lo = fminf(lo, qx - (g.minx + (c.x - r + 1) * g.cell));
+            if (c.x + r < g.nx) lo = fminf(lo, (g.minx + (c.x + r) * g.cell) - qx);
+            if (c.y - r + 1 > 0) lo = fminf(lo, qy - (g.miny + (c.y - r + 1) * g.cell));
+            if (c.y + r < g.ny) lo = fminf(lo, (g.miny + (c.y + r) * g.cell) - qy);
+            if (c.z - r + 1 > 0) lo = fminf(lo, qz - (g.minz + (c.z - r + 1) * g.cell));
+            if (c.z + r < g.nz) lo = fminf(lo, (g.minz + (c.z + r) * g.cell) - qz);
+            if (lo == inf) break;  // every cell has been examined
+            const float eps = 4e-7f * (fabsf(qx) + fabsf(qy) + fabsf(qz) + fabsf(g.minx) + fabsf(g.miny) + fabsf(g.minz) +
+                                       g.cell * (float)maxr);
+            const float bound = fmaxf(lo - eps, 0.0f) * 0.999f;
+            if (bound * bound > best) break;
+        }
+        const int z0 = max(c.z - r, 0), z1 = min(c.z + r, g.nz - 1);
+        const int y0 = max(c.y - r, 0), y1 = min(c.y + r, g.ny - 1);
+        const int x0 = max(c.x - r, 0), x1 = min(c.x + r, g.nx - 1);
+        for (int zz = z0; zz <= z1; zz++)
+            for (int yy = y0; yy <= y1; yy++) {
+                const bool shell_row = (abs(zz - c.z) == r) || (abs(yy - c.y) == r);
+                const int row = (zz * g.ny + yy) * g.nx;
+                for (int e = 0; e < 2; e++) {
+                    uint32_t a, b;
+                    if (shell_row) {
+                        if (e) break;
+                        a = starts[row + x0]; b = starts[row + x1 + 1];
+                    } else {
+                        const int xx = e ? c.x + r : c.x - r;
+                        if (xx < 0 || xx >= g.nx || (e && r == 0)) continue;
+                        a = starts[row + xx]; b = starts[row + xx + 1];
+                    }
+                    for (uint32_t k = a; k < b; k++) {
+                        const float4 v = sorted[k];
+                        const float d = dist2(qx, qy, qz, v.x, v.y, v.z);
+                        const int id = __float_as_int(v.w);
+                        if (d < best || (d == best && id < best_id)) { best = d; best_id = id; }
+                    }
+                }
+            }
+    }
+    vid[i] = best_id;
+}
+
 constexpr int kMaxCells = 1 << 22;
 
 size_t knn_workspace_bytes(int P)
@@ -262,6 +324,55 @@ cudaError_t launch_knn(int P, const float* points, float* out, char* ws, size_t 
     if (e != cudaSuccess) return e;
     knn_fill_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, points, grid, starts, counts, sorted);
     knn_grid_search_kernel<<<(P + 127) / 128, 128, 0, s>>>(P, grid, starts, sorted, out);
+    return cudaGetLastError();
+}
+
+
+// grid workspace: aabb(32 B @0) + KnnGrid(@64) | counts[cells] | starts[cells+1] | sorted float4[V]
+static size_t grid_ws_bytes(int n)
+{
+    return 256 + align_up(sizeof(uint32_t) * (size_t)kMaxCells) + align_up(sizeof(uint32_t) * ((size_t)kMaxCells + 1)) +
+           align_up(sizeof(float4) * (size_t)n);
+}
+size_t vertex_grid_workspace_bytes(int V) { return V < 0 ? 0 : grid_ws_bytes(V); }
+
+static cudaError_t build_grid(int P, const float* points, char* ws, cudaStream_t s)
+{
+    float* aabb = reinterpret_cast<float*>(ws);
+    KnnGrid* grid = reinterpret_cast<KnnGrid*>(ws + 64);
+    uint32_t* counts = reinterpret_cast<uint32_t*>(ws + 256);
+    uint32_t* starts = reinterpret_cast<uint32_t*>(ws + 256 + align_up(sizeof(uint32_t) * (size_t)kMaxCells));
+    float4* sorted = reinterpret_cast<float4*>(reinterpret_cast<char*>(starts) + align_up(sizeof(uint32_t) * ((size_t)kMaxCells + 1)));
+    const int init[6] = {0x7F7FFFFF, 0x7F7FFFFF, 0x7F7FFFFF, (int)0x80800000, (int)0x80800000, (int)0x80800000};
+    cudaError_t e = cudaMemcpyAsync(aabb, init, sizeof(init), cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) return e;
+    knn_aabb_kernel<<<148 * 4, 256, 0, s>>>(P, points, aabb);
+    knn_grid_setup_kernel<<<1, 1, 0, s>>>(P, aabb, grid, kMaxCells);
+    e = cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (size_t)kMaxCells, s);
+    if (e != cudaSuccess) return e;
+    knn_count_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, points, grid, counts);
+    knn_scan_kernel<<<1, 1024, 0, s>>>(grid, counts, starts);
+    e = cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (size_t)kMaxCells, s);
+    if (e != cudaSuccess) return e;
+    knn_fill_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, points, grid, starts, counts, sorted);
+    count_launch(5);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_vertex_grid_build(int V, const float* verts, char* ws, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_KNN, s);
+    return build_grid(V, verts, ws, s);
+}
+
+cudaError_t launch_nearest_vertex(int P, const float* query, const char* ws, int32_t* vid, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_KNN, s);
+    const KnnGrid* grid = reinterpret_cast<const KnnGrid*>(ws + 64);
+    const uint32_t* starts = reinterpret_cast<const uint32_t*>(ws + 256 + align_up(sizeof(uint32_t) * (size_t)kMaxCells));
+    const float4* sorted = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(starts) + align_up(sizeof(uint32_t) * ((size_t)kMaxCells + 1)));
+    count_launch();
+    nearest_vertex_kernel<<<(P + 127) / 128, 128, 0, s>>>(P, query, grid, starts, sorted, vid);
     return cudaGetLastError();
 }
 

@@ -1,0 +1,343 @@
+// Pose-level part of the LBS deformation (24 joints, a few hundred floats):
+//   ghr_lbs_prepare         fold J_regressor into template / shape directions
+//   ghr_lbs_pose            Rodrigues + rest joints + kinematic chain + pose feature
+//   ghr_lbs_vertex_offsets  per-vertex blend-shape displacement (GEMV over posedirs)
+//   ghr_lbs_pose_backward   gradient of the chain / pose feature w.r.t. correct_Rs
+//   ghr_smpl_lbs_vertices   smplx lbs() over the model's own vertices
+// Reference: scene/gaussian_model.py:894-980, :805-844; smplx/lbs.py:156-405.
+// The reference runs ~60 ATen micro-kernels for this; here the whole
+// pose stage is ONE single-warp kernel and the 17 MB posedirs GEMV is one
+// HBM-streaming kernel (algorithmic bytes 4*(V*3*207 + V*3*NB)).
+#include "ghr_common.cuh"
+#include "ghr_internal.h"
+
+namespace ghr {
+
+constexpr int kJ = GHR_LBS_JOINTS;
+
+// ---------------------------------------------------------------------------
+// prepare: joint_template[j][c] = sum_v Jreg[j][v] vt[v][c];  joint_shapedirs[j][c][b] likewise
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) lbs_prepare_kernel(int V, int NB, const float* __restrict__ vt,
+                                                          const float* __restrict__ sd, const float* __restrict__ Jreg,
+                                                          float* __restrict__ jt, float* __restrict__ jsd)
+{
+    // one block per (joint, component c, slot b) with b == NB meaning the template
+    const int j = blockIdx.x / (3 * (NB + 1));
+    const int rem = blockIdx.x % (3 * (NB + 1));
+    const int c = rem / (NB + 1), b = rem % (NB + 1);
+    double acc = 0.0;  // one-time, fp64 accumulation: more accurate than the reference's fp32 matmul
+    for (int v = threadIdx.x; v < V; v += 256) {
+        const float w = Jreg[(size_t)j * V + v];
+        if (w != 0.0f) acc += (double)w * (double)(b == NB ? vt[3 * v + c] : sd[((size_t)v * 3 + c) * NB + b]);
+    }
+    __shared__ double s[256];
+    s[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o; o >>= 1) {
+        if (threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        if (b == NB) jt[j * 3 + c] = (float)s[0];
+        else jsd[(j * 3 + c) * NB + b] = (float)s[0];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// pose: one warp
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void mat3_mul(const float* A, const float* B, float* C)
+{
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int c = 0; c < 3; c++) C[3 * r + c] = A[3 * r] * B[c] + A[3 * r + 1] * B[3 + c] + A[3 * r + 2] * B[6 + c];
+}
+
+__device__ __forceinline__ void mat3_inverse(const float* m, float* inv)
+{
+    const float c00 = m[4] * m[8] - m[5] * m[7], c01 = m[5] * m[6] - m[3] * m[8], c02 = m[3] * m[7] - m[4] * m[6];
+    const float det = m[0] * c00 + m[1] * c01 + m[2] * c02;
+    const float id = 1.0f / det;
+    inv[0] = c00 * id; inv[1] = (m[2] * m[7] - m[1] * m[8]) * id; inv[2] = (m[1] * m[5] - m[2] * m[4]) * id;
+    inv[3] = c01 * id; inv[4] = (m[0] * m[8] - m[2] * m[6]) * id; inv[5] = (m[2] * m[3] - m[0] * m[5]) * id;
+    inv[6] = c02 * id; inv[7] = (m[1] * m[6] - m[0] * m[7]) * id; inv[8] = (m[0] * m[4] - m[1] * m[3]) * id;
+}
+
+__global__ void __launch_bounds__(32) lbs_pose_kernel(int NB, const float* __restrict__ jt, const float* __restrict__ jsd,
+                                                      const int32_t* __restrict__ parents, const float* __restrict__ poses,
+                                                      const float* __restrict__ shapes, const float* __restrict__ correct_Rs,
+                                                      const float* __restrict__ Rg, const float* __restrict__ Th,
+                                                      float* __restrict__ out)
+{
+    __shared__ float s_rot[kJ][9];
+    __shared__ float s_joint[kJ][3];
+    __shared__ float s_G[kJ][12];
+    const int j = threadIdx.x;
+    if (j < kJ) {
+        // Rodrigues (gaussian_model.py:894-912): angle = |r + 1e-8|, k = r/angle
+        const float rx = poses[3 * j], ry = poses[3 * j + 1], rz = poses[3 * j + 2];
+        const float ax = rx + 1e-8f, ay = ry + 1e-8f, az = rz + 1e-8f;
+        const float angle = sqrtf(ax * ax + ay * ay + az * az);
+        const float kx = rx / angle, ky = ry / angle, kz = rz / angle;
+        const float s = sinf(angle), c1 = 1.0f - cosf(angle);
+        // K = [0 -kz ky; kz 0 -kx; -ky kx 0];  R = I + s K + c1 K K
+        float R[9];
+        R[0] = 1.0f + c1 * (-kz * kz - ky * ky); R[1] = s * -kz + c1 * (kx * ky); R[2] = s * ky + c1 * (kx * kz);
+        R[3] = s * kz + c1 * (kx * ky); R[4] = 1.0f + c1 * (-kz * kz - kx * kx); R[5] = s * -kx + c1 * (ky * kz);
+        R[6] = s * -ky + c1 * (kx * kz); R[7] = s * kx + c1 * (ky * kz); R[8] = 1.0f + c1 * (-ky * ky - kx * kx);
+#pragma unroll
+        for (int k = 0; k < 9; k++) out[GHR_POSE_ROD + 9 * j + k] = R[k];
+        if (correct_Rs && j > 0) {
+            float C[9], RC[9];
+#pragma unroll
+            for (int k = 0; k < 9; k++) C[k] = correct_Rs[9 * (j - 1) + k];
+            mat3_mul(R, C, RC);
+#pragma unroll
+            for (int k = 0; k < 9; k++) R[k] = RC[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 9; k++) { s_rot[j][k] = R[k]; out[GHR_POSE_ROT + 9 * j + k] = R[k]; }
+        if (j > 0) {
+#pragma unroll
+            for (int k = 0; k < 9; k++) out[GHR_POSE_PF + 9 * (j - 1) + k] = R[k] - ((k == 0 || k == 4 || k == 8) ? 1.0f : 0.0f);
+        }
+        // rest joints: J_regressor (v_template + shapedirs beta), folded (gaussian_model.py:951-970)
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            float v = jt[3 * j + c];
+            for (int b = 0; b < NB; b++) v += jsd[(3 * j + c) * NB + b] * shapes[b];
+            s_joint[j][c] = v;
+            out[GHR_POSE_JOINTS + 3 * j + c] = v;
+        }
+    }
+    if (j < 9) { out[GHR_POSE_RG + j] = Rg[j]; }
+    if (j < 3) { out[GHR_POSE_TH + j] = Th[j]; }
+    __syncwarp();
+    if (j == 0) {
+        float inv[9], R[9];
+#pragma unroll
+        for (int k = 0; k < 9; k++) R[k] = Rg[k];
+        mat3_inverse(R, inv);
+#pragma unroll
+        for (int k = 0; k < 9; k++) out[GHR_POSE_RGINV + k] = inv[k];
+        // kinematic chain (gaussian_model.py:914-944): G_0 = [R_0 | j_0]; G_i = G_parent [R_i | j_i - j_parent]
+        for (int i = 0; i < kJ; i++) {
+            float G[12];
+            if (i == 0) {
+#pragma unroll
+                for (int r = 0; r < 3; r++) {
+                    G[4 * r] = s_rot[0][3 * r]; G[4 * r + 1] = s_rot[0][3 * r + 1]; G[4 * r + 2] = s_rot[0][3 * r + 2];
+                    G[4 * r + 3] = s_joint[0][r];
+                }
+            } else {
+                const int p = parents[i];
+                const float rel[3] = {s_joint[i][0] - s_joint[p][0], s_joint[i][1] - s_joint[p][1],
+                                      s_joint[i][2] - s_joint[p][2]};
+#pragma unroll
+                for (int r = 0; r < 3; r++) {
+                    const float g0 = s_G[p][4 * r], g1 = s_G[p][4 * r + 1], g2 = s_G[p][4 * r + 2], g3 = s_G[p][4 * r + 3];
+#pragma unroll
+                    for (int c = 0; c < 3; c++) G[4 * r + c] = g0 * s_rot[i][c] + g1 * s_rot[i][3 + c] + g2 * s_rot[i][6 + c];
+                    G[4 * r + 3] = g0 * rel[0] + g1 * rel[1] + g2 * rel[2] + g3;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 12; k++) { s_G[i][k] = G[k]; out[GHR_POSE_G + 12 * i + k] = G[k]; }
+            // A_i = G_i with translation - G_i^{3x3} j_i (:939-942)
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                out[GHR_POSE_A + 12 * i + 4 * r] = G[4 * r];
+                out[GHR_POSE_A + 12 * i + 4 * r + 1] = G[4 * r + 1];
+                out[GHR_POSE_A + 12 * i + 4 * r + 2] = G[4 * r + 2];
+                out[GHR_POSE_A + 12 * i + 4 * r + 3] =
+                    G[4 * r + 3] - (G[4 * r] * s_joint[i][0] + G[4 * r + 1] * s_joint[i][1] + G[4 * r + 2] * s_joint[i][2]);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// vertex offsets: one warp per row r of posedirs [V*3, 207]
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) lbs_vertex_offsets_kernel(int rows, int NB, const float* __restrict__ posedirs,
+                                                                 const float* __restrict__ shapedirs,
+                                                                 const float* __restrict__ pose_big,
+                                                                 const float* __restrict__ pose_tgt,
+                                                                 const float* __restrict__ shapes, float* __restrict__ off)
+{
+    __shared__ float s_dpf[GHR_LBS_POSE_DIM];
+    for (int k = threadIdx.x; k < GHR_LBS_POSE_DIM; k += 256)
+        s_dpf[k] = pose_tgt[GHR_POSE_PF + k] - (pose_big ? pose_big[GHR_POSE_PF + k] : 0.0f);
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const float* pr = posedirs + (size_t)row * GHR_LBS_POSE_DIM;
+    float acc = 0.0f;
+    for (int k = lane; k < GHR_LBS_POSE_DIM; k += 32) acc = fmaf(pr[k], s_dpf[k], acc);
+    if (shapes && lane < NB) acc = fmaf(shapedirs[(size_t)row * NB + lane], shapes[lane], acc);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) off[row] = acc;
+}
+
+// dpf[k] = sum_r posedirs[r][k] * doff[r]  (transposed GEMV; 207 outputs)
+__global__ void __launch_bounds__(256) lbs_vertex_offsets_backward_kernel(int rows, const float* __restrict__ posedirs,
+                                                                          const float* __restrict__ doff,
+                                                                          float* __restrict__ dpf /*[207], zeroed*/)
+{
+    // each block handles a slab of rows; thread k < 207 accumulates column k (coalesced across k)
+    const int k = threadIdx.x;
+    const int rows_per_block = (rows + gridDim.x - 1) / gridDim.x;
+    const int r0 = blockIdx.x * rows_per_block, r1 = min(rows, r0 + rows_per_block);
+    if (k >= GHR_LBS_POSE_DIM) return;
+    float acc = 0.0f;
+    for (int r = r0; r < r1; r++) {
+        const float d = doff[r];
+        if (d != 0.0f) acc = fmaf(posedirs[(size_t)r * GHR_LBS_POSE_DIM + k], d, acc);
+    }
+    atomicAdd(&dpf[k], acc);
+}
+
+// ---------------------------------------------------------------------------
+// pose backward: dA[24][12], dpf[207] -> d correct_Rs[23][9]   (one thread; ~2k flops)
+// ---------------------------------------------------------------------------
+__global__ void lbs_pose_backward_kernel(const int32_t* __restrict__ parents, const float* __restrict__ pose,
+                                         const float* __restrict__ dA, const float* __restrict__ dpf,
+                                         float* __restrict__ dC)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    float dG3[kJ][9], dg[kJ][3];
+    for (int i = 0; i < kJ; i++) {
+        const float* j = pose + GHR_POSE_JOINTS + 3 * i;
+        for (int r = 0; r < 3; r++) {
+            const float da = dA[12 * i + 4 * r + 3];
+            dg[i][r] = da;
+            for (int c = 0; c < 3; c++) dG3[i][3 * r + c] = dA[12 * i + 4 * r + c] - da * j[c];
+        }
+    }
+    for (int i = kJ - 1; i >= 0; i--) {
+        float dR[9];
+        if (i == 0) {
+            for (int k = 0; k < 9; k++) dR[k] = dG3[0][k];
+        } else {
+            const int p = parents[i];
+            const float* Gp = pose + GHR_POSE_G + 12 * p;
+            const float* Ri = pose + GHR_POSE_ROT + 9 * i;
+            const float* ji = pose + GHR_POSE_JOINTS + 3 * i;
+            const float* jp = pose + GHR_POSE_JOINTS + 3 * p;
+            const float rel[3] = {ji[0] - jp[0], ji[1] - jp[1], ji[2] - jp[2]};
+            // G_i3 = Gp3 R_i ; g_i = Gp3 rel + g_p
+            for (int r = 0; r < 3; r++)
+                for (int c = 0; c < 3; c++) {
+                    // dGp3[r][c] += sum_k dG3_i[r][k] R_i[c][k] + dg_i[r] rel[c]
+                    dG3[p][3 * r + c] += dG3[i][3 * r] * Ri[3 * c] + dG3[i][3 * r + 1] * Ri[3 * c + 1] +
+                                         dG3[i][3 * r + 2] * Ri[3 * c + 2] + dg[i][r] * rel[c];
+                    // dR_i[r][c] = sum_k Gp3[k][r] dG3_i[k][c]
+                    dR[3 * r + c] = Gp[r] * dG3[i][c] + Gp[4 + r] * dG3[i][3 + c] + Gp[8 + r] * dG3[i][6 + c];
+                }
+            for (int r = 0; r < 3; r++) dg[p][r] += dg[i][r];
+            // pose feature = rot[i] - I for i >= 1
+            if (dpf)
+                for (int k = 0; k < 9; k++) dR[k] += dpf[9 * (i - 1) + k];
+            // rot_i = Rod_i C_i  ->  dC_i = Rod_i^T dR_i
+            const float* Rod = pose + GHR_POSE_ROD + 9 * i;
+            for (int r = 0; r < 3; r++)
+                for (int c = 0; c < 3; c++)
+                    dC[9 * (i - 1) + 3 * r + c] = Rod[r] * dR[c] + Rod[3 + r] * dR[3 + c] + Rod[6 + r] * dR[6 + c];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// smplx lbs() over the template vertices
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) smpl_lbs_vertices_kernel(int V, int NB, const float* __restrict__ vt,
+                                                                const float* __restrict__ weights,
+                                                                const float* __restrict__ offsets,
+                                                                const float* __restrict__ pose, float* __restrict__ verts,
+                                                                float* __restrict__ T_out)
+{
+    __shared__ float s_A[kJ * 12];
+    for (int k = threadIdx.x; k < kJ * 12; k += 128) s_A[k] = pose[GHR_POSE_A + k];
+    __syncthreads();
+    const int v = blockIdx.x * 128 + threadIdx.x;
+    if (v >= V) return;
+    float T[12];
+#pragma unroll
+    for (int k = 0; k < 12; k++) T[k] = 0.0f;
+    for (int j = 0; j < kJ; j++) {
+        const float w = weights[(size_t)v * kJ + j];
+#pragma unroll
+        for (int k = 0; k < 12; k++) T[k] = fmaf(w, s_A[12 * j + k], T[k]);
+    }
+    const float x = vt[3 * v] + offsets[3 * v], y = vt[3 * v + 1] + offsets[3 * v + 1], z = vt[3 * v + 2] + offsets[3 * v + 2];
+#pragma unroll
+    for (int r = 0; r < 3; r++) verts[3 * v + r] = T[4 * r] * x + T[4 * r + 1] * y + T[4 * r + 2] * z + T[4 * r + 3];
+    if (T_out)
+#pragma unroll
+        for (int k = 0; k < 12; k++) T_out[(size_t)v * 12 + k] = T[k];
+}
+
+// ---------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------
+cudaError_t launch_lbs_prepare(int V, int NB, const float* vt, const float* sd, const float* Jreg, float* jt, float* jsd,
+                               cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_LBS_JOINTS, s);
+    count_launch();
+    lbs_prepare_kernel<<<kJ * 3 * (NB + 1), 256, 0, s>>>(V, NB, vt, sd, Jreg, jt, jsd);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lbs_pose(const ghr_lbs_model& m, const float* poses, const float* shapes, const float* correct_Rs,
+                            const float* R, const float* Th, float* out, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_LBS_JOINTS, s);
+    count_launch();
+    lbs_pose_kernel<<<1, 32, 0, s>>>(m.NB, m.joint_template, m.joint_shapedirs, m.parents, poses, shapes, correct_Rs, R,
+                                     Th, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lbs_vertex_offsets(const ghr_lbs_model& m, const float* pose_big, const float* pose_tgt,
+                                      const float* shapes, float* off, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_LBS_JOINTS, s);
+    count_launch();
+    const int rows = m.V * 3;
+    lbs_vertex_offsets_kernel<<<(rows + 7) / 8, 256, 0, s>>>(rows, m.NB, m.posedirs, m.shapedirs, pose_big, pose_tgt,
+                                                             shapes, off);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lbs_pose_backward(const ghr_lbs_model& m, const float* pose_tgt, const float* dA, const float* doff,
+                                     float* dC, float* dpf_scratch, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_LBS_BWD, s);
+    const float* dpf = nullptr;
+    if (doff) {
+        cudaError_t e = cudaMemsetAsync(dpf_scratch, 0, sizeof(float) * GHR_LBS_POSE_DIM, s);
+        if (e != cudaSuccess) return e;
+        count_launch();
+        lbs_vertex_offsets_backward_kernel<<<148, 224, 0, s>>>(m.V * 3, m.posedirs, doff, dpf_scratch);
+        dpf = dpf_scratch;
+    }
+    count_launch();
+    lbs_pose_backward_kernel<<<1, 32, 0, s>>>(m.parents, pose_tgt, dA, dpf, dC);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_smpl_lbs_vertices(const ghr_lbs_model& m, const float* vt, const float* pose, const float* offsets,
+                                     float* verts, float* T_out, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_LBS_FWD, s);
+    count_launch();
+    smpl_lbs_vertices_kernel<<<(m.V + 127) / 128, 128, 0, s>>>(m.V, m.NB, vt, m.weights, offsets, pose, verts, T_out);
+    return cudaGetLastError();
+}
+
+}  // namespace ghr

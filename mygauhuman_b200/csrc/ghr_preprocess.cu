@@ -31,38 +31,6 @@ struct PreArgs {
     int nblocks;
 };
 
-// forward.cu:20-71 computeColorFromSH (fp32; tolerance-checked, not bit-pinned)
-__device__ __forceinline__ void sh_to_rgb(int deg, const float* __restrict__ sh, float dx, float dy, float dz,
-                                          float* rgb, uint32_t& clamp_mask)
-{
-    const float len = sqrtf(dx * dx + dy * dy + dz * dz);
-    const float x = dx / len, y = dy / len, z = dz / len;
-    clamp_mask = 0;
-#pragma unroll
-    for (int c = 0; c < 3; c++) {
-        float res = GHR_SH_C0 * sh[c];
-        if (deg > 0) {
-            res = res - GHR_SH_C1 * y * sh[3 + c] + GHR_SH_C1 * z * sh[6 + c] - GHR_SH_C1 * x * sh[9 + c];
-            if (deg > 1) {
-                const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-                res = res + kSH_C2[0] * xy * sh[12 + c] + kSH_C2[1] * yz * sh[15 + c] +
-                      kSH_C2[2] * (2.0f * zz - xx - yy) * sh[18 + c] + kSH_C2[3] * xz * sh[21 + c] +
-                      kSH_C2[4] * (xx - yy) * sh[24 + c];
-                if (deg > 2) {
-                    res = res + kSH_C3[0] * y * (3.0f * xx - yy) * sh[27 + c] + kSH_C3[1] * xy * z * sh[30 + c] +
-                          kSH_C3[2] * y * (4.0f * zz - xx - yy) * sh[33 + c] +
-                          kSH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * sh[36 + c] +
-                          kSH_C3[4] * x * (4.0f * zz - xx - yy) * sh[39 + c] + kSH_C3[5] * z * (xx - yy) * sh[42 + c] +
-                          kSH_C3[6] * x * (xx - 3.0f * yy) * sh[45 + c];
-                }
-            }
-        }
-        res += 0.5f;
-        if (res < 0.0f) clamp_mask |= 1u << c;
-        rgb[c] = fmaxf(res, 0.0f);
-    }
-}
-
 constexpr uint64_t kFlagAgg = 1ull << 32;
 constexpr uint64_t kFlagIncl = 2ull << 32;
 

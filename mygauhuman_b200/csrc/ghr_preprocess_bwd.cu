@@ -21,75 +21,6 @@ struct PreBwdArgs {
     float *dL_dmean2D, *dL_dcolor, *dL_dopacity, *dL_dmean3D, *dL_dcov3D, *dL_dsh, *dL_dscale, *dL_drot;
 };
 
-// backward.cu:20-139
-__device__ __forceinline__ void sh_backward(int deg, int M, const float* __restrict__ sh, float dox, float doy,
-                                            float doz, uint32_t clamp_mask, const float* dL_dcolor, float* dm,
-                                            float* __restrict__ dL_dsh)
-{
-    const float len = sqrtf(dox * dox + doy * doy + doz * doz);
-    const float x = dox / len, y = doy / len, z = doz / len;
-    float dRGB[3];
-#pragma unroll
-    for (int c = 0; c < 3; c++) dRGB[c] = (clamp_mask >> c) & 1u ? 0.0f : dL_dcolor[c];
-    float ddx = 0.f, ddy = 0.f, ddz = 0.f;
-    float coef[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) coef[k] = 0.0f;
-    coef[0] = GHR_SH_C0;
-    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-    if (deg > 0) {
-        coef[1] = -GHR_SH_C1 * y; coef[2] = GHR_SH_C1 * z; coef[3] = -GHR_SH_C1 * x;
-        if (deg > 1) {
-            coef[4] = kSH_C2[0] * xy; coef[5] = kSH_C2[1] * yz; coef[6] = kSH_C2[2] * (2.f * zz - xx - yy);
-            coef[7] = kSH_C2[3] * xz; coef[8] = kSH_C2[4] * (xx - yy);
-            if (deg > 2) {
-                coef[9] = kSH_C3[0] * y * (3.f * xx - yy); coef[10] = kSH_C3[1] * xy * z;
-                coef[11] = kSH_C3[2] * y * (4.f * zz - xx - yy);
-                coef[12] = kSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy);
-                coef[13] = kSH_C3[4] * x * (4.f * zz - xx - yy); coef[14] = kSH_C3[5] * z * (xx - yy);
-                coef[15] = kSH_C3[6] * x * (xx - 3.f * yy);
-            }
-        }
-    }
-    const int ncoef = (deg + 1) * (deg + 1);
-    for (int k = 0; k < M; k++) {
-        const float cf = k < ncoef && k < 16 ? coef[k] : 0.0f;
-        dL_dsh[3 * k] = cf * dRGB[0]; dL_dsh[3 * k + 1] = cf * dRGB[1]; dL_dsh[3 * k + 2] = cf * dRGB[2];
-    }
-#pragma unroll
-    for (int c = 0; c < 3; c++) {
-        float gx = 0.f, gy = 0.f, gz = 0.f;
-#define SHV(i) sh[(i) * 3 + c]
-        if (deg > 0) {
-            gx = -GHR_SH_C1 * SHV(3); gy = -GHR_SH_C1 * SHV(1); gz = GHR_SH_C1 * SHV(2);
-            if (deg > 1) {
-                gx += kSH_C2[0] * y * SHV(4) + kSH_C2[2] * 2.f * -x * SHV(6) + kSH_C2[3] * z * SHV(7) + kSH_C2[4] * 2.f * x * SHV(8);
-                gy += kSH_C2[0] * x * SHV(4) + kSH_C2[1] * z * SHV(5) + kSH_C2[2] * 2.f * -y * SHV(6) + kSH_C2[4] * 2.f * -y * SHV(8);
-                gz += kSH_C2[1] * y * SHV(5) + kSH_C2[2] * 2.f * 2.f * z * SHV(6) + kSH_C2[3] * x * SHV(7);
-                if (deg > 2) {
-                    gx += (kSH_C3[0] * SHV(9) * 3.f * 2.f * xy + kSH_C3[1] * SHV(10) * yz + kSH_C3[2] * SHV(11) * -2.f * xy +
-                           kSH_C3[3] * SHV(12) * -3.f * 2.f * xz + kSH_C3[4] * SHV(13) * (-3.f * xx + 4.f * zz - yy) +
-                           kSH_C3[5] * SHV(14) * 2.f * xz + kSH_C3[6] * SHV(15) * 3.f * (xx - yy));
-                    gy += (kSH_C3[0] * SHV(9) * 3.f * (xx - yy) + kSH_C3[1] * SHV(10) * xz +
-                           kSH_C3[2] * SHV(11) * (-3.f * yy + 4.f * zz - xx) + kSH_C3[3] * SHV(12) * -3.f * 2.f * yz +
-                           kSH_C3[4] * SHV(13) * -2.f * xy + kSH_C3[5] * SHV(14) * -2.f * yz + kSH_C3[6] * SHV(15) * -3.f * 2.f * xy);
-                    gz += (kSH_C3[1] * SHV(10) * xy + kSH_C3[2] * SHV(11) * 4.f * 2.f * yz +
-                           kSH_C3[3] * SHV(12) * 3.f * (2.f * zz - xx - yy) + kSH_C3[4] * SHV(13) * 4.f * 2.f * xz +
-                           kSH_C3[5] * SHV(14) * (xx - yy));
-                }
-            }
-        }
-#undef SHV
-        ddx += gx * dRGB[c]; ddy += gy * dRGB[c]; ddz += gz * dRGB[c];
-    }
-    // auxiliary.h:108-119 dnormvdv
-    const float sum2 = dox * dox + doy * doy + doz * doz;
-    const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
-    dm[0] += ((+sum2 - dox * dox) * ddx - doy * dox * ddy - doz * dox * ddz) * invsum32;
-    dm[1] += (-dox * doy * ddx + (sum2 - doy * doy) * ddy - doz * doy * ddz) * invsum32;
-    dm[2] += (-dox * doz * ddx - doy * doz * ddy + (sum2 - doz * doz) * ddz) * invsum32;
-}
-
 // backward.cu:278-341
 __device__ __forceinline__ void cov3d_backward(float s0, float s1, float s2, float mod, float r, float x, float y,
                                                float z, const float* d, float* dL_dscale, float* dL_drot)
