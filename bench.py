@@ -35,7 +35,7 @@ if ROOT not in sys.path:
 import numpy as np
 import torch
 
-METRIC = "raster_fwd_bwd_iters_per_s"
+METRIC = "lbs_raster_fwd_bwd_iters_per_s"
 UNIT = "iters/s"
 
 WORKLOADS = {
@@ -55,7 +55,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-cpu"])
     ap.add_argument("--workload", default="zju_512", choices=list(WORKLOADS))
     ap.add_argument("--views", type=int, default=64, help="distinct cameras cycled through (sharded across ranks)")
-    ap.add_argument("--cpu-iters", type=int, default=60, help="CPU-oracle iterations for cpu_baseline")
+    ap.add_argument("--cpu-iters", type=int, default=20, help="CPU-oracle iterations for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sync-free", action="store_true",
                     help="ours: size the binning buffer from the previous step instead of a blocking read")
@@ -145,37 +145,57 @@ class ClockSampler:
 # workload
 # ---------------------------------------------------------------------------
 
+PACK = dict(view=(0, 16), proj=(16, 32), campos=(32, 35), poses=(35, 107), shapes=(107, 117), R=(117, 126), Th=(126, 129))
+PACK_FLOATS = 129
+
+
 def build_workload(args, rank, world):
-    """Seeded synthetic inputs (mygauhuman_b200/synthetic.py).  Host tensors."""
+    """Seeded synthetic inputs (mygauhuman_b200/synthetic.py).  Host tensors.
+    Canonical Gaussians sit on the big-pose SMPL-topology surface; every view has its own camera AND its own
+    body pose (as a ZJU-MoCap frame does)."""
     from mygauhuman_b200 import synthetic as S
     wl = WORKLOADS[args.workload]
     P, W, H = wl["P"], wl["W"], wl["H"]
-    if args.workload == "stress_1080p":
-        g = S.make_scene_cloud(P, seed=0)
-        cams = [S.make_camera(W, H, angle=0.0, radius=0.0, target=(0, 0, 1.0), elev=0.0, seed=i) for i in range(1)]
-    else:
-        base = S.make_smpl_model(0)["v_template"].numpy()
-        g = S.make_gaussians(P, base, seed=0, sh_degree=3)
-        n_views = max(args.views, world)
-        cams = [S.make_camera(W, H, angle=2 * np.pi * i / n_views, radius=3.0, seed=i) for i in range(n_views)]
-        cams = cams[rank::world]  # view sharding: rank r renders views r, r+world, ...
-    params = {
-        "means3D": g["xyz"].contiguous(),
-        "shs": g["features"].contiguous(),
-        "opacity": torch.sigmoid(g["opacity_logit"]).contiguous(),
-        "scales": torch.exp(g["log_scale"]).contiguous(),
-        "rotations": g["rotation"].contiguous(),
-    }
+    smpl = S.make_smpl_model(0)
+    big = S.big_pose_params()
+    t_vertices = S.big_pose_vertices(smpl, big)
+    g = S.make_gaussians(P, t_vertices.numpy(), seed=0, sh_degree=3)
+    n_views = max(args.views, world)
+    views = []
+    for i in range(n_views):
+        cam = S.make_camera(W, H, angle=2 * np.pi * i / n_views, radius=3.0, seed=i)
+        pose = S.make_pose_params(i)
+        pose["Th"] = pose["Th"] * 0.2  # keep the body inside the frustum of the ring cameras
+        views.append(dict(cam=cam, pose=pose))
+    views = views[rank::world]  # view sharding: rank r renders views r, r+world, ...
+    leaves = {"xyz": g["xyz"], "log_scale": g["log_scale"], "rotation": g["rotation"], "features": g["features"],
+              "opacity_logit": g["opacity_logit"], "normals": g["normals"]}
     gen = torch.Generator().manual_seed(1234 + rank)
-    targets = torch.randn(5, H, W, generator=gen)  # dL/dcolor (3), dL/ddepth, dL/dalpha seeds == linear loss weights
-    return dict(P=P, W=W, H=H, params=params, cams=cams, targets=targets, bg=torch.zeros(3))
+    targets = torch.randn(5, H, W, generator=gen)  # linear loss weights on colour (3), depth, alpha
+    return dict(P=P, W=W, H=H, smpl=smpl, big=big, t_vertices=t_vertices, leaves=leaves, views=views, targets=targets,
+                bg=torch.zeros(3))
 
 
-def cam_pack(cam):
-    """[view 16 | proj 16 | campos 3] as one pinned host vector."""
+def view_pack(view):
+    """[view 16 | proj 16 | campos 3 | poses 72 | shapes 10 | R 9 | Th 3] as one pinned host vector: the
+    per-step input besides the target planes."""
+    cam, pose = view["cam"], view["pose"]
     v = torch.cat([cam["world_view_transform"].reshape(-1), cam["full_proj_transform"].reshape(-1),
-                   cam["camera_center"].reshape(-1)]).float()
+                   cam["camera_center"].reshape(-1), pose["poses"].reshape(-1), pose["shapes"].reshape(-1),
+                   pose["R"].reshape(-1), pose["Th"].reshape(-1)]).float()
+    assert v.numel() == PACK_FLOATS
     return v.pin_memory() if torch.cuda.is_available() else v
+
+
+def unpack(vec):
+    g = lambda k: vec[PACK[k][0]:PACK[k][1]]
+    cam = dict(view=g("view").view(4, 4), proj=g("proj").view(4, 4), campos=g("campos"))
+    pose = dict(poses=g("poses").view(1, 72), shapes=g("shapes").view(1, 10), R=g("R").view(3, 3), Th=g("Th").view(1, 3))
+    return cam, pose
+
+
+def linear_loss(color, depth, alpha, targets):
+    return (color * targets[0:3]).sum() + (depth * targets[3:4]).sum() + (alpha * targets[4:5]).sum()
 
 
 # ---------------------------------------------------------------------------
@@ -183,125 +203,169 @@ def cam_pack(cam):
 # ---------------------------------------------------------------------------
 
 class OursArm:
-    """The product: mygauhuman_b200.diff_gaussian_rasterization (libghr.so through the C ABI)."""
+    """The product: fused LBS+covariance+SH (mygauhuman_b200.lbs) -> rasteriser
+    (mygauhuman_b200.diff_gaussian_rasterization), all on libghr.so through the C ABI."""
     name = "ours"
 
     def __init__(self, wl, dev, sync_free):
         from mygauhuman_b200 import _lib
         from mygauhuman_b200 import diff_gaussian_rasterization as dgr
+        from mygauhuman_b200.lbs import SMPLDeformer
         self._lib, self.dgr, self.wl, self.dev = _lib, dgr, wl, dev
         _lib.lib()  # fail loudly if the CUDA library is missing
-        self.leaves = {k: v.to(dev).requires_grad_(True) for k, v in wl["params"].items()}
+        self.deformer = SMPLDeformer(wl["smpl"], dev)
+        self.leaves = {k: v.to(dev).requires_grad_(True) for k, v in wl["leaves"].items()}
+        self.big = {k: v.to(dev) for k, v in wl["big"].items()}
+        self.t_vertices = wl["t_vertices"].to(dev)
         self.bg = wl["bg"].to(dev)
         self.sync_free = sync_free
         self.last_n = None
 
-    def step(self, cam, camvec_dev, targets_dev):
+    def step(self, view, vec_dev, targets_dev):
         dgr, L = self.dgr, self.leaves
+        camd, pose = unpack(vec_dev)
+        cam = view["cam"]
+        d = self.deformer.deform_gaussians(L["xyz"], pose, self.big, self.t_vertices, normals=L["normals"],
+                                           scaling=torch.exp(L["log_scale"]), rotation=L["rotation"],
+                                           scaling_modifier=1.0, features=L["features"], sh_degree=3,
+                                           campos=camd["campos"])
         if self.sync_free:
             dgr._C.set_sync_free_capacity(None if self.last_n is None else int(self.last_n * 1.3) + 4096)
         rs = dgr.GaussianRasterizationSettings(
             image_height=self.wl["H"], image_width=self.wl["W"], tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
-            bg=self.bg, scale_modifier=1.0, viewmatrix=camvec_dev[0:16].view(4, 4),
-            projmatrix=camvec_dev[16:32].view(4, 4), sh_degree=3, campos=camvec_dev[32:35], prefiltered=False,
-            debug=False)
-        rast = dgr.GaussianRasterizer(rs)
-        means2D = torch.zeros_like(L["means3D"], requires_grad=True)
-        color, radii, depth, alpha = rast(means3D=L["means3D"], means2D=means2D, opacities=L["opacity"],
-                                          shs=L["shs"], scales=L["scales"], rotations=L["rotations"])
-        loss = (color * targets_dev[0:3]).sum() + (depth * targets_dev[3:4]).sum() + (alpha * targets_dev[4:5]).sum()
+            bg=self.bg, scale_modifier=1.0, viewmatrix=camd["view"], projmatrix=camd["proj"], sh_degree=3,
+            campos=camd["campos"], prefiltered=False, debug=False)
+        means2D = torch.zeros_like(d["means3D"], requires_grad=True)
+        color, radii, depth, alpha = dgr.GaussianRasterizer(rs)(
+            means3D=d["means3D"], means2D=means2D, opacities=torch.sigmoid(L["opacity_logit"]),
+            colors_precomp=d["colors"], cov3D_precomp=d["cov3D"])
+        loss = linear_loss(color, depth, alpha, targets_dev)
         for t in L.values():
             t.grad = None
         loss.backward()
-        self.radii = radii
-        return loss, [L[k].grad for k in ("means3D", "shs", "opacity", "scales", "rotations")]
+        return loss, [L[k].grad for k in ("xyz", "features", "opacity_logit", "log_scale", "rotation")]
 
-    def num_rendered(self, cam, camvec_dev):
-        L = self.leaves
-        e = torch.Tensor([])
+    def measure_NV(self, view, vec_dev):
+        """(num_rendered, visible Gaussians) of one view, for the algorithmic-byte formulas."""
+        camd, pose = unpack(vec_dev)
+        cam, L, e = view["cam"], self.leaves, torch.Tensor([])
         with torch.no_grad():
-            out = self.dgr._C.rasterize_gaussians(self.bg, L["means3D"], e, L["opacity"], L["scales"], L["rotations"],
-                                                  1.0, e, camvec_dev[0:16].view(4, 4), camvec_dev[16:32].view(4, 4),
-                                                  cam["tanfovx"], cam["tanfovy"], self.wl["H"], self.wl["W"], L["shs"],
-                                                  3, camvec_dev[32:35], False, False)
+            d = self.deformer.deform_gaussians(L["xyz"], pose, self.big, self.t_vertices,
+                                               scaling=torch.exp(L["log_scale"]), rotation=L["rotation"],
+                                               features=L["features"], sh_degree=3, campos=camd["campos"])
+            out = self.dgr._C.rasterize_gaussians(self.bg, d["means3D"], d["colors"], torch.sigmoid(L["opacity_logit"]),
+                                                  e, e, 1.0, d["cov3D"], camd["view"], camd["proj"], cam["tanfovx"],
+                                                  cam["tanfovy"], self.wl["H"], self.wl["W"], e, 3, camd["campos"],
+                                                  False, False)
         return int(out[0]), int((out[4] > 0).sum())
 
 
 class _RefRasterize(torch.autograd.Function):
-    """Same protocol as the reference's _RasterizeGaussians (dgr __init__.py:44-158) around the
-    reference's own native forward/backward (through oracle/ref_shim.cu instead of its torch binding)."""
+    """Same protocol as the reference's _RasterizeGaussians (dgr __init__.py:44-158) around the reference's own
+    native forward/backward (through oracle/ref_shim.cu instead of its torch binding); precomputed colour +
+    covariance inputs, which is how the reference's render() calls it."""
 
     @staticmethod
-    def forward(ctx, ref, means3D, means2D, sh, opacities, scales, rotations, bg, view, proj, campos, tfx, tfy, H, W):
-        n, color, depth, alpha, radii = ref.forward(bg, means3D, None, opacities, scales, rotations, 1.0, None, view,
-                                                    proj, tfx, tfy, H, W, sh, 3, campos)
+    def forward(ctx, ref, means3D, means2D, colors, opacities, cov3D, bg, view, proj, campos, tfx, tfy, H, W):
+        n, color, depth, alpha, radii = ref.forward(bg, means3D, colors, opacities, None, None, 1.0, cov3D, view, proj,
+                                                    tfx, tfy, H, W, None, 3, campos)
         ctx.ref, ctx.cfg = ref, (bg, view, proj, campos, tfx, tfy)
-        ctx.save_for_backward(means3D, sh, scales, rotations, radii, alpha)
+        ctx.save_for_backward(means3D, colors, cov3D, radii, alpha)
         ctx.mark_non_differentiable(radii)
         return color, radii, depth, alpha
 
     @staticmethod
     def backward(ctx, gc, gr, gd, ga):
-        means3D, sh, scales, rotations, radii, alpha = ctx.saved_tensors
+        means3D, colors, cov3D, radii, alpha = ctx.saved_tensors
         bg, view, proj, campos, tfx, tfy = ctx.cfg
-        g = ctx.ref.backward(bg, means3D, radii, None, scales, rotations, 1.0, None, view, proj, tfx, tfy, gc, gd, ga,
-                             sh, 3, campos, alpha)
-        return (None, g["dL_dmeans3D"], g["dL_dmeans2D"], g["dL_dsh"], g["dL_dopacity"], g["dL_dscales"],
-                g["dL_drotations"]) + (None,) * 8
+        g = ctx.ref.backward(bg, means3D, radii, colors, None, None, 1.0, cov3D, view, proj, tfx, tfy, gc, gd, ga, None,
+                             3, campos, alpha)
+        return (None, g["dL_dmeans3D"], g["dL_dmeans2D"], g["dL_dcolors"], g["dL_dopacity"], g["dL_dcov3D"]) + (None,) * 8
 
 
 class ReferenceArm:
-    """The UNMODIFIED reference CUDA rasteriser built for sm_100 (oracle/_ref), same GPU."""
+    """The reference's path on the same GPU: its PyTorch LBS / covariance / eval_sh (the restatement in
+    oracle/lbs_oracle.py run on CUDA tensors -- the reference module itself cannot travel to the GPU box; knn_cuda
+    is replaced by torch.cdist + argmin as SURVEY 8c plans) followed by the UNMODIFIED reference CUDA rasteriser
+    built for sm_100 (oracle/_ref).  None of libghr's kernels are on this path."""
     name = "reference"
 
     def __init__(self, wl, dev):
-        from oracle import ref_cuda
+        from oracle import lbs_oracle, ref_cuda
         if not ref_cuda.available():
             raise FileNotFoundError(ref_cuda.LIB_PATH)
+        self.LO = lbs_oracle
         self.ref = ref_cuda.RefRasterizer()
         self.wl, self.dev = wl, dev
-        self.leaves = {k: v.to(dev).requires_grad_(True) for k, v in wl["params"].items()}
+        self.smpl = {k: v.to(dev) for k, v in wl["smpl"].items()}
+        self.leaves = {k: v.to(dev).requires_grad_(True) for k, v in wl["leaves"].items()}
+        self.big = {k: v.to(dev) for k, v in wl["big"].items()}
+        self.t_vertices = wl["t_vertices"].to(dev)
         self.bg = wl["bg"].to(dev)
 
-    def step(self, cam, camvec_dev, targets_dev):
-        L = self.leaves
-        means2D = torch.zeros_like(L["means3D"], requires_grad=True)
+    def step(self, view, vec_dev, targets_dev):
+        L, LO = self.leaves, self.LO
+        camd, pose = unpack(vec_dev)
+        cam = view["cam"]
+        with torch.no_grad():
+            vid = torch.cdist(L["xyz"], self.t_vertices).argmin(1)  # stand-in for knn_cuda KNN(k=1)
+        _, world, _, T, _, wn, _ = LO.coarse_deform_c2source(self.smpl, L["xyz"], pose, self.big, self.t_vertices,
+                                                             normals=L["normals"] / L["normals"].norm(dim=1, keepdim=True),
+                                                             vert_ids=vid)
+        cov = LO.covariance(torch.exp(L["log_scale"]), 1.0, L["rotation"], T)
+        col = LO.view_colors(3, L["features"], world, camd["campos"])
+        means2D = torch.zeros_like(world, requires_grad=True)
         color, radii, depth, alpha = _RefRasterize.apply(
-            self.ref, L["means3D"], means2D, L["shs"], L["opacity"], L["scales"], L["rotations"], self.bg,
-            camvec_dev[0:16].view(4, 4).contiguous(), camvec_dev[16:32].view(4, 4).contiguous(),
-            camvec_dev[32:35].contiguous(), cam["tanfovx"], cam["tanfovy"], self.wl["H"], self.wl["W"])
-        loss = (color * targets_dev[0:3]).sum() + (depth * targets_dev[3:4]).sum() + (alpha * targets_dev[4:5]).sum()
+            self.ref, world, means2D, col, torch.sigmoid(L["opacity_logit"]), cov, self.bg, camd["view"].contiguous(),
+            camd["proj"].contiguous(), camd["campos"].contiguous(), cam["tanfovx"], cam["tanfovy"], self.wl["H"],
+            self.wl["W"])
+        loss = linear_loss(color, depth, alpha, targets_dev)
         for t in L.values():
             t.grad = None
         loss.backward()
-        return loss, [L[k].grad for k in ("means3D", "shs", "opacity", "scales", "rotations")]
+        return loss, [L[k].grad for k in ("xyz", "features", "opacity_logit", "log_scale", "rotation")]
 
 
 # ---------------------------------------------------------------------------
 # CPU baseline (the oracle port on the host cores) -- reported, not the target
 # ---------------------------------------------------------------------------
 
-def cpu_baseline(wl, cam, iters):
-    """fwd+bwd of the same workload by oracle/raster_oracle.c (OpenMP) on the host cores."""
+def cpu_baseline(wl, view, iters):
+    """One full step (LBS + covariance + SH -> raster fwd -> raster bwd -> LBS bwd) on the host cores:
+    the reference's PyTorch LBS math (oracle/lbs_oracle.py, torch CPU, autograd for its backward) and the C
+    restatement of the rasteriser (oracle/raster_oracle.c, OpenMP)."""
     import oracle as O
-    p = wl["params"]
+    from oracle import lbs_oracle as LO
+    cam, pose = view["cam"], view["pose"]
     a = lambda t: np.ascontiguousarray(t.detach().cpu().numpy(), dtype=np.float32)
-    view, proj, campos = a(cam["world_view_transform"]), a(cam["full_proj_transform"]), a(cam["camera_center"])
+    vm, pm, campos = a(cam["world_view_transform"]), a(cam["full_proj_transform"]), a(cam["camera_center"])
     tg = a(wl["targets"])
-    args_f = (a(wl["bg"]), a(p["means3D"]), None, a(p["opacity"]), a(p["scales"]), a(p["rotations"]), 1.0, None, view,
-              proj, cam["tanfovx"], cam["tanfovy"], wl["H"], wl["W"], a(p["shs"]), 3, campos)
+    bg = a(wl["bg"])
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
     ts = []
     for _ in range(max(1, iters)):
+        L = {k: v.clone().requires_grad_(True) for k, v in wl["leaves"].items()}
         t0 = time.perf_counter()
-        st = O.raster_forward(*args_f)
-        O.raster_backward(st, a(wl["bg"]), a(p["means3D"]), None, a(p["scales"]), a(p["rotations"]), 1.0, None, view,
-                          proj, cam["tanfovx"], cam["tanfovy"], tg[0:3], tg[3:4], tg[4:5], a(p["shs"]), 3, campos)
+        with torch.no_grad():
+            vid = torch.cdist(L["xyz"], wl["t_vertices"]).argmin(1)
+        _, world, _, T, _, wn, _ = LO.coarse_deform_c2source(wl["smpl"], L["xyz"], pose, wl["big"], wl["t_vertices"],
+                                                             normals=L["normals"], vert_ids=vid)
+        cov = LO.covariance(torch.exp(L["log_scale"]), 1.0, L["rotation"], T)
+        col = LO.view_colors(3, L["features"], world, cam["camera_center"])
+        opa = torch.sigmoid(L["opacity_logit"])
+        st = O.raster_forward(bg, a(world), a(col), a(opa), None, None, 1.0, a(cov), vm, pm, cam["tanfovx"],
+                              cam["tanfovy"], wl["H"], wl["W"], None, 3, campos)
+        g = O.raster_backward(st, bg, a(world), a(col), None, None, 1.0, a(cov), vm, pm, cam["tanfovx"], cam["tanfovy"],
+                              tg[0:3], tg[3:4], tg[4:5], None, 3, campos)
+        torch.autograd.backward([world, cov, col, opa],
+                                [torch.from_numpy(g["dL_dmeans3D"]), torch.from_numpy(g["dL_dcov3D"]),
+                                 torch.from_numpy(g["dL_dcolors"]), torch.from_numpy(g["dL_dopacity"])])
         ts.append(time.perf_counter() - t0)
     best = min(ts)
-    cores = int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))
     return {"value": 1.0 / best, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{len(ts)} fwd+bwd iterations of the full workload (view 0) by oracle/raster_oracle.c "
-                      f"(C, OpenMP), best of {len(ts)}; {sum(ts):.1f} s CPU wall"}
+            "sample": f"{len(ts)} full steps of the workload (view 0): torch-CPU LBS/cov/SH restatement with autograd + "
+                      f"oracle/raster_oracle.c (C, OpenMP) fwd+bwd; best of {len(ts)}; {sum(ts):.1f} s CPU wall"}
 
 
 # ---------------------------------------------------------------------------
@@ -311,13 +375,15 @@ def cpu_baseline(wl, cam, iters):
 def stage_bytes(stage, P, V, N, X, tiles, passes):
     """ALGORITHMIC bytes per launch (DESIGN.md 'Kernels')."""
     return {
-        "preprocess": 244 * P + 67 * V,  # SH deg 3 + scale/rot inputs
+        "preprocess": 48 * P + 28 * V,  # precomputed colour + covariance inputs
+        "lbs_fwd": 453 * P,             # fused LBS + covariance + SH deg 3 (ghr_lbs_deform.cu header)
+        "lbs_bwd": (453 - 97 + 96 + 12 + 12 + 12 + 16 + 192) * P,
         "emit_keys": 8 * P + 12 * V + 12 * N,
         "sort": N * (8 + 24 * passes),
         "tile_ranges": 8 * N + 8 * tiles,
         "blend_fwd": 44 * N + 28 * X,
         "blend_bwd": 44 * N + 28 * X + 36 * V,
-        "preprocess_bwd": 580 * P,
+        "preprocess_bwd": 132 * P,
     }.get(stage)
 
 
@@ -347,7 +413,7 @@ def run_reference_cpu(args, world, rank):
     if rank != 0:
         return
     wl = build_workload(args, 0, 1)
-    res = cpu_baseline(wl, wl["cams"][0], args.steps if args.steps <= 10 else 3)
+    res = cpu_baseline(wl, wl["views"][0], args.steps if args.steps <= 10 else 3)
     line = {"impl": "reference-cpu", "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": 0,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / res["value"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -380,26 +446,25 @@ def main():
             if rank == 0:
                 print(json.dumps({"impl": "reference", "unavailable": f"oracle/_ref not built: {e}"}), flush=True)
             return
-    cams = wl["cams"]
-    cam_host = [cam_pack(c) for c in cams]
-    cam_dev = [c.to(dev) for c in cam_host]
+    views = wl["views"]
+    vec_host = [view_pack(v) for v in views]
+    vec_dev = [v.to(dev) for v in vec_host]
     targets_host = wl["targets"].pin_memory()
     targets_dev = targets_host.to(dev)
-    cam_stage = torch.empty(35, device=dev)
+    vec_stage = torch.empty(PACK_FLOATS, device=dev)
     targets_stage = torch.empty_like(targets_dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    flat = None
     if world > 1:
         import torch.distributed as dist
 
     def one_step(i, e2e):
-        cam = cams[i % len(cams)]
+        k = i % len(views)
         if e2e:
-            cam_stage.copy_(cam_host[i % len(cams)], non_blocking=True)
+            vec_stage.copy_(vec_host[k], non_blocking=True)
             targets_stage.copy_(targets_host, non_blocking=True)
-            loss, grads = arm.step(cam, cam_stage, targets_stage)
+            loss, grads = arm.step(views[k], vec_stage, targets_stage)
         else:
-            loss, grads = arm.step(cam, cam_dev[i % len(cams)], targets_dev)
+            loss, grads = arm.step(views[k], vec_dev[k], targets_dev)
         if world > 1:
             # view-sharded data parallelism: sum the Gaussian-parameter gradients over ranks (NCCL over NVLink)
             fl = torch.cat([g.reshape(-1) for g in grads])
@@ -449,7 +514,7 @@ def main():
         prof = arm._lib.profile_read()
         arm._lib.profile_enable(False)
         # N, V per view (measured, averaged over the views this rank cycles through)
-        nv = [arm.num_rendered(cams[i % len(cams)], cam_dev[i % len(cams)]) for i in range(min(K, len(cams)))]
+        nv = [arm.measure_NV(views[i % len(views)], vec_dev[i % len(views)]) for i in range(min(K, len(views)))]
         N = float(np.mean([a for a, _ in nv])); V = float(np.mean([b for _, b in nv]))
         from mygauhuman_b200 import _lib
         passes = _lib.state_layout(P, 1, W, H).sort_passes
@@ -473,24 +538,25 @@ def main():
         return
     cpu = None
     if args.impl == "ours" and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline(wl, cams[0], args.cpu_iters)
+        cpu = cpu_baseline(wl, views[0], args.cpu_iters)
 
     views_per_step = world  # one view per rank per step
     value = views_per_step * K / (ms_dev * 1e-3)
     e2e_val = views_per_step * K / (ms_e2e * 1e-3)
-    h2d = 35 * 4 + 5 * X * 4
+    h2d = PACK_FLOATS * 4 + 5 * X * 4
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
         "ms_per_step": round(ms_dev / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "impl": args.impl,
         "config": {"workload": args.workload, "desc": WORKLOADS[args.workload]["desc"], "P": P, "W": W, "H": H,
-                   "sh_degree": 3, "views_cycled": len(cams) * world, "parallelism": f"view-sharded dp{world}",
+                   "sh_degree": 3, "views_cycled": len(views) * world, "parallelism": f"view-sharded dp{world}",
                    "l2": "flushed between steps (256 MiB fill outside the per-step event pair)",
                    "sync_free": bool(args.sync_free)},
         "e2e": {"value": round(e2e_val, 2), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-                "what": "GaussianRasterizer fwd + loss + backward; camera + 5 target planes copied from pinned host "
-                        "memory and loss.item() read back inside every step's event pair"},
+                "what": "public API step (SMPLDeformer.deform_gaussians -> GaussianRasterizer -> loss -> backward); "
+                        "camera + SMPL pose + 5 target planes copied from pinned host memory and loss.item() read back "
+                        "inside every step's event pair; Gaussian parameters stay resident (model state)"},
         "gpu_launches": launches, "clocks": clocks,
     }
     if roof is not None:

@@ -185,3 +185,27 @@ def make_scene_cloud(P, seed=0, box=10.0, scale=0.02, sh_degree=3):
     pts = g.uniform(-box / 2, box / 2, size=(P, 3))
     pts[:, 2] += box / 2 + 1.0
     return make_gaussians(P, pts.astype(np.float32), seed=seed, sh_degree=sh_degree, jitter=0.0, scale=scale)
+
+
+def big_pose_vertices(smpl, big):
+    """SMPL surface skinned into the big pose: the `big_pose_world_vertex` every reference camera carries
+    (reference scene/dataset_readers.py:586-600).  Host-side numpy (fp64) -- input generation, not the hot path."""
+    poses = big["poses"].numpy().reshape(24, 3).astype(np.float64)
+    betas = big["shapes"].numpy().reshape(-1).astype(np.float64)
+    vt = smpl["v_template"].numpy().astype(np.float64)
+    v_shaped = vt + smpl["shapedirs"].numpy().astype(np.float64) @ betas
+    joints = smpl["J_regressor"].numpy().astype(np.float64) @ v_shaped
+    R = np.stack([_rodrigues_np(p) for p in poses])
+    pf = (R[1:] - np.eye(3)[None]).reshape(-1)
+    v_posed = v_shaped + (smpl["posedirs"].numpy().astype(np.float64).reshape(-1, 207) @ pf).reshape(-1, 3)
+    G = np.zeros((24, 4, 4))
+    for i in range(24):
+        M = np.eye(4)
+        M[:3, :3] = R[i]
+        M[:3, 3] = joints[i] - (joints[SMPL_PARENTS[i]] if i else 0.0)
+        G[i] = M if i == 0 else G[SMPL_PARENTS[i]] @ M
+    A = G.copy()
+    A[:, :3, 3] -= np.einsum("jab,jb->ja", G[:, :3, :3], joints)
+    T = np.einsum("vj,jab->vab", smpl["weights"].numpy().astype(np.float64), A)
+    verts = np.einsum("vab,vb->va", T[:, :3, :3], v_posed) + T[:, :3, 3]
+    return torch.from_numpy(verts.astype(np.float32))

@@ -27,7 +27,7 @@ def rodrigues(rvec):
     K = torch.stack([zero, -kz, ky, kz, zero, -kx, -ky, kx, zero], dim=1).reshape(n, 3, 3)
     s = torch.sin(angle)[:, :, None]
     c = torch.cos(angle)[:, :, None]
-    eye = torch.eye(3, dtype=rvec.dtype)[None]
+    eye = torch.eye(3, dtype=rvec.dtype, device=rvec.device)[None]
     return eye + s * K + (1.0 - c) * (K @ K)
 
 
@@ -35,15 +35,16 @@ def rigid_chain(rot, joints, parents=SMPL_PARENTS):
     """scene/gaussian_model.py:914-944 get_rigid_transformation_torch (== smplx/lbs.py:349-405):
     G_0 = [R_0 | j_0], G_i = G_parent(i) [R_i | j_i - j_parent(i)], A_i = G_i with translation - G_i^{3x3} j_i."""
     J = joints.shape[0]
+    par = torch.as_tensor(list(parents), dtype=torch.long, device=joints.device)
     rel = joints.clone()
-    for i in range(1, J):
-        rel[i] = joints[i] - joints[parents[i]]
-    G = []
-    for i in range(J):
-        M = torch.eye(4, dtype=rot.dtype)
-        M[:3, :3] = rot[i]
-        M[:3, 3] = rel[i]
-        G.append(M if i == 0 else G[parents[i]] @ M)
+    rel[1:] = rel[1:] - joints[par[1:]]                                    # :923-924
+    top = torch.cat([rot, rel[:, :, None]], dim=-1)                        # :927 [J,3,4]
+    bottom = torch.zeros(J, 1, 4, dtype=rot.dtype, device=rot.device)
+    bottom[..., 3] = 1
+    mats = torch.cat([top, bottom], dim=-2)                                # :928-930 [J,4,4]
+    G = [mats[0]]
+    for i in range(1, J):                                                  # :933-936 serial chain
+        G.append(G[parents[i]] @ mats[i])
     A = torch.stack(G)
     A = A.clone()
     A[:, :3, 3] = A[:, :3, 3] - torch.einsum("jab,jb->ja", A[:, :3, :3], joints)
@@ -70,7 +71,7 @@ def transform_params(smpl, params, rot=None, correct_Rs=None):
 
 def nearest_vertex(t_vertices, query):
     """KNN(k=1, transpose_mode=True)(ref=t_vertices, query) -> index of the closest vertex (gaussian_model.py:775)."""
-    out = torch.empty(query.shape[0], dtype=torch.long)
+    out = torch.empty(query.shape[0], dtype=torch.long, device=query.device)
     tv = t_vertices.double()
     q = query.double()
     for s in range(0, q.shape[0], 4096):
@@ -81,7 +82,7 @@ def nearest_vertex(t_vertices, query):
 
 def pose_feature(rot):
     """(rot_mats[1:] - I) flattened, gaussian_model.py:811,838."""
-    return (rot[1:] - torch.eye(3, dtype=rot.dtype)[None]).reshape(-1)
+    return (rot[1:] - torch.eye(3, dtype=rot.dtype, device=rot.device)[None]).reshape(-1)
 
 
 def coarse_deform_c2source(smpl, query_pts, params, t_params, t_vertices, lbs_weights=None, correct_Rs=None,
