@@ -456,6 +456,8 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     if world > 1:
         import torch.distributed as dist
+    from mygauhuman_b200.multiview import GradientAllReducer
+    reducer = GradientAllReducer()
 
     def one_step(i, e2e):
         k = i % len(views)
@@ -467,8 +469,7 @@ def main():
             loss, grads = arm.step(views[k], vec_dev[k], targets_dev)
         if world > 1:
             # view-sharded data parallelism: sum the Gaussian-parameter gradients over ranks (NCCL over NVLink)
-            fl = torch.cat([g.reshape(-1) for g in grads])
-            dist.all_reduce(fl)
+            reducer(grads)
         if e2e:
             return float(loss.item())  # the device->host read of the step's result
         return None
