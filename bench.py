@@ -57,6 +57,7 @@ def parse():
     ap.add_argument("--views", type=int, default=64, help="distinct cameras cycled through (sharded across ranks)")
     ap.add_argument("--cpu-iters", type=int, default=20, help="CPU-oracle iterations for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--host-profile", action="store_true", help="cProfile of 50 un-synchronised steps to stderr")
     ap.add_argument("--sync-free", action="store_true",
                     help="ours: size the binning buffer from the previous step instead of a blocking read")
     return ap.parse_args()
@@ -496,6 +497,22 @@ def main():
         one_step(i, False)
         one_step(i, True)
     torch.cuda.synchronize()
+
+    if args.host_profile and rank == 0:
+        import cProfile, pstats
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        pr = cProfile.Profile()
+        pr.enable()
+        for i in range(50):
+            one_step(i, False)
+        pr.disable()
+        t1 = time.perf_counter()
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        print(f"[host-profile] 50 steps: host issue {1e3 * (t1 - t0) / 50:.3f} ms/step, drained after "
+              f"{1e3 * (t2 - t1):.3f} ms", file=sys.stderr)
+        pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(35)
 
     sampler = ClockSampler(torch.cuda.current_device() if "CUDA_VISIBLE_DEVICES" not in os.environ else local)
     if rank == 0:

@@ -237,10 +237,11 @@ int ghr_lbs_vertex_offsets(const ghr_lbs_model* model, const float* pose_big, co
 
 /* Nearest SMPL vertex (the reference's knn_cuda KNN(k=1), gaussian_model.py:775).
  * build: bins t_vertices [V,3] into a uniform grid inside `workspace`;
- * query: exact nearest vertex (lowest index on ties) for P points -> vert_ids [P] int32. */
+ * query: exact nearest vertex (lowest index on ties) for P points -> vert_ids [P] int32; V as built. */
 size_t ghr_vertex_grid_workspace_bytes(int32_t V);
 int ghr_vertex_grid_build(int32_t V, const float* t_vertices, void* workspace, size_t workspace_bytes, void* stream);
-int ghr_nearest_vertex(int32_t P, const float* query, const void* workspace, int32_t* vert_ids, void* stream);
+int ghr_nearest_vertex(int32_t P, const float* query, int32_t V, const void* workspace, int32_t* vert_ids,
+                       void* stream);
 
 /* Fused per-Gaussian deformation: skinning-weight blend (optionally
  * softmax(log(w+1e-9)+offset), :776-781), big pose -> T pose (:785-799), blend-shape

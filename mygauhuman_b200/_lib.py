@@ -82,7 +82,7 @@ SIGNATURES = {
     "ghr_lbs_vertex_offsets": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 5),
     "ghr_vertex_grid_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "ghr_vertex_grid_build": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
-    "ghr_nearest_vertex": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ghr_nearest_vertex": (C.c_int, [C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ghr_lbs_deform_forward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 10),
     "ghr_lbs_deform_backward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 15),
     "ghr_lbs_pose_backward": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
@@ -128,6 +128,34 @@ def error_string(status):
 def check(status, where):
     if status != GHR_OK:
         raise GhrError(status, where)
+
+
+def raw_stream(device_index):
+    """cudaStream_t of torch's current stream on `device_index` as an int (fast path: no Stream object)."""
+    import torch
+    return torch._C._cuda_getCurrentRawStream(device_index)
+
+
+class on_device:
+    """`with on_device(dev):` = torch.cuda.device(dev) but free when dev is already current (the common case)."""
+    __slots__ = ("idx", "ctx")
+
+    def __init__(self, dev):
+        self.idx = dev.index if dev.index is not None else 0
+        self.ctx = None
+
+    def __enter__(self):
+        import torch
+        if torch._C._cuda_getDevice() != self.idx:
+            self.ctx = torch.cuda.device(self.idx)
+            self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *a):
+        if self.ctx is not None:
+            self.ctx.__exit__(*a)
+            self.ctx = None
+        return False
 
 
 def launch_count():

@@ -307,12 +307,12 @@ int ghr_vertex_grid_build(int32_t V, const float* t_vertices, void* workspace, s
     return check_cuda(launch_vertex_grid_build(V, t_vertices, (char*)workspace, (cudaStream_t)stream), "vertex_grid_build");
 }
 
-int ghr_nearest_vertex(int32_t P, const float* query, const void* workspace, int32_t* vert_ids, void* stream)
+int ghr_nearest_vertex(int32_t P, const float* query, int32_t V, const void* workspace, int32_t* vert_ids, void* stream)
 {
-    if (P < 0) return GHR_ERR_BAD_ARG;
+    if (P < 0 || V <= 0) return GHR_ERR_BAD_ARG;
     if (P == 0) return GHR_OK;
     if (!query || !workspace || !vert_ids) return GHR_ERR_BAD_ARG;
-    return check_cuda(launch_nearest_vertex(P, query, (const char*)workspace, vert_ids, (cudaStream_t)stream), "nearest_vertex");
+    return check_cuda(launch_nearest_vertex(P, query, V, (const char*)workspace, vert_ids, (cudaStream_t)stream), "nearest_vertex");
 }
 
 int ghr_lbs_deform_forward(const ghr_deform_params* prm, float* smpl_pts, float* world_pts, float* bweights,

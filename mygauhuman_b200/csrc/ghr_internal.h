@@ -108,7 +108,7 @@ cudaError_t launch_lbs_deform_forward(const ghr_deform_params& p, const DeformOu
 cudaError_t launch_lbs_deform_backward(const ghr_deform_params& p, const DeformGrads& g, cudaStream_t s);
 size_t vertex_grid_workspace_bytes(int V);
 cudaError_t launch_vertex_grid_build(int V, const float* verts, char* ws, cudaStream_t s);
-cudaError_t launch_nearest_vertex(int P, const float* query, const char* ws, int32_t* vid, cudaStream_t s);
+cudaError_t launch_nearest_vertex(int P, const float* query, int V, const char* ws, int32_t* vid, cudaStream_t s);
 size_t knn_workspace_bytes(int P);
 cudaError_t launch_knn(int P, const float* points, float* out, char* ws, size_t ws_bytes, cudaStream_t s);
 

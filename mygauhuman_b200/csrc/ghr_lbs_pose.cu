@@ -122,38 +122,36 @@ __global__ void __launch_bounds__(32) lbs_pose_kernel(int NB, const float* __res
         mat3_inverse(R, inv);
 #pragma unroll
         for (int k = 0; k < 9; k++) out[GHR_POSE_RGINV + k] = inv[k];
-        // kinematic chain (gaussian_model.py:914-944): G_0 = [R_0 | j_0]; G_i = G_parent [R_i | j_i - j_parent]
-        for (int i = 0; i < kJ; i++) {
-            float G[12];
+    }
+    // kinematic chain (gaussian_model.py:914-944): G_0 = [R_0 | j_0]; G_i = G_parent [R_i | j_i - j_parent].
+    // 24 dependent steps; lanes 0..11 each own one element (r,c) of the 3x4 matrix, so a step is ~4 FMAs deep.
+    const int r = (j < 12) ? j / 4 : 0, c = (j < 12) ? j % 4 : 0;
+    const int my_parent = (j > 0 && j < kJ) ? parents[j] : 0;  // one global load up front, not one per chain step
+    for (int i = 0; i < kJ; i++) {
+        float gval = 0.0f;
+        const int p = __shfl_sync(0xffffffffu, my_parent, i);
+        if (j < 12) {
             if (i == 0) {
-#pragma unroll
-                for (int r = 0; r < 3; r++) {
-                    G[4 * r] = s_rot[0][3 * r]; G[4 * r + 1] = s_rot[0][3 * r + 1]; G[4 * r + 2] = s_rot[0][3 * r + 2];
-                    G[4 * r + 3] = s_joint[0][r];
-                }
+                gval = c < 3 ? s_rot[0][3 * r + c] : s_joint[0][r];
             } else {
-                const int p = parents[i];
-                const float rel[3] = {s_joint[i][0] - s_joint[p][0], s_joint[i][1] - s_joint[p][1],
-                                      s_joint[i][2] - s_joint[p][2]};
-#pragma unroll
-                for (int r = 0; r < 3; r++) {
-                    const float g0 = s_G[p][4 * r], g1 = s_G[p][4 * r + 1], g2 = s_G[p][4 * r + 2], g3 = s_G[p][4 * r + 3];
-#pragma unroll
-                    for (int c = 0; c < 3; c++) G[4 * r + c] = g0 * s_rot[i][c] + g1 * s_rot[i][3 + c] + g2 * s_rot[i][6 + c];
-                    G[4 * r + 3] = g0 * rel[0] + g1 * rel[1] + g2 * rel[2] + g3;
+                const float g0 = s_G[p][4 * r], g1 = s_G[p][4 * r + 1], g2 = s_G[p][4 * r + 2], g3 = s_G[p][4 * r + 3];
+                if (c < 3) {
+                    gval = g0 * s_rot[i][c] + g1 * s_rot[i][3 + c] + g2 * s_rot[i][6 + c];
+                } else {
+                    gval = g0 * (s_joint[i][0] - s_joint[p][0]) + g1 * (s_joint[i][1] - s_joint[p][1]) +
+                           g2 * (s_joint[i][2] - s_joint[p][2]) + g3;
                 }
             }
-#pragma unroll
-            for (int k = 0; k < 12; k++) { s_G[i][k] = G[k]; out[GHR_POSE_G + 12 * i + k] = G[k]; }
+            s_G[i][j] = gval;
+            out[GHR_POSE_G + 12 * i + j] = gval;
+        }
+        __syncwarp();
+        if (j < 12) {
             // A_i = G_i with translation - G_i^{3x3} j_i (:939-942)
-#pragma unroll
-            for (int r = 0; r < 3; r++) {
-                out[GHR_POSE_A + 12 * i + 4 * r] = G[4 * r];
-                out[GHR_POSE_A + 12 * i + 4 * r + 1] = G[4 * r + 1];
-                out[GHR_POSE_A + 12 * i + 4 * r + 2] = G[4 * r + 2];
-                out[GHR_POSE_A + 12 * i + 4 * r + 3] =
-                    G[4 * r + 3] - (G[4 * r] * s_joint[i][0] + G[4 * r + 1] * s_joint[i][1] + G[4 * r + 2] * s_joint[i][2]);
-            }
+            float a = gval;
+            if (c == 3)
+                a = gval - (s_G[i][4 * r] * s_joint[i][0] + s_G[i][4 * r + 1] * s_joint[i][1] + s_G[i][4 * r + 2] * s_joint[i][2]);
+            out[GHR_POSE_A + 12 * i + j] = a;
         }
     }
 }

@@ -18,6 +18,25 @@ import torch
 from .. import _lib
 from .._lib import RasterParams, check, lib, state_layout
 
+# Default mode ("optimistic launch"): the binning buffer of a call is sized from the previous call with the same
+# (P, W, H) plus 25 % headroom and the whole forward is enqueued at once; the host then waits only for the FIRST kernel
+# (an event right after preprocess), reads the exact num_rendered from pinned memory while the GPU is already sorting
+# and blending, and re-runs the render stage with an exact-size buffer in the rare case the guess was too small.
+# Results are always exact; unlike the reference's blocking read (rasterizer_impl.cu:283) the GPU never idles.
+_cap_hint = {}      # (device index, P, W, H) -> capacity guess
+_cap_of = {}        # binning buffer data_ptr -> capacity it was laid out for (backward needs it)
+
+
+def _round_cap(n):
+    return (int(n) + 63) // 64 * 64
+
+
+def _remember_capacity(binning, capacity):
+    if len(_cap_of) > 4096:
+        _cap_of.clear()
+    _cap_of[binning.data_ptr()] = capacity
+
+
 # Sync-free mode: when set to an int, forward() does not read num_rendered back
 # to the host; the binning buffer is sized for that many (Gaussian, tile) pairs
 # and the returned "num_rendered" is that capacity.  Overflow is latched on the
@@ -45,8 +64,8 @@ def _ptr(t, align=4):
     return t.data_ptr(), t
 
 
-def _stream():
-    return torch.cuda.current_stream().cuda_stream
+def _stream(dev=None):
+    return _lib.raw_stream(torch._C._cuda_getDevice() if dev is None or dev.index is None else dev.index)
 
 
 def _params(keep, background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
@@ -93,7 +112,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         return (0, torch.zeros(3, H, W, **f32), torch.zeros(1, H, W, **f32), torch.zeros(1, H, W, **f32),
                 torch.zeros(0, dtype=torch.int32, device=dev), torch.empty(0, **u8), torch.empty(0, **u8),
                 torch.empty(0, **u8))
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         keep = []
         p = _params(keep, background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                     viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug)
@@ -105,22 +124,44 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         out_depth = torch.empty(1, H, W, **f32)
         out_alpha = torch.empty(1, H, W, **f32)
         l = lib()
-        s = _stream()
-        if _capacity is None:
+        s = _stream(dev)
+
+        def render(capacity):
+            L = state_layout(P, capacity, W, H)
+            binning = torch.empty(L.binning_bytes, dtype=torch.uint8, device=dev)
+            check(l.ghr_forward_render(C.byref(p), geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(),
+                                       capacity, img.data_ptr(), img.numel(), out_color.data_ptr(), out_depth.data_ptr(),
+                                       out_alpha.data_ptr(), s), "ghr_forward_render")
+            return binning
+
+        if _capacity is not None:  # explicit sync-free mode
+            check(l.ghr_forward_preprocess(C.byref(p), radii.data_ptr(), geom.data_ptr(), geom.numel(), None, s),
+                  "ghr_forward_preprocess")
+            capacity = num_rendered = _round_cap(_capacity)
+            binning = render(capacity)
+        else:
             counter = _pinned_counter(dev)
             check(l.ghr_forward_preprocess(C.byref(p), radii.data_ptr(), geom.data_ptr(), geom.numel(),
                                            counter.data_ptr(), s), "ghr_forward_preprocess")
-            torch.cuda.current_stream().synchronize()  # the reference's blocking D2H read, rasterizer_impl.cu:283
-            capacity = num_rendered = int(counter[0])
-        else:
-            check(l.ghr_forward_preprocess(C.byref(p), radii.data_ptr(), geom.data_ptr(), geom.numel(), None, s),
-                  "ghr_forward_preprocess")
-            capacity = num_rendered = _capacity
-        L = state_layout(P, capacity, W, H)
-        binning = torch.empty(L.binning_bytes, dtype=torch.uint8, device=dev)
-        check(l.ghr_forward_render(C.byref(p), geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(),
-                                   capacity, img.data_ptr(), img.numel(), out_color.data_ptr(), out_depth.data_ptr(),
-                                   out_alpha.data_ptr(), s), "ghr_forward_render")
+            key = (dev.index, P, W, H)
+            guess = _cap_hint.get(key)
+            if guess is None:
+                torch.cuda.current_stream().synchronize()  # first call: the reference's blocking read
+                num_rendered = int(counter[0])
+                capacity = _round_cap(num_rendered)
+                binning = render(capacity)
+            else:
+                ev = torch.cuda.Event()
+                ev.record()
+                capacity = guess
+                binning = render(capacity)       # GPU keeps working while the host waits for preprocess only
+                ev.synchronize()
+                num_rendered = int(counter[0])
+                if num_rendered > capacity:      # rare: guess too small -> kernels exited early; redo exactly
+                    capacity = _round_cap(num_rendered)
+                    binning = render(capacity)
+            _cap_hint[key] = _round_cap(num_rendered + num_rendered // 4 + 1024)
+        _remember_capacity(binning, capacity)
         if debug:
             read_status(geom, raise_on_error=True)
     return num_rendered, out_color, out_depth, out_alpha, radii, geom, binning, img
@@ -138,7 +179,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     if P == 0:
         z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
         return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
-    with torch.cuda.device(dev):
+    capacity = _cap_of.get(binningBuffer.data_ptr(), int(R))
+    with _lib.on_device(dev):
         keep = []
         # opacities are not an input of the reference backward (they live in the saved geometry state)
         p = _params(keep, background, means3D, colors, means3D, scales, rotations, scale_modifier, cov3D_precomp,
@@ -156,11 +198,11 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
              for t in (dL_dout_color, dL_dout_depth, dL_dout_alpha)]
         radii = radii.contiguous()
         check(lib().ghr_backward(C.byref(p), radii.data_ptr(), geomBuffer.data_ptr(), geomBuffer.numel(),
-                                 binningBuffer.data_ptr(), binningBuffer.numel(), int(R), imageBuffer.data_ptr(),
+                                 binningBuffer.data_ptr(), binningBuffer.numel(), capacity, imageBuffer.data_ptr(),
                                  imageBuffer.numel(), g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(),
                                  accum.data_ptr(), dmeans2D.data_ptr(), dcolors.data_ptr(), dopacity.data_ptr(),
                                  dmeans3D.data_ptr(), dcov3D.data_ptr(), dsh.data_ptr() if M else None,
-                                 dscales.data_ptr(), drot.data_ptr(), _stream()), "ghr_backward")
+                                 dscales.data_ptr(), drot.data_ptr(), _stream(dev)), "ghr_backward")
     return (dmeans2D.view(P, 3), dcolors.view(P, 3), dopacity.view(P, 1), dmeans3D.view(P, 3), dcov3D.view(P, 6),
             dsh.view(P, M, 3), dscales.view(P, 3), drot.view(P, 4))
 
@@ -170,14 +212,14 @@ def mark_visible(means3D, viewmatrix, projmatrix):
     P = means3D.size(0)
     present = torch.zeros(P, dtype=torch.bool, device=means3D.device)
     if P:
-        with torch.cuda.device(means3D.device):
+        with _lib.on_device(means3D.device):
             keep = []
             ptrs = []
             for t in (means3D, viewmatrix, projmatrix):
                 ptr, t = _ptr(t)
                 keep.append(t)
                 ptrs.append(ptr)
-            check(lib().ghr_mark_visible(P, ptrs[0], ptrs[1], ptrs[2], present.data_ptr(), _stream()),
+            check(lib().ghr_mark_visible(P, ptrs[0], ptrs[1], ptrs[2], present.data_ptr(), _stream(means3D.device)),
                   "ghr_mark_visible")
     return present
 
@@ -194,7 +236,10 @@ def read_status(geomBuffer, raise_on_error=False):
 
 
 def state_views(P, capacity, W, H, geomBuffer, binningBuffer, imageBuffer):
-    """Typed views of the internal state the reference keeps in its three buffers."""
+    """Typed views of the internal state the reference keeps in its three buffers.
+    `capacity` is the num_rendered the forward returned; the capacity the binning buffer was actually laid
+    out for (>= num_rendered) is looked up."""
+    capacity = _cap_of.get(binningBuffer.data_ptr(), capacity) if binningBuffer.numel() else capacity
     L = state_layout(P, capacity, W, H)
     X = W * H
     tiles = ((W + 15) // 16) * ((H + 15) // 16)

@@ -25,7 +25,7 @@ NJ = 24
 
 
 def _stream():
-    return torch.cuda.current_stream().cuda_stream
+    return _lib.raw_stream(torch._C._cuda_getDevice())
 
 
 def _f32c(t):
@@ -65,7 +65,7 @@ class SMPLDeformer:
         self.parents = smpl["kintree_table"][0].to(dev).to(torch.int32).contiguous()
         self.joint_template = torch.empty(NJ, 3, device=dev)
         self.joint_shapedirs = torch.empty(NJ, 3, max(self.NB, 1), device=dev)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             check(lib().ghr_lbs_prepare(self.V, self.NB, self.v_template.data_ptr(), self.shapedirs.data_ptr(),
                                         self.J_regressor.data_ptr(), self.joint_template.data_ptr(),
                                         self.joint_shapedirs.data_ptr(), _stream()), "ghr_lbs_prepare")
@@ -85,7 +85,7 @@ class SMPLDeformer:
         Th = _f32c(params["Th"].to(dev)).reshape(-1)
         cr = None if correct_Rs is None else _f32c(correct_Rs.detach().to(dev)).reshape(-1)
         out = torch.empty(_lib.POSE_FLOATS, device=dev)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             check(lib().ghr_lbs_pose(C.byref(self._model), poses.data_ptr(), shapes.data_ptr(), _ptr(cr), R.data_ptr(),
                                      Th.data_ptr(), out.data_ptr(), _stream()), "ghr_lbs_pose")
         return out
@@ -111,7 +111,7 @@ class SMPLDeformer:
     def vertex_offsets(self, pose_big, pose_target, shapes):
         off = torch.empty(self.V, 3, device=self.device)
         sh = None if shapes is None else _f32c(shapes.to(self.device)).reshape(-1)[: self.NB]
-        with torch.cuda.device(self.device):
+        with _lib.on_device(self.device):
             check(lib().ghr_lbs_vertex_offsets(C.byref(self._model), _ptr(pose_big), pose_target.data_ptr(), _ptr(sh),
                                                off.data_ptr(), _stream()), "ghr_lbs_vertex_offsets")
         return off
@@ -121,7 +121,7 @@ class SMPLDeformer:
         """Exact nearest vertex index [P] int32 (the reference's knn_cuda KNN(k=1), gaussian_model.py:775)."""
         tv = _f32c(t_vertices.detach()).reshape(-1, 3)
         key = (tv.data_ptr(), t_vertices._version, tv.shape[0])
-        with torch.cuda.device(self.device):
+        with _lib.on_device(self.device):
             if key != self._grid_key:
                 nbytes = lib().ghr_vertex_grid_workspace_bytes(tv.shape[0])
                 ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
@@ -130,7 +130,8 @@ class SMPLDeformer:
                 self._grid, self._grid_key, self._grid_src = ws, key, tv
             q = _f32c(query.detach()).reshape(-1, 3)
             vid = torch.empty(q.shape[0], dtype=torch.int32, device=self.device)
-            check(lib().ghr_nearest_vertex(q.shape[0], q.data_ptr(), self._grid.data_ptr(), vid.data_ptr(), _stream()),
+            check(lib().ghr_nearest_vertex(q.shape[0], q.data_ptr(), self._grid_key[2], self._grid.data_ptr(), vid.data_ptr(),
+                                           _stream()),
                   "ghr_nearest_vertex")
         return vid
 
@@ -169,7 +170,7 @@ class SMPLDeformer:
         off = self.vertex_offsets(None, buf, betas)
         verts = torch.empty(self.V, 3, device=dev)
         T12 = torch.empty(self.V, 12, device=dev)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             check(lib().ghr_smpl_lbs_vertices(C.byref(self._model), self.v_template.data_ptr(), buf.data_ptr(),
                                               off.data_ptr(), verts.data_ptr(), T12.data_ptr(), _stream()),
                   "ghr_smpl_lbs_vertices")
@@ -230,7 +231,7 @@ class _DeformFn(torch.autograd.Function):
         col = torch.empty(P, 3, **f) if shs is not None else None
         clamped = torch.empty(P, dtype=torch.uint8, device=dev) if shs is not None else None
         if P:
-            with torch.cuda.device(dev):
+            with _lib.on_device(dev):
                 check(lib().ghr_lbs_deform_forward(C.byref(p), smpl_pts.data_ptr(), world.data_ptr(), bw.data_ptr(),
                                                    transforms.data_ptr(), _ptr(transl), _ptr(wn), _ptr(cov), _ptr(col),
                                                    _ptr(clamped), _stream()), "ghr_lbs_deform_forward")
@@ -265,7 +266,7 @@ class _DeformFn(torch.autograd.Function):
         d_A = torch.zeros(NJ * 12, **f) if want_pose else None
         d_off = torch.zeros(self.V, 3, **f) if want_pose else None
         if P:
-            with torch.cuda.device(dev):
+            with _lib.on_device(dev):
                 check(lib().ghr_lbs_deform_backward(
                     C.byref(p), _ptr(clamped), _ptr(g_world), _ptr(g_transforms), _ptr(g_wn), _ptr(g_cov), _ptr(g_col),
                     d_xyz.data_ptr(), _ptr(d_n), _ptr(d_lw), _ptr(d_sc), _ptr(d_rot), _ptr(d_sh), _ptr(d_A), _ptr(d_off),
@@ -273,7 +274,7 @@ class _DeformFn(torch.autograd.Function):
         d_cr = None
         if want_pose:
             buf = torch.empty(23 * 9 + 207, **f)
-            with torch.cuda.device(dev):
+            with _lib.on_device(dev):
                 check(lib().ghr_lbs_pose_backward(C.byref(self._model), pose_tgt.data_ptr(), None, d_A.data_ptr(),
                                                   d_off.data_ptr(), buf.data_ptr(), _stream()), "ghr_lbs_pose_backward")
             d_cr = buf[:207].view(23, 3, 3).reshape(ctx.correct_Rs.shape)
@@ -299,7 +300,7 @@ def batch_rodrigues(rot_vecs, epsilon=1e-8, dtype=torch.float32):
         n = min(NJ, N - s)
         chunk[:n] = rv[s:s + n]
         buf = torch.empty(_lib.POSE_FLOATS, device=dev)
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             check(lib().ghr_lbs_pose(C.byref(model[0]), chunk.data_ptr(), zero.data_ptr(), None, eye.data_ptr(),
                                      zero.data_ptr(), buf.data_ptr(), _stream()), "ghr_lbs_pose")
         out[s:s + n] = buf[_lib.POSE_ROD:_lib.POSE_ROD + 216].view(NJ, 3, 3)[:n]
