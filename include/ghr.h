@@ -97,6 +97,7 @@ typedef struct ghr_layout {
     int64_t capacity;       /* pairs the binning buffer holds                     */
     int32_t sort_bits;      /* 32 + getHigherMsb(tiles), rasterizer_impl.cu:302   */
     int32_t sort_passes;
+    size_t i_order;         /* uint32[tiles]: tile ids by decreasing list length (blend work queue) */
 } ghr_layout;
 
 /* First bytes of the geom buffer (device memory). */
@@ -104,7 +105,9 @@ typedef struct ghr_geom_header {
     uint32_t num_rendered;  /* N = sum of tiles_touched (rasterizer_impl.cu:283)  */
     uint32_t error;         /* 0 or -(ghr_status) raised on the device            */
     uint32_t scan_ticket;   /* work counter of the fused preprocess+scan kernel   */
-    uint32_t reserved[61];
+    uint32_t blend_fwd_ticket; /* work-queue heads of the two blend kernels        */
+    uint32_t blend_bwd_ticket;
+    uint32_t reserved[59];
 } ghr_geom_header;
 
 int ghr_version(void);

@@ -37,7 +37,7 @@ class Layout(C.Structure):
         ("img_bytes", C.c_size_t), ("i_final_T", C.c_size_t), ("i_n_contrib", C.c_size_t), ("i_ranges", C.c_size_t),
         ("binning_bytes", C.c_size_t), ("b_header", C.c_size_t), ("b_keys_a", C.c_size_t), ("b_keys_b", C.c_size_t),
         ("b_vals_a", C.c_size_t), ("b_vals_b", C.c_size_t), ("b_status", C.c_size_t),
-        ("capacity", C.c_int64), ("sort_bits", C.c_int32), ("sort_passes", C.c_int32),
+        ("capacity", C.c_int64), ("sort_bits", C.c_int32), ("sort_passes", C.c_int32), ("i_order", C.c_size_t),
     ]
 
 

@@ -82,6 +82,7 @@ int ghr_state_layout(int32_t P, int64_t capacity, int32_t W, int32_t H, ghr_layo
     L->i_final_T = o; o += align_up(sizeof(float) * X);
     L->i_n_contrib = o; o += align_up(sizeof(uint32_t) * X);
     L->i_ranges = o; o += align_up(sizeof(uint2) * tiles);
+    L->i_order = o; o += align_up(sizeof(uint32_t) * tiles);
     L->img_bytes = o;
 
     L->capacity = capacity;

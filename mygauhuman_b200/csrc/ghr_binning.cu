@@ -80,6 +80,33 @@ __global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_kernel(ghr_geom_header*
     }
 }
 
+// Tile ids ordered by decreasing list length (power-of-two buckets): the blend kernels pull (tile, block)
+// work items from a queue in this order, so the few heavy tiles of a human-shaped scene start first and
+// spread over all SMs (longest-processing-time-first) instead of landing wherever blockIdx order puts them.
+__global__ void __launch_bounds__(1024) tile_order_kernel(int tiles, const uint2* __restrict__ ranges,
+                                                          const ghr_geom_header* __restrict__ hdr, int64_t capacity,
+                                                          uint32_t* __restrict__ order)
+{
+    __shared__ uint32_t s_hist[33], s_base[33];
+    const bool overflow = (int64_t)hdr->num_rendered > capacity;
+    if (threadIdx.x < 33) s_hist[threadIdx.x] = 0;
+    __syncthreads();
+    for (int t = threadIdx.x; t < tiles; t += 1024) {
+        const uint32_t n = overflow ? 0u : ranges[t].y - ranges[t].x;
+        atomicAdd(&s_hist[n ? 32 - __clz(n) : 0], 1u);  // bucket b holds lengths in [2^(b-1), 2^b)
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t acc = 0;
+        for (int b = 32; b >= 0; b--) { s_base[b] = acc; acc += s_hist[b]; }
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < tiles; t += 1024) {
+        const uint32_t n = overflow ? 0u : ranges[t].y - ranges[t].x;
+        order[atomicAdd(&s_base[n ? 32 - __clz(n) : 0], 1u)] = (uint32_t)t;
+    }
+}
+
 cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binning,
                              const ghr_layout& L, int64_t capacity, cudaStream_t s)
 {
@@ -111,6 +138,10 @@ cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, cha
         reinterpret_cast<const SortHeader*>(binning + L.b_header),
         reinterpret_cast<const uint64_t*>(binning + L.b_keys_a),
         reinterpret_cast<const uint64_t*>(binning + L.b_keys_b), reinterpret_cast<uint2*>(img + L.i_ranges));
+    count_launch();
+    tile_order_kernel<<<1, 1024, 0, s>>>(tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
+                                         reinterpret_cast<const ghr_geom_header*>(geom + L.g_header), capacity,
+                                         reinterpret_cast<uint32_t*>(img + L.i_order));
     return cudaGetLastError();
 }
 

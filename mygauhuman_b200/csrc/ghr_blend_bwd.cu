@@ -67,170 +67,201 @@ __device__ __forceinline__ int reduce_slot(uint32_t lane)
     return local < 5 ? local : 99;
 }
 
-template <int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) blend_backward_kernel(
-    int W, int H, const uint2* __restrict__ ranges, const SortHeader* __restrict__ sh,
-    const uint32_t* __restrict__ vals_a, const uint32_t* __restrict__ vals_b, const float4* __restrict__ rec,
-    const ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
+constexpr int kBwdWarps = 4;     // independent warps per CTA
+constexpr int kBwdBatch = 64;    // Gaussians per staging round and warp
+constexpr int kBwdStages = 3;
+constexpr int kBwdCtasPerSm = 4;
+
+// Persistent kernel: warps pull (tile, 8x4 block) work items from a queue ordered by decreasing tile-list
+// length (tile_order_kernel) and work independently (no block-level barrier); see ghr_blend_fwd.cu.
+__global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
+    int W, int H, int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
+    const SortHeader* __restrict__ sh, const uint32_t* __restrict__ vals_a, const uint32_t* __restrict__ vals_b,
+    const float4* __restrict__ rec, ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
     const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
     const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas, float* __restrict__ accum)
 {
-    constexpr int THREADS = WARPS * 32;
-    constexpr int SUBS = 8 / WARPS;
-    constexpr int BATCH = 128;
-    constexpr int PER_THREAD = BATCH / THREADS;
-    static_assert(BATCH % THREADS == 0, "batch/threads");
-    __shared__ __align__(16) float4 s_rec[2][BATCH * 3];
-    __shared__ uint32_t s_id[2][BATCH];
+    constexpr int BATCH = kBwdBatch, NSTAGE = kBwdStages, PER_LANE = BATCH / 32;
+    __shared__ __align__(16) float4 s_all[kBwdWarps][NSTAGE][BATCH * 3];
+    __shared__ uint32_t s_id_all[kBwdWarps][NSTAGE][BATCH];
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float4(*s_rec)[BATCH * 3] = s_all[warp];
+    uint32_t(*s_id)[BATCH] = s_id_all[warp];
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
-    const uint32_t tile_x = blockIdx.x / SUBS, sub = blockIdx.x % SUBS, tile_y = blockIdx.y;
-    const uint32_t wb = sub * WARPS + warp;  // same 8x4 pixel blocks as the forward
-    const uint32_t bx0 = tile_x * GHR_TILE + (wb & 1u) * 8u, by0 = tile_y * GHR_TILE + (wb >> 1) * 4u;
-    const uint32_t pixx = bx0 + (lane & 7u), pixy = by0 + (lane >> 3);
-    const bool inside = pixx < (uint32_t)W && pixy < (uint32_t)H;
-    const float pxf = (float)pixx, pyf = (float)pixy;
-    const float rx0 = (float)bx0, rx1 = (float)(bx0 + 7u), ry0 = (float)by0, ry1 = (float)(by0 + 3u);
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
-    const uint2 range = overflow ? make_uint2(0, 0) : ranges[tile_y * gx + tile_x];
     const uint32_t* __restrict__ point_list = sh->sorted_sel ? vals_b : vals_a;
-    const int todo_total = (int)(range.y - range.x);
-
-    const size_t pix = (size_t)pixy * W + pixx, HW = (size_t)H * W;
-    const float T_final = inside ? final_Ts[pix] : 0.0f;
-    float T = T_final;
-    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
-    // the CTA only walks the part of the list some pixel of it still needs
-    __shared__ int s_cta_last[WARPS];
-    const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
-    if (lane == 0) s_cta_last[warp] = warp_last;
-    __syncthreads();
-    int cta_last = 0;
-#pragma unroll
-    for (int w = 0; w < WARPS; w++) cta_last = max(cta_last, s_cta_last[w]);
-    // list positions [0, cta_last) are needed; walk them back to front
-    const int walk = min(todo_total, cta_last);
-    const int rounds = (walk + BATCH - 1) / BATCH;
-    if (rounds == 0) return;
-
-    float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, dL_ddepth = 0.f, dL_dalpha = 0.f;
-    if (inside) {
-        dpix0 = dL_dpixels[pix]; dpix1 = dL_dpixels[HW + pix]; dpix2 = dL_dpixels[2 * HW + pix];
-        dL_ddepth = dL_ddepths[pix]; dL_dalpha = dL_dalphas[pix];
-    }
-    const float bg_dot = bg[0] * dpix0 + bg[1] * dpix1 + bg[2] * dpix2;
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
-    float accum_depth_rec = 0.f, accum_alpha_rec = 0.f, last_alpha = 0.f, last_depth = 0.f;
+    const float bgc0 = bg[0], bgc1 = bg[1], bgc2 = bg[2];
     const float ddelx_dx = (float)(0.5 * W), ddely_dy = (float)(0.5 * H);
     const int slot = reduce_slot(lane);
     const bool writer = slot < 9 && !(lane & 1);
+    const size_t HW = (size_t)H * W;
+    const uint32_t n_items = (uint32_t)tiles * 8u;
 
-    // round r stages list positions walk-1-r*BATCH-slot (back to front)
-    auto stage = [&](int round, int buf) {
-#pragma unroll
-        for (int u = 0; u < PER_THREAD; u++) {
-            const int sl = (int)threadIdx.x + u * THREADS;
-            const int progress = round * BATCH + sl;
-            if (progress < walk) {
-                const uint32_t id = point_list[range.x + (uint32_t)(walk - 1 - progress)];
-                s_id[buf][sl] = id;
-                const float4* src = rec + 3 * (size_t)id;
-                float4* dst = &s_rec[buf][sl * 3];
-                cp_async16b(dst, src);
-                cp_async16b(dst + 1, src + 1);
-                cp_async16b(dst + 2, src + 2);
-            }
+    for (;;) {
+        uint32_t item = 0;
+        if (lane == 0) item = atomicAdd(&hdr->blend_bwd_ticket, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= n_items) break;
+        const uint32_t tile = order[item >> 3], wb = item & 7u;  // same 8x4 pixel blocks as the forward
+        const uint2 range = overflow ? make_uint2(0, 0) : ranges[tile];
+        const int todo_total = (int)(range.y - range.x);
+        if (todo_total == 0) break;  // the queue is sorted by length: everything after this is empty too
+        const uint32_t tile_x = tile % gx, tile_y = tile / gx;
+        const uint32_t bx0 = tile_x * GHR_TILE + (wb & 1u) * 8u, by0 = tile_y * GHR_TILE + (wb >> 1) * 4u;
+        const uint32_t pixx = bx0 + (lane & 7u), pixy = by0 + (lane >> 3);
+        const bool inside = pixx < (uint32_t)W && pixy < (uint32_t)H;
+        const float pxf = (float)pixx, pyf = (float)pixy;
+        const float rx0 = (float)bx0, rx1 = (float)(bx0 + 7u), ry0 = (float)by0, ry1 = (float)(by0 + 3u);
+
+        const size_t pix = (size_t)pixy * W + pixx;
+        const float T_final = inside ? final_Ts[pix] : 0.0f;
+        float T = T_final;
+        const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+        // the warp only walks the part of the list some pixel of it still needs: positions [0, warp_last)
+        const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+        const int walk = min(todo_total, warp_last);
+        const int rounds = (walk + BATCH - 1) / BATCH;
+        if (rounds == 0) continue;
+
+        float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, dL_ddepth = 0.f, dL_dalpha = 0.f;
+        if (inside) {
+            dpix0 = dL_dpixels[pix]; dpix1 = dL_dpixels[HW + pix]; dpix2 = dL_dpixels[2 * HW + pix];
+            dL_ddepth = dL_ddepths[pix]; dL_dalpha = dL_dalphas[pix];
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
+        const float bg_dot = bgc0 * dpix0 + bgc1 * dpix1 + bgc2 * dpix2;
+        float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
+        float accum_depth_rec = 0.f, accum_alpha_rec = 0.f, last_alpha = 0.f, last_depth = 0.f;
 
-    stage(0, 0);
-    int toDo = walk;
-    for (int i = 0; i < rounds; i++, toDo -= BATCH) {
-        const int buf = i & 1;
-        if (i + 1 < rounds) { stage(i + 1, buf ^ 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
-        else asm volatile("cp.async.wait_group 0;" ::: "memory");
-        __syncthreads();
-        const int n = min(BATCH, toDo);
-        const float4* r = s_rec[buf];
-        // entry j of this round sits at list position pos(j) = walk-1-(i*BATCH+j); the reference's
-        // `contributor` for it equals pos(j) (backward.cu:499-501: skip if contributor >= last_contributor)
-        const int pos0 = walk - 1 - i * BATCH;
-        // first j this warp needs: pos(j) < warp_last
-        int j0 = pos0 - warp_last + 1;
-        j0 = j0 < 0 ? 0 : j0;
-        for (int g = (j0 & ~31); g < n; g += 32) {
-            const int jj = g + (int)lane;
-            bool keep = false;
-            if (jj >= j0 && jj < n) {
-                const float4 c0 = r[3 * jj];
-                float ex, ey;
-                unpack_cull_extent(__float_as_uint(r[3 * jj + 2].w), ex, ey);
-                const float ddx = fmaxf(fmaxf(rx0 - c0.x, c0.x - rx1), 0.0f);
-                const float ddy = fmaxf(fmaxf(ry0 - c0.y, c0.y - ry1), 0.0f);
-                keep = !(ddx > ex) && !(ddy > ey);
+        // round r stages list positions walk-1-r*BATCH-slot (back to front).  Ids are fetched one round ahead of
+        // the record copies (two dependent L2 round trips otherwise), records two rounds ahead of their use.
+        uint32_t nid[PER_LANE];
+        auto load_ids = [&](int round) {
+#pragma unroll
+            for (int u = 0; u < PER_LANE; u++) {
+                const int progress = round * BATCH + (int)lane + u * 32;
+                nid[u] = (round < rounds && progress < walk) ? point_list[range.x + (uint32_t)(walk - 1 - progress)] : 0xFFFFFFFFu;
             }
-            uint32_t mask = __ballot_sync(0xffffffffu, keep);
-            while (mask) {
-                const int j = g + __ffs(mask) - 1;
-                mask &= mask - 1;
-                const int contributor = pos0 - j;
-                const float4 r0 = r[3 * j], r1 = r[3 * j + 1];
-                const float dx = __fsub_rn(r0.x, pxf), dy = __fsub_rn(r0.y, pyf);
-                const float power = pair_power(dx, dy, r1.x, r1.y, r1.z);
-                const float G = expf(power);
-                const float alpha = fminf(0.99f, __fmul_rn(r1.w, G));
-                const bool valid = (contributor < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
-                if (vmask == 0) continue;
-                float v[9];
+        };
+        auto stage = [&](int buf) {
 #pragma unroll
-                for (int k = 0; k < 9; k++) v[k] = 0.0f;
-                if (valid) {
-                    const float4 r2 = r[3 * j + 2];
-                    T = T / (1.0f - alpha);
-                    const float dchannel_dcolor = alpha * T;
-                    float dL_dopa = 0.0f;
-                    acc0 = last_alpha * lc0 + (1.0f - last_alpha) * acc0; lc0 = r2.x;
-                    dL_dopa += (r2.x - acc0) * dpix0; v[0] = dchannel_dcolor * dpix0;
-                    acc1 = last_alpha * lc1 + (1.0f - last_alpha) * acc1; lc1 = r2.y;
-                    dL_dopa += (r2.y - acc1) * dpix1; v[1] = dchannel_dcolor * dpix1;
-                    acc2 = last_alpha * lc2 + (1.0f - last_alpha) * acc2; lc2 = r2.z;
-                    dL_dopa += (r2.z - acc2) * dpix2; v[2] = dchannel_dcolor * dpix2;
-                    accum_depth_rec = last_alpha * last_depth + (1.0f - last_alpha) * accum_depth_rec;
-                    last_depth = r0.z;
-                    dL_dopa += (r0.z - accum_depth_rec) * dL_ddepth;
-                    accum_alpha_rec = last_alpha + (1.0f - last_alpha) * accum_alpha_rec;
-                    dL_dopa += (1.0f - accum_alpha_rec) * dL_dalpha;
-                    dL_dopa *= T;
-                    last_alpha = alpha;
-                    dL_dopa += (-T_final / (1.0f - alpha)) * bg_dot;
-                    const float dL_dG = r1.w * dL_dopa;
-                    const float gdx = G * dx, gdy = G * dy;
-                    const float dG_ddelx = -gdx * r1.x - gdy * r1.y;
-                    const float dG_ddely = -gdy * r1.z - gdx * r1.y;
-                    v[3] = dL_dG * dG_ddelx * ddelx_dx;
-                    v[4] = dL_dG * dG_ddely * ddely_dy;
-                    v[5] = -0.5f * gdx * dx * dL_dG;
-                    v[6] = -0.5f * gdx * dy * dL_dG;
-                    v[7] = -0.5f * gdy * dy * dL_dG;
-                    v[8] = G * dL_dopa;
+            for (int u = 0; u < PER_LANE; u++) {
+                const int sl = (int)lane + u * 32;
+                if (nid[u] != 0xFFFFFFFFu) {
+                    s_id[buf][sl] = nid[u];
+                    const float4* src = rec + 3 * (size_t)nid[u];
+                    float4* dst = &s_rec[buf][sl * 3];
+                    cp_async16b(dst, src);
+                    cp_async16b(dst + 1, src + 1);
+                    cp_async16b(dst + 2, src + 2);
                 }
-                float* dst = accum + 12 * (size_t)s_id[buf][j];
-                if (__popc(vmask) <= 2) {
-                    // one or two pixels: cheaper to let them add directly than to reduce
-                    if (valid) {
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+
+        load_ids(0); stage(0);
+        load_ids(1); stage(1);
+        load_ids(2);
+        int toDo = walk;
+        for (int i = 0; i < rounds; i++, toDo -= BATCH) {
+            const int buf = i % NSTAGE;
+            stage((i + 2) % NSTAGE);
+            load_ids(i + 3);
+            asm volatile("cp.async.wait_group 2;" ::: "memory");
+            __syncwarp();
+            const int n = min(BATCH, toDo);
+            const float4* r = s_rec[buf];
+            // entry j of this round sits at list position pos(j) = walk-1-(i*BATCH+j); the reference's
+            // `contributor` for it equals pos(j) (backward.cu:499-501: skip if contributor >= last_contributor)
+            const int pos0 = walk - 1 - i * BATCH;
+            for (int g = 0; g < n; g += 32) {
+                const int jj = g + (int)lane;
+                bool keep = false;
+                if (jj < n) {
+                    const float4 c0 = r[3 * jj];
+                    float ex, ey;
+                    unpack_cull_extent(__float_as_uint(r[3 * jj + 2].w), ex, ey);
+                    const float ddx = fmaxf(fmaxf(rx0 - c0.x, c0.x - rx1), 0.0f);
+                    const float ddy = fmaxf(fmaxf(ry0 - c0.y, c0.y - ry1), 0.0f);
+                    keep = !(ddx > ex) && !(ddy > ey);
+                }
+                uint32_t mask = __ballot_sync(0xffffffffu, keep);
+                // Survivors four at a time.  Phase 1 (independent: ILP) evaluates G/alpha of the four; phase 2
+                // runs the transmittance / accumulated-colour recurrences in list order; phase 3 reduces the
+                // 4 x 9 partial gradients with four interleaved butterflies.
+                while (mask) {
+                    int j[4];
+                    bool v_ok[4];
 #pragma unroll
-                        for (int k = 0; k < 9; k++) atomicAdd(dst + k, v[k]);
+                    for (int u = 0; u < 4; u++) {
+                        v_ok[u] = mask != 0;
+                        j[u] = v_ok[u] ? g + __ffs(mask) - 1 : j[0];
+                        mask &= mask - 1;
                     }
-                } else {
-                    const float total = warp_reduce9(v, lane);
-                    if (writer) atomicAdd(dst + slot, total);
+                    float G[4], alpha[4], dx[4], dy[4];
+                    float4 r0[4], r1[4];
+                    bool valid[4];
+                    uint32_t vm[4];
+    #pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        r0[u] = r[3 * j[u]]; r1[u] = r[3 * j[u] + 1];
+                        dx[u] = __fsub_rn(r0[u].x, pxf); dy[u] = __fsub_rn(r0[u].y, pyf);
+                        const float power = pair_power(dx[u], dy[u], r1[u].x, r1[u].y, r1[u].z);
+                        G[u] = expf(power);
+                        alpha[u] = fminf(0.99f, __fmul_rn(r1[u].w, G[u]));
+                        valid[u] = v_ok[u] && (pos0 - j[u] < last_contributor) && !(power > 0.0f) && !(alpha[u] < 1.0f / 255.0f);
+                        vm[u] = __ballot_sync(0xffffffffu, valid[u]);
+                    }
+                    if ((vm[0] | vm[1] | vm[2] | vm[3]) == 0) continue;
+                    float v[4][9];
+    #pragma unroll
+                    for (int u = 0; u < 4; u++) {
+    #pragma unroll
+                        for (int k = 0; k < 9; k++) v[u][k] = 0.0f;
+                        if (valid[u]) {
+                            const float4 r2 = r[3 * j[u] + 2];
+                            const float a = alpha[u];
+                            T = T / (1.0f - a);
+                            const float dchannel_dcolor = a * T;
+                            float dL_dopa = 0.0f;
+                            acc0 = last_alpha * lc0 + (1.0f - last_alpha) * acc0; lc0 = r2.x;
+                            dL_dopa += (r2.x - acc0) * dpix0; v[u][0] = dchannel_dcolor * dpix0;
+                            acc1 = last_alpha * lc1 + (1.0f - last_alpha) * acc1; lc1 = r2.y;
+                            dL_dopa += (r2.y - acc1) * dpix1; v[u][1] = dchannel_dcolor * dpix1;
+                            acc2 = last_alpha * lc2 + (1.0f - last_alpha) * acc2; lc2 = r2.z;
+                            dL_dopa += (r2.z - acc2) * dpix2; v[u][2] = dchannel_dcolor * dpix2;
+                            accum_depth_rec = last_alpha * last_depth + (1.0f - last_alpha) * accum_depth_rec;
+                            last_depth = r0[u].z;
+                            dL_dopa += (r0[u].z - accum_depth_rec) * dL_ddepth;
+                            accum_alpha_rec = last_alpha + (1.0f - last_alpha) * accum_alpha_rec;
+                            dL_dopa += (1.0f - accum_alpha_rec) * dL_dalpha;
+                            dL_dopa *= T;
+                            last_alpha = a;
+                            dL_dopa += (-T_final / (1.0f - a)) * bg_dot;
+                            const float dL_dG = r1[u].w * dL_dopa;
+                            const float gdx = G[u] * dx[u], gdy = G[u] * dy[u];
+                            const float dG_ddelx = -gdx * r1[u].x - gdy * r1[u].y;
+                            const float dG_ddely = -gdy * r1[u].z - gdx * r1[u].y;
+                            v[u][3] = dL_dG * dG_ddelx * ddelx_dx;
+                            v[u][4] = dL_dG * dG_ddely * ddely_dy;
+                            v[u][5] = -0.5f * gdx * dx[u] * dL_dG;
+                            v[u][6] = -0.5f * gdx * dy[u] * dL_dG;
+                            v[u][7] = -0.5f * gdy * dy[u] * dL_dG;
+                            v[u][8] = G[u] * dL_dopa;
+                        }
+                    }
+                    float total[4];
+    #pragma unroll
+                    for (int u = 0; u < 4; u++) total[u] = warp_reduce9(v[u], lane);
+    #pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (vm[u] != 0 && writer) atomicAdd(accum + 12 * (size_t)s_id[buf][j[u]] + slot, total[u]);
                 }
             }
+            __syncwarp();  // buffer `buf` is re-filled by the next iteration's stage()
         }
-        __syncthreads();
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
     }
 }
 
@@ -240,15 +271,21 @@ cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, 
 {
     StageTimer timer(GHR_STAGE_BLEND_BWD, s);
     count_launch();
-    constexpr int WARPS = 2;
-    dim3 grid(((p.W + GHR_TILE - 1) / GHR_TILE) * (8 / WARPS), (p.H + GHR_TILE - 1) / GHR_TILE);
-    blend_backward_kernel<WARPS><<<grid, WARPS * 32, 0, s>>>(
-        p.W, p.H, reinterpret_cast<const uint2*>(img + L.i_ranges),
-        reinterpret_cast<const SortHeader*>(binning + L.b_header),
+    const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
+    ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
+    // the queue head is scratch state inside the (otherwise read-only) geometry buffer
+    cudaError_t e = cudaMemsetAsync(&hdr->blend_bwd_ticket, 0, sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    const int64_t items = (int64_t)tiles * 8;
+    int64_t ctas = (items + kBwdWarps - 1) / kBwdWarps;
+    if (ctas > 148 * kBwdCtasPerSm) ctas = 148 * kBwdCtasPerSm;
+    blend_backward_kernel<<<(unsigned)ctas, kBwdWarps * 32, 0, s>>>(
+        p.W, p.H, tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
+        reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),
         reinterpret_cast<const uint32_t*>(binning + L.b_vals_a), reinterpret_cast<const uint32_t*>(binning + L.b_vals_b),
-        reinterpret_cast<const float4*>(geom + L.g_rec), reinterpret_cast<const ghr_geom_header*>(geom + L.g_header),
-        L.capacity, p.background, reinterpret_cast<const float*>(img + L.i_final_T),
-        reinterpret_cast<const uint32_t*>(img + L.i_n_contrib), dL_dpix, dL_ddepth, dL_dalpha, accum);
+        reinterpret_cast<const float4*>(geom + L.g_rec), hdr, L.capacity, p.background,
+        reinterpret_cast<const float*>(img + L.i_final_T), reinterpret_cast<const uint32_t*>(img + L.i_n_contrib), dL_dpix,
+        dL_ddepth, dL_dalpha, accum);
     return cudaGetLastError();
 }
 

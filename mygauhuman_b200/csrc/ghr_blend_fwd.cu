@@ -1,14 +1,18 @@
 // Per-tile front-to-back alpha blending with depth and alpha-mask outputs
 // (reference forward.cu:261-383 renderCUDA).
 //
-// Work decomposition (ours): a 16x16 tile is covered by 8 warps, each owning an
-// 8x4 pixel block; a CTA holds WARPS of them (2 by default, so a heavy tile is
-// spread over 4 CTAs / SMs instead of serialising on one).  Per CTA, Gaussians
-// are staged in batches of packed 48-byte records
+// Work decomposition (ours): a 16x16 tile is covered by eight 8x4 pixel blocks;
+// one (tile, block) pair is a work item processed by ONE warp, independently of
+// every other warp (no block-level barrier anywhere).  The kernel is persistent:
+// 148 x 5 CTAs of 4 warps pull items from a global queue ordered by decreasing
+// tile-list length (tile_order_kernel), so the few heavy tiles of a human-shaped
+// scene start first and spread over all SMs.  Per warp, Gaussians are staged in
+// batches of 64 packed 48-byte records
 //   {px,py,depth,radius | conic.xyz,opacity | r,g,b,cull-extent}
-// with cp.async (LDGSTS) into a double-buffered shared-memory ring, so the
-// inner loop never touches global memory (the reference gathers colour and
-// depth from global per contributing pair, forward.cu:360,362).
+// with cp.async (LDGSTS) into a 3-deep private shared-memory ring (list ids are
+// fetched one batch ahead of the record copies), so the inner loop never
+// touches global memory (the reference gathers colour and depth from global per
+// contributing pair, forward.cu:360,362).
 //
 // Per warp and batch: (1) each lane tests one Gaussian's conservative bounding
 // box (pack_cull_extent) against the warp's 8x4 block; a ballot yields the
@@ -38,71 +42,89 @@ __device__ __forceinline__ void cp_async_wait()
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-template <int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
-    int W, int H, const uint2* __restrict__ ranges, const SortHeader* __restrict__ sh,
-    const uint32_t* __restrict__ vals_a, const uint32_t* __restrict__ vals_b, const float4* __restrict__ rec,
-    const ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
+constexpr int kBlendWarps = 4;    // warps per CTA (independent workers)
+constexpr int kBlendBatch = 64;   // Gaussians per staging round and warp
+constexpr int kBlendStages = 3;
+constexpr int kBlendCtasPerSm = 5;
+
+__global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(
+    int W, int H, int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
+    const SortHeader* __restrict__ sh, const uint32_t* __restrict__ vals_a, const uint32_t* __restrict__ vals_b,
+    const float4* __restrict__ rec, ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
     float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha,
     float* __restrict__ final_T, uint32_t* __restrict__ n_contrib)
 {
-    constexpr int THREADS = WARPS * 32;
-    constexpr int SUBS = 8 / WARPS;     // CTAs per tile
-    constexpr int BATCH = 128;          // Gaussians staged per round
-    constexpr int PER_THREAD = BATCH / THREADS > 0 ? BATCH / THREADS : 1;
-    static_assert(BATCH % THREADS == 0 || THREADS > BATCH, "batch/threads");
-    __shared__ __align__(16) float4 s_rec[2][BATCH * 3];
+    constexpr int BATCH = kBlendBatch, NSTAGE = kBlendStages, PER_LANE = BATCH / 32;
+    __shared__ __align__(16) float4 s_all[kBlendWarps][NSTAGE][BATCH * 3];
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float4(*s_rec)[BATCH * 3] = s_all[warp];
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
-    const uint32_t tile_x = blockIdx.x / SUBS, sub = blockIdx.x % SUBS, tile_y = blockIdx.y;
-    const uint32_t wb = sub * WARPS + warp;  // which of the tile's eight 8x4 blocks
-    const uint32_t bx0 = tile_x * GHR_TILE + (wb & 1u) * 8u, by0 = tile_y * GHR_TILE + (wb >> 1) * 4u;
-    const uint32_t pixx = bx0 + (lane & 7u), pixy = by0 + (lane >> 3);
-    const bool inside = pixx < (uint32_t)W && pixy < (uint32_t)H;
-    const float pxf = (float)pixx, pyf = (float)pixy;
-    const float rx0 = (float)bx0, rx1 = (float)(bx0 + 7u), ry0 = (float)by0, ry1 = (float)(by0 + 3u);
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
-    const uint2 range = overflow ? make_uint2(0, 0) : ranges[tile_y * gx + tile_x];
     const uint32_t* __restrict__ point_list = sh->sorted_sel ? vals_b : vals_a;
+    const float bg0 = bg[0], bg1 = bg[1], bg2 = bg[2];
+    const uint32_t n_items = (uint32_t)tiles * 8u;
 
-    const int todo_total = (int)(range.y - range.x);
-    const int rounds = (todo_total + BATCH - 1) / BATCH;
+    for (;;) {
+        uint32_t item = 0;
+        if (lane == 0) item = atomicAdd(&hdr->blend_fwd_ticket, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= n_items) break;
+        const uint32_t tile = order[item >> 3], wb = item & 7u;  // which of the tile's eight 8x4 blocks
+        const uint32_t tile_x = tile % gx, tile_y = tile / gx;
+        const uint32_t bx0 = tile_x * GHR_TILE + (wb & 1u) * 8u, by0 = tile_y * GHR_TILE + (wb >> 1) * 4u;
+        const uint32_t pixx = bx0 + (lane & 7u), pixy = by0 + (lane >> 3);
+        const bool inside = pixx < (uint32_t)W && pixy < (uint32_t)H;
+        const float pxf = (float)pixx, pyf = (float)pixy;
+        const float rx0 = (float)bx0, rx1 = (float)(bx0 + 7u), ry0 = (float)by0, ry1 = (float)(by0 + 3u);
+        const uint2 range = overflow ? make_uint2(0, 0) : ranges[tile];
+        const int todo_total = (int)(range.y - range.x);
+        const int rounds = (todo_total + BATCH - 1) / BATCH;
 
-    auto stage = [&](int round, int buf) {
+        // Staging pipeline.  A record gather is two dependent L2 round trips (list entry -> record); the list
+        // entries of a round are therefore loaded into registers one round before their records are copied.
+        uint32_t nid[PER_LANE];
+        auto load_ids = [&](int round) {
 #pragma unroll
-        for (int u = 0; u < PER_THREAD; u++) {
-            const uint32_t slot = threadIdx.x + u * THREADS;
-            const uint32_t k = range.x + (uint32_t)round * BATCH + slot;
-            if (slot < (uint32_t)BATCH && k < range.y) {
-                const uint32_t id = point_list[k];
-                const float4* src = rec + 3 * (size_t)id;
-                float4* dst = &s_rec[buf][slot * 3];
-                cp_async16(dst, src);
-                cp_async16(dst + 1, src + 1);
-                cp_async16(dst + 2, src + 2);
+            for (int u = 0; u < PER_LANE; u++) {
+                const uint32_t k = range.x + (uint32_t)round * BATCH + lane + u * 32;
+                nid[u] = (round < rounds && k < range.y) ? point_list[k] : 0xFFFFFFFFu;
             }
+        };
+        auto stage = [&](int buf) {  // copies the records of the ids held in nid[]
+#pragma unroll
+            for (int u = 0; u < PER_LANE; u++) {
+                if (nid[u] != 0xFFFFFFFFu) {
+                    const float4* src = rec + 3 * (size_t)nid[u];
+                    float4* dst = &s_rec[buf][(lane + u * 32) * 3];
+                    cp_async16(dst, src);
+                    cp_async16(dst + 1, src + 1);
+                    cp_async16(dst + 2, src + 2);
+                }
+            }
+            cp_async_commit();
+        };
+
+        bool done = !inside;
+        float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, wsum = 0.f, Dacc = 0.f;
+        uint32_t last_contributor = 0;
+
+        if (rounds > 0) {
+            load_ids(0); stage(0);
+            load_ids(1); stage(1);
+            load_ids(2);
         }
-        cp_async_commit();
-    };
-
-    bool done = !inside;
-    float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, wsum = 0.f, Dacc = 0.f;
-    uint32_t last_contributor = 0;
-
-    if (rounds > 0) stage(0, 0);
-    int toDo = todo_total;
-    for (int i = 0; i < rounds; i++, toDo -= BATCH) {
-        const int buf = i & 1;
-        if (i + 1 < rounds) { stage(i + 1, buf ^ 1); cp_async_wait<1>(); }
-        else cp_async_wait<0>();
-        // barrier doubles as the "whole CTA done" vote (forward.cu:313-315)
-        const int num_done = __syncthreads_count(done);
-        if (num_done == THREADS) break;
-        const int n = min(BATCH, toDo);
-        const float4* r = s_rec[buf];
-        const uint32_t base = (uint32_t)i * BATCH;  // list position of r[0]
-        if (!__all_sync(0xffffffffu, done)) {
+        int toDo = todo_total;
+        for (int i = 0; i < rounds; i++, toDo -= BATCH) {
+            const int buf = i % NSTAGE;
+            stage((i + 2) % NSTAGE);  // records of round i+2 (an empty group past the end keeps the count uniform)
+            load_ids(i + 3);
+            cp_async_wait<2>();       // this lane's copies for rounds <= i have landed
+            __syncwarp();             // ... and everybody else's
+            if (__all_sync(0xffffffffu, done)) break;  // forward.cu:313-315, per block instead of per tile
+            const int n = min(BATCH, toDo);
+            const float4* r = s_rec[buf];
+            const uint32_t base = (uint32_t)i * BATCH;  // list position of r[0]
             for (int g = 0; g < n; g += 32) {
                 // (1) conservative bounding-box cull, one Gaussian per lane
                 const int jj = g + (int)lane;
@@ -157,20 +179,21 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
                     if (__all_sync(0xffffffffu, done)) { mask = 0; g = n; }
                 }
             }
+            __syncwarp();  // buffer `buf` is re-filled by the stage() of the next iteration (round i+3)
         }
-        __syncthreads();  // buffer `buf` is re-filled two rounds later by stage(i+2)
-    }
-    cp_async_wait<0>();
+        cp_async_wait<0>();
+        __syncwarp();
 
-    if (inside) {
-        const size_t pix = (size_t)pixy * W + pixx, HW = (size_t)H * W;
-        final_T[pix] = T;
-        n_contrib[pix] = last_contributor;
-        out_color[pix] = __fmaf_rn(T, bg[0], C0);
-        out_color[HW + pix] = __fmaf_rn(T, bg[1], C1);
-        out_color[2 * HW + pix] = __fmaf_rn(T, bg[2], C2);
-        out_alpha[pix] = wsum;
-        out_depth[pix] = Dacc;
+        if (inside) {
+            const size_t pix = (size_t)pixy * W + pixx, HW = (size_t)H * W;
+            final_T[pix] = T;
+            n_contrib[pix] = last_contributor;
+            out_color[pix] = __fmaf_rn(T, bg0, C0);
+            out_color[HW + pix] = __fmaf_rn(T, bg1, C1);
+            out_color[2 * HW + pix] = __fmaf_rn(T, bg2, C2);
+            out_alpha[pix] = wsum;
+            out_depth[pix] = Dacc;
+        }
     }
 }
 
@@ -180,16 +203,20 @@ cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, c
 {
     StageTimer timer(GHR_STAGE_BLEND_FWD, s);
     count_launch();
-    constexpr int WARPS = 2;
-    dim3 grid(((p.W + GHR_TILE - 1) / GHR_TILE) * (8 / WARPS), (p.H + GHR_TILE - 1) / GHR_TILE);
+    const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
+    const int64_t items = (int64_t)tiles * 8;
+    int64_t ctas = (items + kBlendWarps - 1) / kBlendWarps;
+    if (ctas > 148 * kBlendCtasPerSm) ctas = 148 * kBlendCtasPerSm;
     const int64_t capacity = L.capacity;
-    blend_forward_kernel<WARPS><<<grid, WARPS * 32, 0, s>>>(
-        p.W, p.H, reinterpret_cast<const uint2*>(img + L.i_ranges),
-        reinterpret_cast<const SortHeader*>(binning + L.b_header),
+    ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
+    cudaError_t e = cudaMemsetAsync(&hdr->blend_fwd_ticket, 0, sizeof(uint32_t), s);  // render may run twice per preprocess
+    if (e != cudaSuccess) return e;
+    blend_forward_kernel<<<(unsigned)ctas, kBlendWarps * 32, 0, s>>>(
+        p.W, p.H, tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
+        reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),
         reinterpret_cast<const uint32_t*>(binning + L.b_vals_a), reinterpret_cast<const uint32_t*>(binning + L.b_vals_b),
-        reinterpret_cast<const float4*>(geom + L.g_rec), reinterpret_cast<const ghr_geom_header*>(geom + L.g_header),
-        capacity, p.background, out_color, out_depth, out_alpha, reinterpret_cast<float*>(img + L.i_final_T),
-        reinterpret_cast<uint32_t*>(img + L.i_n_contrib));
+        reinterpret_cast<const float4*>(geom + L.g_rec), hdr, capacity, p.background, out_color,
+        out_depth, out_alpha, reinterpret_cast<float*>(img + L.i_final_T), reinterpret_cast<uint32_t*>(img + L.i_n_contrib));
     return cudaGetLastError();
 }
 

@@ -347,7 +347,30 @@ __global__ void __launch_bounds__(1024, 1) nearest_vertex_smem_kernel(int P, int
         // phase B: shells r = 1, 2, ...; a cell is skipped when its box is provably farther than the best so far
         bool done = !live;
         for (int r = 1; r <= maxr + 1; r++) {
-            if (!done) {
+            if (!done && r == 1) {
+                // 3x3x3 shell: per axis, a neighbour slab is needed only if its face is closer than the bound
+                // from phase A (group-uniform).  The few needed cells are walked one after the other with the
+                // eight lanes splitting each cell's vertices.
+                const float bnd = best;
+                const float fxm = fmaxf(qx - (g.minx + c.x * g.cell) - eps, 0.0f), fxp = fmaxf((g.minx + (c.x + 1) * g.cell) - qx - eps, 0.0f);
+                const float fym = fmaxf(qy - (g.miny + c.y * g.cell) - eps, 0.0f), fyp = fmaxf((g.miny + (c.y + 1) * g.cell) - qy - eps, 0.0f);
+                const float fzm = fmaxf(qz - (g.minz + c.z * g.cell) - eps, 0.0f), fzp = fmaxf((g.minz + (c.z + 1) * g.cell) - qz - eps, 0.0f);
+                const float xm2 = fxm * fxm * 0.998f, xp2 = fxp * fxp * 0.998f, ym2 = fym * fym * 0.998f,
+                            yp2 = fyp * fyp * 0.998f, zm2 = fzm * fzm * 0.998f, zp2 = fzp * fzp * 0.998f;
+                const int ox0 = (c.x > 0 && xm2 <= bnd) ? -1 : 0, ox1 = (c.x + 1 < g.nx && xp2 <= bnd) ? 1 : 0;
+                const int oy0 = (c.y > 0 && ym2 <= bnd) ? -1 : 0, oy1 = (c.y + 1 < g.ny && yp2 <= bnd) ? 1 : 0;
+                const int oz0 = (c.z > 0 && zm2 <= bnd) ? -1 : 0, oz1 = (c.z + 1 < g.nz && zp2 <= bnd) ? 1 : 0;
+                for (int oz = oz0; oz <= oz1; oz++)
+                    for (int oy = oy0; oy <= oy1; oy++)
+                        for (int ox = ox0; ox <= ox1; ox++) {
+                            if ((ox | oy | oz) == 0) continue;  // own cell: phase A
+                            const float lb = (ox < 0 ? xm2 : (ox > 0 ? xp2 : 0.0f)) + (oy < 0 ? ym2 : (oy > 0 ? yp2 : 0.0f)) +
+                                             (oz < 0 ? zm2 : (oz > 0 ? zp2 : 0.0f));
+                            if (lb > bnd) continue;
+                            const int cid = ((c.z + oz) * g.ny + (c.y + oy)) * g.nx + (c.x + ox);
+                            scan(s_starts[cid], s_starts[cid + 1], sub, 8);
+                        }
+            } else if (!done) {
                 const int z0 = max(c.z - r, 0), z1 = min(c.z + r, g.nz - 1);
                 const int y0 = max(c.y - r, 0), y1 = min(c.y + r, g.ny - 1);
                 const int x0 = max(c.x - r, 0), x1 = min(c.x + r, g.nx - 1);
