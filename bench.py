@@ -58,6 +58,9 @@ def parse():
     ap.add_argument("--cpu-iters", type=int, default=20, help="CPU-oracle iterations for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--host-profile", action="store_true", help="cProfile of 50 un-synchronised steps to stderr")
+    ap.add_argument("--mode", default="graph", choices=["graph", "eager"],
+                    help="ours: replay the step as one CUDA graph (mygauhuman_b200.graphed.GraphedRenderStep, default) "
+                         "or issue it kernel by kernel through the eager operator API")
     ap.add_argument("--sync-free", action="store_true",
                     help="ours: size the binning buffer from the previous step instead of a blocking read")
     return ap.parse_args()
@@ -196,7 +199,8 @@ def unpack(vec):
 
 
 def linear_loss(color, depth, alpha, targets):
-    return (color * targets[0:3]).sum() + (depth * targets[3:4]).sum() + (alpha * targets[4:5]).sum()
+    """sum(colour*t[0:3]) + sum(depth*t[3]) + sum(alpha*t[4]): every output plane gets a dense random gradient."""
+    return (torch.cat([color, depth, alpha]) * targets).sum()
 
 
 # ---------------------------------------------------------------------------
@@ -208,7 +212,7 @@ class OursArm:
     (mygauhuman_b200.diff_gaussian_rasterization), all on libghr.so through the C ABI."""
     name = "ours"
 
-    def __init__(self, wl, dev, sync_free):
+    def __init__(self, wl, dev, sync_free, graph=False):
         from mygauhuman_b200 import _lib
         from mygauhuman_b200 import diff_gaussian_rasterization as dgr
         from mygauhuman_b200.lbs import SMPLDeformer
@@ -221,9 +225,22 @@ class OursArm:
         self.bg = wl["bg"].to(dev)
         self.sync_free = sync_free
         self.last_n = None
+        self.graphed, self.use_graph = None, False
+        if graph:
+            from mygauhuman_b200.graphed import GraphedRenderStep
+            cam = wl["views"][0]["cam"]
+            assert all(v["cam"]["tanfovx"] == cam["tanfovx"] and v["cam"]["tanfovy"] == cam["tanfovy"] for v in wl["views"])
+            self.graphed = GraphedRenderStep(self.deformer, self.leaves, self.big, self.t_vertices, wl["H"], wl["W"],
+                                             cam["tanfovx"], cam["tanfovy"], self.bg, linear_loss, sh_degree=3)
+
+    def capture(self, vecs, targets_dev):
+        self.graphed.capture(vecs, [targets_dev])
 
     def step(self, view, vec_dev, targets_dev):
         dgr, L = self.dgr, self.leaves
+        if self.graphed is not None and self.use_graph:
+            loss = self.graphed(vec_dev, targets_dev)
+            return loss, [L[k].grad for k in ("xyz", "features", "opacity_logit", "log_scale", "rotation")]
         camd, pose = unpack(vec_dev)
         cam = view["cam"]
         d = self.deformer.deform_gaussians(L["xyz"], pose, self.big, self.t_vertices, normals=L["normals"],
@@ -439,7 +456,7 @@ def main():
     P, W, H = wl["P"], wl["W"], wl["H"]
     X, tiles = W * H, ((W + 15) // 16) * ((H + 15) // 16)
     if args.impl == "ours":
-        arm = OursArm(wl, dev, args.sync_free)
+        arm = OursArm(wl, dev, args.sync_free, graph=(args.mode == "graph"))
     else:
         try:
             arm = ReferenceArm(wl, dev)
@@ -462,7 +479,14 @@ def main():
 
     def one_step(i, e2e):
         k = i % len(views)
-        if e2e:
+        if args.impl == "ours" and arm.use_graph:
+            # the graphed step owns the static input buffers: it copies from pinned host memory itself (e2e), or from
+            # the resident device copies (the target planes already sit in its static buffer)
+            if e2e:
+                loss, grads = arm.step(views[k], vec_host[k], targets_host)
+            else:
+                loss, grads = arm.step(views[k], vec_dev[k], arm.graphed.loss_inputs[0])
+        elif e2e:
             vec_stage.copy_(vec_host[k], non_blocking=True)
             targets_stage.copy_(targets_host, non_blocking=True)
             loss, grads = arm.step(views[k], vec_stage, targets_stage)
@@ -497,6 +521,15 @@ def main():
         one_step(i, False)
         one_step(i, True)
     torch.cuda.synchronize()
+    graphed = args.impl == "ours" and args.mode == "graph"
+    if graphed:
+        # capacity sized from every view this rank cycles through, then one capture; warm the replay path too
+        arm.capture(vec_dev, targets_dev)
+        arm.use_graph = True
+        for i in range(Wm):
+            one_step(i, False)
+            one_step(i, True)
+        torch.cuda.synchronize()
 
     if args.host_profile and rank == 0:
         import cProfile, pstats
@@ -521,6 +554,16 @@ def main():
     ms_dev = timed(K, False)
     launches = (arm._lib.launch_count() - launches0) if args.impl == "ours" else None
     ms_e2e = timed(K, True)
+    eager = None
+    if graphed:
+        launches = K * arm.graphed.kernels_per_replay  # libghr kernels inside the K replays
+        if not arm.graphed.check():  # a view overflowed the captured binning capacity: re-captured, measure again
+            ms_dev, ms_e2e = timed(K, False), timed(K, True)
+            assert arm.graphed.check()
+        arm.use_graph = False  # the same step issued kernel by kernel, for comparison
+        for i in range(3):
+            one_step(i, False)
+        eager = (timed(K, False), timed(K, True))
     clocks = sampler.stop() if rank == 0 else None
 
     # per-stage device time (ours): a third identical pass with the library's stage events enabled
@@ -569,14 +612,20 @@ def main():
         "config": {"workload": args.workload, "desc": WORKLOADS[args.workload]["desc"], "P": P, "W": W, "H": H,
                    "sh_degree": 3, "views_cycled": len(views) * world, "parallelism": f"view-sharded dp{world}",
                    "l2": "flushed between steps (256 MiB fill outside the per-step event pair)",
-                   "sync_free": bool(args.sync_free)},
+                   "sync_free": bool(args.sync_free),
+                   "mode": (args.mode if args.impl == "ours" else "eager")},
         "e2e": {"value": round(e2e_val, 2), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-                "what": "public API step (SMPLDeformer.deform_gaussians -> GaussianRasterizer -> loss -> backward); "
+                "what": "public API step (GraphedRenderStep replay, or in eager mode SMPLDeformer.deform_gaussians -> "
+                        "GaussianRasterizer -> loss -> backward); "
                         "camera + SMPL pose + 5 target planes copied from pinned host memory and loss.item() read back "
                         "inside every step's event pair; Gaussian parameters stay resident (model state)"},
         "gpu_launches": launches, "clocks": clocks,
     }
+    if eager is not None:
+        line["eager"] = {"value": round(views_per_step * K / (eager[0] * 1e-3), 2), "ms_per_step": round(eager[0] / K, 4),
+                         "e2e": round(views_per_step * K / (eager[1] * 1e-3), 2),
+                         "what": "same step through the eager operator API (one Python call per kernel); host-bound"}
     if roof is not None:
         line["roofline"] = roof
         line["stages"] = stages

@@ -44,6 +44,7 @@ def _remember_capacity(binning, capacity):
 # (one 4-byte host read after the first kernel).
 _capacity = None
 _pinned = {}
+_last_geom = None   # geometry state of the most recent forward (graphed.py reads num_rendered from it on the device)
 
 
 def set_sync_free_capacity(capacity):
@@ -164,6 +165,8 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         _remember_capacity(binning, capacity)
         if debug:
             read_status(geom, raise_on_error=True)
+    global _last_geom
+    _last_geom = geom
     return num_rendered, out_color, out_depth, out_alpha, radii, geom, binning, img
 
 

@@ -1,0 +1,162 @@
+"""CUDA-graph capture of one full hot-path step (LBS + covariance + SH -> rasteriser forward -> loss ->
+rasteriser backward -> LBS backward).
+
+At the ZJU shape the step is ~45 kernel launches of a few microseconds each: issued one by one from Python
+the host, not the GPU, sets the pace (measured: 0.85 ms/step of host issue time vs 0.55 ms of GPU work).
+The reference has the same problem many times over (~60 ATen launches for LBS alone).  Here the
+whole step is captured once into a CUDA graph and replayed per view with one launch:
+
+* the per-view inputs (camera matrices, camera position, SMPL pose/shape/R/Th: 129 floats, and whatever the
+  loss needs, e.g. the ground-truth image) live in static device buffers that are overwritten before a replay;
+* the rasteriser runs in its sync-free mode with a fixed binning capacity (no host read of num_rendered);
+  the largest num_rendered ever seen is tracked ON THE DEVICE inside the graph, so an overflow of that
+  capacity (which would silently drop splats) is detected at the next host synchronisation and the graph is
+  re-captured with a larger capacity;
+* gradients land in the leaves' ``.grad`` tensors, which are static across replays.
+
+Nothing here changes numerics: the captured kernels are the same ones the eager API launches.
+"""
+import torch
+
+from . import _lib
+from . import diff_gaussian_rasterization as dgr
+from .diff_gaussian_rasterization import _C
+
+PACK = dict(view=(0, 16), proj=(16, 32), campos=(32, 35), poses=(35, 107), shapes=(107, 117), R=(117, 126), Th=(126, 129))
+PACK_FLOATS = 129
+
+
+def pack_view(world_view_transform, full_proj_transform, camera_center, smpl_param):
+    """[view 16 | proj 16 | campos 3 | poses 72 | shapes 10 | R 9 | Th 3] -> one fp32 vector (any device)."""
+    v = torch.cat([world_view_transform.reshape(-1), full_proj_transform.reshape(-1), camera_center.reshape(-1),
+                   smpl_param["poses"].reshape(-1), smpl_param["shapes"].reshape(-1), smpl_param["R"].reshape(-1),
+                   smpl_param["Th"].reshape(-1)]).float()
+    assert v.numel() == PACK_FLOATS, "expects 72 pose and 10 shape coefficients"
+    return v
+
+
+def unpack_view(vec):
+    g = lambda k: vec[PACK[k][0]:PACK[k][1]]
+    cam = dict(view=g("view").view(4, 4), proj=g("proj").view(4, 4), campos=g("campos"))
+    pose = dict(poses=g("poses").view(1, 72), shapes=g("shapes").view(1, 10), R=g("R").view(3, 3), Th=g("Th").view(1, 3))
+    return cam, pose
+
+
+class GraphedRenderStep:
+    """One training-style step of the hot path as a replayable CUDA graph.
+
+    leaves: dict of leaf tensors (requires_grad) -- xyz [P,3], log_scale [P,3], rotation [P,4], features [P,M,3],
+            opacity_logit [P,1], normals [P,3] (optional).  Activations (exp / sigmoid) mirror the reference's
+            get_scaling / get_opacity (scene/gaussian_model.py:152-175).
+    loss_fn(color, depth, alpha, *loss_inputs) -> scalar tensor; it is captured too, so it must be sync-free.
+    """
+
+    def __init__(self, deformer, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx, tanfovy, bg,
+                 loss_fn, n_loss_inputs=1, sh_degree=3, scaling_modifier=1.0, capacity_hint=None, use_graph=True):
+        self.deformer, self.leaves = deformer, leaves
+        self.big, self.t_vertices = big_pose_params, t_vertices
+        self.H, self.W, self.tanfovx, self.tanfovy = int(image_height), int(image_width), float(tanfovx), float(tanfovy)
+        self.bg, self.loss_fn, self.sh_degree, self.mod = bg, loss_fn, int(sh_degree), float(scaling_modifier)
+        self.use_graph = use_graph
+        dev = deformer.device
+        self.vec = torch.zeros(PACK_FLOATS, device=dev)
+        self.loss_inputs = None
+        self.n_loss_inputs = n_loss_inputs
+        self.n_seen = torch.zeros(1, dtype=torch.int32, device=dev)  # max num_rendered over all replays (device)
+        self.capacity = None if capacity_hint is None else int(capacity_hint)
+        self.graph = None
+        self.kernels_per_replay = None
+        self.loss = None
+        self.out = None
+
+    # ---- the eager step (also what gets captured) -------------------------------------------------
+    def _eager(self, vec, loss_inputs, capacity):
+        L = self.leaves
+        camd, pose = unpack_view(vec)
+        d = self.deformer.deform_gaussians(L["xyz"], pose, self.big, self.t_vertices, normals=L.get("normals"),
+                                           scaling=torch.exp(L["log_scale"]), rotation=L["rotation"],
+                                           scaling_modifier=self.mod, features=L["features"], sh_degree=self.sh_degree,
+                                           campos=camd["campos"])
+        rs = dgr.GaussianRasterizationSettings(
+            image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=self.bg,
+            scale_modifier=self.mod, viewmatrix=camd["view"], projmatrix=camd["proj"], sh_degree=self.sh_degree,
+            campos=camd["campos"], prefiltered=False, debug=False)
+        means2D = torch.zeros_like(d["means3D"], requires_grad=True)
+        _C.set_sync_free_capacity(capacity)
+        try:
+            color, radii, depth, alpha = dgr.rasterize_gaussians(
+                d["means3D"], means2D, _C_absent(), d["colors"], torch.sigmoid(L["opacity_logit"]), _C_absent(),
+                _C_absent(), d["cov3D"], rs)
+        finally:
+            _C.set_sync_free_capacity(None)
+        if capacity is not None:
+            geom = _C._last_geom
+            torch.maximum(self.n_seen, geom[:4].view(torch.int32), out=self.n_seen)
+        loss = self.loss_fn(color, depth, alpha, *loss_inputs)
+        for t in L.values():
+            t.grad = None
+        loss.backward()
+        return loss, dict(color=color, depth=depth, alpha=alpha, radii=radii, means2D=means2D)
+
+    # ---- capture ------------------------------------------------------------------------------------
+    def _measure(self, vec, loss_inputs):
+        """Exact (blocking) eager step: returns num_rendered of this view."""
+        self._eager(vec, loss_inputs, None)
+        torch.cuda.synchronize()
+        return _C.read_status(_C._last_geom)[0]
+
+    def capture(self, sample_vecs, loss_inputs):
+        """Size the binning capacity from `sample_vecs` (a list of packed views), then capture."""
+        self.loss_inputs = [t.clone() for t in loss_inputs]
+        n_max = max(self._measure(v, self.loss_inputs) for v in sample_vecs)
+        cap = max(int(n_max * 1.5) + 4096, self.capacity or 0)
+        self._capture(cap)
+
+    def _capture(self, capacity):
+        self.capacity = _C._round_cap(capacity)
+        self.n_seen.zero_()
+        if not self.use_graph:
+            return
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(3):  # warm-up on a side stream, as torch.cuda.graph requires
+                self._eager(self.vec, self.loss_inputs, self.capacity)
+        torch.cuda.current_stream().wait_stream(s)
+        for t in self.leaves.values():
+            t.grad = None
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = _lib.launch_count()
+        with torch.cuda.graph(self.graph):
+            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity)
+        self.kernels_per_replay = _lib.launch_count() - n0  # libghr kernels inside one replay
+        self.n_seen.zero_()
+
+    # ---- replay ---------------------------------------------------------------------------------------
+    def __call__(self, vec, *loss_inputs):
+        """Run the step for the view packed in `vec` (device or pinned-host tensor).  Returns the loss tensor
+        (static; overwritten by the next call).  Gradients are in leaves[k].grad."""
+        if self.capacity is None:
+            raise RuntimeError("call capture() first")
+        self.vec.copy_(vec, non_blocking=True)
+        for dst, src in zip(self.loss_inputs, loss_inputs):
+            if src is not dst:
+                dst.copy_(src, non_blocking=True)
+        if self.graph is None:
+            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity)
+        else:
+            self.graph.replay()
+        return self.loss
+
+    def check(self):
+        """Synchronises; if some replay needed more binning capacity than the graph was captured with, re-captures
+        with a larger capacity and returns False (the caller should redo the affected steps)."""
+        n = int(self.n_seen.item())
+        if n > self.capacity:
+            self._capture(int(n * 1.5) + 4096)
+            return False
+        return True
+
+
+def _C_absent():
+    return torch.Tensor([])

@@ -1,0 +1,97 @@
+"""-m gpu: the CUDA-graph step (mygauhuman_b200.graphed.GraphedRenderStep) replays exactly what the eager
+operator API computes, for every view, and notices when a view needs more binning capacity than it was
+captured with.
+
+Tolerance: same kernels on both sides; the only difference is the order of the fp32 atomics in the backward
+accumulators, hence 2e-5 of each gradient tensor's scale (images and loss: 1e-6).
+"""
+import numpy as np
+import pytest
+import torch
+
+from mygauhuman_b200 import synthetic as S
+from tests.common import rel_err as _rel_err
+
+pytestmark = pytest.mark.gpu
+
+P, W, H = 6000, 160, 128
+
+
+def rel_err(a, b):
+    return _rel_err(a.detach().cpu().numpy(), b.detach().cpu().numpy())
+
+
+def _loss(color, depth, alpha, targets):
+    return (torch.cat([color, depth, alpha]) * targets).sum()
+
+
+def _setup(smpl_model, radii):
+    from mygauhuman_b200.graphed import GraphedRenderStep, pack_view
+    from mygauhuman_b200.lbs import SMPLDeformer
+    dev = torch.device("cuda")
+    big = S.big_pose_params()
+    tv = S.big_pose_vertices(smpl_model, big)
+    g = S.make_gaussians(P, tv.numpy(), seed=3, sh_degree=3)
+    leaves = {k: g[k].to(dev).requires_grad_(True) for k in ("xyz", "log_scale", "rotation", "features", "opacity_logit",
+                                                             "normals")}
+    vecs, cam = [], None
+    for i, r in enumerate(radii):
+        cam = S.make_camera(W, H, angle=0.7 * i, radius=r, seed=i, focal=537.0 * W / 512)
+        pose = S.make_pose_params(i)
+        pose["Th"] = pose["Th"] * 0.2
+        vecs.append(pack_view(cam["world_view_transform"], cam["full_proj_transform"], cam["camera_center"], pose).to(dev))
+    step = GraphedRenderStep(SMPLDeformer(smpl_model, dev), leaves, {k: v.to(dev) for k, v in big.items()}, tv.to(dev), H, W,
+                             cam["tanfovx"], cam["tanfovy"], torch.zeros(3, device=dev), _loss)
+    targets = torch.randn(5, H, W, generator=torch.Generator().manual_seed(5)).to(dev)
+    return step, leaves, vecs, targets
+
+
+def _eager_reference(step, leaves, vec, targets):
+    loss, out = step._eager(vec, [targets], None)
+    torch.cuda.synchronize()
+    return float(loss.detach()), {k: v.grad.clone() for k, v in leaves.items()}, out["color"].detach().clone()
+
+
+def test_replay_matches_eager_for_every_view(smpl_model):
+    step, leaves, vecs, targets = _setup(smpl_model, [3.0, 3.0, 2.6, 3.4])
+    step.capture(vecs, [targets])
+    assert step.graph is not None and step.kernels_per_replay >= 10
+    for vec in vecs + vecs[:1]:
+        want_loss, want_grads, want_color = _eager_reference(step, leaves, vec, targets)
+        loss = step(vec, targets)
+        torch.cuda.synchronize()
+        assert abs(float(loss) - want_loss) <= 1e-5 * max(1.0, abs(want_loss))
+        np.testing.assert_allclose(step.out["color"].detach().cpu().numpy(), want_color.cpu().numpy(), atol=1e-6)
+        for k, t in leaves.items():
+            assert t.grad is not None, k
+            assert rel_err(t.grad, want_grads[k]) < 2e-5, k
+    assert step.check()
+
+
+def test_pinned_host_inputs_and_static_outputs(smpl_model):
+    step, leaves, vecs, targets = _setup(smpl_model, [3.0, 3.0])
+    step.capture(vecs, [targets])
+    grad_ptr = leaves["xyz"].grad.data_ptr()
+    host_vec = vecs[1].cpu().pin_memory()
+    host_targets = targets.cpu().pin_memory()
+    a = float(step(host_vec, host_targets))
+    b = float(step(vecs[1], targets))
+    assert abs(a - b) <= 1e-5 * max(1.0, abs(b))
+    assert leaves["xyz"].grad.data_ptr() == grad_ptr  # gradients are written in place, replay after replay
+
+
+def test_capacity_overflow_is_detected_and_recaptured(smpl_model):
+    # captured with room for 512 (Gaussian, tile) pairs only; every view needs thousands
+    step, leaves, vecs, targets = _setup(smpl_model, [9.0, 1.6])
+    step.capture(vecs[:1], [targets])
+    step._capture(512)
+    small = step.capacity
+    assert small == 512
+    step(vecs[1], targets)
+    assert not step.check()          # overflow seen on the device, graph re-captured
+    assert step.capacity > small
+    want_loss, want_grads, _ = _eager_reference(step, leaves, vecs[1], targets)
+    loss = step(vecs[1], targets)
+    assert step.check()
+    assert abs(float(loss) - want_loss) <= 1e-5 * max(1.0, abs(want_loss))
+    assert rel_err(leaves["xyz"].grad, want_grads["xyz"]) < 2e-5
