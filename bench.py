@@ -61,6 +61,8 @@ def parse():
     ap.add_argument("--mode", default="graph", choices=["graph", "eager"],
                     help="ours: replay the step as one CUDA graph (mygauhuman_b200.graphed.GraphedRenderStep, default) "
                          "or issue it kernel by kernel through the eager operator API")
+    ap.add_argument("--all-reduce", default="after", choices=["captured", "after"],
+                    help="N>1, graph mode: gradient all-reduce inside the CUDA graph, or issued after each replay")
     ap.add_argument("--sync-free", action="store_true",
                     help="ours: size the binning buffer from the previous step instead of a blocking read")
     return ap.parse_args()
@@ -78,6 +80,7 @@ def init_dist(args):
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29511")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
         dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo", rank=rank, world_size=world,
                                 device_id=torch.device("cuda", local) if torch.cuda.is_available() else None)
     return world, rank, local
@@ -212,7 +215,7 @@ class OursArm:
     (mygauhuman_b200.diff_gaussian_rasterization), all on libghr.so through the C ABI."""
     name = "ours"
 
-    def __init__(self, wl, dev, sync_free, graph=False):
+    def __init__(self, wl, dev, sync_free, graph=False, all_reduce=None):
         from mygauhuman_b200 import _lib
         from mygauhuman_b200 import diff_gaussian_rasterization as dgr
         from mygauhuman_b200.lbs import SMPLDeformer
@@ -231,7 +234,8 @@ class OursArm:
             cam = wl["views"][0]["cam"]
             assert all(v["cam"]["tanfovx"] == cam["tanfovx"] and v["cam"]["tanfovy"] == cam["tanfovy"] for v in wl["views"])
             self.graphed = GraphedRenderStep(self.deformer, self.leaves, self.big, self.t_vertices, wl["H"], wl["W"],
-                                             cam["tanfovx"], cam["tanfovy"], self.bg, linear_loss, sh_degree=3)
+                                             cam["tanfovx"], cam["tanfovy"], self.bg, linear_loss, sh_degree=3,
+                                             all_reduce=all_reduce)
 
     def capture(self, vecs, targets_dev):
         self.graphed.capture(vecs, [targets_dev])
@@ -456,7 +460,8 @@ def main():
     P, W, H = wl["P"], wl["W"], wl["H"]
     X, tiles = W * H, ((W + 15) // 16) * ((H + 15) // 16)
     if args.impl == "ours":
-        arm = OursArm(wl, dev, args.sync_free, graph=(args.mode == "graph"))
+        arm = OursArm(wl, dev, args.sync_free, graph=(args.mode == "graph"),
+                      all_reduce=(args.all_reduce if world > 1 else None))
     else:
         try:
             arm = ReferenceArm(wl, dev)
@@ -477,7 +482,9 @@ def main():
     from mygauhuman_b200.multiview import GradientAllReducer
     reducer = GradientAllReducer()
 
-    def one_step(i, e2e):
+    ar_err = None
+
+    def one_step(i, e2e, want_grads=False):
         k = i % len(views)
         if args.impl == "ours" and arm.use_graph:
             # the graphed step owns the static input buffers: it copies from pinned host memory itself (e2e), or from
@@ -492,12 +499,13 @@ def main():
             loss, grads = arm.step(views[k], vec_stage, targets_stage)
         else:
             loss, grads = arm.step(views[k], vec_dev[k], targets_dev)
-        if world > 1:
-            # view-sharded data parallelism: sum the Gaussian-parameter gradients over ranks (NCCL over NVLink)
+        if world > 1 and not (args.impl == "ours" and arm.use_graph):
+            # view-sharded data parallelism: sum the Gaussian-parameter gradients over ranks (NCCL over NVLink);
+            # the graphed step does this itself on its flat gradient bucket
             reducer(grads)
         if e2e:
             return float(loss.item())  # the device->host read of the step's result
-        return None
+        return grads if want_grads else None
 
     def timed(K, e2e):
         starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
@@ -560,7 +568,11 @@ def main():
         if not arm.graphed.check():  # a view overflowed the captured binning capacity: re-captured, measure again
             ms_dev, ms_e2e = timed(K, False), timed(K, True)
             assert arm.graphed.check()
+        reduced = [g.clone() for g in one_step(0, False, want_grads=True)] if world > 1 else None
         arm.use_graph = False  # the same step issued kernel by kernel, for comparison
+        if world > 1:  # the in-graph all-reduce must give what the bucketed NCCL all-reduce of the eager step gives
+            ref = one_step(0, False, want_grads=True)
+            ar_err = max(float((a - b).abs().max() / b.abs().max().clamp_min(1e-30)) for a, b in zip(reduced, ref))
         for i in range(3):
             one_step(i, False)
         eager = (timed(K, False), timed(K, True))
@@ -613,7 +625,8 @@ def main():
                    "sh_degree": 3, "views_cycled": len(views) * world, "parallelism": f"view-sharded dp{world}",
                    "l2": "flushed between steps (256 MiB fill outside the per-step event pair)",
                    "sync_free": bool(args.sync_free),
-                   "mode": (args.mode if args.impl == "ours" else "eager")},
+                   "mode": (args.mode if args.impl == "ours" else "eager"),
+                   "all_reduce": (None if world == 1 else (args.all_reduce if graphed else "after"))},
         "e2e": {"value": round(e2e_val, 2), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                 "what": "public API step (GraphedRenderStep replay, or in eager mode SMPLDeformer.deform_gaussians -> "
@@ -626,6 +639,8 @@ def main():
         line["eager"] = {"value": round(views_per_step * K / (eager[0] * 1e-3), 2), "ms_per_step": round(eager[0] / K, 4),
                          "e2e": round(views_per_step * K / (eager[1] * 1e-3), 2),
                          "what": "same step through the eager operator API (one Python call per kernel); host-bound"}
+        if ar_err is not None:
+            line["eager"]["graph_vs_eager_reduced_grad_rel_err"] = ar_err
     if roof is not None:
         line["roofline"] = roof
         line["stages"] = stages

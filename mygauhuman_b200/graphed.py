@@ -52,7 +52,10 @@ class GraphedRenderStep:
     """
 
     def __init__(self, deformer, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx, tanfovy, bg,
-                 loss_fn, n_loss_inputs=1, sh_degree=3, scaling_modifier=1.0, capacity_hint=None, use_graph=True):
+                 loss_fn, n_loss_inputs=1, sh_degree=3, scaling_modifier=1.0, capacity_hint=None, use_graph=True,
+                 all_reduce=None, group=None):
+        """all_reduce: None (single GPU), "after" (one NCCL sum all-reduce of the flat gradient bucket issued right
+        after the replay) or "captured" (the all-reduce is part of the graph: every rank replays in lockstep)."""
         self.deformer, self.leaves = deformer, leaves
         self.big, self.t_vertices = big_pose_params, t_vertices
         self.H, self.W, self.tanfovx, self.tanfovy = int(image_height), int(image_width), float(tanfovx), float(tanfovy)
@@ -64,13 +67,25 @@ class GraphedRenderStep:
         self.n_loss_inputs = n_loss_inputs
         self.n_seen = torch.zeros(1, dtype=torch.int32, device=dev)  # max num_rendered over all replays (device)
         self.capacity = None if capacity_hint is None else int(capacity_hint)
+        assert all_reduce in (None, "after", "captured")
+        self.all_reduce, self.group = all_reduce, group
+        self.flat, self.flat_views = None, None
+        if all_reduce is not None:
+            # gradients of all leaves in one bucket (59 floats per Gaussian at SH degree 3): one collective per step,
+            # and leaves[k].grad are views of it, so nothing is copied back after the reduction
+            n = sum(t.numel() for t in leaves.values())
+            self.flat = torch.zeros(n, device=dev)
+            self.flat_views, o = {}, 0
+            for k, t in leaves.items():
+                self.flat_views[k] = self.flat[o:o + t.numel()].view_as(t)
+                o += t.numel()
         self.graph = None
         self.kernels_per_replay = None
         self.loss = None
         self.out = None
 
     # ---- the eager step (also what gets captured) -------------------------------------------------
-    def _eager(self, vec, loss_inputs, capacity):
+    def _eager(self, vec, loss_inputs, capacity, reduce=False):
         L = self.leaves
         camd, pose = unpack_view(vec)
         d = self.deformer.deform_gaussians(L["xyz"], pose, self.big, self.t_vertices, normals=L.get("normals"),
@@ -96,7 +111,27 @@ class GraphedRenderStep:
         for t in L.values():
             t.grad = None
         loss.backward()
+        if self.flat is not None:
+            with torch.no_grad():
+                torch._foreach_copy_([self.flat_views[k] for k in L], [L[k].grad for k in L])  # one multi-tensor kernel
+                if reduce:
+                    self._reduce()
+            for k in L:
+                L[k].grad = self.flat_views[k]
         return loss, dict(color=color, depth=depth, alpha=alpha, radii=radii, means2D=means2D)
+
+    def _max_over_ranks(self, n):
+        import torch.distributed as dist
+        if self.all_reduce is None or not (dist.is_available() and dist.is_initialized()):
+            return n
+        t = torch.tensor([n], dtype=torch.int64, device=self.vec.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return int(t.item())
+
+    def _reduce(self):
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
 
     # ---- capture ------------------------------------------------------------------------------------
     def _measure(self, vec, loss_inputs):
@@ -108,7 +143,7 @@ class GraphedRenderStep:
     def capture(self, sample_vecs, loss_inputs):
         """Size the binning capacity from `sample_vecs` (a list of packed views), then capture."""
         self.loss_inputs = [t.clone() for t in loss_inputs]
-        n_max = max(self._measure(v, self.loss_inputs) for v in sample_vecs)
+        n_max = self._max_over_ranks(max(self._measure(v, self.loss_inputs) for v in sample_vecs))
         cap = max(int(n_max * 1.5) + 4096, self.capacity or 0)
         self._capture(cap)
 
@@ -117,18 +152,19 @@ class GraphedRenderStep:
         self.n_seen.zero_()
         if not self.use_graph:
             return
+        in_graph = self.all_reduce == "captured"
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             for _ in range(3):  # warm-up on a side stream, as torch.cuda.graph requires
-                self._eager(self.vec, self.loss_inputs, self.capacity)
+                self._eager(self.vec, self.loss_inputs, self.capacity, reduce=in_graph)
         torch.cuda.current_stream().wait_stream(s)
         for t in self.leaves.values():
             t.grad = None
         self.graph = torch.cuda.CUDAGraph()
         n0 = _lib.launch_count()
         with torch.cuda.graph(self.graph):
-            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity)
+            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity, reduce=in_graph)
         self.kernels_per_replay = _lib.launch_count() - n0  # libghr kernels inside one replay
         self.n_seen.zero_()
 
@@ -143,15 +179,17 @@ class GraphedRenderStep:
             if src is not dst:
                 dst.copy_(src, non_blocking=True)
         if self.graph is None:
-            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity)
+            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity, reduce=self.all_reduce is not None)
         else:
             self.graph.replay()
+            if self.all_reduce == "after":
+                self._reduce()
         return self.loss
 
     def check(self):
         """Synchronises; if some replay needed more binning capacity than the graph was captured with, re-captures
         with a larger capacity and returns False (the caller should redo the affected steps)."""
-        n = int(self.n_seen.item())
+        n = self._max_over_ranks(int(self.n_seen.item()))  # every rank re-captures together, with the same capacity
         if n > self.capacity:
             self._capture(int(n * 1.5) + 4096)
             return False
