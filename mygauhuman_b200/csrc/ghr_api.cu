@@ -87,7 +87,7 @@ int ghr_state_layout(int32_t P, int64_t capacity, int32_t W, int32_t H, ghr_layo
 
     L->capacity = capacity;
     L->sort_bits = 32 + (int32_t)higher_msb((uint32_t)tiles);
-    L->sort_passes = (L->sort_bits + kRadixBits - 1) / kRadixBits;
+    L->sort_passes = sort_passes_for(L->sort_bits);
     const size_t cap = (size_t)capacity;
     o = 0;
     L->b_header = o; o += align_up(sizeof(SortHeader));
@@ -217,13 +217,12 @@ int ghr_sort_pairs_u64(int64_t N, int32_t bits, uint64_t* keys_a, uint64_t* keys
     char* w = (char*)workspace;
     SortHeader* hdr = reinterpret_cast<SortHeader*>(w);
     uint32_t* status = reinterpret_cast<uint32_t*>(w + align_up(sizeof(SortHeader)));
-    uint32_t* n_dev = reinterpret_cast<uint32_t*>(w + workspace_bytes - 256);  // last 256 B hold N
-    int r = check_cuda(cudaMemsetAsync(w, 0, workspace_bytes, s), "sort memset");
+    // clear the header and the look-back words of the passes this key width needs
+    const size_t used = align_up(sizeof(SortHeader)) +
+                        sizeof(uint32_t) * (size_t)sort_passes_for(bits) * (size_t)sort_tiles(N) * kRadix;
+    int r = check_cuda(cudaMemsetAsync(w, 0, used, s), "sort memset");
     if (r != GHR_OK) return r;
-    const uint32_t n32 = (uint32_t)N;
-    r = check_cuda(cudaMemcpyAsync(n_dev, &n32, sizeof(n32), cudaMemcpyHostToDevice, s), "sort N upload");
-    if (r != GHR_OK) return r;
-    r = check_cuda(launch_sort(hdr, status, n_dev, N, bits, keys_a, keys_b, vals_a, vals_b, s), "sort");
+    r = check_cuda(launch_sort(hdr, status, nullptr, N, bits, keys_a, keys_b, vals_a, vals_b, s), "sort");
     if (r != GHR_OK) return r;
     if (sorted_sel_dev)
         r = check_cuda(cudaMemcpyAsync(sorted_sel_dev, &hdr->sorted_sel, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s),

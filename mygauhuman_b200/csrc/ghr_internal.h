@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <atomic>
 #include "../../include/ghr.h"
 
@@ -24,15 +25,17 @@ private:
 };
 
 constexpr int kMaxPasses = 8;
-constexpr int kRadixBits = 8;
+constexpr int kRadixBits = 9;  // 512 bins: ceil(bits/9) passes (5 for the 43..45-bit keys of 512^2..1080p frames)
 constexpr int kRadix = 1 << kRadixBits;
-constexpr int kSortThreads = 256;
+constexpr int kSortThreads = 512;
+inline int sort_passes_for(int bits) { return (bits + kRadixBits - 1) / kRadixBits; }
 
 // Control block at the start of the binning buffer (device memory).
 struct SortHeader {
     uint32_t sorted_sel;              // buffer holding the sorted result: 0 = A, 1 = B
     uint32_t num_passes;
-    uint32_t pad[2];
+    uint32_t hist_done;               // histogram CTAs finished (the last one writes the plan)
+    uint32_t pad;
     uint32_t pass_trivial[kMaxPasses];  // 1: all keys share this digit -> pass skipped
     uint32_t pass_src[kMaxPasses];      // buffer a pass reads from
     uint32_t ticket[kMaxPasses];        // dynamic tile counters (one per pass)
@@ -41,7 +44,12 @@ struct SortHeader {
 };
 
 // keys per onesweep tile for a given capacity (must match between layout and launch)
-inline int sort_items_per_thread(int64_t capacity) { return capacity <= (int64_t(1) << 20) ? 4 : 16; }
+inline int sort_items_per_thread(int64_t capacity)
+{
+    static const int forced = [] { const char* e = getenv("GHR_SORT_ITEMS"); return e ? atoi(e) : 0; }();  // tuning only
+    if (forced == 2 || forced == 4 || forced == 8) return forced;
+    return capacity <= (int64_t(1) << 17) ? 2 : capacity <= (int64_t(3) << 17) ? 4 : 8;  // measured on B200
+}
 inline int64_t sort_tiles(int64_t capacity)
 {
     const int64_t tile = int64_t(kSortThreads) * sort_items_per_thread(capacity);

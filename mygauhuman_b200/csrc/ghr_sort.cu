@@ -3,18 +3,25 @@
 // reference rasterizer_impl.cu:305-310.  Stable, so the output is the unique
 // stably-sorted sequence (bit-identical to CUB's).
 //
-//   histogram kernel : one read of the keys, all passes' 256-bin histograms
-//   plan kernel      : exclusive scans -> bin bases; marks passes whose digit
-//                      is identical for every key as trivial (skipped: the
-//                      permutation of such a pass is the identity); assigns
-//                      ping-pong sources on the device (no host sync)
-//   pass kernel (xK) : one sweep per non-trivial pass: per-tile ranking with
-//                      warp match-any, chained-scan (decoupled look-back) of
-//                      per-digit tile counts, scatter.
+//   digits           : 9 bits (512 bins), so the 43..45-bit depth|tile keys of
+//                      a 512^2 .. 1080p frame take 5 passes where an 8-bit
+//                      sort (CUB's SortPairs) takes 6
+//   histogram kernel : one read of the keys, all passes' histograms; the last
+//                      CTA to finish also does the plan: exclusive scans ->
+//                      bin bases, marks passes whose digit is identical for
+//                      every key as trivial (skipped: such a pass is the
+//                      identity permutation), assigns ping-pong sources on
+//                      the device (no host sync)
+//   pass kernel (xK) : one sweep per non-trivial pass: per-warp ranking with
+//                      match-any, per-digit chained scan over tiles
+//                      (decoupled look-back, 4 predecessors per round trip),
+//                      then the tile is put in digit order in shared memory
+//                      and written out so that consecutive threads write
+//                      consecutive addresses of a digit's run.
 //
 // Roofline: HBM stream, algorithmic bytes N*(8 + 24*passes).
-// The pair count N is read from device memory (no D2H sync); the grid is sized
-// for `capacity` and surplus tiles exit.
+// The pair count N is read from device memory (no D2H sync) when n_dev is
+// given; the grid is sized for `capacity` and surplus tiles exit.
 #include "ghr_common.cuh"
 #include "ghr_internal.h"
 
@@ -23,58 +30,83 @@ namespace ghr {
 constexpr uint32_t kStAgg = 1u << 30;
 constexpr uint32_t kStIncl = 2u << 30;
 constexpr uint32_t kStMask = (1u << 30) - 1u;
+constexpr int kSortWarps = kSortThreads / 32;
+static_assert(kSortThreads == kRadix, "one thread per digit in the scans");
 
-__global__ void __launch_bounds__(256) sort_histogram_kernel(const uint64_t* __restrict__ keys,
-                                                             const uint32_t* __restrict__ n_dev, int64_t capacity,
-                                                             int bits, int passes, SortHeader* hdr)
+__device__ __forceinline__ int64_t sort_count(const uint32_t* n_dev, int64_t capacity)
+{
+    return n_dev ? min((int64_t)*n_dev, capacity) : capacity;
+}
+
+// Exclusive scan of one value per thread over the 512-thread block.  s_warp: 17 words; two barriers inside.
+// Back-to-back calls must alternate between two s_warp buffers.
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t w = lane < kSortWarps ? s_warp[lane] : 0u;
+        uint32_t winc = w;
+#pragma unroll
+        for (int o = 1; o < kSortWarps; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += n;
+        }
+        if (lane < kSortWarps) s_warp[lane] = winc - w;
+    }
+    __syncthreads();
+    return s_warp[warp] + inc - v;
+}
+
+__global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint64_t* __restrict__ keys,
+                                                                      const uint32_t* __restrict__ n_dev,
+                                                                      int64_t capacity, int bits, int passes,
+                                                                      SortHeader* hdr)
 {
     __shared__ uint32_t s_hist[kMaxPasses * kRadix];
-    const int64_t N = min((int64_t)*n_dev, capacity);
-    for (int i = threadIdx.x; i < passes * kRadix; i += blockDim.x) s_hist[i] = 0;
+    __shared__ uint32_t s_warp[2][kSortWarps + 1];
+    __shared__ uint32_t s_trivial[kMaxPasses];
+    __shared__ uint32_t s_last;
+    const int64_t N = sort_count(n_dev, capacity);
+    const int t = threadIdx.x;
+    for (int i = t; i < passes * kRadix; i += kSortThreads) s_hist[i] = 0;
     __syncthreads();
-    const uint32_t lastmask = (bits - (passes - 1) * kRadixBits) >= kRadixBits
-                                  ? 0xFFu
-                                  : ((1u << (bits - (passes - 1) * kRadixBits)) - 1u);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x) {
+    const int lastbits = bits - (passes - 1) * kRadixBits;
+    const uint32_t lastmask = (1u << lastbits) - 1u;  // lastbits in [1, kRadixBits]
+    for (int64_t i = (int64_t)blockIdx.x * kSortThreads + t; i < N; i += (int64_t)gridDim.x * kSortThreads) {
         const uint64_t k = keys[i];
         for (int p = 0; p < passes; p++) {
-            uint32_t d = (uint32_t)(k >> (p * kRadixBits)) & 0xFFu;
+            uint32_t d = (uint32_t)(k >> (p * kRadixBits)) & (uint32_t)(kRadix - 1);
             if (p == passes - 1) d &= lastmask;
             atomicAdd(&s_hist[p * kRadix + d], 1u);
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < passes * kRadix; i += blockDim.x) {
+    for (int i = t; i < passes * kRadix; i += kSortThreads) {
         const uint32_t c = s_hist[i];
         if (c) atomicAdd(&hdr->hist[i / kRadix][i % kRadix], c);
     }
-}
-
-// one block of 256 threads
-__global__ void __launch_bounds__(256) sort_plan_kernel(const uint32_t* __restrict__ n_dev, int64_t capacity,
-                                                        int passes, SortHeader* hdr)
-{
-    __shared__ uint32_t s_scan[kRadix];
-    __shared__ uint32_t s_trivial[kMaxPasses];
-    const uint32_t N = (uint32_t)min((int64_t)*n_dev, capacity);
-    const int t = threadIdx.x;
+    // the last CTA to get here owns the complete histograms and writes the plan
+    __threadfence();
+    __syncthreads();
+    if (t == 0) s_last = (atomicAdd(&hdr->hist_done, 1u) == gridDim.x - 1u);
     if (t < kMaxPasses) s_trivial[t] = 0;
     __syncthreads();
+    if (!s_last) return;
+    __threadfence();
     for (int p = 0; p < passes; p++) {
-        const uint32_t c = hdr->hist[p][t];
-        if (c == N) s_trivial[p] = 1;  // N == 0 also lands here (every pass trivial)
-        // exclusive scan over 256 bins (Hillis-Steele in smem)
-        s_scan[t] = c;
-        __syncthreads();
-        for (int o = 1; o < kRadix; o <<= 1) {
-            const uint32_t v = (t >= o) ? s_scan[t - o] : 0;
-            __syncthreads();
-            s_scan[t] += v;
-            __syncthreads();
-        }
-        hdr->bin_base[p][t] = s_scan[t] - c;
-        __syncthreads();
+        const uint32_t c = __ldcg(&hdr->hist[p][t]);
+        if (c == (uint32_t)N) s_trivial[p] = 1;  // N == 0 also lands here (every pass trivial)
+        hdr->bin_base[p][t] = block_excl_scan(c, s_warp[p & 1]);
     }
+    __syncthreads();
     if (t == 0) {
         uint32_t sel = 0;
         for (int p = 0; p < passes; p++) {
@@ -88,15 +120,24 @@ __global__ void __launch_bounds__(256) sort_plan_kernel(const uint32_t* __restri
 }
 
 template <int ITEMS>
-__global__ void __launch_bounds__(kSortThreads) onesweep_pass_kernel(uint64_t* keys_a, uint64_t* keys_b,
-                                                                     uint32_t* vals_a, uint32_t* vals_b,
-                                                                     const uint32_t* __restrict__ n_dev,
-                                                                     int64_t capacity, int pass, uint32_t digit_mask,
-                                                                     SortHeader* hdr, uint32_t* status /*[tiles][256]*/)
+__global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t* keys_a, uint64_t* keys_b,
+                                                                        uint32_t* vals_a, uint32_t* vals_b,
+                                                                        const uint32_t* __restrict__ n_dev,
+                                                                        int64_t capacity, int pass, uint32_t digit_mask,
+                                                                        SortHeader* hdr,
+                                                                        uint32_t* status /*[tiles][kRadix]*/)
 {
     constexpr int TILE = kSortThreads * ITEMS;
-    __shared__ uint32_t s_hist[8][kRadix];  // per-warp digit counts -> per-warp exclusive offsets
-    __shared__ uint32_t s_base[kRadix];     // global output offset of this tile's first key of each digit
+    // hist: per-warp digit counts, then (after the scans) the tile-local position of each warp's first key of each
+    // digit.  Once every key knows its position the same storage stages the keys, then the values.
+    union Stage {
+        uint32_t hist[kSortWarps][kRadix];
+        uint64_t keys[TILE];
+        uint32_t vals[TILE];
+    };
+    __shared__ Stage sm;
+    __shared__ uint32_t s_base[kRadix];  // global offset of the tile's digit run minus its tile-local start
+    __shared__ uint32_t s_warp[kSortWarps + 1];
     __shared__ uint32_t s_tile;
 
     if (hdr->pass_trivial[pass]) return;
@@ -108,81 +149,129 @@ __global__ void __launch_bounds__(kSortThreads) onesweep_pass_kernel(uint64_t* k
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(&hdr->ticket[pass], 1u);
-    for (int i = tid; i < 8 * kRadix; i += kSortThreads) (&s_hist[0][0])[i] = 0;
+    for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&sm.hist[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = s_tile;
-    const int64_t N = min((int64_t)*n_dev, capacity);
+    const int64_t N = sort_count(n_dev, capacity);
     const int64_t tile_start = (int64_t)tile * TILE;
     if (tile_start >= N) return;
+    const int valid = (int)min((int64_t)TILE, N - tile_start);
 
     const int shift = pass * kRadixBits;
     uint64_t key[ITEMS];
     uint32_t val[ITEMS];
-    uint32_t rank[ITEMS];  // low 16: rank inside the warp for its digit; high 16: digit (256 = invalid)
-    const int64_t wbase = tile_start + (int64_t)warp * (32 * ITEMS) + lane;
+    uint32_t pos[ITEMS];  // first: digit << 16 | rank among the warp's keys of that digit; then: tile-local position
+    const int wbase = warp * (32 * ITEMS) + lane;
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
-        const int64_t idx = wbase + i * 32;
-        if (idx < N) { key[i] = kin[idx]; val[i] = vin[idx]; }
+        const int idx = wbase + i * 32;
+        if (idx < valid) { key[i] = kin[tile_start + idx]; val[i] = vin[tile_start + idx]; }
         else { key[i] = ~0ull; val[i] = 0; }
     }
     const uint32_t lt = lanemask_lt();
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
-        const bool valid = (wbase + i * 32) < N;
-        const uint32_t d = valid ? ((uint32_t)(key[i] >> shift) & digit_mask) : 256u;
+        const bool ok = (wbase + i * 32) < valid;
+        const uint32_t d = ok ? ((uint32_t)(key[i] >> shift) & digit_mask) : (uint32_t)kRadix;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
-        if (valid && lane == leader) {
-            old = s_hist[warp][d];
-            s_hist[warp][d] = old + __popc(peers);
+        if (ok && lane == leader) {
+            old = sm.hist[warp][d];
+            sm.hist[warp][d] = old + __popc(peers);
         }
         old = __shfl_sync(0xffffffffu, old, leader);
-        rank[i] = (d << 16) | (old + __popc(peers & lt));
+        pos[i] = (d << 16) | (old + __popc(peers & lt));
         __syncwarp();
     }
     __syncthreads();
 
-    // thread t owns digit t: exclusive scan over the 8 warps, publish, look back
-    {
-        uint32_t sum = 0;
+    // thread t owns digit t: tile count, publish, tile-local digit starts
+    uint32_t sum = 0;
 #pragma unroll
-        for (int w = 0; w < 8; w++) {
-            const uint32_t c = s_hist[w][tid];
-            s_hist[w][tid] = sum;
-            sum += c;
+    for (int w = 0; w < kSortWarps; w++) sum += sm.hist[w][tid];
+    uint32_t* my = status + (size_t)tile * kRadix + tid;
+    st_relaxed_u32(my, (tile == 0 ? kStIncl : kStAgg) | sum);
+    const uint32_t tile_excl = block_excl_scan(sum, s_warp);
+    {
+        uint32_t run = tile_excl;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; w++) {
+            const uint32_t c = sm.hist[w][tid];
+            sm.hist[w][tid] = run;
+            run += c;
         }
-        uint32_t* my = status + (size_t)tile * kRadix + tid;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t d = pos[i] >> 16;
+        pos[i] = d < (uint32_t)kRadix ? sm.hist[warp][d] + (pos[i] & 0xFFFFu) : 0xFFFFFFFFu;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++)
+        if (pos[i] != 0xFFFFFFFFu) sm.keys[pos[i]] = key[i];
+
+    // decoupled look-back over the predecessors' counts of digit t, four tiles per round trip
+    {
         uint32_t excl = 0;
-        if (tile == 0) {
-            st_relaxed_u32(my, kStIncl | sum);
-        } else {
-            st_relaxed_u32(my, kStAgg | sum);
+        if (tile != 0) {
             int j = (int)tile - 1;
-            while (true) {
-                const uint32_t s = ld_relaxed_u32(status + (size_t)j * kRadix + tid);
-                const uint32_t f = s & ~kStMask;
-                if (f == 0) continue;
-                excl += s & kStMask;
-                if (f == kStIncl) break;
-                --j;
+            bool done = false;
+            while (!done) {
+                uint32_t s[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    s[u] = (j - u) >= 0 ? ld_relaxed_u32(status + (size_t)(j - u) * kRadix + tid) : kStIncl;
+                bool stall = false;
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const uint32_t f = s[u] & ~kStMask;
+                    if (!done && !stall) {
+                        if (f == 0) stall = true;
+                        else {
+                            excl += s[u] & kStMask;
+                            if (f == kStIncl) done = true; else --j;
+                        }
+                    }
+                }
             }
             st_relaxed_u32(my, kStIncl | (excl + sum));
         }
-        s_base[tid] = hdr->bin_base[pass][tid] + excl;
+        s_base[tid] = hdr->bin_base[pass][tid] + excl - tile_excl;
     }
     __syncthreads();
 
+    uint32_t dst[ITEMS];
 #pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        const uint32_t d = rank[i] >> 16;
-        if (d < 256u) {
-            const uint32_t dst = s_base[d] + s_hist[warp][d] + (rank[i] & 0xFFFFu);
-            kout[dst] = key[i];
-            vout[dst] = val[i];
+    for (int k = 0; k < ITEMS; k++) {
+        const int idx = k * kSortThreads + tid;
+        if (idx < valid) {
+            const uint64_t kk = sm.keys[idx];
+            dst[k] = s_base[(uint32_t)(kk >> shift) & digit_mask] + idx;
+            kout[dst[k]] = kk;
         }
     }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++)
+        if (pos[i] != 0xFFFFFFFFu) sm.vals[pos[i]] = val[i];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) {
+        const int idx = k * kSortThreads + tid;
+        if (idx < valid) vout[dst[k]] = sm.vals[idx];
+    }
+}
+
+template <int ITEMS>
+static void launch_pass(int64_t tiles, uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
+                        const uint32_t* n_dev, int64_t capacity, int p, uint32_t mask, SortHeader* hdr, uint32_t* st,
+                        cudaStream_t s)
+{
+    onesweep_pass_kernel<ITEMS><<<(unsigned)tiles, kSortThreads, 0, s>>>(keys_a, keys_b, vals_a, vals_b, n_dev, capacity,
+                                                                         p, mask, hdr, st);
 }
 
 cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev, int64_t capacity, int bits,
@@ -190,24 +279,22 @@ cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev
 {
     if (capacity <= 0) return cudaSuccess;
     StageTimer timer(GHR_STAGE_SORT, s);
-    const int passes = (bits + kRadixBits - 1) / kRadixBits;
+    const int passes = sort_passes_for(bits);
     const int items = sort_items_per_thread(capacity);
     const int64_t tiles = sort_tiles(capacity);
-    int64_t hg = (capacity + 256 * 8 - 1) / (256 * 8);
-    const int hgrid = (int)(hg < 148 * 8 ? hg : 148 * 8);
-    sort_histogram_kernel<<<hgrid, 256, 0, s>>>(keys_a, n_dev, capacity, bits, passes, hdr);
-    sort_plan_kernel<<<1, 256, 0, s>>>(n_dev, capacity, passes, hdr);
-    count_launch(2 + passes);
+    int64_t hg = (capacity + kSortThreads * 8 - 1) / (kSortThreads * 8);
+    const int hgrid = (int)(hg < 148 * 4 ? hg : 148 * 4);
+    sort_histogram_kernel<<<hgrid, kSortThreads, 0, s>>>(keys_a, n_dev, capacity, bits, passes, hdr);
+    count_launch(1 + passes);
     for (int p = 0; p < passes; p++) {
         const int rem = bits - p * kRadixBits;
-        const uint32_t mask = rem >= kRadixBits ? 0xFFu : ((1u << rem) - 1u);
+        const uint32_t mask = rem >= kRadixBits ? (uint32_t)(kRadix - 1) : ((1u << rem) - 1u);
         uint32_t* st = status + (size_t)p * tiles * kRadix;
-        if (items == 4)
-            onesweep_pass_kernel<4><<<(unsigned)tiles, kSortThreads, 0, s>>>(keys_a, keys_b, vals_a, vals_b, n_dev,
-                                                                             capacity, p, mask, hdr, st);
-        else
-            onesweep_pass_kernel<16><<<(unsigned)tiles, kSortThreads, 0, s>>>(keys_a, keys_b, vals_a, vals_b, n_dev,
-                                                                              capacity, p, mask, hdr, st);
+        switch (items) {
+            case 2: launch_pass<2>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, s); break;
+            case 4: launch_pass<4>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, s); break;
+            default: launch_pass<8>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, s); break;
+        }
     }
     return cudaGetLastError();
 }

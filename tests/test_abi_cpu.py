@@ -36,7 +36,7 @@ def test_error_strings():
 
 def test_layout_is_aligned_and_monotone():
     L = _lib.state_layout(50000, 180000, 512, 512)
-    assert L.sort_bits == 43 and L.sort_passes == 6          # ZJU 512^2 -> 1024 tiles
+    assert L.sort_bits == 43 and L.sort_passes == 5          # ZJU 512^2 -> 1024 tiles
     assert _lib.state_layout(10, 10, 1024, 1024).sort_bits == 45
     assert _lib.state_layout(10, 10, 1920, 1080).sort_bits == 45
     offs = [L.g_header, L.g_scan_status, L.g_rec, L.g_tiles_touched, L.g_point_offsets, L.g_cov3D, L.g_clamped]
