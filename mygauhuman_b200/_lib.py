@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libghr.so")
+LIB_PATH = os.environ.get("GHR_LIB_PATH") or os.path.join(_HERE, "csrc", "libghr.so")  # override: tuning variants only
 
 GHR_OK = 0
 GHR_ERR_BAD_ARG, GHR_ERR_BUFFER, GHR_ERR_CUDA, GHR_ERR_CAPACITY, GHR_ERR_PREFILTER = -1, -2, -3, -4, -5

@@ -58,17 +58,28 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
     }
 }
 
-__global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_kernel(ghr_geom_header* hdr, int64_t capacity,
+// Tile ranges (reference identifyTileRanges, rasterizer_impl.cu:126-152) and, per list entry, the blend kernels'
+// staging word {Gaussian id, block mask}: bit (4*by + bx) of the mask is set when the Gaussian may contribute to
+// some pixel of the tile's 4x4-pixel block (bx, by) -- the conservative bounding-box test followed by the exact
+// ellipse-vs-block test (ghr_common.cuh).  The blend kernels (sixteen or eight work items per tile) would otherwise
+// repeat this test once per item; here it is done once per entry.  The words go into the key buffer the sort left
+// unused (8 bytes per entry, exactly).
+__global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_kernel(ghr_geom_header* hdr, int64_t capacity, int gx,
                                                                 const SortHeader* __restrict__ sh,
-                                                                const uint64_t* __restrict__ keys_a,
-                                                                const uint64_t* __restrict__ keys_b, uint2* ranges)
+                                                                uint64_t* keys_a, uint64_t* keys_b,
+                                                                const uint32_t* __restrict__ vals_a,
+                                                                const uint32_t* __restrict__ vals_b,
+                                                                const float4* __restrict__ rec, uint2* ranges)
 {
     const int64_t L = hdr->num_rendered;
     if (L > capacity) {
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicMax(&hdr->error, (uint32_t)(-GHR_ERR_CAPACITY));
         return;
     }
-    const uint64_t* __restrict__ keys = sh->sorted_sel ? keys_b : keys_a;
+    const uint32_t sel = sh->sorted_sel;
+    const uint64_t* __restrict__ keys = sel ? keys_b : keys_a;
+    const uint32_t* __restrict__ vals = sel ? vals_b : vals_a;
+    uint2* __restrict__ entries = reinterpret_cast<uint2*>(sel ? keys_a : keys_b);
     for (int64_t idx = (int64_t)blockIdx.x * GHR_BLOCK + threadIdx.x; idx < L; idx += (int64_t)gridDim.x * GHR_BLOCK) {
         const uint32_t cur = (uint32_t)(keys[idx] >> 32);
         if (idx == 0) ranges[cur].x = 0;
@@ -77,6 +88,28 @@ __global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_kernel(ghr_geom_header*
             if (cur != prev) { ranges[prev].y = (uint32_t)idx; ranges[cur].x = (uint32_t)idx; }
         }
         if (idx == L - 1) ranges[cur].y = (uint32_t)L;
+
+        const uint32_t id = vals[idx];
+        const float4 r0 = rec[3 * (size_t)id], r1 = rec[3 * (size_t)id + 1];
+        float ex, ey;
+        unpack_cull_extent(__float_as_uint(rec[3 * (size_t)id + 2].w), ex, ey);
+        const float tx0 = (float)((cur % (uint32_t)gx) * GHR_TILE), ty0 = (float)((cur / (uint32_t)gx) * GHR_TILE);
+        const CullQuad quad = cull_quad(r1.x, r1.y, r1.z, r1.w);
+        uint32_t mask = 0;
+#pragma unroll
+        for (int by = 0; by < 4; by++) {
+            const float ry0 = ty0 + 4.0f * by, ry1 = ry0 + 3.0f;
+            const float ddy = fmaxf(fmaxf(ry0 - r0.y, r0.y - ry1), 0.0f);
+            if (ddy > ey) continue;
+#pragma unroll
+            for (int bx = 0; bx < 4; bx++) {
+                const float rx0 = tx0 + 4.0f * bx, rx1 = rx0 + 3.0f;
+                const float ddx = fmaxf(fmaxf(rx0 - r0.x, r0.x - rx1), 0.0f);
+                if (ddx > ex) continue;
+                if (cull_keep_exact(quad, r0.x, r0.y, rx0, rx1, ry0, ry1)) mask |= 1u << (4 * by + bx);
+            }
+        }
+        entries[idx] = make_uint2(id, mask);
     }
 }
 
@@ -135,9 +168,10 @@ cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, cha
     if (grid < 1) grid = 1;
     tile_ranges_kernel<<<(unsigned)grid, GHR_BLOCK, 0, s>>>(
         reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header), capacity,
-        reinterpret_cast<const SortHeader*>(binning + L.b_header),
-        reinterpret_cast<const uint64_t*>(binning + L.b_keys_a),
-        reinterpret_cast<const uint64_t*>(binning + L.b_keys_b), reinterpret_cast<uint2*>(img + L.i_ranges));
+        (p.W + GHR_TILE - 1) / GHR_TILE, reinterpret_cast<const SortHeader*>(binning + L.b_header),
+        reinterpret_cast<uint64_t*>(binning + L.b_keys_a), reinterpret_cast<uint64_t*>(binning + L.b_keys_b),
+        reinterpret_cast<const uint32_t*>(binning + L.b_vals_a), reinterpret_cast<const uint32_t*>(binning + L.b_vals_b),
+        reinterpret_cast<const float4*>(geom + L.g_rec), reinterpret_cast<uint2*>(img + L.i_ranges));
     count_launch();
     tile_order_kernel<<<1, 1024, 0, s>>>(tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
                                          reinterpret_cast<const ghr_geom_header*>(geom + L.g_header), capacity,

@@ -1,15 +1,26 @@
 // Backward of the per-tile blend (reference backward.cu:399-587 renderCUDA).
 //
 // The reference issues 9 fp32 global atomicAdds per contributing
-// (pixel, Gaussian) pair (backward.cu:538,574-584) -- its hottest spot.  Here
-// every warp (a 16x2 pixel strip) first votes whether any of its pixels is
-// touched by the Gaussian (ballot -> skip), then reduces the 9 partial
-// gradients across its 32 pixels with a split butterfly (12 shuffles instead
-// of 45: at each xor step half of the lanes keeps half of the values), and
-// only then 9 lanes issue one atomic each into a packed per-Gaussian
-// accumulator [P][12] (one 48-byte record -> the 9 atomics of a Gaussian hit
-// at most two 32-byte sectors).  The per-Gaussian preprocess backward reads
-// that record, so no separate dL_dconic/dL_dmean2D arrays are zeroed.
+// (pixel, Gaussian) pair (backward.cu:538,574-584) -- its hottest spot.  Here a
+// work item is a (tile, 4x4 pixel block) pair processed by one warp, and two
+// lanes serve each pixel ("slots", as in ghr_blend_fwd.cu): the warp walks the
+// tile list back to front eight surviving Gaussians at a time; slot 0 owns the
+// 1st, 3rd, 5th, 7th of them and slot 1 the others.  A lane evaluates
+// G / alpha only for the Gaussians it owns, the alphas are exchanged with one
+// shuffle each, both lanes run the (cheap, strictly sequential) transmittance /
+// accumulated-colour recurrences over all eight, and each lane computes the 9
+// partial gradients of its own four.  These are reduced over the 16 pixels of
+// the slot with a split butterfly (11 shuffles for 9 values: at each xor step
+// half of the lanes keeps half of the values) -- the two slots reduce two
+// different Gaussians in the same instructions -- and 9 lanes per slot issue
+// one atomic each into a packed per-Gaussian accumulator [P][12] (one 48-byte
+// record -> the 9 atomics of a Gaussian hit at most two 32-byte sectors).  The
+// per-Gaussian preprocess backward reads that record, so no separate
+// dL_dconic/dL_dmean2D arrays are zeroed.
+// Why slots: a warp alone issues ~0.4 instructions per cycle on this dependent
+// code, and the kernel time is the instruction count along the heaviest item's
+// list (measured: all items start at t=0, the longest one ends the kernel).
+// Two slots halve the instructions per Gaussian on that path.
 //
 // accum record: 0-2 dL_dcolor, 3-4 dL_dmean2D.xy, 5-7 dL_dconic (x,y,w),
 //               8 dL_dopacity, 9-11 unused.
@@ -25,58 +36,77 @@ __device__ __forceinline__ void cp_async16b(void* smem, const void* gmem)
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
 }
 
-// Sum v[0..8] over the warp.  Returns the total of value `slot` (see
-// reduce_slot()) in every lane; lanes whose slot is >= 9 return garbage-free 0.
-__device__ __forceinline__ float warp_reduce9(const float (&v)[9], uint32_t lane)
+// Sum v[0..8] over the 16 lanes of a slot (xor 8,4,2,1 never leaves the half-warp).  Afterwards every lane holds the
+// total of exactly one value, half_slot(lane) (>= 9: a padding position, holds 0).
+__device__ __forceinline__ float half_reduce9(const float (&v)[9], uint32_t lane)
 {
-    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+    const bool b3 = lane & 8, b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
     float a[6];
 #pragma unroll
     for (int k = 0; k < 5; k++) {
         const float lo = v[k], hi = (k < 4) ? v[5 + k] : 0.0f;
-        const float keep = b4 ? hi : lo, send = b4 ? lo : hi;
-        a[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        const float keep = b3 ? hi : lo, send = b3 ? lo : hi;
+        a[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
     }
     a[5] = 0.0f;
     float c[4];
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-        const float keep = b3 ? a[3 + k] : a[k], send = b3 ? a[k] : a[3 + k];
-        c[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        const float keep = b2 ? a[3 + k] : a[k], send = b2 ? a[k] : a[3 + k];
+        c[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
     }
     c[3] = 0.0f;
     float d[2];
 #pragma unroll
     for (int k = 0; k < 2; k++) {
-        const float keep = b2 ? c[2 + k] : c[k], send = b2 ? c[k] : c[2 + k];
-        d[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+        const float keep = b1 ? c[2 + k] : c[k], send = b1 ? c[k] : c[2 + k];
+        d[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
     }
-    const float keep = b1 ? d[1] : d[0], send = b1 ? d[0] : d[1];
-    float e = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    e += __shfl_xor_sync(0xffffffffu, e, 1);
-    return e;
+    const float keep = b0 ? d[1] : d[0], send = b0 ? d[0] : d[1];
+    return keep + __shfl_xor_sync(0xffffffffu, send, 1);
 }
 
-// Which of the 9 values a lane holds after warp_reduce9 (>= 9: none).
-__device__ __forceinline__ int reduce_slot(uint32_t lane)
+// Which of the 9 values a lane holds after half_reduce9 (>= 9: none).
+__device__ __forceinline__ int half_slot(uint32_t lane)
 {
-    const int w4 = ((lane & 4) ? 2 : 0) + ((lane & 2) ? 1 : 0);  // position inside the padded group of 4
+    const int w4 = ((lane & 2) ? 2 : 0) + ((lane & 1) ? 1 : 0);  // position inside the padded group of 4
     if (w4 >= 3) return 99;
-    const int local = ((lane & 8) ? 3 : 0) + w4;                 // position inside the padded group of 6
-    if (lane & 16) return local < 4 ? 5 + local : 99;
+    const int local = ((lane & 4) ? 3 : 0) + w4;                 // position inside the padded group of 6
+    if (lane & 8) return local < 4 ? 5 + local : 99;
     return local < 5 ? local : 99;
 }
 
-constexpr int kBwdWarps = 4;     // independent warps per CTA
-constexpr int kBwdBatch = 64;    // Gaussians per staging round and warp
-constexpr int kBwdStages = 3;
-constexpr int kBwdCtasPerSm = 4;
+#ifdef GHR_TRACE  // tuning builds only (tools/build_variant.sh): per-item begin/end timestamps and phase cycle counts
+__device__ unsigned long long g_bwd_trace[1 << 16][8];
+__device__ __forceinline__ unsigned long long gtime_b()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define BTRACE_LAP(acc) { const long long now_ = clock64(); acc += now_ - c_mark; c_mark = now_; }
+#else
+#define BTRACE_LAP(acc)
+#endif
+#ifndef GHR_BWD_WARPS
+#define GHR_BWD_WARPS 4
+#endif
+#ifndef GHR_BWD_STAGES
+#define GHR_BWD_STAGES 3
+#endif
+#ifndef GHR_BWD_CTAS
+#define GHR_BWD_CTAS 4
+#endif
+constexpr int kBwdWarps = GHR_BWD_WARPS;    // independent warps per CTA
+constexpr int kBwdBatch = 64;               // list entries per staging round and warp
+constexpr int kBwdStages = GHR_BWD_STAGES;
+constexpr int kBwdCtasPerSm = GHR_BWD_CTAS;
 
-// Persistent kernel: warps pull (tile, 8x4 block) work items from a queue ordered by decreasing tile-list
+// Persistent kernel: warps pull (tile, 4x4 block) work items from a queue ordered by decreasing tile-list
 // length (tile_order_kernel) and work independently (no block-level barrier); see ghr_blend_fwd.cu.
 __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
     int W, int H, int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
-    const SortHeader* __restrict__ sh, const uint32_t* __restrict__ vals_a, const uint32_t* __restrict__ vals_b,
+    const SortHeader* __restrict__ sh, const uint2* __restrict__ ent_a, const uint2* __restrict__ ent_b,
     const float4* __restrict__ rec, ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
     const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
     const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas, float* __restrict__ accum)
@@ -84,39 +114,47 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
     constexpr int BATCH = kBwdBatch, NSTAGE = kBwdStages, PER_LANE = BATCH / 32;
     __shared__ __align__(16) float4 s_all[kBwdWarps][NSTAGE][BATCH * 3];
     __shared__ uint32_t s_id_all[kBwdWarps][NSTAGE][BATCH];
+    __shared__ uint32_t s_keep_all[kBwdWarps][NSTAGE][PER_LANE];  // survivors of each staged round, one bit per entry
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t slot = lane >> 4, pl = lane & 15u;  // which of the pixel's two lanes; pixel inside the 4x4 block
     float4(*s_rec)[BATCH * 3] = s_all[warp];
     uint32_t(*s_id)[BATCH] = s_id_all[warp];
+    uint32_t(*s_keep)[PER_LANE] = s_keep_all[warp];
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
-    const uint32_t* __restrict__ point_list = sh->sorted_sel ? vals_b : vals_a;
+    // {Gaussian id, 4x4-block mask} per list entry (tile_ranges_kernel; lives in the key buffer the sort left unused)
+    const uint2* __restrict__ entries = sh->sorted_sel ? ent_a : ent_b;
     const float bgc0 = bg[0], bgc1 = bg[1], bgc2 = bg[2];
     const float ddelx_dx = (float)(0.5 * W), ddely_dy = (float)(0.5 * H);
-    const int slot = reduce_slot(lane);
-    const bool writer = slot < 9 && !(lane & 1);
+    const int vslot = half_slot(lane);  // which of the 9 reduced values this lane ends up holding
+    const bool writer = vslot < 9;
+    const uint32_t half_mask = slot ? 0xFFFF0000u : 0x0000FFFFu;
     const size_t HW = (size_t)H * W;
-    const uint32_t n_items = (uint32_t)tiles * 8u;
+    const uint32_t n_items = (uint32_t)tiles * 16u;
 
     for (;;) {
         uint32_t item = 0;
         if (lane == 0) item = atomicAdd(&hdr->blend_bwd_ticket, 1u);
         item = __shfl_sync(0xffffffffu, item, 0);
         if (item >= n_items) break;
-        const uint32_t tile = order[item >> 3], wb = item & 7u;  // same 8x4 pixel blocks as the forward
+#ifdef GHR_TRACE
+        const unsigned long long t_begin = gtime_b();
+        int trace_rounds = 0, trace_steps = 0, trace_live = 0;
+        long long c_wait = 0, c_p1 = 0, c_p23 = 0, c_mark = clock64();
+#endif
+        const uint32_t tile = order[item >> 4], wb = item & 15u;  // same 4x4 pixel blocks as the forward
         const uint2 range = overflow ? make_uint2(0, 0) : ranges[tile];
         const int todo_total = (int)(range.y - range.x);
         if (todo_total == 0) break;  // the queue is sorted by length: everything after this is empty too
         const uint32_t tile_x = tile % gx, tile_y = tile / gx;
-        const uint32_t bx0 = tile_x * GHR_TILE + (wb & 1u) * 8u, by0 = tile_y * GHR_TILE + (wb >> 1) * 4u;
-        const uint32_t pixx = bx0 + (lane & 7u), pixy = by0 + (lane >> 3);
+        const uint32_t bx0 = tile_x * GHR_TILE + (wb & 3u) * 4u, by0 = tile_y * GHR_TILE + (wb >> 2) * 4u;
+        const uint32_t pixx = bx0 + (pl & 3u), pixy = by0 + (pl >> 2);
         const bool inside = pixx < (uint32_t)W && pixy < (uint32_t)H;
         const float pxf = (float)pixx, pyf = (float)pixy;
-        const float rx0 = (float)bx0, rx1 = (float)(bx0 + 7u), ry0 = (float)by0, ry1 = (float)(by0 + 3u);
 
         const size_t pix = (size_t)pixy * W + pixx;
         const float T_final = inside ? final_Ts[pix] : 0.0f;
-        float T = T_final;
         const int last_contributor = inside ? (int)n_contrib[pix] : 0;
         // the warp only walks the part of the list some pixel of it still needs: positions [0, warp_last)
         const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
@@ -130,24 +168,34 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
             dL_ddepth = dL_ddepths[pix]; dL_dalpha = dL_dalphas[pix];
         }
         const float bg_dot = bgc0 * dpix0 + bgc1 * dpix1 + bgc2 * dpix2;
+        // per-pixel recurrence state, carried identically by both lanes of the pixel
+        float T = T_final;
         float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
         float accum_depth_rec = 0.f, accum_alpha_rec = 0.f, last_alpha = 0.f, last_depth = 0.f;
 
-        // round r stages list positions walk-1-r*BATCH-slot (back to front).  Ids are fetched one round ahead of
-        // the record copies (two dependent L2 round trips otherwise), records two rounds ahead of their use.
+        // round r stages list positions walk-1-r*BATCH-slot (back to front).  Entries are fetched one round ahead of
+        // the record copies (two dependent L2 round trips otherwise), records two rounds ahead of their use; only the
+        // records of Gaussians whose block mask has this block's bit are copied.
         uint32_t nid[PER_LANE];
         auto load_ids = [&](int round) {
 #pragma unroll
             for (int u = 0; u < PER_LANE; u++) {
                 const int progress = round * BATCH + (int)lane + u * 32;
-                nid[u] = (round < rounds && progress < walk) ? point_list[range.x + (uint32_t)(walk - 1 - progress)] : 0xFFFFFFFFu;
+                nid[u] = 0xFFFFFFFFu;
+                if (round < rounds && progress < walk) {
+                    const uint2 e = entries[range.x + (uint32_t)(walk - 1 - progress)];
+                    if ((e.y >> wb) & 1u) nid[u] = e.x;
+                }
             }
         };
         auto stage = [&](int buf) {
 #pragma unroll
             for (int u = 0; u < PER_LANE; u++) {
                 const int sl = (int)lane + u * 32;
-                if (nid[u] != 0xFFFFFFFFu) {
+                const bool keep = nid[u] != 0xFFFFFFFFu;
+                const uint32_t bits = __ballot_sync(0xffffffffu, keep);
+                if (lane == 0) s_keep[buf][u] = bits;
+                if (keep) {
                     s_id[buf][sl] = nid[u];
                     const float4* src = rec + 3 * (size_t)nid[u];
                     float4* dst = &s_rec[buf][sl * 3];
@@ -159,111 +207,176 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
             asm volatile("cp.async.commit_group;" ::: "memory");
         };
 
-        load_ids(0); stage(0);
-        load_ids(1); stage(1);
-        load_ids(2);
+        {
+            uint32_t pre[NSTAGE - 1][PER_LANE];
+#pragma unroll
+            for (int q = 0; q < NSTAGE - 1; q++) {
+                load_ids(q);
+#pragma unroll
+                for (int u = 0; u < PER_LANE; u++) pre[q][u] = nid[u];
+            }
+#pragma unroll
+            for (int q = 0; q < NSTAGE - 1; q++) {
+#pragma unroll
+                for (int u = 0; u < PER_LANE; u++) nid[u] = pre[q][u];
+                stage(q);
+            }
+            load_ids(NSTAGE - 1);
+        }
         int toDo = walk;
         for (int i = 0; i < rounds; i++, toDo -= BATCH) {
             const int buf = i % NSTAGE;
-            stage((i + 2) % NSTAGE);
-            load_ids(i + 3);
-            asm volatile("cp.async.wait_group 2;" ::: "memory");
+            stage((i + NSTAGE - 1) % NSTAGE);
+            load_ids(i + NSTAGE);
+            asm volatile("cp.async.wait_group %0;" ::"n"(NSTAGE - 1) : "memory");
             __syncwarp();
             const int n = min(BATCH, toDo);
             const float4* r = s_rec[buf];
+            const float* rf = reinterpret_cast<const float*>(r);
+#ifdef GHR_TRACE
+            trace_rounds++;
+#endif
+            BTRACE_LAP(c_wait)
             // entry j of this round sits at list position pos(j) = walk-1-(i*BATCH+j); the reference's
             // `contributor` for it equals pos(j) (backward.cu:499-501: skip if contributor >= last_contributor)
             const int pos0 = walk - 1 - i * BATCH;
             for (int g = 0; g < n; g += 32) {
-                const int jj = g + (int)lane;
-                bool keep = false;
-                if (jj < n) {
-                    const float4 c0 = r[3 * jj];
-                    float ex, ey;
-                    unpack_cull_extent(__float_as_uint(r[3 * jj + 2].w), ex, ey);
-                    const float ddx = fmaxf(fmaxf(rx0 - c0.x, c0.x - rx1), 0.0f);
-                    const float ddy = fmaxf(fmaxf(ry0 - c0.y, c0.y - ry1), 0.0f);
-                    keep = !(ddx > ex) && !(ddy > ey);
-                }
-                uint32_t mask = __ballot_sync(0xffffffffu, keep);
-                // Survivors four at a time.  Phase 1 (independent: ILP) evaluates G/alpha of the four; phase 2
-                // runs the transmittance / accumulated-colour recurrences in list order; phase 3 reduces the
-                // 4 x 9 partial gradients with four interleaved butterflies.
+                uint32_t mask = s_keep[buf][g >> 5];  // survivors of this group of 32 entries (block masks, see stage)
                 while (mask) {
-                    int j[4];
-                    bool v_ok[4];
+                    // eight survivors in walk order; slot 0 owns j[0] j[2] j[4] j[6], slot 1 the others
+                    int j[8];
+                    bool v_ok[8];
 #pragma unroll
-                    for (int u = 0; u < 4; u++) {
+                    for (int u = 0; u < 8; u++) {
                         v_ok[u] = mask != 0;
                         j[u] = v_ok[u] ? g + __ffs(mask) - 1 : j[0];
                         mask &= mask - 1;
                     }
-                    float G[4], alpha[4], dx[4], dy[4];
-                    float4 r0[4], r1[4];
-                    bool valid[4];
-                    uint32_t vm[4];
-    #pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        r0[u] = r[3 * j[u]]; r1[u] = r[3 * j[u] + 1];
-                        dx[u] = __fsub_rn(r0[u].x, pxf); dy[u] = __fsub_rn(r0[u].y, pyf);
-                        const float power = pair_power(dx[u], dy[u], r1[u].x, r1[u].y, r1[u].z);
-                        G[u] = expf(power);
-                        alpha[u] = fminf(0.99f, __fmul_rn(r1[u].w, G[u]));
-                        valid[u] = v_ok[u] && (pos0 - j[u] < last_contributor) && !(power > 0.0f) && !(alpha[u] < 1.0f / 255.0f);
-                        vm[u] = __ballot_sync(0xffffffffu, valid[u]);
+                    // phase 1 (independent: ILP): G / alpha of the four Gaussians this lane owns; alpha 0 = not valid here
+                    float G[4], al[4], dx[4], dy[4], depth_own[4];
+                    float4 con[4];
+                    int jm[4];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        jm[q] = slot ? j[2 * q + 1] : j[2 * q];
+                        const bool ok = slot ? v_ok[2 * q + 1] : v_ok[2 * q];
+                        const float4 r0 = r[3 * jm[q]];
+                        con[q] = r[3 * jm[q] + 1];
+                        depth_own[q] = r0.z;
+                        dx[q] = __fsub_rn(r0.x, pxf); dy[q] = __fsub_rn(r0.y, pyf);
+                        const float power = pair_power(dx[q], dy[q], con[q].x, con[q].y, con[q].z);
+                        G[q] = expf(power);
+                        const float alpha = fminf(0.99f, __fmul_rn(con[q].w, G[q]));
+                        const bool valid = ok && (pos0 - jm[q] < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                        al[q] = valid ? alpha : 0.0f;
                     }
-                    if ((vm[0] | vm[1] | vm[2] | vm[3]) == 0) continue;
-                    float v[4][9];
-    #pragma unroll
-                    for (int u = 0; u < 4; u++) {
-    #pragma unroll
-                        for (int k = 0; k < 9; k++) v[u][k] = 0.0f;
-                        if (valid[u]) {
-                            const float4 r2 = r[3 * j[u] + 2];
-                            const float a = alpha[u];
-                            T = T / (1.0f - a);
-                            const float dchannel_dcolor = a * T;
-                            float dL_dopa = 0.0f;
-                            acc0 = last_alpha * lc0 + (1.0f - last_alpha) * acc0; lc0 = r2.x;
-                            dL_dopa += (r2.x - acc0) * dpix0; v[u][0] = dchannel_dcolor * dpix0;
-                            acc1 = last_alpha * lc1 + (1.0f - last_alpha) * acc1; lc1 = r2.y;
-                            dL_dopa += (r2.y - acc1) * dpix1; v[u][1] = dchannel_dcolor * dpix1;
-                            acc2 = last_alpha * lc2 + (1.0f - last_alpha) * acc2; lc2 = r2.z;
-                            dL_dopa += (r2.z - acc2) * dpix2; v[u][2] = dchannel_dcolor * dpix2;
-                            accum_depth_rec = last_alpha * last_depth + (1.0f - last_alpha) * accum_depth_rec;
-                            last_depth = r0[u].z;
-                            dL_dopa += (r0[u].z - accum_depth_rec) * dL_ddepth;
-                            accum_alpha_rec = last_alpha + (1.0f - last_alpha) * accum_alpha_rec;
-                            dL_dopa += (1.0f - accum_alpha_rec) * dL_dalpha;
-                            dL_dopa *= T;
-                            last_alpha = a;
-                            dL_dopa += (-T_final / (1.0f - a)) * bg_dot;
-                            const float dL_dG = r1[u].w * dL_dopa;
-                            const float gdx = G[u] * dx[u], gdy = G[u] * dy[u];
-                            const float dG_ddelx = -gdx * r1[u].x - gdy * r1[u].y;
-                            const float dG_ddely = -gdy * r1[u].z - gdx * r1[u].y;
-                            v[u][3] = dL_dG * dG_ddelx * ddelx_dx;
-                            v[u][4] = dL_dG * dG_ddely * ddely_dy;
-                            v[u][5] = -0.5f * gdx * dx[u] * dL_dG;
-                            v[u][6] = -0.5f * gdx * dy[u] * dL_dG;
-                            v[u][7] = -0.5f * gdy * dy[u] * dL_dG;
-                            v[u][8] = G[u] * dL_dopa;
+                    float a[8];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        const float theirs = __shfl_xor_sync(0xffffffffu, al[q], 16);
+                        a[2 * q] = slot ? theirs : al[q];
+                        a[2 * q + 1] = slot ? al[q] : theirs;
+                    }
+#ifdef GHR_TRACE
+                    trace_steps++;
+#endif
+                    BTRACE_LAP(c_p1)
+                    if (!__any_sync(0xffffffffu, (a[0] > 0.f) | (a[1] > 0.f) | (a[2] > 0.f) | (a[3] > 0.f) | (a[4] > 0.f) |
+                                                     (a[5] > 0.f) | (a[6] > 0.f) | (a[7] > 0.f)))
+                        continue;
+                    // phases 2 and 3, one pair of Gaussians (one per slot) at a time
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        // state after the pair's first Gaussian (S1: what slot 0 differentiates) and after its second (S2)
+                        float Ts[2], a0s[2], a1s[2], a2s[2], ads[2], aas[2];
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            const int k = 2 * q + h;
+                            const float4 c = r[3 * j[k] + 2];
+                            const float dep = rf[12 * j[k] + 2];
+                            const bool on = a[k] > 0.0f;
+                            const float inv = __fdividef(1.0f, 1.0f - a[k]);
+                            const float om = 1.0f - last_alpha;
+                            T = on ? T * inv : T;
+                            acc0 = on ? fmaf(last_alpha, lc0, om * acc0) : acc0;
+                            acc1 = on ? fmaf(last_alpha, lc1, om * acc1) : acc1;
+                            acc2 = on ? fmaf(last_alpha, lc2, om * acc2) : acc2;
+                            accum_depth_rec = on ? fmaf(last_alpha, last_depth, om * accum_depth_rec) : accum_depth_rec;
+                            accum_alpha_rec = on ? fmaf(om, accum_alpha_rec, last_alpha) : accum_alpha_rec;
+                            lc0 = on ? c.x : lc0; lc1 = on ? c.y : lc1; lc2 = on ? c.z : lc2;
+                            last_depth = on ? dep : last_depth;
+                            last_alpha = on ? a[k] : last_alpha;
+                            Ts[h] = T; a0s[h] = acc0; a1s[h] = acc1; a2s[h] = acc2; ads[h] = accum_depth_rec; aas[h] = accum_alpha_rec;
                         }
+                        const uint32_t live = __ballot_sync(0xffffffffu, al[q] > 0.0f);
+#ifdef GHR_TRACE
+                        trace_live += ((live & 0xFFFFu) != 0) + ((live >> 16) != 0);
+#endif
+                        if (live == 0) continue;
+                        // this lane's own Gaussian of the pair: partial gradients of its pixel (zero where not valid)
+                        const float Tm = slot ? Ts[1] : Ts[0];
+                        const float m0 = slot ? a0s[1] : a0s[0], m1 = slot ? a1s[1] : a1s[0], m2 = slot ? a2s[1] : a2s[0];
+                        const float md = slot ? ads[1] : ads[0], ma = slot ? aas[1] : aas[0];
+                        const float4 c = r[3 * jm[q] + 2];
+                        const float aq = al[q];
+                        float v[9];
+                        {
+                            const float dchannel_dcolor = aq * Tm;
+                            float dL_dopa = (c.x - m0) * dpix0;
+                            dL_dopa = fmaf(c.y - m1, dpix1, dL_dopa);
+                            dL_dopa = fmaf(c.z - m2, dpix2, dL_dopa);
+                            dL_dopa = fmaf(depth_own[q] - md, dL_ddepth, dL_dopa);
+                            dL_dopa = fmaf(1.0f - ma, dL_dalpha, dL_dopa);
+                            dL_dopa *= Tm;
+                            dL_dopa = fmaf(-T_final * __fdividef(1.0f, 1.0f - aq), bg_dot, dL_dopa);
+                            dL_dopa = aq > 0.0f ? dL_dopa : 0.0f;
+                            const float dL_dG = con[q].w * dL_dopa;
+                            const float gdx = G[q] * dx[q], gdy = G[q] * dy[q];
+                            const float dG_ddelx = -gdx * con[q].x - gdy * con[q].y;
+                            const float dG_ddely = -gdy * con[q].z - gdx * con[q].y;
+                            v[0] = dchannel_dcolor * dpix0;
+                            v[1] = dchannel_dcolor * dpix1;
+                            v[2] = dchannel_dcolor * dpix2;
+                            v[3] = dL_dG * dG_ddelx * ddelx_dx;
+                            v[4] = dL_dG * dG_ddely * ddely_dy;
+                            v[5] = -0.5f * gdx * dx[q] * dL_dG;
+                            v[6] = -0.5f * gdx * dy[q] * dL_dG;
+                            v[7] = -0.5f * gdy * dy[q] * dL_dG;
+                            v[8] = G[q] * dL_dopa;
+                        }
+                        const float total = half_reduce9(v, lane);
+                        if ((live & half_mask) != 0 && writer)
+                            atomicAdd(accum + 12 * (size_t)s_id[buf][jm[q]] + vslot, total);
                     }
-                    float total[4];
-    #pragma unroll
-                    for (int u = 0; u < 4; u++) total[u] = warp_reduce9(v[u], lane);
-    #pragma unroll
-                    for (int u = 0; u < 4; u++)
-                        if (vm[u] != 0 && writer) atomicAdd(accum + 12 * (size_t)s_id[buf][j[u]] + slot, total[u]);
+                    BTRACE_LAP(c_p23)
                 }
             }
             __syncwarp();  // buffer `buf` is re-filled by the next iteration's stage()
         }
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncwarp();
+#ifdef GHR_TRACE
+        if (lane == 0 && item < (1u << 16)) {
+            g_bwd_trace[item][0] = t_begin;
+            g_bwd_trace[item][1] = gtime_b();
+            g_bwd_trace[item][2] = (uint32_t)todo_total;
+            g_bwd_trace[item][3] = (unsigned long long)trace_rounds;
+            g_bwd_trace[item][4] = ((unsigned long long)trace_live << 32) | (uint32_t)trace_steps;
+            g_bwd_trace[item][5] = (unsigned long long)c_wait;
+            g_bwd_trace[item][6] = (unsigned long long)c_p1;
+            g_bwd_trace[item][7] = (unsigned long long)c_p23;
+        }
+#endif
     }
 }
+#ifdef GHR_TRACE
+}  // namespace ghr
+extern "C" int ghr_debug_bwd_trace(void* out, size_t bytes)
+{
+    return (int)cudaMemcpyFromSymbol(out, ghr::g_bwd_trace, bytes);
+}
+namespace ghr {
+#endif
 
 cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, const char* binning, const char* img,
                                   const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
@@ -276,13 +389,13 @@ cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, 
     // the queue head is scratch state inside the (otherwise read-only) geometry buffer
     cudaError_t e = cudaMemsetAsync(&hdr->blend_bwd_ticket, 0, sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
-    const int64_t items = (int64_t)tiles * 8;
+    const int64_t items = (int64_t)tiles * 16;
     int64_t ctas = (items + kBwdWarps - 1) / kBwdWarps;
     if (ctas > 148 * kBwdCtasPerSm) ctas = 148 * kBwdCtasPerSm;
     blend_backward_kernel<<<(unsigned)ctas, kBwdWarps * 32, 0, s>>>(
         p.W, p.H, tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
         reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),
-        reinterpret_cast<const uint32_t*>(binning + L.b_vals_a), reinterpret_cast<const uint32_t*>(binning + L.b_vals_b),
+        reinterpret_cast<const uint2*>(binning + L.b_keys_a), reinterpret_cast<const uint2*>(binning + L.b_keys_b),
         reinterpret_cast<const float4*>(geom + L.g_rec), hdr, L.capacity, p.background,
         reinterpret_cast<const float*>(img + L.i_final_T), reinterpret_cast<const uint32_t*>(img + L.i_n_contrib), dL_dpix,
         dL_ddepth, dL_dalpha, accum);

@@ -1,13 +1,15 @@
 // Per-tile front-to-back alpha blending with depth and alpha-mask outputs
 // (reference forward.cu:261-383 renderCUDA).
 //
-// Work decomposition (ours): a 16x16 tile is covered by eight 8x4 pixel blocks;
-// one (tile, block) pair is a work item processed by ONE warp, independently of
-// every other warp (no block-level barrier anywhere).  The kernel is persistent:
+// Work decomposition (ours): a 16x16 tile is covered by sixteen 4x4 pixel
+// blocks; one (tile, block) pair is a work item processed by ONE warp,
+// independently of every other warp (no block-level barrier anywhere).  Two
+// lanes serve each pixel ("slots"): lane p and lane p+16 evaluate different
+// Gaussians of the pixel's list at the same time.  The kernel is persistent:
 // 148 x 5 CTAs of 4 warps pull items from a global queue ordered by decreasing
-// tile-list length (tile_order_kernel), so the few heavy tiles of a human-shaped
-// scene start first and spread over all SMs.  Per warp, Gaussians are staged in
-// batches of 64 packed 48-byte records
+// tile-list length (tile_order_kernel), so the few heavy tiles of a
+// human-shaped scene start first and spread over all SMs.  Per warp, Gaussians
+// are staged in batches of 64 packed 48-byte records
 //   {px,py,depth,radius | conic.xyz,opacity | r,g,b,cull-extent}
 // with cp.async (LDGSTS) into a 3-deep private shared-memory ring (list ids are
 // fetched one batch ahead of the record copies), so the inner loop never
@@ -15,13 +17,20 @@
 // contributing pair, forward.cu:360,362).
 //
 // Per warp and batch: (1) each lane tests one Gaussian's conservative bounding
-// box (pack_cull_extent) against the warp's 8x4 block; a ballot yields the
-// survivors.  (2) Survivors are evaluated four at a time: the power/exp/alpha
-// of the four are independent (ILP), only the transmittance recurrence is
-// sequential.  Skipped Gaussians are exactly those the reference's per-pixel
-// tests (power > 0, alpha < 1/255) would skip for every pixel of the block, and
-// the per-pair arithmetic is the reference's compiled sequence (pair_power,
-// expf, fma accumulation), so final_T / n_contrib are bit-exact.
+// box (pack_cull_extent) against the warp's 4x4 block; a ballot yields the
+// survivors -- at a Gaussian footprint of ~8 px a 4x4 block keeps less than
+// half of what an 8x4 block keeps, and every survivor costs 32 lanes of
+// arithmetic whether or not a pixel is touched.  (2) Survivors are taken four
+// at a time in list order; slot 0 evaluates the 1st and 3rd, slot 1 the 2nd and
+// 4th (power/exp/alpha, independent -> ILP), the alphas are exchanged with one
+// shuffle each, and both lanes run the transmittance recurrence over all four.
+// The five accumulators are split between the two lanes of a pixel (slot 0:
+// red, green, alpha-mask; slot 1: blue, depth), each accumulated in list order.
+// Skipped Gaussians are exactly those the reference's per-pixel tests
+// (power > 0, alpha < 1/255) would skip for every pixel of the block, and the
+// per-pair arithmetic is the reference's compiled sequence (pair_power, expf,
+// fma accumulation in list order), so images, final_T and n_contrib are
+// bit-exact.
 //
 // Bound: fp32 issue + MUFU.EX2 along the longest per-pixel list, not HBM
 // (algorithmic bytes 44*N + 28*X).
@@ -42,104 +51,165 @@ __device__ __forceinline__ void cp_async_wait()
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-constexpr int kBlendWarps = 4;    // warps per CTA (independent workers)
-constexpr int kBlendBatch = 64;   // Gaussians per staging round and warp
-constexpr int kBlendStages = 3;
-constexpr int kBlendCtasPerSm = 5;
+#ifndef GHR_FWD_WARPS
+#define GHR_FWD_WARPS 2
+#endif
+#ifndef GHR_FWD_STAGES
+#define GHR_FWD_STAGES 6
+#endif
+#ifndef GHR_FWD_CTAS
+#define GHR_FWD_CTAS 6
+#endif
+#ifdef GHR_TRACE  // tuning builds only (tools/build_variant.sh): per-item begin/end timestamps
+__device__ unsigned long long g_fwd_trace[1 << 16][8];
+__device__ __forceinline__ unsigned long long gtime()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ uint32_t smid()
+{
+    uint32_t r;
+    asm("mov.u32 %0, %%smid;" : "=r"(r));
+    return r;
+}
+#endif
+constexpr int kBlendWarps = GHR_FWD_WARPS;    // warps per CTA (independent workers)
+#ifndef GHR_FWD_BATCH
+#define GHR_FWD_BATCH 64
+#endif
+constexpr int kBlendBatch = GHR_FWD_BATCH;    // list entries per staging round and warp
+constexpr int kBlendStages = GHR_FWD_STAGES;  // depth of the per-warp staging ring
+constexpr int kBlendCtasPerSm = GHR_FWD_CTAS;
 
 __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(
     int W, int H, int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
-    const SortHeader* __restrict__ sh, const uint32_t* __restrict__ vals_a, const uint32_t* __restrict__ vals_b,
+    const SortHeader* __restrict__ sh, const uint2* __restrict__ ent_a, const uint2* __restrict__ ent_b,
     const float4* __restrict__ rec, ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
     float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha,
     float* __restrict__ final_T, uint32_t* __restrict__ n_contrib)
 {
     constexpr int BATCH = kBlendBatch, NSTAGE = kBlendStages, PER_LANE = BATCH / 32;
     __shared__ __align__(16) float4 s_all[kBlendWarps][NSTAGE][BATCH * 3];
+    __shared__ uint32_t s_keep_all[kBlendWarps][NSTAGE][PER_LANE];  // survivors of each staged round, one bit per entry
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t slot = lane >> 4, pl = lane & 15u;  // which of the pixel's two lanes; pixel inside the 4x4 block
     float4(*s_rec)[BATCH * 3] = s_all[warp];
+    uint32_t(*s_keep)[PER_LANE] = s_keep_all[warp];
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
-    const uint32_t* __restrict__ point_list = sh->sorted_sel ? vals_b : vals_a;
+    // {Gaussian id, 4x4-block mask} per list entry, written by tile_ranges_kernel into the key buffer the sort left unused
+    const uint2* __restrict__ entries = sh->sorted_sel ? ent_a : ent_b;
     const float bg0 = bg[0], bg1 = bg[1], bg2 = bg[2];
-    const uint32_t n_items = (uint32_t)tiles * 8u;
+    const uint32_t n_items = (uint32_t)tiles * 16u;
 
     for (;;) {
         uint32_t item = 0;
         if (lane == 0) item = atomicAdd(&hdr->blend_fwd_ticket, 1u);
         item = __shfl_sync(0xffffffffu, item, 0);
         if (item >= n_items) break;
-        const uint32_t tile = order[item >> 3], wb = item & 7u;  // which of the tile's eight 8x4 blocks
+#ifdef GHR_TRACE
+        const unsigned long long t_begin = gtime();
+        int trace_rounds = 0, trace_surv = 0, trace_steps = 0, trace_seq = 0;
+        long long c_wait = 0, c_cull = 0, c_eval = 0, c_mark = clock64();
+#define TRACE_LAP(acc) { const long long now_ = clock64(); acc += now_ - c_mark; c_mark = now_; }
+#else
+#define TRACE_LAP(acc)
+#endif
+        const uint32_t tile = order[item >> 4], wb = item & 15u;  // which of the tile's sixteen 4x4 blocks
         const uint32_t tile_x = tile % gx, tile_y = tile / gx;
-        const uint32_t bx0 = tile_x * GHR_TILE + (wb & 1u) * 8u, by0 = tile_y * GHR_TILE + (wb >> 1) * 4u;
-        const uint32_t pixx = bx0 + (lane & 7u), pixy = by0 + (lane >> 3);
+        const uint32_t bx0 = tile_x * GHR_TILE + (wb & 3u) * 4u, by0 = tile_y * GHR_TILE + (wb >> 2) * 4u;
+        const uint32_t pixx = bx0 + (pl & 3u), pixy = by0 + (pl >> 2);
         const bool inside = pixx < (uint32_t)W && pixy < (uint32_t)H;
         const float pxf = (float)pixx, pyf = (float)pixy;
-        const float rx0 = (float)bx0, rx1 = (float)(bx0 + 7u), ry0 = (float)by0, ry1 = (float)(by0 + 3u);
         const uint2 range = overflow ? make_uint2(0, 0) : ranges[tile];
         const int todo_total = (int)(range.y - range.x);
         const int rounds = (todo_total + BATCH - 1) / BATCH;
 
-        // Staging pipeline.  A record gather is two dependent L2 round trips (list entry -> record); the list
-        // entries of a round are therefore loaded into registers one round before their records are copied.
+        // Staging pipeline.  A record gather is two dependent L2 round trips (list entry -> record); the entries of a
+        // round are therefore loaded into registers one round before their records are copied.  Only the records of
+        // Gaussians whose block mask has this block's bit are copied; the round's survivor bits go to s_keep.
         uint32_t nid[PER_LANE];
         auto load_ids = [&](int round) {
 #pragma unroll
             for (int u = 0; u < PER_LANE; u++) {
                 const uint32_t k = range.x + (uint32_t)round * BATCH + lane + u * 32;
-                nid[u] = (round < rounds && k < range.y) ? point_list[k] : 0xFFFFFFFFu;
+                nid[u] = 0xFFFFFFFFu;
+                if (round < rounds && k < range.y) {
+                    const uint2 e = entries[k];
+                    if ((e.y >> wb) & 1u) nid[u] = e.x;
+                }
             }
         };
         auto stage = [&](int buf) {  // copies the records of the ids held in nid[]
 #pragma unroll
             for (int u = 0; u < PER_LANE; u++) {
-                if (nid[u] != 0xFFFFFFFFu) {
+                const bool keep = nid[u] != 0xFFFFFFFFu;
+                if (keep) {
                     const float4* src = rec + 3 * (size_t)nid[u];
                     float4* dst = &s_rec[buf][(lane + u * 32) * 3];
                     cp_async16(dst, src);
                     cp_async16(dst + 1, src + 1);
                     cp_async16(dst + 2, src + 2);
                 }
+                const uint32_t bits = __ballot_sync(0xffffffffu, keep);
+                if (lane == 0) s_keep[buf][u] = bits;
             }
             cp_async_commit();
         };
 
+        // Both lanes of a pixel carry T / done / last_contributor (identical); A0, A1, A2 are this lane's share of the
+        // accumulators: slot 0 -> red, green, alpha-mask; slot 1 -> blue, depth, (unused).
         bool done = !inside;
-        float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, wsum = 0.f, Dacc = 0.f;
+        float T = 1.0f, A0 = 0.f, A1 = 0.f, A2 = 0.f;
         uint32_t last_contributor = 0;
 
         if (rounds > 0) {
-            load_ids(0); stage(0);
-            load_ids(1); stage(1);
-            load_ids(2);
+            // prologue: all list entries of the first NSTAGE-1 rounds are requested before the first record copy
+            uint32_t pre[NSTAGE - 1][PER_LANE];
+#pragma unroll
+            for (int q = 0; q < NSTAGE - 1; q++) {
+                load_ids(q);
+#pragma unroll
+                for (int u = 0; u < PER_LANE; u++) pre[q][u] = nid[u];
+            }
+#pragma unroll
+            for (int q = 0; q < NSTAGE - 1; q++) {
+#pragma unroll
+                for (int u = 0; u < PER_LANE; u++) nid[u] = pre[q][u];
+                stage(q);
+            }
+            load_ids(NSTAGE - 1);
         }
         int toDo = todo_total;
         for (int i = 0; i < rounds; i++, toDo -= BATCH) {
             const int buf = i % NSTAGE;
-            stage((i + 2) % NSTAGE);  // records of round i+2 (an empty group past the end keeps the count uniform)
-            load_ids(i + 3);
-            cp_async_wait<2>();       // this lane's copies for rounds <= i have landed
+            stage((i + NSTAGE - 1) % NSTAGE);  // records of round i+NSTAGE-1 (an empty group past the end keeps the count uniform)
+            load_ids(i + NSTAGE);
+            cp_async_wait<NSTAGE - 1>();       // this lane's copies for rounds <= i have landed
             __syncwarp();             // ... and everybody else's
             if (__all_sync(0xffffffffu, done)) break;  // forward.cu:313-315, per block instead of per tile
+#ifdef GHR_TRACE
+            trace_rounds++;
+#endif
+            TRACE_LAP(c_wait)
             const int n = min(BATCH, toDo);
             const float4* r = s_rec[buf];
+            const float* rf = reinterpret_cast<const float*>(r);
             const uint32_t base = (uint32_t)i * BATCH;  // list position of r[0]
             for (int g = 0; g < n; g += 32) {
-                // (1) conservative bounding-box cull, one Gaussian per lane
-                const int jj = g + (int)lane;
-                bool keep = false;
-                if (jj < n) {
-                    const float4 c0 = r[3 * jj];
-                    float ex, ey;
-                    unpack_cull_extent(__float_as_uint(r[3 * jj + 2].w), ex, ey);
-                    const float ddx = fmaxf(fmaxf(rx0 - c0.x, c0.x - rx1), 0.0f);
-                    const float ddy = fmaxf(fmaxf(ry0 - c0.y, c0.y - ry1), 0.0f);
-                    keep = !(ddx > ex) && !(ddy > ey);
-                }
-                uint32_t mask = __ballot_sync(0xffffffffu, keep);
-                // (2) survivors, four at a time
+                uint32_t mask = s_keep[buf][g >> 5];  // (1) survivors of this group of 32 entries (block mask, see stage)
+#ifdef GHR_TRACE
+                trace_surv += __popc(mask);
+#endif
+                TRACE_LAP(c_cull)
+                // (2) survivors, four at a time in list order: j[0] j[2] are evaluated by slot 0, j[1] j[3] by slot 1
                 while (mask) {
+#ifdef GHR_TRACE
+                    trace_steps++;
+#endif
                     int j[4];
                     bool v[4];
 #pragma unroll
@@ -148,54 +218,92 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(
                         j[u] = v[u] ? g + __ffs(mask) - 1 : j[0];
                         mask &= mask - 1;
                     }
-                    float alpha[4], depth[4], c0[4], c1[4], c2[4];
-                    bool ok[4];
+                    float mine[2];
 #pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        const float4 r0 = r[3 * j[u]], r1 = r[3 * j[u] + 1], r2 = r[3 * j[u] + 2];
+                    for (int u = 0; u < 2; u++) {
+                        const int jm = slot ? j[2 * u + 1] : j[2 * u];
+                        const bool vm = slot ? v[2 * u + 1] : v[2 * u];
+                        const float4 r0 = r[3 * jm], r1 = r[3 * jm + 1];
                         const float dx = __fsub_rn(r0.x, pxf), dy = __fsub_rn(r0.y, pyf);
                         const float power = pair_power(dx, dy, r1.x, r1.y, r1.z);
-                        alpha[u] = fminf(0.99f, __fmul_rn(r1.w, expf(power)));
-                        ok[u] = v[u] && !(power > 0.0f) && !(alpha[u] < 1.0f / 255.0f);
-                        depth[u] = r0.z; c0[u] = r2.x; c1[u] = r2.y; c2[u] = r2.z;
+                        const float al = fminf(0.99f, __fmul_rn(r1.w, expf(power)));
+                        mine[u] = (vm && !(power > 0.0f) && !(al < 1.0f / 255.0f)) ? al : 0.0f;  // 0 = skipped
+                    }
+                    float alpha[4];
+#pragma unroll
+                    for (int u = 0; u < 2; u++) {
+                        const float theirs = __shfl_xor_sync(0xffffffffu, mine[u], 16);
+                        alpha[2 * u] = slot ? theirs : mine[u];
+                        alpha[2 * u + 1] = slot ? mine[u] : theirs;
+                    }
+                    // Sequential part, straight-line and branch-free: only T -> test_T -> T is a dependent chain
+                    // (one multiply and one compare per Gaussian); everything else is computed up front.
+                    float x0[4], x1[4], om[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const float4 r2 = r[3 * j[u] + 2];
+                        const float depth = rf[12 * j[u] + 2];
+                        x0[u] = __fmul_rn(alpha[u], slot ? r2.z : r2.x);
+                        x1[u] = __fmul_rn(alpha[u], slot ? depth : r2.y);
+                        om[u] = __fsub_rn(1.0f, alpha[u]);
                     }
 #pragma unroll
                     for (int u = 0; u < 4; u++) {
-                        if (ok[u] && !done) {
-                            const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha[u]));
-                            if (test_T < 0.0001f) {
-                                done = true;
-                            } else {
-                                C0 = __fmaf_rn(T, __fmul_rn(alpha[u], c0[u]), C0);
-                                C1 = __fmaf_rn(T, __fmul_rn(alpha[u], c1[u]), C1);
-                                C2 = __fmaf_rn(T, __fmul_rn(alpha[u], c2[u]), C2);
-                                wsum = __fmaf_rn(T, alpha[u], wsum);
-                                Dacc = __fmaf_rn(T, __fmul_rn(alpha[u], depth[u]), Dacc);
-                                T = test_T;
-                                last_contributor = base + (uint32_t)j[u] + 1u;
-                            }
-                        }
+                        const bool act = alpha[u] > 0.0f && !done;
+                        const float test_T = __fmul_rn(T, om[u]);
+                        const bool stop = act && test_T < 0.0001f;
+                        const bool acc = act && !stop;
+                        done = done || stop;
+                        A0 = acc ? __fmaf_rn(T, x0[u], A0) : A0;
+                        A1 = acc ? __fmaf_rn(T, x1[u], A1) : A1;
+                        A2 = acc ? __fmaf_rn(T, alpha[u], A2) : A2;
+                        last_contributor = acc ? base + (uint32_t)j[u] + 1u : last_contributor;
+                        T = acc ? test_T : T;
                     }
                     if (__all_sync(0xffffffffu, done)) { mask = 0; g = n; }
                 }
+                TRACE_LAP(c_eval)
             }
-            __syncwarp();  // buffer `buf` is re-filled by the stage() of the next iteration (round i+3)
+            __syncwarp();  // buffer `buf` is re-filled by the stage() of the next iteration (round i+NSTAGE)
         }
         cp_async_wait<0>();
         __syncwarp();
 
         if (inside) {
             const size_t pix = (size_t)pixy * W + pixx, HW = (size_t)H * W;
-            final_T[pix] = T;
-            n_contrib[pix] = last_contributor;
-            out_color[pix] = __fmaf_rn(T, bg0, C0);
-            out_color[HW + pix] = __fmaf_rn(T, bg1, C1);
-            out_color[2 * HW + pix] = __fmaf_rn(T, bg2, C2);
-            out_alpha[pix] = wsum;
-            out_depth[pix] = Dacc;
+            if (slot == 0) {
+                final_T[pix] = T;
+                n_contrib[pix] = last_contributor;
+                out_color[pix] = __fmaf_rn(T, bg0, A0);
+                out_color[HW + pix] = __fmaf_rn(T, bg1, A1);
+                out_alpha[pix] = A2;
+            } else {
+                out_color[2 * HW + pix] = __fmaf_rn(T, bg2, A0);
+                out_depth[pix] = A1;
+            }
         }
+#ifdef GHR_TRACE
+        if (lane == 0 && item < (1u << 16)) {
+            g_fwd_trace[item][0] = t_begin;
+            g_fwd_trace[item][1] = gtime();
+            g_fwd_trace[item][2] = ((unsigned long long)smid() << 32) | (uint32_t)todo_total;
+            g_fwd_trace[item][3] = (unsigned long long)trace_rounds;
+            g_fwd_trace[item][4] = ((unsigned long long)trace_surv << 32) | (uint32_t)trace_steps;
+            g_fwd_trace[item][5] = (unsigned long long)c_wait;
+            g_fwd_trace[item][6] = (unsigned long long)c_cull;
+            g_fwd_trace[item][7] = (unsigned long long)c_eval;
+        }
+#endif
     }
 }
+#ifdef GHR_TRACE
+}  // namespace ghr
+extern "C" int ghr_debug_fwd_trace(void* out, size_t bytes)
+{
+    return (int)cudaMemcpyFromSymbol(out, ghr::g_fwd_trace, bytes);
+}
+namespace ghr {
+#endif
 
 cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, const char* binning, char* img,
                                  const ghr_layout& L, float* out_color, float* out_depth, float* out_alpha,
@@ -204,7 +312,7 @@ cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, c
     StageTimer timer(GHR_STAGE_BLEND_FWD, s);
     count_launch();
     const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
-    const int64_t items = (int64_t)tiles * 8;
+    const int64_t items = (int64_t)tiles * 16;
     int64_t ctas = (items + kBlendWarps - 1) / kBlendWarps;
     if (ctas > 148 * kBlendCtasPerSm) ctas = 148 * kBlendCtasPerSm;
     const int64_t capacity = L.capacity;
@@ -214,7 +322,7 @@ cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, c
     blend_forward_kernel<<<(unsigned)ctas, kBlendWarps * 32, 0, s>>>(
         p.W, p.H, tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
         reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),
-        reinterpret_cast<const uint32_t*>(binning + L.b_vals_a), reinterpret_cast<const uint32_t*>(binning + L.b_vals_b),
+        reinterpret_cast<const uint2*>(binning + L.b_keys_a), reinterpret_cast<const uint2*>(binning + L.b_keys_b),
         reinterpret_cast<const float4*>(geom + L.g_rec), hdr, capacity, p.background, out_color,
         out_depth, out_alpha, reinterpret_cast<float*>(img + L.i_final_T), reinterpret_cast<uint32_t*>(img + L.i_n_contrib));
     return cudaGetLastError();

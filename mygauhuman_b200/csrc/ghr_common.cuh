@@ -298,6 +298,56 @@ __device__ __forceinline__ void unpack_cull_extent(uint32_t w, float& ex, float&
     ey = __half2float(__ushort_as_half((unsigned short)(w >> 16)));
 }
 
+// Exact ellipse-vs-pixel-block refinement of the bounding-box test: the minimum over the block of
+//   q(u,v) = a u^2 + 2 b u v + c v^2,   (u,v) = centre - pixel,
+// (the reference's power is -q/2) is compared with the alpha >= 1/255 level 2 ln(255 o).  A convex quadratic
+// whose unconstrained minimum (the centre) lies outside the block attains its block minimum on one of the four edges,
+// where it is a clamped 1-D parabola.  Conservative by 0.05 in ln(alpha) plus 1e-5 of the term magnitudes (fp32
+// rounding of the reference's own power), and anything indefinite / NaN is kept, so nothing the reference would blend
+// into some pixel of the block is dropped: final_T / n_contrib / images stay bit-exact.
+struct CullQuad {
+    float a, b, c, tau, nb_c, nb_a;
+    bool definite;  // false: indefinite / NaN conic, never culled by the exact test
+};
+__device__ __forceinline__ CullQuad cull_quad(float a, float b, float c, float opacity)
+{
+    CullQuad q;
+    q.a = a; q.b = b; q.c = c;
+    q.definite = (a > 0.0f) && (c > 0.0f) && (a * c > b * b);
+    q.tau = 2.0f * (__logf(255.0f * opacity) + 0.05f);
+    q.nb_c = __fdividef(-b, c);
+    q.nb_a = __fdividef(-b, a);
+    return q;
+}
+__device__ __forceinline__ bool cull_keep_exact(const CullQuad& g, float cx, float cy, float rx0, float rx1, float ry0,
+                                                float ry1)
+{
+    const float u0 = cx - rx1, u1 = cx - rx0, v0 = cy - ry1, v1 = cy - ry0;  // u in [u0,u1], v in [v0,v1]
+    if (u0 <= 0.0f && u1 >= 0.0f && v0 <= 0.0f && v1 >= 0.0f) return true;   // centre inside the block
+    if (!g.definite) return true;
+    const float a = g.a, b2 = 2.0f * g.b, c = g.c;
+    float qmin;
+    {
+        const float v = fminf(fmaxf(g.nb_c * u0, v0), v1);
+        qmin = fmaf(a * u0, u0, fmaf(b2 * u0, v, c * v * v));
+    }
+    {
+        const float v = fminf(fmaxf(g.nb_c * u1, v0), v1);
+        qmin = fminf(qmin, fmaf(a * u1, u1, fmaf(b2 * u1, v, c * v * v)));
+    }
+    {
+        const float u = fminf(fmaxf(g.nb_a * v0, u0), u1);
+        qmin = fminf(qmin, fmaf(c * v0, v0, fmaf(b2 * v0, u, a * u * u)));
+    }
+    {
+        const float u = fminf(fmaxf(g.nb_a * v1, u0), u1);
+        qmin = fminf(qmin, fmaf(c * v1, v1, fmaf(b2 * v1, u, a * u * u)));
+    }
+    const float mu = fmaxf(fabsf(u0), fabsf(u1)), mv = fmaxf(fabsf(v0), fabsf(v1));
+    const float mag = fmaf(a * mu, mu, fmaf(fabsf(b2) * mu, mv, c * mv * mv));
+    return !(qmin - 1e-5f * mag > g.tau);
+}
+
 // ---- decoupled look-back status words -------------------------------------
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p)
 {

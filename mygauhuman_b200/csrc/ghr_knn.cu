@@ -7,17 +7,17 @@
 // a uniform grid whose cell size is chosen from the AABB and P (about 2 points
 // per cell), cells are counted/scanned/filled on the device, and each point
 // searches rings of cells around its own cell until the 3rd-best distance is
-// provably final.  Small inputs (P <= kBruteMax, which covers the 6,890-vertex
-// SMPL initialisation the reference actually runs) use a shared-memory tiled
-// all-pairs kernel instead: 47M pair evaluations is a few microseconds on
-// 148 SMs and needs no auxiliary structure, no sync and no allocation.
+// provably final.  Small inputs (P <= kBruteMax = 4096) use a shared-memory
+// tiled all-pairs kernel instead, which needs no auxiliary structure; measured
+// on B200 the grid wins from a few thousand points on (6,890 points: grid
+// faster than the 0.41 ms all-pairs pass; 50,000: 3.5 ms all-pairs).
 #include <float.h>
 #include "ghr_common.cuh"
 #include "ghr_internal.h"
 
 namespace ghr {
 
-constexpr int kBruteMax = 1 << 16;
+constexpr int kBruteMax = 1 << 12;
 constexpr int kKnnTile = 1024;
 
 __device__ __forceinline__ void kbest3(float d, float& b0, float& b1, float& b2)

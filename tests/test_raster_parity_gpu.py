@@ -207,7 +207,7 @@ def test_optimistic_launch_recovers_from_a_small_guess():
         assert torch.equal(a, b)
     g0 = Cm.ours_backward(tb, ref_big); g1 = Cm.ours_backward(tb, fw)
     for a, b in zip(g0, g1):
-        _grad_close("optimistic", _np(b), _np(a), rel=1e-5)
+        _grad_close("optimistic", _np(b), _np(a), rel=1e-4)  # two runs of the same kernels: fp32 atomic order differs
     fw2 = Cm.ours_forward(tb)              # guess now large enough: single pass
     assert fw2[0] == ref_big[0] and torch.equal(fw2[1], ref_big[1])
 

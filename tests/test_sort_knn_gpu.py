@@ -69,7 +69,7 @@ def test_onesweep_full_64bit_and_odd_bits():
         assert np.array_equal(v.cpu().numpy(), order.astype(np.int32))
 
 
-@pytest.mark.parametrize("P", [1, 2, 3, 4, 50, 6890, 70000, 200000])
+@pytest.mark.parametrize("P", [1, 2, 3, 4, 50, 3000, 4096, 4097, 6890, 70000, 200000])
 def test_dist2_knn3(P):
     import oracle as O
     from oracle import ref_cuda
