@@ -55,7 +55,7 @@ __device__ __forceinline__ void cp_async_wait()
 #define GHR_FWD_WARPS 2
 #endif
 #ifndef GHR_FWD_STAGES
-#define GHR_FWD_STAGES 6
+#define GHR_FWD_STAGES 3
 #endif
 #ifndef GHR_FWD_CTAS
 #define GHR_FWD_CTAS 6
@@ -77,7 +77,7 @@ __device__ __forceinline__ uint32_t smid()
 #endif
 constexpr int kBlendWarps = GHR_FWD_WARPS;    // warps per CTA (independent workers)
 #ifndef GHR_FWD_BATCH
-#define GHR_FWD_BATCH 64
+#define GHR_FWD_BATCH 128
 #endif
 constexpr int kBlendBatch = GHR_FWD_BATCH;    // list entries per staging round and warp
 constexpr int kBlendStages = GHR_FWD_STAGES;  // depth of the per-warp staging ring

@@ -74,6 +74,7 @@ class SMPLDeformer:
                                self.joint_shapedirs.data_ptr(), self.parents.data_ptr())
         self._grid_key, self._grid = None, None
         self._pose_key, self._pose_cached = None, None
+        self._side_stream = torch.cuda.Stream(device=self.device) if torch.cuda.is_available() else None
 
     # ---- pose stage --------------------------------------------------------
     def pose_buffer(self, params, correct_Rs=None):
@@ -117,7 +118,7 @@ class SMPLDeformer:
         return off
 
     # ---- nearest vertex ----------------------------------------------------
-    def nearest_vertex(self, t_vertices, query):
+    def nearest_vertex(self, t_vertices, query, out=None):
         """Exact nearest vertex index [P] int32 (the reference's knn_cuda KNN(k=1), gaussian_model.py:775)."""
         tv = _f32c(t_vertices.detach()).reshape(-1, 3)
         key = (tv.data_ptr(), t_vertices._version, tv.shape[0])
@@ -129,7 +130,7 @@ class SMPLDeformer:
                       "ghr_vertex_grid_build")
                 self._grid, self._grid_key, self._grid_src = ws, key, tv
             q = _f32c(query.detach()).reshape(-1, 3)
-            vid = torch.empty(q.shape[0], dtype=torch.int32, device=self.device)
+            vid = torch.empty(q.shape[0], dtype=torch.int32, device=self.device) if out is None else out
             check(lib().ghr_nearest_vertex(q.shape[0], q.data_ptr(), self._grid_key[2], self._grid.data_ptr(), vid.data_ptr(),
                                            _stream()),
                   "ghr_nearest_vertex")
@@ -206,9 +207,24 @@ class _DeformFn(torch.autograd.Function):
         M = 0 if shs is None else shs.shape[1]
         cam = None if campos is None else _f32c(campos.detach().to(dev)).reshape(-1)
         pose_big = self._big_pose_buffer(t_params)
+        # The nearest-vertex search (depends on xyz only) runs on a side stream next to the pose chain and the pose
+        # blend-shape offsets (depend on the pose only); both are short, latency-bound kernels.  Fork/join through
+        # stream waits, so the overlap is kept when the step is captured into a CUDA graph.  Every buffer the side
+        # stream touches is allocated on the caller's stream beforehand.
+        vid = torch.empty(P, dtype=torch.int32, device=dev)
+        tv = _f32c(t_vertices.detach())
+        cur = torch.cuda.current_stream(dev)
+        side = self._side_stream
+        if P and side is not None:
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                self.nearest_vertex(tv, xyz_c, out=vid)
         pose_tgt = self.pose_buffer(params, correct_Rs)
         off = self.vertex_offsets(pose_big, pose_tgt, params["shapes"])
-        vid = self.nearest_vertex(t_vertices, xyz_c)
+        if P and side is not None:
+            cur.wait_stream(side)
+        elif P:
+            self.nearest_vertex(tv, xyz_c, out=vid)
 
         p = DeformParams()
         p.P, p.V, p.sh_degree, p.M = P, self.V, sh_degree, M
