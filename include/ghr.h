@@ -271,6 +271,14 @@ typedef struct ghr_deform_params {
     const float* rotations;      /* [P,4] raw quaternions (normalised inside)           */
     const float* shs;            /* [P,M,3] or NULL                                     */
     const float* campos;         /* [3]                                                 */
+    /* Optional fused activations (reference get_scaling = exp, get_opacity = sigmoid, gaussian_model.py:152-175).
+     * All zero / NULL = plain behaviour. */
+    int32_t scales_are_log;      /* 1: `scales` holds log-scales; exp() is applied inside and dL_dscales is returned
+                                    with respect to the log-scales                                                  */
+    const float* opacity_logits; /* [P] or NULL                                                                     */
+    float* opacity_out;          /* forward: [P] sigmoid(opacity_logits)                                            */
+    const float* dL_dopacity;    /* backward: [P] incoming gradient of opacity_out, or NULL (= zero)                */
+    float* dL_dopacity_logits;   /* backward: [P] written when opacity_logits is given                              */
 } ghr_deform_params;
 
 int ghr_lbs_deform_forward(const ghr_deform_params* prm, float* smpl_pts /*[P,3]|NULL*/, float* world_pts /*[P,3]*/,

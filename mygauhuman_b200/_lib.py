@@ -53,7 +53,9 @@ class DeformParams(C.Structure):
                 ("scale_modifier", C.c_float), ("xyz", c_f32p), ("normals", c_f32p), ("vert_ids", C.c_void_p),
                 ("weights", c_f32p), ("lbs_offsets", c_f32p), ("lbs_stride_p", C.c_int64), ("lbs_stride_j", C.c_int64),
                 ("vertex_offsets", c_f32p), ("pose_big", c_f32p), ("pose_target", c_f32p), ("scales", c_f32p),
-                ("rotations", c_f32p), ("shs", c_f32p), ("campos", c_f32p)]
+                ("rotations", c_f32p), ("shs", c_f32p), ("campos", c_f32p), ("scales_are_log", C.c_int32),
+                ("opacity_logits", c_f32p), ("opacity_out", c_f32p), ("dL_dopacity", c_f32p),
+                ("dL_dopacity_logits", c_f32p)]
 
 
 POSE_FLOATS = 1536

@@ -325,6 +325,7 @@ int ghr_lbs_deform_forward(const ghr_deform_params* prm, float* smpl_pts, float*
     if (!world_pts || !transforms) return GHR_ERR_BAD_ARG;
     if (world_normals && !prm->normals) return GHR_ERR_BAD_ARG;
     if (cov3D && !prm->scales) return GHR_ERR_BAD_ARG;
+    if (prm->opacity_logits && !prm->opacity_out) return GHR_ERR_BAD_ARG;
     if (colors && !prm->shs) return GHR_ERR_BAD_ARG;
     DeformOut o{smpl_pts, world_pts, bweights, transforms, translation, world_normals, cov3D, colors, clamped};
     return check_cuda(launch_lbs_deform_forward(*prm, o, (cudaStream_t)stream), "lbs_deform_forward");

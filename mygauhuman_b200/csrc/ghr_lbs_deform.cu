@@ -200,13 +200,16 @@ __global__ void __launch_bounds__(128) lbs_deform_forward_kernel(const ghr_defor
 #pragma unroll
         for (int c = 0; c < 3; c++) o.translation[3 * (size_t)idx + c] = tw[c] + s.Th[c];
     }
+    if (p.opacity_logits && p.opacity_out)  // get_opacity (gaussian_model.py:174): sigmoid
+        p.opacity_out[idx] = 1.0f / (1.0f + expf(-p.opacity_logits[idx]));
     if (o.cov3D && p.scales) {
         // L = R(q) diag(mod*s); Sigma = L L^T; Sigma' = Tw Sigma Tw^T (gaussian_model.py:35-42)
         const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
         float Rq[9], inv_norm;
         quat_rot(q.x, q.y, q.z, q.w, Rq, inv_norm);
-        const float sc[3] = {p.scale_modifier * p.scales[3 * idx], p.scale_modifier * p.scales[3 * idx + 1],
-                             p.scale_modifier * p.scales[3 * idx + 2]};
+        float sa[3] = {p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]};
+        if (p.scales_are_log) { sa[0] = expf(sa[0]); sa[1] = expf(sa[1]); sa[2] = expf(sa[2]); }
+        const float sc[3] = {p.scale_modifier * sa[0], p.scale_modifier * sa[1], p.scale_modifier * sa[2]};
         float L[9], TL[9];
 #pragma unroll
         for (int r = 0; r < 3; r++)
@@ -290,6 +293,10 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
             }
         }
 
+        if (p.opacity_logits && p.dL_dopacity_logits) {
+            const float sg = 1.0f / (1.0f + expf(-p.opacity_logits[idx]));
+            p.dL_dopacity_logits[idx] = p.dL_dopacity ? p.dL_dopacity[idx] * sg * (1.0f - sg) : 0.0f;
+        }
         // ---- covariance: Sigma' = (Tw L)(Tw L)^T, L = R(q^) diag(mod*s) ----
         if (p.scales && g.d_scales) {
             float dsc[3] = {0.f, 0.f, 0.f}, dq[4] = {0.f, 0.f, 0.f, 0.f};
@@ -297,8 +304,9 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
                 const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
                 float Rq[9], inv_norm;
                 quat_rot(q.x, q.y, q.z, q.w, Rq, inv_norm);
-                const float sc[3] = {p.scale_modifier * p.scales[3 * idx], p.scale_modifier * p.scales[3 * idx + 1],
-                                     p.scale_modifier * p.scales[3 * idx + 2]};
+                float sa[3] = {p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]};
+                if (p.scales_are_log) { sa[0] = expf(sa[0]); sa[1] = expf(sa[1]); sa[2] = expf(sa[2]); }
+                const float sc[3] = {p.scale_modifier * sa[0], p.scale_modifier * sa[1], p.scale_modifier * sa[2]};
                 float L[9], TL[9];
 #pragma unroll
                 for (int r = 0; r < 3; r++)
@@ -334,6 +342,7 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
                 dq[2] = (dy_ - y * dot) * inv_norm; dq[3] = (dz_ - z * dot) * inv_norm;
 #pragma unroll
                 for (int c = 0; c < 3; c++) dsc[c] *= p.scale_modifier;
+                if (p.scales_are_log) { dsc[0] *= sa[0]; dsc[1] *= sa[1]; dsc[2] *= sa[2]; }  // d exp(l) / dl = exp(l)
             }
             g.d_scales[3 * idx] = dsc[0]; g.d_scales[3 * idx + 1] = dsc[1]; g.d_scales[3 * idx + 2] = dsc[2];
             if (g.d_rot) reinterpret_cast<float4*>(g.d_rot)[idx] = make_float4(dq[0], dq[1], dq[2], dq[3]);

@@ -80,12 +80,20 @@ __global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint
     __syncthreads();
     const int lastbits = bits - (passes - 1) * kRadixBits;
     const uint32_t lastmask = (1u << lastbits) - 1u;  // lastbits in [1, kRadixBits]
-    for (int64_t i = (int64_t)blockIdx.x * kSortThreads + t; i < N; i += (int64_t)gridDim.x * kSortThreads) {
-        const uint64_t k = keys[i];
-        for (int p = 0; p < passes; p++) {
-            uint32_t d = (uint32_t)(k >> (p * kRadixBits)) & (uint32_t)(kRadix - 1);
-            if (p == passes - 1) d &= lastmask;
-            atomicAdd(&s_hist[p * kRadix + d], 1u);
+    // four independent key loads in flight per thread
+    const int64_t stride = (int64_t)gridDim.x * kSortThreads;
+    for (int64_t i0 = (int64_t)blockIdx.x * kSortThreads + t; i0 < N; i0 += 4 * stride) {
+        uint64_t k[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) k[u] = (i0 + u * stride < N) ? keys[i0 + u * stride] : 0ull;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            if (i0 + u * stride >= N) break;
+            for (int p = 0; p < passes; p++) {
+                uint32_t d = (uint32_t)(k[u] >> (p * kRadixBits)) & (uint32_t)(kRadix - 1);
+                if (p == passes - 1) d &= lastmask;
+                atomicAdd(&s_hist[p * kRadix + d], 1u);
+            }
         }
     }
     __syncthreads();
@@ -282,7 +290,7 @@ cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev
     const int passes = sort_passes_for(bits);
     const int items = sort_items_per_thread(capacity);
     const int64_t tiles = sort_tiles(capacity);
-    int64_t hg = (capacity + kSortThreads * 8 - 1) / (kSortThreads * 8);
+    int64_t hg = (capacity + kSortThreads * 4 - 1) / (kSortThreads * 4);
     const int hgrid = (int)(hg < 148 * 4 ? hg : 148 * 4);
     sort_histogram_kernel<<<hgrid, kSortThreads, 0, s>>>(keys_a, n_dev, capacity, bits, passes, hdr);
     count_launch(1 + passes);

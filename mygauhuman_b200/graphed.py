@@ -88,10 +88,11 @@ class GraphedRenderStep:
     def _eager(self, vec, loss_inputs, capacity, reduce=False):
         L = self.leaves
         camd, pose = unpack_view(vec)
+        # exp / sigmoid of the raw parameters are fused into the deform kernels (no separate ATen launches)
         d = self.deformer.deform_gaussians(L["xyz"], pose, self.big, self.t_vertices, normals=L.get("normals"),
-                                           scaling=torch.exp(L["log_scale"]), rotation=L["rotation"],
+                                           log_scaling=L["log_scale"], rotation=L["rotation"],
                                            scaling_modifier=self.mod, features=L["features"], sh_degree=self.sh_degree,
-                                           campos=camd["campos"])
+                                           campos=camd["campos"], opacity_logit=L["opacity_logit"])
         rs = dgr.GaussianRasterizationSettings(
             image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=self.bg,
             scale_modifier=self.mod, viewmatrix=camd["view"], projmatrix=camd["proj"], sh_degree=self.sh_degree,
@@ -100,7 +101,7 @@ class GraphedRenderStep:
         _C.set_sync_free_capacity(capacity)
         try:
             color, radii, depth, alpha = dgr.rasterize_gaussians(
-                d["means3D"], means2D, _C_absent(), d["colors"], torch.sigmoid(L["opacity_logit"]), _C_absent(),
+                d["means3D"], means2D, _C_absent(), d["colors"], d["opacity"], _C_absent(),
                 _C_absent(), d["cov3D"], rs)
         finally:
             _C.set_sync_free_capacity(None)

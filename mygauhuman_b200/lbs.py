@@ -139,13 +139,21 @@ class SMPLDeformer:
     # ---- the operators -----------------------------------------------------
     def deform_gaussians(self, xyz, params, t_params, t_vertices, normals=None, lbs_weights=None, correct_Rs=None,
                          scaling=None, rotation=None, scaling_modifier=1.0, features=None, sh_degree=0, campos=None,
-                         return_transl=False):
+                         return_transl=False, log_scaling=None, opacity_logit=None):
         """Fused LBS + world covariance + view-dependent colour.  xyz [P,3]; lbs_weights [P,24] (any strides);
         scaling [P,3] (activated), rotation [P,4] (raw), features [P,M,3].
-        Returns dict(smpl_pts, means3D, bweights, transforms, translation, world_normals, cov3D, colors)."""
+        Optionally the reference's parameter activations are fused in as well: pass `log_scaling` [P,3] instead of
+        `scaling` (exp, get_scaling) and/or `opacity_logit` [P,1] (sigmoid, get_opacity -> returned as "opacity").
+        Returns dict(smpl_pts, means3D, bweights, transforms, translation, world_normals, cov3D, colors, opacity)."""
+        if log_scaling is not None:
+            if scaling is not None:
+                raise ValueError("pass either scaling or log_scaling")
+            scaling = log_scaling
         out = _DeformFn.apply(self, params, t_params, t_vertices, float(scaling_modifier), int(sh_degree), campos,
-                              bool(return_transl), xyz, normals, lbs_weights, correct_Rs, scaling, rotation, features)
-        keys = ("smpl_pts", "means3D", "bweights", "transforms", "translation", "world_normals", "cov3D", "colors")
+                              bool(return_transl), log_scaling is not None, xyz, normals, lbs_weights, correct_Rs, scaling,
+                              rotation, features, opacity_logit)
+        keys = ("smpl_pts", "means3D", "bweights", "transforms", "translation", "world_normals", "cov3D", "colors",
+                "opacity")
         return dict(zip(keys, out))
 
     def coarse_deform_c2source(self, query_pts, params, t_params, t_vertices, lbs_weights=None, correct_Rs=None,
@@ -189,10 +197,11 @@ class _DeformFn(torch.autograd.Function):
     """ghr_lbs_deform_forward / _backward (+ ghr_lbs_pose_backward for correct_Rs)."""
 
     @staticmethod
-    def forward(ctx, deformer, params, t_params, t_vertices, scaling_modifier, sh_degree, campos, return_transl, xyz,
-                normals, lbs_weights, correct_Rs, scaling, rotation, features):
+    def forward(ctx, deformer, params, t_params, t_vertices, scaling_modifier, sh_degree, campos, return_transl,
+                scales_are_log, xyz, normals, lbs_weights, correct_Rs, scaling, rotation, features, opacity_logit):
         self = deformer
         dev = self.device
+        ctx.set_materialize_grads(False)  # unused outputs arrive as None in backward instead of zero-filled tensors
         if not xyz.is_cuda:
             raise RuntimeError("libghr: tensor arguments must live on a CUDA device (there is no CPU fallback)")
         P = xyz.shape[0]
@@ -235,6 +244,8 @@ class _DeformFn(torch.autograd.Function):
             p.lbs_stride_p, p.lbs_stride_j = lw.stride(0), lw.stride(1)
         p.vertex_offsets, p.pose_big, p.pose_target = off.data_ptr(), pose_big.data_ptr(), pose_tgt.data_ptr()
         p.scales, p.rotations, p.shs, p.campos = _ptr(sc), _ptr(rot), _ptr(shs), _ptr(cam)
+        p.scales_are_log = int(bool(scales_are_log) and sc is not None)
+        ol = None if opacity_logit is None else _f32c(opacity_logit.detach())
 
         f = dict(dtype=torch.float32, device=dev)
         smpl_pts = torch.empty(P, 3, **f)
@@ -246,6 +257,10 @@ class _DeformFn(torch.autograd.Function):
         cov = torch.empty(P, 6, **f) if sc is not None else None
         col = torch.empty(P, 3, **f) if shs is not None else None
         clamped = torch.empty(P, dtype=torch.uint8, device=dev) if shs is not None else None
+        opac = None
+        if ol is not None:
+            opac = torch.empty(ol.shape, **f)
+            p.opacity_logits, p.opacity_out = ol.data_ptr() if P else None, opac.data_ptr() if P else None
         if P:
             with _lib.on_device(dev):
                 check(lib().ghr_lbs_deform_forward(C.byref(p), smpl_pts.data_ptr(), world.data_ptr(), bw.data_ptr(),
@@ -253,16 +268,17 @@ class _DeformFn(torch.autograd.Function):
                                                    _ptr(clamped), _stream()), "ghr_lbs_deform_forward")
         ctx.deformer, ctx.p = self, p
         ctx.keep = (xyz_c, nrm, lw, sc, rot, shs, cam, pose_big, pose_tgt, off, vid, clamped)
+        ctx.ol = ol
         ctx.correct_Rs = correct_Rs
         ctx.has = (normals is not None, lbs_weights is not None, correct_Rs is not None, scaling is not None,
                    rotation is not None, features is not None)
         ctx.lw_shape = None if lbs_weights is None else lbs_weights.shape
-        outs = (smpl_pts, world, bw, transforms, transl, wn, cov, col)
+        outs = (smpl_pts, world, bw, transforms, transl, wn, cov, col, opac)
         ctx.mark_non_differentiable(*[t for t in (smpl_pts, bw, transl) if t is not None])
         return outs
 
     @staticmethod
-    def backward(ctx, g_smpl, g_world, g_bw, g_transforms, g_transl, g_wn, g_cov, g_col):
+    def backward(ctx, g_smpl, g_world, g_bw, g_transforms, g_transl, g_wn, g_cov, g_col, g_opac):
         self, p = ctx.deformer, ctx.p
         xyz_c, nrm, lw, sc, rot, shs, cam, pose_big, pose_tgt, off, vid, clamped = ctx.keep
         has_n, has_lw, has_cr, has_sc, has_rot, has_sh = ctx.has
@@ -271,14 +287,19 @@ class _DeformFn(torch.autograd.Function):
         f = dict(dtype=torch.float32, device=dev)
         c = lambda t: None if t is None else _f32c(t)
         g_world, g_transforms, g_wn, g_cov, g_col = c(g_world), c(g_transforms), c(g_wn), c(g_cov), c(g_col)
-        need = ctx.needs_input_grad  # positions 8.. = xyz, normals, lbs_weights, correct_Rs, scaling, rotation, features
+        need = ctx.needs_input_grad  # positions 9.. = xyz, normals, lbs_weights, correct_Rs, scaling, rotation, features, logit
+        d_ol = None
+        if ctx.ol is not None and P:
+            g_opac = c(g_opac)
+            d_ol = torch.empty(ctx.ol.shape, **f)
+            p.dL_dopacity, p.dL_dopacity_logits = _ptr(g_opac), d_ol.data_ptr()
         d_xyz = torch.empty(P, 3, **f)
         d_n = torch.empty(P, 3, **f) if has_n else None
         d_lw = torch.empty(P, NJ, **f) if has_lw else None
         d_sc = torch.empty(P, 3, **f) if has_sc else None
         d_rot = torch.empty(P, 4, **f) if has_sc else None
         d_sh = torch.empty(P, M, 3, **f) if has_sh else None
-        want_pose = has_cr and need[11]
+        want_pose = has_cr and need[12]
         d_A = torch.zeros(NJ * 12, **f) if want_pose else None
         d_off = torch.zeros(self.V, 3, **f) if want_pose else None
         if P:
@@ -296,7 +317,7 @@ class _DeformFn(torch.autograd.Function):
             d_cr = buf[:207].view(23, 3, 3).reshape(ctx.correct_Rs.shape)
         if d_lw is not None:
             d_lw = d_lw.view(ctx.lw_shape)
-        return (None,) * 8 + (d_xyz, d_n, d_lw, d_cr, d_sc, d_rot if has_rot else None, d_sh)
+        return (None,) * 9 + (d_xyz, d_n, d_lw, d_cr, d_sc, d_rot if has_rot else None, d_sh, d_ol)
 
 
 # ---- module-level mirrors of the small reference helpers ---------------------

@@ -186,3 +186,34 @@ def test_backward_matches_fp64_autograd(name, deformer, smpl_model):
         assert a.grad is not None, nm
         e = rel_err(a.grad.cpu().numpy(), b.grad.numpy())
         assert e <= 1e-4, (nm, e)
+
+
+def test_fused_activations_match_separate_ops(deformer):
+    """log_scaling= / opacity_logit= (exp and sigmoid inside the deform kernels) give what exp / sigmoid applied
+    outside give: outputs to 1e-6 relative, gradients to 1e-5 of each tensor's scale."""
+    g = _load("lbs_plain_p1500")
+    P = g["xyz"].shape[0]
+    params, big = _cuda_params(g)
+    tv = _t(g["t_vertices"]).cuda()
+    gen = torch.Generator().manual_seed(4)
+    logit0 = torch.randn(P, 1, generator=gen)
+    w_cov, w_op = (torch.randn(P, 6, generator=gen) * 1e3).cuda(), torch.randn(P, 1, generator=gen).cuda()
+
+    def run(fused):
+        leaf = lambda a: a.clone().cuda().requires_grad_(True)
+        xyz, logs, rot, logit = leaf(_t(g["xyz"])), leaf(_t(g["log_scale"])), leaf(_t(g["rotation"])), leaf(logit0)
+        kw = dict(rotation=rot, scaling_modifier=1.1)
+        if fused:
+            d = deformer.deform_gaussians(xyz, params, big, tv, log_scaling=logs, opacity_logit=logit, **kw)
+            op = d["opacity"]
+        else:
+            d = deformer.deform_gaussians(xyz, params, big, tv, scaling=torch.exp(logs), **kw)
+            assert d["opacity"] is None
+            op = torch.sigmoid(logit)
+        ((d["cov3D"] * w_cov).sum() + (op * w_op).sum()).backward()
+        return d["cov3D"].detach(), op.detach(), logs.grad, logit.grad, rot.grad, xyz.grad
+
+    a, b = run(True), run(False)
+    assert a[1].shape == (P, 1)
+    for x, y, tol in zip(a, b, (1e-6, 1e-6, 1e-5, 1e-5, 1e-5, 1e-5)):
+        assert rel_err(x.cpu().numpy(), y.cpu().numpy()) <= tol
