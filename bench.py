@@ -61,8 +61,9 @@ def parse():
     ap.add_argument("--mode", default="graph", choices=["graph", "eager"],
                     help="ours: replay the step as one CUDA graph (mygauhuman_b200.graphed.GraphedRenderStep, default) "
                          "or issue it kernel by kernel through the eager operator API")
-    ap.add_argument("--all-reduce", default="after", choices=["captured", "after"],
-                    help="N>1, graph mode: gradient all-reduce inside the CUDA graph, or issued after each replay")
+    ap.add_argument("--batch-views", type=int, default=8,
+                    help="views each rank renders per optimisation step (multi-view batch): gradients are accumulated over "
+                         "them and summed over the ranks ONCE per step (NCCL).  1 = an all-reduce after every view")
     ap.add_argument("--sync-free", action="store_true",
                     help="ours: size the binning buffer from the previous step instead of a blocking read")
     return ap.parse_args()
@@ -215,7 +216,7 @@ class OursArm:
     (mygauhuman_b200.diff_gaussian_rasterization), all on libghr.so through the C ABI."""
     name = "ours"
 
-    def __init__(self, wl, dev, sync_free, graph=False, all_reduce=None):
+    def __init__(self, wl, dev, sync_free, graph=False):
         from mygauhuman_b200 import _lib
         from mygauhuman_b200 import diff_gaussian_rasterization as dgr
         from mygauhuman_b200.lbs import SMPLDeformer
@@ -235,7 +236,7 @@ class OursArm:
             assert all(v["cam"]["tanfovx"] == cam["tanfovx"] and v["cam"]["tanfovy"] == cam["tanfovy"] for v in wl["views"])
             self.graphed = GraphedRenderStep(self.deformer, self.leaves, self.big, self.t_vertices, wl["H"], wl["W"],
                                              cam["tanfovx"], cam["tanfovy"], self.bg, linear_loss, sh_degree=3,
-                                             all_reduce=all_reduce)
+                                             accumulate=True)
 
     def capture(self, vecs, targets_dev):
         self.graphed.capture(vecs, [targets_dev])
@@ -460,8 +461,7 @@ def main():
     P, W, H = wl["P"], wl["W"], wl["H"]
     X, tiles = W * H, ((W + 15) // 16) * ((H + 15) // 16)
     if args.impl == "ours":
-        arm = OursArm(wl, dev, args.sync_free, graph=(args.mode == "graph"),
-                      all_reduce=(args.all_reduce if world > 1 else None))
+        arm = OursArm(wl, dev, args.sync_free, graph=(args.mode == "graph"))
     else:
         try:
             arm = ReferenceArm(wl, dev)
@@ -484,9 +484,25 @@ def main():
 
     ar_err = None
 
-    def one_step(i, e2e, want_grads=False):
+    B = max(1, args.batch_views)
+
+    def graph_on():
+        return args.impl == "ours" and arm.use_graph
+
+    def begin_batch():
+        if graph_on():
+            arm.graphed.zero_grads()  # the graphed step accumulates the batch's gradients in its flat bucket
+
+    def end_batch(grads):
+        # view-sharded data parallelism: ONE sum of the Gaussian-parameter gradients over the ranks per batch
+        if graph_on():
+            arm.graphed.reduce_grads()
+        elif world > 1:
+            reducer(grads)
+
+    def one_view(i, e2e):
         k = i % len(views)
-        if args.impl == "ours" and arm.use_graph:
+        if graph_on():
             # the graphed step owns the static input buffers: it copies from pinned host memory itself (e2e), or from
             # the resident device copies (the target planes already sit in its static buffer)
             if e2e:
@@ -499,22 +515,35 @@ def main():
             loss, grads = arm.step(views[k], vec_stage, targets_stage)
         else:
             loss, grads = arm.step(views[k], vec_dev[k], targets_dev)
-        if world > 1 and not (args.impl == "ours" and arm.use_graph):
-            # view-sharded data parallelism: sum the Gaussian-parameter gradients over ranks (NCCL over NVLink);
-            # the graphed step does this itself on its flat gradient bucket
-            reducer(grads)
+        return loss, grads
+
+    def one_step(i, e2e, want_grads=False):
+        """A batch of one view (warm-up, verification)."""
+        begin_batch()
+        loss, grads = one_view(i, e2e)
+        end_batch(grads)
         if e2e:
-            return float(loss.item())  # the device->host read of the step's result
+            return float(loss.item())
         return grads if want_grads else None
 
     def timed(K, e2e):
-        starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-        ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+        """K steps of B views.  Every view has its own event pair (L2 flushed before it, outside the pair); the first
+        view's pair includes the bucket reset, the last one's the all-reduce.  e2e: inputs from pinned host memory and
+        the view's loss read back inside the pair."""
+        n = K * B
+        starts = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
+        ends = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
         torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
-        for i in range(K):
+        for i in range(n):
             flush.fill_(i & 0xFF)  # L2 flush, outside the event pair
             starts[i].record()
-            one_step(i, e2e)
+            if i % B == 0:
+                begin_batch()
+            loss, grads = one_view(i, e2e)
+            if i % B == B - 1:
+                end_batch(grads)
+            if e2e:
+                float(loss.item())  # the device->host read of the view's result
             ends[i].record()
         torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
         ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
@@ -564,7 +593,7 @@ def main():
     ms_e2e = timed(K, True)
     eager = None
     if graphed:
-        launches = K * arm.graphed.kernels_per_replay  # libghr kernels inside the K replays
+        launches = K * B * arm.graphed.kernels_per_replay  # libghr kernels inside the K*B replays
         if not arm.graphed.check():  # a view overflowed the captured binning capacity: re-captured, measure again
             ms_dev, ms_e2e = timed(K, False), timed(K, True)
             assert arm.graphed.check()
@@ -613,7 +642,7 @@ def main():
     if args.impl == "ours" and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline(wl, views[0], args.cpu_iters)
 
-    views_per_step = world  # one view per rank per step
+    views_per_step = world * B  # B views per rank per step
     value = views_per_step * K / (ms_dev * 1e-3)
     e2e_val = views_per_step * K / (ms_e2e * 1e-3)
     h2d = PACK_FLOATS * 4 + 5 * X * 4
@@ -623,16 +652,17 @@ def main():
         "dtype": "f32", "data": "synthetic", "impl": args.impl,
         "config": {"workload": args.workload, "desc": WORKLOADS[args.workload]["desc"], "P": P, "W": W, "H": H,
                    "sh_degree": 3, "views_cycled": len(views) * world, "parallelism": f"view-sharded dp{world}",
-                   "l2": "flushed between steps (256 MiB fill outside the per-step event pair)",
+                   "l2": "flushed before every view (256 MiB fill outside the per-view event pair)",
                    "sync_free": bool(args.sync_free),
                    "mode": (args.mode if args.impl == "ours" else "eager"),
-                   "all_reduce": (None if world == 1 else (args.all_reduce if graphed else "after"))},
+                   "batch_views_per_rank": B,
+                   "all_reduce": (None if world == 1 else "one NCCL sum of the flat gradient bucket per step (batch)")},
         "e2e": {"value": round(e2e_val, 2), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                "h2d_bytes_per_step": h2d * B, "d2h_bytes_per_step": 4 * B,
                 "what": "public API step (GraphedRenderStep replay, or in eager mode SMPLDeformer.deform_gaussians -> "
                         "GaussianRasterizer -> loss -> backward); "
                         "camera + SMPL pose + 5 target planes copied from pinned host memory and loss.item() read back "
-                        "inside every step's event pair; Gaussian parameters stay resident (model state)"},
+                        "inside every view's event pair; Gaussian parameters stay resident (model state)"},
         "gpu_launches": launches, "clocks": clocks,
     }
     if eager is not None:

@@ -55,7 +55,7 @@ class DeformParams(C.Structure):
                 ("vertex_offsets", c_f32p), ("pose_big", c_f32p), ("pose_target", c_f32p), ("scales", c_f32p),
                 ("rotations", c_f32p), ("shs", c_f32p), ("campos", c_f32p), ("scales_are_log", C.c_int32),
                 ("opacity_logits", c_f32p), ("opacity_out", c_f32p), ("dL_dopacity", c_f32p),
-                ("dL_dopacity_logits", c_f32p)]
+                ("dL_dopacity_logits", c_f32p), ("accumulate_grads", C.c_int32)]
 
 
 POSE_FLOATS = 1536

@@ -268,6 +268,9 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
     for (int k = 0; k < 12; k++) dAt[k] = 0.0f;
 #pragma unroll
     for (int j = 0; j < kJ; j++) bw_keep[j] = 0.0f;
+    // per-Gaussian gradients are stored, or added to what the buffers hold (multi-view gradient accumulation)
+    const bool acc = p.accumulate_grads != 0;
+    auto put = [acc](float* dst, float v) { *dst = acc ? *dst + v : v; };
     if (active) {
         const int vid = p.vert_ids[idx];
         DeformState d;
@@ -287,15 +290,15 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
             if (g.g_colors) {
                 const float gc[3] = {g.g_colors[3 * idx], g.g_colors[3 * idx + 1], g.g_colors[3 * idx + 2]};
                 sh_backward(p.sh_degree, p.M, p.shs + (size_t)idx * p.M * 3, xw[0] - s.campos[0], xw[1] - s.campos[1],
-                            xw[2] - s.campos[2], g.clamped ? g.clamped[idx] : 0u, gc, gxw, dsh);
-            } else {
+                            xw[2] - s.campos[2], g.clamped ? g.clamped[idx] : 0u, gc, gxw, dsh, acc);
+            } else if (!acc) {
                 for (int k = 0; k < p.M * 3; k++) dsh[k] = 0.0f;
             }
         }
 
         if (p.opacity_logits && p.dL_dopacity_logits) {
             const float sg = 1.0f / (1.0f + expf(-p.opacity_logits[idx]));
-            p.dL_dopacity_logits[idx] = p.dL_dopacity ? p.dL_dopacity[idx] * sg * (1.0f - sg) : 0.0f;
+            put(p.dL_dopacity_logits + idx, p.dL_dopacity ? p.dL_dopacity[idx] * sg * (1.0f - sg) : 0.0f);
         }
         // ---- covariance: Sigma' = (Tw L)(Tw L)^T, L = R(q^) diag(mod*s) ----
         if (p.scales && g.d_scales) {
@@ -344,8 +347,13 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
                 for (int c = 0; c < 3; c++) dsc[c] *= p.scale_modifier;
                 if (p.scales_are_log) { dsc[0] *= sa[0]; dsc[1] *= sa[1]; dsc[2] *= sa[2]; }  // d exp(l) / dl = exp(l)
             }
-            g.d_scales[3 * idx] = dsc[0]; g.d_scales[3 * idx + 1] = dsc[1]; g.d_scales[3 * idx + 2] = dsc[2];
-            if (g.d_rot) reinterpret_cast<float4*>(g.d_rot)[idx] = make_float4(dq[0], dq[1], dq[2], dq[3]);
+            put(g.d_scales + 3 * idx, dsc[0]); put(g.d_scales + 3 * idx + 1, dsc[1]); put(g.d_scales + 3 * idx + 2, dsc[2]);
+            if (g.d_rot) {
+                float4* o4 = reinterpret_cast<float4*>(g.d_rot) + idx;
+                float4 v4 = make_float4(dq[0], dq[1], dq[2], dq[3]);
+                if (acc) { const float4 old = *o4; v4.x += old.x; v4.y += old.y; v4.z += old.z; v4.w += old.w; }
+                *o4 = v4;
+            }
         }
 
         // ---- world <- smpl <- T pose <- big pose ----
@@ -364,7 +372,7 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
                     for (int c = 0; c < 3; c++) dM[3 * r + c] += dn3[r] * n[c];
                 mat3_tvec(d.M, dn3, dn);
             }
-            if (g.d_normals) { g.d_normals[3 * idx] = dn[0]; g.d_normals[3 * idx + 1] = dn[1]; g.d_normals[3 * idx + 2] = dn[2]; }
+            if (g.d_normals) { put(g.d_normals + 3 * idx, dn[0]); put(g.d_normals + 3 * idx + 1, dn[1]); put(g.d_normals + 3 * idx + 2, dn[2]); }
         }
         float dx3[3], dx2[3];
         mat3_vec(s.Rginv, gxw, dx3);  // xw = Rginv^T x3 + Th
@@ -388,7 +396,7 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
         for (int r = 0; r < 3; r++)
 #pragma unroll
             for (int c = 0; c < 3; c++) dRinv[3 * r + c] += dx2[r] * d.xc[c];
-        g.d_xyz[3 * idx] = dxc[0]; g.d_xyz[3 * idx + 1] = dxc[1]; g.d_xyz[3 * idx + 2] = dxc[2];
+        put(g.d_xyz + 3 * idx, dxc[0]); put(g.d_xyz + 3 * idx + 1, dxc[1]); put(g.d_xyz + 3 * idx + 2, dxc[2]);
         // Rinv = Ab3^-1: dAb3 = -Rinv^T dRinv Rinv^T
         float dAb3[9];
         mat3_tmul_d(d.Rinv, dRinv, t9);
@@ -416,7 +424,7 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
                 dot += d.bw[j] * v;
             }
 #pragma unroll
-            for (int j = 0; j < kJ; j++) g.d_offsets[kJ * (size_t)idx + j] = d.bw[j] * (dbw[j] - dot);
+            for (int j = 0; j < kJ; j++) put(g.d_offsets + kJ * (size_t)idx + j, d.bw[j] * (dbw[j] - dot));
         }
     }
     // ---- dL/dA_target[j] = sum over Gaussians of bw_j dAt  (pose branch) ----

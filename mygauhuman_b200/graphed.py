@@ -53,9 +53,12 @@ class GraphedRenderStep:
 
     def __init__(self, deformer, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx, tanfovy, bg,
                  loss_fn, n_loss_inputs=1, sh_degree=3, scaling_modifier=1.0, capacity_hint=None, use_graph=True,
-                 all_reduce=None, group=None):
+                 all_reduce=None, group=None, accumulate=False):
         """all_reduce: None (single GPU), "after" (one NCCL sum all-reduce of the flat gradient bucket issued right
-        after the replay) or "captured" (the all-reduce is part of the graph: every rank replays in lockstep)."""
+        after the replay) or "captured" (the all-reduce is part of the graph: every rank replays in lockstep).
+        accumulate=True: multi-view batches.  Every call ADDS its gradients to the flat bucket (leaves[k].grad are
+        views of it); zero_grads() starts a batch and reduce_grads() sums the bucket over the ranks once per batch
+        (all_reduce must then be None: the collective is per batch, not per view)."""
         self.deformer, self.leaves = deformer, leaves
         self.big, self.t_vertices = big_pose_params, t_vertices
         self.H, self.W, self.tanfovx, self.tanfovy = int(image_height), int(image_width), float(tanfovx), float(tanfovy)
@@ -68,17 +71,26 @@ class GraphedRenderStep:
         self.n_seen = torch.zeros(1, dtype=torch.int32, device=dev)  # max num_rendered over all replays (device)
         self.capacity = None if capacity_hint is None else int(capacity_hint)
         assert all_reduce in (None, "after", "captured")
-        self.all_reduce, self.group = all_reduce, group
+        assert not (accumulate and all_reduce is not None)
+        self.all_reduce, self.group, self.accumulate = all_reduce, group, accumulate
         self.flat, self.flat_views = None, None
-        if all_reduce is not None:
+        if all_reduce is not None or accumulate:
             # gradients of all leaves in one bucket (59 floats per Gaussian at SH degree 3): one collective per step,
             # and leaves[k].grad are views of it, so nothing is copied back after the reduction
-            n = sum(t.numel() for t in leaves.values())
-            self.flat = torch.zeros(n, device=dev)
+            pad = lambda n: (n + 3) // 4 * 4  # every view starts on a 16-byte boundary
+            self.flat = torch.zeros(sum(pad(t.numel()) for t in leaves.values()), device=dev)
             self.flat_views, o = {}, 0
             for k, t in leaves.items():
                 self.flat_views[k] = self.flat[o:o + t.numel()].view_as(t)
-                o += t.numel()
+                o += pad(t.numel())
+        self._sink = None
+        if accumulate:
+            # the deform backward kernel adds straight into the bucket: no separate accumulation pass
+            names = {"xyz": "xyz", "normals": "normals", "log_scale": "scaling", "rotation": "rotation",
+                     "features": "features", "opacity_logit": "opacity_logit"}
+            self._sink = {names[k]: v for k, v in self.flat_views.items()}
+            for k, t in leaves.items():
+                t.grad = self.flat_views[k]
         self.graph = None
         self.kernels_per_replay = None
         self.loss = None
@@ -109,6 +121,13 @@ class GraphedRenderStep:
             geom = _C._last_geom
             torch.maximum(self.n_seen, geom[:4].view(torch.int32), out=self.n_seen)
         loss = self.loss_fn(color, depth, alpha, *loss_inputs)
+        if self._sink is not None:
+            self.deformer.grad_sink = self._sink
+            try:
+                loss.backward()
+            finally:
+                self.deformer.grad_sink = None
+            return loss, dict(color=color, depth=depth, alpha=alpha, radii=radii, means2D=means2D)
         for t in L.values():
             t.grad = None
         loss.backward()
@@ -121,9 +140,18 @@ class GraphedRenderStep:
                 L[k].grad = self.flat_views[k]
         return loss, dict(color=color, depth=depth, alpha=alpha, radii=radii, means2D=means2D)
 
+    def zero_grads(self):
+        """accumulate mode: start a batch of views."""
+        self.flat.zero_()
+
+    def reduce_grads(self):
+        """accumulate mode: end of a batch -- one sum all-reduce of the bucket over the ranks (no-op on one rank)."""
+        self._reduce()
+        return self.flat_views
+
     def _max_over_ranks(self, n):
         import torch.distributed as dist
-        if self.all_reduce is None or not (dist.is_available() and dist.is_initialized()):
+        if (self.all_reduce is None and not self.accumulate) or not (dist.is_available() and dist.is_initialized()):
             return n
         t = torch.tensor([n], dtype=torch.int64, device=self.vec.device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
@@ -160,8 +188,8 @@ class GraphedRenderStep:
             for _ in range(3):  # warm-up on a side stream, as torch.cuda.graph requires
                 self._eager(self.vec, self.loss_inputs, self.capacity, reduce=in_graph)
         torch.cuda.current_stream().wait_stream(s)
-        for t in self.leaves.values():
-            t.grad = None
+        for k, t in self.leaves.items():
+            t.grad = None if self._sink is None else self.flat_views[k]
         self.graph = torch.cuda.CUDAGraph()
         n0 = _lib.launch_count()
         with torch.cuda.graph(self.graph):

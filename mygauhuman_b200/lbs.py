@@ -75,6 +75,10 @@ class SMPLDeformer:
         self._grid_key, self._grid = None, None
         self._pose_key, self._pose_cached = None, None
         self._side_stream = torch.cuda.Stream(device=self.device) if torch.cuda.is_available() else None
+        # Optional gradient sink (multi-view accumulation, see graphed.py): dict name -> fp32 contiguous tensor for
+        # "xyz", "normals", "scaling", "rotation", "features", "opacity_logit".  When set, the backward kernels ADD the
+        # per-Gaussian gradients of those inputs into the given tensors and autograd receives None for them.
+        self.grad_sink = None
 
     # ---- pose stage --------------------------------------------------------
     def pose_buffer(self, params, correct_Rs=None):
@@ -293,12 +297,26 @@ class _DeformFn(torch.autograd.Function):
             g_opac = c(g_opac)
             d_ol = torch.empty(ctx.ol.shape, **f)
             p.dL_dopacity, p.dL_dopacity_logits = _ptr(g_opac), d_ol.data_ptr()
-        d_xyz = torch.empty(P, 3, **f)
-        d_n = torch.empty(P, 3, **f) if has_n else None
-        d_lw = torch.empty(P, NJ, **f) if has_lw else None
-        d_sc = torch.empty(P, 3, **f) if has_sc else None
-        d_rot = torch.empty(P, 4, **f) if has_sc else None
-        d_sh = torch.empty(P, M, 3, **f) if has_sh else None
+        sink = self.grad_sink
+        if sink is not None:
+            pick = lambda k, on: sink[k] if on else None
+            d_xyz, d_n, d_lw = sink["xyz"], pick("normals", has_n), None
+            d_sc, d_rot, d_sh = pick("scaling", has_sc), pick("rotation", has_sc), pick("features", has_sh)
+            assert not has_lw, "grad_sink does not cover lbs_weights"
+            for t in (d_xyz, d_n, d_sc, d_rot, d_sh):
+                assert t is None or (t.is_contiguous() and t.dtype == torch.float32 and t.data_ptr() % 16 == 0)
+            p.accumulate_grads = 1
+            if ctx.ol is not None and P:
+                d_ol = sink["opacity_logit"]
+                p.dL_dopacity_logits = d_ol.data_ptr()
+        else:
+            p.accumulate_grads = 0
+            d_xyz = torch.empty(P, 3, **f)
+            d_n = torch.empty(P, 3, **f) if has_n else None
+            d_lw = torch.empty(P, NJ, **f) if has_lw else None
+            d_sc = torch.empty(P, 3, **f) if has_sc else None
+            d_rot = torch.empty(P, 4, **f) if has_sc else None
+            d_sh = torch.empty(P, M, 3, **f) if has_sh else None
         want_pose = has_cr and need[12]
         d_A = torch.zeros(NJ * 12, **f) if want_pose else None
         d_off = torch.zeros(self.V, 3, **f) if want_pose else None
@@ -317,6 +335,8 @@ class _DeformFn(torch.autograd.Function):
             d_cr = buf[:207].view(23, 3, 3).reshape(ctx.correct_Rs.shape)
         if d_lw is not None:
             d_lw = d_lw.view(ctx.lw_shape)
+        if sink is not None:  # already added to the sink tensors
+            return (None,) * 12 + (d_cr, None, None, None, None)
         return (None,) * 9 + (d_xyz, d_n, d_lw, d_cr, d_sc, d_rot if has_rot else None, d_sh, d_ol)
 
 

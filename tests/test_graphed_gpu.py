@@ -95,3 +95,26 @@ def test_capacity_overflow_is_detected_and_recaptured(smpl_model):
     assert step.check()
     assert abs(float(loss) - want_loss) <= 1e-5 * max(1.0, abs(want_loss))
     assert rel_err(leaves["xyz"].grad, want_grads["xyz"]) < 2e-5
+
+
+def test_accumulate_mode_sums_the_views_of_a_batch(smpl_model):
+    """accumulate=True: the deform backward adds every view's gradients straight into the flat bucket."""
+    from mygauhuman_b200.graphed import GraphedRenderStep
+    step, leaves, vecs, targets = _setup(smpl_model, [3.0, 2.7, 3.3])
+    want = None
+    for vec in vecs:  # per-view gradients through the plain (non-accumulating) eager path
+        _, grads, _ = _eager_reference(step, leaves, vec, targets)
+        want = grads if want is None else {k: want[k] + grads[k] for k in want}
+    acc = GraphedRenderStep(step.deformer, leaves, step.big, step.t_vertices, H, W, step.tanfovx, step.tanfovy, step.bg,
+                            _loss, accumulate=True)
+    acc.capture(vecs, [targets])
+    for _ in range(2):  # two batches: zero_grads() really restarts the sum
+        acc.zero_grads()
+        for vec in vecs:
+            acc(vec, targets)
+        got = acc.reduce_grads()
+        torch.cuda.synchronize()
+        for k in want:
+            assert leaves[k].grad.data_ptr() == got[k].data_ptr()
+            assert rel_err(got[k], want[k]) < 3e-5, k
+    assert acc.check()
