@@ -92,15 +92,21 @@ __device__ __forceinline__ unsigned long long gtime_b()
 #define GHR_BWD_WARPS 4
 #endif
 #ifndef GHR_BWD_STAGES
-#define GHR_BWD_STAGES 3
+#define GHR_BWD_STAGES 2
 #endif
 #ifndef GHR_BWD_CTAS
-#define GHR_BWD_CTAS 4
+#define GHR_BWD_CTAS 2
 #endif
 constexpr int kBwdWarps = GHR_BWD_WARPS;    // independent warps per CTA
-constexpr int kBwdBatch = 64;               // list entries per staging round and warp
+#ifndef GHR_BWD_BATCH
+#define GHR_BWD_BATCH 256
+#endif
+constexpr int kBwdBatch = GHR_BWD_BATCH;    // list entries per staging round and warp
 constexpr int kBwdStages = GHR_BWD_STAGES;
 constexpr int kBwdCtasPerSm = GHR_BWD_CTAS;
+constexpr size_t kBwdWarpSmem =
+    (sizeof(float4) * 3 + sizeof(uint32_t)) * kBwdStages * kBwdBatch + sizeof(uint32_t) * kBwdStages * (kBwdBatch / 32) + 0;
+static_assert(kBwdWarpSmem % 16 == 0, "per-warp staging area must keep float4 alignment");
 
 // Persistent kernel: warps pull (tile, 4x4 block) work items from a queue ordered by decreasing tile-list
 // length (tile_order_kernel) and work independently (no block-level barrier); see ghr_blend_fwd.cu.
@@ -112,15 +118,16 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
     const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas, float* __restrict__ accum)
 {
     constexpr int BATCH = kBwdBatch, NSTAGE = kBwdStages, PER_LANE = BATCH / 32;
-    __shared__ __align__(16) float4 s_all[kBwdWarps][NSTAGE][BATCH * 3];
-    __shared__ uint32_t s_id_all[kBwdWarps][NSTAGE][BATCH];
-    __shared__ uint32_t s_keep_all[kBwdWarps][NSTAGE][PER_LANE];  // survivors of each staged round, one bit per entry
-
+    // per-warp staging ring in dynamic shared memory: records, ids, survivor bits
+    extern __shared__ __align__(16) unsigned char bwd_smem[];
+    constexpr size_t kWarpBytes = kBwdWarpSmem;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t slot = lane >> 4, pl = lane & 15u;  // which of the pixel's two lanes; pixel inside the 4x4 block
-    float4(*s_rec)[BATCH * 3] = s_all[warp];
-    uint32_t(*s_id)[BATCH] = s_id_all[warp];
-    uint32_t(*s_keep)[PER_LANE] = s_keep_all[warp];
+    unsigned char* wbase = bwd_smem + warp * kWarpBytes;
+    float4(*s_rec)[BATCH * 3] = reinterpret_cast<float4(*)[BATCH * 3]>(wbase);
+    uint32_t(*s_id)[BATCH] = reinterpret_cast<uint32_t(*)[BATCH]>(wbase + sizeof(float4) * NSTAGE * BATCH * 3);
+    uint32_t(*s_keep)[PER_LANE] =
+        reinterpret_cast<uint32_t(*)[PER_LANE]>(wbase + sizeof(float4) * NSTAGE * BATCH * 3 + sizeof(uint32_t) * NSTAGE * BATCH);
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
     // {Gaussian id, 4x4-block mask} per list entry (tile_ranges_kernel; lives in the key buffer the sort left unused)
@@ -240,14 +247,21 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
             // entry j of this round sits at list position pos(j) = walk-1-(i*BATCH+j); the reference's
             // `contributor` for it equals pos(j) (backward.cu:499-501: skip if contributor >= last_contributor)
             const int pos0 = walk - 1 - i * BATCH;
-            for (int g = 0; g < n; g += 32) {
-                uint32_t mask = s_keep[buf][g >> 5];  // survivors of this group of 32 entries (block masks, see stage)
-                while (mask) {
+            // The round's survivors (one bit per staged entry, see stage) are consumed eight at a time ACROSS the 32-entry
+            // words, so a step is full except at the end of the round.
+            (void)n;
+            int g = 0;
+            uint32_t mask = s_keep[buf][0];
+            for (;;) {
+                while (mask == 0 && g + 32 < BATCH) { g += 32; mask = s_keep[buf][g >> 5]; }
+                if (mask == 0) break;
+                {
                     // eight survivors in walk order; slot 0 owns j[0] j[2] j[4] j[6], slot 1 the others
                     int j[8];
                     bool v_ok[8];
 #pragma unroll
                     for (int u = 0; u < 8; u++) {
+                        while (mask == 0 && g + 32 < BATCH) { g += 32; mask = s_keep[buf][g >> 5]; }
                         v_ok[u] = mask != 0;
                         j[u] = v_ok[u] ? g + __ffs(mask) - 1 : j[0];
                         mask &= mask - 1;
@@ -392,7 +406,10 @@ cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, 
     const int64_t items = (int64_t)tiles * 16;
     int64_t ctas = (items + kBwdWarps - 1) / kBwdWarps;
     if (ctas > 148 * kBwdCtasPerSm) ctas = 148 * kBwdCtasPerSm;
-    blend_backward_kernel<<<(unsigned)ctas, kBwdWarps * 32, 0, s>>>(
+    const size_t smem = kBwdWarpSmem * kBwdWarps;
+    e = cudaFuncSetAttribute(blend_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    blend_backward_kernel<<<(unsigned)ctas, kBwdWarps * 32, smem, s>>>(
         p.W, p.H, tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
         reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),
         reinterpret_cast<const uint2*>(binning + L.b_keys_a), reinterpret_cast<const uint2*>(binning + L.b_keys_b),
