@@ -529,22 +529,42 @@ def main():
     def timed(K, e2e):
         """K steps of B views.  Every view has its own event pair (L2 flushed before it, outside the pair); the first
         view's pair includes the bucket reset, the last one's the all-reduce.  e2e: inputs from pinned host memory and
-        the view's loss read back inside the pair."""
+        the view's loss read back.  With the graphed step the e2e loop is pipelined the way a training loop would be:
+        the inputs of view i+1 travel on a copy stream while view i computes, and the loss of view i is copied to
+        pinned memory asynchronously and consumed one view later -- every copy still happens inside the timed region."""
         n = K * B
         starts = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
         ends = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
+        piped = e2e and graph_on()
+        pending, host_losses = None, 0.0
         torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
+        if piped:
+            arm.graphed.prefetch(vec_host[0], targets_host)
         for i in range(n):
             flush.fill_(i & 0xFF)  # L2 flush, outside the event pair
             starts[i].record()
             if i % B == 0:
                 begin_batch()
-            loss, grads = one_view(i, e2e)
+            if piped:
+                loss = arm.graphed.run_prefetched()
+                grads = None
+                arm.graphed.prefetch(vec_host[(i + 1) % len(views)], targets_host)
+            else:
+                loss, grads = one_view(i, e2e)
             if i % B == B - 1:
                 end_batch(grads)
-            if e2e:
-                float(loss.item())  # the device->host read of the view's result
+            if piped:
+                nxt = arm.graphed.loss_to_host()
+                if pending is not None:  # the previous view's loss: its copy finished long ago
+                    pending[1].synchronize()
+                    host_losses += float(pending[0][0])
+                pending = nxt
+            elif e2e:
+                host_losses += float(loss.item())  # the device->host read of the view's result
             ends[i].record()
+        if pending is not None:
+            pending[1].synchronize()
+            host_losses += float(pending[0][0])
         torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
         ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
         if world > 1:
@@ -661,8 +681,10 @@ def main():
                 "h2d_bytes_per_step": h2d * B, "d2h_bytes_per_step": 4 * B,
                 "what": "public API step (GraphedRenderStep replay, or in eager mode SMPLDeformer.deform_gaussians -> "
                         "GaussianRasterizer -> loss -> backward); "
-                        "camera + SMPL pose + 5 target planes copied from pinned host memory and loss.item() read back "
-                        "inside every view's event pair; Gaussian parameters stay resident (model state)"},
+                        "camera + SMPL pose + 5 target planes copied from pinned host memory and the loss copied back to "
+                        "pinned memory for every view inside the timed region (graph mode: input copy of view i+1 on a "
+                        "copy stream during view i, loss consumed one view later; eager/reference: blocking loss.item()); "
+                        "Gaussian parameters stay resident (model state)"},
         "gpu_launches": launches, "clocks": clocks,
     }
     if eager is not None:

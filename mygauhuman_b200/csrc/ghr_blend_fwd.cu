@@ -52,13 +52,13 @@ __device__ __forceinline__ void cp_async_wait()
 }
 
 #ifndef GHR_FWD_WARPS
-#define GHR_FWD_WARPS 2
+#define GHR_FWD_WARPS 1
 #endif
 #ifndef GHR_FWD_STAGES
-#define GHR_FWD_STAGES 3
+#define GHR_FWD_STAGES 2
 #endif
 #ifndef GHR_FWD_CTAS
-#define GHR_FWD_CTAS 6
+#define GHR_FWD_CTAS 8
 #endif
 #ifdef GHR_TRACE  // tuning builds only (tools/build_variant.sh): per-item begin/end timestamps
 __device__ unsigned long long g_fwd_trace[1 << 16][8];
@@ -77,11 +77,15 @@ __device__ __forceinline__ uint32_t smid()
 #endif
 constexpr int kBlendWarps = GHR_FWD_WARPS;    // warps per CTA (independent workers)
 #ifndef GHR_FWD_BATCH
-#define GHR_FWD_BATCH 128
+#define GHR_FWD_BATCH 256
 #endif
 constexpr int kBlendBatch = GHR_FWD_BATCH;    // list entries per staging round and warp
 constexpr int kBlendStages = GHR_FWD_STAGES;  // depth of the per-warp staging ring
 constexpr int kBlendCtasPerSm = GHR_FWD_CTAS;
+#ifndef GHR_FWD_KSTEP
+#define GHR_FWD_KSTEP 8
+#endif
+constexpr int KSTEP = GHR_FWD_KSTEP;          // survivors per step (half of them evaluated by each slot)
 
 __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(
     int W, int H, int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
@@ -199,69 +203,73 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(
             const float4* r = s_rec[buf];
             const float* rf = reinterpret_cast<const float*>(r);
             const uint32_t base = (uint32_t)i * BATCH;  // list position of r[0]
-            for (int g = 0; g < n; g += 32) {
-                uint32_t mask = s_keep[buf][g >> 5];  // (1) survivors of this group of 32 entries (block mask, see stage)
-#ifdef GHR_TRACE
-                trace_surv += __popc(mask);
-#endif
+            // (1) The round's survivors (one bit per staged entry: block mask, see stage) are consumed (2) KSTEP at a
+            // time in list order, across the 32-entry words: even ones are evaluated by slot 0, odd ones by slot 1.
+            (void)n;
+            int g = 0;
+            uint32_t mask = s_keep[buf][0];
+            for (;;) {
+                while (mask == 0 && g + 32 < BATCH) { g += 32; mask = s_keep[buf][g >> 5]; }
+                if (mask == 0) break;
                 TRACE_LAP(c_cull)
-                // (2) survivors, four at a time in list order: j[0] j[2] are evaluated by slot 0, j[1] j[3] by slot 1
-                while (mask) {
 #ifdef GHR_TRACE
-                    trace_steps++;
+                trace_steps++;
 #endif
-                    int j[4];
-                    bool v[4];
+                int j[KSTEP];
+                bool v[KSTEP];
 #pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        v[u] = mask != 0;
-                        j[u] = v[u] ? g + __ffs(mask) - 1 : j[0];
-                        mask &= mask - 1;
-                    }
-                    float mine[2];
-#pragma unroll
-                    for (int u = 0; u < 2; u++) {
-                        const int jm = slot ? j[2 * u + 1] : j[2 * u];
-                        const bool vm = slot ? v[2 * u + 1] : v[2 * u];
-                        const float4 r0 = r[3 * jm], r1 = r[3 * jm + 1];
-                        const float dx = __fsub_rn(r0.x, pxf), dy = __fsub_rn(r0.y, pyf);
-                        const float power = pair_power(dx, dy, r1.x, r1.y, r1.z);
-                        const float al = fminf(0.99f, __fmul_rn(r1.w, expf(power)));
-                        mine[u] = (vm && !(power > 0.0f) && !(al < 1.0f / 255.0f)) ? al : 0.0f;  // 0 = skipped
-                    }
-                    float alpha[4];
-#pragma unroll
-                    for (int u = 0; u < 2; u++) {
-                        const float theirs = __shfl_xor_sync(0xffffffffu, mine[u], 16);
-                        alpha[2 * u] = slot ? theirs : mine[u];
-                        alpha[2 * u + 1] = slot ? mine[u] : theirs;
-                    }
-                    // Sequential part, straight-line and branch-free: only T -> test_T -> T is a dependent chain
-                    // (one multiply and one compare per Gaussian); everything else is computed up front.
-                    float x0[4], x1[4], om[4];
-#pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        const float4 r2 = r[3 * j[u] + 2];
-                        const float depth = rf[12 * j[u] + 2];
-                        x0[u] = __fmul_rn(alpha[u], slot ? r2.z : r2.x);
-                        x1[u] = __fmul_rn(alpha[u], slot ? depth : r2.y);
-                        om[u] = __fsub_rn(1.0f, alpha[u]);
-                    }
-#pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        const bool act = alpha[u] > 0.0f && !done;
-                        const float test_T = __fmul_rn(T, om[u]);
-                        const bool stop = act && test_T < 0.0001f;
-                        const bool acc = act && !stop;
-                        done = done || stop;
-                        A0 = acc ? __fmaf_rn(T, x0[u], A0) : A0;
-                        A1 = acc ? __fmaf_rn(T, x1[u], A1) : A1;
-                        A2 = acc ? __fmaf_rn(T, alpha[u], A2) : A2;
-                        last_contributor = acc ? base + (uint32_t)j[u] + 1u : last_contributor;
-                        T = acc ? test_T : T;
-                    }
-                    if (__all_sync(0xffffffffu, done)) { mask = 0; g = n; }
+                for (int u = 0; u < KSTEP; u++) {
+                    while (mask == 0 && g + 32 < BATCH) { g += 32; mask = s_keep[buf][g >> 5]; }
+                    v[u] = mask != 0;
+#ifdef GHR_TRACE
+                    trace_surv += v[u];
+#endif
+                    j[u] = v[u] ? g + __ffs(mask) - 1 : j[0];
+                    mask &= mask - 1;
                 }
+                float mine[KSTEP / 2];
+#pragma unroll
+                for (int u = 0; u < KSTEP / 2; u++) {
+                    const int jm = slot ? j[2 * u + 1] : j[2 * u];
+                    const bool vm = slot ? v[2 * u + 1] : v[2 * u];
+                    const float4 r0 = r[3 * jm], r1 = r[3 * jm + 1];
+                    const float dx = __fsub_rn(r0.x, pxf), dy = __fsub_rn(r0.y, pyf);
+                    const float power = pair_power(dx, dy, r1.x, r1.y, r1.z);
+                    const float al = fminf(0.99f, __fmul_rn(r1.w, expf(power)));
+                    mine[u] = (vm && !(power > 0.0f) && !(al < 1.0f / 255.0f)) ? al : 0.0f;  // 0 = skipped
+                }
+                float alpha[KSTEP];
+#pragma unroll
+                for (int u = 0; u < KSTEP / 2; u++) {
+                    const float theirs = __shfl_xor_sync(0xffffffffu, mine[u], 16);
+                    alpha[2 * u] = slot ? theirs : mine[u];
+                    alpha[2 * u + 1] = slot ? mine[u] : theirs;
+                }
+                // Sequential part, straight-line and branch-free: only T -> test_T -> T is a dependent chain
+                // (one multiply and one compare per Gaussian); everything else is computed up front.
+                float x0[KSTEP], x1[KSTEP], om[KSTEP];
+#pragma unroll
+                for (int u = 0; u < KSTEP; u++) {
+                    const float4 r2 = r[3 * j[u] + 2];
+                    const float depth = rf[12 * j[u] + 2];
+                    x0[u] = __fmul_rn(alpha[u], slot ? r2.z : r2.x);
+                    x1[u] = __fmul_rn(alpha[u], slot ? depth : r2.y);
+                    om[u] = __fsub_rn(1.0f, alpha[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < KSTEP; u++) {
+                    const bool act = alpha[u] > 0.0f && !done;
+                    const float test_T = __fmul_rn(T, om[u]);
+                    const bool stop = act && test_T < 0.0001f;
+                    const bool acc = act && !stop;
+                    done = done || stop;
+                    A0 = acc ? __fmaf_rn(T, x0[u], A0) : A0;
+                    A1 = acc ? __fmaf_rn(T, x1[u], A1) : A1;
+                    A2 = acc ? __fmaf_rn(T, alpha[u], A2) : A2;
+                    last_contributor = acc ? base + (uint32_t)j[u] + 1u : last_contributor;
+                    T = acc ? test_T : T;
+                }
+                if (__all_sync(0xffffffffu, done)) { mask = 0; g = BATCH; }
                 TRACE_LAP(c_eval)
             }
             __syncwarp();  // buffer `buf` is re-filled by the stage() of the next iteration (round i+NSTAGE)

@@ -91,6 +91,7 @@ class GraphedRenderStep:
             self._sink = {names[k]: v for k, v in self.flat_views.items()}
             for k, t in leaves.items():
                 t.grad = self.flat_views[k]
+        self._copy_stream, self._staged, self._loss_ring = None, None, None
         self.graph = None
         self.kernels_per_replay = None
         self.loss = None
@@ -201,12 +202,18 @@ class GraphedRenderStep:
     def __call__(self, vec, *loss_inputs):
         """Run the step for the view packed in `vec` (device or pinned-host tensor).  Returns the loss tensor
         (static; overwritten by the next call).  Gradients are in leaves[k].grad."""
+        self._load_inputs(vec, loss_inputs)
+        return self._run()
+
+    def _load_inputs(self, vec, loss_inputs):
         if self.capacity is None:
             raise RuntimeError("call capture() first")
         self.vec.copy_(vec, non_blocking=True)
         for dst, src in zip(self.loss_inputs, loss_inputs):
             if src is not dst:
                 dst.copy_(src, non_blocking=True)
+
+    def _run(self):
         if self.graph is None:
             self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity, reduce=self.all_reduce is not None)
         else:
@@ -214,6 +221,45 @@ class GraphedRenderStep:
             if self.all_reduce == "after":
                 self._reduce()
         return self.loss
+
+    # ---- host-side pipelining ---------------------------------------------------------------------------
+    def prefetch(self, vec, *loss_inputs):
+        """Start copying the NEXT view's inputs (pinned host or device tensors) into staging buffers on a copy stream.
+        The following run_prefetched() waits for that copy only, so the transfer of view i+1 overlaps the kernels of
+        view i instead of preceding its own (a 512x512 target with 5 planes is 5 MB: ~100 us over PCIe)."""
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.vec.device)
+            self._staged = [torch.empty_like(self.vec)] + [torch.empty_like(t) for t in self.loss_inputs]
+            self._staged_ready = torch.cuda.Event()
+            self._staged_free = torch.cuda.Event()
+            self._staged_free.record()
+        cs = self._copy_stream
+        cs.wait_event(self._staged_free)  # the previous run_prefetched() has consumed the staging buffers
+        with torch.cuda.stream(cs):
+            self._staged[0].copy_(vec, non_blocking=True)
+            for dst, src in zip(self._staged[1:], loss_inputs):
+                dst.copy_(src, non_blocking=True)
+            self._staged_ready.record()
+
+    def run_prefetched(self):
+        """Run the step on the inputs handed to the last prefetch()."""
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self._staged_ready)
+        self._load_inputs(self._staged[0], self._staged[1:])  # device-to-device into the graph's static inputs
+        self._staged_free.record()                            # the copy stream may refill the staging buffers now
+        return self._run()
+
+    def loss_to_host(self):
+        """Asynchronous device-to-host copy of the last step's loss into a pinned ring; returns (slot tensor, event).
+        Read the value after event.synchronize() -- typically one step later, so the host never stalls the GPU."""
+        if self._loss_ring is None:
+            self._loss_ring = [(torch.zeros(1, dtype=torch.float32).pin_memory(), torch.cuda.Event()) for _ in range(4)]
+            self._loss_i = 0
+        slot, ev = self._loss_ring[self._loss_i % 4]
+        self._loss_i += 1
+        slot.copy_(self.loss.detach().reshape(1), non_blocking=True)
+        ev.record()
+        return slot, ev
 
     def check(self):
         """Synchronises; if some replay needed more binning capacity than the graph was captured with, re-captures

@@ -118,3 +118,29 @@ def test_accumulate_mode_sums_the_views_of_a_batch(smpl_model):
             assert leaves[k].grad.data_ptr() == got[k].data_ptr()
             assert rel_err(got[k], want[k]) < 3e-5, k
     assert acc.check()
+
+
+def test_prefetch_pipeline_gives_the_same_results(smpl_model):
+    """prefetch() / run_prefetched() / loss_to_host(): inputs staged on the copy stream while the previous view runs."""
+    step, leaves, vecs, targets = _setup(smpl_model, [3.0, 2.8, 3.2])
+    step.capture(vecs, [targets])
+    want = []
+    for vec in vecs:
+        want.append(float(step(vec, targets)))
+    host_vecs = [v.cpu().pin_memory() for v in vecs]
+    host_targets = targets.cpu().pin_memory()
+    got, pending = [], None
+    step.prefetch(host_vecs[0], host_targets)
+    for i in range(len(vecs)):
+        step.run_prefetched()
+        if i + 1 < len(vecs):
+            step.prefetch(host_vecs[i + 1], host_targets)
+        nxt = step.loss_to_host()
+        if pending is not None:
+            pending[1].synchronize()
+            got.append(float(pending[0][0]))
+        pending = nxt
+    pending[1].synchronize()
+    got.append(float(pending[0][0]))
+    for a, b in zip(got, want):
+        assert abs(a - b) <= 1e-5 * max(1.0, abs(b))
