@@ -69,7 +69,8 @@ __global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_kernel(ghr_geom_header*
                                                                 uint64_t* keys_a, uint64_t* keys_b,
                                                                 const uint32_t* __restrict__ vals_a,
                                                                 const uint32_t* __restrict__ vals_b,
-                                                                const float4* __restrict__ rec, uint2* ranges)
+                                                                const float4* __restrict__ rec, uint2* ranges,
+                                                                int with_masks)
 {
     const int64_t L = hdr->num_rendered;
     if (L > capacity) {
@@ -89,6 +90,7 @@ __global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_kernel(ghr_geom_header*
         }
         if (idx == L - 1) ranges[cur].y = (uint32_t)L;
 
+        if (!with_masks) continue;  // throughput regime: the wide blend kernels cull inside (ghr_blend_fwd_wide.cu)
         const uint32_t id = vals[idx];
         const float4 r0 = rec[3 * (size_t)id], r1 = rec[3 * (size_t)id + 1];
         float ex, ey;
@@ -171,7 +173,8 @@ cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, cha
         (p.W + GHR_TILE - 1) / GHR_TILE, reinterpret_cast<const SortHeader*>(binning + L.b_header),
         reinterpret_cast<uint64_t*>(binning + L.b_keys_a), reinterpret_cast<uint64_t*>(binning + L.b_keys_b),
         reinterpret_cast<const uint32_t*>(binning + L.b_vals_a), reinterpret_cast<const uint32_t*>(binning + L.b_vals_b),
-        reinterpret_cast<const float4*>(geom + L.g_rec), reinterpret_cast<uint2*>(img + L.i_ranges));
+        reinterpret_cast<const float4*>(geom + L.g_rec), reinterpret_cast<uint2*>(img + L.i_ranges),
+        blend_throughput_regime(capacity) ? 0 : 1);
     count_launch();
     tile_order_kernel<<<1, 1024, 0, s>>>(tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
                                          reinterpret_cast<const ghr_geom_header*>(geom + L.g_header), capacity,

@@ -88,28 +88,18 @@ __device__ __forceinline__ unsigned long long gtime_b()
 #else
 #define BTRACE_LAP(acc)
 #endif
-#ifndef GHR_BWD_WARPS
-#define GHR_BWD_WARPS 4
-#endif
-#ifndef GHR_BWD_STAGES
-#define GHR_BWD_STAGES 2
-#endif
-#ifndef GHR_BWD_CTAS
-#define GHR_BWD_CTAS 2
-#endif
-constexpr int kBwdWarps = GHR_BWD_WARPS;    // independent warps per CTA
-#ifndef GHR_BWD_BATCH
-#define GHR_BWD_BATCH 256
-#endif
-constexpr int kBwdBatch = GHR_BWD_BATCH;    // list entries per staging round and warp
-constexpr int kBwdStages = GHR_BWD_STAGES;
-constexpr int kBwdCtasPerSm = GHR_BWD_CTAS;
-constexpr size_t kBwdWarpSmem =
-    (sizeof(float4) * 3 + sizeof(uint32_t)) * kBwdStages * kBwdBatch + sizeof(uint32_t) * kBwdStages * (kBwdBatch / 32) + 0;
-static_assert(kBwdWarpSmem % 16 == 0, "per-warp staging area must keep float4 alignment");
+constexpr int kBwdWarps = 4;  // independent warps per CTA
+// Staging as in ghr_blend_fwd.cu: 256-entry rounds, 2-deep ring, 8 warps per SM; frames with millions of pairs take
+// ghr_blend_bwd_wide.cu instead (launch_blend_backward).
+template <int BATCH, int NSTAGE>
+__host__ __device__ constexpr size_t blend_bwd_warp_smem()
+{
+    return ((sizeof(float4) * 3 + sizeof(uint32_t)) * NSTAGE * BATCH + sizeof(uint32_t) * NSTAGE * (BATCH / 32) + 15) / 16 * 16;
+}
 
 // Persistent kernel: warps pull (tile, 4x4 block) work items from a queue ordered by decreasing tile-list
 // length (tile_order_kernel) and work independently (no block-level barrier); see ghr_blend_fwd.cu.
+template <int BATCH, int NSTAGE>
 __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
     int W, int H, int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
     const SortHeader* __restrict__ sh, const uint2* __restrict__ ent_a, const uint2* __restrict__ ent_b,
@@ -117,10 +107,11 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
     const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
     const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas, float* __restrict__ accum)
 {
-    constexpr int BATCH = kBwdBatch, NSTAGE = kBwdStages, PER_LANE = BATCH / 32;
+    constexpr int PER_LANE = BATCH / 32;
     // per-warp staging ring in dynamic shared memory: records, ids, survivor bits
     extern __shared__ __align__(16) unsigned char bwd_smem[];
-    constexpr size_t kWarpBytes = kBwdWarpSmem;
+    constexpr size_t kWarpBytes = blend_bwd_warp_smem<BATCH, NSTAGE>();
+    static_assert(kWarpBytes % 16 == 0, "per-warp staging area must keep float4 alignment");
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t slot = lane >> 4, pl = lane & 15u;  // which of the pixel's two lanes; pixel inside the 4x4 block
     unsigned char* wbase = bwd_smem + warp * kWarpBytes;
@@ -392,24 +383,21 @@ extern "C" int ghr_debug_bwd_trace(void* out, size_t bytes)
 namespace ghr {
 #endif
 
-cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, const char* binning, const char* img,
-                                  const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
-                                  const float* dL_dalpha, float* accum, cudaStream_t s)
+template <int BATCH, int NSTAGE>
+static cudaError_t launch_bwd_config(int ctas_per_sm, const ghr_raster_params& p, const char* geom, const char* binning,
+                                     const char* img, const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
+                                     const float* dL_dalpha, float* accum, cudaStream_t s)
 {
-    StageTimer timer(GHR_STAGE_BLEND_BWD, s);
-    count_launch();
     const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
-    // the queue head is scratch state inside the (otherwise read-only) geometry buffer
-    cudaError_t e = cudaMemsetAsync(&hdr->blend_bwd_ticket, 0, sizeof(uint32_t), s);
-    if (e != cudaSuccess) return e;
     const int64_t items = (int64_t)tiles * 16;
     int64_t ctas = (items + kBwdWarps - 1) / kBwdWarps;
-    if (ctas > 148 * kBwdCtasPerSm) ctas = 148 * kBwdCtasPerSm;
-    const size_t smem = kBwdWarpSmem * kBwdWarps;
-    e = cudaFuncSetAttribute(blend_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (ctas > 148 * ctas_per_sm) ctas = 148 * ctas_per_sm;
+    auto kernel = blend_backward_kernel<BATCH, NSTAGE>;
+    const size_t smem = blend_bwd_warp_smem<BATCH, NSTAGE>() * kBwdWarps;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    blend_backward_kernel<<<(unsigned)ctas, kBwdWarps * 32, smem, s>>>(
+    kernel<<<(unsigned)ctas, kBwdWarps * 32, smem, s>>>(
         p.W, p.H, tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
         reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),
         reinterpret_cast<const uint2*>(binning + L.b_keys_a), reinterpret_cast<const uint2*>(binning + L.b_keys_b),
@@ -417,6 +405,21 @@ cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, 
         reinterpret_cast<const float*>(img + L.i_final_T), reinterpret_cast<const uint32_t*>(img + L.i_n_contrib), dL_dpix,
         dL_ddepth, dL_dalpha, accum);
     return cudaGetLastError();
+}
+
+cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, const char* binning, const char* img,
+                                  const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
+                                  const float* dL_dalpha, float* accum, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_BLEND_BWD, s);
+    count_launch();
+    if (blend_throughput_regime(L.capacity))
+        return launch_blend_backward_wide(p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, s);
+    ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
+    // the queue head is scratch state inside the (otherwise read-only) geometry buffer
+    cudaError_t e = cudaMemsetAsync(&hdr->blend_bwd_ticket, 0, sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    return launch_bwd_config<256, 2>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, s);
 }
 
 }  // namespace ghr

@@ -51,57 +51,36 @@ __device__ __forceinline__ void cp_async_wait()
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-#ifndef GHR_FWD_WARPS
-#define GHR_FWD_WARPS 1
-#endif
-#ifndef GHR_FWD_STAGES
-#define GHR_FWD_STAGES 2
-#endif
-#ifndef GHR_FWD_CTAS
-#define GHR_FWD_CTAS 8
-#endif
-#ifdef GHR_TRACE  // tuning builds only (tools/build_variant.sh): per-item begin/end timestamps
-__device__ unsigned long long g_fwd_trace[1 << 16][8];
-__device__ __forceinline__ unsigned long long gtime()
-{
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-__device__ __forceinline__ uint32_t smid()
-{
-    uint32_t r;
-    asm("mov.u32 %0, %%smid;" : "=r"(r));
-    return r;
-}
-#endif
-constexpr int kBlendWarps = GHR_FWD_WARPS;    // warps per CTA (independent workers)
-#ifndef GHR_FWD_BATCH
-#define GHR_FWD_BATCH 256
-#endif
-constexpr int kBlendBatch = GHR_FWD_BATCH;    // list entries per staging round and warp
-constexpr int kBlendStages = GHR_FWD_STAGES;  // depth of the per-warp staging ring
-constexpr int kBlendCtasPerSm = GHR_FWD_CTAS;
+// Staging: 256-entry rounds in a 2-deep per-warp ring, one warp per CTA, 8 CTAs per SM.  Long rounds amortise the
+// per-round cost and few co-resident warps leave the heavy items the issue slots (measured, tools/fwd_trace.py).
+// Frames with millions of pairs take the other kernel family (ghr_blend_fwd_wide.cu), see launch_blend_forward.
 #ifndef GHR_FWD_KSTEP
 #define GHR_FWD_KSTEP 8
 #endif
-constexpr int KSTEP = GHR_FWD_KSTEP;          // survivors per step (half of them evaluated by each slot)
+constexpr int KSTEP = GHR_FWD_KSTEP;  // survivors per step (half of them evaluated by each slot)
+template <int BATCH, int NSTAGE>
+__host__ __device__ constexpr size_t blend_fwd_warp_smem()
+{
+    return (sizeof(float4) * 3 * BATCH * NSTAGE + sizeof(uint32_t) * (BATCH / 32) * NSTAGE + 15) / 16 * 16;
+}
 
-__global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(
+template <int BATCH, int NSTAGE, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
     int W, int H, int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
     const SortHeader* __restrict__ sh, const uint2* __restrict__ ent_a, const uint2* __restrict__ ent_b,
     const float4* __restrict__ rec, ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
     float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha,
     float* __restrict__ final_T, uint32_t* __restrict__ n_contrib)
 {
-    constexpr int BATCH = kBlendBatch, NSTAGE = kBlendStages, PER_LANE = BATCH / 32;
-    __shared__ __align__(16) float4 s_all[kBlendWarps][NSTAGE][BATCH * 3];
-    __shared__ uint32_t s_keep_all[kBlendWarps][NSTAGE][PER_LANE];  // survivors of each staged round, one bit per entry
+    constexpr int PER_LANE = BATCH / 32;
+    // per-warp staging ring in dynamic shared memory: records, then one survivor bit per staged entry
+    extern __shared__ __align__(16) unsigned char fwd_smem[];
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t slot = lane >> 4, pl = lane & 15u;  // which of the pixel's two lanes; pixel inside the 4x4 block
-    float4(*s_rec)[BATCH * 3] = s_all[warp];
-    uint32_t(*s_keep)[PER_LANE] = s_keep_all[warp];
+    unsigned char* wbase = fwd_smem + warp * blend_fwd_warp_smem<BATCH, NSTAGE>();
+    float4(*s_rec)[BATCH * 3] = reinterpret_cast<float4(*)[BATCH * 3]>(wbase);
+    uint32_t(*s_keep)[PER_LANE] = reinterpret_cast<uint32_t(*)[PER_LANE]>(wbase + sizeof(float4) * 3 * BATCH * NSTAGE);
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
     // {Gaussian id, 4x4-block mask} per list entry, written by tile_ranges_kernel into the key buffer the sort left unused
@@ -313,27 +292,41 @@ extern "C" int ghr_debug_fwd_trace(void* out, size_t bytes)
 namespace ghr {
 #endif
 
+template <int BATCH, int NSTAGE, int WARPS>
+static cudaError_t launch_fwd_config(int ctas_per_sm, const ghr_raster_params& p, const char* geom, const char* binning,
+                                     char* img, const ghr_layout& L, float* out_color, float* out_depth, float* out_alpha,
+                                     cudaStream_t s)
+{
+    const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
+    const int64_t items = (int64_t)tiles * 16;
+    int64_t ctas = (items + WARPS - 1) / WARPS;
+    if (ctas > 148 * ctas_per_sm) ctas = 148 * ctas_per_sm;
+    ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
+    auto kernel = blend_forward_kernel<BATCH, NSTAGE, WARPS>;
+    const size_t smem = blend_fwd_warp_smem<BATCH, NSTAGE>() * WARPS;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kernel<<<(unsigned)ctas, WARPS * 32, smem, s>>>(
+        p.W, p.H, tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
+        reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),
+        reinterpret_cast<const uint2*>(binning + L.b_keys_a), reinterpret_cast<const uint2*>(binning + L.b_keys_b),
+        reinterpret_cast<const float4*>(geom + L.g_rec), hdr, L.capacity, p.background, out_color,
+        out_depth, out_alpha, reinterpret_cast<float*>(img + L.i_final_T), reinterpret_cast<uint32_t*>(img + L.i_n_contrib));
+    return cudaGetLastError();
+}
+
 cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, const char* binning, char* img,
                                  const ghr_layout& L, float* out_color, float* out_depth, float* out_alpha,
                                  cudaStream_t s)
 {
     StageTimer timer(GHR_STAGE_BLEND_FWD, s);
     count_launch();
-    const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
-    const int64_t items = (int64_t)tiles * 16;
-    int64_t ctas = (items + kBlendWarps - 1) / kBlendWarps;
-    if (ctas > 148 * kBlendCtasPerSm) ctas = 148 * kBlendCtasPerSm;
-    const int64_t capacity = L.capacity;
+    if (blend_throughput_regime(L.capacity))
+        return launch_blend_forward_wide(p, geom, binning, img, L, out_color, out_depth, out_alpha, s);
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
     cudaError_t e = cudaMemsetAsync(&hdr->blend_fwd_ticket, 0, sizeof(uint32_t), s);  // render may run twice per preprocess
     if (e != cudaSuccess) return e;
-    blend_forward_kernel<<<(unsigned)ctas, kBlendWarps * 32, 0, s>>>(
-        p.W, p.H, tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
-        reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),
-        reinterpret_cast<const uint2*>(binning + L.b_keys_a), reinterpret_cast<const uint2*>(binning + L.b_keys_b),
-        reinterpret_cast<const float4*>(geom + L.g_rec), hdr, capacity, p.background, out_color,
-        out_depth, out_alpha, reinterpret_cast<float*>(img + L.i_final_T), reinterpret_cast<uint32_t*>(img + L.i_n_contrib));
-    return cudaGetLastError();
+    return launch_fwd_config<256, 2, 1>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, s);
 }
 
 }  // namespace ghr

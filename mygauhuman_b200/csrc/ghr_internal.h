@@ -56,6 +56,18 @@ inline int64_t sort_tiles(int64_t capacity)
     return (capacity + tile - 1) / tile;
 }
 
+// Blend kernels: staging configuration by problem size (see ghr_blend_fwd.cu).  `capacity` bounds the number of
+// (Gaussian, tile) pairs; GHR_BLEND_REGIME=latency|throughput overrides (tuning).
+inline bool blend_throughput_regime(int64_t capacity)
+{
+    static const int forced = [] {
+        const char* e = getenv("GHR_BLEND_REGIME");
+        return !e ? 0 : (e[0] == 't' ? 2 : 1);
+    }();
+    if (forced) return forced == 2;
+    return capacity > (int64_t(1) << 19);
+}
+
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
 // rasterizer_impl.cu:35-50 getHigherMsb
@@ -86,6 +98,13 @@ cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, c
 cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, const char* binning, const char* img,
                                   const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
                                   const float* dL_dalpha, float* accum, cudaStream_t s);
+// throughput-regime variants (ghr_blend_{fwd,bwd}_wide.cu); called by the two launchers above
+cudaError_t launch_blend_forward_wide(const ghr_raster_params& p, const char* geom, const char* binning, char* img,
+                                      const ghr_layout& L, float* out_color, float* out_depth, float* out_alpha,
+                                      cudaStream_t s);
+cudaError_t launch_blend_backward_wide(const ghr_raster_params& p, const char* geom, const char* binning, const char* img,
+                                       const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
+                                       const float* dL_dalpha, float* accum, cudaStream_t s);
 cudaError_t launch_preprocess_backward(const ghr_raster_params& p, const int32_t* radii, const char* geom,
                                        const ghr_layout& L, const float* accum, float* dL_dmean2D, float* dL_dcolor,
                                        float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,

@@ -242,3 +242,19 @@ def test_autograd_module_matches_raw_calls():
         GaussianRasterizer(rs)(means3D=means3D, means2D=means2D, opacities=opac, cov3D_precomp=cov)
     with pytest.raises(Exception):
         GaussianRasterizer(rs)(means3D=means3D, means2D=means2D, opacities=opac, colors_precomp=colors)
+
+
+def test_throughput_regime_kernels_pass_the_same_parity_tests():
+    """Frames with more than 2^19 (Gaussian, tile) pairs take the other blend kernel family (ghr_blend_*_wide.cu,
+    8x4-pixel blocks, no block masks).  The regime is chosen once per process, so the forward/backward parity tests of
+    this file are re-run in a child process with GHR_BLEND_REGIME=throughput."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("GHR_BLEND_REGIME"):
+        pytest.skip("already inside a forced-regime run")
+    env = dict(os.environ, GHR_BLEND_REGIME="throughput")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_raster_parity_gpu.py", "-x", "-q", "-m", "gpu", "-W", "ignore",
+                        "-p", "no:cacheprovider"], cwd=root, env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]

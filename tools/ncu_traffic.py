@@ -1,0 +1,53 @@
+"""Summarise an `ncu --set full` capture of one bench step (ncu -i X.ncu-rep --page raw --csv > raw.csv):
+per kernel: duration, DRAM bytes read/written, issue activity, registers; per bench stage: DRAM bytes per launch
+(profiles/traffic.json, what bench.py reports as roofline.traffic).
+
+    python tools/ncu_traffic.py raw.csv profiles/rNN_ncu_full_summary.csv profiles/traffic.json
+"""
+import csv, json, sys
+
+STAGE_OF = {"preprocess_kernel": "preprocess", "emit_keys_kernel": "emit_keys", "sort_histogram_kernel": "sort",
+            "onesweep_pass_kernel": "sort", "tile_ranges_kernel": "tile_ranges", "tile_order_kernel": "tile_ranges",
+            "blend_forward_kernel": "blend_fwd", "blend_backward_kernel": "blend_bwd",
+            "preprocess_backward_kernel": "preprocess_bwd", "lbs_deform_forward_kernel": "lbs_fwd",
+            "lbs_deform_backward_kernel": "lbs_bwd", "nearest_vertex_smem_kernel": "knn", "lbs_pose_kernel": "lbs_joints",
+            "lbs_vertex_offsets_kernel": "lbs_joints"}
+UNIT = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+COLS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "smsp__inst_executed.sum",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_sector_hit_rate.pct", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum"]
+
+
+def main(raw, out_csv, out_json):
+    rows = list(csv.reader(open(raw)))
+    h, units = rows[0], rows[1]
+    kn = h.index("Kernel Name")
+    cols = [c for c in COLS if c in h]
+    per_stage, seen = {}, {}
+    with open(out_csv, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["kernel", "stage"] + [f"{c} [{units[h.index(c)]}]" for c in cols])
+        for r in rows[2:]:
+            name = r[kn]
+            base = name.split("(")[0].replace("void ", "").split("<")[0].split("::")[-1].strip()
+            stage = STAGE_OF.get(base, "")
+            w.writerow([name[:70], stage] + [r[h.index(c)] for c in cols])
+            if stage:
+                rd = float(r[h.index("dram__bytes_read.sum")].replace(",", "")) * UNIT[units[h.index("dram__bytes_read.sum")]]
+                wr = float(r[h.index("dram__bytes_write.sum")].replace(",", "")) * UNIT[units[h.index("dram__bytes_write.sum")]]
+                key = (stage, base)
+                seen.setdefault(key, []).append(rd + wr)
+    # a stage's traffic = sum over its kernels of (mean per launch x launches per step); the sort has 1 histogram + its passes
+    launches_per_step = {"onesweep_pass_kernel": None}
+    for (stage, base), v in seen.items():
+        n = len(v) if base == "onesweep_pass_kernel" else 1
+        if base == "onesweep_pass_kernel":
+            n = 5  # passes of a 43-45 bit key
+        per_stage[stage] = per_stage.get(stage, 0.0) + n * sum(v) / len(v)
+    json.dump({k: int(v) for k, v in sorted(per_stage.items())}, open(out_json, "w"), indent=1)
+    print(json.dumps(per_stage, indent=1))
+
+
+if __name__ == "__main__":
+    main(*sys.argv[1:4])
