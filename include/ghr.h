@@ -160,6 +160,33 @@ int ghr_backward(const ghr_raster_params* prm, const int32_t* radii, const void*
                  float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
                  float* dL_dsh, float* dL_dscales, float* dL_drotations, void* stream);
 
+/* ---- multi-attribute rendering ------------------------------------------------------------------------------------
+ * The reference's render() (gaussian_renderer/__init__.py:203-272) calls the whole rasteriser seven times per view on the
+ * same Gaussians, changing only colors_precomp (image, normal, world normal, albedo, occlusion, roughness, axis).  Here
+ * projection, key emission, sort, tile ranges and block masks are done once (ghr_forward_preprocess + ghr_forward_render
+ * with the first attribute) and every further attribute only re-runs the blend on the same lists:
+ *
+ *   ghr_forward_reblend   writes `colors` ([P,3], used as given, like colors_precomp) into the geometry records and
+ *                         blends again; out_depth / out_alpha receive the same values as in the first pass.
+ *   ghr_backward_blend    blend backward of ONE attribute (its colours, its image gradient).  It ADDS into `accum`
+ *                         ([P,12] floats, zeroed by the caller before the first attribute): slots 3-8 (mean2D, conic,
+ *                         opacity) sum over the attributes; slots 0-2 hold this attribute's dL_dcolors, which the
+ *                         caller copies out and clears before the next attribute.
+ *   ghr_backward_finish   the per-Gaussian backward (reference backward.cu:144-396) from the summed record.
+ * dL_dout_depth / dL_dout_alpha may be NULL (= zero) in ghr_backward_blend. */
+int ghr_forward_reblend(const ghr_raster_params* prm, const float* colors, void* geom, size_t geom_bytes,
+                        const void* binning, size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes,
+                        float* out_color, float* out_depth, float* out_alpha, void* stream);
+int ghr_backward_blend(const ghr_raster_params* prm, const float* colors, void* geom, size_t geom_bytes,
+                       const void* binning, size_t binning_bytes, int64_t capacity, const void* img, size_t img_bytes,
+                       const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+                       const float* zeros_plane /* [H*W] zeros, used when a gradient plane is NULL */, float* accum,
+                       void* stream);
+int ghr_backward_finish(const ghr_raster_params* prm, const int32_t* radii, const void* geom, size_t geom_bytes,
+                        int64_t capacity, const float* accum, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                        float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+                        void* stream);
+
 /* Rasterizer::markVisible / checkFrustum (rasterizer_impl.cu:54-66,141-153)
  * for _C.mark_visible (dgr/rasterize_points.cu:209-228).  present: uint8[P]. */
 int ghr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

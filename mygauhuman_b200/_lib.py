@@ -74,6 +74,12 @@ SIGNATURES = {
                                      C.c_void_p]),
     "ghr_backward": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
                                C.c_int64, C.c_void_p, C.c_size_t] + [C.c_void_p] * 13),
+    "ghr_forward_reblend": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                      C.c_int64, C.c_void_p, C.c_size_t] + [C.c_void_p] * 4),
+    "ghr_backward_blend": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                     C.c_int64, C.c_void_p, C.c_size_t] + [C.c_void_p] * 6),
+    "ghr_backward_finish": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_int64]
+                            + [C.c_void_p] * 10),
     "ghr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ghr_sort_workspace_bytes": (C.c_size_t, [C.c_int64]),
     "ghr_sort_pairs_u64": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_size_t, C.c_void_p, C.c_void_p]),

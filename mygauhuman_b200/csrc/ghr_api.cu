@@ -190,6 +190,80 @@ int ghr_backward(const ghr_raster_params* prm, const int32_t* radii, const void*
                       s, "preprocess_backward");
 }
 
+// ---- multi-attribute rendering (include/ghr.h) ------------------------------------------------------------------
+static int multi_layout(const ghr_raster_params* prm, int64_t capacity, const void* geom, size_t geom_bytes,
+                        const void* binning, size_t binning_bytes, const void* img, size_t img_bytes, ghr_layout* L)
+{
+    if (ghr_state_layout(prm->P, capacity, prm->W, prm->H, L) != GHR_OK) return GHR_ERR_BAD_ARG;
+    if (!geom || geom_bytes < L->geom_bytes || !img || img_bytes < L->img_bytes || !binning ||
+        binning_bytes < L->binning_bytes)
+        return GHR_ERR_BUFFER;
+    return GHR_OK;
+}
+
+int ghr_forward_reblend(const ghr_raster_params* prm, const float* colors, void* geom, size_t geom_bytes,
+                        const void* binning, size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes,
+                        float* out_color, float* out_depth, float* out_alpha, void* stream)
+{
+    int r = validate(prm);
+    if (r != GHR_OK) return r;
+    if (!colors || !out_color || !out_depth || !out_alpha) return GHR_ERR_BAD_ARG;
+    if (prm->P == 0) return GHR_OK;
+    ghr_layout L;
+    if ((r = multi_layout(prm, capacity, geom, geom_bytes, binning, binning_bytes, img, img_bytes, &L)) != GHR_OK) return r;
+    cudaStream_t s = (cudaStream_t)stream;
+    r = check_cuda(launch_recolor(prm->P, colors, (char*)geom, L, s), "recolor");
+    if (r != GHR_OK) return r;
+    return stage_done(prm,
+                      launch_blend_forward(*prm, (const char*)geom, (const char*)binning, (char*)img, L, out_color,
+                                           out_depth, out_alpha, s),
+                      s, "blend_forward");
+}
+
+int ghr_backward_blend(const ghr_raster_params* prm, const float* colors, void* geom, size_t geom_bytes,
+                       const void* binning, size_t binning_bytes, int64_t capacity, const void* img, size_t img_bytes,
+                       const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+                       const float* zeros_plane, float* accum, void* stream)
+{
+    int r = validate(prm);
+    if (r != GHR_OK) return r;
+    if (prm->P == 0) return GHR_OK;
+    if (!colors || !dL_dout_color || !accum || misaligned(accum, 16)) return GHR_ERR_BAD_ARG;
+    if ((!dL_dout_depth || !dL_dout_alpha) && !zeros_plane) return GHR_ERR_BAD_ARG;
+    ghr_layout L;
+    if ((r = multi_layout(prm, capacity, geom, geom_bytes, binning, binning_bytes, img, img_bytes, &L)) != GHR_OK) return r;
+    cudaStream_t s = (cudaStream_t)stream;
+    r = check_cuda(launch_recolor(prm->P, colors, (char*)geom, L, s), "recolor");
+    if (r != GHR_OK) return r;
+    return stage_done(prm,
+                      launch_blend_backward(*prm, (const char*)geom, (const char*)binning, (const char*)img, L,
+                                            dL_dout_color, dL_dout_depth ? dL_dout_depth : zeros_plane,
+                                            dL_dout_alpha ? dL_dout_alpha : zeros_plane, accum, s),
+                      s, "blend_backward");
+}
+
+int ghr_backward_finish(const ghr_raster_params* prm, const int32_t* radii, const void* geom, size_t geom_bytes,
+                        int64_t capacity, const float* accum, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                        float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+                        void* stream)
+{
+    int r = validate(prm);
+    if (r != GHR_OK) return r;
+    if (prm->P == 0) return GHR_OK;
+    if (!radii || !accum || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dmeans3D || !dL_dcov3D ||
+        misaligned(accum, 16) || misaligned(dL_drotations, 16))
+        return GHR_ERR_BAD_ARG;
+    if (prm->shs && !dL_dsh) return GHR_ERR_BAD_ARG;
+    ghr_layout L;
+    if (ghr_state_layout(prm->P, capacity, prm->W, prm->H, &L) != GHR_OK) return GHR_ERR_BAD_ARG;
+    if (!geom || geom_bytes < L.geom_bytes) return GHR_ERR_BUFFER;
+    cudaStream_t s = (cudaStream_t)stream;
+    return stage_done(prm,
+                      launch_preprocess_backward(*prm, radii, (const char*)geom, L, accum, dL_dmeans2D, dL_dcolors,
+                                                 dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, s),
+                      s, "preprocess_backward");
+}
+
 int ghr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream)
 {

@@ -142,6 +142,23 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(int tiles, const uint2
     }
 }
 
+__global__ void __launch_bounds__(256) recolor_kernel(int P, const float* __restrict__ colors, float4* __restrict__ rec)
+{
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= P) return;
+    float4 r2 = rec[3 * (size_t)idx + 2];
+    r2.x = colors[3 * (size_t)idx]; r2.y = colors[3 * (size_t)idx + 1]; r2.z = colors[3 * (size_t)idx + 2];
+    rec[3 * (size_t)idx + 2] = r2;  // .w (cull extent) kept
+}
+
+cudaError_t launch_recolor(int P, const float* colors, char* geom, const ghr_layout& L, cudaStream_t s)
+{
+    if (P <= 0) return cudaSuccess;
+    count_launch();
+    recolor_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, colors, reinterpret_cast<float4*>(geom + L.g_rec));
+    return cudaGetLastError();
+}
+
 cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binning,
                              const ghr_layout& L, int64_t capacity, cudaStream_t s)
 {

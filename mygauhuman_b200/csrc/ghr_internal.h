@@ -109,6 +109,8 @@ cudaError_t launch_preprocess_backward(const ghr_raster_params& p, const int32_t
                                        const ghr_layout& L, const float* accum, float* dL_dmean2D, float* dL_dcolor,
                                        float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                                        float* dL_dscale, float* dL_drot, cudaStream_t s);
+// rec[idx].rgb = colors[idx] for every Gaussian (multi-attribute rendering)
+cudaError_t launch_recolor(int P, const float* colors, char* geom, const ghr_layout& L, cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* V, uint8_t* present, cudaStream_t s);
 // ---- LBS (ghr_lbs_pose.cu, ghr_lbs_deform.cu, ghr_knn.cu) -------------------
 struct DeformOut {

@@ -210,6 +210,109 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             dsh.view(P, M, 3), dscales.view(P, 3), drot.view(P, 4))
 
 
+# ---- multi-attribute rendering: one projection / sort / tile binning, one blend per attribute --------------------
+# (reference gaussian_renderer/__init__.py:203-272 runs the whole rasteriser once per attribute; see include/ghr.h)
+
+def _rec_colors(P, W, H, geom):
+    L = state_layout(P, 0, W, H)
+    return geom[L.g_rec:L.g_rec + P * 48].view(torch.float32).view(P, 3, 4)[:, 2, 0:3]
+
+
+def rasterize_gaussians_multi(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                              viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree,
+                              campos, prefiltered, debug, extra_colors):
+    """rasterize_gaussians for the first attribute (SH or `colors`), then one re-blend per [P,3] tensor of
+    `extra_colors` on the same sorted lists.  Returns the tuple of rasterize_gaussians plus (extra images, colours the
+    first attribute was blended with)."""
+    out = rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                              viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree,
+                              campos, prefiltered, debug)
+    num_rendered, out_color, out_depth, out_alpha, radii, geom, binning, img = out
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    dev = means3D.device
+    images = []
+    if P == 0:
+        return out + ([torch.zeros(3, H, W, dtype=torch.float32, device=dev) + background.view(3, 1, 1)
+                       for _ in extra_colors], torch.zeros(0, 3, device=dev))
+    first_colors = _rec_colors(P, W, H, geom).clone() if extra_colors else None
+    capacity = _cap_of.get(binning.data_ptr(), int(num_rendered))
+    with _lib.on_device(dev):
+        keep = []
+        p = _params(keep, background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                    viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug)
+        scratch = torch.empty(2, H, W, dtype=torch.float32, device=dev)  # depth / alpha come out the same every time
+        l, s = lib(), _stream(dev)
+        for c in extra_colors:
+            if c.dim() != 2 or c.size(0) != P or c.size(1) != 3:
+                raise RuntimeError("every extra attribute must have dimensions (num_points, 3)")
+            cp, c = _ptr(c)
+            keep.append(c)
+            image = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+            check(l.ghr_forward_reblend(C.byref(p), cp, geom.data_ptr(), geom.numel(), binning.data_ptr(),
+                                        binning.numel(), capacity, img.data_ptr(), img.numel(), image.data_ptr(),
+                                        scratch[0].data_ptr(), scratch[1].data_ptr(), s), "ghr_forward_reblend")
+            images.append(image)
+    return out + (images, first_colors)
+
+
+def rasterize_gaussians_multi_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                       cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color,
+                                       dL_dout_depth, dL_dout_alpha, sh, degree, campos, geomBuffer, R, binningBuffer,
+                                       imageBuffer, alphas, debug, first_colors, extra_colors, dL_dextra):
+    """Backward of rasterize_gaussians_multi: one blend backward per attribute into a shared accumulator, then one
+    per-Gaussian backward.  `dL_dextra[k]` may be None (attribute k did not reach the loss).  Returns the tuple of
+    rasterize_gaussians_backward plus the list of dL_dextra_colors."""
+    P = means3D.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    dev = means3D.device
+    if P == 0:
+        z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
+        return (z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4), [z(0, 3) for _ in extra_colors])
+    capacity = _cap_of.get(binningBuffer.data_ptr(), int(R))
+    with _lib.on_device(dev):
+        keep = []
+        p = _params(keep, background, means3D, colors, means3D, scales, rotations, scale_modifier, cov3D_precomp,
+                    viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, False, debug)
+        sizes = [12, 4, 3, 3, 1, 3, 6, 3, 3 * M]
+        flat = torch.empty(P * sum(sizes), dtype=torch.float32, device=dev)
+        views, o = [], 0
+        for n in sizes:
+            views.append(flat[o:o + P * n])
+            o += P * n
+        accum, drot, dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dscales, dsh = views
+        accum.zero_()
+        accum2 = accum.view(P, 12)
+        zeros_plane = torch.zeros(H * W, dtype=torch.float32, device=dev)
+        f32c = lambda t: t.contiguous() if t.dtype == torch.float32 else t.float().contiguous()
+        radii = radii.contiguous()
+        l, s = lib(), _stream(dev)
+        geo = (geomBuffer.data_ptr(), geomBuffer.numel(), binningBuffer.data_ptr(), binningBuffer.numel(), capacity,
+               imageBuffer.data_ptr(), imageBuffer.numel())
+        dextra = []
+        for c, g in zip(extra_colors, dL_dextra):
+            if g is None:
+                dextra.append(None)
+                continue
+            cp, c = _ptr(c)
+            g = f32c(g)
+            check(l.ghr_backward_blend(C.byref(p), cp, *geo, g.data_ptr(), None, None, zeros_plane.data_ptr(),
+                                       accum.data_ptr(), s), "ghr_backward_blend")
+            dextra.append(accum2[:, 0:3].clone())
+            accum2[:, 0:3].zero_()
+        # the first attribute last: its colour gradient stays in the record for the SH backward
+        g = [f32c(t) for t in (dL_dout_color, dL_dout_depth, dL_dout_alpha)]
+        cp, c0 = _ptr(first_colors)
+        check(l.ghr_backward_blend(C.byref(p), cp, *geo, g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(),
+                                   zeros_plane.data_ptr(), accum.data_ptr(), s), "ghr_backward_blend")
+        check(l.ghr_backward_finish(C.byref(p), radii.data_ptr(), geomBuffer.data_ptr(), geomBuffer.numel(), capacity,
+                                    accum.data_ptr(), dmeans2D.data_ptr(), dcolors.data_ptr(), dopacity.data_ptr(),
+                                    dmeans3D.data_ptr(), dcov3D.data_ptr(), dsh.data_ptr() if M else None,
+                                    dscales.data_ptr(), drot.data_ptr(), s), "ghr_backward_finish")
+    return (dmeans2D.view(P, 3), dcolors.view(P, 3), dopacity.view(P, 1), dmeans3D.view(P, 3), dcov3D.view(P, 6),
+            dsh.view(P, M, 3), dscales.view(P, 3), drot.view(P, 4), dextra)
+
+
 def mark_visible(means3D, viewmatrix, projmatrix):
     """markVisible, rasterize_points.cu:209-228."""
     P = means3D.size(0)

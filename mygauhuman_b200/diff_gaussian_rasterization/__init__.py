@@ -88,6 +88,48 @@ class _RasterizeGaussians(torch.autograd.Function):
         return g_means3D, g_means2D, g_sh, g_colors, g_opacities, g_scales, g_rotations, g_cov3D, None
 
 
+class _RasterizeGaussiansMulti(torch.autograd.Function):
+    """Several attributes over one set of Gaussians: projection, sort and tile binning once, one blend per attribute
+    (what the reference's render(), gaussian_renderer/__init__.py:203-272, does with one full rasteriser call each)."""
+
+    @staticmethod
+    def forward(ctx, raster_settings, means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                cov3Ds_precomp, *extra_colors):
+        rs = raster_settings
+        native_args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
+                       cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
+                       rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, extra_colors)
+        (num_rendered, color, depth, alpha, radii, geom_state, binning_state, image_state, extra_images,
+         first_colors) = _call_native(_C.rasterize_gaussians_multi, native_args, rs.debug, "fw")
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.has_means2D = torch.is_tensor(means2D)
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom_state,
+                              binning_state, image_state, alpha, first_colors, *extra_colors)
+        ctx.mark_non_differentiable(radii)
+        ctx.set_materialize_grads(False)
+        return (color, radii, depth, alpha) + tuple(extra_images)
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_radii, grad_depth, grad_alpha, *grad_extra):
+        rs = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom_state, binning_state,
+         image_state, alpha, first_colors) = ctx.saved_tensors[:12]
+        extra_colors = ctx.saved_tensors[12:]
+        zeros = lambda c: torch.zeros(c, rs.image_height, rs.image_width, dtype=torch.float32, device=means3D.device)
+        grad_color = zeros(3) if grad_color is None else grad_color
+        grad_depth = zeros(1) if grad_depth is None else grad_depth
+        grad_alpha = zeros(1) if grad_alpha is None else grad_alpha
+        native_args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+                       rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha, sh,
+                       rs.sh_degree, rs.campos, geom_state, ctx.num_rendered, binning_state, image_state, alpha,
+                       rs.debug, first_colors, extra_colors, grad_extra)
+        (g_means2D, g_colors, g_opacities, g_means3D, g_cov3D, g_sh, g_scales, g_rotations,
+         g_extra) = _call_native(_C.rasterize_gaussians_multi_backward, native_args, rs.debug, "bw")
+        return (None, g_means3D, g_means2D if ctx.has_means2D else None, g_sh, g_colors, g_opacities, g_scales,
+                g_rotations, g_cov3D) + tuple(g_extra)
+
+
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
@@ -125,3 +167,24 @@ class GaussianRasterizer(nn.Module):
         cov3D_precomp = _absent() if cov3D_precomp is None else cov3D_precomp
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
                                    self.raster_settings)
+
+    def forward_multi(self, means3D, means2D, opacities, extra_colors, shs=None, colors_precomp=None, scales=None,
+                      rotations=None, cov3D_precomp=None):
+        """forward() plus one more image per [P,3] tensor in `extra_colors`, all blended over the same projected,
+        sorted and tile-binned Gaussians.  Equivalent to calling forward() once per attribute with
+        colors_precomp=extra_colors[k] (reference gaussian_renderer/__init__.py:214-272), bit for bit in the images.
+        Returns (color, radii, depth, alpha, [extra images])."""
+        if (shs is None) == (colors_precomp is None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        has_scale_rot = scales is not None or rotations is not None
+        incomplete_scale_rot = scales is None or rotations is None
+        if (incomplete_scale_rot and cov3D_precomp is None) or (has_scale_rot and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        shs = _absent() if shs is None else shs
+        colors_precomp = _absent() if colors_precomp is None else colors_precomp
+        scales = _absent() if scales is None else scales
+        rotations = _absent() if rotations is None else rotations
+        cov3D_precomp = _absent() if cov3D_precomp is None else cov3D_precomp
+        out = _RasterizeGaussiansMulti.apply(self.raster_settings, means3D, means2D, shs, colors_precomp, opacities,
+                                             scales, rotations, cov3D_precomp, *extra_colors)
+        return out[0], out[1], out[2], out[3], list(out[4:])

@@ -1,0 +1,157 @@
+"""-m gpu: GaussianRasterizer.forward_multi -- the reference's render() (gaussian_renderer/__init__.py:203-272) blends
+seven attributes with seven full rasteriser calls; forward_multi projects / sorts / bins once and re-blends per
+attribute.  Checked against one forward() per attribute (the reference's own call pattern), through our operator API and,
+when oracle/_ref is built, through the UNMODIFIED reference CUDA rasteriser.
+
+Bars: images bit-identical to the per-attribute calls of our own operator (same kernels, same lists, same order),
+<= 1e-5 abs against the reference CUDA; gradients <= 1e-4 of each tensor's scale (fp32 atomics order).
+"""
+import numpy as np
+import pytest
+import torch
+
+from tests import common as Cm
+
+pytestmark = pytest.mark.gpu
+
+N_ATTR = 6  # normal, world normal, albedo, occlusion, roughness, axis (the reference's extra passes)
+
+
+def _settings(tc):
+    from mygauhuman_b200.diff_gaussian_rasterization import GaussianRasterizationSettings
+    return GaussianRasterizationSettings(tc["H"], tc["W"], tc["tanfovx"], tc["tanfovy"], tc["bg"], tc["scale_modifier"],
+                                         tc["view"], tc["proj"], tc["degree"], tc["campos"], False, False)
+
+
+def _leaves(tc, mode, seed):
+    g = torch.Generator().manual_seed(seed)
+    P = tc["P"]
+    lv = {"means3D": tc["means3D"].clone(), "opacity": tc["opacity"].clone()}
+    if mode == "precomp":
+        lv["colors"] = tc["colors"].clone()
+        lv["cov3D"] = tc["cov3D"].clone()
+    else:
+        lv["sh"] = tc["sh"].clone()
+        lv["scales"] = tc["scales"].clone()
+        lv["rotations"] = tc["rotations"].clone()
+    for k in range(N_ATTR):
+        lv[f"attr{k}"] = torch.rand(P, 3, generator=g).cuda()
+    return {k: v.requires_grad_(True) for k, v in lv.items()}
+
+
+def _geometry_kwargs(lv):
+    kw = dict(means3D=lv["means3D"], means2D=torch.zeros_like(lv["means3D"], requires_grad=True), opacities=lv["opacity"])
+    if "cov3D" in lv:
+        kw.update(colors_precomp=lv["colors"], cov3D_precomp=lv["cov3D"])
+    else:
+        kw.update(shs=lv["sh"], scales=lv["scales"], rotations=lv["rotations"])
+    return kw
+
+
+def _weights(tc, seed):
+    g = torch.Generator().manual_seed(seed)
+    H, W = tc["H"], tc["W"]
+    return [torch.randn(3, H, W, generator=g).cuda() for _ in range(N_ATTR + 1)], \
+        torch.randn(1, H, W, generator=g).cuda(), torch.randn(1, H, W, generator=g).cuda()
+
+
+def _loss(images, depth, alpha, weights):
+    wi, wd, wa = weights
+    loss = (depth * wd).sum() + (alpha * wa).sum()
+    for im, w in zip(images, wi):
+        loss = loss + (im * w).sum()
+    return loss
+
+
+def _separate(rast, lv, used):
+    """The reference's call pattern: one forward() per attribute."""
+    kw = _geometry_kwargs(lv)
+    color, radii, depth, alpha = rast(**kw)
+    images = [color]
+    geo = {k: v for k, v in kw.items() if k not in ("shs", "colors_precomp")}
+    for k in used:
+        images.append(rast(colors_precomp=lv[f"attr{k}"], **geo)[0])
+    return images, radii, depth, alpha
+
+
+def _multi(rast, lv, used):
+    kw = _geometry_kwargs(lv)
+    color, radii, depth, alpha, extra = rast.forward_multi(extra_colors=[lv[f"attr{k}"] for k in used], **kw)
+    return [color] + extra, radii, depth, alpha
+
+
+def _run(fn, rast, lv, used, weights):
+    for v in lv.values():
+        v.grad = None
+    images, radii, depth, alpha = fn(rast, lv, used)
+    wi = [weights[0][0]] + [weights[0][k + 1] for k in used]
+    _loss(images, depth, alpha, (wi, weights[1], weights[2])).backward()
+    torch.cuda.synchronize()
+    grads = {k: (None if v.grad is None else v.grad.clone()) for k, v in lv.items()}
+    return [im.detach().clone() for im in images], radii.clone(), depth.detach().clone(), alpha.detach().clone(), grads
+
+
+@pytest.mark.parametrize("P,W,H,mode", [(3000, 160, 128, "precomp"), (2500, 200, 152, "sh_scale_rot"),
+                                        (20000, 512, 512, "precomp")])
+def test_forward_multi_equals_one_call_per_attribute(P, W, H, mode):
+    from mygauhuman_b200.diff_gaussian_rasterization import GaussianRasterizer
+    tc = Cm.to_torch(Cm.raster_case(P, W, H, seed=P, mode=mode), "cuda")
+    lv = _leaves(tc, mode, seed=1)
+    rast = GaussianRasterizer(_settings(tc))
+    weights = _weights(tc, seed=2)
+    used = list(range(N_ATTR))
+    si, sr, sd, sa, sg = _run(_separate, rast, lv, used, weights)
+    mi, mr, md, ma, mg = _run(_multi, rast, lv, used, weights)
+    assert torch.equal(sr, mr)
+    assert torch.equal(sd, md) and torch.equal(sa, ma)
+    assert len(si) == len(mi) == N_ATTR + 1
+    for k, (a, b) in enumerate(zip(si, mi)):
+        assert torch.equal(a, b), f"attribute image {k} differs"
+    for k in sg:
+        assert (sg[k] is None) == (mg[k] is None), k
+        if sg[k] is not None:
+            assert Cm.rel_err(mg[k].cpu().numpy(), sg[k].cpu().numpy()) < 1e-4, k
+
+
+def test_unused_attributes_and_missing_gradients():
+    """An attribute image that does not reach the loss gets no backward pass; depth/alpha may be unused too."""
+    from mygauhuman_b200.diff_gaussian_rasterization import GaussianRasterizer
+    tc = Cm.to_torch(Cm.raster_case(2000, 128, 96, seed=9, mode="precomp"), "cuda")
+    lv = _leaves(tc, "precomp", seed=3)
+    rast = GaussianRasterizer(_settings(tc))
+    kw = _geometry_kwargs(lv)
+    color, radii, depth, alpha, extra = rast.forward_multi(extra_colors=[lv["attr0"], lv["attr1"]], **kw)
+    w = torch.randn(3, tc["H"], tc["W"], generator=torch.Generator().manual_seed(4)).cuda()
+    (extra[1] * w).sum().backward()           # only the second extra attribute is used
+    g_multi = {k: v.grad.clone() for k, v in lv.items() if v.grad is not None}
+    assert "attr0" not in g_multi or float(g_multi["attr0"].abs().max()) == 0.0
+    assert float(lv["colors"].grad.abs().max()) == 0.0
+    for v in lv.values():
+        v.grad = None
+    geo = {k: v for k, v in kw.items() if k != "colors_precomp"}
+    (rast(colors_precomp=lv["attr1"], **geo)[0] * w).sum().backward()
+    for k in ("attr1", "means3D", "opacity", "cov3D"):
+        assert Cm.rel_err(g_multi[k].cpu().numpy(), lv[k].grad.cpu().numpy()) < 1e-4, k
+
+
+def test_forward_multi_vs_reference_cuda_per_attribute():
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        pytest.skip("oracle/_ref not built")
+    from mygauhuman_b200.diff_gaussian_rasterization import GaussianRasterizer
+    tc = Cm.to_torch(Cm.raster_case(4000, 256, 192, seed=21, mode="precomp"), "cuda")
+    lv = _leaves(tc, "precomp", seed=5)
+    rast = GaussianRasterizer(_settings(tc))
+    with torch.no_grad():
+        images, radii, depth, alpha = _multi(rast, lv, list(range(N_ATTR)))
+    ref = ref_cuda.RefRasterizer()
+    attrs = [lv["colors"]] + [lv[f"attr{k}"] for k in range(N_ATTR)]
+    for k, c in enumerate(attrs):
+        n, rcolor, rdepth, ralpha, rradii = ref.forward(tc["bg"], tc["means3D"], c.detach(), tc["opacity"], Cm.empty(),
+                                                        Cm.empty(), tc["scale_modifier"], tc["cov3D"], tc["view"],
+                                                        tc["proj"], tc["tanfovx"], tc["tanfovy"], tc["H"], tc["W"],
+                                                        Cm.empty(), tc["degree"], tc["campos"])
+        np.testing.assert_allclose(images[k].cpu().numpy(), rcolor.cpu().numpy(), atol=1e-5, rtol=0)
+        assert torch.equal(radii, rradii)
+        np.testing.assert_allclose(depth.cpu().numpy(), rdepth.cpu().numpy(), atol=1e-5, rtol=0)
+        np.testing.assert_allclose(alpha.cpu().numpy(), ralpha.cpu().numpy(), atol=1e-5, rtol=0)

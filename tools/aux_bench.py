@@ -5,6 +5,8 @@
   * forward-only render FPS at the ZJU 512x512 shape (LBS + cov + SH + rasteriser forward), ours vs reference
   * stress render: 3M Gaussians at 1920x1080, forward only, ours vs the reference CUDA rasteriser
   * distCUDA2 (simple-knn) at 6 890 / 50 000 / 300 000 points, ours vs reference
+  * seven-attribute render (reference render(): image + normal + world normal + albedo + occlusion + roughness +
+    axis), rasteriser forward + backward at the ZJU shape: forward_multi vs one call per attribute vs the reference CUDA
 
 Every timing: CUDA events on the launching stream around each call, L2 flushed (256 MiB fill) between calls,
 median over the iterations.  Prints one JSON object.
@@ -235,13 +237,80 @@ def knn(quick):
     return rows
 
 
+# ---------------------------------------------------------------------------------------------------------
+def render7(quick):
+    """Rasteriser forward + backward of the reference's seven attribute passes (gaussian_renderer/__init__.py:203-272),
+    50k Gaussians on the posed template, 512x512, colours and covariances precomputed (what render() feeds it)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from tests import common as Cm
+    P, W, H, NA = 50_000, 512, 512, 6
+    smpl = S.make_smpl_model(0)
+    tv = S.big_pose_vertices(smpl, S.big_pose_params())
+    tc = Cm.to_torch(Cm.raster_case(P, W, H, seed=0, mode="precomp", cloud=tv.numpy()), "cuda")
+    gen = torch.Generator().manual_seed(0)
+    attrs = [torch.rand(P, 3, generator=gen).to(DEV).requires_grad_(True) for _ in range(NA)]
+    wts = [torch.randn(3, H, W, generator=gen).to(DEV) for _ in range(NA + 1)]
+    wd, wa = torch.randn(1, H, W, generator=gen).to(DEV), torch.randn(1, H, W, generator=gen).to(DEV)
+    lv = {k: tc[k].clone().requires_grad_(True) for k in ("means3D", "opacity", "colors", "cov3D")}
+    rs = dgr.GaussianRasterizationSettings(H, W, tc["tanfovx"], tc["tanfovy"], tc["bg"], 1.0, tc["view"], tc["proj"], 3,
+                                           tc["campos"], False, False)
+    rast = dgr.GaussianRasterizer(rs)
+    geo = dict(means3D=lv["means3D"], means2D=torch.zeros(P, 3, device=DEV, requires_grad=True), opacities=lv["opacity"], cov3D_precomp=lv["cov3D"])
+
+    def clear():
+        for t in list(lv.values()) + attrs:
+            t.grad = None
+
+    def multi():
+        color, radii, depth, alpha, extra = rast.forward_multi(extra_colors=attrs, colors_precomp=lv["colors"], **geo)
+        loss = (depth * wd).sum() + (alpha * wa).sum()
+        for im, w in zip([color] + extra, wts):
+            loss = loss + (im * w).sum()
+        loss.backward()
+
+    def separate():
+        color, radii, depth, alpha = rast(colors_precomp=lv["colors"], **geo)
+        loss = (depth * wd).sum() + (alpha * wa).sum() + (color * wts[0]).sum()
+        for a, w in zip(attrs, wts[1:]):
+            loss = loss + (rast(colors_precomp=a, **geo)[0] * w).sum()
+        loss.backward()
+
+    n = 10 if quick else 40
+    med_m, _ = timed(multi, n, warm=5, before=clear)
+    med_s, _ = timed(separate, n, warm=5, before=clear)
+    out = {"P": P, "W": W, "H": H, "attributes": NA + 1, "forward_multi_ms": round(med_m, 4),
+           "one_call_per_attribute_ms": round(med_s, 4), "multi_vs_separate": round(med_s / med_m, 2),
+           "what": "rasteriser forward + backward through torch autograd (linear loss on every image), L2 flushed"}
+    ref = ref_or_none()
+    if ref is not None:
+        e = torch.Tensor([])
+        rrs = [ref.RefRasterizer() for _ in range(NA + 1)]
+        zero1 = torch.zeros(1, H, W, device=DEV)
+        cols = [tc["colors"]] + [a.detach() for a in attrs]
+
+        def theirs():
+            for k, (rr, c) in enumerate(zip(rrs, cols)):
+                n_, color, depth, alpha, radii = rr.forward(tc["bg"], tc["means3D"], c, tc["opacity"], e, e, 1.0, tc["cov3D"],
+                                                            tc["view"], tc["proj"], tc["tanfovx"], tc["tanfovy"], H, W, e, 3,
+                                                            tc["campos"])
+                rr.backward(tc["bg"], tc["means3D"], radii, c, e, e, 1.0, tc["cov3D"], tc["view"], tc["proj"], tc["tanfovx"],
+                            tc["tanfovy"], wts[k], wd if k == 0 else zero1, wa if k == 0 else zero1, e, 3, tc["campos"], alpha)
+        try:
+            med_r, _ = timed(theirs, 5 if quick else 20, warm=3)
+            out.update(ref_ms=round(med_r, 4), speedup_vs_ref=round(med_r / med_m, 2),
+                       ref_what="seven forward+backward calls of the reference's unmodified CUDA rasteriser (no autograd overhead)")
+        except Exception as ex:
+            out["ref_error"] = repr(ex)[:200]
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--only", default="")
     a = ap.parse_args()
     parts = {"sort_sweep": sort_sweep, "forward_fps_zju_512": forward_fps_zju, "stress_1080p_forward": stress_1080p,
-             "dist_cuda2": knn}
+             "dist_cuda2": knn, "render7_zju_512": render7}
     out = {"device": torch.cuda.get_device_name(0), "ref_cuda_available": ref_or_none() is not None}
     for k, f in parts.items():
         if a.only and k not in a.only.split(","):
