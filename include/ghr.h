@@ -187,6 +187,36 @@ int ghr_backward_finish(const ghr_raster_params* prm, const int32_t* radii, cons
                         float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
                         void* stream);
 
+/* Fused form of the above, for 2, 4 or 6 extra attributes at a time: ONE blend kernel walks the tile lists once and
+ * accumulates the main colour, depth, alpha AND the attribute channels (forward), and one backward kernel produces the
+ * gradients of all of them.  Attribute colours travel packed, ghr_attribute_stride(n) floats per Gaussian:
+ *
+ *   ghr_attribute_stride       floats per Gaussian of a packed row for n attributes; 0 = n is not fused (use reblend)
+ *   ghr_attributes_fused       1 if the fused kernels serve a frame of this binning capacity, 0 = use reblend (frames
+ *                              with millions of (Gaussian, tile) pairs run the throughput kernel family, which has no
+ *                              fused variant)
+ *   ghr_pack_attributes        colors[k] ([P,3], k < n) -> packed [P][stride]
+ *   ghr_forward_render_multi   ghr_forward_render + out_images [3n][H][W] (attribute k = planes 3k..3k+2); every image
+ *                              equals a separate single-attribute pass bit for bit
+ *   ghr_backward_multi         ghr_backward with dL_dout_images [3n][H][W]; packed_grad [P][stride] receives the colour
+ *                              gradients of the attributes (zeroed here)
+ *   ghr_unpack_attribute_grads packed_grad -> dL_dcolors[k] ([P,3]; NULL entries are skipped)
+ * `colors` / `dL_dcolors` are HOST arrays of n device pointers. */
+int ghr_attribute_stride(int n_attr);
+int ghr_attributes_fused(int64_t capacity);
+int ghr_pack_attributes(int32_t P, int n_attr, const float* const* colors, float* packed, void* stream);
+int ghr_unpack_attribute_grads(int32_t P, int n_attr, const float* packed_grad, float* const* dL_dcolors, void* stream);
+int ghr_forward_render_multi(const ghr_raster_params* prm, void* geom, size_t geom_bytes, void* binning,
+                             size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
+                             float* out_depth, float* out_alpha, int n_attr, const float* packed, float* out_images,
+                             void* stream);
+int ghr_backward_multi(const ghr_raster_params* prm, const int32_t* radii, const void* geom, size_t geom_bytes,
+                       const void* binning, size_t binning_bytes, int64_t capacity, const void* img, size_t img_bytes,
+                       const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha, int n_attr,
+                       const float* packed, const float* dL_dout_images, float* packed_grad, float* accum,
+                       float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                       float* dL_dsh, float* dL_dscales, float* dL_drotations, void* stream);
+
 /* Rasterizer::markVisible / checkFrustum (rasterizer_impl.cu:54-66,141-153)
  * for _C.mark_visible (dgr/rasterize_points.cu:209-228).  present: uint8[P]. */
 int ghr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -80,6 +80,16 @@ SIGNATURES = {
                                      C.c_int64, C.c_void_p, C.c_size_t] + [C.c_void_p] * 6),
     "ghr_backward_finish": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_int64]
                             + [C.c_void_p] * 10),
+    "ghr_attribute_stride": (C.c_int, [C.c_int]),
+    "ghr_attributes_fused": (C.c_int, [C.c_int64]),
+    "ghr_pack_attributes": (C.c_int, [C.c_int32, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ghr_unpack_attribute_grads": (C.c_int, [C.c_int32, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ghr_forward_render_multi": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                           C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ghr_backward_multi": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                     C.c_int64, C.c_void_p, C.c_size_t] + [C.c_void_p] * 3 + [C.c_int]
+                           + [C.c_void_p] * 13),
     "ghr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ghr_sort_workspace_bytes": (C.c_size_t, [C.c_int64]),
     "ghr_sort_pairs_u64": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_size_t, C.c_void_p, C.c_void_p]),

@@ -118,13 +118,20 @@ int ghr_forward_preprocess(const ghr_raster_params* prm, int32_t* radii, void* g
     return stage_done(prm, launch_preprocess(*prm, radii, (char*)geom, L, num_rendered_host, s), s, "preprocess");
 }
 
-int ghr_forward_render(const ghr_raster_params* prm, void* geom, size_t geom_bytes, void* binning,
-                       size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
-                       float* out_depth, float* out_alpha, void* stream)
+static int multi_layout(const ghr_raster_params* prm, int64_t capacity, const void* geom, size_t geom_bytes,
+                        const void* binning, size_t binning_bytes, const void* img, size_t img_bytes, ghr_layout* L);
+
+static int forward_render_impl(const ghr_raster_params* prm, void* geom, size_t geom_bytes, void* binning,
+                               size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
+                               float* out_depth, float* out_alpha, int n_attr, const float* packed, float* out_images,
+                               void* stream)
 {
     int r = validate(prm);
     if (r != GHR_OK) return r;
     if (!out_color || !out_depth || !out_alpha) return GHR_ERR_BAD_ARG;
+    if (n_attr && (attr_stride(n_attr) == 0 || blend_throughput_regime(capacity) || !packed || !out_images ||
+                   misaligned(packed, 16)))
+        return GHR_ERR_BAD_ARG;
     cudaStream_t s = (cudaStream_t)stream;
     ghr_layout L;
     if (ghr_state_layout(prm->P, capacity, prm->W, prm->H, &L) != GHR_OK) return GHR_ERR_BAD_ARG;
@@ -138,6 +145,7 @@ int ghr_forward_render(const ghr_raster_params* prm, void* geom, size_t geom_byt
         r = check_cuda(cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * X, s), "P=0 memset");
         if (r == GHR_OK) r = check_cuda(cudaMemsetAsync(out_depth, 0, sizeof(float) * X, s), "P=0 memset");
         if (r == GHR_OK) r = check_cuda(cudaMemsetAsync(out_alpha, 0, sizeof(float) * X, s), "P=0 memset");
+        if (r == GHR_OK && n_attr) r = check_cuda(cudaMemsetAsync(out_images, 0, sizeof(float) * 3 * n_attr * X, s), "P=0 memset");
         return r;
     }
     // one memset clears the sort header (tickets, histograms) and every pass's look-back words
@@ -157,7 +165,95 @@ int ghr_forward_render(const ghr_raster_params* prm, void* geom, size_t geom_byt
     }
     r = stage_done(prm, launch_tile_ranges(*prm, g, b, im, L, capacity, s), s, "tile_ranges");
     if (r != GHR_OK) return r;
+    if (n_attr)
+        return stage_done(prm,
+                          launch_blend_forward_multi(*prm, g, b, im, L, out_color, out_depth, out_alpha, n_attr, packed,
+                                                     out_images, s),
+                          s, "blend_forward_multi");
     return stage_done(prm, launch_blend_forward(*prm, g, b, im, L, out_color, out_depth, out_alpha, s), s, "blend_forward");
+}
+
+int ghr_forward_render(const ghr_raster_params* prm, void* geom, size_t geom_bytes, void* binning,
+                       size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
+                       float* out_depth, float* out_alpha, void* stream)
+{
+    return forward_render_impl(prm, geom, geom_bytes, binning, binning_bytes, capacity, img, img_bytes, out_color,
+                               out_depth, out_alpha, 0, nullptr, nullptr, stream);
+}
+
+int ghr_forward_render_multi(const ghr_raster_params* prm, void* geom, size_t geom_bytes, void* binning,
+                             size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
+                             float* out_depth, float* out_alpha, int n_attr, const float* packed, float* out_images,
+                             void* stream)
+{
+    if (n_attr <= 0) return GHR_ERR_BAD_ARG;
+    return forward_render_impl(prm, geom, geom_bytes, binning, binning_bytes, capacity, img, img_bytes, out_color,
+                               out_depth, out_alpha, n_attr, packed, out_images, stream);
+}
+
+int ghr_attribute_stride(int n_attr) { return attr_stride(n_attr); }
+int ghr_attributes_fused(int64_t capacity) { return blend_throughput_regime(capacity) ? 0 : 1; }
+
+static int attr_ptrs(int n_attr, const float* const* src, float* const* dst, AttrPtrs* out)
+{
+    if (attr_stride(n_attr) == 0) return GHR_ERR_BAD_ARG;
+    for (int k = 0; k < 6; k++) {
+        out->src[k] = (src && k < n_attr) ? src[k] : nullptr;
+        out->dst[k] = (dst && k < n_attr) ? dst[k] : nullptr;
+        if (src && k < n_attr && !src[k]) return GHR_ERR_BAD_ARG;
+    }
+    return GHR_OK;
+}
+
+int ghr_pack_attributes(int32_t P, int n_attr, const float* const* colors, float* packed, void* stream)
+{
+    AttrPtrs ptrs;
+    if (P < 0 || !colors || !packed || misaligned(packed, 16) || attr_ptrs(n_attr, colors, nullptr, &ptrs) != GHR_OK)
+        return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_pack_attributes(P, n_attr, ptrs, packed, (cudaStream_t)stream), "pack_attributes");
+}
+
+int ghr_unpack_attribute_grads(int32_t P, int n_attr, const float* packed_grad, float* const* dL_dcolors, void* stream)
+{
+    AttrPtrs ptrs;
+    if (P < 0 || !dL_dcolors || !packed_grad || attr_ptrs(n_attr, nullptr, dL_dcolors, &ptrs) != GHR_OK)
+        return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_unpack_attributes(P, n_attr, packed_grad, ptrs, (cudaStream_t)stream), "unpack_attributes");
+}
+
+int ghr_backward_multi(const ghr_raster_params* prm, const int32_t* radii, const void* geom, size_t geom_bytes,
+                       const void* binning, size_t binning_bytes, int64_t capacity, const void* img, size_t img_bytes,
+                       const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha, int n_attr,
+                       const float* packed, const float* dL_dout_images, float* packed_grad, float* accum,
+                       float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                       float* dL_dsh, float* dL_dscales, float* dL_drotations, void* stream)
+{
+    int r = validate(prm);
+    if (r != GHR_OK) return r;
+    if (prm->P == 0) return GHR_OK;
+    if (!radii || !dL_dout_color || !dL_dout_depth || !dL_dout_alpha || !accum || !dL_dmeans2D || !dL_dcolors ||
+        !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || misaligned(accum, 16) || misaligned(dL_drotations, 16))
+        return GHR_ERR_BAD_ARG;
+    if (prm->shs && !dL_dsh) return GHR_ERR_BAD_ARG;
+    const int stride = attr_stride(n_attr);
+    if (stride == 0 || blend_throughput_regime(capacity) || !packed || !dL_dout_images || !packed_grad ||
+        misaligned(packed, 16))
+        return GHR_ERR_BAD_ARG;
+    ghr_layout L;
+    if ((r = multi_layout(prm, capacity, geom, geom_bytes, binning, binning_bytes, img, img_bytes, &L)) != GHR_OK) return r;
+    cudaStream_t s = (cudaStream_t)stream;
+    r = check_cuda(cudaMemsetAsync(packed_grad, 0, sizeof(float) * stride * (size_t)prm->P, s), "packed_grad memset");
+    if (r != GHR_OK) return r;
+    r = stage_done(prm,
+                   launch_blend_backward_multi(*prm, (const char*)geom, (const char*)binning, (const char*)img, L,
+                                               dL_dout_color, dL_dout_depth, dL_dout_alpha, accum, n_attr, packed,
+                                               dL_dout_images, packed_grad, s),
+                   s, "blend_backward_multi");
+    if (r != GHR_OK) return r;
+    return stage_done(prm,
+                      launch_preprocess_backward(*prm, radii, (const char*)geom, L, accum, dL_dmeans2D, dL_dcolors,
+                                                 dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, s),
+                      s, "preprocess_backward");
 }
 
 int ghr_backward(const ghr_raster_params* prm, const int32_t* radii, const void* geom, size_t geom_bytes,

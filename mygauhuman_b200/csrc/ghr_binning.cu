@@ -151,6 +151,52 @@ __global__ void __launch_bounds__(256) recolor_kernel(int P, const float* __rest
     rec[3 * (size_t)idx + 2] = r2;  // .w (cull extent) kept
 }
 
+// packed[idx][attr_offset(n,k) + c] <-> attribute k, colour c (AttrLayout, ghr_internal.h); padding floats are zeroed
+__global__ void __launch_bounds__(256) pack_attributes_kernel(int P, int n, int stride, AttrPtrs ptrs, float* __restrict__ packed)
+{
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= P) return;
+    float* row = packed + (size_t)idx * stride;
+    const int half = stride / 2, used = 3 * n / 2;
+    for (int c = used; c < half; c++) { row[c] = 0.f; row[half + c] = 0.f; }
+    for (int k = 0; k < n; k++) {
+        const float* src = ptrs.src[k] + 3 * (size_t)idx;
+        float* dst = row + (k / (n / 2)) * half + 3 * (k % (n / 2));
+        dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+    }
+}
+
+__global__ void __launch_bounds__(256) unpack_attributes_kernel(int P, int n, int stride, const float* __restrict__ packed,
+                                                                AttrPtrs ptrs)
+{
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= P) return;
+    const float* row = packed + (size_t)idx * stride;
+    const int half = stride / 2;
+    for (int k = 0; k < n; k++) {
+        if (!ptrs.dst[k]) continue;
+        const float* src = row + (k / (n / 2)) * half + 3 * (k % (n / 2));
+        float* dst = ptrs.dst[k] + 3 * (size_t)idx;
+        dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+    }
+}
+
+cudaError_t launch_pack_attributes(int P, int n, const AttrPtrs& ptrs, float* packed, cudaStream_t s)
+{
+    if (P <= 0) return cudaSuccess;
+    count_launch();
+    pack_attributes_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, n, attr_stride(n), ptrs, packed);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_unpack_attributes(int P, int n, const float* packed, const AttrPtrs& ptrs, cudaStream_t s)
+{
+    if (P <= 0) return cudaSuccess;
+    count_launch();
+    unpack_attributes_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, n, attr_stride(n), packed, ptrs);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_recolor(int P, const float* colors, char* geom, const ghr_layout& L, cudaStream_t s)
 {
     if (P <= 0) return cudaSuccess;

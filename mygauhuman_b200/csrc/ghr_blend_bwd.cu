@@ -76,6 +76,55 @@ __device__ __forceinline__ int half_slot(uint32_t lane)
     return local < 5 ? local : 99;
 }
 
+// Split butterfly for N values over the 16 lanes of a slot: at each xor step (8, 4, 2, 1) a lane keeps one half of its
+// values and sends the other, so N values cost about N shuffles instead of 4N.  Afterwards a lane holds the totals of
+// (at most) two of the values: out[0], out[1] are the totals, reduce_index<N>(lane, t) says of which value (-1: padding).
+template <int N>
+__device__ __forceinline__ void half_reduce_n(const float (&v)[N], uint32_t lane, float (&out)[2])
+{
+    constexpr int N1 = (N + 1) / 2, N2 = (N1 + 1) / 2, N3 = (N2 + 1) / 2, N4 = (N3 + 1) / 2;
+    static_assert(N4 <= 2, "at most two totals per lane");
+    const bool b3 = lane & 8, b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
+    float a[N1 + 1], c[N2 + 1], d[N3 + 1], e[N4 + 1];
+#pragma unroll
+    for (int k = 0; k < N1; k++) {
+        const float lo = v[k], hi = (N1 + k < N) ? v[(N1 + k < N) ? N1 + k : 0] : 0.0f;
+        a[k] = (b3 ? hi : lo) + __shfl_xor_sync(0xffffffffu, b3 ? lo : hi, 8);
+    }
+#pragma unroll
+    for (int k = 0; k < N2; k++) {
+        const float lo = a[k], hi = (N2 + k < N1) ? a[(N2 + k < N1) ? N2 + k : 0] : 0.0f;
+        c[k] = (b2 ? hi : lo) + __shfl_xor_sync(0xffffffffu, b2 ? lo : hi, 4);
+    }
+#pragma unroll
+    for (int k = 0; k < N3; k++) {
+        const float lo = c[k], hi = (N3 + k < N2) ? c[(N3 + k < N2) ? N3 + k : 0] : 0.0f;
+        d[k] = (b1 ? hi : lo) + __shfl_xor_sync(0xffffffffu, b1 ? lo : hi, 2);
+    }
+#pragma unroll
+    for (int k = 0; k < N4; k++) {
+        const float lo = d[k], hi = (N4 + k < N3) ? d[(N4 + k < N3) ? N4 + k : 0] : 0.0f;
+        e[k] = (b0 ? hi : lo) + __shfl_xor_sync(0xffffffffu, b0 ? lo : hi, 1);
+    }
+    out[0] = e[0];
+    out[1] = N4 > 1 ? e[N4 > 1 ? 1 : 0] : 0.0f;
+}
+
+template <int N>
+__device__ __forceinline__ int reduce_index(uint32_t lane, int t)
+{
+    constexpr int N1 = (N + 1) / 2, N2 = (N1 + 1) / 2, N3 = (N2 + 1) / 2, N4 = (N3 + 1) / 2;
+    if (t >= N4) return -1;
+    const int i4 = ((lane & 1) ? N4 : 0) + t;
+    if (i4 >= N3) return -1;
+    const int i3 = ((lane & 2) ? N3 : 0) + i4;
+    if (i3 >= N2) return -1;
+    const int i2 = ((lane & 4) ? N2 : 0) + i3;
+    if (i2 >= N1) return -1;
+    const int i1 = ((lane & 8) ? N1 : 0) + i2;
+    return i1 < N ? i1 : -1;
+}
+
 #ifdef GHR_TRACE  // tuning builds only (tools/build_variant.sh): per-item begin/end timestamps and phase cycle counts
 __device__ unsigned long long g_bwd_trace[1 << 16][8];
 __device__ __forceinline__ unsigned long long gtime_b()
@@ -91,26 +140,36 @@ __device__ __forceinline__ unsigned long long gtime_b()
 constexpr int kBwdWarps = 4;  // independent warps per CTA
 // Staging as in ghr_blend_fwd.cu: 256-entry rounds, 2-deep ring, 8 warps per SM; frames with millions of pairs take
 // ghr_blend_bwd_wide.cu instead (launch_blend_backward).
-template <int BATCH, int NSTAGE>
+// NX > 0 (multi-attribute rendering, include/ghr.h): NX more [P,3] attributes were blended by the forward; their packed
+// colour rows (AttrLayout<NX>) are staged next to the records.  The two lanes of a pixel split the attribute channels
+// (slot 0 the first half of a row, slot 1 the second): each runs the accumulated-colour recurrence of its channels over
+// BOTH Gaussians of a pair, the partial sums of (c - accum) * dL_dpixel are exchanged with one shuffle and join the
+// main channels' dL_dalpha, and the 2 * CHS colour gradients of the pair go through half_reduce_n into xaccum (same row
+// layout as the colours).
+template <int BATCH, int NSTAGE, int NX>
 __host__ __device__ constexpr size_t blend_bwd_warp_smem()
 {
-    return ((sizeof(float4) * 3 + sizeof(uint32_t)) * NSTAGE * BATCH + sizeof(uint32_t) * NSTAGE * (BATCH / 32) + 15) / 16 * 16;
+    return ((sizeof(float4) * 3 + sizeof(uint32_t) + sizeof(float) * attr_row_floats<NX>()) * NSTAGE * BATCH +
+            sizeof(uint32_t) * NSTAGE * (BATCH / 32) + 15) / 16 * 16;
 }
 
 // Persistent kernel: warps pull (tile, 4x4 block) work items from a queue ordered by decreasing tile-list
 // length (tile_order_kernel) and work independently (no block-level barrier); see ghr_blend_fwd.cu.
-template <int BATCH, int NSTAGE>
+template <int BATCH, int NSTAGE, int NX>
 __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
     int W, int H, int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
     const SortHeader* __restrict__ sh, const uint2* __restrict__ ent_a, const uint2* __restrict__ ent_b,
     const float4* __restrict__ rec, ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
     const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
-    const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas, float* __restrict__ accum)
+    const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas, float* __restrict__ accum,
+    const float* __restrict__ xcol, const float* __restrict__ xdpix, float* __restrict__ xaccum)
 {
     constexpr int PER_LANE = BATCH / 32;
-    // per-warp staging ring in dynamic shared memory: records, ids, survivor bits
+    using AL = AttrLayout<(NX ? NX : 2)>;
+    constexpr int XS = attr_row_floats<NX>(), XH = AL::XH, CHS = AL::CHS;
+    // per-warp staging ring in dynamic shared memory: records, ids, survivor bits(, attribute rows)
     extern __shared__ __align__(16) unsigned char bwd_smem[];
-    constexpr size_t kWarpBytes = blend_bwd_warp_smem<BATCH, NSTAGE>();
+    constexpr size_t kWarpBytes = blend_bwd_warp_smem<BATCH, NSTAGE, NX>();
     static_assert(kWarpBytes % 16 == 0, "per-warp staging area must keep float4 alignment");
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t slot = lane >> 4, pl = lane & 15u;  // which of the pixel's two lanes; pixel inside the 4x4 block
@@ -119,6 +178,11 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
     uint32_t(*s_id)[BATCH] = reinterpret_cast<uint32_t(*)[BATCH]>(wbase + sizeof(float4) * NSTAGE * BATCH * 3);
     uint32_t(*s_keep)[PER_LANE] =
         reinterpret_cast<uint32_t(*)[PER_LANE]>(wbase + sizeof(float4) * NSTAGE * BATCH * 3 + sizeof(uint32_t) * NSTAGE * BATCH);
+    float* s_x = reinterpret_cast<float*>(wbase + (sizeof(float4) * 3 + sizeof(uint32_t)) * NSTAGE * BATCH +
+                                          (sizeof(uint32_t) * NSTAGE * PER_LANE + 15) / 16 * 16);  // [NSTAGE][BATCH][XS]
+    int xidx[2];  // which of the pair's 2*CHS attribute colour gradients this lane holds after half_reduce_n
+    xidx[0] = reduce_index<2 * CHS>(lane, 0);
+    xidx[1] = reduce_index<2 * CHS>(lane, 1);
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
     // {Gaussian id, 4x4-block mask} per list entry (tile_ranges_kernel; lives in the key buffer the sort left unused)
@@ -165,7 +229,19 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
             dpix0 = dL_dpixels[pix]; dpix1 = dL_dpixels[HW + pix]; dpix2 = dL_dpixels[2 * HW + pix];
             dL_ddepth = dL_ddepths[pix]; dL_dalpha = dL_dalphas[pix];
         }
-        const float bg_dot = bgc0 * dpix0 + bgc1 * dpix1 + bgc2 * dpix2;
+        float bg_dot = bgc0 * dpix0 + bgc1 * dpix1 + bgc2 * dpix2;
+        float dpx[CHS], accx[CHS], lcx[CHS];  // NX > 0: this lane's half of the attribute channels
+        if constexpr (NX > 0) {
+            float part = 0.f;
+#pragma unroll
+            for (int c = 0; c < CHS; c++) {
+                const int ch = (int)slot * CHS + c;
+                dpx[c] = inside ? xdpix[(size_t)ch * HW + pix] : 0.f;
+                accx[c] = 0.f; lcx[c] = 0.f;
+                part = fmaf((ch % 3 == 0) ? bgc0 : (ch % 3 == 1) ? bgc1 : bgc2, dpx[c], part);
+            }
+            bg_dot += part + __shfl_xor_sync(0xffffffffu, part, 16);
+        }
         // per-pixel recurrence state, carried identically by both lanes of the pixel
         float T = T_final;
         float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
@@ -200,6 +276,12 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
                     cp_async16b(dst, src);
                     cp_async16b(dst + 1, src + 1);
                     cp_async16b(dst + 2, src + 2);
+                    if constexpr (NX > 0) {
+                        const float* xsrc = xcol + (size_t)nid[u] * XS;
+                        float* xdst = s_x + ((size_t)buf * BATCH + sl) * XS;
+#pragma unroll
+                        for (int c = 0; c < XS; c += 4) cp_async16b(xdst + c, xsrc + c);
+                    }
                 }
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
@@ -294,6 +376,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
                     for (int q = 0; q < 4; q++) {
                         // state after the pair's first Gaussian (S1: what slot 0 differentiates) and after its second (S2)
                         float Ts[2], a0s[2], a1s[2], a2s[2], ads[2], aas[2];
+                        float xpart[2];  // this lane's channels' share of sum_ch (c - accum) * dL_dpixel, per Gaussian
 #pragma unroll
                         for (int h = 0; h < 2; h++) {
                             const int k = 2 * q + h;
@@ -308,6 +391,20 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
                             acc2 = on ? fmaf(last_alpha, lc2, om * acc2) : acc2;
                             accum_depth_rec = on ? fmaf(last_alpha, last_depth, om * accum_depth_rec) : accum_depth_rec;
                             accum_alpha_rec = on ? fmaf(om, accum_alpha_rec, last_alpha) : accum_alpha_rec;
+                            if constexpr (NX > 0) {
+                                const float2* cx =
+                                    reinterpret_cast<const float2*>(s_x + ((size_t)buf * BATCH + j[k]) * XS + slot * XH);
+                                float part = 0.f;
+#pragma unroll
+                                for (int c = 0; c < CHS; c++) {
+                                    const float2 cc = cx[c >> 1];
+                                    const float col = (c & 1) ? cc.y : cc.x;
+                                    accx[c] = on ? fmaf(last_alpha, lcx[c], om * accx[c]) : accx[c];
+                                    lcx[c] = on ? col : lcx[c];
+                                    part = fmaf(col - accx[c], dpx[c], part);
+                                }
+                                xpart[h] = part;
+                            }
                             lc0 = on ? c.x : lc0; lc1 = on ? c.y : lc1; lc2 = on ? c.z : lc2;
                             last_depth = on ? dep : last_depth;
                             last_alpha = on ? a[k] : last_alpha;
@@ -318,6 +415,27 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
                         trace_live += ((live & 0xFFFFu) != 0) + ((live >> 16) != 0);
 #endif
                         if (live == 0) continue;
+                        float xdot = 0.f;
+                        if constexpr (NX > 0) {
+                            // colour gradients of both Gaussians of the pair, this lane's channels
+                            float xv[2 * CHS];
+                            const float w0 = a[2 * q] * Ts[0], w1 = a[2 * q + 1] * Ts[1];
+#pragma unroll
+                            for (int c = 0; c < CHS; c++) { xv[c] = w0 * dpx[c]; xv[CHS + c] = w1 * dpx[c]; }
+                            float tot[2];
+                            half_reduce_n<2 * CHS>(xv, lane, tot);
+#pragma unroll
+                            for (int t = 0; t < 2; t++) {
+                                if (xidx[t] >= 0) {
+                                    const int h = xidx[t] >= CHS, c = xidx[t] - h * CHS;
+                                    if ((live & (h ? 0xFFFF0000u : 0x0000FFFFu)) != 0)
+                                        atomicAdd(xaccum + (size_t)s_id[buf][h ? j[2 * q + 1] : j[2 * q]] * XS + slot * XH + c, tot[t]);
+                                }
+                            }
+                            // the other lane of the pixel holds the other half of the channels of MY Gaussian
+                            const float theirs = __shfl_xor_sync(0xffffffffu, slot ? xpart[0] : xpart[1], 16);
+                            xdot = (slot ? xpart[1] : xpart[0]) + theirs;
+                        }
                         // this lane's own Gaussian of the pair: partial gradients of its pixel (zero where not valid)
                         const float Tm = slot ? Ts[1] : Ts[0];
                         const float m0 = slot ? a0s[1] : a0s[0], m1 = slot ? a1s[1] : a1s[0], m2 = slot ? a2s[1] : a2s[0];
@@ -332,6 +450,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
                             dL_dopa = fmaf(c.z - m2, dpix2, dL_dopa);
                             dL_dopa = fmaf(depth_own[q] - md, dL_ddepth, dL_dopa);
                             dL_dopa = fmaf(1.0f - ma, dL_dalpha, dL_dopa);
+                            if constexpr (NX > 0) dL_dopa += xdot;
                             dL_dopa *= Tm;
                             dL_dopa = fmaf(-T_final * __fdividef(1.0f, 1.0f - aq), bg_dot, dL_dopa);
                             dL_dopa = aq > 0.0f ? dL_dopa : 0.0f;
@@ -383,18 +502,19 @@ extern "C" int ghr_debug_bwd_trace(void* out, size_t bytes)
 namespace ghr {
 #endif
 
-template <int BATCH, int NSTAGE>
+template <int BATCH, int NSTAGE, int NX>
 static cudaError_t launch_bwd_config(int ctas_per_sm, const ghr_raster_params& p, const char* geom, const char* binning,
                                      const char* img, const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
-                                     const float* dL_dalpha, float* accum, cudaStream_t s)
+                                     const float* dL_dalpha, float* accum, const float* xcol, const float* xdpix,
+                                     float* xaccum, cudaStream_t s)
 {
     const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
     const int64_t items = (int64_t)tiles * 16;
     int64_t ctas = (items + kBwdWarps - 1) / kBwdWarps;
     if (ctas > 148 * ctas_per_sm) ctas = 148 * ctas_per_sm;
-    auto kernel = blend_backward_kernel<BATCH, NSTAGE>;
-    const size_t smem = blend_bwd_warp_smem<BATCH, NSTAGE>() * kBwdWarps;
+    auto kernel = blend_backward_kernel<BATCH, NSTAGE, NX>;
+    const size_t smem = blend_bwd_warp_smem<BATCH, NSTAGE, NX>() * kBwdWarps;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kernel<<<(unsigned)ctas, kBwdWarps * 32, smem, s>>>(
@@ -403,7 +523,7 @@ static cudaError_t launch_bwd_config(int ctas_per_sm, const ghr_raster_params& p
         reinterpret_cast<const uint2*>(binning + L.b_keys_a), reinterpret_cast<const uint2*>(binning + L.b_keys_b),
         reinterpret_cast<const float4*>(geom + L.g_rec), hdr, L.capacity, p.background,
         reinterpret_cast<const float*>(img + L.i_final_T), reinterpret_cast<const uint32_t*>(img + L.i_n_contrib), dL_dpix,
-        dL_ddepth, dL_dalpha, accum);
+        dL_ddepth, dL_dalpha, accum, xcol, xdpix, xaccum);
     return cudaGetLastError();
 }
 
@@ -419,7 +539,31 @@ cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, 
     // the queue head is scratch state inside the (otherwise read-only) geometry buffer
     cudaError_t e = cudaMemsetAsync(&hdr->blend_bwd_ticket, 0, sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
-    return launch_bwd_config<256, 2>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, s);
+    return launch_bwd_config<256, 2, 0>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, nullptr, nullptr,
+                                        nullptr, s);
+}
+
+// Main image + n_attr (2, 4 or 6) packed attributes in one walk; latency regime only (ghr_api.cu checks).
+cudaError_t launch_blend_backward_multi(const ghr_raster_params& p, const char* geom, const char* binning, const char* img,
+                                        const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
+                                        const float* dL_dalpha, float* accum, int n_attr, const float* xcol,
+                                        const float* xdpix, float* xaccum, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_BLEND_BWD, s);
+    count_launch();
+    ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
+    cudaError_t e = cudaMemsetAsync(&hdr->blend_bwd_ticket, 0, sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    switch (n_attr) {
+    case 2: return launch_bwd_config<128, 2, 2>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, xcol, xdpix, xaccum, s);
+    case 4: return launch_bwd_config<128, 2, 4>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, xcol, xdpix, xaccum, s);
+#ifdef GHR_MB_BATCH  // tuning builds only
+    case 6: return launch_bwd_config<GHR_MB_BATCH, GHR_MB_NSTAGE, 6>(GHR_MB_CTAS, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, xcol, xdpix, xaccum, s);
+#else
+    case 6: return launch_bwd_config<96, 2, 6>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, xcol, xdpix, xaccum, s);
+#endif
+    default: return cudaErrorInvalidValue;
+    }
 }
 
 }  // namespace ghr

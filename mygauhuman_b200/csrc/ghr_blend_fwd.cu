@@ -58,29 +58,39 @@ __device__ __forceinline__ void cp_async_wait()
 #define GHR_FWD_KSTEP 8
 #endif
 constexpr int KSTEP = GHR_FWD_KSTEP;  // survivors per step (half of them evaluated by each slot)
-template <int BATCH, int NSTAGE>
+// NX > 0: NX more [P,3] attributes are blended in the same walk (multi-attribute rendering, include/ghr.h).  Their
+// colours come packed as AttrLayout<NX>::XS floats per Gaussian (ghr_pack_attributes): the first half of a row holds the
+// channels accumulated by slot 0, the second half those of slot 1, each channel with the arithmetic of the main colour
+// channels (fmul alpha*c, fma with T, list order), so every attribute image equals a separate pass bit for bit.
+template <int BATCH, int NSTAGE, int NX>
 __host__ __device__ constexpr size_t blend_fwd_warp_smem()
 {
-    return (sizeof(float4) * 3 * BATCH * NSTAGE + sizeof(uint32_t) * (BATCH / 32) * NSTAGE + 15) / 16 * 16;
+    return ((sizeof(float4) * 3 + sizeof(float) * attr_row_floats<NX>()) * BATCH * NSTAGE +
+            sizeof(uint32_t) * (BATCH / 32) * NSTAGE + 15) / 16 * 16;
 }
 
-template <int BATCH, int NSTAGE, int WARPS>
+template <int BATCH, int NSTAGE, int WARPS, int NX>
 __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
     int W, int H, int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
     const SortHeader* __restrict__ sh, const uint2* __restrict__ ent_a, const uint2* __restrict__ ent_b,
     const float4* __restrict__ rec, ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
     float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha,
-    float* __restrict__ final_T, uint32_t* __restrict__ n_contrib)
+    float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, const float* __restrict__ xcol,
+    float* __restrict__ out_x)
 {
     constexpr int PER_LANE = BATCH / 32;
-    // per-warp staging ring in dynamic shared memory: records, then one survivor bit per staged entry
+    using AL = AttrLayout<(NX ? NX : 2)>;
+    constexpr int XS = attr_row_floats<NX>(), XH = AL::XH, CHS = AL::CHS;
+    // per-warp staging ring in dynamic shared memory: records, (attribute rows,) then one survivor bit per staged entry
     extern __shared__ __align__(16) unsigned char fwd_smem[];
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t slot = lane >> 4, pl = lane & 15u;  // which of the pixel's two lanes; pixel inside the 4x4 block
-    unsigned char* wbase = fwd_smem + warp * blend_fwd_warp_smem<BATCH, NSTAGE>();
+    unsigned char* wbase = fwd_smem + warp * blend_fwd_warp_smem<BATCH, NSTAGE, NX>();
     float4(*s_rec)[BATCH * 3] = reinterpret_cast<float4(*)[BATCH * 3]>(wbase);
-    uint32_t(*s_keep)[PER_LANE] = reinterpret_cast<uint32_t(*)[PER_LANE]>(wbase + sizeof(float4) * 3 * BATCH * NSTAGE);
+    float* s_x = reinterpret_cast<float*>(wbase + sizeof(float4) * 3 * BATCH * NSTAGE);  // [NSTAGE][BATCH][XS]
+    uint32_t(*s_keep)[PER_LANE] = reinterpret_cast<uint32_t(*)[PER_LANE]>(
+        wbase + (sizeof(float4) * 3 + sizeof(float) * XS) * BATCH * NSTAGE);
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
     // {Gaussian id, 4x4-block mask} per list entry, written by tile_ranges_kernel into the key buffer the sort left unused
@@ -136,6 +146,12 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
                     cp_async16(dst, src);
                     cp_async16(dst + 1, src + 1);
                     cp_async16(dst + 2, src + 2);
+                    if constexpr (NX > 0) {
+                        const float* xsrc = xcol + (size_t)nid[u] * XS;
+                        float* xdst = s_x + ((size_t)buf * BATCH + lane + u * 32) * XS;
+#pragma unroll
+                        for (int c = 0; c < XS; c += 4) cp_async16(xdst + c, xsrc + c);
+                    }
                 }
                 const uint32_t bits = __ballot_sync(0xffffffffu, keep);
                 if (lane == 0) s_keep[buf][u] = bits;
@@ -148,6 +164,9 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
         bool done = !inside;
         float T = 1.0f, A0 = 0.f, A1 = 0.f, A2 = 0.f;
         uint32_t last_contributor = 0;
+        float X[CHS];  // NX > 0: this lane's half of the attribute channels
+#pragma unroll
+        for (int c = 0; c < CHS; c++) X[c] = 0.f;
 
         if (rounds > 0) {
             // prologue: all list entries of the first NSTAGE-1 rounds are requested before the first record copy
@@ -245,6 +264,15 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
                     A0 = acc ? __fmaf_rn(T, x0[u], A0) : A0;
                     A1 = acc ? __fmaf_rn(T, x1[u], A1) : A1;
                     A2 = acc ? __fmaf_rn(T, alpha[u], A2) : A2;
+                    if constexpr (NX > 0) {
+                        const float2* cx = reinterpret_cast<const float2*>(s_x + ((size_t)buf * BATCH + j[u]) * XS + slot * XH);
+#pragma unroll
+                        for (int c = 0; c < CHS; c += 2) {
+                            const float2 cc = cx[c >> 1];
+                            X[c] = acc ? __fmaf_rn(T, __fmul_rn(alpha[u], cc.x), X[c]) : X[c];
+                            if (c + 1 < CHS) X[c + 1] = acc ? __fmaf_rn(T, __fmul_rn(alpha[u], cc.y), X[c + 1]) : X[c + 1];
+                        }
+                    }
                     last_contributor = acc ? base + (uint32_t)j[u] + 1u : last_contributor;
                     T = acc ? test_T : T;
                 }
@@ -267,6 +295,14 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
             } else {
                 out_color[2 * HW + pix] = __fmaf_rn(T, bg2, A0);
                 out_depth[pix] = A1;
+            }
+            if constexpr (NX > 0) {
+#pragma unroll
+                for (int c = 0; c < CHS; c++) {
+                    const int ch = (int)slot * CHS + c;  // channel ch = colour (ch % 3) of attribute ch / 3
+                    const float b = (ch % 3 == 0) ? bg0 : (ch % 3 == 1) ? bg1 : bg2;
+                    out_x[(size_t)ch * HW + pix] = __fmaf_rn(T, b, X[c]);
+                }
             }
         }
 #ifdef GHR_TRACE
@@ -292,18 +328,18 @@ extern "C" int ghr_debug_fwd_trace(void* out, size_t bytes)
 namespace ghr {
 #endif
 
-template <int BATCH, int NSTAGE, int WARPS>
+template <int BATCH, int NSTAGE, int WARPS, int NX>
 static cudaError_t launch_fwd_config(int ctas_per_sm, const ghr_raster_params& p, const char* geom, const char* binning,
                                      char* img, const ghr_layout& L, float* out_color, float* out_depth, float* out_alpha,
-                                     cudaStream_t s)
+                                     const float* xcol, float* out_x, cudaStream_t s)
 {
     const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
     const int64_t items = (int64_t)tiles * 16;
     int64_t ctas = (items + WARPS - 1) / WARPS;
     if (ctas > 148 * ctas_per_sm) ctas = 148 * ctas_per_sm;
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
-    auto kernel = blend_forward_kernel<BATCH, NSTAGE, WARPS>;
-    const size_t smem = blend_fwd_warp_smem<BATCH, NSTAGE>() * WARPS;
+    auto kernel = blend_forward_kernel<BATCH, NSTAGE, WARPS, NX>;
+    const size_t smem = blend_fwd_warp_smem<BATCH, NSTAGE, NX>() * WARPS;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kernel<<<(unsigned)ctas, WARPS * 32, smem, s>>>(
@@ -311,7 +347,8 @@ static cudaError_t launch_fwd_config(int ctas_per_sm, const ghr_raster_params& p
         reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),
         reinterpret_cast<const uint2*>(binning + L.b_keys_a), reinterpret_cast<const uint2*>(binning + L.b_keys_b),
         reinterpret_cast<const float4*>(geom + L.g_rec), hdr, L.capacity, p.background, out_color,
-        out_depth, out_alpha, reinterpret_cast<float*>(img + L.i_final_T), reinterpret_cast<uint32_t*>(img + L.i_n_contrib));
+        out_depth, out_alpha, reinterpret_cast<float*>(img + L.i_final_T), reinterpret_cast<uint32_t*>(img + L.i_n_contrib),
+        xcol, out_x);
     return cudaGetLastError();
 }
 
@@ -326,7 +363,29 @@ cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, c
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
     cudaError_t e = cudaMemsetAsync(&hdr->blend_fwd_ticket, 0, sizeof(uint32_t), s);  // render may run twice per preprocess
     if (e != cudaSuccess) return e;
-    return launch_fwd_config<256, 2, 1>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, s);
+    return launch_fwd_config<256, 2, 1, 0>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, nullptr, nullptr, s);
+}
+
+// Main image + n_attr (2, 4 or 6) packed attributes in one walk; latency regime only (ghr_api.cu checks).
+cudaError_t launch_blend_forward_multi(const ghr_raster_params& p, const char* geom, const char* binning, char* img,
+                                       const ghr_layout& L, float* out_color, float* out_depth, float* out_alpha,
+                                       int n_attr, const float* xcol, float* out_x, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_BLEND_FWD, s);
+    count_launch();
+    ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
+    cudaError_t e = cudaMemsetAsync(&hdr->blend_fwd_ticket, 0, sizeof(uint32_t), s);
+    if (e != cudaSuccess) return e;
+    switch (n_attr) {
+    case 2: return launch_fwd_config<128, 2, 1, 2>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, xcol, out_x, s);
+    case 4: return launch_fwd_config<128, 2, 1, 4>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, xcol, out_x, s);
+#ifdef GHR_MF_BATCH  // tuning builds only
+    case 6: return launch_fwd_config<GHR_MF_BATCH, GHR_MF_NSTAGE, 1, 6>(GHR_MF_CTAS, p, geom, binning, img, L, out_color, out_depth, out_alpha, xcol, out_x, s);
+#else
+    case 6: return launch_fwd_config<96, 2, 1, 6>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, xcol, out_x, s);
+#endif
+    default: return cudaErrorInvalidValue;
+    }
 }
 
 }  // namespace ghr

@@ -109,6 +109,33 @@ cudaError_t launch_preprocess_backward(const ghr_raster_params& p, const int32_t
                                        const ghr_layout& L, const float* accum, float* dL_dmean2D, float* dL_dcolor,
                                        float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                                        float* dL_dscale, float* dL_drot, cudaStream_t s);
+// Packed attribute rows (multi-attribute rendering): N attributes = 3N channels, split in two halves of CHS channels (one
+// per pixel slot of the blend kernels), each half padded to XH floats; row stride XS = 2*XH floats, a 16-byte multiple.
+// Attribute k lives in half k / (N/2) at floats 3 * (k % (N/2)) .. +2 of that half.
+template <int N>
+struct AttrLayout {
+    static_assert(N >= 2 && N % 2 == 0, "attributes are fused in pairs");
+    static constexpr int CH = 3 * N, CHS = CH / 2, XH = (CHS + 1) / 2 * 2, XS = 2 * XH;
+    static_assert(XS % 4 == 0, "rows are copied 16 bytes at a time");
+};
+template <int NX>
+__host__ __device__ constexpr int attr_row_floats()  // 0 attributes: no row
+{
+    if constexpr (NX == 0) return 0;
+    else return AttrLayout<NX>::XS;
+}
+inline int attr_stride(int n) { return n == 2 ? AttrLayout<2>::XS : n == 4 ? AttrLayout<4>::XS : n == 6 ? AttrLayout<6>::XS : 0; }
+inline int attr_offset(int n, int k) { return (k / (n / 2)) * (attr_stride(n) / 2) + 3 * (k % (n / 2)); }
+struct AttrPtrs { const float* src[6]; float* dst[6]; };
+cudaError_t launch_pack_attributes(int P, int n, const AttrPtrs& ptrs, float* packed, cudaStream_t s);
+cudaError_t launch_unpack_attributes(int P, int n, const float* packed, const AttrPtrs& ptrs, cudaStream_t s);
+cudaError_t launch_blend_forward_multi(const ghr_raster_params& p, const char* geom, const char* binning, char* img,
+                                       const ghr_layout& L, float* out_color, float* out_depth, float* out_alpha,
+                                       int n_attr, const float* xcol, float* out_x, cudaStream_t s);
+cudaError_t launch_blend_backward_multi(const ghr_raster_params& p, const char* geom, const char* binning, const char* img,
+                                        const ghr_layout& L, const float* dL_dpix, const float* dL_ddepth,
+                                        const float* dL_dalpha, float* accum, int n_attr, const float* xcol,
+                                        const float* xdpix, float* xaccum, cudaStream_t s);
 // rec[idx].rgb = colors[idx] for every Gaussian (multi-attribute rendering)
 cudaError_t launch_recolor(int P, const float* colors, char* geom, const ghr_layout& L, cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* V, uint8_t* present, cudaStream_t s);

@@ -99,8 +99,8 @@ def _pinned_counter(device):
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
-                        prefiltered, debug):
-    """RasterizeGaussiansCUDA, rasterize_points.cu:36-120."""
+                        prefiltered, debug, _attrs=None):
+    """RasterizeGaussiansCUDA, rasterize_points.cu:36-120.  (`_attrs`: rasterize_gaussians_multi's packed attributes.)"""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     P, H, W = means3D.size(0), int(image_height), int(image_width)
@@ -130,6 +130,15 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         def render(capacity):
             L = state_layout(P, capacity, W, H)
             binning = torch.empty(L.binning_bytes, dtype=torch.uint8, device=dev)
+            if _attrs is not None:
+                _attrs.fused = bool(l.ghr_attributes_fused(capacity))
+                if _attrs.fused:
+                    check(l.ghr_forward_render_multi(C.byref(p), geom.data_ptr(), geom.numel(), binning.data_ptr(),
+                                                     binning.numel(), capacity, img.data_ptr(), img.numel(),
+                                                     out_color.data_ptr(), out_depth.data_ptr(), out_alpha.data_ptr(),
+                                                     _attrs.n, _attrs.packed.data_ptr(), _attrs.images.data_ptr(), s),
+                          "ghr_forward_render_multi")
+                    return binning
             check(l.ghr_forward_render(C.byref(p), geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(),
                                        capacity, img.data_ptr(), img.numel(), out_color.data_ptr(), out_depth.data_ptr(),
                                        out_alpha.data_ptr(), s), "ghr_forward_render")
@@ -210,58 +219,82 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             dsh.view(P, M, 3), dscales.view(P, 3), drot.view(P, 4))
 
 
-# ---- multi-attribute rendering: one projection / sort / tile binning, one blend per attribute --------------------
+# ---- multi-attribute rendering: one projection / sort / tile binning for all attributes --------------------------
 # (reference gaussian_renderer/__init__.py:203-272 runs the whole rasteriser once per attribute; see include/ghr.h)
+
+_FUSED_MAX = 6  # attributes blended inside the main kernel (in pairs); any further ones are re-blended one by one
+
+
+class _Attrs:
+    def __init__(self, n, packed, images):
+        self.n, self.packed, self.images, self.fused = n, packed, images, False
+
 
 def _rec_colors(P, W, H, geom):
     L = state_layout(P, 0, W, H)
     return geom[L.g_rec:L.g_rec + P * 48].view(torch.float32).view(P, 3, 4)[:, 2, 0:3]
 
 
+def _ptr_array(tensors):
+    return (C.c_void_p * len(tensors))(*[None if t is None else t.data_ptr() for t in tensors])
+
+
 def rasterize_gaussians_multi(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                               viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree,
                               campos, prefiltered, debug, extra_colors):
-    """rasterize_gaussians for the first attribute (SH or `colors`), then one re-blend per [P,3] tensor of
-    `extra_colors` on the same sorted lists.  Returns the tuple of rasterize_gaussians plus (extra images, colours the
-    first attribute was blended with)."""
-    out = rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
-                              viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree,
-                              campos, prefiltered, debug)
-    num_rendered, out_color, out_depth, out_alpha, radii, geom, binning, img = out
+    """rasterize_gaussians for the first attribute (SH or `colors`) plus one image per [P,3] tensor of `extra_colors`,
+    all over the same sorted lists: up to six of them inside the same blend kernel, the rest re-blended.  Returns the
+    tuple of rasterize_gaussians plus (extra images, colours of the first attribute or None, packed attributes or None)."""
     P, H, W = means3D.size(0), int(image_height), int(image_width)
     dev = means3D.device
-    images = []
+    extra = []
+    for c in extra_colors:
+        if c.dim() != 2 or c.size(0) != P or c.size(1) != 3:
+            raise RuntimeError("every extra attribute must have dimensions (num_points, 3)")
+        extra.append(_ptr(c)[1] if P else c)
+    nf = min(_FUSED_MAX, len(extra) - len(extra) % 2) if P else 0
+    att = None
+    if nf:
+        with _lib.on_device(dev):
+            l = lib()
+            packed = torch.empty(P, l.ghr_attribute_stride(nf), dtype=torch.float32, device=dev)
+            check(l.ghr_pack_attributes(P, nf, _ptr_array(extra[:nf]), packed.data_ptr(), _stream(dev)),
+                  "ghr_pack_attributes")
+            att = _Attrs(nf, packed, torch.empty(3 * nf, H, W, dtype=torch.float32, device=dev))
+    out = rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                              viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree,
+                              campos, prefiltered, debug, _attrs=att)
+    num_rendered, out_color, out_depth, out_alpha, radii, geom, binning, img = out
     if P == 0:
-        return out + ([torch.zeros(3, H, W, dtype=torch.float32, device=dev) + background.view(3, 1, 1)
-                       for _ in extra_colors], torch.zeros(0, 3, device=dev))
-    first_colors = _rec_colors(P, W, H, geom).clone() if extra_colors else None
+        return out + ([torch.zeros(3, H, W, dtype=torch.float32, device=dev) for _ in extra], None, None)
+    fused = att is not None and att.fused
+    images = [att.images[3 * k:3 * k + 3] for k in range(nf)] if fused else []
+    rest = extra[nf:] if fused else extra
+    first_colors = _rec_colors(P, W, H, geom).clone() if rest else None
     capacity = _cap_of.get(binning.data_ptr(), int(num_rendered))
-    with _lib.on_device(dev):
-        keep = []
-        p = _params(keep, background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
-                    viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug)
-        scratch = torch.empty(2, H, W, dtype=torch.float32, device=dev)  # depth / alpha come out the same every time
-        l, s = lib(), _stream(dev)
-        for c in extra_colors:
-            if c.dim() != 2 or c.size(0) != P or c.size(1) != 3:
-                raise RuntimeError("every extra attribute must have dimensions (num_points, 3)")
-            cp, c = _ptr(c)
-            keep.append(c)
-            image = torch.empty(3, H, W, dtype=torch.float32, device=dev)
-            check(l.ghr_forward_reblend(C.byref(p), cp, geom.data_ptr(), geom.numel(), binning.data_ptr(),
-                                        binning.numel(), capacity, img.data_ptr(), img.numel(), image.data_ptr(),
-                                        scratch[0].data_ptr(), scratch[1].data_ptr(), s), "ghr_forward_reblend")
-            images.append(image)
-    return out + (images, first_colors)
+    if rest:
+        with _lib.on_device(dev):
+            keep = []
+            p = _params(keep, background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug)
+            scratch = torch.empty(2, H, W, dtype=torch.float32, device=dev)  # depth / alpha come out the same every time
+            l, s = lib(), _stream(dev)
+            for c in rest:
+                image = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+                check(l.ghr_forward_reblend(C.byref(p), c.data_ptr(), geom.data_ptr(), geom.numel(), binning.data_ptr(),
+                                            binning.numel(), capacity, img.data_ptr(), img.numel(), image.data_ptr(),
+                                            scratch[0].data_ptr(), scratch[1].data_ptr(), s), "ghr_forward_reblend")
+                images.append(image)
+            _rec_colors(P, W, H, geom).copy_(first_colors)  # the records again hold the first attribute
+    return out + (images, first_colors, att.packed if fused else None)
 
 
 def rasterize_gaussians_multi_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color,
                                        dL_dout_depth, dL_dout_alpha, sh, degree, campos, geomBuffer, R, binningBuffer,
-                                       imageBuffer, alphas, debug, first_colors, extra_colors, dL_dextra):
-    """Backward of rasterize_gaussians_multi: one blend backward per attribute into a shared accumulator, then one
-    per-Gaussian backward.  `dL_dextra[k]` may be None (attribute k did not reach the loss).  Returns the tuple of
-    rasterize_gaussians_backward plus the list of dL_dextra_colors."""
+                                       imageBuffer, alphas, debug, first_colors, packed, extra_colors, dL_dextra):
+    """Backward of rasterize_gaussians_multi.  `dL_dextra[k]` may be None (attribute k did not reach the loss).
+    Returns the tuple of rasterize_gaussians_backward plus the list of dL_dextra_colors."""
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     M = sh.size(1) if sh.numel() != 0 else 0
@@ -270,6 +303,7 @@ def rasterize_gaussians_multi_backward(background, means3D, radii, colors, scale
         z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
         return (z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4), [z(0, 3) for _ in extra_colors])
     capacity = _cap_of.get(binningBuffer.data_ptr(), int(R))
+    nf = 0 if packed is None else min(_FUSED_MAX, len(extra_colors) - len(extra_colors) % 2)
     with _lib.on_device(dev):
         keep = []
         p = _params(keep, background, means3D, colors, means3D, scales, rotations, scale_modifier, cov3D_precomp,
@@ -283,32 +317,46 @@ def rasterize_gaussians_multi_backward(background, means3D, radii, colors, scale
         accum, drot, dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dscales, dsh = views
         accum.zero_()
         accum2 = accum.view(P, 12)
-        zeros_plane = torch.zeros(H * W, dtype=torch.float32, device=dev)
         f32c = lambda t: t.contiguous() if t.dtype == torch.float32 else t.float().contiguous()
         radii = radii.contiguous()
         l, s = lib(), _stream(dev)
         geo = (geomBuffer.data_ptr(), geomBuffer.numel(), binningBuffer.data_ptr(), binningBuffer.numel(), capacity,
                imageBuffer.data_ptr(), imageBuffer.numel())
-        dextra = []
-        for c, g in zip(extra_colors, dL_dextra):
-            if g is None:
-                dextra.append(None)
+        dextra = [None] * len(extra_colors)
+        zeros_plane = None
+        # attributes that were re-blended: one blend backward each into the shared accumulator
+        for k in range(nf, len(extra_colors)):
+            if dL_dextra[k] is None:
                 continue
-            cp, c = _ptr(c)
-            g = f32c(g)
+            if zeros_plane is None:
+                zeros_plane = torch.zeros(H * W, dtype=torch.float32, device=dev)
+            cp, c = _ptr(extra_colors[k])
+            g = f32c(dL_dextra[k])
             check(l.ghr_backward_blend(C.byref(p), cp, *geo, g.data_ptr(), None, None, zeros_plane.data_ptr(),
                                        accum.data_ptr(), s), "ghr_backward_blend")
-            dextra.append(accum2[:, 0:3].clone())
+            dextra[k] = accum2[:, 0:3].clone()
             accum2[:, 0:3].zero_()
-        # the first attribute last: its colour gradient stays in the record for the SH backward
         g = [f32c(t) for t in (dL_dout_color, dL_dout_depth, dL_dout_alpha)]
-        cp, c0 = _ptr(first_colors)
-        check(l.ghr_backward_blend(C.byref(p), cp, *geo, g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(),
-                                   zeros_plane.data_ptr(), accum.data_ptr(), s), "ghr_backward_blend")
-        check(l.ghr_backward_finish(C.byref(p), radii.data_ptr(), geomBuffer.data_ptr(), geomBuffer.numel(), capacity,
-                                    accum.data_ptr(), dmeans2D.data_ptr(), dcolors.data_ptr(), dopacity.data_ptr(),
-                                    dmeans3D.data_ptr(), dcov3D.data_ptr(), dsh.data_ptr() if M else None,
-                                    dscales.data_ptr(), drot.data_ptr(), s), "ghr_backward_finish")
+        if zeros_plane is not None:
+            _rec_colors(P, W, H, geomBuffer).copy_(first_colors)  # ghr_backward_blend left another attribute there
+        grads = (dmeans2D.data_ptr(), dcolors.data_ptr(), dopacity.data_ptr(), dmeans3D.data_ptr(), dcov3D.data_ptr(),
+                 dsh.data_ptr() if M else None, dscales.data_ptr(), drot.data_ptr())
+        if nf and any(dL_dextra[k] is not None for k in range(nf)):
+            planes = [f32c(dL_dextra[k]) if dL_dextra[k] is not None
+                      else torch.zeros(3, H, W, dtype=torch.float32, device=dev) for k in range(nf)]
+            xdpix = torch.cat(planes)
+            packed_grad = torch.empty_like(packed)
+            check(l.ghr_backward_multi(C.byref(p), radii.data_ptr(), *geo, g[0].data_ptr(), g[1].data_ptr(),
+                                       g[2].data_ptr(), nf, packed.data_ptr(), xdpix.data_ptr(), packed_grad.data_ptr(),
+                                       accum.data_ptr(), *grads, s), "ghr_backward_multi")
+            outs = [torch.empty(P, 3, dtype=torch.float32, device=dev) if dL_dextra[k] is not None else None
+                    for k in range(nf)]
+            check(l.ghr_unpack_attribute_grads(P, nf, packed_grad.data_ptr(), _ptr_array(outs), s),
+                  "ghr_unpack_attribute_grads")
+            dextra[:nf] = outs
+        else:
+            check(l.ghr_backward(C.byref(p), radii.data_ptr(), *geo, g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(),
+                                 accum.data_ptr(), *grads, s), "ghr_backward")
     return (dmeans2D.view(P, 3), dcolors.view(P, 3), dopacity.view(P, 1), dmeans3D.view(P, 3), dcov3D.view(P, 6),
             dsh.view(P, M, 3), dscales.view(P, 3), drot.view(P, 4), dextra)
 

@@ -100,12 +100,12 @@ class _RasterizeGaussiansMulti(torch.autograd.Function):
                        cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
                        rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, extra_colors)
         (num_rendered, color, depth, alpha, radii, geom_state, binning_state, image_state, extra_images,
-         first_colors) = _call_native(_C.rasterize_gaussians_multi, native_args, rs.debug, "fw")
+         first_colors, packed) = _call_native(_C.rasterize_gaussians_multi, native_args, rs.debug, "fw")
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
         ctx.has_means2D = torch.is_tensor(means2D)
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom_state,
-                              binning_state, image_state, alpha, first_colors, *extra_colors)
+                              binning_state, image_state, alpha, first_colors, packed, *extra_colors)
         ctx.mark_non_differentiable(radii)
         ctx.set_materialize_grads(False)
         return (color, radii, depth, alpha) + tuple(extra_images)
@@ -114,8 +114,8 @@ class _RasterizeGaussiansMulti(torch.autograd.Function):
     def backward(ctx, grad_color, grad_radii, grad_depth, grad_alpha, *grad_extra):
         rs = ctx.raster_settings
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom_state, binning_state,
-         image_state, alpha, first_colors) = ctx.saved_tensors[:12]
-        extra_colors = ctx.saved_tensors[12:]
+         image_state, alpha, first_colors, packed) = ctx.saved_tensors[:13]
+        extra_colors = ctx.saved_tensors[13:]
         zeros = lambda c: torch.zeros(c, rs.image_height, rs.image_width, dtype=torch.float32, device=means3D.device)
         grad_color = zeros(3) if grad_color is None else grad_color
         grad_depth = zeros(1) if grad_depth is None else grad_depth
@@ -123,7 +123,7 @@ class _RasterizeGaussiansMulti(torch.autograd.Function):
         native_args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                        rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha, sh,
                        rs.sh_degree, rs.campos, geom_state, ctx.num_rendered, binning_state, image_state, alpha,
-                       rs.debug, first_colors, extra_colors, grad_extra)
+                       rs.debug, first_colors, packed, extra_colors, grad_extra)
         (g_means2D, g_colors, g_opacities, g_means3D, g_cov3D, g_sh, g_scales, g_rotations,
          g_extra) = _call_native(_C.rasterize_gaussians_multi_backward, native_args, rs.debug, "bw")
         return (None, g_means3D, g_means2D if ctx.has_means2D else None, g_sh, g_colors, g_opacities, g_scales,

@@ -14,7 +14,8 @@ from tests import common as Cm
 
 pytestmark = pytest.mark.gpu
 
-N_ATTR = 6  # normal, world normal, albedo, occlusion, roughness, axis (the reference's extra passes)
+N_ATTR = 7  # the reference has six extra passes (normal, world normal, albedo, occlusion, roughness, axis); one more here
+            # so that both the fused (pairs, up to six) and the re-blended attributes are exercised
 
 
 def _settings(tc):
@@ -91,20 +92,22 @@ def _run(fn, rast, lv, used, weights):
     return [im.detach().clone() for im in images], radii.clone(), depth.detach().clone(), alpha.detach().clone(), grads
 
 
-@pytest.mark.parametrize("P,W,H,mode", [(3000, 160, 128, "precomp"), (2500, 200, 152, "sh_scale_rot"),
-                                        (20000, 512, 512, "precomp")])
-def test_forward_multi_equals_one_call_per_attribute(P, W, H, mode):
+@pytest.mark.parametrize("P,W,H,mode,n_used", [(3000, 160, 128, "precomp", 6), (2500, 200, 152, "sh_scale_rot", 7),
+                                               (20000, 512, 512, "precomp", 6), (3000, 160, 128, "precomp", 1),
+                                               (3000, 160, 128, "sh_scale_rot", 2), (3000, 160, 128, "precomp", 3),
+                                               (3000, 100, 72, "precomp", 4), (3000, 160, 128, "precomp", 5)])
+def test_forward_multi_equals_one_call_per_attribute(P, W, H, mode, n_used):
     from mygauhuman_b200.diff_gaussian_rasterization import GaussianRasterizer
     tc = Cm.to_torch(Cm.raster_case(P, W, H, seed=P, mode=mode), "cuda")
     lv = _leaves(tc, mode, seed=1)
     rast = GaussianRasterizer(_settings(tc))
     weights = _weights(tc, seed=2)
-    used = list(range(N_ATTR))
+    used = list(range(n_used))
     si, sr, sd, sa, sg = _run(_separate, rast, lv, used, weights)
     mi, mr, md, ma, mg = _run(_multi, rast, lv, used, weights)
     assert torch.equal(sr, mr)
     assert torch.equal(sd, md) and torch.equal(sa, ma)
-    assert len(si) == len(mi) == N_ATTR + 1
+    assert len(si) == len(mi) == n_used + 1
     for k, (a, b) in enumerate(zip(si, mi)):
         assert torch.equal(a, b), f"attribute image {k} differs"
     for k in sg:
@@ -120,9 +123,9 @@ def test_unused_attributes_and_missing_gradients():
     lv = _leaves(tc, "precomp", seed=3)
     rast = GaussianRasterizer(_settings(tc))
     kw = _geometry_kwargs(lv)
-    color, radii, depth, alpha, extra = rast.forward_multi(extra_colors=[lv["attr0"], lv["attr1"]], **kw)
+    color, radii, depth, alpha, extra = rast.forward_multi(extra_colors=[lv["attr0"], lv["attr1"], lv["attr2"]], **kw)
     w = torch.randn(3, tc["H"], tc["W"], generator=torch.Generator().manual_seed(4)).cuda()
-    (extra[1] * w).sum().backward()           # only the second extra attribute is used
+    (extra[1] * w).sum().backward()           # only the second extra attribute (a fused one) is used
     g_multi = {k: v.grad.clone() for k, v in lv.items() if v.grad is not None}
     assert "attr0" not in g_multi or float(g_multi["attr0"].abs().max()) == 0.0
     assert float(lv["colors"].grad.abs().max()) == 0.0
@@ -131,6 +134,17 @@ def test_unused_attributes_and_missing_gradients():
     geo = {k: v for k, v in kw.items() if k != "colors_precomp"}
     (rast(colors_precomp=lv["attr1"], **geo)[0] * w).sum().backward()
     for k in ("attr1", "means3D", "opacity", "cov3D"):
+        assert Cm.rel_err(g_multi[k].cpu().numpy(), lv[k].grad.cpu().numpy()) < 1e-4, k
+    # ... and only the re-blended one
+    for v in lv.values():
+        v.grad = None
+    color, radii, depth, alpha, extra = rast.forward_multi(extra_colors=[lv["attr0"], lv["attr1"], lv["attr2"]], **kw)
+    (extra[2] * w).sum().backward()
+    g_multi = {k: v.grad.clone() for k, v in lv.items() if v.grad is not None}
+    for v in lv.values():
+        v.grad = None
+    (rast(colors_precomp=lv["attr2"], **geo)[0] * w).sum().backward()
+    for k in ("attr2", "means3D", "opacity", "cov3D"):
         assert Cm.rel_err(g_multi[k].cpu().numpy(), lv[k].grad.cpu().numpy()) < 1e-4, k
 
 
@@ -146,6 +160,7 @@ def test_forward_multi_vs_reference_cuda_per_attribute():
         images, radii, depth, alpha = _multi(rast, lv, list(range(N_ATTR)))
     ref = ref_cuda.RefRasterizer()
     attrs = [lv["colors"]] + [lv[f"attr{k}"] for k in range(N_ATTR)]
+    assert len(images) == len(attrs)
     for k, c in enumerate(attrs):
         n, rcolor, rdepth, ralpha, rradii = ref.forward(tc["bg"], tc["means3D"], c.detach(), tc["opacity"], Cm.empty(),
                                                         Cm.empty(), tc["scale_modifier"], tc["cov3D"], tc["view"],

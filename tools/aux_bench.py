@@ -278,7 +278,31 @@ def render7(quick):
     n = 10 if quick else 40
     med_m, _ = timed(multi, n, warm=5, before=clear)
     med_s, _ = timed(separate, n, warm=5, before=clear)
+    e0 = torch.Tensor([])
+    det = [a.detach() for a in attrs]
+
+    def direct():  # the drop-in _C entry points without autograd, as the reference arm below is timed
+        fw = _C.rasterize_gaussians_multi(tc["bg"], tc["means3D"], tc["colors"], tc["opacity"], e0, e0, 1.0, tc["cov3D"],
+                                          tc["view"], tc["proj"], tc["tanfovx"], tc["tanfovy"], H, W, e0, 3, tc["campos"],
+                                          False, False, det)
+        n_, color, depth, alpha, radii, geom, binning, img, images, first, packed = fw
+        _C.rasterize_gaussians_multi_backward(tc["bg"], tc["means3D"], radii, tc["colors"], e0, e0, 1.0, tc["cov3D"],
+                                              tc["view"], tc["proj"], tc["tanfovx"], tc["tanfovy"], wts[0], wd, wa, e0, 3,
+                                              tc["campos"], geom, n_, binning, img, alpha, False, first, packed, det,
+                                              wts[1:])
+    med_d, _ = timed(direct, n, warm=5)
+    _lib.profile_enable(True)
+    _lib.profile_read()
+    for i in range(10):
+        clear()
+        _flush.fill_(i)
+        multi()
+    stages = {k: round(1e3 * ms / max(c, 1), 1) for k, (ms, c) in _lib.profile_read().items() if c}
+    _lib.profile_enable(False)
     out = {"P": P, "W": W, "H": H, "attributes": NA + 1, "forward_multi_ms": round(med_m, 4),
+           "forward_multi_direct_ms": round(med_d, 4),
+           "direct_what": "_C.rasterize_gaussians_multi + _multi_backward called directly (no autograd, no loss kernels)",
+           "forward_multi_stage_us": stages,
            "one_call_per_attribute_ms": round(med_s, 4), "multi_vs_separate": round(med_s / med_m, 2),
            "what": "rasteriser forward + backward through torch autograd (linear loss on every image), L2 flushed"}
     ref = ref_or_none()
@@ -298,6 +322,7 @@ def render7(quick):
         try:
             med_r, _ = timed(theirs, 5 if quick else 20, warm=3)
             out.update(ref_ms=round(med_r, 4), speedup_vs_ref=round(med_r / med_m, 2),
+                       direct_speedup_vs_ref=round(med_r / med_d, 2),
                        ref_what="seven forward+backward calls of the reference's unmodified CUDA rasteriser (no autograd overhead)")
         except Exception as ex:
             out["ref_error"] = repr(ex)[:200]
