@@ -370,6 +370,39 @@ int ghr_smpl_lbs_vertices(const ghr_lbs_model* model, const float* v_template, c
                           float* verts /*[V,3]*/, float* T_out /*[V,12]|NULL*/, void* stream);
 
 /*
+ * Optimiser side of the training iteration (no native counterpart in the reference, which runs
+ * these as chains of ATen kernels).
+ *
+ * ghr_adam_step: torch.optim.Adam(l, lr=0.0, eps=1e-15).step() of scene/gaussian_model.py:283 / train.py:418
+ * (no weight decay, no amsgrad, maximize=False) for up to GHR_ADAM_MAX_GROUPS parameter tensors in ONE launch:
+ *   exp_avg += (1-beta1)(grad - exp_avg); exp_avg_sq = beta2 exp_avg_sq + (1-beta2) grad^2;
+ *   param  -= lr/(1-beta1^step) * exp_avg / (sqrt(exp_avg_sq)/sqrt(1-beta2^step) + eps)
+ * `step` is the group's 1-based step count after this step (torch keeps state['step'] per parameter; tensors
+ * re-created by densification carry theirs along, gaussian_model.py:423-483).  The groups table is host memory, the
+ * pointers in it device memory, fp32.  zero_grads != 0 also clears the gradients in
+ * the same pass (optimizer.zero_grad, train.py:419).  28 (32) bytes of HBM traffic per parameter.
+ */
+#define GHR_ADAM_MAX_GROUPS 16
+typedef struct ghr_adam_group {
+    float* param;
+    float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    int64_t count;  /* floats */
+    float lr;       /* param_group['lr'] of this step (update_learning_rate, gaussian_model.py:290-295) */
+    int32_t step;   /* >= 1 */
+} ghr_adam_group;
+int ghr_adam_step(int n_groups, const ghr_adam_group* groups, float beta1, float beta2, float eps, int zero_grads,
+                  void* stream);
+
+/* train.py:401-404 + GaussianModel.add_densification_stats (scene/gaussian_model.py:764-766) with
+ * visibility_filter = radii > 0, fused: max_radii2D[i] = max(max_radii2D[i], radii[i]);
+ * xyz_gradient_accum[i] += ||dL_dmean2D[i, :2]||; denom[i] += 1.  Any of the three outputs may be NULL.
+ * grad_stride = floats per row of dL_dmean2D (3 for the [P,3] viewspace tensor). */
+int ghr_densify_stats(int32_t P, const int32_t* radii, const float* dL_dmean2D, int32_t grad_stride, float* max_radii2D,
+                      float* xyz_gradient_accum, float* denom, void* stream);
+
+/*
  * Measurement hooks (no reference counterpart; the reference has no profiling
  * facility beyond wall-clock prints, train.py:209).  Process-wide, off by
  * default, the only state the library keeps between calls.
@@ -392,7 +425,8 @@ enum ghr_stage {
     GHR_STAGE_LBS_FWD = 9,
     GHR_STAGE_LBS_BWD = 10,
     GHR_STAGE_MISC = 11,
-    GHR_STAGE_COUNT = 12
+    GHR_STAGE_OPTIMIZER = 12,   /* fused Adam, densification statistics           */
+    GHR_STAGE_COUNT = 13
 };
 uint64_t ghr_launch_count(void);
 int ghr_profile_enable(int on);

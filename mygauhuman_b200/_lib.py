@@ -58,6 +58,13 @@ class DeformParams(C.Structure):
                 ("dL_dopacity_logits", c_f32p), ("accumulate_grads", C.c_int32)]
 
 
+class AdamGroup(C.Structure):
+    """ghr_adam_group (include/ghr.h)."""
+    _fields_ = [("param", c_f32p), ("grad", c_f32p), ("exp_avg", c_f32p), ("exp_avg_sq", c_f32p), ("count", C.c_int64),
+                ("lr", C.c_float), ("step", C.c_int32)]
+
+
+ADAM_MAX_GROUPS = 16
 POSE_FLOATS = 1536
 POSE_A, POSE_ROT, POSE_PF, POSE_JOINTS, POSE_RGINV, POSE_RG, POSE_TH, POSE_G, POSE_ROD = 0, 288, 504, 720, 800, 816, 832, 848, 1136
 
@@ -105,13 +112,16 @@ SIGNATURES = {
     "ghr_lbs_deform_backward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 15),
     "ghr_lbs_pose_backward": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
     "ghr_smpl_lbs_vertices": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
+    "ghr_adam_step": (C.c_int, [C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_void_p]),
+    "ghr_densify_stats": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p]),
     "ghr_launch_count": (C.c_uint64, []),
     "ghr_profile_enable": (C.c_int, [C.c_int]),
     "ghr_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
 }
 
 STAGES = ("preprocess", "emit_keys", "sort", "tile_ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "knn",
-          "lbs_joints", "lbs_fwd", "lbs_bwd", "misc")
+          "lbs_joints", "lbs_fwd", "lbs_bwd", "misc", "optimizer")
 
 _lib = None
 

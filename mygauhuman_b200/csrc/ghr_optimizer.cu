@@ -1,0 +1,191 @@
+// Optimiser-side kernels of the training iteration:
+//   * adam_multi_kernel  -- torch.optim.Adam(l, lr=0.0, eps=1e-15).step() of the reference
+//     (scene/gaussian_model.py:283, train.py:418-419) for ALL parameter groups in one launch,
+//     optionally zeroing the gradients in the same pass (optimizer.zero_grad / bucket reset);
+//   * densify_stats_kernel -- the per-iteration densification statistics
+//     (train.py:401-404, scene/gaussian_model.py:764-766).
+// Both are pure HBM streams: 28 (32 with the gradient reset) bytes per parameter, 40 bytes per Gaussian.
+#include <math.h>
+#include <stdio.h>
+#include "ghr_internal.h"
+
+namespace ghr {
+namespace {
+
+constexpr int kAdamThreads = 256;
+constexpr int kAdamVec = 2;                                   // float4 per array per thread
+constexpr int kAdamChunk = kAdamThreads * kAdamVec * 4;       // floats per CTA (2 048)
+
+struct AdamSeg {
+    float* p;
+    float* g;
+    float* m;
+    float* v;
+    int64_t count;
+    float neg_step_size;   // -lr / (1 - beta1^t)
+    float inv_bc2_sqrt;    // 1 / sqrt(1 - beta2^t)
+    uint32_t first_chunk;  // CTA index of the segment's first chunk
+    uint32_t vec_ok;       // all four pointers 16-byte aligned
+};
+struct AdamTable {
+    AdamSeg seg[GHR_ADAM_MAX_GROUPS];
+    int n;
+    float w1;      // 1 - beta1
+    float beta2;
+    float w2;      // 1 - beta2
+    float eps;
+    int zero_grads;
+};
+
+// One element of torch's _single_tensor_adam (torch/optim/adam.py): exp_avg.lerp_(grad, 1 - beta1);
+// exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2); denom = (exp_avg_sq.sqrt() / bias_correction2_sqrt) + eps;
+// param.addcdiv_(exp_avg, denom, value=-step_size).  The CUDA foreach path multiplies by the reciprocal of the scalar
+// divisor, which is what inv_bc2_sqrt does.
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamTable& t, const AdamSeg& s)
+{
+    m = __fmaf_rn(g - m, t.w1, m);
+    v = __fmaf_rn(g * g, t.w2, v * t.beta2);
+    const float denom = __fmaf_rn(sqrtf(v), s.inv_bc2_sqrt, t.eps);
+    p = __fmaf_rn(s.neg_step_size, m / denom, p);
+}
+
+__global__ void __launch_bounds__(kAdamThreads) adam_multi_kernel(const __grid_constant__ AdamTable t)
+{
+    // which segment does this CTA work on?  (<= 16 entries, uniform per CTA)
+    int k = 0;
+#pragma unroll 1
+    for (int i = 1; i < t.n; ++i)
+        if (blockIdx.x >= t.seg[i].first_chunk) k = i;
+    const AdamSeg& s = t.seg[k];
+    const int64_t base = int64_t(blockIdx.x - s.first_chunk) * kAdamChunk;
+    const int64_t left = s.count - base;
+    if (s.vec_ok && left >= kAdamChunk) {
+        float4 p[kAdamVec], g[kAdamVec], m[kAdamVec], v[kAdamVec];
+#pragma unroll
+        for (int j = 0; j < kAdamVec; ++j) {  // all loads first: 8 independent 16-byte requests per thread
+            const int64_t i = base / 4 + j * kAdamThreads + threadIdx.x;
+            p[j] = reinterpret_cast<const float4*>(s.p)[i];
+            g[j] = reinterpret_cast<const float4*>(s.g)[i];
+            m[j] = reinterpret_cast<const float4*>(s.m)[i];
+            v[j] = reinterpret_cast<const float4*>(s.v)[i];
+        }
+#pragma unroll
+        for (int j = 0; j < kAdamVec; ++j) {
+            const int64_t i = base / 4 + j * kAdamThreads + threadIdx.x;
+            adam_one(p[j].x, g[j].x, m[j].x, v[j].x, t, s);
+            adam_one(p[j].y, g[j].y, m[j].y, v[j].y, t, s);
+            adam_one(p[j].z, g[j].z, m[j].z, v[j].z, t, s);
+            adam_one(p[j].w, g[j].w, m[j].w, v[j].w, t, s);
+            reinterpret_cast<float4*>(s.p)[i] = p[j];
+            reinterpret_cast<float4*>(s.m)[i] = m[j];
+            reinterpret_cast<float4*>(s.v)[i] = v[j];
+            if (t.zero_grads) reinterpret_cast<float4*>(s.g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        return;
+    }
+    // ragged tail of a segment, or unaligned views: scalar
+    const int64_t n = left < kAdamChunk ? left : kAdamChunk;
+    for (int64_t i = threadIdx.x; i < n; i += kAdamThreads) {
+        float p = s.p[base + i], m = s.m[base + i], v = s.v[base + i];
+        const float g = s.g[base + i];
+        adam_one(p, g, m, v, t, s);
+        s.p[base + i] = p;
+        s.m[base + i] = m;
+        s.v[base + i] = v;
+        if (t.zero_grads) s.g[base + i] = 0.f;
+    }
+}
+
+// train.py:401-404 + gaussian_model.py:764-766 for visibility_filter = radii > 0:
+//   max_radii2D[f] = max(max_radii2D[f], radii[f]); xyz_gradient_accum[f] += ||viewspace.grad[f, :2]||; denom[f] += 1
+__global__ void __launch_bounds__(256) densify_stats_kernel(int P, const int32_t* __restrict__ radii,
+                                                            const float* __restrict__ dL_dmean2D, int stride,
+                                                            float* __restrict__ max_radii2D,
+                                                            float* __restrict__ grad_accum, float* __restrict__ denom)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const int r = radii[i];
+    if (r <= 0) return;
+    if (max_radii2D) max_radii2D[i] = fmaxf(max_radii2D[i], (float)r);
+    const float gx = dL_dmean2D[(int64_t)i * stride], gy = dL_dmean2D[(int64_t)i * stride + 1];
+    if (grad_accum) grad_accum[i] += sqrtf(__fmaf_rn(gy, gy, gx * gx));
+    if (denom) denom[i] += 1.f;
+}
+
+inline bool misaligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) != 0; }
+
+}  // namespace
+}  // namespace ghr
+
+using namespace ghr;
+
+extern "C" {
+
+int ghr_adam_step(int n_groups, const ghr_adam_group* groups, float beta1, float beta2, float eps, int zero_grads,
+                  void* stream)
+{
+    if (n_groups < 0 || n_groups > GHR_ADAM_MAX_GROUPS) return GHR_ERR_BAD_ARG;
+    if (n_groups == 0) return GHR_OK;
+    if (!groups) return GHR_ERR_BAD_ARG;
+    if (!(beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f && eps >= 0.f)) return GHR_ERR_BAD_ARG;
+    AdamTable t;
+    t.n = 0;
+    t.w1 = (float)(1.0 - (double)beta1);  // torch: the lerp weight is the Python double 1 - beta1 rounded to fp32
+    t.beta2 = beta2;
+    t.w2 = (float)(1.0 - (double)beta2);
+    t.eps = eps;
+    t.zero_grads = zero_grads ? 1 : 0;
+    uint64_t chunks = 0;
+    for (int i = 0; i < n_groups; ++i) {
+        const ghr_adam_group& g = groups[i];
+        if (g.count < 0 || g.step < 1) return GHR_ERR_BAD_ARG;
+        if (g.count == 0) continue;
+        if (!g.param || !g.grad || !g.exp_avg || !g.exp_avg_sq) return GHR_ERR_BAD_ARG;
+        AdamSeg& s = t.seg[t.n++];
+        s.p = g.param; s.g = g.grad; s.m = g.exp_avg; s.v = g.exp_avg_sq;
+        s.count = g.count;
+        // bias corrections in double, like the Python scalars of torch/optim/adam.py
+        const double bc1 = 1.0 - pow((double)beta1, (double)g.step);
+        const double bc2 = 1.0 - pow((double)beta2, (double)g.step);
+        const double bc2_sqrt = sqrt(bc2);
+        s.neg_step_size = (float)(-(double)g.lr / bc1);
+        s.inv_bc2_sqrt = (float)(1.0 / bc2_sqrt);
+        s.first_chunk = (uint32_t)chunks;
+        s.vec_ok = !(misaligned16(g.param) || misaligned16(g.grad) || misaligned16(g.exp_avg) || misaligned16(g.exp_avg_sq));
+        chunks += (uint64_t)((g.count + kAdamChunk - 1) / kAdamChunk);
+        if (chunks >= (uint64_t(1) << 31)) return GHR_ERR_BAD_ARG;
+    }
+    if (t.n == 0) return GHR_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    StageTimer timer(GHR_STAGE_OPTIMIZER, s);
+    adam_multi_kernel<<<(unsigned)chunks, kAdamThreads, 0, s>>>(t);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        fprintf(stderr, "[libghr] CUDA error in adam_step: %s\n", cudaGetErrorString(e));
+        return GHR_ERR_CUDA;
+    }
+    return GHR_OK;
+}
+
+int ghr_densify_stats(int32_t P, const int32_t* radii, const float* dL_dmean2D, int32_t grad_stride, float* max_radii2D,
+                      float* xyz_gradient_accum, float* denom, void* stream)
+{
+    if (P < 0 || grad_stride < 2) return GHR_ERR_BAD_ARG;
+    if (P == 0) return GHR_OK;
+    if (!radii || !dL_dmean2D) return GHR_ERR_BAD_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    StageTimer timer(GHR_STAGE_OPTIMIZER, s);
+    densify_stats_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, dL_dmean2D, grad_stride, max_radii2D,
+                                                         xyz_gradient_accum, denom);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        fprintf(stderr, "[libghr] CUDA error in densify_stats: %s\n", cudaGetErrorString(e));
+        return GHR_ERR_CUDA;
+    }
+    return GHR_OK;
+}
+
+}  // extern "C"
