@@ -389,11 +389,12 @@ typedef struct ghr_adam_group {
     float* exp_avg;
     float* exp_avg_sq;
     int64_t count;  /* floats */
-    float lr;       /* param_group['lr'] of this step (update_learning_rate, gaussian_model.py:290-295) */
+    double lr;      /* param_group['lr'] of this step (update_learning_rate, gaussian_model.py:290-295) */
     int32_t step;   /* >= 1 */
+    int32_t pad;
 } ghr_adam_group;
-int ghr_adam_step(int n_groups, const ghr_adam_group* groups, float beta1, float beta2, float eps, int zero_grads,
-                  void* stream);
+int ghr_adam_step(int n_groups, const ghr_adam_group* groups, double beta1, double beta2, double eps, int zero_grads,
+                  void* stream); /* betas / eps as the Python doubles torch holds: 1 - beta is rounded to fp32 once */
 
 /* train.py:401-404 + GaussianModel.add_densification_stats (scene/gaussian_model.py:764-766) with
  * visibility_filter = radii > 0, fused: max_radii2D[i] = max(max_radii2D[i], radii[i]);

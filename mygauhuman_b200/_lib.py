@@ -61,7 +61,7 @@ class DeformParams(C.Structure):
 class AdamGroup(C.Structure):
     """ghr_adam_group (include/ghr.h)."""
     _fields_ = [("param", c_f32p), ("grad", c_f32p), ("exp_avg", c_f32p), ("exp_avg_sq", c_f32p), ("count", C.c_int64),
-                ("lr", C.c_float), ("step", C.c_int32)]
+                ("lr", C.c_double), ("step", C.c_int32), ("pad", C.c_int32)]
 
 
 ADAM_MAX_GROUPS = 16
@@ -112,7 +112,7 @@ SIGNATURES = {
     "ghr_lbs_deform_backward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 15),
     "ghr_lbs_pose_backward": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
     "ghr_smpl_lbs_vertices": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
-    "ghr_adam_step": (C.c_int, [C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_void_p]),
+    "ghr_adam_step": (C.c_int, [C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int, C.c_void_p]),
     "ghr_densify_stats": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_void_p]),
     "ghr_launch_count": (C.c_uint64, []),

@@ -122,19 +122,19 @@ using namespace ghr;
 
 extern "C" {
 
-int ghr_adam_step(int n_groups, const ghr_adam_group* groups, float beta1, float beta2, float eps, int zero_grads,
+int ghr_adam_step(int n_groups, const ghr_adam_group* groups, double beta1, double beta2, double eps, int zero_grads,
                   void* stream)
 {
     if (n_groups < 0 || n_groups > GHR_ADAM_MAX_GROUPS) return GHR_ERR_BAD_ARG;
     if (n_groups == 0) return GHR_OK;
     if (!groups) return GHR_ERR_BAD_ARG;
-    if (!(beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f && eps >= 0.f)) return GHR_ERR_BAD_ARG;
+    if (!(beta1 >= 0.0 && beta1 < 1.0 && beta2 >= 0.0 && beta2 < 1.0 && eps >= 0.0)) return GHR_ERR_BAD_ARG;
     AdamTable t;
     t.n = 0;
-    t.w1 = (float)(1.0 - (double)beta1);  // torch: the lerp weight is the Python double 1 - beta1 rounded to fp32
-    t.beta2 = beta2;
-    t.w2 = (float)(1.0 - (double)beta2);
-    t.eps = eps;
+    t.w1 = (float)(1.0 - beta1);  // torch: the lerp weight is the Python double 1 - beta1, rounded to fp32 once
+    t.beta2 = (float)beta2;
+    t.w2 = (float)(1.0 - beta2);
+    t.eps = (float)eps;
     t.zero_grads = zero_grads ? 1 : 0;
     uint64_t chunks = 0;
     for (int i = 0; i < n_groups; ++i) {
@@ -146,10 +146,10 @@ int ghr_adam_step(int n_groups, const ghr_adam_group* groups, float beta1, float
         s.p = g.param; s.g = g.grad; s.m = g.exp_avg; s.v = g.exp_avg_sq;
         s.count = g.count;
         // bias corrections in double, like the Python scalars of torch/optim/adam.py
-        const double bc1 = 1.0 - pow((double)beta1, (double)g.step);
-        const double bc2 = 1.0 - pow((double)beta2, (double)g.step);
+        const double bc1 = 1.0 - pow(beta1, (double)g.step);
+        const double bc2 = 1.0 - pow(beta2, (double)g.step);
         const double bc2_sqrt = sqrt(bc2);
-        s.neg_step_size = (float)(-(double)g.lr / bc1);
+        s.neg_step_size = (float)(-g.lr / bc1);
         s.inv_bc2_sqrt = (float)(1.0 / bc2_sqrt);
         s.first_chunk = (uint32_t)chunks;
         s.vec_ok = !(misaligned16(g.param) || misaligned16(g.grad) || misaligned16(g.exp_avg) || misaligned16(g.exp_avg_sq));
