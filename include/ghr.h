@@ -370,6 +370,25 @@ int ghr_smpl_lbs_vertices(const ghr_lbs_model* model, const float* v_template, c
                           float* verts /*[V,3]*/, float* T_out /*[V,12]|NULL*/, void* stream);
 
 /*
+ * View-batched forward rasterisation: n_views small views of the SAME Gaussians in one set of
+ * launches -- what baking.py::bake_set (:136-309) does with one _C.rasterize_gaussians call per cube-map face
+ * (six 32x32 faces per occupied grid cell, thousands of calls).  prm carries the shared inputs (its viewmatrix /
+ * projmatrix / campos are ignored); cameras is a device array of n_views rows of 36 floats
+ * [viewmatrix 16 | projmatrix 16 | campos 3 | pad 1] in the reference's transposed convention.  If labels [P] and
+ * skip_labels [n_views] are given, view v leaves out every Gaussian g with labels[g] == skip_labels[v] (the
+ * reference gathers means3D[pc_grid_indices != grid_id] per cell, baking.py:237-246; the images are the same).
+ * Outputs: out_alpha [n_views,1,H,W]; optional out_color [n_views,3,H,W], out_depth [n_views,1,H,W] (needs
+ * out_color), radii [n_views,P].  Per view they equal ghr_forward_preprocess + ghr_forward_render on that view.
+ * The workspace (ghr_views_workspace_bytes, 256-byte aligned) begins with a ghr_geom_header: after the stream has
+ * drained, num_rendered is the total number of (view, Gaussian, tile) pairs and error is -GHR_ERR_CAPACITY if that
+ * exceeded `capacity` (outputs are then not written: call again with a larger capacity).
+ */
+size_t ghr_views_workspace_bytes(int32_t P, int32_t n_views, int32_t W, int32_t H, int64_t capacity);
+int ghr_forward_views(const ghr_raster_params* prm, int32_t n_views, const float* cameras, const int32_t* labels,
+                      const int32_t* skip_labels, void* workspace, size_t workspace_bytes, int64_t capacity,
+                      float* out_color, float* out_depth, float* out_alpha, int32_t* radii, void* stream);
+
+/*
  * Optimiser side of the training iteration (no native counterpart in the reference, which runs
  * these as chains of ATen kernels).
  *

@@ -8,63 +8,9 @@
 // Roofline: HBM stream.  Algorithmic bytes per Gaussian:
 // 48*P + 28*V (precomputed colour + cov3D) or 244*P + 67*V (SH deg3 + scale/rot);
 // we additionally write the packed 48-B blend record per visible Gaussian.
-#include "ghr_common.cuh"
-#include "ghr_internal.h"
+#include "ghr_project.cuh"
 
 namespace ghr {
-
-struct PreArgs {
-    int P, D, M, W, H;
-    float scale_modifier, tan_fovx, tan_fovy, focal_x, focal_y;
-    int prefiltered;
-    const float *means3D, *shs, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
-    const float *view, *proj, *campos;
-    int32_t* radii;
-    float4* rec;
-    uint32_t* tiles_touched;
-    uint32_t* point_offsets;
-    float* cov3D_out;
-    uint8_t* clamped;
-    uint64_t* scan_status;
-    ghr_geom_header* hdr;
-    int32_t* n_host;
-    int nblocks;
-};
-
-constexpr uint64_t kFlagAgg = 1ull << 32;
-constexpr uint64_t kFlagIncl = 2ull << 32;
-
-// Decoupled look-back over 64-bit {flag,value} words; called by all lanes of warp 0.
-__device__ __forceinline__ uint32_t lookback_exclusive(uint64_t* status, int tile, uint32_t aggregate)
-{
-    const uint32_t lane = lane_id();
-    if (tile == 0) {
-        if (lane == 0) st_relaxed_u64(&status[0], kFlagIncl | aggregate);
-        return 0;
-    }
-    if (lane == 0) st_relaxed_u64(&status[tile], kFlagAgg | aggregate);
-    uint32_t excl = 0;
-    int base = tile - 1;
-    while (true) {
-        const int j = base - (int)lane;
-        const uint64_t s = (j >= 0) ? ld_relaxed_u64(&status[j]) : kFlagIncl;
-        const uint32_t flag = (uint32_t)(s >> 32);
-        const uint32_t invalid = __ballot_sync(0xffffffffu, flag == 0);
-        const uint32_t incl = __ballot_sync(0xffffffffu, flag == 2);
-        if (incl) {
-            const int fi = __ffs(incl) - 1;
-            if (invalid & ((1u << fi) - 1u)) continue;  // a nearer predecessor is not published yet
-            uint32_t v = ((int)lane <= fi) ? (uint32_t)s : 0u;
-            excl += __reduce_add_sync(0xffffffffu, v);
-            break;
-        }
-        if (invalid) continue;
-        excl += __reduce_add_sync(0xffffffffu, (uint32_t)s);
-        base -= 32;
-    }
-    if (lane == 0) st_relaxed_u64(&status[tile], kFlagIncl | (uint64_t)(excl + aggregate));
-    return excl;
-}
 
 __global__ void __launch_bounds__(GHR_BLOCK) preprocess_kernel(const PreArgs a)
 {
@@ -86,84 +32,10 @@ __global__ void __launch_bounds__(GHR_BLOCK) preprocess_kernel(const PreArgs a)
 
     uint32_t tiles = 0;
     if (idx < a.P) {
-        int radius = 0;
-        const float x = a.means3D[3 * idx], y = a.means3D[3 * idx + 1], z = a.means3D[3 * idx + 2];
-        const float pvz = affine_row(x, y, z, V[2], V[6], V[10], V[14]);
-        if (pvz <= 0.2f) {
-            if (a.prefiltered) atomicMax(&a.hdr->error, (uint32_t)(-GHR_ERR_PREFILTER));
-        } else {
-            const float hx = affine_row(x, y, z, Pm[0], Pm[4], Pm[8], Pm[12]);
-            const float hy = affine_row(x, y, z, Pm[1], Pm[5], Pm[9], Pm[13]);
-            const float hw = affine_row(x, y, z, Pm[3], Pm[7], Pm[11], Pm[15]);
-            const float p_w = __frcp_rn(__fadd_rn(hw, 0.0000001f));
-            const float projx = __fmul_rn(hx, p_w), projy = __fmul_rn(hy, p_w);
-            float c3[6];
-            if (a.cov3D_precomp) {
-                const float2* cp = reinterpret_cast<const float2*>(a.cov3D_precomp + 6 * (size_t)idx);
-                const float2 c01 = __ldg(cp), c23 = __ldg(cp + 1), c45 = __ldg(cp + 2);
-                c3[0] = c01.x; c3[1] = c01.y; c3[2] = c23.x; c3[3] = c23.y; c3[4] = c45.x; c3[5] = c45.y;
-            } else {
-                const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
-                cov3d_from_scale_rot(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2],
-                                     a.scale_modifier, q.x, q.y, q.z, q.w, c3);
-                float2* co = reinterpret_cast<float2*>(a.cov3D_out + 6 * (size_t)idx);
-                co[0] = make_float2(c3[0], c3[1]); co[1] = make_float2(c3[2], c3[3]); co[2] = make_float2(c3[4], c3[5]);
-            }
-            Cov2DCtx ctx;
-            cov2d_T(x, y, z, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, V, ctx);
-            float c00, c01, c11;
-            cov2d(ctx, c3, c00, c01, c11);
-            const float det = __fmaf_rn(c00, c11, -__fmul_rn(c01, c01));
-            if (det != 0.0f) {
-                const float det_inv = __frcp_rn(det);
-                const float con0 = __fmul_rn(c11, det_inv), con1 = __fmul_rn(det_inv, -c01),
-                            con2 = __fmul_rn(c00, det_inv);
-                const float mid = __fmul_rn(__fadd_rn(c00, c11), 0.5f);
-                const float sq = __fsqrt_rn(fmaxf(__fmaf_rn(mid, mid, -det), 0.1f));
-                const float lambda1 = __fadd_rn(mid, sq), lambda2 = __fsub_rn(mid, sq);
-                const float my_radius = ceilf(__fmul_rn(__fsqrt_rn(fmaxf(lambda1, lambda2)), 3.0f));
-                const float px = ndc2pix(projx, a.W), py = ndc2pix(projy, a.H);
-                const uint32_t gx = (a.W + GHR_TILE - 1) / GHR_TILE, gy = (a.H + GHR_TILE - 1) / GHR_TILE;
-                uint32_t minx, miny, maxx, maxy;
-                const int ri = __float2int_rz(my_radius);
-                get_rect(px, py, ri, gx, gy, minx, miny, maxx, maxy);
-                const uint32_t cnt = (maxx - minx) * (maxy - miny);
-                if (cnt != 0) {
-                    float rgb[3];
-                    if (a.colors_precomp) {
-                        rgb[0] = a.colors_precomp[3 * idx]; rgb[1] = a.colors_precomp[3 * idx + 1];
-                        rgb[2] = a.colors_precomp[3 * idx + 2];
-                    } else {
-                        float sh[48];
-                        const int nf = min(a.M * 3, 48);
-                        const float* sp = a.shs + (size_t)idx * a.M * 3;
-                        if ((nf & 3) == 0) {
-                            const float4* sp4 = reinterpret_cast<const float4*>(sp);
-#pragma unroll
-                            for (int k = 0; k < 12; k++)
-                                if (4 * k < nf) {
-                                    const float4 v = __ldg(sp4 + k);
-                                    sh[4 * k] = v.x; sh[4 * k + 1] = v.y; sh[4 * k + 2] = v.z; sh[4 * k + 3] = v.w;
-                                }
-                        } else {
-#pragma unroll
-                            for (int k = 0; k < 48; k++)
-                                if (k < nf) sh[k] = __ldg(sp + k);
-                        }
-                        uint32_t cm;
-                        sh_to_rgb(a.D, sh, x - s_cam[32], y - s_cam[33], z - s_cam[34], rgb, cm);
-                        a.clamped[idx] = (uint8_t)cm;
-                    }
-                    radius = ri;
-                    tiles = cnt;
-                    float4* r = a.rec + 3 * (size_t)idx;
-                    r[0] = make_float4(px, py, pvz, __int_as_float(ri));
-                    const float opac = a.opacities[idx];
-                    r[1] = make_float4(con0, con1, con2, opac);
-                    r[2] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(pack_cull_extent(con0, con1, con2, opac)));
-                }
-            }
-        }
+        int radius;
+        bool near_culled;
+        tiles = project_gaussian(a, idx, (size_t)idx, V, Pm, s_cam + 32, radius, near_culled);
+        if (near_culled && a.prefiltered) atomicMax(&a.hdr->error, (uint32_t)(-GHR_ERR_PREFILTER));
         a.radii[idx] = radius;
         a.tiles_touched[idx] = tiles;
     }
@@ -234,6 +106,7 @@ cudaError_t launch_preprocess(const ghr_raster_params& p, int32_t* radii, char* 
     a.hdr = reinterpret_cast<ghr_geom_header*>(geom + L.g_header);
     a.n_host = n_host;
     a.nblocks = (p.P + GHR_BLOCK - 1) / GHR_BLOCK;
+    a.skip_rgb = 0;
     // header + look-back words are contiguous: one memset
     cudaError_t e = cudaMemsetAsync(geom + L.g_header, 0, L.g_rec - L.g_header, s);
     if (e != cudaSuccess) return e;
