@@ -19,6 +19,8 @@
 namespace ghr {
 namespace {
 
+constexpr int kViewsSlots = 4;  // (view, Gaussian) slots per thread of views_preprocess_kernel
+
 struct ViewsArgs {
     PreArgs pre;             // shared Gaussian inputs; view / proj / campos unused
     int n_views;
@@ -38,21 +40,31 @@ __global__ void __launch_bounds__(GHR_BLOCK) views_preprocess_kernel(const Views
     if (tid == 0) s_ticket = atomicAdd(&a.hdr->scan_ticket, 1u);
     __syncthreads();
     const int tile = (int)s_ticket;
-    const int64_t idx = (int64_t)tile * GHR_BLOCK + tid;
+    // kViewsSlots consecutive (view, Gaussian) slots per thread: the look-back chain has one link per CTA, and with one
+    // slot per thread the 2*10^5 links of a bake (5.5*10^7 slots) were the kernel time (ncu: issue active 14 %)
+    const int64_t idx0 = ((int64_t)tile * GHR_BLOCK + tid) * kViewsSlots;
 
+    uint32_t t[kViewsSlots];
     uint32_t tiles = 0;
-    if (idx < va.total) {
-        const int v = (int)(idx / a.P);
-        const int g = (int)(idx - (int64_t)v * a.P);
-        int radius = 0;
-        bool near_culled;
-        const bool skipped = va.labels && va.skip && va.labels[g] == va.skip[v];
-        if (!skipped) {
-            const float* cam = va.cameras + 36 * (size_t)v;
-            tiles = project_gaussian(a, g, (size_t)idx, cam, cam + 16, cam + 32, radius, near_culled);
+#pragma unroll 1
+    for (int k = 0; k < kViewsSlots; k++) {
+        const int64_t idx = idx0 + k;
+        uint32_t n = 0;
+        if (idx < va.total) {
+            const int v = (int)(idx / a.P);
+            const int g = (int)(idx - (int64_t)v * a.P);
+            int radius = 0;
+            bool near_culled;
+            const bool skipped = va.labels && va.skip && va.labels[g] == va.skip[v];
+            if (!skipped) {
+                const float* cam = va.cameras + 36 * (size_t)v;
+                n = project_gaussian(a, g, (size_t)idx, cam, cam + 16, cam + 32, radius, near_culled);
+            }
+            if (a.radii) a.radii[idx] = radius;
+            a.tiles_touched[idx] = n;
         }
-        if (a.radii) a.radii[idx] = radius;
-        a.tiles_touched[idx] = tiles;
+        t[k] = n;
+        tiles += n;
     }
 
     // block-wide inclusive scan + decoupled look-back (same as preprocess_kernel)
@@ -60,8 +72,8 @@ __global__ void __launch_bounds__(GHR_BLOCK) views_preprocess_kernel(const Views
     uint32_t v = tiles;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
-        if (lane >= (uint32_t)o) v += t;
+        const uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= (uint32_t)o) v += u;
     }
     if (lane == 31) s_warp[warp] = v;
     __syncthreads();
@@ -69,8 +81,8 @@ __global__ void __launch_bounds__(GHR_BLOCK) views_preprocess_kernel(const Views
         uint32_t w = lane < 8 ? s_warp[lane] : 0;
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
-            if (lane >= (uint32_t)o) w += t;
+            const uint32_t u = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= (uint32_t)o) w += u;
         }
         const uint32_t block_total = __shfl_sync(0xffffffffu, w, 7);
         const uint32_t prev = __shfl_up_sync(0xffffffffu, w, 1);
@@ -82,7 +94,12 @@ __global__ void __launch_bounds__(GHR_BLOCK) views_preprocess_kernel(const Views
         }
     }
     __syncthreads();
-    if (idx < va.total) a.point_offsets[idx] = s_excl + s_warp[warp] + v;
+    uint32_t run = s_excl + s_warp[warp] + v - tiles;  // exclusive prefix of this thread's first slot
+#pragma unroll
+    for (int k = 0; k < kViewsSlots; k++) {
+        run += t[k];
+        if (idx0 + k < va.total) a.point_offsets[idx0 + k] = run;
+    }
 }
 
 // rasterizer_impl.cu:70-111 duplicateWithKeys over the flattened (view, Gaussian) space
@@ -234,7 +251,7 @@ bool views_layout(int64_t P, int64_t n_views, int W, int H, int64_t capacity, Vi
     const size_t T = (size_t)total;
     size_t o = 0;
     L->header = o; o += align_up(sizeof(ghr_geom_header));
-    L->scan_status = o; o += align_up(sizeof(uint64_t) * ((T + GHR_BLOCK - 1) / GHR_BLOCK + 1));
+    L->scan_status = o; o += align_up(sizeof(uint64_t) * ((T + GHR_BLOCK * kViewsSlots - 1) / (GHR_BLOCK * kViewsSlots) + 1));
     L->rec = o; o += align_up(sizeof(float4) * 3 * T);
     L->tiles_touched = o; o += align_up(sizeof(uint32_t) * T);
     L->point_offsets = o; o += align_up(sizeof(uint32_t) * T);
@@ -323,7 +340,8 @@ int ghr_forward_views(const ghr_raster_params* prm, int32_t n_views, const float
     a.skip_rgb = want_color ? 0 : 1;
     va.n_views = n_views; va.cameras = cameras; va.labels = labels; va.skip = skip_labels;
     va.total = (int64_t)prm->P * n_views;
-    a.nblocks = (int)((va.total + GHR_BLOCK - 1) / GHR_BLOCK);
+    a.nblocks = (int)((va.total + GHR_BLOCK * kViewsSlots - 1) / (GHR_BLOCK * kViewsSlots));
+    const int emit_blocks = (int)((va.total + GHR_BLOCK - 1) / GHR_BLOCK);
     const int tiles_per_view = ((prm->W + GHR_TILE - 1) / GHR_TILE) * ((prm->H + GHR_TILE - 1) / GHR_TILE);
     const int64_t tiles = (int64_t)tiles_per_view * n_views;
 
@@ -340,7 +358,7 @@ int ghr_forward_views(const ghr_raster_params* prm, int32_t n_views, const float
     if (capacity > 0) {
         {
             StageTimer t(GHR_STAGE_EMIT_KEYS, s);
-            views_emit_keys_kernel<<<a.nblocks, GHR_BLOCK, 0, s>>>(va.total, prm->P, prm->W, prm->H, a.tiles_touched, a.rec,
+            views_emit_keys_kernel<<<emit_blocks, GHR_BLOCK, 0, s>>>(va.total, prm->P, prm->W, prm->H, a.tiles_touched, a.rec,
                                                                    a.point_offsets, a.hdr, capacity,
                                                                    reinterpret_cast<uint64_t*>(w + L.keys_a),
                                                                    reinterpret_cast<uint32_t*>(w + L.vals_a));
