@@ -423,6 +423,24 @@ int ghr_densify_stats(int32_t P, const int32_t* radii, const float* dL_dmean2D, 
                       float* xyz_gradient_accum, float* denom, void* stream);
 
 /*
+ * PLY checkpoint rows: the interleaved float rows of the file GaussianModel.save_ply writes and
+ * load_ply reads (scene/gaussian_model.py:309-407), packed / unpacked on the device in one pass.  Row =
+ * x y z | nx ny nz | ar ag ab | roughness | f_dc_0..2 | f_rest_0..3(M-1)-1 (channel-major, :330) | opacity |
+ * scale_0..2 | rot_0..3 = ghr_ply_row_floats(M) = 18 + 3M floats; M = SH coefficients per channel incl. DC (16).
+ * Tensors: xyz [P,3], normal [P,3], albedo [P,3], roughness [P,1], f_dc [P,1,3], f_rest [P,M-1,3], opacity [P,1],
+ * scaling [P,3], rotation [P,4] (the reference's raw parameters); normal / albedo / roughness may be NULL (written
+ * as zeros, skipped on unpack).  unpack: rows may hold row_floats >= 18+3M columns in any order; columns[c] (host
+ * array of 18+3M ints, NULL = identity) is the file column of canonical column c.
+ */
+int ghr_ply_row_floats(int32_t M);
+int ghr_ply_pack_rows(int32_t P, int32_t M, const float* xyz, const float* normal, const float* albedo,
+                      const float* roughness, const float* f_dc, const float* f_rest, const float* opacity,
+                      const float* scaling, const float* rotation, float* rows, void* stream);
+int ghr_ply_unpack_rows(int32_t P, int32_t M, const float* rows, int32_t row_floats, const int32_t* columns, float* xyz,
+                        float* normal, float* albedo, float* roughness, float* f_dc, float* f_rest, float* opacity,
+                        float* scaling, float* rotation, void* stream);
+
+/*
  * Measurement hooks (no reference counterpart; the reference has no profiling
  * facility beyond wall-clock prints, train.py:209).  Process-wide, off by
  * default, the only state the library keeps between calls.

@@ -118,6 +118,9 @@ SIGNATURES = {
     "ghr_adam_step": (C.c_int, [C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int, C.c_void_p]),
     "ghr_densify_stats": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_void_p]),
+    "ghr_ply_row_floats": (C.c_int, [C.c_int32]),
+    "ghr_ply_pack_rows": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 11),
+    "ghr_ply_unpack_rows": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p] + [C.c_void_p] * 10),
     "ghr_launch_count": (C.c_uint64, []),
     "ghr_profile_enable": (C.c_int, [C.c_int]),
     "ghr_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
