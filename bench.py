@@ -21,6 +21,7 @@ oracle/build_ref.sh) on the same GPU, same inputs, same Python-level protocol.
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -64,6 +65,9 @@ def parse():
     ap.add_argument("--batch-views", type=int, default=8,
                     help="views each rank renders per optimisation step (multi-view batch): gradients are accumulated over "
                          "them and summed over the ranks ONCE per step (NCCL).  1 = an all-reduce after every view")
+    ap.add_argument("--lanes", type=int, default=8,
+                    help="graph mode: views of a batch replayed concurrently on this many CUDA streams "
+                         "(MultiLaneRenderStep); reduced to a divisor of --batch-views; 1 = one view at a time")
     ap.add_argument("--sync-free", action="store_true",
                     help="ours: size the binning buffer from the previous step instead of a blocking read")
     return ap.parse_args()
@@ -216,7 +220,7 @@ class OursArm:
     (mygauhuman_b200.diff_gaussian_rasterization), all on libghr.so through the C ABI."""
     name = "ours"
 
-    def __init__(self, wl, dev, sync_free, graph=False):
+    def __init__(self, wl, dev, sync_free, graph=False, lanes=1):
         from mygauhuman_b200 import _lib
         from mygauhuman_b200 import diff_gaussian_rasterization as dgr
         from mygauhuman_b200.lbs import SMPLDeformer
@@ -229,17 +233,28 @@ class OursArm:
         self.bg = wl["bg"].to(dev)
         self.sync_free = sync_free
         self.last_n = None
-        self.graphed, self.use_graph = None, False
+        self.graphed, self.use_graph, self.multi = None, False, None
         if graph:
             from mygauhuman_b200.graphed import GraphedRenderStep
             cam = wl["views"][0]["cam"]
             assert all(v["cam"]["tanfovx"] == cam["tanfovx"] and v["cam"]["tanfovy"] == cam["tanfovy"] for v in wl["views"])
-            self.graphed = GraphedRenderStep(self.deformer, self.leaves, self.big, self.t_vertices, wl["H"], wl["W"],
-                                             cam["tanfovx"], cam["tanfovy"], self.bg, linear_loss, sh_degree=3,
-                                             accumulate=True)
+            self.multi = None
+            if lanes > 1:
+                from mygauhuman_b200.graphed import MultiLaneRenderStep
+                deformers = [self.deformer] + [SMPLDeformer(wl["smpl"], dev) for _ in range(lanes - 1)]
+                self.multi = MultiLaneRenderStep(deformers, self.leaves, self.big, self.t_vertices, wl["H"], wl["W"],
+                                                 cam["tanfovx"], cam["tanfovy"], self.bg, linear_loss, sh_degree=3)
+                self.graphed = self.multi.lanes[0]  # single-view calls (warm-up, verification) go through lane 0
+            else:
+                self.graphed = GraphedRenderStep(self.deformer, self.leaves, self.big, self.t_vertices, wl["H"], wl["W"],
+                                                 cam["tanfovx"], cam["tanfovy"], self.bg, linear_loss, sh_degree=3,
+                                                 accumulate=True)
 
     def capture(self, vecs, targets_dev):
-        self.graphed.capture(vecs, [targets_dev])
+        if self.multi is not None:
+            self.multi.capture(vecs, [targets_dev])
+        else:
+            self.graphed.capture(vecs, [targets_dev])
 
     def step(self, view, vec_dev, targets_dev):
         dgr, L = self.dgr, self.leaves
@@ -461,7 +476,8 @@ def main():
     P, W, H = wl["P"], wl["W"], wl["H"]
     X, tiles = W * H, ((W + 15) // 16) * ((H + 15) // 16)
     if args.impl == "ours":
-        arm = OursArm(wl, dev, args.sync_free, graph=(args.mode == "graph"))
+        lanes = math.gcd(max(1, args.lanes), max(1, args.batch_views)) if args.mode == "graph" else 1
+        arm = OursArm(wl, dev, args.sync_free, graph=(args.mode == "graph"), lanes=lanes)
     else:
         try:
             arm = ReferenceArm(wl, dev)
@@ -526,12 +542,65 @@ def main():
             return float(loss.item())
         return grads if want_grads else None
 
+    def timed_lanes(K, e2e):
+        """K steps of B views, the views of a batch replayed `lanes` at a time on as many streams (MultiLaneRenderStep).
+        One event pair per GROUP of concurrent views on the stream the lanes fork from and join into (L2 flushed before
+        every group, outside the pair); the first group's pair of a batch includes the bucket reset, the last one's the
+        fold of the lanes' buckets and the all-reduce.  e2e: every view's inputs come from pinned host memory (the next
+        group's copies are issued right after this group's replays, on the lanes' copy streams) and every view's loss
+        goes back to pinned memory, consumed one group later -- all inside the timed region."""
+        ml = arm.multi
+        Kl = ml.K
+        groups = K * (B // Kl)
+        starts = [torch.cuda.Event(enable_timing=True) for _ in range(groups)]
+        ends = [torch.cuda.Event(enable_timing=True) for _ in range(groups)]
+        nv = len(views)
+        pending, host_losses = [], 0.0
+        torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
+        if e2e:
+            for j in range(Kl):
+                ml.lanes[j].prefetch(vec_host[j % nv], targets_host)
+        i = 0
+        for gi in range(groups):
+            flush.fill_(gi & 0xFF)  # L2 flush, outside the event pair
+            starts[gi].record()
+            if (gi * Kl) % B == 0:
+                ml.zero_grads()
+            if e2e:
+                nxt = [(i + Kl + j) % nv for j in range(Kl)]
+                ml.run_group([None] * Kl, prefetched=True, next_vecs=[vec_host[k] for k in nxt],
+                             next_loss_inputs=[(targets_host,)] * Kl)
+            else:
+                ml.run_group([vec_dev[(i + j) % nv] for j in range(Kl)])
+            if ((gi + 1) * Kl) % B == 0:
+                ml.reduce_grads()
+            if e2e:
+                new_pending = [ml.lanes[j].loss_to_host() for j in range(Kl)]
+                for slot, ev in pending:  # the previous group's losses: their copies finished long ago
+                    ev.synchronize()
+                    host_losses += float(slot[0])
+                pending = new_pending
+            ends[gi].record()
+            i += Kl
+        for slot, ev in pending:
+            ev.synchronize()
+            host_losses += float(slot[0])
+        torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
+        ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
     def timed(K, e2e):
         """K steps of B views.  Every view has its own event pair (L2 flushed before it, outside the pair); the first
         view's pair includes the bucket reset, the last one's the all-reduce.  e2e: inputs from pinned host memory and
         the view's loss read back.  With the graphed step the e2e loop is pipelined the way a training loop would be:
         the inputs of view i+1 travel on a copy stream while view i computes, and the loss of view i is copied to
         pinned memory asynchronously and consumed one view later -- every copy still happens inside the timed region."""
+        if graph_on() and arm.multi is not None:
+            return timed_lanes(K, e2e)
         n = K * B
         starts = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
         ends = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
@@ -614,9 +683,10 @@ def main():
     eager = None
     if graphed:
         launches = K * B * arm.graphed.kernels_per_replay  # libghr kernels inside the K*B replays
-        if not arm.graphed.check():  # a view overflowed the captured binning capacity: re-captured, measure again
+        checker = arm.multi if arm.multi is not None else arm.graphed
+        if not checker.check():  # a view overflowed the captured binning capacity: re-captured, measure again
             ms_dev, ms_e2e = timed(K, False), timed(K, True)
-            assert arm.graphed.check()
+            assert checker.check()
         reduced = [g.clone() for g in one_step(0, False, want_grads=True)] if world > 1 else None
         arm.use_graph = False  # the same step issued kernel by kernel, for comparison
         if world > 1:  # the in-graph all-reduce must give what the bucketed NCCL all-reduce of the eager step gives
@@ -663,6 +733,7 @@ def main():
         cpu = cpu_baseline(wl, views[0], args.cpu_iters)
 
     views_per_step = world * B  # B views per rank per step
+    n_lanes = arm.multi.K if (args.impl == "ours" and getattr(arm, "multi", None) is not None) else 1
     value = views_per_step * K / (ms_dev * 1e-3)
     e2e_val = views_per_step * K / (ms_e2e * 1e-3)
     h2d = PACK_FLOATS * 4 + 5 * X * 4
@@ -672,7 +743,9 @@ def main():
         "dtype": "f32", "data": "synthetic", "impl": args.impl,
         "config": {"workload": args.workload, "desc": WORKLOADS[args.workload]["desc"], "P": P, "W": W, "H": H,
                    "sh_degree": 3, "views_cycled": len(views) * world, "parallelism": f"view-sharded dp{world}",
-                   "l2": "flushed before every view (256 MiB fill outside the per-view event pair)",
+                   "l2": ("flushed before every view (256 MiB fill outside the per-view event pair)" if n_lanes == 1 else
+                          f"flushed before every group of {n_lanes} concurrent views (256 MiB fill outside the per-group event pair)"),
+                   "lanes": n_lanes,
                    "sync_free": bool(args.sync_free),
                    "mode": (args.mode if args.impl == "ours" else "eager"),
                    "batch_views_per_rank": B,
@@ -682,8 +755,10 @@ def main():
                 "what": "public API step (GraphedRenderStep replay, or in eager mode SMPLDeformer.deform_gaussians -> "
                         "GaussianRasterizer -> loss -> backward); "
                         "camera + SMPL pose + 5 target planes copied from pinned host memory and the loss copied back to "
-                        "pinned memory for every view inside the timed region (graph mode: input copy of view i+1 on a "
-                        "copy stream during view i, loss consumed one view later; eager/reference: blocking loss.item()); "
+                        "pinned memory for every view inside the timed region (graph mode: input copies of the next view(s) on "
+                        "copy streams during the current one(s), losses consumed one view / group later; with lanes > 1 "
+                        "the views of a batch are replayed `lanes` at a time on as many streams (MultiLaneRenderStep); "
+                        "eager/reference: blocking loss.item()); "
                         "Gaussian parameters stay resident (model state)"},
         "gpu_launches": launches, "clocks": clocks,
     }

@@ -338,7 +338,8 @@ typedef struct ghr_deform_params {
     float* dL_dopacity_logits;   /* backward: [P] written when opacity_logits is given                              */
     int32_t accumulate_grads;    /* backward: 1 = the per-Gaussian outputs (dL_dxyz, dL_dnormals, dL_dlbs_offsets,
                                     dL_dscales, dL_drotations, dL_dshs, dL_dopacity_logits) are ADDED to the buffers
-                                    (gradient accumulation over a batch of views) instead of stored               */
+                                    (gradient accumulation over a batch of views) instead of stored; 2 = added with
+                                    atomics (views of the batch running concurrently on several streams)          */
 } ghr_deform_params;
 
 int ghr_lbs_deform_forward(const ghr_deform_params* prm, float* smpl_pts /*[P,3]|NULL*/, float* world_pts /*[P,3]*/,

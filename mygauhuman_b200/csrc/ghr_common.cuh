@@ -185,7 +185,7 @@ __device__ __forceinline__ void sh_to_rgb(int deg, const float* __restrict__ sh,
 // backward.cu:20-139
 __device__ __forceinline__ void sh_backward(int deg, int M, const float* __restrict__ sh, float dox, float doy,
                                             float doz, uint32_t clamp_mask, const float* dL_dcolor, float* dm,
-                                            float* __restrict__ dL_dsh, bool accumulate = false)
+                                            float* __restrict__ dL_dsh, int accumulate = 0)
 {
     const float len = sqrtf(dox * dox + doy * doy + doz * doz);
     const float x = dox / len, y = doy / len, z = doz / len;
@@ -215,7 +215,10 @@ __device__ __forceinline__ void sh_backward(int deg, int M, const float* __restr
     const int ncoef = (deg + 1) * (deg + 1);
     for (int k = 0; k < M; k++) {
         const float cf = k < ncoef && k < 16 ? coef[k] : 0.0f;
-        if (accumulate) {
+        if (accumulate == 2) {  // several streams add into the same buffer (multi-lane batches): L2 reductions
+            atomicAdd(dL_dsh + 3 * k, cf * dRGB[0]); atomicAdd(dL_dsh + 3 * k + 1, cf * dRGB[1]);
+            atomicAdd(dL_dsh + 3 * k + 2, cf * dRGB[2]);
+        } else if (accumulate) {
             dL_dsh[3 * k] += cf * dRGB[0]; dL_dsh[3 * k + 1] += cf * dRGB[1]; dL_dsh[3 * k + 2] += cf * dRGB[2];
         } else {
             dL_dsh[3 * k] = cf * dRGB[0]; dL_dsh[3 * k + 1] = cf * dRGB[1]; dL_dsh[3 * k + 2] = cf * dRGB[2];

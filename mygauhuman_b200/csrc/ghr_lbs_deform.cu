@@ -269,8 +269,12 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
 #pragma unroll
     for (int j = 0; j < kJ; j++) bw_keep[j] = 0.0f;
     // per-Gaussian gradients are stored, or added to what the buffers hold (multi-view gradient accumulation)
-    const bool acc = p.accumulate_grads != 0;
-    auto put = [acc](float* dst, float v) { *dst = acc ? *dst + v : v; };
+    // (2 = with atomics: concurrent views on several streams add into one buffer, MultiLaneRenderStep)
+    const int acc = p.accumulate_grads;
+    auto put = [acc](float* dst, float v) {
+        if (acc == 2) atomicAdd(dst, v);
+        else *dst = acc ? *dst + v : v;
+    };
     if (active) {
         const int vid = p.vert_ids[idx];
         DeformState d;
@@ -351,8 +355,12 @@ __global__ void __launch_bounds__(128) lbs_deform_backward_kernel(const ghr_defo
             if (g.d_rot) {
                 float4* o4 = reinterpret_cast<float4*>(g.d_rot) + idx;
                 float4 v4 = make_float4(dq[0], dq[1], dq[2], dq[3]);
-                if (acc) { const float4 old = *o4; v4.x += old.x; v4.y += old.y; v4.z += old.z; v4.w += old.w; }
-                *o4 = v4;
+                if (acc == 2) {
+                    atomicAdd(&o4->x, v4.x); atomicAdd(&o4->y, v4.y); atomicAdd(&o4->z, v4.z); atomicAdd(&o4->w, v4.w);
+                } else {
+                    if (acc) { const float4 old = *o4; v4.x += old.x; v4.y += old.y; v4.z += old.z; v4.w += old.w; }
+                    *o4 = v4;
+                }
             }
         }
 

@@ -53,12 +53,14 @@ class GraphedRenderStep:
 
     def __init__(self, deformer, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx, tanfovy, bg,
                  loss_fn, n_loss_inputs=1, sh_degree=3, scaling_modifier=1.0, capacity_hint=None, use_graph=True,
-                 all_reduce=None, group=None, accumulate=False):
+                 all_reduce=None, group=None, accumulate=False, shared_flat=None):
         """all_reduce: None (single GPU), "after" (one NCCL sum all-reduce of the flat gradient bucket issued right
         after the replay) or "captured" (the all-reduce is part of the graph: every rank replays in lockstep).
         accumulate=True: multi-view batches.  Every call ADDS its gradients to the flat bucket (leaves[k].grad are
         views of it); zero_grads() starts a batch and reduce_grads() sums the bucket over the ranks once per batch
-        (all_reduce must then be None: the collective is per batch, not per view)."""
+        (all_reduce must then be None: the collective is per batch, not per view).
+        shared_flat (accumulate mode): another step's flat bucket to add into, with atomics -- the lanes of a
+        MultiLaneRenderStep run concurrently on several streams and sum into one bucket."""
         self.deformer, self.leaves = deformer, leaves
         self.big, self.t_vertices = big_pose_params, t_vertices
         self.H, self.W, self.tanfovx, self.tanfovy = int(image_height), int(image_width), float(tanfovx), float(tanfovy)
@@ -78,12 +80,14 @@ class GraphedRenderStep:
             # gradients of all leaves in one bucket (59 floats per Gaussian at SH degree 3): one collective per step,
             # and leaves[k].grad are views of it, so nothing is copied back after the reduction
             pad = lambda n: (n + 3) // 4 * 4  # every view starts on a 16-byte boundary
-            self.flat = torch.zeros(sum(pad(t.numel()) for t in leaves.values()), device=dev)
+            n_flat = sum(pad(t.numel()) for t in leaves.values())
+            assert shared_flat is None or (accumulate and shared_flat.numel() == n_flat)
+            self.flat = torch.zeros(n_flat, device=dev) if shared_flat is None else shared_flat
             self.flat_views, o = {}, 0
             for k, t in leaves.items():
                 self.flat_views[k] = self.flat[o:o + t.numel()].view_as(t)
                 o += pad(t.numel())
-        self._sink = None
+        self._sink, self._sink_atomic = None, False
         if accumulate:
             # the deform backward kernel adds straight into the bucket: no separate accumulation pass
             names = {"xyz": "xyz", "normals": "normals", "log_scale": "scaling", "rotation": "rotation",
@@ -123,11 +127,11 @@ class GraphedRenderStep:
             torch.maximum(self.n_seen, geom[:4].view(torch.int32), out=self.n_seen)
         loss = self.loss_fn(color, depth, alpha, *loss_inputs)
         if self._sink is not None:
-            self.deformer.grad_sink = self._sink
+            self.deformer.grad_sink, self.deformer.grad_sink_atomic = self._sink, self._sink_atomic
             try:
                 loss.backward()
             finally:
-                self.deformer.grad_sink = None
+                self.deformer.grad_sink, self.deformer.grad_sink_atomic = None, False
             return loss, dict(color=color, depth=depth, alpha=alpha, radii=radii, means2D=means2D)
         for t in L.values():
             t.grad = None
@@ -267,6 +271,103 @@ class GraphedRenderStep:
         n = self._max_over_ranks(int(self.n_seen.item()))  # every rank re-captures together, with the same capacity
         if n > self.capacity:
             self._capture(int(n * 1.5) + 4096)
+            return False
+        return True
+
+
+class MultiLaneRenderStep:
+    """K graphed lanes over the SAME leaves: the views of a multi-view batch run concurrently on K CUDA streams.
+
+    One view of the ZJU shape is ~20 kernels that are each bound by latency or by the instruction stream of a few heavy
+    tiles, not by the machine: one replay keeps a fraction of the 148 SMs busy.  Views of a batch are
+    independent until their parameter gradients are summed, so lane k owns a GraphedRenderStep (own deformer scratch,
+    own static inputs) and a stream, and all lanes add into ONE flat gradient bucket with fp32 atomics
+    (``accumulate_grads = 2`` of ghr_lbs_deform_backward: a bucket per lane cost K-1 extra clears and adds of 11.8 MB
+    per batch, 11 % of an 8-view batch).  ``run_group`` replays up to K views at once; ``reduce_grads`` is the one
+    NCCL all-reduce of the batch.  Measured on B200 (ZJU shape, tools/overlap_probe.py): 1 / 2 / 3 / 4 lanes =
+    2 337 / 3 543 / 3 899 / 4 105 views/s.  Numerics are those of the single-lane step; only the order in which the
+    views are ADDED into the batch gradient changes.
+    """
+
+    def __init__(self, deformers, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx, tanfovy, bg,
+                 loss_fn, n_loss_inputs=1, sh_degree=3, scaling_modifier=1.0, use_graph=True, group=None):
+        """deformers: one SMPLDeformer per lane (they hold per-call scratch the lanes must not share)."""
+        assert len(deformers) >= 1
+        self.leaves, self.group = leaves, group
+        self.lanes = []
+        for d in deformers:
+            self.lanes.append(GraphedRenderStep(d, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx,
+                                                tanfovy, bg, loss_fn, n_loss_inputs=n_loss_inputs, sh_degree=sh_degree,
+                                                scaling_modifier=scaling_modifier, use_graph=use_graph, group=group,
+                                                accumulate=True,
+                                                shared_flat=self.lanes[0].flat if self.lanes else None))
+        for lane in self.lanes:
+            lane._sink_atomic = len(self.lanes) > 1
+        dev = deformers[0].device
+        self.streams = [torch.cuda.Stream(device=dev) for _ in self.lanes]
+        self._fork = torch.cuda.Event()
+        self._joins = [torch.cuda.Event() for _ in self.lanes]
+        self._alias_grads()
+
+    K = property(lambda self: len(self.lanes))
+    flat = property(lambda self: self.lanes[0].flat)
+    flat_views = property(lambda self: self.lanes[0].flat_views)
+    kernels_per_replay = property(lambda self: self.lanes[0].kernels_per_replay)
+    capacity = property(lambda self: self.lanes[0].capacity)
+
+    def _alias_grads(self):
+        for k, t in self.leaves.items():
+            t.grad = self.lanes[0].flat_views[k]
+
+    def capture(self, sample_vecs, loss_inputs):
+        """Lane 0 sizes the binning capacity from the sample views; every lane is captured with it."""
+        self.lanes[0].capture(sample_vecs, loss_inputs)
+        for lane in self.lanes[1:]:
+            lane.loss_inputs = [t.clone() for t in loss_inputs]
+            lane._capture(self.lanes[0].capacity)
+        self._alias_grads()
+
+    def zero_grads(self):
+        """Start a batch (on the current stream; the lanes fork from it)."""
+        self.lanes[0].flat.zero_()
+
+    def run_group(self, vecs, loss_inputs=None, prefetched=False, next_vecs=None, next_loss_inputs=None):
+        """Replay len(vecs) <= K views concurrently, view j on lane j.  loss_inputs: one tuple per view (None: keep the
+        lanes' resident loss inputs).  prefetched=True: run what each lane's last prefetch() staged instead of `vecs`
+        (only its length is used); next_vecs / next_loss_inputs: what to prefetch per lane right after issuing (the host
+        copies of the next group then overlap this group's kernels).  Returns the lanes' loss tensors (static buffers)."""
+        cur = torch.cuda.current_stream()
+        self._fork.record(cur)
+        losses = []
+        for j in range(len(vecs)):
+            lane, s = self.lanes[j], self.streams[j]
+            s.wait_event(self._fork)
+            with torch.cuda.stream(s):
+                if prefetched:
+                    losses.append(lane.run_prefetched())
+                else:
+                    li = lane.loss_inputs if loss_inputs is None else loss_inputs[j]
+                    losses.append(lane(vecs[j], *li))
+                self._joins[j].record(s)
+            if next_vecs is not None and j < len(next_vecs):
+                lane.prefetch(next_vecs[j], *(next_loss_inputs[j] if next_loss_inputs is not None else ()))
+        for j in range(len(vecs)):
+            cur.wait_event(self._joins[j])
+        return losses
+
+    def reduce_grads(self):
+        """End of a batch: one sum all-reduce of the shared bucket over the ranks (call after run_group has joined)."""
+        self.lanes[0]._reduce()
+        return self.lanes[0].flat_views
+
+    def check(self):
+        """Synchronises; re-captures every lane with a larger capacity if any replay overflowed (returns False then)."""
+        n = max(int(lane.n_seen.item()) for lane in self.lanes)
+        n = self.lanes[0]._max_over_ranks(n)
+        if n > self.lanes[0].capacity:
+            for lane in self.lanes:
+                lane._capture(int(n * 1.5) + 4096)
+            self._alias_grads()
             return False
         return True
 

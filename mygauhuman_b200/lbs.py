@@ -79,6 +79,7 @@ class SMPLDeformer:
         # "xyz", "normals", "scaling", "rotation", "features", "opacity_logit".  When set, the backward kernels ADD the
         # per-Gaussian gradients of those inputs into the given tensors and autograd receives None for them.
         self.grad_sink = None
+        self.grad_sink_atomic = False  # True: add with atomics (several streams share the sink, MultiLaneRenderStep)
 
     # ---- pose stage --------------------------------------------------------
     def pose_buffer(self, params, correct_Rs=None):
@@ -305,7 +306,7 @@ class _DeformFn(torch.autograd.Function):
             assert not has_lw, "grad_sink does not cover lbs_weights"
             for t in (d_xyz, d_n, d_sc, d_rot, d_sh):
                 assert t is None or (t.is_contiguous() and t.dtype == torch.float32 and t.data_ptr() % 16 == 0)
-            p.accumulate_grads = 1
+            p.accumulate_grads = 2 if self.grad_sink_atomic else 1
             if ctx.ol is not None and P:
                 d_ol = sink["opacity_logit"]
                 p.dL_dopacity_logits = d_ol.data_ptr()

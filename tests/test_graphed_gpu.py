@@ -144,3 +144,75 @@ def test_prefetch_pipeline_gives_the_same_results(smpl_model):
     got.append(float(pending[0][0]))
     for a, b in zip(got, want):
         assert abs(a - b) <= 1e-5 * max(1.0, abs(b))
+
+
+def test_multi_lane_batches_match_the_single_lane_sum(smpl_model):
+    """MultiLaneRenderStep: the views of a batch replayed concurrently on K streams (own bucket per lane, folded at the
+    end of the batch) give the per-view losses and the batch gradient of the one-view-at-a-time path, with resident
+    inputs and through the prefetch pipeline, and report capacity overflows."""
+    from mygauhuman_b200.graphed import MultiLaneRenderStep
+    from mygauhuman_b200.lbs import SMPLDeformer
+    step, leaves, vecs, targets = _setup(smpl_model, [3.0, 2.7, 3.3, 2.9, 3.1, 2.8])
+    want, want_loss = None, []
+    for vec in vecs:
+        loss, grads, _ = _eager_reference(step, leaves, vec, targets)
+        want_loss.append(loss)
+        want = grads if want is None else {k: want[k] + grads[k] for k in want}
+    dev = torch.device("cuda")
+    K = 3
+    ml = MultiLaneRenderStep([SMPLDeformer(smpl_model, dev) for _ in range(K)], leaves, step.big, step.t_vertices, H, W,
+                             step.tanfovx, step.tanfovy, step.bg, _loss)
+    ml.capture(vecs, [targets])
+    assert ml.K == K and ml.kernels_per_replay >= 10
+    # resident inputs: two batches of six views, three at a time
+    for _ in range(2):
+        ml.zero_grads()
+        got_loss = []
+        for g0 in range(0, len(vecs), K):
+            losses = ml.run_group(vecs[g0:g0 + K])
+            torch.cuda.synchronize()
+            got_loss += [float(l) for l in losses]
+        got = ml.reduce_grads()
+        torch.cuda.synchronize()
+        for a, b in zip(got_loss, want_loss):
+            assert abs(a - b) <= 1e-5 * max(1.0, abs(b))
+        for k in want:
+            assert leaves[k].grad.data_ptr() == got[k].data_ptr()
+            assert rel_err(got[k], want[k]) < 3e-5, k
+    # a ragged last group (2 of 3 lanes) and host inputs through the prefetch pipeline
+    host_vecs = [v.cpu().pin_memory() for v in vecs]
+    host_targets = targets.cpu().pin_memory()
+    ml.zero_grads()
+    order = [0, 1, 2, 3, 4]
+    for j in range(K):
+        ml.lanes[j].prefetch(host_vecs[order[j]], host_targets)
+    nxt = [host_vecs[order[3]], host_vecs[order[4]]]
+    l1 = [float(x) for x in _sync(ml.run_group([None] * 3, prefetched=True, next_vecs=nxt,
+                                                next_loss_inputs=[(host_targets,)] * 2))]
+    l2 = [float(x) for x in _sync(ml.run_group([None] * 2, prefetched=True))]
+    got = ml.reduce_grads()
+    torch.cuda.synchronize()
+    for a, i in zip(l1 + l2, order):
+        assert abs(a - want_loss[i]) <= 1e-5 * max(1.0, abs(want_loss[i]))
+    part = None
+    for i in order:
+        _, grads, _ = _eager_reference(step, leaves, vecs[i], targets)
+        part = grads if part is None else {k: part[k] + grads[k] for k in part}
+    ml._alias_grads()  # (the eager reference above re-pointed leaves[k].grad)
+    for k in part:
+        assert rel_err(got[k], part[k]) < 3e-5, k
+    assert ml.check()
+    # overflow on any lane is seen and every lane is re-captured
+    for lane in ml.lanes:
+        lane._capture(512)
+    ml.run_group(vecs[:K])
+    assert not ml.check()
+    assert all(lane.capacity > 512 for lane in ml.lanes)
+    ml.zero_grads()
+    ml.run_group(vecs[:K])
+    assert ml.check()
+
+
+def _sync(x):
+    torch.cuda.synchronize()
+    return x
