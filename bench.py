@@ -458,11 +458,29 @@ def run_reference_cpu(args, world, rank):
             "config": {"workload": args.workload, "desc": WORKLOADS[args.workload]["desc"]}, "cpu_baseline": res,
             "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process's real stdout; everything else any library prints goes to stderr."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
+    global _REAL_STDOUT
     args = parse()
+    # NCCL (version banner), nvidia-smi children and the like write to fd 1 behind Python's back: point fd 1 at stderr for
+    # the whole run and keep the original for the result line
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     world, rank, local = init_dist(args)
     if args.impl == "reference-cpu":
         run_reference_cpu(args, world, rank)
@@ -483,7 +501,7 @@ def main():
             arm = ReferenceArm(wl, dev)
         except (FileNotFoundError, OSError) as e:
             if rank == 0:
-                print(json.dumps({"impl": "reference", "unavailable": f"oracle/_ref not built: {e}"}), flush=True)
+                emit({"impl": "reference", "unavailable": f"oracle/_ref not built: {e}"})
             return
     views = wl["views"]
     vec_host = [view_pack(v) for v in views]
@@ -778,7 +796,7 @@ def main():
                                 "sample": "the reference's own implementation of this path is CUDA: unmodified "
                                           "rasteriser sources built for sm_100 (oracle/_ref), timed on the same GPU; "
                                           "its CPU port is `--impl reference-cpu`"}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 if __name__ == "__main__":
