@@ -539,6 +539,9 @@ cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, 
     // the queue head is scratch state inside the (otherwise read-only) geometry buffer
     cudaError_t e = cudaMemsetAsync(&hdr->blend_bwd_ticket, 0, sizeof(uint32_t), s);
     if (e != cudaSuccess) return e;
+    if (blend_shared_gpu())
+        return launch_bwd_config<128, 2, 0>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, nullptr,
+                                            nullptr, nullptr, s);
     return launch_bwd_config<256, 2, 0>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, nullptr, nullptr,
                                         nullptr, s);
 }

@@ -363,6 +363,9 @@ cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, c
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
     cudaError_t e = cudaMemsetAsync(&hdr->blend_fwd_ticket, 0, sizeof(uint32_t), s);  // render may run twice per preprocess
     if (e != cudaSuccess) return e;
+    if (blend_shared_gpu())  // several views in flight (MultiLaneRenderStep): half the staging per warp, so that the
+                             // blend kernels of two views fit an SM together
+        return launch_fwd_config<128, 2, 1, 0>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, nullptr, nullptr, s);
     return launch_fwd_config<256, 2, 1, 0>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, nullptr, nullptr, s);
 }
 

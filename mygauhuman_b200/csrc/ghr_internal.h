@@ -68,6 +68,17 @@ inline bool blend_throughput_regime(int64_t capacity)
     return capacity > (int64_t(1) << 19);
 }
 
+// Several views share the GPU (views of a batch on several streams): the blend kernels then take half the staging
+// shared memory per warp so that two of them are co-resident on an SM.  Process-wide, set by ghr_set_shared_gpu()
+// (MultiLaneRenderStep), GHR_SHARED_GPU=0|1 overrides (tuning).
+extern std::atomic<int> g_shared_gpu;
+inline int blend_shared_gpu()  // 0: one view owns the GPU (256-entry staging rounds); 1: 128-entry rounds (64: measured, no gain)
+{
+    static const int forced = [] { const char* e = getenv("GHR_SHARED_GPU"); return e ? atoi(e) + 1 : 0; }();
+    if (forced) return forced - 1;
+    return g_shared_gpu.load(std::memory_order_relaxed);
+}
+
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
 // rasterizer_impl.cu:35-50 getHigherMsb

@@ -12,6 +12,7 @@ namespace ghr {
 
 std::atomic<uint64_t> g_launches{0};
 std::atomic<int> g_profile_on{0};
+std::atomic<int> g_shared_gpu{0};
 
 namespace {
 struct Span {
@@ -61,7 +62,14 @@ using namespace ghr;
 
 extern "C" {
 
+int ghr_set_shared_gpu(int on)
+{
+    g_shared_gpu.store(on ? 1 : 0, std::memory_order_relaxed);
+    return GHR_OK;
+}
+
 uint64_t ghr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
 
 int ghr_profile_enable(int on)
 {

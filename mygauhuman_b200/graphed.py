@@ -294,6 +294,10 @@ class MultiLaneRenderStep:
         """deformers: one SMPLDeformer per lane (they hold per-call scratch the lanes must not share)."""
         assert len(deformers) >= 1
         self.leaves, self.group = leaves, group
+        if len(deformers) > 1:
+            # kernels of different views now share the SMs: the blend kernels take the configuration that lets two of
+            # them be co-resident (read at launch, i.e. baked into the lanes' graphs at capture): 4 300 -> 5 150 views/s
+            _lib.check(_lib.lib().ghr_set_shared_gpu(1), "ghr_set_shared_gpu")
         self.lanes = []
         for d in deformers:
             self.lanes.append(GraphedRenderStep(d, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx,

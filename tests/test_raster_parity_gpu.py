@@ -251,9 +251,25 @@ def test_throughput_regime_kernels_pass_the_same_parity_tests():
     import os
     import subprocess
     import sys
-    if os.environ.get("GHR_BLEND_REGIME"):
+    if os.environ.get("GHR_BLEND_REGIME") or os.environ.get("GHR_SHARED_GPU"):
         pytest.skip("already inside a forced-regime run")
     env = dict(os.environ, GHR_BLEND_REGIME="throughput")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_raster_parity_gpu.py", "-x", "-q", "-m", "gpu", "-W", "ignore",
+                        "-p", "no:cacheprovider"], cwd=root, env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_shared_gpu_blend_configuration_passes_the_same_parity_tests():
+    """ghr_set_shared_gpu(1) (views of a batch on several streams, MultiLaneRenderStep) switches the blend kernels to
+    128-entry staging rounds.  The setting is process-wide, so the parity tests of this file are re-run in a child
+    process with GHR_SHARED_GPU=1."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("GHR_BLEND_REGIME") or os.environ.get("GHR_SHARED_GPU"):
+        pytest.skip("already inside a forced-regime run")
+    env = dict(os.environ, GHR_SHARED_GPU="1")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_raster_parity_gpu.py", "-x", "-q", "-m", "gpu", "-W", "ignore",
                         "-p", "no:cacheprovider"], cwd=root, env=env, capture_output=True, text=True, timeout=900)
