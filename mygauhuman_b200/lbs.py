@@ -79,6 +79,7 @@ class SMPLDeformer:
         # "xyz", "normals", "scaling", "rotation", "features", "opacity_logit".  When set, the backward kernels ADD the
         # per-Gaussian gradients of those inputs into the given tensors and autograd receives None for them.
         self.grad_sink = None
+        self.vert_ids_override = None  # int32 [P]: nearest-vertex ids computed by the caller (once per multi-view batch)
         self.grad_sink_atomic = False  # True: add with atomics (several streams share the sink, MultiLaneRenderStep)
 
     # ---- pose stage --------------------------------------------------------
@@ -225,17 +226,26 @@ class _DeformFn(torch.autograd.Function):
         # blend-shape offsets (depend on the pose only); both are short, latency-bound kernels.  Fork/join through
         # stream waits, so the overlap is kept when the step is captured into a CUDA graph.  Every buffer the side
         # stream touches is allocated on the caller's stream beforehand.
-        vid = torch.empty(P, dtype=torch.int32, device=dev)
+        vid = self.vert_ids_override
+        have_vid = vid is not None
+        if have_vid:
+            assert vid.dtype == torch.int32 and vid.numel() == P and vid.is_contiguous() and vid.device == xyz_c.device
+        else:
+            vid = torch.empty(P, dtype=torch.int32, device=dev)
         tv = _f32c(t_vertices.detach())
         cur = torch.cuda.current_stream(dev)
-        side = self._side_stream
-        if P and side is not None:
+        side = self._side_stream if not have_vid else None
+        if have_vid:
+            pass
+        elif P and side is not None:
             side.wait_stream(cur)
             with torch.cuda.stream(side):
                 self.nearest_vertex(tv, xyz_c, out=vid)
         pose_tgt = self.pose_buffer(params, correct_Rs)
         off = self.vertex_offsets(pose_big, pose_tgt, params["shapes"])
-        if P and side is not None:
+        if have_vid:
+            pass
+        elif P and side is not None:
             cur.wait_stream(side)
         elif P:
             self.nearest_vertex(tv, xyz_c, out=vid)
