@@ -216,3 +216,59 @@ def test_multi_lane_batches_match_the_single_lane_sum(smpl_model):
 def _sync(x):
     torch.cuda.synchronize()
     return x
+
+
+def test_training_iterations_multi_lane_with_fused_adam_track_torch_adam(smpl_model):
+    """The pieces compose into the reference's iteration (train.py:395-419 over a batch of views): multi-lane batch ->
+    densification statistics -> FusedAdam.step(zero_grads=True), against one view at a time + torch.optim.Adam.  Adam's
+    first steps are ~lr * sign(g), so an element whose gradient is at the fp32-atomics noise floor may move the other
+    way: the comparison is on the bulk (99 % of the elements within 1e-3 of the total update) and on the loss."""
+    from mygauhuman_b200.graphed import GraphedRenderStep, MultiLaneRenderStep
+    from mygauhuman_b200.lbs import SMPLDeformer
+    from mygauhuman_b200.optim import FusedAdam, add_densification_stats
+    step, leaves_a, vecs, targets = _setup(smpl_model, [3.0, 2.7, 3.3, 2.9])
+    dev = torch.device("cuda")
+    leaves_b = {k: v.detach().clone().requires_grad_(True) for k, v in leaves_a.items()}
+    lrs = dict(xyz=1.6e-4, features=2.5e-3, opacity_logit=5e-2, log_scale=5e-3, rotation=1e-3, normals=2e-4)
+    groups = lambda L: [{"params": [L[k]], "lr": lrs[k], "name": k} for k in lrs]
+    ml = MultiLaneRenderStep([SMPLDeformer(smpl_model, dev) for _ in range(2)], leaves_a, step.big, step.t_vertices, H, W,
+                             step.tanfovx, step.tanfovy, step.bg, _loss)
+    ml.capture(vecs, [targets])
+    one = GraphedRenderStep(SMPLDeformer(smpl_model, dev), leaves_b, step.big, step.t_vertices, H, W, step.tanfovx,
+                            step.tanfovy, step.bg, _loss, accumulate=True)
+    one.capture(vecs, [targets])
+    opt_a = FusedAdam(groups(leaves_a), lr=0.0, eps=1e-15)
+    opt_b = torch.optim.Adam(groups(leaves_b), lr=0.0, eps=1e-15)
+    P_ = leaves_a["xyz"].shape[0]
+    max_r, acc, den = torch.zeros(P_, device=dev), torch.zeros(P_, 1, device=dev), torch.zeros(P_, 1, device=dev)
+    first = last = None
+    n_steps = 3
+    for it in range(n_steps):
+        ml.zero_grads()
+        losses = []
+        for g0 in range(0, len(vecs), 2):
+            ls = ml.run_group(vecs[g0:g0 + 2])
+            torch.cuda.synchronize()
+            losses += [float(l) for l in ls]
+            for lane in ml.lanes[:2]:  # statistics of the views just rendered
+                add_densification_stats(lane.out["radii"], lane.out["means2D"].grad, max_r, acc, den)
+        ml.reduce_grads()
+        assert all(leaves_a[k].grad.data_ptr() == ml.flat_views[k].data_ptr() for k in lrs)
+        opt_a.step(zero_grads=True)
+        assert float(ml.flat.abs().max()) == 0.0  # cleared in the same launch
+        one.zero_grads()
+        for v in vecs:
+            one(v, targets)
+        one.reduce_grads()
+        for k in lrs:
+            leaves_b[k].grad = one.flat_views[k]
+        opt_b.step()
+        first = first if first is not None else sum(losses)
+        last = sum(losses)
+    assert last < first  # the linear loss goes down
+    assert float(den.max()) == n_steps * len(vecs) and float(max_r.max()) > 0 and float(acc.max()) > 0
+    for k in lrs:
+        d = (leaves_a[k].detach() - leaves_b[k].detach()).abs().flatten()
+        ok = (d <= 1e-3 * n_steps * lrs[k]).float().mean().item()
+        assert ok >= 0.99, (k, ok)
+        assert float(d.max()) <= 2.0 * n_steps * lrs[k] * 1.001, k

@@ -7,8 +7,6 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench
 
-args = bench.parse() if False else None
-
 
 class A:  # bench args
     workload, views, batch_views, mode, sync_free = "zju_512", 64, 8, "graph", False
