@@ -371,6 +371,30 @@ int ghr_smpl_lbs_vertices(const ghr_lbs_model* model, const float* v_template, c
                           float* verts /*[V,3]*/, float* T_out /*[V,12]|NULL*/, void* stream);
 
 /*
+ * Stand-alone forms of two operators that ghr_lbs_deform_forward/_backward also compute fused,
+ * for callers that use them on their own.
+ *  - covariance: GaussianModel.get_covariance(scaling_modifier, transforms) (scene/gaussian_model.py:35-42,208-209;
+ *    utils/general_utils.py:60-117): q^ = q/|q|, L = R(q^) diag(mod*s), Sigma = L L^T, Sigma' = T Sigma T^T, packed
+ *    [xx,xy,xz,yy,yz,zz].  scaling [P,3] is the ACTIVATED scaling (get_scaling), rotation [P,4] the raw quaternion,
+ *    transforms [P,3,3] or NULL (identity).  backward writes dL_dscaling [P,3], dL_drotation [P,4] and, if non-NULL,
+ *    dL_dtransforms [P,3,3].
+ *  - sh_colors: clamp_min(eval_sh(deg, shs, (means3D - campos)/|.|) + 0.5, 0) (gaussian_renderer/__init__.py:124-125,
+ *    191-195; utils/sh_utils.py:135-190).  shs [P,M,3] (get_features layout), clamped [P] uint8 (bit c = channel c was
+ *    clamped; forward output, backward input, may be NULL).  backward writes dL_dshs [P,M,3] and, if non-NULL,
+ *    dL_dmeans3D [P,3] (through the view direction).
+ */
+int ghr_covariance_forward(int32_t P, const float* scaling, const float* rotation, float scaling_modifier,
+                           const float* transforms, float* cov3D, void* stream);
+int ghr_covariance_backward(int32_t P, const float* scaling, const float* rotation, float scaling_modifier,
+                            const float* transforms, const float* dL_dcov3D, float* dL_dscaling, float* dL_drotation,
+                            float* dL_dtransforms, void* stream);
+int ghr_sh_colors_forward(int32_t P, int32_t sh_degree, int32_t M, const float* shs, const float* means3D,
+                          const float* campos, float* colors, uint8_t* clamped, void* stream);
+int ghr_sh_colors_backward(int32_t P, int32_t sh_degree, int32_t M, const float* shs, const float* means3D,
+                           const float* campos, const uint8_t* clamped, const float* dL_dcolors, float* dL_dshs,
+                           float* dL_dmeans3D, void* stream);
+
+/*
  * View-batched forward rasterisation: n_views small views of the SAME Gaussians in one set of
  * launches -- what baking.py::bake_set (:136-309) does with one _C.rasterize_gaussians call per cube-map face
  * (six 32x32 faces per occupied grid cell, thousands of calls).  prm carries the shared inputs (its viewmatrix /

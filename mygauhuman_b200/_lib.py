@@ -112,6 +112,10 @@ SIGNATURES = {
     "ghr_lbs_deform_backward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 15),
     "ghr_lbs_pose_backward": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
     "ghr_smpl_lbs_vertices": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
+    "ghr_covariance_forward": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ghr_covariance_backward": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_float] + [C.c_void_p] * 6),
+    "ghr_sh_colors_forward": (C.c_int, [C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 6),
+    "ghr_sh_colors_backward": (C.c_int, [C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 8),
     "ghr_views_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64]),
     "ghr_forward_views": (C.c_int, [C.POINTER(RasterParams), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_size_t, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -15,6 +15,7 @@
 //   write world 12 + transform 36 + normal 12 + cov 24 + colour 12 + clamp 1
 //   = 453 B at M=16 without offsets.  Backward re-reads the inputs, reads the five
 //   incoming gradients (96 B) and writes 12+12+12+16+12*M (+96) B.
+#include <stdio.h>
 #include "ghr_common.cuh"
 #include "ghr_internal.h"
 
@@ -473,4 +474,205 @@ cudaError_t launch_lbs_deform_backward(const ghr_deform_params& p, const DeformG
     return cudaGetLastError();
 }
 
+// ---- stand-alone operators: the same math as the fused kernels above, for callers that use
+// GaussianModel.get_covariance (scene/gaussian_model.py:35-42,208-209) or eval_sh + clamp
+// (gaussian_renderer/__init__.py:124-125,191-195; utils/sh_utils.py:135-190) on their own. ----------------------------
+
+// Sigma' = (T L)(T L)^T, L = R(q/|q|) diag(mod * s), packed [xx,xy,xz,yy,yz,zz]; T = identity when transforms == NULL
+__global__ void __launch_bounds__(128) covariance_forward_kernel(int P, const float* __restrict__ scaling,
+                                                                 const float* __restrict__ rotation, float modifier,
+                                                                 const float* __restrict__ transforms,
+                                                                 float* __restrict__ cov)
+{
+    const int idx = blockIdx.x * 128 + threadIdx.x;
+    if (idx >= P) return;
+    const float4 q = __ldg(reinterpret_cast<const float4*>(rotation) + idx);
+    float Rq[9], inv_norm;
+    quat_rot(q.x, q.y, q.z, q.w, Rq, inv_norm);
+    const float sc[3] = {modifier * scaling[3 * idx], modifier * scaling[3 * idx + 1], modifier * scaling[3 * idx + 2]};
+    float L[9], TL[9];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int c = 0; c < 3; c++) L[3 * r + c] = Rq[3 * r + c] * sc[c];
+    if (transforms) {
+        float T[9];
+#pragma unroll
+        for (int k = 0; k < 9; k++) T[k] = transforms[9 * (size_t)idx + k];
+        mat3_mul_d(T, L, TL);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 9; k++) TL[k] = L[k];
+    }
+    float* co = cov + 6 * (size_t)idx;
+    co[0] = TL[0] * TL[0] + TL[1] * TL[1] + TL[2] * TL[2];
+    co[1] = TL[0] * TL[3] + TL[1] * TL[4] + TL[2] * TL[5];
+    co[2] = TL[0] * TL[6] + TL[1] * TL[7] + TL[2] * TL[8];
+    co[3] = TL[3] * TL[3] + TL[4] * TL[4] + TL[5] * TL[5];
+    co[4] = TL[3] * TL[6] + TL[4] * TL[7] + TL[5] * TL[8];
+    co[5] = TL[6] * TL[6] + TL[7] * TL[7] + TL[8] * TL[8];
+}
+
+__global__ void __launch_bounds__(128) covariance_backward_kernel(int P, const float* __restrict__ scaling,
+                                                                  const float* __restrict__ rotation, float modifier,
+                                                                  const float* __restrict__ transforms,
+                                                                  const float* __restrict__ g_cov,
+                                                                  float* __restrict__ d_scaling,
+                                                                  float* __restrict__ d_rotation,
+                                                                  float* __restrict__ d_transforms)
+{
+    const int idx = blockIdx.x * 128 + threadIdx.x;
+    if (idx >= P) return;
+    const float4 q = __ldg(reinterpret_cast<const float4*>(rotation) + idx);
+    float Rq[9], inv_norm;
+    quat_rot(q.x, q.y, q.z, q.w, Rq, inv_norm);
+    const float sc[3] = {modifier * scaling[3 * idx], modifier * scaling[3 * idx + 1], modifier * scaling[3 * idx + 2]};
+    float L[9], TL[9], T[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f};
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int c = 0; c < 3; c++) L[3 * r + c] = Rq[3 * r + c] * sc[c];
+    if (transforms) {
+#pragma unroll
+        for (int k = 0; k < 9; k++) T[k] = transforms[9 * (size_t)idx + k];
+    }
+    mat3_mul_d(T, L, TL);
+    const float* gc = g_cov + 6 * (size_t)idx;
+    // dS' + dS'^T for the upper-triangular packing [xx,xy,xz,yy,yz,zz] (strip_symmetric, general_utils.py:64-72)
+    const float S2[9] = {2.f * gc[0], gc[1], gc[2], gc[1], 2.f * gc[3], gc[4], gc[2], gc[4], 2.f * gc[5]};
+    float dTL[9], dL[9], t[9];
+    mat3_mul_d(S2, TL, dTL);
+    if (d_transforms) {
+        mat3_mult_d(dTL, L, t);  // dT = dTL L^T
+#pragma unroll
+        for (int k = 0; k < 9; k++) d_transforms[9 * (size_t)idx + k] = t[k];
+    }
+    mat3_tmul_d(T, dTL, dL);  // dL = T^T dTL
+    float dsc[3], dR[9];
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        dsc[c] = (Rq[c] * dL[c] + Rq[3 + c] * dL[3 + c] + Rq[6 + c] * dL[6 + c]) * modifier;
+        dR[c] = dL[c] * sc[c]; dR[3 + c] = dL[3 + c] * sc[c]; dR[6 + c] = dL[6 + c] * sc[c];
+    }
+    const float r = q.x * inv_norm, x = q.y * inv_norm, y = q.z * inv_norm, z = q.w * inv_norm;
+    const float dr_ = 2.f * (-z * dR[1] + y * dR[2] + z * dR[3] - x * dR[5] - y * dR[6] + x * dR[7]);
+    const float dx_ = 2.f * (y * dR[1] + z * dR[2] + y * dR[3] - r * dR[5] + z * dR[6] + r * dR[7]) - 4.f * x * (dR[4] + dR[8]);
+    const float dy_ = 2.f * (x * dR[1] + r * dR[2] + x * dR[3] + z * dR[5] - r * dR[6] + z * dR[7]) - 4.f * y * (dR[0] + dR[8]);
+    const float dz_ = 2.f * (-r * dR[1] + x * dR[2] + r * dR[3] + y * dR[5] + x * dR[6] + y * dR[7]) - 4.f * z * (dR[0] + dR[4]);
+    const float dot = r * dr_ + x * dx_ + y * dy_ + z * dz_;  // q^ = q/|q|: dq = (dq^ - q^ (q^ . dq^)) / |q|
+    d_scaling[3 * idx] = dsc[0]; d_scaling[3 * idx + 1] = dsc[1]; d_scaling[3 * idx + 2] = dsc[2];
+    reinterpret_cast<float4*>(d_rotation)[idx] = make_float4((dr_ - r * dot) * inv_norm, (dx_ - x * dot) * inv_norm,
+                                                             (dy_ - y * dot) * inv_norm, (dz_ - z * dot) * inv_norm);
+}
+
+// colors = clamp_min(eval_sh(deg, shs, (means - campos)/|.|) + 0.5, 0); clamped[i] bit c = channel c was clamped
+__global__ void __launch_bounds__(128) sh_colors_forward_kernel(int P, int deg, int M, const float* __restrict__ shs,
+                                                                const float* __restrict__ means,
+                                                                const float* __restrict__ campos,
+                                                                float* __restrict__ colors, uint8_t* __restrict__ clamped)
+{
+    const int idx = blockIdx.x * 128 + threadIdx.x;
+    if (idx >= P) return;
+    float sh[48];
+    const int nf = min(M * 3, 48);
+    const float* sp = shs + (size_t)idx * M * 3;
+#pragma unroll
+    for (int k = 0; k < 48; k++)
+        if (k < nf) sh[k] = __ldg(sp + k);
+    float rgb[3];
+    uint32_t cm;
+    sh_to_rgb(deg, sh, means[3 * idx] - campos[0], means[3 * idx + 1] - campos[1], means[3 * idx + 2] - campos[2], rgb, cm);
+    colors[3 * (size_t)idx] = rgb[0]; colors[3 * (size_t)idx + 1] = rgb[1]; colors[3 * (size_t)idx + 2] = rgb[2];
+    if (clamped) clamped[idx] = (uint8_t)cm;
+}
+
+__global__ void __launch_bounds__(128) sh_colors_backward_kernel(int P, int deg, int M, const float* __restrict__ shs,
+                                                                 const float* __restrict__ means,
+                                                                 const float* __restrict__ campos,
+                                                                 const uint8_t* __restrict__ clamped,
+                                                                 const float* __restrict__ g_colors,
+                                                                 float* __restrict__ d_shs, float* __restrict__ d_means)
+{
+    const int idx = blockIdx.x * 128 + threadIdx.x;
+    if (idx >= P) return;
+    const float gc[3] = {g_colors[3 * idx], g_colors[3 * idx + 1], g_colors[3 * idx + 2]};
+    float dm[3] = {0.f, 0.f, 0.f};
+    sh_backward(deg, M, shs + (size_t)idx * M * 3, means[3 * idx] - campos[0], means[3 * idx + 1] - campos[1],
+                means[3 * idx + 2] - campos[2], clamped ? clamped[idx] : 0u, gc, dm, d_shs + (size_t)idx * M * 3, 0);
+    if (d_means) { d_means[3 * idx] = dm[0]; d_means[3 * idx + 1] = dm[1]; d_means[3 * idx + 2] = dm[2]; }
+}
+
 }  // namespace ghr
+
+using namespace ghr;
+
+extern "C" {
+
+static int ops_status(const char* what)
+{
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) return GHR_OK;
+    fprintf(stderr, "[libghr] CUDA error in %s: %s\n", what, cudaGetErrorString(e));
+    return GHR_ERR_CUDA;
+}
+
+int ghr_covariance_forward(int32_t P, const float* scaling, const float* rotation, float scaling_modifier,
+                           const float* transforms, float* cov3D, void* stream)
+{
+    if (P < 0) return GHR_ERR_BAD_ARG;
+    if (P == 0) return GHR_OK;
+    if (!scaling || !rotation || !cov3D || (reinterpret_cast<uintptr_t>(rotation) & 15)) return GHR_ERR_BAD_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    StageTimer timer(GHR_STAGE_LBS_FWD, s);
+    count_launch();
+    covariance_forward_kernel<<<(P + 127) / 128, 128, 0, s>>>(P, scaling, rotation, scaling_modifier, transforms, cov3D);
+    return ops_status("covariance_forward");
+}
+
+int ghr_covariance_backward(int32_t P, const float* scaling, const float* rotation, float scaling_modifier,
+                            const float* transforms, const float* dL_dcov3D, float* dL_dscaling, float* dL_drotation,
+                            float* dL_dtransforms, void* stream)
+{
+    if (P < 0) return GHR_ERR_BAD_ARG;
+    if (P == 0) return GHR_OK;
+    if (!scaling || !rotation || !dL_dcov3D || !dL_dscaling || !dL_drotation ||
+        (reinterpret_cast<uintptr_t>(rotation) & 15) || (reinterpret_cast<uintptr_t>(dL_drotation) & 15))
+        return GHR_ERR_BAD_ARG;
+    if (dL_dtransforms && !transforms) return GHR_ERR_BAD_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    StageTimer timer(GHR_STAGE_LBS_BWD, s);
+    count_launch();
+    covariance_backward_kernel<<<(P + 127) / 128, 128, 0, s>>>(P, scaling, rotation, scaling_modifier, transforms, dL_dcov3D,
+                                                               dL_dscaling, dL_drotation, dL_dtransforms);
+    return ops_status("covariance_backward");
+}
+
+int ghr_sh_colors_forward(int32_t P, int32_t sh_degree, int32_t M, const float* shs, const float* means3D,
+                          const float* campos, float* colors, uint8_t* clamped, void* stream)
+{
+    if (P < 0 || sh_degree < 0 || sh_degree > 3 || M < (sh_degree + 1) * (sh_degree + 1) || M > 16) return GHR_ERR_BAD_ARG;
+    if (P == 0) return GHR_OK;
+    if (!shs || !means3D || !campos || !colors) return GHR_ERR_BAD_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    StageTimer timer(GHR_STAGE_LBS_FWD, s);
+    count_launch();
+    sh_colors_forward_kernel<<<(P + 127) / 128, 128, 0, s>>>(P, sh_degree, M, shs, means3D, campos, colors, clamped);
+    return ops_status("sh_colors_forward");
+}
+
+int ghr_sh_colors_backward(int32_t P, int32_t sh_degree, int32_t M, const float* shs, const float* means3D,
+                           const float* campos, const uint8_t* clamped, const float* dL_dcolors, float* dL_dshs,
+                           float* dL_dmeans3D, void* stream)
+{
+    if (P < 0 || sh_degree < 0 || sh_degree > 3 || M < (sh_degree + 1) * (sh_degree + 1) || M > 16) return GHR_ERR_BAD_ARG;
+    if (P == 0) return GHR_OK;
+    if (!shs || !means3D || !campos || !dL_dcolors || !dL_dshs) return GHR_ERR_BAD_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    StageTimer timer(GHR_STAGE_LBS_BWD, s);
+    count_launch();
+    sh_colors_backward_kernel<<<(P + 127) / 128, 128, 0, s>>>(P, sh_degree, M, shs, means3D, campos, clamped, dL_dcolors,
+                                                              dL_dshs, dL_dmeans3D);
+    return ops_status("sh_colors_backward");
+}
+
+}  // extern "C"

@@ -390,3 +390,86 @@ def _rodrigues_model(dev):
         m = (model, (w, pd, jt, par))
         _RODRIGUES_MODELS[dev] = m
     return m
+
+
+# ---- stand-alone forms of the fused covariance / colour math ----------------------------------
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("libghr: tensor arguments must live on a CUDA device (there is no CPU fallback)")
+
+
+class _CovarianceFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, scaling, rotation, scaling_modifier, transforms):
+        _need_cuda(scaling, rotation, transforms)
+        sc, rot = _f32c(scaling.detach()), _f32c(rotation.detach())
+        if rot.data_ptr() % 16:
+            rot = rot.clone()
+        tr = None if transforms is None else _f32c(transforms.detach()).reshape(-1, 3, 3)
+        P = sc.shape[0]
+        cov = torch.empty(P, 6, dtype=torch.float32, device=sc.device)
+        with _lib.on_device(sc.device):
+            check(lib().ghr_covariance_forward(P, sc.data_ptr(), rot.data_ptr(), float(scaling_modifier), _ptr(tr),
+                                               cov.data_ptr(), _stream()), "ghr_covariance_forward")
+        ctx.save_for_backward(sc, rot, tr)
+        ctx.mod, ctx.tr_shape = float(scaling_modifier), None if transforms is None else transforms.shape
+        return cov
+
+    @staticmethod
+    def backward(ctx, g_cov):
+        sc, rot, tr = ctx.saved_tensors
+        P = sc.shape[0]
+        g = _f32c(g_cov)
+        d_sc, d_rot = torch.empty_like(sc), torch.empty_like(rot)
+        d_tr = torch.empty_like(tr) if (tr is not None and ctx.needs_input_grad[3]) else None
+        with _lib.on_device(sc.device):
+            check(lib().ghr_covariance_backward(P, sc.data_ptr(), rot.data_ptr(), ctx.mod, _ptr(tr), g.data_ptr(),
+                                                d_sc.data_ptr(), d_rot.data_ptr(), _ptr(d_tr), _stream()),
+                  "ghr_covariance_backward")
+        return d_sc, d_rot, None, None if d_tr is None else d_tr.view(ctx.tr_shape)
+
+
+def get_covariance(scaling, rotation, scaling_modifier=1.0, transforms=None):
+    """GaussianModel.get_covariance(scaling_modifier, transforms) (scene/gaussian_model.py:35-42,208-209): scaling [P,3]
+    = get_scaling (activated), rotation [P,4] = the raw quaternion (normalised inside, general_utils.py:79), transforms
+    [P,3,3] or None -> [P,6] packed [xx,xy,xz,yy,yz,zz].  Differentiable in scaling, rotation and transforms."""
+    return _CovarianceFn.apply(scaling, rotation, scaling_modifier, transforms)
+
+
+class _ShColorsFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, sh_degree, features, means3D, campos):
+        _need_cuda(features, means3D, campos)
+        shs, mean = _f32c(features.detach()), _f32c(means3D.detach())
+        cam = _f32c(campos.detach()).reshape(-1)
+        P, M = shs.shape[0], shs.shape[1]
+        colors = torch.empty(P, 3, dtype=torch.float32, device=shs.device)
+        clamped = torch.empty(P, dtype=torch.uint8, device=shs.device)
+        with _lib.on_device(shs.device):
+            check(lib().ghr_sh_colors_forward(P, int(sh_degree), M, shs.data_ptr(), mean.data_ptr(), cam.data_ptr(),
+                                              colors.data_ptr(), clamped.data_ptr(), _stream()), "ghr_sh_colors_forward")
+        ctx.save_for_backward(shs, mean, cam, clamped)
+        ctx.deg = int(sh_degree)
+        return colors
+
+    @staticmethod
+    def backward(ctx, g_colors):
+        shs, mean, cam, clamped = ctx.saved_tensors
+        P, M = shs.shape[0], shs.shape[1]
+        g = _f32c(g_colors)
+        d_shs = torch.empty_like(shs)
+        d_mean = torch.empty_like(mean) if ctx.needs_input_grad[2] else None
+        with _lib.on_device(shs.device):
+            check(lib().ghr_sh_colors_backward(P, ctx.deg, M, shs.data_ptr(), mean.data_ptr(), cam.data_ptr(),
+                                               clamped.data_ptr(), g.data_ptr(), d_shs.data_ptr(), _ptr(d_mean), _stream()),
+                  "ghr_sh_colors_backward")
+        return None, d_shs, d_mean, None
+
+
+def eval_sh_colors(sh_degree, features, means3D, campos):
+    """colors_precomp of render() when pipe.convert_SHs_python is set (gaussian_renderer/__init__.py:124-125,191-195):
+    clamp_min(eval_sh(sh_degree, features.transpose(1, 2), normalize(means3D - campos)) + 0.5, 0).  features [P,M,3]
+    (pc.get_features), means3D [P,3], campos [3] -> [P,3].  Differentiable in features and means3D."""
+    return _ShColorsFn.apply(sh_degree, features, means3D, campos)

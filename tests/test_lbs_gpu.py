@@ -217,3 +217,64 @@ def test_fused_activations_match_separate_ops(deformer):
     assert a[1].shape == (P, 1)
     for x, y, tol in zip(a, b, (1e-6, 1e-6, 1e-5, 1e-5, 1e-5, 1e-5)):
         assert rel_err(x.cpu().numpy(), y.cpu().numpy()) <= tol
+
+
+@pytest.mark.parametrize("name", ["lbs_plain_p1500", "lbs_offsets_p1200"])
+def test_standalone_covariance_and_colours_match_reference_goldens(name):
+    """get_covariance / eval_sh_colors on their own against the reference's golden outputs."""
+    from mygauhuman_b200.lbs import eval_sh_colors, get_covariance
+    g = _load(name)
+    cov = get_covariance(torch.exp(_t(g["log_scale"])).cuda(), _t(g["rotation"]).cuda(), 1.0, _t(g["out_transforms"]).cuda())
+    np.testing.assert_allclose(cov.cpu().numpy(), g["out_cov3D"], rtol=2e-4, atol=1e-9)
+    for deg in range(4):
+        col = eval_sh_colors(deg, _t(g["features"]).cuda(), _t(g["out_world_pts"]).cuda(), _t(g["campos"]).cuda())
+        np.testing.assert_allclose(col.cpu().numpy(), g["out_colors"][deg], atol=5e-6)
+
+
+def test_standalone_covariance_and_colours_backward_vs_fp64_autograd():
+    from mygauhuman_b200.lbs import eval_sh_colors, get_covariance
+    from oracle import lbs_oracle as LO
+    gen = torch.Generator().manual_seed(11)
+    P = 2000
+    s = torch.exp(torch.randn(P, 3, generator=gen) * 0.3 - 4.0)
+    q = torch.randn(P, 4, generator=gen) * 1.3
+    T = torch.eye(3)[None] + 0.3 * torch.randn(P, 3, 3, generator=gen)
+    gc = torch.randn(P, 6, generator=gen)
+    for use_T in (True, False):
+        a = [t.clone().cuda().requires_grad_(True) for t in (s, q, T)]
+        cov = get_covariance(a[0], a[1], 1.3, a[2] if use_T else None)
+        cov.backward(gc.cuda())
+        b = [t.clone().double().requires_grad_(True) for t in (s, q, T)]
+        ref = LO.covariance(b[0], 1.3, b[1], b[2] if use_T else None)
+        ref.backward(gc.double())
+        assert _rel(cov.detach().cpu().numpy(), ref.detach().numpy()) < 1e-5  # fp32 vs fp64, off-diagonals cancel
+        for x, y, n in zip(a, b, ("scaling", "rotation", "transforms")):
+            if n == "transforms" and not use_T:
+                assert x.grad is None
+                continue
+            assert _rel(x.grad.cpu().numpy(), y.grad.numpy()) < 1e-4, n
+    sh = torch.cat([torch.rand(P, 1, 3, generator=gen) * 6 - 3, torch.randn(P, 15, 3, generator=gen) * 0.3], 1)
+    m = torch.randn(P, 3, generator=gen)
+    cam = torch.tensor([0.2, 1.0, 3.0])
+    gcol = torch.randn(P, 3, generator=gen)
+    for deg in range(4):
+        a = [t.clone().cuda().requires_grad_(True) for t in (sh, m)]
+        col = eval_sh_colors(deg, a[0], a[1], cam.cuda())
+        col.backward(gcol.cuda())
+        b = [t.clone().double().requires_grad_(True) for t in (sh, m)]
+        ref = LO.view_colors(deg, b[0], b[1], cam.double())
+        ref.backward(gcol.double())
+        np.testing.assert_allclose(col.detach().cpu().numpy(), ref.detach().numpy(), atol=5e-6)
+        assert (col == 0).any()  # some channels are clamped: their gradient must vanish
+        assert _rel(a[0].grad.cpu().numpy(), b[0].grad.numpy()) < 1e-4, deg
+        if b[1].grad is None:  # degree 0: no view dependence
+            assert float(a[1].grad.abs().max()) == 0.0
+        else:
+            assert _rel(a[1].grad.cpu().numpy(), b[1].grad.numpy()) < 1e-4, deg
+    with pytest.raises(RuntimeError):
+        get_covariance(s, q)  # CPU tensors: no fallback
+
+
+def _rel(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
