@@ -211,7 +211,9 @@ cudaError_t launch_blend_forward_wide(const ghr_raster_params& p, const char* ge
     const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
     const int64_t items = (int64_t)tiles * 8;
     int64_t ctas = (items + kWideWarps - 1) / kWideWarps;
-    if (ctas > 148 * kWideCtasPerSm) ctas = 148 * kWideCtasPerSm;
+    // several views in flight (ghr_set_shared_gpu): leave half of every SM's shared memory to another view's blend
+    const int per_sm = blend_shared_gpu() ? (kWideCtasPerSm + 1) / 2 : kWideCtasPerSm;
+    if (ctas > 148 * per_sm) ctas = 148 * per_sm;
     const int64_t capacity = L.capacity;
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
     cudaError_t e = cudaMemsetAsync(&hdr->blend_fwd_ticket, 0, sizeof(uint32_t), s);  // render may run twice per preprocess
