@@ -440,6 +440,38 @@ typedef struct ghr_adam_group {
 int ghr_adam_step(int n_groups, const ghr_adam_group* groups, double beta1, double beta2, double eps, int zero_grads,
                   void* stream); /* betas / eps as the Python doubles torch holds: 1 - beta is rounded to fp32 once */
 
+/*
+ * View-sharded data parallelism, optimiser step fused with its collective (no counterpart in the reference, which is
+ * single-GPU): reduce-scatter of the ranks' flat gradient buckets + Adam on the owned slice + all-gather of the new
+ * parameters, in ONE kernel over NVLink peer memory.  peer_grads[r] / peer_params[r] (host arrays of `world` device
+ * pointers, r = rank order, entry `rank` = this process's own buffers) are the ranks' flat gradient buckets and flat
+ * parameter replicas, mapped into this process (CUDA IPC; mygauhuman_b200/optim.py ShardedFusedAdam does the exchange).
+ * This rank owns floats [shard_lo, shard_hi) (multiples of 4) and holds the moments of that slice only
+ * (exp_avg_shard / exp_avg_sq_shard, shard_hi - shard_lo floats, 16-byte aligned).  groups: the parameter groups as
+ * (offset, count) ranges of the flat layout (offsets multiples of 4) with their lr and 1-based step.  The caller
+ * brackets the call with cross-rank barriers on the stream (all buckets complete before; no bucket reset or parameter
+ * read before every rank is done).  Element arithmetic = ghr_adam_step on the rank-ordered sum of the gradients.
+ */
+#define GHR_MAX_PEERS 8
+typedef struct ghr_shard_group {
+    int64_t offset;
+    int64_t count;
+    double lr;
+    int32_t step;
+    int32_t pad;
+} ghr_shard_group;
+int ghr_adam_step_sharded(int world, int rank, const float* const* peer_grads, float* const* peer_params, float* exp_avg_shard,
+                          float* exp_avg_sq_shard, int64_t shard_lo, int64_t shard_hi, int n_groups,
+                          const ghr_shard_group* groups, double beta1, double beta2, double eps, void* stream);
+/* Lets kernels on the CURRENT device dereference memory of `peer_device` (cudaDeviceEnablePeerAccess; already enabled
+ * is not an error).  Needed once per peer before ghr_adam_step_sharded. */
+int ghr_enable_peer_access(int peer_device);
+/* Maps another process's allocation (64-byte cudaIpcMemHandle_t, e.g. the one torch's storage._share_cuda_() returns)
+ * into THIS process under the CURRENT device, with peer access enabled as needed; *base_out is the allocation's base.
+ * One open per handle and process.  ghr_ipc_close unmaps. */
+int ghr_ipc_open(const void* handle, void** base_out);
+int ghr_ipc_close(void* base);
+
 /* train.py:401-404 + GaussianModel.add_densification_stats (scene/gaussian_model.py:764-766) with
  * visibility_filter = radii > 0, fused: max_radii2D[i] = max(max_radii2D[i], radii[i]);
  * xyz_gradient_accum[i] += ||dL_dmean2D[i, :2]||; denom[i] += 1.  Any of the three outputs may be NULL.

@@ -64,7 +64,13 @@ class AdamGroup(C.Structure):
                 ("lr", C.c_double), ("step", C.c_int32), ("pad", C.c_int32)]
 
 
+class ShardGroup(C.Structure):
+    """ghr_shard_group (include/ghr.h)."""
+    _fields_ = [("offset", C.c_int64), ("count", C.c_int64), ("lr", C.c_double), ("step", C.c_int32), ("pad", C.c_int32)]
+
+
 ADAM_MAX_GROUPS = 16
+MAX_PEERS = 8
 POSE_FLOATS = 1536
 POSE_A, POSE_ROT, POSE_PF, POSE_JOINTS, POSE_RGINV, POSE_RG, POSE_TH, POSE_G, POSE_ROD = 0, 288, 504, 720, 800, 816, 832, 848, 1136
 
@@ -120,6 +126,11 @@ SIGNATURES = {
     "ghr_forward_views": (C.c_int, [C.POINTER(RasterParams), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_size_t, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ghr_adam_step": (C.c_int, [C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int, C.c_void_p]),
+    "ghr_adam_step_sharded": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                        C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_void_p]),
+    "ghr_enable_peer_access": (C.c_int, [C.c_int]),
+    "ghr_ipc_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "ghr_ipc_close": (C.c_int, [C.c_void_p]),
     "ghr_densify_stats": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_void_p]),
     "ghr_ply_row_floats": (C.c_int, [C.c_int32]),

@@ -7,6 +7,7 @@
 // Both are pure HBM streams: 28 (32 with the gradient reset) bytes per parameter, 40 bytes per Gaussian.
 #include <math.h>
 #include <stdio.h>
+#include <string.h>
 #include "ghr_internal.h"
 
 namespace ghr {
@@ -113,6 +114,64 @@ __global__ void __launch_bounds__(256) densify_stats_kernel(int P, const int32_t
     if (denom) denom[i] += 1.f;
 }
 
+
+// ---- reduce-scatter + Adam + all-gather in ONE kernel over NVLink peer memory (view-sharded data parallelism) --------
+// Every rank holds a replica of the flat parameter buffer and its own flat gradient bucket (the sum over ITS views).  Rank
+// r owns the slice [lo, hi) of the buffers: it reads that slice of every rank's gradients straight from peer memory (P2P
+// loads), sums them in rank order, applies Adam with ITS shard of the moments (optimizer state is sharded, ZeRO-1), and
+// stores the new parameters into every replica (P2P stores).  Per rank and step: (W-1)/W of the bucket in and out over
+// NVLink -- what a ring all-reduce moves -- but no separate all-reduce, no second pass over the gradients, 1/W of the
+// Adam work and state, and bit-identical replicas (exactly one rank computes each element).
+struct ShardSeg {
+    int64_t begin, end;      // [begin, end) of the flat buffers this (group x shard) piece covers
+    float neg_step_size, inv_bc2_sqrt;
+};
+struct ShardTable {
+    const float* grads[GHR_MAX_PEERS];
+    float* params[GHR_MAX_PEERS];
+    float* m;                // [hi - lo] moments of the owned slice
+    float* v;
+    int64_t lo;
+    ShardSeg seg[GHR_ADAM_MAX_GROUPS];
+    uint32_t first_chunk[GHR_ADAM_MAX_GROUPS];
+    int n_seg, world, rank;
+    float w1, beta2, w2, eps;
+};
+
+__global__ void __launch_bounds__(kAdamThreads) adam_sharded_kernel(const __grid_constant__ ShardTable t)
+{
+    int k = 0;
+#pragma unroll 1
+    for (int i = 1; i < t.n_seg; ++i)
+        if (blockIdx.x >= t.first_chunk[i]) k = i;
+    const ShardSeg& sg = t.seg[k];
+    AdamTable at;  // only the scalars adam_one reads
+    at.w1 = t.w1; at.beta2 = t.beta2; at.w2 = t.w2; at.eps = t.eps;
+    AdamSeg as;
+    as.neg_step_size = sg.neg_step_size; as.inv_bc2_sqrt = sg.inv_bc2_sqrt;
+    const int64_t base = sg.begin + int64_t(blockIdx.x - t.first_chunk[k]) * kAdamChunk;
+    // pieces start and end on 4-float boundaries (the host aligns shard bounds and group offsets), so float4 throughout
+    for (int64_t i = base + 4 * threadIdx.x; i < min(base + (int64_t)kAdamChunk, sg.end); i += 4 * kAdamThreads) {
+        float4 g = *reinterpret_cast<const float4*>(t.grads[0] + i);
+#pragma unroll 1
+        for (int r = 1; r < t.world; ++r) {  // fixed rank order: every replica sees the same sum
+            const float4 x = *reinterpret_cast<const float4*>(t.grads[r] + i);
+            g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+        }
+        float4 p = *reinterpret_cast<const float4*>(t.params[t.rank] + i);
+        float4 m = *reinterpret_cast<const float4*>(t.m + (i - t.lo));
+        float4 v = *reinterpret_cast<const float4*>(t.v + (i - t.lo));
+        adam_one(p.x, g.x, m.x, v.x, at, as);
+        adam_one(p.y, g.y, m.y, v.y, at, as);
+        adam_one(p.z, g.z, m.z, v.z, at, as);
+        adam_one(p.w, g.w, m.w, v.w, at, as);
+        *reinterpret_cast<float4*>(t.m + (i - t.lo)) = m;
+        *reinterpret_cast<float4*>(t.v + (i - t.lo)) = v;
+#pragma unroll 1
+        for (int r = 0; r < t.world; ++r) *reinterpret_cast<float4*>(t.params[r] + i) = p;
+    }
+}
+
 inline bool misaligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) != 0; }
 
 }  // namespace
@@ -164,6 +223,92 @@ int ghr_adam_step(int n_groups, const ghr_adam_group* groups, double beta1, doub
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         fprintf(stderr, "[libghr] CUDA error in adam_step: %s\n", cudaGetErrorString(e));
+        return GHR_ERR_CUDA;
+    }
+    return GHR_OK;
+}
+
+int ghr_enable_peer_access(int peer_device)
+{
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess || peer_device < 0) return GHR_ERR_BAD_ARG;
+    if (cur == peer_device) return GHR_OK;
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, cur, peer_device) != cudaSuccess || !can) return GHR_ERR_CUDA;
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { (void)cudaGetLastError(); return GHR_OK; }
+    if (e != cudaSuccess) {
+        fprintf(stderr, "[libghr] cudaDeviceEnablePeerAccess(%d): %s\n", peer_device, cudaGetErrorString(e));
+        return GHR_ERR_CUDA;
+    }
+    return GHR_OK;
+}
+
+int ghr_ipc_open(const void* handle, void** base_out)
+{
+    if (!handle || !base_out) return GHR_ERR_BAD_ARG;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    const cudaError_t e = cudaIpcOpenMemHandle(base_out, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        fprintf(stderr, "[libghr] cudaIpcOpenMemHandle: %s\n", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return GHR_ERR_CUDA;
+    }
+    return GHR_OK;
+}
+
+int ghr_ipc_close(void* base)
+{
+    if (!base) return GHR_OK;
+    return cudaIpcCloseMemHandle(base) == cudaSuccess ? GHR_OK : GHR_ERR_CUDA;
+}
+
+int ghr_adam_step_sharded(int world, int rank, const float* const* peer_grads, float* const* peer_params, float* exp_avg_shard,
+                          float* exp_avg_sq_shard, int64_t shard_lo, int64_t shard_hi, int n_groups,
+                          const ghr_shard_group* groups, double beta1, double beta2, double eps, void* stream)
+{
+    if (world < 1 || world > GHR_MAX_PEERS || rank < 0 || rank >= world || n_groups < 0 || n_groups > GHR_ADAM_MAX_GROUPS)
+        return GHR_ERR_BAD_ARG;
+    if (shard_lo < 0 || shard_hi < shard_lo || (shard_lo & 3) || (shard_hi & 3)) return GHR_ERR_BAD_ARG;
+    if (shard_hi == shard_lo || n_groups == 0) return GHR_OK;
+    if (!peer_grads || !peer_params || !groups || !exp_avg_shard || !exp_avg_sq_shard || misaligned16(exp_avg_shard) ||
+        misaligned16(exp_avg_sq_shard))
+        return GHR_ERR_BAD_ARG;
+    if (!(beta1 >= 0.0 && beta1 < 1.0 && beta2 >= 0.0 && beta2 < 1.0 && eps >= 0.0)) return GHR_ERR_BAD_ARG;
+    ShardTable t;
+    for (int r = 0; r < world; ++r) {
+        if (!peer_grads[r] || !peer_params[r] || misaligned16(peer_grads[r]) || misaligned16(peer_params[r])) return GHR_ERR_BAD_ARG;
+        t.grads[r] = peer_grads[r];
+        t.params[r] = peer_params[r];
+    }
+    t.m = exp_avg_shard; t.v = exp_avg_sq_shard; t.lo = shard_lo;
+    t.world = world; t.rank = rank; t.n_seg = 0;
+    t.w1 = (float)(1.0 - beta1); t.beta2 = (float)beta2; t.w2 = (float)(1.0 - beta2); t.eps = (float)eps;
+    uint64_t chunks = 0;
+    for (int i = 0; i < n_groups; ++i) {
+        const ghr_shard_group& g = groups[i];
+        if (g.offset < 0 || g.count < 0 || (g.offset & 3) || g.step < 1) return GHR_ERR_BAD_ARG;
+        const int64_t b = g.offset > shard_lo ? g.offset : shard_lo;
+        int64_t e = g.offset + g.count < shard_hi ? g.offset + g.count : shard_hi;
+        if (e <= b) continue;
+        e = (e + 3) / 4 * 4;  // a group's tail is padded to the next group's 4-float boundary: the padding is ours to touch
+        ShardSeg& sg = t.seg[t.n_seg];
+        sg.begin = b; sg.end = e;
+        const double bc1 = 1.0 - pow(beta1, (double)g.step), bc2 = 1.0 - pow(beta2, (double)g.step);
+        sg.neg_step_size = (float)(-g.lr / bc1);
+        sg.inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
+        t.first_chunk[t.n_seg++] = (uint32_t)chunks;
+        chunks += (uint64_t)((e - b + kAdamChunk - 1) / kAdamChunk);
+    }
+    if (t.n_seg == 0) return GHR_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    StageTimer timer(GHR_STAGE_OPTIMIZER, s);
+    adam_sharded_kernel<<<(unsigned)chunks, kAdamThreads, 0, s>>>(t);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        fprintf(stderr, "[libghr] CUDA error in adam_step_sharded: %s\n", cudaGetErrorString(e));
         return GHR_ERR_CUDA;
     }
     return GHR_OK;

@@ -102,3 +102,130 @@ def add_densification_stats(radii, viewspace_grad, max_radii2D=None, xyz_gradien
         _lib.check(_lib.lib().ghr_densify_stats(P, radii.data_ptr(), viewspace_grad.data_ptr(), viewspace_grad.shape[1],
                                                 ptr(max_radii2D), ptr(xyz_gradient_accum), ptr(denom),
                                                 _lib.raw_stream(dev.index or 0)), "ghr_densify_stats")
+
+
+# ---- view-sharded data parallelism: reduce-scatter + Adam + all-gather fused over NVLink peer memory ---------------------
+
+def flat_layout(leaves):
+    """The flat layout GraphedRenderStep / MultiLaneRenderStep give the gradient bucket: the leaves in dict order, each
+    starting on a 4-float (16-byte) boundary.  -> (total floats, {name: (offset, count)})."""
+    pad = lambda n: (n + 3) // 4 * 4
+    table, o = {}, 0
+    for k, t in leaves.items():
+        table[k] = (o, t.numel())
+        o += pad(t.numel())
+    return o, table
+
+
+def flatten_leaves(leaves):
+    """Re-home the leaves in ONE flat fp32 buffer with that layout (what the sharded step needs: a parameter is addressed
+    by its offset on every rank).  -> (flat_params, {name: leaf tensor viewing it, requires_grad})."""
+    total, table = flat_layout(leaves)
+    any_leaf = next(iter(leaves.values()))
+    flat = torch.zeros(total, dtype=torch.float32, device=any_leaf.device)
+    out = {}
+    for k, t in leaves.items():
+        o, n = table[k]
+        flat[o:o + n].copy_(t.detach().reshape(-1))
+        out[k] = flat[o:o + n].view(t.shape).requires_grad_(True)  # a view of a buffer that does not require grad: a leaf
+    return flat, out
+
+
+def shard_bounds(total, world, rank):
+    """Slice [lo, hi) of a `total`-float buffer owned by `rank`: equal 4-float-aligned slices, the last one ragged."""
+    per = ((total + world - 1) // world + 3) // 4 * 4
+    lo = min(rank * per, total)
+    return lo, min(lo + per, total)
+
+
+_ipc_bases = {}  # cudaIpcMemHandle bytes -> base address of the mapping in this process (one open per handle)
+
+
+class ShardedFusedAdam:
+    """Adam over a flat parameter replica per rank, fused with the gradient reduction (ghr_adam_step_sharded): every rank
+    sums ITS slice of all ranks' gradient buckets straight from peer memory, steps it with its shard of the moments
+    (ZeRO-1) and writes the new parameters into every replica -- one kernel instead of NCCL all-reduce + Adam, with
+    bit-identical replicas.  Single node (CUDA IPC over NVLink), <= 8 ranks, torch.distributed initialised with NCCL.
+
+    groups: list of dict(name=, offset=, count=, lr=) in the flat layout (flat_layout); lr may be changed between steps
+    like a torch param_group (update_learning_rate, scene/gaussian_model.py:290-295)."""
+
+    def __init__(self, flat_params, flat_grads, groups, betas=(0.9, 0.999), eps=1e-8, group=None):
+        import torch.distributed as dist
+        if not (flat_params.is_cuda and flat_grads.is_cuda and flat_params.dtype == torch.float32
+                and flat_grads.dtype == torch.float32 and flat_params.numel() == flat_grads.numel()
+                and flat_params.is_contiguous() and flat_grads.is_contiguous() and flat_params.numel() % 4 == 0):
+            raise ValueError("ShardedFusedAdam: flat contiguous CUDA fp32 buffers of equal, 4-float-padded size")
+        self.dist, self.group = dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > _lib.MAX_PEERS:
+            raise ValueError(f"ShardedFusedAdam: at most {_lib.MAX_PEERS} ranks (one node)")
+        self.params, self.grads = flat_params, flat_grads
+        self.param_groups = [dict(g) for g in groups]
+        self.betas, self.eps, self.steps = betas, eps, 0
+        self.lo, self.hi = shard_bounds(flat_params.numel(), self.world, self.rank)
+        dev = flat_params.device
+        self.exp_avg = torch.zeros(max(self.hi - self.lo, 4), device=dev)
+        self.exp_avg_sq = torch.zeros(max(self.hi - self.lo, 4), device=dev)
+        # Exchange the buffers' CUDA IPC handles and map the peers' allocations under OUR device (a mapping opened under
+        # the owner's device, as torch's own rebuild does, is not reachable from kernels running here).
+        def describe(t):
+            st = t.untyped_storage()
+            _, handle, _, storage_off, *_ = st._share_cuda_()
+            handle = bytes(handle)
+            if len(handle) in (65, 66):  # newer torch prefixes the 64-byte cudaIpcMemHandle_t with (version,) kind bytes
+                if handle[-65:-64] != b"c":
+                    raise RuntimeError("ShardedFusedAdam: the buffers must come from cudaMalloc segments (expandable "
+                                       "segments are not supported: unset PYTORCH_CUDA_ALLOC_CONF=expandable_segments)")
+                handle = handle[-64:]
+            if len(handle) != 64:
+                raise RuntimeError(f"ShardedFusedAdam: unexpected CUDA IPC handle of {len(handle)} bytes (expandable "
+                                   "segments are not supported: unset PYTORCH_CUDA_ALLOC_CONF=expandable_segments)")
+            return handle, int(storage_off) + 4 * int(t.storage_offset())
+        self._shared = [flat_params.detach(), flat_grads.detach()]  # producers keep what they shared alive
+        mine = [describe(t) for t in self._shared]
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine, group=group)
+        p_ptrs, g_ptrs = [], []
+        with _lib.on_device(dev):
+            for r in range(self.world):
+                if r == self.rank:
+                    p_ptrs.append(flat_params.data_ptr())
+                    g_ptrs.append(flat_grads.data_ptr())
+                    continue
+                ptrs = []
+                for handle, off in everyone[r]:
+                    base = _ipc_bases.get(handle)
+                    if base is None:
+                        out = C.c_void_p()
+                        _lib.check(_lib.lib().ghr_ipc_open(handle, C.byref(out)), "ghr_ipc_open")
+                        base = _ipc_bases[handle] = int(out.value)
+                    ptrs.append(base + off)
+                p_ptrs.append(ptrs[0])
+                g_ptrs.append(ptrs[1])
+        self._p_ptrs = (C.c_void_p * self.world)(*p_ptrs)
+        self._g_ptrs = (C.c_void_p * self.world)(*g_ptrs)
+        self._token = torch.zeros(1, device=dev)
+        dist.barrier(group=group)
+
+    def _barrier_on_stream(self):
+        # a one-element NCCL all-reduce: completes on this stream only when every rank's stream has reached it
+        self.dist.all_reduce(self._token, group=self.group)
+
+    @torch.no_grad()
+    def step(self):
+        """Call where the reference calls optimizer.step() after the batch's backward passes; NO gradient all-reduce
+        before it.  On return (stream order) every replica holds the new parameters; clear the bucket afterwards
+        (zero_grads of the render step)."""
+        self.steps += 1
+        table = (_lib.ShardGroup * len(self.param_groups))()
+        for e, g in zip(table, self.param_groups):
+            e.offset, e.count, e.lr, e.step = int(g["offset"]), int(g["count"]), float(g["lr"]), self.steps
+        dev = self.params.device
+        with _lib.on_device(dev):
+            self._barrier_on_stream()  # every rank's bucket is complete
+            _lib.check(_lib.lib().ghr_adam_step_sharded(
+                self.world, self.rank, self._g_ptrs, self._p_ptrs, self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
+                self.lo, self.hi, len(self.param_groups), table, float(self.betas[0]), float(self.betas[1]),
+                float(self.eps), _lib.raw_stream(dev.index or 0)), "ghr_adam_step_sharded")
+            self._barrier_on_stream()  # every replica is written, every bucket has been read

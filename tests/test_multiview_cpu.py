@@ -94,3 +94,19 @@ def test_view_sharding_allreduce_equals_batch_accumulation():
     for a, b in zip(got, want):
         assert np.abs(b.numpy()).max() > 0
         np.testing.assert_allclose(a, b.numpy(), rtol=1e-5, atol=1e-7)
+
+
+def test_flat_layout_and_shard_bounds_partition_the_buffer():
+    """Host logic of the sharded optimiser step (mygauhuman_b200.optim): the flat layout pads every leaf to 16 bytes and
+    the ranks' slices tile the buffer without gaps, on 4-float boundaries."""
+    import torch
+    from mygauhuman_b200.optim import flat_layout, shard_bounds
+    leaves = {"xyz": torch.zeros(5001, 3), "rotation": torch.zeros(5001, 4), "opacity": torch.zeros(5001, 1)}
+    total, table = flat_layout(leaves)
+    assert total % 4 == 0 and table["xyz"] == (0, 15003) and table["rotation"][0] == 15004
+    assert table["opacity"][0] == 15004 + 20004 and total == 15004 + 20004 + 5004
+    for world in (1, 2, 3, 4, 8):
+        edges = [shard_bounds(total, world, r) for r in range(world)]
+        assert edges[0][0] == 0 and edges[-1][1] == total
+        assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
+        assert all(lo % 4 == 0 and hi % 4 == 0 and hi >= lo for lo, hi in edges)
