@@ -103,3 +103,68 @@ def test_operator_api_surface_and_argument_errors():
     dgr, sknn = mygauhuman_b200.install()
     import diff_gaussian_rasterization, simple_knn._C
     assert diff_gaussian_rasterization is dgr and callable(simple_knn._C.distCUDA2)
+
+
+def test_new_entry_points_reject_bad_arguments_without_touching_the_gpu():
+    """View-batched forward, optimiser, checkpoint-row and stand-alone operator entry points: argument validation happens
+    before any CUDA call, so it can be checked here."""
+    l = _lib.lib()
+    BAD, BUF, OK = _lib.GHR_ERR_BAD_ARG, _lib.GHR_ERR_BUFFER, _lib.GHR_OK
+    # ghr_forward_views / workspace query
+    assert l.ghr_views_workspace_bytes(1000, 6, 32, 32, 4000) > 0
+    assert l.ghr_views_workspace_bytes(1000, 0, 32, 32, 4000) == 0          # no views
+    assert l.ghr_views_workspace_bytes(1 << 30, 8, 32, 32, 4000) == 0       # n_views * P beyond 2^31
+    assert l.ghr_views_workspace_bytes(1000, 6, 32, 32, 1 << 30) == 0       # capacity beyond 2^30
+    p = _lib.RasterParams()
+    p.P, p.W, p.H = 4, 32, 32
+    assert l.ghr_forward_views(None, 1, None, None, None, None, 0, 0, None, None, None, None, None) == BAD
+    assert l.ghr_forward_views(C.byref(p), -1, None, None, None, None, 0, 0, None, None, None, None, None) == BAD
+    assert l.ghr_forward_views(C.byref(p), 0, None, None, None, None, 0, 0, None, None, None, None, None) == OK
+    assert l.ghr_forward_views(C.byref(p), 2, None, None, None, None, 0, 16, None, None, None, None, None) == BAD  # no cameras
+    # ghr_adam_step
+    t = (_lib.AdamGroup * 1)()
+    t[0].count, t[0].step = 4, 1
+    assert l.ghr_adam_step(1, t, 0.9, 0.999, 1e-15, 0, None) == BAD          # null pointers
+    assert l.ghr_adam_step(17, t, 0.9, 0.999, 1e-15, 0, None) == BAD         # > GHR_ADAM_MAX_GROUPS
+    assert l.ghr_adam_step(0, None, 0.9, 0.999, 1e-15, 0, None) == OK
+    assert l.ghr_adam_step(1, None, 0.9, 0.999, 1e-15, 0, None) == BAD
+    t[0].count = 0
+    assert l.ghr_adam_step(1, t, 0.9, 0.999, 1e-15, 0, None) == OK           # empty group: nothing to do
+    assert l.ghr_adam_step(1, t, 1.0, 0.999, 1e-15, 0, None) == BAD          # beta1 < 1
+    assert l.ghr_adam_step(1, t, 0.9, 0.999, -1.0, 0, None) == BAD           # eps >= 0
+    # ghr_adam_step_sharded
+    g = (_lib.ShardGroup * 1)()
+    g[0].offset, g[0].count, g[0].lr, g[0].step = 0, 8, 1e-3, 1
+    assert l.ghr_adam_step_sharded(0, 0, None, None, None, None, 0, 8, 1, g, 0.9, 0.999, 1e-15, None) == BAD   # world >= 1
+    assert l.ghr_adam_step_sharded(9, 0, None, None, None, None, 0, 8, 1, g, 0.9, 0.999, 1e-15, None) == BAD   # <= 8 peers
+    assert l.ghr_adam_step_sharded(2, 2, None, None, None, None, 0, 8, 1, g, 0.9, 0.999, 1e-15, None) == BAD   # rank < world
+    assert l.ghr_adam_step_sharded(2, 0, None, None, None, None, 2, 8, 1, g, 0.9, 0.999, 1e-15, None) == BAD   # unaligned shard
+    assert l.ghr_adam_step_sharded(2, 0, None, None, None, None, 8, 8, 1, g, 0.9, 0.999, 1e-15, None) == OK    # empty shard
+    assert l.ghr_adam_step_sharded(2, 0, None, None, None, None, 0, 8, 1, g, 0.9, 0.999, 1e-15, None) == BAD   # null tables
+    assert l.ghr_enable_peer_access(-1) == BAD
+    assert l.ghr_ipc_open(None, None) == BAD and l.ghr_ipc_close(None) == OK
+    # ghr_densify_stats
+    assert l.ghr_densify_stats(-1, None, None, 3, None, None, None, None) == BAD
+    assert l.ghr_densify_stats(5, None, None, 3, None, None, None, None) == BAD
+    assert l.ghr_densify_stats(5, None, None, 1, None, None, None, None) == BAD    # rows of >= 2 floats
+    assert l.ghr_densify_stats(0, None, None, 3, None, None, None, None) == OK
+    # checkpoint rows
+    assert l.ghr_ply_row_floats(16) == 66 and l.ghr_ply_row_floats(1) == 21
+    assert l.ghr_ply_row_floats(0) == 0 and l.ghr_ply_row_floats(17) == 0
+    assert l.ghr_ply_pack_rows(3, 16, *([None] * 11)) == BAD
+    assert l.ghr_ply_pack_rows(0, 16, *([None] * 11)) == OK
+    assert l.ghr_ply_pack_rows(3, 0, *([None] * 11)) == BAD
+    assert l.ghr_ply_unpack_rows(3, 16, None, 65, None, *([None] * 10)) == BAD     # fewer columns than the format holds
+    cols = (C.c_int32 * 66)(*range(66))
+    cols[5] = 70
+    assert l.ghr_ply_unpack_rows(3, 16, None, 66, cols, *([None] * 10)) == BAD     # column index out of the row
+    # stand-alone covariance / SH colours
+    assert l.ghr_covariance_forward(4, None, None, 1.0, None, None, None) == BAD
+    assert l.ghr_covariance_forward(0, None, None, 1.0, None, None, None) == OK
+    assert l.ghr_covariance_backward(4, None, None, 1.0, None, None, None, None, None, None) == BAD
+    assert l.ghr_sh_colors_forward(4, 4, 16, None, None, None, None, None, None) == BAD   # degree <= 3
+    assert l.ghr_sh_colors_forward(4, 3, 9, None, None, None, None, None, None) == BAD    # M >= (deg+1)^2
+    assert l.ghr_sh_colors_forward(4, 3, 16, None, None, None, None, None, None) == BAD   # null inputs
+    assert l.ghr_sh_colors_backward(0, 3, 16, None, None, None, None, None, None, None, None) == OK
+    assert l.ghr_set_shared_gpu(1) == OK and l.ghr_set_shared_gpu(0) == OK
+    assert BUF != BAD
