@@ -463,6 +463,17 @@ typedef struct ghr_shard_group {
 int ghr_adam_step_sharded(int world, int rank, const float* const* peer_grads, float* const* peer_params, float* exp_avg_shard,
                           float* exp_avg_sq_shard, int64_t shard_lo, int64_t shard_hi, int n_groups,
                           const ghr_shard_group* groups, double beta1, double beta2, double eps, void* stream);
+/* Same step with the two cross-rank barriers INSIDE the kernel (no NCCL call at all): peer_flags[r] = rank r's flag buffer
+ * (ghr_sharded_flag_words() zero-initialised uint32 words, mapped like the other buffers), epoch = 1, 2, 3, ... (the step
+ * count, the same on every rank).  At its start the kernel publishes "rank arrived" to every peer with a system-scope
+ * release store and waits for all peers; at its end the last CTA publishes "rank done" and waits for all peers, so
+ * kernel completion means every replica is written and every bucket has been read.  Every rank must make the call
+ * (also one whose slice is empty). */
+int ghr_adam_step_sharded_synced(int world, int rank, const float* const* peer_grads, float* const* peer_params,
+                                 float* exp_avg_shard, float* exp_avg_sq_shard, int64_t shard_lo, int64_t shard_hi,
+                                 int n_groups, const ghr_shard_group* groups, double beta1, double beta2, double eps,
+                                 uint32_t* const* peer_flags, uint32_t epoch, void* stream);
+int ghr_sharded_flag_words(void);
 /* Lets kernels on the CURRENT device dereference memory of `peer_device` (cudaDeviceEnablePeerAccess; already enabled
  * is not an error).  Needed once per peer before ghr_adam_step_sharded. */
 int ghr_enable_peer_access(int peer_device);

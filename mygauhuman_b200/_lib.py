@@ -128,6 +128,10 @@ SIGNATURES = {
     "ghr_adam_step": (C.c_int, [C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int, C.c_void_p]),
     "ghr_adam_step_sharded": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
                                         C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_void_p]),
+    "ghr_adam_step_sharded_synced": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                               C.c_int64, C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_double,
+                                               C.c_void_p, C.c_uint32, C.c_void_p]),
+    "ghr_sharded_flag_words": (C.c_int, []),
     "ghr_enable_peer_access": (C.c_int, [C.c_int]),
     "ghr_ipc_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
     "ghr_ipc_close": (C.c_int, [C.c_void_p]),

@@ -136,10 +136,36 @@ struct ShardTable {
     uint32_t first_chunk[GHR_ADAM_MAX_GROUPS];
     int n_seg, world, rank;
     float w1, beta2, w2, eps;
+    // optional in-kernel cross-rank barriers: flags[r] = rank r's flag words, mapped here (uint32 [kFlagWords]):
+    // [ARRIVE + q] / [DONE + q] = last step for which rank q has arrived / finished, [COUNT] = local CTA counter
+    uint32_t* flags[GHR_MAX_PEERS];
+    uint32_t epoch;
 };
+constexpr int kFlagArrive = 0, kFlagDone = GHR_MAX_PEERS, kFlagCount = 2 * GHR_MAX_PEERS;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
 __global__ void __launch_bounds__(kAdamThreads) adam_sharded_kernel(const __grid_constant__ ShardTable t)
 {
+    const bool synced = t.flags[0] != nullptr;
+    if (synced) {
+        // Arrive: this kernel runs after this rank's backward passes (stream order), so its bucket is complete; tell
+        // every peer, then wait until every peer has said the same.  Every CTA polls this rank's OWN flag words only.
+        if (blockIdx.x == 0 && threadIdx.x < t.world)
+            st_release_sys(t.flags[threadIdx.x] + kFlagArrive + t.rank, t.epoch);
+        if (threadIdx.x < t.world)
+            while ((int32_t)(ld_acquire_sys(t.flags[t.rank] + kFlagArrive + threadIdx.x) - t.epoch) < 0) {}
+        __syncthreads();
+    }
     int k = 0;
 #pragma unroll 1
     for (int i = 1; i < t.n_seg; ++i)
@@ -169,6 +195,23 @@ __global__ void __launch_bounds__(kAdamThreads) adam_sharded_kernel(const __grid
         *reinterpret_cast<float4*>(t.v + (i - t.lo)) = v;
 #pragma unroll 1
         for (int r = 0; r < t.world; ++r) *reinterpret_cast<float4*>(t.params[r] + i) = p;
+    }
+    if (synced) {
+        // Done: when the last CTA of this rank has finished (its peer stores fenced), tell every peer; the kernel only
+        // retires once every peer has said the same -- then every replica is written and every bucket has been read.
+        __shared__ bool s_last;
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicAdd(t.flags[t.rank] + kFlagCount, 1u) == gridDim.x - 1;
+        __syncthreads();
+        if (s_last) {
+            if (threadIdx.x == 0) t.flags[t.rank][kFlagCount] = 0;  // for the next launch
+            __threadfence_system();
+            if (threadIdx.x < t.world) {
+                st_release_sys(t.flags[threadIdx.x] + kFlagDone + t.rank, t.epoch);
+                while ((int32_t)(ld_acquire_sys(t.flags[t.rank] + kFlagDone + threadIdx.x) - t.epoch) < 0) {}
+            }
+        }
     }
 }
 
@@ -264,14 +307,41 @@ int ghr_ipc_close(void* base)
     return cudaIpcCloseMemHandle(base) == cudaSuccess ? GHR_OK : GHR_ERR_CUDA;
 }
 
+static int adam_sharded_impl(int world, int rank, const float* const* peer_grads, float* const* peer_params,
+                             float* exp_avg_shard, float* exp_avg_sq_shard, int64_t shard_lo, int64_t shard_hi, int n_groups,
+                             const ghr_shard_group* groups, double beta1, double beta2, double eps,
+                             uint32_t* const* peer_flags, uint32_t epoch, void* stream);
+
 int ghr_adam_step_sharded(int world, int rank, const float* const* peer_grads, float* const* peer_params, float* exp_avg_shard,
                           float* exp_avg_sq_shard, int64_t shard_lo, int64_t shard_hi, int n_groups,
                           const ghr_shard_group* groups, double beta1, double beta2, double eps, void* stream)
 {
+    return adam_sharded_impl(world, rank, peer_grads, peer_params, exp_avg_shard, exp_avg_sq_shard, shard_lo, shard_hi,
+                             n_groups, groups, beta1, beta2, eps, nullptr, 0, stream);
+}
+
+int ghr_adam_step_sharded_synced(int world, int rank, const float* const* peer_grads, float* const* peer_params,
+                                 float* exp_avg_shard, float* exp_avg_sq_shard, int64_t shard_lo, int64_t shard_hi,
+                                 int n_groups, const ghr_shard_group* groups, double beta1, double beta2, double eps,
+                                 uint32_t* const* peer_flags, uint32_t epoch, void* stream)
+{
+    if (!peer_flags || epoch == 0) return GHR_ERR_BAD_ARG;
+    return adam_sharded_impl(world, rank, peer_grads, peer_params, exp_avg_shard, exp_avg_sq_shard, shard_lo, shard_hi,
+                             n_groups, groups, beta1, beta2, eps, peer_flags, epoch, stream);
+}
+
+int ghr_sharded_flag_words(void) { return 2 * GHR_MAX_PEERS + 8; }
+
+static int adam_sharded_impl(int world, int rank, const float* const* peer_grads, float* const* peer_params,
+                             float* exp_avg_shard, float* exp_avg_sq_shard, int64_t shard_lo, int64_t shard_hi, int n_groups,
+                             const ghr_shard_group* groups, double beta1, double beta2, double eps,
+                             uint32_t* const* peer_flags, uint32_t epoch, void* stream)
+{
     if (world < 1 || world > GHR_MAX_PEERS || rank < 0 || rank >= world || n_groups < 0 || n_groups > GHR_ADAM_MAX_GROUPS)
         return GHR_ERR_BAD_ARG;
     if (shard_lo < 0 || shard_hi < shard_lo || (shard_lo & 3) || (shard_hi & 3)) return GHR_ERR_BAD_ARG;
-    if (shard_hi == shard_lo || n_groups == 0) return GHR_OK;
+    const bool synced = peer_flags != nullptr;  // a rank with nothing to step still takes part in the barriers
+    if ((shard_hi == shard_lo || n_groups == 0) && !synced) return GHR_OK;
     if (!peer_grads || !peer_params || !groups || !exp_avg_shard || !exp_avg_sq_shard || misaligned16(exp_avg_shard) ||
         misaligned16(exp_avg_sq_shard))
         return GHR_ERR_BAD_ARG;
@@ -281,7 +351,10 @@ int ghr_adam_step_sharded(int world, int rank, const float* const* peer_grads, f
         if (!peer_grads[r] || !peer_params[r] || misaligned16(peer_grads[r]) || misaligned16(peer_params[r])) return GHR_ERR_BAD_ARG;
         t.grads[r] = peer_grads[r];
         t.params[r] = peer_params[r];
+        if (synced && (!peer_flags[r] || (reinterpret_cast<uintptr_t>(peer_flags[r]) & 3))) return GHR_ERR_BAD_ARG;
     }
+    for (int r = 0; r < GHR_MAX_PEERS; ++r) t.flags[r] = (synced && r < world) ? peer_flags[r] : nullptr;
+    t.epoch = epoch;
     t.m = exp_avg_shard; t.v = exp_avg_sq_shard; t.lo = shard_lo;
     t.world = world; t.rank = rank; t.n_seg = 0;
     t.w1 = (float)(1.0 - beta1); t.beta2 = (float)beta2; t.w2 = (float)(1.0 - beta2); t.eps = (float)eps;
@@ -301,7 +374,12 @@ int ghr_adam_step_sharded(int world, int rank, const float* const* peer_grads, f
         t.first_chunk[t.n_seg++] = (uint32_t)chunks;
         chunks += (uint64_t)((e - b + kAdamChunk - 1) / kAdamChunk);
     }
-    if (t.n_seg == 0) return GHR_OK;
+    if (t.n_seg == 0) {
+        if (!synced) return GHR_OK;
+        t.seg[0].begin = t.seg[0].end = 0;  // one CTA, no elements: barriers only
+        t.first_chunk[0] = 0;
+        chunks = 1;
+    }
     cudaStream_t s = (cudaStream_t)stream;
     StageTimer timer(GHR_STAGE_OPTIMIZER, s);
     adam_sharded_kernel<<<(unsigned)chunks, kAdamThreads, 0, s>>>(t);

@@ -150,8 +150,13 @@ class ShardedFusedAdam:
     groups: list of dict(name=, offset=, count=, lr=) in the flat layout (flat_layout); lr may be changed between steps
     like a torch param_group (update_learning_rate, scene/gaussian_model.py:290-295)."""
 
-    def __init__(self, flat_params, flat_grads, groups, betas=(0.9, 0.999), eps=1e-8, group=None):
+    def __init__(self, flat_params, flat_grads, groups, betas=(0.9, 0.999), eps=1e-8, group=None, sync="flags"):
+        """sync: "flags" = the two cross-rank barriers of a step are flag exchanges in peer memory INSIDE the kernel (no
+        NCCL call in step()); "nccl" = one-element NCCL all-reduces around the kernel."""
         import torch.distributed as dist
+        if sync not in ("flags", "nccl"):
+            raise ValueError("sync must be 'flags' or 'nccl'")
+        self.sync = sync
         if not (flat_params.is_cuda and flat_grads.is_cuda and flat_params.dtype == torch.float32
                 and flat_grads.dtype == torch.float32 and flat_params.numel() == flat_grads.numel()
                 and flat_params.is_contiguous() and flat_grads.is_contiguous() and flat_params.numel() % 4 == 0):
@@ -182,16 +187,18 @@ class ShardedFusedAdam:
                 raise RuntimeError(f"ShardedFusedAdam: unexpected CUDA IPC handle of {len(handle)} bytes (expandable "
                                    "segments are not supported: unset PYTORCH_CUDA_ALLOC_CONF=expandable_segments)")
             return handle, int(storage_off) + 4 * int(t.storage_offset())
-        self._shared = [flat_params.detach(), flat_grads.detach()]  # producers keep what they shared alive
+        self._flags = torch.zeros(_lib.lib().ghr_sharded_flag_words(), dtype=torch.int32, device=dev)
+        self._shared = [flat_params.detach(), flat_grads.detach(), self._flags]  # producers keep what they shared alive
         mine = [describe(t) for t in self._shared]
         everyone = [None] * self.world
         dist.all_gather_object(everyone, mine, group=group)
-        p_ptrs, g_ptrs = [], []
+        p_ptrs, g_ptrs, f_ptrs = [], [], []
         with _lib.on_device(dev):
             for r in range(self.world):
                 if r == self.rank:
                     p_ptrs.append(flat_params.data_ptr())
                     g_ptrs.append(flat_grads.data_ptr())
+                    f_ptrs.append(self._flags.data_ptr())
                     continue
                 ptrs = []
                 for handle, off in everyone[r]:
@@ -203,8 +210,10 @@ class ShardedFusedAdam:
                     ptrs.append(base + off)
                 p_ptrs.append(ptrs[0])
                 g_ptrs.append(ptrs[1])
+                f_ptrs.append(ptrs[2])
         self._p_ptrs = (C.c_void_p * self.world)(*p_ptrs)
         self._g_ptrs = (C.c_void_p * self.world)(*g_ptrs)
+        self._f_ptrs = (C.c_void_p * self.world)(*f_ptrs)
         self._token = torch.zeros(1, device=dev)
         dist.barrier(group=group)
 
@@ -222,6 +231,14 @@ class ShardedFusedAdam:
         for e, g in zip(table, self.param_groups):
             e.offset, e.count, e.lr, e.step = int(g["offset"]), int(g["count"]), float(g["lr"]), self.steps
         dev = self.params.device
+        if self.sync == "flags":
+            with _lib.on_device(dev):
+                _lib.check(_lib.lib().ghr_adam_step_sharded_synced(
+                    self.world, self.rank, self._g_ptrs, self._p_ptrs, self.exp_avg.data_ptr(),
+                    self.exp_avg_sq.data_ptr(), self.lo, self.hi, len(self.param_groups), table, float(self.betas[0]),
+                    float(self.betas[1]), float(self.eps), self._f_ptrs, self.steps, _lib.raw_stream(dev.index or 0)),
+                    "ghr_adam_step_sharded_synced")
+            return
         with _lib.on_device(dev):
             self._barrier_on_stream()  # every rank's bucket is complete
             _lib.check(_lib.lib().ghr_adam_step_sharded(

@@ -16,6 +16,15 @@ def main():
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    for sync in ("flags", "nccl"):
+        run(rank, world, dev, sync)
+    if rank == 0:
+        print("SHARDED_ADAM_OK", world, flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def run(rank, world, dev, sync):
     P = 5001  # odd sizes: padded groups, ragged last shard
     shapes = {"xyz": (P, 3), "log_scale": (P, 3), "rotation": (P, 4), "features": (P, 16, 3), "opacity_logit": (P, 1)}
     lrs = {"xyz": 1.6e-4, "log_scale": 5e-3, "rotation": 1e-3, "features": 2.5e-3, "opacity_logit": 5e-2}
@@ -26,7 +35,7 @@ def main():
     assert flat.numel() == total and total % 4 == 0
     bucket = torch.zeros_like(flat)
     groups = [dict(name=k, offset=table[k][0], count=table[k][1], lr=lrs[k]) for k in shapes]
-    opt = ShardedFusedAdam(flat, bucket, groups, eps=1e-15)
+    opt = ShardedFusedAdam(flat, bucket, groups, eps=1e-15, sync=sync)
     lo, hi = shard_bounds(total, world, rank)
     assert (opt.lo, opt.hi) == (lo, hi) and opt.exp_avg.numel() >= hi - lo
     # the unfused path on copies: all-reduce the bucket, FusedAdam over the separate tensors
@@ -61,10 +70,6 @@ def main():
         other = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(other, mine)
         assert all(torch.equal(o, other[0]) for o in other)
-    if rank == 0:
-        print("SHARDED_ADAM_OK", world, flush=True)
-    dist.barrier()
-    dist.destroy_process_group()
 
 
 if __name__ == "__main__":

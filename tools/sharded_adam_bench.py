@@ -53,7 +53,8 @@ def main():
         total, table = flat_layout(leaves)
         bucket = torch.randn(total, generator=torch.Generator().manual_seed(1 + rank)).to(dev) * 1e-3
         groups = [dict(name=k, offset=table[k][0], count=table[k][1], lr=LRS[k]) for k in SHAPES]
-        fused = ShardedFusedAdam(flat, bucket, groups, eps=1e-15)
+        fused = ShardedFusedAdam(flat, bucket, groups, eps=1e-15, sync="flags")
+        fused_nccl = ShardedFusedAdam(flat, bucket, groups, eps=1e-15, sync="nccl")
         ref = {k: torch.nn.Parameter(v.clone()) for k, v in leaves.items()}
         for k in ref:
             o, n = table[k]
@@ -75,12 +76,13 @@ def main():
 
         res = {"P": P, "floats": total, "world": world,
                "fused_ms": round(timed(fused.step, dev), 4),
+               "fused_nccl_barriers_ms": round(timed(fused_nccl.step, dev), 4),
                "unfused_allreduce_plus_fused_adam_ms": round(timed(unfused, dev), 4),
                "allreduce_only_ms": round(timed(lambda: dist.all_reduce(bucket), dev), 4),
                "allreduce_plus_torch_adam_ms": round(timed(torch_path, dev), 4),
                "nvlink_bytes_per_rank": int(2 * 4 * total * (world - 1) / world)}
         out.append(res)
-        del fused
+        del fused, fused_nccl
     if rank == 0:
         sys.stderr.flush()
         print(json.dumps({"sharded_adam": out, "gpu": torch.cuda.get_device_name(0)}), flush=True)
