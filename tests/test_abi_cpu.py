@@ -141,6 +141,10 @@ def test_new_entry_points_reject_bad_arguments_without_touching_the_gpu():
     assert l.ghr_adam_step_sharded(2, 0, None, None, None, None, 2, 8, 1, g, 0.9, 0.999, 1e-15, None) == BAD   # unaligned shard
     assert l.ghr_adam_step_sharded(2, 0, None, None, None, None, 8, 8, 1, g, 0.9, 0.999, 1e-15, None) == OK    # empty shard
     assert l.ghr_adam_step_sharded(2, 0, None, None, None, None, 0, 8, 1, g, 0.9, 0.999, 1e-15, None) == BAD   # null tables
+    assert l.ghr_adam_step_sharded_synced(2, 0, None, None, None, None, 0, 8, 1, g, 0.9, 0.999, 1e-15, None, 1, None) == BAD  # flags
+    f = (C.c_void_p * 2)()
+    assert l.ghr_adam_step_sharded_synced(2, 0, None, None, None, None, 0, 8, 1, g, 0.9, 0.999, 1e-15, f, 0, None) == BAD     # epoch >= 1
+    assert l.ghr_sharded_flag_words() >= 17
     assert l.ghr_enable_peer_access(-1) == BAD
     assert l.ghr_ipc_open(None, None) == BAD and l.ghr_ipc_close(None) == OK
     # ghr_densify_stats
