@@ -117,6 +117,12 @@ const char* ghr_error_string(int status);
  * the binning buffer can hold (the reference sizes it exactly from a blocking
  * D2H read of num_rendered, rasterizer_impl.cu:283-287).                     */
 int ghr_state_layout(int32_t P, int64_t capacity, int32_t W, int32_t H, ghr_layout* out);
+/* The capacity (a multiple of 64) whose binning buffer is exactly `binning_bytes` long, or -1 if there is none.  The
+ * reference's backward takes only the buffer and num_rendered (dgr/rasterize_points.cu:122-147); here the buffer may have
+ * been sized from a guess larger than num_rendered, and its array offsets depend on that capacity, so the backward entry
+ * points recover it from the size (binning_bytes is strictly increasing in the capacity) instead of trusting a side
+ * table, and reject a buffer whose size does not match the capacity they are given (GHR_ERR_BUFFER). */
+int64_t ghr_binning_capacity(int32_t P, int32_t W, int32_t H, size_t binning_bytes);
 
 /*
  * Stage 1 of Rasterizer::forward (dgr/cuda_rasterizer/rasterizer_impl.cu:198-283):
@@ -474,6 +480,14 @@ int ghr_adam_step_sharded_synced(int world, int rank, const float* const* peer_g
                                  int n_groups, const ghr_shard_group* groups, double beta1, double beta2, double eps,
                                  uint32_t* const* peer_flags, uint32_t epoch, void* stream);
 int ghr_sharded_flag_words(void);
+/* The in-kernel waits are BOUNDED (GHR_SHARDED_TIMEOUT_MS, default 20 000 ms): a rank whose peer never arrives (its host
+ * raised before the launch, it skipped a step, its epoch differs) gives up, skips its update, latches the reason in word
+ * ghr_sharded_error_word() of ITS flag buffer (1 = timed out waiting for the buckets, 2 = timed out waiting for the
+ * replicas, 3 = aborted by a peer) and raises the abort word of every peer, so that the whole node stops at once.  The
+ * host reads the error word at its next synchronisation point (ShardedFusedAdam.check()).  ghr_sharded_abort raises the
+ * abort word of every rank from the host side (enqueued on `stream`): call it when a step cannot be launched. */
+int ghr_sharded_error_word(void);
+int ghr_sharded_abort(int world, uint32_t* const* peer_flags, void* stream);
 /* Lets kernels on the CURRENT device dereference memory of `peer_device` (cudaDeviceEnablePeerAccess; already enabled
  * is not an error).  Needed once per peer before ghr_adam_step_sharded. */
 int ghr_enable_peer_access(int peer_device);

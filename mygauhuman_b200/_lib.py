@@ -80,6 +80,7 @@ SIGNATURES = {
     "ghr_version": (C.c_int, []),
     "ghr_error_string": (C.c_char_p, [C.c_int]),
     "ghr_state_layout": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.POINTER(Layout)]),
+    "ghr_binning_capacity": (C.c_int64, [C.c_int32, C.c_int32, C.c_int32, C.c_size_t]),
     "ghr_forward_preprocess": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
                                          C.c_void_p]),
     "ghr_forward_render": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
@@ -132,6 +133,8 @@ SIGNATURES = {
                                                C.c_int64, C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_double,
                                                C.c_void_p, C.c_uint32, C.c_void_p]),
     "ghr_sharded_flag_words": (C.c_int, []),
+    "ghr_sharded_error_word": (C.c_int, []),
+    "ghr_sharded_abort": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p]),
     "ghr_enable_peer_access": (C.c_int, [C.c_int]),
     "ghr_ipc_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
     "ghr_ipc_close": (C.c_int, [C.c_void_p]),
@@ -195,7 +198,12 @@ class on_device:
     __slots__ = ("idx", "ctx")
 
     def __init__(self, dev):
-        self.idx = dev.index if dev.index is not None else 0
+        # a device without an index ("cuda") means the CURRENT device, as everywhere in torch -- not device 0
+        if dev.index is not None:
+            self.idx = dev.index
+        else:
+            import torch
+            self.idx = torch._C._cuda_getDevice()
         self.ctx = None
 
     def __enter__(self):

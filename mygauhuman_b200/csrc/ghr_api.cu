@@ -91,13 +91,30 @@ int ghr_state_layout(int32_t P, int64_t capacity, int32_t W, int32_t H, ghr_layo
     const size_t cap = (size_t)capacity;
     o = 0;
     L->b_header = o; o += align_up(sizeof(SortHeader));
-    L->b_status = o; o += align_up(sizeof(uint32_t) * (size_t)L->sort_passes * (size_t)sort_tiles(capacity) * kRadix);
+    // The look-back area is never smaller than at a smaller capacity (the keys-per-tile regime changes at two capacity
+    // thresholds, where the tile count halves): binning_bytes is then strictly increasing in the capacity (multiples of
+    // 64), which is what lets ghr_binning_capacity recover the capacity from the buffer size alone.
+    L->b_status = o; o += align_up(sort_status_bytes_monotone(L->sort_passes, capacity));
     L->b_keys_a = o; o += align_up(sizeof(uint64_t) * cap);
     L->b_keys_b = o; o += align_up(sizeof(uint64_t) * cap);
     L->b_vals_a = o; o += align_up(sizeof(uint32_t) * cap);
     L->b_vals_b = o; o += align_up(sizeof(uint32_t) * cap);
     L->binning_bytes = o;
     return GHR_OK;
+}
+
+int64_t ghr_binning_capacity(int32_t P, int32_t W, int32_t H, size_t binning_bytes)
+{
+    // binning_bytes is strictly increasing over capacities that are multiples of 64 (ghr_state_layout): bisect
+    ghr_layout L;
+    int64_t lo = 0, hi = (int64_t(1) << 30) / 64 - 1;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) / 2;
+        if (ghr_state_layout(P, mid * 64, W, H, &L) != GHR_OK) return -1;
+        if (L.binning_bytes < binning_bytes) lo = mid + 1; else hi = mid;
+    }
+    if (ghr_state_layout(P, lo * 64, W, H, &L) != GHR_OK || L.binning_bytes != binning_bytes) return -1;
+    return lo * 64;
 }
 
 int ghr_forward_preprocess(const ghr_raster_params* prm, int32_t* radii, void* geom, size_t geom_bytes,
@@ -149,7 +166,8 @@ static int forward_render_impl(const ghr_raster_params* prm, void* geom, size_t 
         return r;
     }
     // one memset clears the sort header (tickets, histograms) and every pass's look-back words
-    r = check_cuda(cudaMemsetAsync(b + L.b_header, 0, L.b_keys_a - L.b_header, s), "binning memset");
+    r = check_cuda(cudaMemsetAsync(b + L.b_header, 0, (L.b_status - L.b_header) + sort_status_bytes(L.sort_passes, capacity), s),
+                   "binning memset");
     if (r != GHR_OK) return r;
     const uint32_t* n_dev = reinterpret_cast<const uint32_t*>(g + L.g_header);
     if (capacity > 0 && prm->P > 0) {
@@ -273,7 +291,7 @@ int ghr_backward(const ghr_raster_params* prm, const int32_t* radii, const void*
     ghr_layout L;
     if (ghr_state_layout(prm->P, capacity, prm->W, prm->H, &L) != GHR_OK) return GHR_ERR_BAD_ARG;
     if (!geom || geom_bytes < L.geom_bytes || !img || img_bytes < L.img_bytes || !binning ||
-        binning_bytes < L.binning_bytes)
+        binning_bytes != L.binning_bytes)  // a different size means a different capacity, i.e. different array offsets
         return GHR_ERR_BUFFER;
     r = stage_done(prm,
                    launch_blend_backward(*prm, (const char*)geom, (const char*)binning, (const char*)img, L,
@@ -292,7 +310,7 @@ static int multi_layout(const ghr_raster_params* prm, int64_t capacity, const vo
 {
     if (ghr_state_layout(prm->P, capacity, prm->W, prm->H, L) != GHR_OK) return GHR_ERR_BAD_ARG;
     if (!geom || geom_bytes < L->geom_bytes || !img || img_bytes < L->img_bytes || !binning ||
-        binning_bytes < L->binning_bytes)
+        binning_bytes != L->binning_bytes)  // a different size means a different capacity, i.e. different array offsets
         return GHR_ERR_BUFFER;
     return GHR_OK;
 }

@@ -77,6 +77,8 @@ __global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_kernel(ghr_geom_header*
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicMax(&hdr->error, (uint32_t)(-GHR_ERR_CAPACITY));
         return;
     }
+    // a render stage re-run with a large enough buffer (optimistic launch, _C.py) clears the latch the first try left
+    if (blockIdx.x == 0 && threadIdx.x == 0 && hdr->error == (uint32_t)(-GHR_ERR_CAPACITY)) hdr->error = 0;
     const uint32_t sel = sh->sorted_sel;
     const uint64_t* __restrict__ keys = sel ? keys_b : keys_a;
     const uint32_t* __restrict__ vals = sel ? vals_b : vals_a;
@@ -229,7 +231,7 @@ cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, cha
     cudaError_t e = cudaMemsetAsync(img + L.i_ranges, 0, sizeof(uint2) * (size_t)tiles, s);
     if (e != cudaSuccess) return e;
     int64_t grid = (capacity + GHR_BLOCK - 1) / GHR_BLOCK;
-    if (grid > 148 * 16) grid = 148 * 16;
+    if (grid > sm_count() * 16) grid = sm_count() * 16;
     if (grid < 1) grid = 1;
     tile_ranges_kernel<<<(unsigned)grid, GHR_BLOCK, 0, s>>>(
         reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header), capacity,

@@ -512,7 +512,7 @@ static cudaError_t launch_bwd_config(int ctas_per_sm, const ghr_raster_params& p
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
     const int64_t items = (int64_t)tiles * 16;
     int64_t ctas = (items + kBwdWarps - 1) / kBwdWarps;
-    if (ctas > 148 * ctas_per_sm) ctas = 148 * ctas_per_sm;
+    if (ctas > (int64_t)sm_count() * ctas_per_sm) ctas = (int64_t)sm_count() * ctas_per_sm;
     auto kernel = blend_backward_kernel<BATCH, NSTAGE, NX>;
     const size_t smem = blend_bwd_warp_smem<BATCH, NSTAGE, NX>() * kBwdWarps;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -284,7 +284,7 @@ cudaError_t launch_blend_backward_wide(const ghr_raster_params& p, const char* g
     const int64_t items = (int64_t)tiles * 8;
     int64_t ctas = (items + kWideBwdWarps - 1) / kWideBwdWarps;
     const int per_sm = blend_shared_gpu() ? kWideBwdCtasPerSm / 2 : kWideBwdCtasPerSm;  // see ghr_blend_fwd_wide.cu
-    if (ctas > 148 * per_sm) ctas = 148 * per_sm;
+    if (ctas > (int64_t)sm_count() * per_sm) ctas = (int64_t)sm_count() * per_sm;
     blend_backward_wide_kernel<<<(unsigned)ctas, kWideBwdWarps * 32, 0, s>>>(
         p.W, p.H, tiles, reinterpret_cast<const uint2*>(img + L.i_ranges),
         reinterpret_cast<const uint32_t*>(img + L.i_order), reinterpret_cast<const SortHeader*>(binning + L.b_header),

@@ -6,24 +6,24 @@
 // independently of every other warp (no block-level barrier anywhere).  Two
 // lanes serve each pixel ("slots"): lane p and lane p+16 evaluate different
 // Gaussians of the pixel's list at the same time.  The kernel is persistent:
-// 148 x 5 CTAs of 4 warps pull items from a global queue ordered by decreasing
-// tile-list length (tile_order_kernel), so the few heavy tiles of a
-// human-shaped scene start first and spread over all SMs.  Per warp, Gaussians
-// are staged in batches of 64 packed 48-byte records
+// (SM count) x 8 single-warp CTAs pull items from a global queue ordered by
+// decreasing tile-list length (tile_order_kernel), so the few heavy tiles of a
+// human-shaped scene start first and spread over all SMs.  Per warp, list
+// entries are staged in rounds of 256 (128 when several views share the GPU,
+// ghr_set_shared_gpu) packed 48-byte records
 //   {px,py,depth,radius | conic.xyz,opacity | r,g,b,cull-extent}
-// with cp.async (LDGSTS) into a 3-deep private shared-memory ring (list ids are
-// fetched one batch ahead of the record copies), so the inner loop never
+// with cp.async (LDGSTS) into a 2-deep private shared-memory ring (list entries
+// are fetched one round ahead of the record copies), so the inner loop never
 // touches global memory (the reference gathers colour and depth from global per
 // contributing pair, forward.cu:360,362).
 //
-// Per warp and batch: (1) each lane tests one Gaussian's conservative bounding
-// box (pack_cull_extent) against the warp's 4x4 block; a ballot yields the
-// survivors -- at a Gaussian footprint of ~8 px a 4x4 block keeps less than
-// half of what an 8x4 block keeps, and every survivor costs 32 lanes of
-// arithmetic whether or not a pixel is touched.  (2) Survivors are taken four
-// at a time in list order; slot 0 evaluates the 1st and 3rd, slot 1 the 2nd and
-// 4th (power/exp/alpha, independent -> ILP), the alphas are exchanged with one
-// shuffle each, and both lanes run the transmittance recurrence over all four.
+// Per warp and round: (1) only entries whose per-entry 4x4-block mask
+// (tile_ranges_kernel: bounding box, then the exact ellipse-vs-block test) has
+// this block's bit are staged; their bits form the round's survivor words.
+// (2) Survivors are taken KSTEP = 8 at a time in list order, across the 32-entry
+// words; slot 0 evaluates the even ones, slot 1 the odd ones (power/exp/alpha,
+// independent -> ILP), the alphas are exchanged with one shuffle each, and both
+// lanes run the transmittance recurrence over all eight.
 // The five accumulators are split between the two lanes of a pixel (slot 0:
 // red, green, alpha-mask; slot 1: blue, depth), each accumulated in list order.
 // Skipped Gaussians are exactly those the reference's per-pixel tests
@@ -336,7 +336,7 @@ static cudaError_t launch_fwd_config(int ctas_per_sm, const ghr_raster_params& p
     const int tiles = ((p.W + GHR_TILE - 1) / GHR_TILE) * ((p.H + GHR_TILE - 1) / GHR_TILE);
     const int64_t items = (int64_t)tiles * 16;
     int64_t ctas = (items + WARPS - 1) / WARPS;
-    if (ctas > 148 * ctas_per_sm) ctas = 148 * ctas_per_sm;
+    if (ctas > (int64_t)sm_count() * ctas_per_sm) ctas = (int64_t)sm_count() * ctas_per_sm;
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
     auto kernel = blend_forward_kernel<BATCH, NSTAGE, WARPS, NX>;
     const size_t smem = blend_fwd_warp_smem<BATCH, NSTAGE, NX>() * WARPS;

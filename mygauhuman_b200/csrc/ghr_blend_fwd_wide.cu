@@ -10,7 +10,7 @@
 // Work decomposition (ours): a 16x16 tile is covered by eight 8x4 pixel blocks;
 // one (tile, block) pair is a work item processed by ONE warp, independently of
 // every other warp (no block-level barrier anywhere).  The kernel is persistent:
-// 148 x 5 CTAs of 4 warps pull items from a global queue ordered by decreasing
+// (SM count) x 5 CTAs of 4 warps pull items from a global queue ordered by decreasing
 // tile-list length (tile_order_kernel), so the few heavy tiles of a human-shaped
 // scene start first and spread over all SMs.  Per warp, Gaussians are staged in
 // batches of 64 packed 48-byte records
@@ -213,7 +213,7 @@ cudaError_t launch_blend_forward_wide(const ghr_raster_params& p, const char* ge
     int64_t ctas = (items + kWideWarps - 1) / kWideWarps;
     // several views in flight (ghr_set_shared_gpu): leave half of every SM's shared memory to another view's blend
     const int per_sm = blend_shared_gpu() ? (kWideCtasPerSm + 1) / 2 : kWideCtasPerSm;
-    if (ctas > 148 * per_sm) ctas = 148 * per_sm;
+    if (ctas > (int64_t)sm_count() * per_sm) ctas = (int64_t)sm_count() * per_sm;
     const int64_t capacity = L.capacity;
     ghr_geom_header* hdr = reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header);
     cudaError_t e = cudaMemsetAsync(&hdr->blend_fwd_ticket, 0, sizeof(uint32_t), s);  // render may run twice per preprocess

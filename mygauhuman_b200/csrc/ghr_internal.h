@@ -56,6 +56,21 @@ inline int64_t sort_tiles(int64_t capacity)
     return (capacity + tile - 1) / tile;
 }
 
+// Bytes of decoupled-look-back words the onesweep passes use at this capacity, and the never-shrinking figure the
+// layout reserves (see ghr_state_layout).
+inline size_t sort_status_bytes(int passes, int64_t capacity)
+{
+    return sizeof(uint32_t) * (size_t)passes * (size_t)sort_tiles(capacity) * kRadix;
+}
+inline size_t sort_status_bytes_monotone(int passes, int64_t capacity)
+{
+    size_t b = sort_status_bytes(passes, capacity);
+    const int64_t thresholds[2] = {int64_t(1) << 17, int64_t(3) << 17};  // regime ends of sort_items_per_thread
+    for (int64_t t : thresholds)
+        if (capacity > t) { const size_t at = sort_status_bytes(passes, t); b = b > at ? b : at; }
+    return b;
+}
+
 // Blend kernels: staging configuration by problem size (see ghr_blend_fwd.cu).  `capacity` bounds the number of
 // (Gaussian, tile) pairs; GHR_BLEND_REGIME=latency|throughput overrides (tuning).
 inline bool blend_throughput_regime(int64_t capacity)
@@ -80,6 +95,10 @@ inline int blend_shared_gpu()  // 0: one view owns the GPU (256-entry staging ro
 }
 
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// Streaming multiprocessors of the CURRENT device (148 on B200), queried once per device and cached (ghr_profile.cu):
+// every persistent / grid-capped launch sizes itself as a multiple of this.
+int sm_count();
 
 // rasterizer_impl.cu:35-50 getHigherMsb
 inline uint32_t higher_msb(uint32_t n)

@@ -56,7 +56,7 @@ int launch(bool pack, const PlyFields& f, float* rows, cudaStream_t s)
 {
     const int64_t total = (int64_t)f.P * (18 + 3 * f.M);
     int64_t grid = (total + 255) / 256;
-    if (grid > 148 * 32) grid = 148 * 32;
+    if (grid > sm_count() * 32) grid = sm_count() * 32;
     StageTimer timer(GHR_STAGE_MISC, s);
     if (pack) ply_rows_kernel<true><<<(unsigned)grid, 256, 0, s>>>(f, rows);
     else ply_rows_kernel<false><<<(unsigned)grid, 256, 0, s>>>(f, rows);

@@ -439,7 +439,7 @@ cudaError_t launch_knn(int P, const float* points, float* out, char* ws, size_t 
     const int init[6] = {0x7F7FFFFF, 0x7F7FFFFF, 0x7F7FFFFF, (int)0x80800000, (int)0x80800000, (int)0x80800000};
     cudaError_t e = cudaMemcpyAsync(aabb, init, sizeof(init), cudaMemcpyHostToDevice, s);
     if (e != cudaSuccess) return e;
-    knn_aabb_kernel<<<148 * 4, 256, 0, s>>>(P, points, aabb);
+    knn_aabb_kernel<<<sm_count() * 4, 256, 0, s>>>(P, points, aabb);
     knn_grid_setup_kernel<<<1, 1, 0, s>>>(P, aabb, grid, kMaxCells);
     e = cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (size_t)kMaxCells, s);
     if (e != cudaSuccess) return e;
@@ -473,7 +473,7 @@ static cudaError_t build_grid(int P, const float* points, char* ws, int max_cell
     const int init[6] = {0x7F7FFFFF, 0x7F7FFFFF, 0x7F7FFFFF, (int)0x80800000, (int)0x80800000, (int)0x80800000};
     cudaError_t e = cudaMemcpyAsync(aabb, init, sizeof(init), cudaMemcpyHostToDevice, s);
     if (e != cudaSuccess) return e;
-    knn_aabb_kernel<<<148 * 4, 256, 0, s>>>(P, points, aabb);
+    knn_aabb_kernel<<<sm_count() * 4, 256, 0, s>>>(P, points, aabb);
     knn_grid_setup_kernel<<<1, 1, 0, s>>>(P, aabb, grid, max_cells);
     e = cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (size_t)max_cells, s);
     if (e != cudaSuccess) return e;
@@ -508,7 +508,7 @@ cudaError_t launch_nearest_vertex(int P, const float* query, int V, const char* 
             attr_set = true;
         }
         const int need = (P + 127) / 128;  // 128 eight-lane groups per 1024-thread block
-        const int blocks = need < 148 ? need : 148;
+        const int blocks = need < sm_count() ? need : sm_count();
         nearest_vertex_smem_kernel<<<blocks, 1024, smem, s>>>(P, V, query, grid, starts, sorted, vid);
     } else {
         nearest_vertex_kernel<<<(P + 127) / 128, 128, 0, s>>>(P, query, grid, starts, sorted, vid);

@@ -321,7 +321,7 @@ cudaError_t launch_lbs_pose_backward(const ghr_lbs_model& m, const float* pose_t
         cudaError_t e = cudaMemsetAsync(dpf_scratch, 0, sizeof(float) * GHR_LBS_POSE_DIM, s);
         if (e != cudaSuccess) return e;
         count_launch();
-        lbs_vertex_offsets_backward_kernel<<<148, 224, 0, s>>>(m.V * 3, m.posedirs, doff, dpf_scratch);
+        lbs_vertex_offsets_backward_kernel<<<sm_count(), 224, 0, s>>>(m.V * 3, m.posedirs, doff, dpf_scratch);
         dpf = dpf_scratch;
     }
     count_launch();

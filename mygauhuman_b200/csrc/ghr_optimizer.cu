@@ -140,8 +140,13 @@ struct ShardTable {
     // [ARRIVE + q] / [DONE + q] = last step for which rank q has arrived / finished, [COUNT] = local CTA counter
     uint32_t* flags[GHR_MAX_PEERS];
     uint32_t epoch;
+    unsigned long long spin_budget_ns;  // a wait that lasts longer than this gives up (see wait_for_peers)
 };
-constexpr int kFlagArrive = 0, kFlagDone = GHR_MAX_PEERS, kFlagCount = 2 * GHR_MAX_PEERS;
+// [ERROR]: 0 or why this rank gave up a wait (kSpin*), latched until the host clears it; [ABORT]: non-zero = some rank
+// gave up or its host raised (ghr_sharded_abort) -- every wait on every rank then returns at once
+constexpr int kFlagArrive = 0, kFlagDone = GHR_MAX_PEERS, kFlagCount = 2 * GHR_MAX_PEERS, kFlagError = kFlagCount + 1,
+              kFlagAbort = kFlagCount + 2;
+constexpr uint32_t kSpinTimeoutArrive = 1, kSpinTimeoutDone = 2, kSpinAborted = 3;
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v)
 {
@@ -154,6 +159,42 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
     return v;
 }
 
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long v;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v));
+    return v;
+}
+
+// Thread q < world waits until peer q has published `epoch` in this rank's word `base + q`.  The wait is BOUNDED: a peer
+// that never launches (its host raised, it skipped a step, its step count differs) must not hang every GPU of the node.
+// After spin_budget_ns, or as soon as somebody raised the abort word, the wait gives up: the reason is latched in this
+// rank's error word, the abort word of every peer is raised (so they stop at once instead of timing out one by one) and
+// false is returned -- the caller then skips its work.  The host sees the error at its next ShardedFusedAdam.check().
+__device__ __forceinline__ bool wait_for_peers(const ShardTable& t, int base, uint32_t timeout_code)
+{
+    bool ok = true;
+    if (threadIdx.x < t.world) {
+        const uint32_t* word = t.flags[t.rank] + base + threadIdx.x;
+        const uint32_t* abort_word = t.flags[t.rank] + kFlagAbort;
+        const unsigned long long t0 = global_ns();
+        uint32_t spins = 0;
+        while ((int32_t)(ld_acquire_sys(word) - t.epoch) < 0) {
+            if ((++spins & 63u) != 0) continue;
+            uint32_t why = 0;
+            if (ld_acquire_sys(abort_word) != 0) why = kSpinAborted;
+            else if (global_ns() - t0 > t.spin_budget_ns) why = timeout_code;
+            if (why) {
+                atomicCAS(t.flags[t.rank] + kFlagError, 0u, why);
+                for (int r = 0; r < t.world; ++r) st_release_sys(t.flags[r] + kFlagAbort, t.epoch);
+                ok = false;
+                break;
+            }
+        }
+    }
+    return __syncthreads_and(ok) != 0;
+}
+
 __global__ void __launch_bounds__(kAdamThreads) adam_sharded_kernel(const __grid_constant__ ShardTable t)
 {
     const bool synced = t.flags[0] != nullptr;
@@ -162,9 +203,7 @@ __global__ void __launch_bounds__(kAdamThreads) adam_sharded_kernel(const __grid
         // every peer, then wait until every peer has said the same.  Every CTA polls this rank's OWN flag words only.
         if (blockIdx.x == 0 && threadIdx.x < t.world)
             st_release_sys(t.flags[threadIdx.x] + kFlagArrive + t.rank, t.epoch);
-        if (threadIdx.x < t.world)
-            while ((int32_t)(ld_acquire_sys(t.flags[t.rank] + kFlagArrive + threadIdx.x) - t.epoch) < 0) {}
-        __syncthreads();
+        if (!wait_for_peers(t, kFlagArrive, kSpinTimeoutArrive)) return;  // gave up: no update, error latched
     }
     int k = 0;
 #pragma unroll 1
@@ -207,12 +246,24 @@ __global__ void __launch_bounds__(kAdamThreads) adam_sharded_kernel(const __grid
         if (s_last) {
             if (threadIdx.x == 0) t.flags[t.rank][kFlagCount] = 0;  // for the next launch
             __threadfence_system();
-            if (threadIdx.x < t.world) {
-                st_release_sys(t.flags[threadIdx.x] + kFlagDone + t.rank, t.epoch);
-                while ((int32_t)(ld_acquire_sys(t.flags[t.rank] + kFlagDone + threadIdx.x) - t.epoch) < 0) {}
-            }
+            if (threadIdx.x < t.world) st_release_sys(t.flags[threadIdx.x] + kFlagDone + t.rank, t.epoch);
+            (void)wait_for_peers(t, kFlagDone, kSpinTimeoutDone);
         }
     }
+}
+
+__global__ void sharded_abort_kernel(ShardTable t)
+{
+    if ((int)threadIdx.x < t.world) st_release_sys(t.flags[threadIdx.x] + kFlagAbort, 0xFFFFFFFFu);
+}
+unsigned long long spin_budget_ns()
+{
+    static const unsigned long long ns = [] {
+        const char* e = getenv("GHR_SHARDED_TIMEOUT_MS");
+        const double ms = e ? atof(e) : 20000.0;
+        return (unsigned long long)((ms > 0 ? ms : 20000.0) * 1e6);
+    }();
+    return ns;
 }
 
 inline bool misaligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) != 0; }
@@ -331,6 +382,22 @@ int ghr_adam_step_sharded_synced(int world, int rank, const float* const* peer_g
 }
 
 int ghr_sharded_flag_words(void) { return 2 * GHR_MAX_PEERS + 8; }
+int ghr_sharded_error_word(void) { return kFlagError; }
+
+
+int ghr_sharded_abort(int world, uint32_t* const* peer_flags, void* stream)
+{
+    if (world < 1 || world > GHR_MAX_PEERS || !peer_flags) return GHR_ERR_BAD_ARG;
+    ShardTable t;
+    for (int r = 0; r < GHR_MAX_PEERS; ++r) {
+        t.flags[r] = r < world ? peer_flags[r] : nullptr;
+        if (r < world && !peer_flags[r]) return GHR_ERR_BAD_ARG;
+    }
+    t.world = world;
+    sharded_abort_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(t);
+    count_launch();
+    return cudaGetLastError() == cudaSuccess ? GHR_OK : GHR_ERR_CUDA;
+}
 
 static int adam_sharded_impl(int world, int rank, const float* const* peer_grads, float* const* peer_params,
                              float* exp_avg_shard, float* exp_avg_sq_shard, int64_t shard_lo, int64_t shard_hi, int n_groups,
@@ -355,6 +422,7 @@ static int adam_sharded_impl(int world, int rank, const float* const* peer_grads
     }
     for (int r = 0; r < GHR_MAX_PEERS; ++r) t.flags[r] = (synced && r < world) ? peer_flags[r] : nullptr;
     t.epoch = epoch;
+    t.spin_budget_ns = spin_budget_ns();
     t.m = exp_avg_shard; t.v = exp_avg_sq_shard; t.lo = shard_lo;
     t.world = world; t.rank = rank; t.n_seg = 0;
     t.w1 = (float)(1.0 - beta1); t.beta2 = (float)beta2; t.w2 = (float)(1.0 - beta2); t.eps = (float)eps;

@@ -37,6 +37,19 @@ cudaEvent_t get_event()
 }
 }  // namespace
 
+int sm_count()
+{
+    static std::atomic<int> cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int n = cached[dev].load(std::memory_order_relaxed);
+    if (n == 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev].store(n, std::memory_order_relaxed);
+    }
+    return n;
+}
+
 StageTimer::StageTimer(int stage, cudaStream_t s) : stage_(stage), stream_(s), beg_(nullptr)
 {
     if (!g_profile_on.load(std::memory_order_relaxed)) return;

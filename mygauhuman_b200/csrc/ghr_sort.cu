@@ -291,7 +291,7 @@ cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev
     const int items = sort_items_per_thread(capacity);
     const int64_t tiles = sort_tiles(capacity);
     int64_t hg = (capacity + kSortThreads * 4 - 1) / (kSortThreads * 4);
-    const int hgrid = (int)(hg < 148 * 4 ? hg : 148 * 4);
+    const int hgrid = (int)(hg < sm_count() * 4 ? hg : sm_count() * 4);
     sort_histogram_kernel<<<hgrid, kSortThreads, 0, s>>>(keys_a, n_dev, capacity, bits, passes, hdr);
     count_launch(1 + passes);
     for (int p = 0; p < passes; p++) {

@@ -375,7 +375,7 @@ int ghr_forward_views(const ghr_raster_params* prm, int32_t n_views, const float
     {
         StageTimer t(GHR_STAGE_TILE_RANGES, s);
         int64_t grid = (capacity + GHR_BLOCK - 1) / GHR_BLOCK;
-        grid = grid > 148 * 16 ? 148 * 16 : grid < 1 ? 1 : grid;
+        grid = grid > sm_count() * 16 ? sm_count() * 16 : grid < 1 ? 1 : grid;
         views_ranges_kernel<<<(unsigned)grid, GHR_BLOCK, 0, s>>>(a.hdr, capacity, reinterpret_cast<const SortHeader*>(w + L.s_header),
                                                                  reinterpret_cast<const uint64_t*>(w + L.keys_a),
                                                                  reinterpret_cast<const uint64_t*>(w + L.keys_b),

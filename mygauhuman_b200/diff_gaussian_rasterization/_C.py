@@ -24,17 +24,22 @@ from .._lib import RasterParams, check, lib, state_layout
 # and blending, and re-runs the render stage with an exact-size buffer in the rare case the guess was too small.
 # Results are always exact; unlike the reference's blocking read (rasterizer_impl.cu:283) the GPU never idles.
 _cap_hint = {}      # (device index, P, W, H) -> capacity guess
-_cap_of = {}        # binning buffer data_ptr -> capacity it was laid out for (backward needs it)
 
 
 def _round_cap(n):
     return (int(n) + 63) // 64 * 64
 
 
-def _remember_capacity(binning, capacity):
-    if len(_cap_of) > 4096:
-        _cap_of.clear()
-    _cap_of[binning.data_ptr()] = capacity
+def _capacity_of(binning, P, W, H):
+    """The capacity a binning buffer was laid out for, recovered from its size (ghr_binning_capacity: the size is
+    strictly increasing in the capacity).  The reference's backward gets num_rendered only; here the buffer may be
+    larger than that (optimistic launch, sync-free mode) and its array offsets depend on the capacity, so nothing but
+    the saved tensor itself is trusted: it survives any number of outstanding forwards, hooks that move saved tensors
+    (save_on_cpu) and allocator address reuse."""
+    cap = int(lib().ghr_binning_capacity(int(P), int(W), int(H), binning.numel()))
+    if cap < 0:
+        raise _lib.GhrError(_lib.GHR_ERR_BUFFER, "binningBuffer does not have the size of any binning layout")
+    return cap
 
 
 # Sync-free mode: when set to an int, forward() does not read num_rendered back
@@ -171,7 +176,6 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                     capacity = _round_cap(num_rendered)
                     binning = render(capacity)
             _cap_hint[key] = _round_cap(num_rendered + num_rendered // 4 + 1024)
-        _remember_capacity(binning, capacity)
         if debug:
             read_status(geom, raise_on_error=True)
     global _last_geom
@@ -191,7 +195,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     if P == 0:
         z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
         return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
-    capacity = _cap_of.get(binningBuffer.data_ptr(), int(R))
+    capacity = _capacity_of(binningBuffer, P, W, H)
     with _lib.on_device(dev):
         keep = []
         # opacities are not an input of the reference backward (they live in the saved geometry state)
@@ -271,7 +275,7 @@ def rasterize_gaussians_multi(background, means3D, colors, opacity, scales, rota
     images = [att.images[3 * k:3 * k + 3] for k in range(nf)] if fused else []
     rest = extra[nf:] if fused else extra
     first_colors = _rec_colors(P, W, H, geom).clone() if rest else None
-    capacity = _cap_of.get(binning.data_ptr(), int(num_rendered))
+    capacity = _capacity_of(binning, P, W, H)
     if rest:
         with _lib.on_device(dev):
             keep = []
@@ -302,7 +306,7 @@ def rasterize_gaussians_multi_backward(background, means3D, radii, colors, scale
     if P == 0:
         z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
         return (z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4), [z(0, 3) for _ in extra_colors])
-    capacity = _cap_of.get(binningBuffer.data_ptr(), int(R))
+    capacity = _capacity_of(binningBuffer, P, W, H)
     nf = 0 if packed is None else min(_FUSED_MAX, len(extra_colors) - len(extra_colors) % 2)
     with _lib.on_device(dev):
         keep = []
@@ -393,7 +397,7 @@ def state_views(P, capacity, W, H, geomBuffer, binningBuffer, imageBuffer):
     """Typed views of the internal state the reference keeps in its three buffers.
     `capacity` is the num_rendered the forward returned; the capacity the binning buffer was actually laid
     out for (>= num_rendered) is looked up."""
-    capacity = _cap_of.get(binningBuffer.data_ptr(), capacity) if binningBuffer.numel() else capacity
+    capacity = _capacity_of(binningBuffer, P, W, H) if binningBuffer.numel() else capacity
     L = state_layout(P, capacity, W, H)
     X = W * H
     tiles = ((W + 15) // 16) * ((H + 15) // 16)

@@ -56,7 +56,7 @@ def pack_rows(xyz, features_dc, features_rest, opacity, scaling, rotation, norma
     with _lib.on_device(xyz.device):
         _lib.check(l.ghr_ply_pack_rows(P, M, ptr("xyz"), ptr("normal"), ptr("albedo"), ptr("roughness"), ptr("f_dc"),
                                        ptr("f_rest"), ptr("opacity"), ptr("scaling"), ptr("rotation"),
-                                       rows.data_ptr() if P else None, _lib.raw_stream(xyz.device.index or 0)),
+                                       rows.data_ptr() if P else None, _lib.raw_stream(xyz.device.index)),
                    "ghr_ply_pack_rows")
     return rows
 
@@ -132,6 +132,8 @@ def load_ply(path, device="cuda", max_sh_degree=3):
             raise KeyError(n)
         columns[c] = where[n]
     dev = torch.device(device)
+    if dev.type == "cuda" and dev.index is None:  # "cuda" = the current device
+        dev = torch.device("cuda", torch.cuda.current_device())
     if dev.type != "cuda":
         raise RuntimeError("io_ply: load_ply unpacks on a CUDA device (there is no CPU fallback)")
     P = rows.shape[0]

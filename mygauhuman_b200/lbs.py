@@ -50,6 +50,8 @@ class SMPLDeformer:
         dev = torch.device(device)
         if dev.type != "cuda":
             raise RuntimeError("SMPLDeformer needs a CUDA device (libghr has no CPU fallback)")
+        if dev.index is None:  # "cuda" = the current device, fixed here so every later call agrees on it
+            dev = torch.device("cuda", torch.cuda.current_device())
         lib()
         self.device = dev
         f = lambda k: _f32c(smpl[k].to(dev))
@@ -73,7 +75,7 @@ class SMPLDeformer:
                                self.shapedirs.data_ptr(), self.joint_template.data_ptr(),
                                self.joint_shapedirs.data_ptr(), self.parents.data_ptr())
         self._grid_key, self._grid = None, None
-        self._pose_key, self._pose_cached = None, None
+        self._pose_key, self._pose_cached, self._pose_src = None, None, ()
         self._side_stream = torch.cuda.Stream(device=self.device) if torch.cuda.is_available() else None
         # Optional gradient sink (multi-view accumulation, see graphed.py): dict name -> fp32 contiguous tensor for
         # "xyz", "normals", "scaling", "rotation", "features", "opacity_logit".  When set, the backward kernels ADD the
@@ -98,11 +100,18 @@ class SMPLDeformer:
         return out
 
     def _big_pose_buffer(self, t_params):
-        key = tuple((t_params[k].data_ptr(), t_params[k]._version) for k in ("poses", "shapes", "R", "Th"))
-        if key != self._pose_key:
-            self._pose_cached = self.pose_buffer(t_params)
-            self._pose_key = key
-        return self._pose_cached
+        """Pose buffer of the big pose, cached while the caller keeps passing the same (unmodified) tensors.  The key
+        tensors are held alive (`_pose_src`), so the allocator cannot hand their addresses to new per-view tensors with
+        other contents; a miss during CUDA-graph capture is computed but not cached (a graph-pool buffer must not
+        leak into later eager calls)."""
+        src = tuple(t_params[k] for k in ("poses", "shapes", "R", "Th"))
+        key = tuple((t.data_ptr(), t._version) for t in src)
+        if key == self._pose_key and all(a is b for a, b in zip(src, self._pose_src)):
+            return self._pose_cached
+        buf = self.pose_buffer(t_params)
+        if not torch.cuda.is_current_stream_capturing():
+            self._pose_cached, self._pose_key, self._pose_src = buf, key, src
+        return buf
 
     def get_transform_params_torch(self, params, rot_mats=None, correct_Rs=None):
         """(A[1,24,4,4], R, Th, joints[1,24,3]) as the reference returns them."""

@@ -216,6 +216,31 @@ class ShardedFusedAdam:
         self._f_ptrs = (C.c_void_p * self.world)(*f_ptrs)
         self._token = torch.zeros(1, device=dev)
         dist.barrier(group=group)
+        self.check()  # every rank starts at the same epoch, no error latched
+
+    def check(self):
+        """Synchronises this rank's device and verifies the in-kernel barriers' state: raises if a wait gave up (a peer
+        never arrived within GHR_SHARDED_TIMEOUT_MS, or some rank aborted) or if the ranks disagree on the step count
+        (the epoch of the flag exchange).  Collective: every rank must call it.  Cheap enough for once per N steps."""
+        err_word = _lib.lib().ghr_sharded_error_word()
+        state = torch.tensor([self.steps, -self.steps, int(self._flags[err_word].item())], dtype=torch.int64,
+                             device=self.params.device)
+        self.dist.all_reduce(state, op=self.dist.ReduceOp.MAX, group=self.group)
+        hi, neg_lo, err = (int(x) for x in state.tolist())
+        if err:
+            why = {1: "timed out waiting for a peer's gradient bucket", 2: "timed out waiting for a peer's replica write",
+                   3: "aborted by a peer"}.get(err, f"error {err}")
+            raise RuntimeError(f"ShardedFusedAdam: an in-kernel barrier gave up at step {hi} ({why}); parameters of the "
+                               "ranks may differ -- restore from a checkpoint")
+        if hi != -neg_lo:
+            raise RuntimeError(f"ShardedFusedAdam: ranks disagree on the step count ({-neg_lo}..{hi})")
+
+    def abort(self):
+        """Raise the abort word of every rank: peers waiting inside a step return at once (and report it in check())."""
+        dev = self.params.device
+        with _lib.on_device(dev):
+            _lib.check(_lib.lib().ghr_sharded_abort(self.world, self._f_ptrs, _lib.raw_stream(dev.index)),
+                       "ghr_sharded_abort")
 
     def _barrier_on_stream(self):
         # a one-element NCCL all-reduce: completes on this stream only when every rank's stream has reached it
@@ -233,11 +258,15 @@ class ShardedFusedAdam:
         dev = self.params.device
         if self.sync == "flags":
             with _lib.on_device(dev):
-                _lib.check(_lib.lib().ghr_adam_step_sharded_synced(
-                    self.world, self.rank, self._g_ptrs, self._p_ptrs, self.exp_avg.data_ptr(),
-                    self.exp_avg_sq.data_ptr(), self.lo, self.hi, len(self.param_groups), table, float(self.betas[0]),
-                    float(self.betas[1]), float(self.eps), self._f_ptrs, self.steps, _lib.raw_stream(dev.index or 0)),
-                    "ghr_adam_step_sharded_synced")
+                try:
+                    _lib.check(_lib.lib().ghr_adam_step_sharded_synced(
+                        self.world, self.rank, self._g_ptrs, self._p_ptrs, self.exp_avg.data_ptr(),
+                        self.exp_avg_sq.data_ptr(), self.lo, self.hi, len(self.param_groups), table, float(self.betas[0]),
+                        float(self.betas[1]), float(self.eps), self._f_ptrs, self.steps, _lib.raw_stream(dev.index)),
+                        "ghr_adam_step_sharded_synced")
+                except Exception:
+                    self.abort()  # the peers are (or will be) waiting for this rank inside their kernels
+                    raise
             return
         with _lib.on_device(dev):
             self._barrier_on_stream()  # every rank's bucket is complete

@@ -1,0 +1,259 @@
+"""-m gpu parity tests AT THE SIZES THE NUMBERS ARE QUOTED ON (BASELINE.json configs 2-5):
+libghr through the drop-in _C / C ABI against the UNMODIFIED reference CUDA build (oracle/_ref) on identical inputs.
+
+  config 2   50 000 Gaussians, 512x512            forward + backward
+  config 3  100 000 Gaussians, 1024x1024          forward + backward
+  config 4  300 000 Gaussians, 1024x1024          forward + backward
+  config 5  3 000 000 Gaussians, 1920x1080, SH + scale/rot, forward (integer state of >= 10^6 Gaussians exact)
+            300 000 Gaussians, 1920x1080          forward + backward (H = 1080 is not a multiple of 16)
+  adversarial: projected centres and extents exactly on / one ulp around tile (16 px) and block (4 px) boundaries
+  fused LBS + covariance + SH at P = 50 000 against the fp64 oracle
+
+Cases with more than 2^19 (Gaussian, tile) pairs select the wide blend kernel family (ghr_blend_*_wide.cu)
+NATURALLY -- the test asserts that it did.
+
+Bars (north_star): radii / tiles_touched / point_offsets / num_rendered / sorted keys + ids / tile ranges /
+n_contrib bit-exact; colour / depth / alpha <= 1e-5 abs; gradients <= 1e-4 rel (per element, see _grad_close).
+oracle/_ref missing is a FAILURE here, not a skip.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from mygauhuman_b200 import synthetic as S
+from tests import common as Cm
+from tests.test_raster_parity_gpu import ABS_IMG, _grad_close, _np, _ref_forward, _state
+
+pytestmark = pytest.mark.gpu
+
+WIDE_PAIRS = 1 << 19  # blend_throughput_regime (ghr_internal.h)
+
+
+def _need_ref():
+    from oracle import ref_cuda
+    assert ref_cuda.available(), ("oracle/_ref/libref_gauhuman.so is missing: build it in the dev container "
+                                  "(python -c 'import __graft_entry__ as g; g.build()'); it ships with the snapshot")
+
+
+def _scene_case(P, W, H, mode, seed=0, scale=0.02, focal=1100.0):
+    """BASELINE.json config 5's scene: uniform cloud in a 10 m box in front of the camera (tools/aux_bench.py)."""
+    g = S.make_scene_cloud(P, seed=seed, scale=scale)
+    cam = S.make_camera(W, H, angle=math.pi, radius=6.0, target=(0.0, 0.0, 6.0), elev=0.0, seed=seed, focal=focal)
+    rng = np.random.default_rng(seed + 5)
+    case = dict(P=P, W=W, H=H, degree=3, bg=np.asarray((0.1, 0.2, 0.3), np.float32), means3D=g["xyz"].numpy(),
+                opacity=torch.sigmoid(g["opacity_logit"]).numpy(), view=cam["world_view_transform"].numpy().copy(),
+                proj=cam["full_proj_transform"].numpy().copy(), campos=cam["camera_center"].numpy().copy(),
+                tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"], scale_modifier=1.0, colors=None, cov3D=None,
+                scales=torch.exp(g["log_scale"]).numpy(), rotations=g["rotation"].numpy(), sh=None)
+    if mode == "sh_scale_rot":
+        case["sh"] = g["features"].numpy()
+    else:
+        case["colors"] = rng.uniform(0, 1, size=(P, 3)).astype(np.float32)
+    case["dL_dcolor"] = rng.normal(size=(3, H, W)).astype(np.float32)
+    case["dL_ddepth"] = rng.normal(size=(1, H, W)).astype(np.float32)
+    case["dL_dalpha"] = rng.normal(size=(1, H, W)).astype(np.float32)
+    return case
+
+
+def _compare_forward(tc, fw, ref, rfw, sh_mode):
+    rn, rcolor, rdepth, ralpha, rradii = rfw
+    n, color, depth, alpha, radii = fw[:5]
+    assert n == rn
+    assert torch.equal(radii, rradii)
+    st, rs = _state(tc, fw), ref.state()
+    for k in ("tiles_touched", "point_offsets"):
+        assert np.array_equal(_np(st[k]).view(np.uint32), rs[k]), k
+    assert np.array_equal(_np(st["point_list_keys"]).view(np.uint64), rs["point_list_keys"])
+    assert np.array_equal(_np(st["point_list"]).view(np.uint32), rs["point_list"])
+    assert np.array_equal(_np(st["ranges"]).view(np.uint32), rs["ranges"])
+    assert np.array_equal(_np(st["n_contrib"]).view(np.uint32), rs["n_contrib"])
+    vis = _np(radii) > 0
+    assert np.array_equal(_np(st["depths"])[vis], rs["depths"][vis])
+    assert np.array_equal(_np(st["means2D"])[vis], rs["means2D"][vis])
+    assert np.array_equal(_np(st["conic_opacity"])[vis], rs["conic_opacity"][vis])
+    assert (color - rcolor).abs().max().item() <= ABS_IMG
+    assert (depth - rdepth).abs().max().item() <= ABS_IMG * max(1.0, rdepth.abs().max().item())
+    assert (alpha - ralpha).abs().max().item() <= ABS_IMG
+    assert np.abs(_np(st["final_T"]) - rs["final_T"]).max() <= ABS_IMG
+    if sh_mode:
+        assert np.abs(_np(st["rgb"])[vis] - rs["rgb"][vis]).max() <= ABS_IMG
+    return int(vis.sum())
+
+
+def _compare_backward(tc, fw, ref, rfw):
+    rn, rcolor, rdepth, ralpha, rradii = rfw
+    g = Cm.ours_backward(tc, fw)
+    rg = ref.backward(tc["bg"], tc["means3D"], rradii, tc["colors"], tc["scales"], tc["rotations"], tc["scale_modifier"],
+                      tc["cov3D"], tc["view"], tc["proj"], tc["tanfovx"], tc["tanfovy"], tc["dL_dcolor"], tc["dL_ddepth"],
+                      tc["dL_dalpha"], tc["sh"], tc["degree"], tc["campos"], ralpha)
+    names = ["dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
+             "dL_drotations"]
+    for name, ours in zip(names, g):
+        assert tuple(ours.shape) == tuple(rg[name].shape), name
+        _grad_close(name, _np(ours), _np(rg[name]))
+
+
+# (P, W, H, expects the wide blend family)
+BODY_CASES = [(50_000, 512, 512), (100_000, 1024, 1024), (300_000, 1024, 1024)]
+
+
+@pytest.mark.parametrize("P,W,H", BODY_CASES)
+def test_baseline_config_sizes_forward_backward_vs_reference_cuda(P, W, H):
+    """BASELINE.json configs 2, 3, 4: the SMPL-topology body cloud of bench.py at the quoted sizes, precomputed colour
+    + covariance inputs (how render() calls the rasteriser)."""
+    _need_ref()
+    case = Cm.raster_case(P, W, H, seed=P // 1000, mode="precomp", scale=0.01)
+    tc = Cm.to_torch(case, "cuda")
+    fw = Cm.ours_forward(tc)
+    ref, rfw = _ref_forward(tc)
+    _compare_forward(tc, fw, ref, rfw, sh_mode=False)
+    _compare_backward(tc, fw, ref, rfw)
+
+
+def test_stress_3m_1080p_forward_integer_state_exact():
+    """BASELINE.json config 5: 3M Gaussians at 1920x1080 through the SH + scale/rotation path; every integer array of
+    the state (>= 10^6 visible Gaussians, ~10^7 sorted pairs) must equal the reference's bit for bit, and this frame
+    selects the wide blend family by itself."""
+    _need_ref()
+    case = _scene_case(3_000_000, 1920, 1080, "sh_scale_rot")
+    tc = Cm.to_torch(case, "cuda")
+    fw = Cm.ours_forward(tc)
+    assert fw[0] > WIDE_PAIRS, "this frame must select the wide blend family naturally"
+    ref, rfw = _ref_forward(tc)
+    visible = _compare_forward(tc, fw, ref, rfw, sh_mode=True)
+    assert visible >= 1_000_000
+
+
+def test_1080p_300k_backward_selects_the_wide_family_naturally():
+    """1920x1080 (H not a multiple of 16: the last tile row is partial, reference backward.cu:435,460-464) with enough
+    pairs for the wide blend kernels, forward + backward."""
+    _need_ref()
+    case = _scene_case(300_000, 1920, 1080, "color_scale_rot", seed=3, scale=0.05)
+    tc = Cm.to_torch(case, "cuda")
+    fw = Cm.ours_forward(tc)
+    assert fw[0] > WIDE_PAIRS, fw[0]
+    ref, rfw = _ref_forward(tc)
+    _compare_forward(tc, fw, ref, rfw, sh_mode=False)
+    _compare_backward(tc, fw, ref, rfw)
+
+
+def _boundary_case(W, H, seed=0):
+    """Gaussians whose projected centres sit exactly on, and one fp32 ulp either side of, tile (16 px) and 4x4-block
+    boundaries, with extents that put centre +- radius on those boundaries too (getRect's integer truncation,
+    reference auxiliary.h:45-55; our per-entry 4x4 block masks).  Camera at the origin looking down +z, power-of-two
+    focal length and depth so the back-projection is exact in fp32."""
+    f, d = 512.0, 2.0
+    K = torch.tensor([[f, 0.0, W / 2.0], [0.0, f, H / 2.0], [0.0, 0.0, 1.0]])
+    proj = S.projection_refine(K, H, W).transpose(0, 1)
+    view = torch.eye(4)
+    full = (view.unsqueeze(0).bmm(proj.unsqueeze(0))).squeeze(0).contiguous()
+    rng = np.random.default_rng(seed)
+    px, py = [], []
+    for bx in range(0, W + 1, 4):
+        for by in range(0, H + 1, 4):
+            if rng.uniform() < 0.35:
+                px.append(bx); py.append(by)
+    px, py = np.asarray(px, np.float64), np.asarray(py, np.float64)
+    n0 = px.size
+    # pixel centre p <-> ndc: p = ((ndc + 1) W - 1) / 2 ; ndc = f x / (d W/2)  =>  x = (p + 0.5 - W/2) d / f
+    x = (px + 0.5 - W / 2.0) * d / f
+    y = (py + 0.5 - H / 2.0) * d / f
+    xyz = np.stack([x, y, np.full(n0, d)], 1).astype(np.float32)
+    # three copies: exact, one ulp down, one ulp up
+    lo = np.nextafter(xyz[:, :2], -np.inf).astype(np.float32)
+    hi = np.nextafter(xyz[:, :2], np.inf).astype(np.float32)
+    xyz = np.concatenate([xyz, np.concatenate([lo, xyz[:, 2:]], 1), np.concatenate([hi, xyz[:, 2:]], 1)], 0)
+    # a handful of depths so the sort has ties in tile and order in depth
+    xyz[:, 2] = np.tile(np.asarray([2.0, 2.0, 4.0, 1.0], np.float32), xyz.shape[0] // 4 + 1)[: xyz.shape[0]]
+    xyz[:, :2] *= (xyz[:, 2:3] / d)
+    P = xyz.shape[0]
+    # isotropic scales chosen so 3 sigma in pixels is an integer (1, 2, 4, 8, 12, 16): radius = ceil(3 sqrt(lambda + .3))
+    r_px = rng.choice(np.asarray([1.0, 2.0, 4.0, 8.0, 12.0, 16.0]), size=P)
+    sigma_px2 = (r_px / 3.0) ** 2 - 0.3
+    sigma_world = np.sqrt(np.maximum(sigma_px2, 1e-4)) * xyz[:, 2] / f
+    scales = np.repeat(sigma_world[:, None], 3, 1).astype(np.float32)
+    rot = np.tile(np.asarray([1.0, 0.0, 0.0, 0.0], np.float32), (P, 1))
+    case = dict(P=P, W=W, H=H, degree=0, bg=np.asarray((0.0, 0.0, 0.0), np.float32), means3D=xyz,
+                opacity=rng.uniform(0.05, 0.9, size=(P, 1)).astype(np.float32), view=view.numpy().copy(),
+                proj=full.numpy().copy(), campos=np.zeros(3, np.float32), tanfovx=W / (2 * f), tanfovy=H / (2 * f),
+                scale_modifier=1.0, colors=rng.uniform(0, 1, size=(P, 3)).astype(np.float32), cov3D=None, scales=scales,
+                rotations=rot, sh=None)
+    case["dL_dcolor"] = rng.normal(size=(3, H, W)).astype(np.float32)
+    case["dL_ddepth"] = rng.normal(size=(1, H, W)).astype(np.float32)
+    case["dL_dalpha"] = rng.normal(size=(1, H, W)).astype(np.float32)
+    return case
+
+
+@pytest.mark.parametrize("W,H", [(256, 208), (250, 203)])
+def test_adversarial_tile_and_block_boundaries(W, H):
+    _need_ref()
+    case = _boundary_case(W, H, seed=W)
+    tc = Cm.to_torch(case, "cuda")
+    fw = Cm.ours_forward(tc)
+    ref, rfw = _ref_forward(tc)
+    _compare_forward(tc, fw, ref, rfw, sh_mode=False)
+    # the construction really does put centres on boundaries
+    st = _state(tc, fw)
+    m2 = _np(st["means2D"])[_np(fw[4]) > 0]
+    on_block = (np.abs(m2 / 4.0 - np.round(m2 / 4.0)) < 1e-3).all(1).mean()
+    assert on_block > 0.9, on_block
+    _compare_backward(tc, fw, ref, rfw)
+
+
+def test_fused_lbs_at_50k_against_fp64_oracle(smpl_model):
+    """The fused LBS + covariance + SH kernel at the ZJU size (P = 50 000) against the fp64 restatement of the
+    reference's PyTorch LBS (oracle/lbs_oracle.py, pinned on reference goldens at P = 1 500): positions / transforms
+    2e-5 abs, colours 1e-5 abs, covariance 2e-4 rel, gradients 1e-4 of each tensor's scale."""
+    from mygauhuman_b200.lbs import SMPLDeformer
+    from oracle import lbs_oracle as LO
+    P = 50_000
+    smpl = smpl_model
+    big = S.big_pose_params()
+    tv = S.big_pose_vertices(smpl, big)
+    gs = S.make_gaussians(P, tv.numpy(), seed=0, sh_degree=3)
+    pose = S.make_pose_params(5)
+    campos = torch.tensor([0.2, 1.0, 3.0])
+    dfm = SMPLDeformer(smpl, "cuda")
+    cu = lambda d: {k: v.cuda() for k, v in d.items()}
+    leaf = lambda t: t.clone().cuda().requires_grad_(True)
+    xyz, nrm, logs, rot, feat = (leaf(gs[k]) for k in ("xyz", "normals", "log_scale", "rotation", "features"))
+    d = dfm.deform_gaussians(xyz, cu(pose), cu(big), tv.cuda(), normals=nrm, log_scaling=logs, rotation=rot,
+                             features=feat, sh_degree=3, campos=campos.cuda())
+    gen = torch.Generator().manual_seed(3)
+    seeds = {k: torch.randn(*s, generator=gen, dtype=torch.float64) for k, s in
+             (("world", (P, 3)), ("n", (P, 3)), ("cov", (P, 6)), ("col", (P, 3)))}
+    seeds["cov"] *= 1e3
+    c = lambda k: seeds[k].float().cuda()
+    loss = ((d["means3D"] * c("world")).sum() + (d["world_normals"] * c("n")).sum() + (d["cov3D"] * c("cov")).sum() +
+            (d["colors"] * c("col")).sum())
+    loss.backward()
+    vid = dfm.nearest_vertex(tv.cuda(), xyz.detach()).cpu().long()
+    # nearest vertex: exact against fp64 brute force wherever the two nearest distances differ by more than fp32 noise
+    sub = torch.arange(0, P, 7)  # (a 50 000 x 6 890 fp64 distance matrix is 2.8 GB: check every 7th Gaussian)
+    dd = torch.cdist(gs["xyz"][sub].double(), tv.double())
+    two = torch.topk(dd, 2, dim=1, largest=False)
+    clear = (two.values[:, 1] - two.values[:, 0]) > 1e-6
+    assert clear.float().mean() > 0.99
+    assert torch.equal(vid[sub][clear], two.indices[clear, 0])
+
+    dt = torch.float64
+    osmpl = {k: (v.to(dt) if v.is_floating_point() else v) for k, v in smpl.items()}
+    dbl = lambda dct: {k: v.to(dt) for k, v in dct.items()}
+    oleaf = lambda t: t.clone().to(dt).requires_grad_(True)
+    oxyz, onrm, ologs, orot, ofeat = (oleaf(gs[k]) for k in ("xyz", "normals", "log_scale", "rotation", "features"))
+    _, world, _, T, _, wn, _ = LO.coarse_deform_c2source(osmpl, oxyz, dbl(pose), dbl(big), tv.to(dt), normals=onrm,
+                                                         vert_ids=vid)
+    cov = LO.covariance(torch.exp(ologs), 1.0, orot, T)
+    col = LO.view_colors(3, ofeat, world, campos.to(dt))
+    oloss = ((world * seeds["world"]).sum() + (wn * seeds["n"]).sum() + (cov * seeds["cov"]).sum() +
+             (col * seeds["col"]).sum())
+    oloss.backward()
+    assert float((d["means3D"].detach().cpu().double() - world.detach()).abs().max()) <= 2e-5
+    assert float((d["transforms"].detach().cpu().double() - T.detach()).abs().max()) <= 2e-5
+    assert float((d["colors"].detach().cpu().double() - col.detach()).abs().max()) <= 1e-5
+    np.testing.assert_allclose(d["cov3D"].detach().cpu().numpy(), cov.detach().numpy(), rtol=2e-4, atol=1e-9)
+    for nm, a, b in (("xyz", xyz, oxyz), ("normals", nrm, onrm), ("log_scale", logs, ologs), ("rotation", rot, orot),
+                     ("features", feat, ofeat)):
+        assert Cm.rel_err(a.grad.cpu().numpy(), b.grad.numpy()) <= 1e-4, nm

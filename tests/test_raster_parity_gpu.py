@@ -60,8 +60,7 @@ def _ref_forward(tc):
 @pytest.mark.parametrize("P,W,H,mode,degree,scale", CASES)
 def test_forward_backward_vs_reference_cuda(P, W, H, mode, degree, scale):
     from oracle import ref_cuda
-    if not ref_cuda.available():
-        pytest.skip("oracle/_ref not built")
+    assert ref_cuda.available(), "oracle/_ref/libref_gauhuman.so is missing (built by __graft_entry__.build(); ships with the snapshot)"
     case = Cm.raster_case(P, W, H, seed=P + W, mode=mode, degree=degree, scale=scale)
     tc = Cm.to_torch(case, "cuda")
     fw = Cm.ours_forward(tc)
@@ -210,6 +209,46 @@ def test_optimistic_launch_recovers_from_a_small_guess():
         _grad_close("optimistic", _np(b), _np(a), rel=1e-4)  # two runs of the same kernels: fp32 atomic order differs
     fw2 = Cm.ours_forward(tb)              # guess now large enough: single pass
     assert fw2[0] == ref_big[0] and torch.equal(fw2[1], ref_big[1])
+
+
+def test_backward_after_many_outstanding_forwards_and_a_redo_in_debug_mode():
+    """the reference's render() keeps 7 forwards outstanding before the first backward, so backward must find
+    the capacity a binning buffer was laid out for from the buffer itself (ghr_binning_capacity), not from a side table
+    that other forwards, address reuse or saved-tensor hooks can invalidate; and debug=True must not raise after a
+    successful redo of an undersized optimistic launch (the CAPACITY latch is cleared by the re-run)."""
+    from mygauhuman_b200.diff_gaussian_rasterization import _C
+    cases = [Cm.to_torch(Cm.raster_case(3000, 128, 96, seed=5 + k, scale=s), "cuda")
+             for k, s in enumerate((0.004, 0.1, 0.01, 0.05, 0.004, 0.1, 0.02, 0.03))]
+    _C._cap_hint.clear()
+    exact = []
+    for tc in cases:                       # references: one forward + backward at a time, exact-size buffers
+        _C._cap_hint.clear()
+        fw = Cm.ours_forward(tc)
+        exact.append((fw, Cm.ours_backward(tc, fw)))
+    _C._cap_hint.clear()
+    fws = [Cm.ours_forward(tc) for tc in cases]   # 8 outstanding forwards; guesses too small AND too large occur
+    caps = [_C._capacity_of(fw[6], tc["P"], tc["W"], tc["H"]) for tc, fw in zip(cases, fws)]
+    assert any(c > fw[0] + 64 for c, fw in zip(caps, fws)), "some buffer must be larger than its num_rendered"
+    for (tc, fw, (efw, eg)) in reversed(list(zip(cases, fws, exact))):
+        assert fw[0] == efw[0] and torch.equal(fw[1], efw[1])
+        moved = (fw[0], *fw[1:5], fw[5].clone(), fw[6].clone(), fw[7].clone())  # saved tensors relocated by a hook
+        for a, b in zip(Cm.ours_backward(tc, moved), eg):
+            _grad_close("outstanding", _np(a), _np(b), rel=1e-4)
+    # wrong-size buffer: rejected, not mis-read
+    tc, fw = cases[1], fws[1]
+    bad = (fw[0], *fw[1:5], fw[5], torch.cat([fw[6], fw[6][:64]]), fw[7])
+    with pytest.raises(Exception):
+        Cm.ours_backward(tc, bad)
+    # debug=True after a redo
+    _C._cap_hint.clear()
+    Cm.ours_forward(cases[0])                       # seeds a small guess
+    e = Cm.empty
+    tb = cases[1]
+    out = _C.rasterize_gaussians(tb["bg"], tb["means3D"], tb["colors"], tb["opacity"], e(), e(), 1.0, tb["cov3D"],
+                                 tb["view"], tb["proj"], tb["tanfovx"], tb["tanfovy"], tb["H"], tb["W"], e(), 3,
+                                 tb["campos"], False, True)
+    assert out[0] == exact[1][0][0] and torch.equal(out[1], exact[1][0][1])
+    assert _C.read_status(out[5]) == (out[0], 0)
 
 
 def test_autograd_module_matches_raw_calls():
