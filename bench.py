@@ -70,6 +70,16 @@ def parse():
                          "(MultiLaneRenderStep); reduced to a divisor of --batch-views; 1 = one view at a time")
     ap.add_argument("--sync-free", action="store_true",
                     help="ours: size the binning buffer from the previous step instead of a blocking read")
+    ap.add_argument("--no-optimizer", action="store_true",
+                    help="leave the optimiser step out of the measured step (round-1 behaviour: gradient all-reduce only)")
+    ap.add_argument("--lr-scale", type=float, default=1e-3,
+                    help="the reference's learning rates (arguments/__init__.py) are multiplied by this: the targets are "
+                         "random, so full-size Adam steps would walk the synthetic scene away from the named config")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the secondary measurements of the line (u1, stages_large, parity vs the reference arm, config 4)")
+    ap.add_argument("--targets", default="u8", choices=["u8", "f32"],
+                    help="dtype of the five target planes a view ships from the host (e2e): uint8 (an image dataset's own "
+                         "dtype, converted to fp32 inside the loss) or fp32 (round-1 behaviour, 4x the bytes)")
     return ap.parse_args()
 
 
@@ -183,7 +193,10 @@ def build_workload(args, rank, world):
     leaves = {"xyz": g["xyz"], "log_scale": g["log_scale"], "rotation": g["rotation"], "features": g["features"],
               "opacity_logit": g["opacity_logit"], "normals": g["normals"]}
     gen = torch.Generator().manual_seed(1234 + rank)
-    targets = torch.randn(5, H, W, generator=gen)  # linear loss weights on colour (3), depth, alpha
+    if args.targets == "u8":
+        targets = torch.randint(0, 256, (5, H, W), generator=gen, dtype=torch.uint8)
+    else:
+        targets = torch.randn(5, H, W, generator=gen)  # linear loss weights on colour (3), depth, alpha
     return dict(P=P, W=W, H=H, smpl=smpl, big=big, t_vertices=t_vertices, leaves=leaves, views=views, targets=targets,
                 bg=torch.zeros(3))
 
@@ -206,8 +219,15 @@ def unpack(vec):
     return cam, pose
 
 
+def targets_f32(t):
+    return t.to(torch.float32) * (1.0 / 127.5) - 1.0 if t.dtype == torch.uint8 else t
+
+
 def linear_loss(color, depth, alpha, targets):
-    """sum(colour*t[0:3]) + sum(depth*t[3]) + sum(alpha*t[4]): every output plane gets a dense random gradient."""
+    """sum(colour*t[0:3]) + sum(depth*t[3]) + sum(alpha*t[4]): every output plane gets a dense random gradient.
+    uint8 targets (what an image dataset holds) are mapped to [-1, 1] here, on the device, inside the step."""
+    if targets.dtype == torch.uint8:
+        targets = targets.to(torch.float32) * (1.0 / 127.5) - 1.0
     return (torch.cat([color, depth, alpha]) * targets).sum()
 
 
@@ -227,7 +247,10 @@ class OursArm:
         self._lib, self.dgr, self.wl, self.dev = _lib, dgr, wl, dev
         _lib.lib()  # fail loudly if the CUDA library is missing
         self.deformer = SMPLDeformer(wl["smpl"], dev)
-        self.leaves = {k: v.to(dev).requires_grad_(True) for k, v in wl["leaves"].items()}
+        # the parameters live in ONE flat buffer with the gradient bucket's layout (leaves = views of it): a parameter is
+        # then addressed by the same offset on every rank, which is what the fused sharded optimiser step needs
+        from mygauhuman_b200.optim import flatten_leaves
+        self.flat_params, self.leaves = flatten_leaves({k: v.to(dev) for k, v in wl["leaves"].items()})
         self.big = {k: v.to(dev) for k, v in wl["big"].items()}
         self.t_vertices = wl["t_vertices"].to(dev)
         self.bg = wl["bg"].to(dev)
@@ -322,14 +345,17 @@ class _RefRasterize(torch.autograd.Function):
 
 
 class ReferenceArm:
-    """The reference's path on the same GPU: its PyTorch LBS / covariance / eval_sh (the restatement in
-    oracle/lbs_oracle.py run on CUDA tensors -- the reference module itself cannot travel to the GPU box; knn_cuda
-    is replaced by torch.cdist + argmin as SURVEY 8c plans) followed by the UNMODIFIED reference CUDA rasteriser
-    built for sm_100 (oracle/_ref).  None of libghr's kernels are on this path."""
+    """The reference's path on the same GPU, none of libghr's kernels on it:
+    * LBS / covariance / SH: the reference's OWN modules -- GaussianModel.coarse_deform_c2source (scene/gaussian_model.py
+      :768-872), GaussianModel.get_covariance (:208-209) and utils/sh_utils.eval_sh (:135-190) exactly as render()
+      (gaussian_renderer/__init__.py:94-96,124-125,181,193-195) calls them -- imported unmodified from baseline/_ref
+      (oracle/install_ref_py.sh + oracle/ref_py.py; knn_cuda, absent from the image, is an exact torch.cdist + topk).
+      Only when baseline/_ref is missing does the arm fall back to the restatement oracle/lbs_oracle.py, and says so.
+    * rasteriser: the UNMODIFIED reference CUDA sources built for sm_100 (oracle/_ref)."""
     name = "reference"
 
     def __init__(self, wl, dev):
-        from oracle import lbs_oracle, ref_cuda
+        from oracle import lbs_oracle, ref_cuda, ref_py
         if not ref_cuda.available():
             raise FileNotFoundError(ref_cuda.LIB_PATH)
         self.LO = lbs_oracle
@@ -340,23 +366,48 @@ class ReferenceArm:
         self.big = {k: v.to(dev) for k, v in wl["big"].items()}
         self.t_vertices = wl["t_vertices"].to(dev)
         self.bg = wl["bg"].to(dev)
+        self.model, self.eval_sh = None, None
+        if ref_py.available():
+            ns = ref_py.load()
+            self.model = ref_py.make_model(self.smpl, self.leaves, dev)
+            self.eval_sh = ns.sh_utils.eval_sh
+        self.lbs_source = ("reference modules from baseline/_ref: scene/gaussian_model.py coarse_deform_c2source + "
+                           "get_covariance, utils/sh_utils.py eval_sh" if self.model is not None else
+                           "RESTATEMENT oracle/lbs_oracle.py (baseline/_ref not installed)")
 
-    def step(self, view, vec_dev, targets_dev):
-        L, LO = self.leaves, self.LO
-        camd, pose = unpack(vec_dev)
-        cam = view["cam"]
+    def deform(self, pose, campos):
+        """-> (world means, covariance, colours, opacity) the way render() computes them."""
+        L = self.leaves
+        if self.model is not None:
+            pc = self.model
+            _, means3D, _, transforms, _, _ = pc.coarse_deform_c2source(
+                pc.get_xyz[None], pose, self.big, self.t_vertices[None], normals=pc.get_normal[None])
+            means3D = means3D.squeeze()
+            cov = pc.get_covariance(1.0, transforms.squeeze())
+            dir_pp = means3D - campos.repeat(pc.get_features.shape[0], 1)
+            dir_pp_normalized = dir_pp / dir_pp.norm(dim=1, keepdim=True)
+            shs_view = pc.get_features.transpose(1, 2).view(-1, 3, (pc.max_sh_degree + 1) ** 2)
+            col = torch.clamp_min(self.eval_sh(pc.active_sh_degree, shs_view, dir_pp_normalized) + 0.5, 0.0)
+            return means3D, cov, col, pc.get_opacity
+        LO = self.LO
         with torch.no_grad():
-            vid = torch.cdist(L["xyz"], self.t_vertices).argmin(1)  # stand-in for knn_cuda KNN(k=1)
+            vid = torch.cdist(L["xyz"], self.t_vertices).argmin(1)
         _, world, _, T, _, wn, _ = LO.coarse_deform_c2source(self.smpl, L["xyz"], pose, self.big, self.t_vertices,
                                                              normals=L["normals"] / L["normals"].norm(dim=1, keepdim=True),
                                                              vert_ids=vid)
-        cov = LO.covariance(torch.exp(L["log_scale"]), 1.0, L["rotation"], T)
-        col = LO.view_colors(3, L["features"], world, camd["campos"])
+        return (world, LO.covariance(torch.exp(L["log_scale"]), 1.0, L["rotation"], T),
+                LO.view_colors(3, L["features"], world, campos), torch.sigmoid(L["opacity_logit"]))
+
+    def step(self, view, vec_dev, targets_dev):
+        L = self.leaves
+        camd, pose = unpack(vec_dev)
+        cam = view["cam"]
+        world, cov, col, opac = self.deform(pose, camd["campos"])
         means2D = torch.zeros_like(world, requires_grad=True)
         color, radii, depth, alpha = _RefRasterize.apply(
-            self.ref, world, means2D, col, torch.sigmoid(L["opacity_logit"]), cov, self.bg, camd["view"].contiguous(),
-            camd["proj"].contiguous(), camd["campos"].contiguous(), cam["tanfovx"], cam["tanfovy"], self.wl["H"],
-            self.wl["W"])
+            self.ref, world.contiguous(), means2D, col.contiguous(), opac.contiguous(), cov.contiguous(), self.bg,
+            camd["view"].contiguous(), camd["proj"].contiguous(), camd["campos"].contiguous(), cam["tanfovx"],
+            cam["tanfovy"], self.wl["H"], self.wl["W"])
         loss = linear_loss(color, depth, alpha, targets_dev)
         for t in L.values():
             t.grad = None
@@ -377,7 +428,7 @@ def cpu_baseline(wl, view, iters):
     cam, pose = view["cam"], view["pose"]
     a = lambda t: np.ascontiguousarray(t.detach().cpu().numpy(), dtype=np.float32)
     vm, pm, campos = a(cam["world_view_transform"]), a(cam["full_proj_transform"]), a(cam["camera_center"])
-    tg = a(wl["targets"])
+    tg = a(targets_f32(wl["targets"]))
     bg = a(wl["bg"])
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
@@ -443,6 +494,337 @@ def load_traffic(stage):
 
 
 # ---------------------------------------------------------------------------
+# optimiser of the measured step
+# ---------------------------------------------------------------------------
+
+# arguments/__init__.py OptimizationParams of the reference: position_lr_init * spatial_lr_scale(=1), feature_lr,
+# opacity_lr, scaling_lr, rotation_lr; `normals` follows the feature rate
+REFERENCE_LRS = {"xyz": 1.6e-4, "log_scale": 5e-3, "rotation": 1e-3, "features": 2.5e-3, "opacity_logit": 5e-2,
+                 "normals": 2.5e-3}
+
+
+def make_optimizer(args, arm, world, bucket):
+    """The optimiser step that ends a batch (reference: torch.optim.Adam(l, lr=0.0, eps=1e-15), gaussian_model.py:283,
+    stepped at train.py:418).  ours, 1 GPU: FusedAdam (one launch).  ours, N GPUs: ShardedFusedAdam(sync="flags") --
+    gradient reduce-scatter + Adam + parameter all-gather in ONE kernel over NVLink peer memory, its two cross-rank
+    barriers inside the kernel; it REPLACES the NCCL all-reduce of the bucket.  reference arm: NCCL all-reduce + the
+    reference's own optimiser (torch.optim.Adam, foreach)."""
+    lrs = {k: REFERENCE_LRS[k] * args.lr_scale for k in arm.leaves}
+    if args.impl != "ours":
+        return torch.optim.Adam([{"params": [t], "lr": lrs[k], "name": k} for k, t in arm.leaves.items()], lr=0.0, eps=1e-15), "torch.optim.Adam (foreach), the reference's"
+    from mygauhuman_b200.optim import FusedAdam, ShardedFusedAdam, flat_layout
+    if world > 1 and bucket is not None:
+        total, table = flat_layout(arm.leaves)
+        assert total == arm.flat_params.numel() == bucket.numel()
+        groups = [dict(name=k, offset=table[k][0], count=table[k][1], lr=lrs[k]) for k in arm.leaves]
+        return ShardedFusedAdam(arm.flat_params, bucket, groups, eps=1e-15, sync="flags"), \
+            "ShardedFusedAdam(sync=flags): reduce-scatter + Adam + all-gather in one kernel over NVLink peer memory (ghr_adam_step_sharded_synced), no NCCL call"
+    return FusedAdam([{"params": [t], "lr": lrs[k], "name": k} for k, t in arm.leaves.items()], lr=0.0, eps=1e-15), \
+        "FusedAdam (ghr_adam_step, one launch)" + (" after one NCCL all-reduce of the bucket" if world > 1 else "")
+
+
+def verify_sharded_step(arm, opt, world, rank, run_batch):
+    """The fused compute+collective kernel against what it replaces, inside the run: one batch of views, then
+    ShardedFusedAdam.step() on the live buffers vs NCCL all-reduce of a copy of the bucket + FusedAdam on a copy of the
+    parameters (fresh moments on both sides: this is the optimiser's first step).  Bit-exact at 2 ranks (a + b commutes),
+    1e-6 relative at 4 / 8 (NCCL's summation order differs).  Returns the worst relative difference."""
+    import torch.distributed as dist
+    from mygauhuman_b200.optim import FusedAdam, flat_layout
+    assert opt.steps == 0
+    run_batch()  # fills the bucket with this rank's gradients
+    torch.cuda.synchronize()
+    total, table = flat_layout(arm.leaves)
+    summed = opt.grads.clone()
+    dist.all_reduce(summed)
+    ref = {k: torch.nn.Parameter(t.detach().clone()) for k, t in arm.leaves.items()}
+    for k, t in ref.items():
+        o, n = table[k]
+        t.grad = summed[o:o + n].view_as(t).clone()
+    lr_of = {g["name"]: g["lr"] for g in opt.param_groups}
+    FusedAdam([{"params": [ref[k]], "lr": lr_of[k]} for k in ref], lr=0.0, eps=1e-15).step()
+    opt.step()
+    torch.cuda.synchronize()
+    opt.check()
+    worst, exact = 0.0, True
+    for k, t in arm.leaves.items():
+        a, b = t.detach(), ref[k].detach()
+        exact = exact and bool(torch.equal(a, b))
+        worst = max(worst, float((a - b).abs().max() / b.abs().max().clamp_min(1e-30)))
+    w = torch.tensor([worst, 0.0 if exact else 1.0], device=summed.device, dtype=torch.float64)
+    dist.all_reduce(w, op=dist.ReduceOp.MAX)
+    worst, exact = float(w[0]), float(w[1]) == 0.0
+    if world == 2:
+        assert exact, f"sharded step differs from all-reduce + FusedAdam at 2 ranks (worst rel {worst:.3e})"
+    assert worst <= 1e-6, f"sharded step differs from all-reduce + FusedAdam: worst rel {worst:.3e}"
+    # replicas stay bit-identical
+    mine = arm.flat_params.detach().clone()
+    other = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(other, mine)
+    assert all(torch.equal(o, other[0]) for o in other), "parameter replicas differ across ranks"
+    return {"vs": "NCCL all-reduce + FusedAdam on copies, first optimiser step", "worst_rel": worst, "bit_exact": exact,
+            "replicas_bit_identical": True}
+
+
+# ---------------------------------------------------------------------------
+# secondary measurements carried by the line (ours arm, rank 0, N = 1)
+# ---------------------------------------------------------------------------
+
+def _event_times(fn, flush, iters, warm=3, sync_each=True):
+    """Device ms of fn() per call: CUDA events on the current stream, L2 flushed before each call (outside the pair)."""
+    for _ in range(warm):
+        fn()
+    ts = []
+    for i in range(iters):
+        flush.fill_(i & 0xFF)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    return float(np.median(ts))
+
+
+def measure_u1(arm, view, vec_dev, targets_dev, flush, iters=40):
+    """U1 (north_star's ">= 2x the reference diff-gaussian-rasterization fwd+bwd iterations/s"): ONE
+    rasteriser call, forward + backward, on the deformed Gaussians of view 0 (precomputed colour + covariance, as
+    render() calls it), through the raw _C entry points.  ours: replayed as a CUDA graph (device time; the eager figure
+    beside it is host-bound) and eagerly; reference: oracle/_ref, the unmodified CUDA sources, eagerly with its blocking
+    num_rendered read, which is its real cost.  L2 flushed before every call."""
+    from mygauhuman_b200.diff_gaussian_rasterization import _C
+    camd, pose = unpack(vec_dev)
+    cam, L, e = view["cam"], arm.leaves, torch.Tensor([])
+    H, W = arm.wl["H"], arm.wl["W"]
+    with torch.no_grad():
+        d = arm.deformer.deform_gaussians(L["xyz"], pose, arm.big, arm.t_vertices, scaling=torch.exp(L["log_scale"]),
+                                          rotation=L["rotation"], features=L["features"], sh_degree=3, campos=camd["campos"])
+        means, col, cov = d["means3D"].contiguous(), d["colors"].contiguous(), d["cov3D"].contiguous()
+        opa = torch.sigmoid(L["opacity_logit"]).contiguous()
+    view_m, proj_m, campos = camd["view"].contiguous(), camd["proj"].contiguous(), camd["campos"].contiguous()
+    tg = targets_f32(targets_dev)
+    gc, gd, ga = tg[0:3].contiguous(), tg[3:4].contiguous(), tg[4:5].contiguous()
+    fargs = (arm.bg, means, col, opa, e, e, 1.0, cov, view_m, proj_m, cam["tanfovx"], cam["tanfovy"], H, W, e, 3, campos,
+             False, False)
+
+    def ours_fwd():
+        return _C.rasterize_gaussians(*fargs)
+
+    def ours_bwd(fw):
+        n, color, depth, alpha, radii, geom, binning, img = fw
+        return _C.rasterize_gaussians_backward(arm.bg, means, radii, col, e, e, 1.0, cov, view_m, proj_m, cam["tanfovx"],
+                                               cam["tanfovy"], gc, gd, ga, e, 3, campos, geom, n, binning, img, alpha, False)
+
+    fw = ours_fwd()
+    n = int(fw[0])
+    out = {"N_pairs": n, "V_visible": int((fw[4] > 0).sum())}
+    out["ours_eager_fwd_us"] = round(1e3 * _event_times(ours_fwd, flush, iters), 1)
+    out["ours_eager_fwd_bwd_us"] = round(1e3 * _event_times(lambda: ours_bwd(ours_fwd()), flush, iters), 1)
+    # graph replay: the same two calls captured once (sync-free binning capacity), what GraphedRenderStep does per view
+    cap = _C._round_cap(int(n * 1.3) + 4096)
+    graphs = {}
+    try:
+        _C.set_sync_free_capacity(cap)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                ours_bwd(ours_fwd())
+        torch.cuda.current_stream().wait_stream(side)
+        for name, body in (("fwd", ours_fwd), ("fwd_bwd", lambda: ours_bwd(ours_fwd()))):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                keep = body()
+            graphs[name] = (g, keep)
+    finally:
+        _C.set_sync_free_capacity(None)
+    out["ours_fwd_us"] = round(1e3 * _event_times(graphs["fwd"][0].replay, flush, iters), 1)
+    out["ours_fwd_bwd_us"] = round(1e3 * _event_times(graphs["fwd_bwd"][0].replay, flush, iters), 1)
+    out["ours_fwd_bwd_iters_per_s"] = round(1e6 / out["ours_fwd_bwd_us"], 1)
+    try:
+        from oracle import ref_cuda
+        have_ref = ref_cuda.available()
+    except Exception:
+        have_ref = False
+    if have_ref:
+        rr = ref_cuda.RefRasterizer()
+
+        def ref_fwd():
+            return rr.forward(arm.bg, means, col, opa, None, None, 1.0, cov, view_m, proj_m, cam["tanfovx"], cam["tanfovy"],
+                              H, W, None, 3, campos)
+
+        def ref_fwd_bwd():
+            rn, rcolor, rdepth, ralpha, rradii = ref_fwd()
+            return rr.backward(arm.bg, means, rradii, col, None, None, 1.0, cov, view_m, proj_m, cam["tanfovx"],
+                               cam["tanfovy"], gc, gd, ga, None, 3, campos, ralpha)
+
+        out["reference_fwd_us"] = round(1e3 * _event_times(ref_fwd, flush, iters), 1)
+        out["reference_fwd_bwd_us"] = round(1e3 * _event_times(ref_fwd_bwd, flush, iters), 1)
+        out["reference_fwd_bwd_iters_per_s"] = round(1e6 / out["reference_fwd_bwd_us"], 1)
+        out["speedup_fwd_bwd"] = round(out["reference_fwd_bwd_us"] / out["ours_fwd_bwd_us"], 2)
+        out["speedup_fwd"] = round(out["reference_fwd_us"] / out["ours_fwd_us"], 2)
+        out["reference"] = "oracle/_ref: unmodified diff-gaussian-rasterization sources built for sm_100, same inputs, same run"
+    else:
+        out["reference"] = "oracle/_ref not built"
+    out["what"] = ("one GaussianRasterizer-equivalent call (raw _C.rasterize_gaussians + _backward), precomputed colour + "
+                   "covariance, view 0; ours_* = CUDA-graph replay, ours_eager_* = same calls issued from Python; "
+                   "median of %d calls, L2 flushed before each" % iters)
+    return out
+
+
+def grad_agreement(got, want, rel=1e-4):
+    """Per-element agreement of two gradient sets (dict name -> tensor): an element passes when
+    |a - b| <= rel * |b| + 0.1 * rel * max|b| (north_star: parameter gradients within 1e-4 rel; the second term is the
+    floor below which fp32 accumulation order decides).  -> (all pass, report dict)."""
+    rep, ok = {}, True
+    for k in want:
+        a, b = got[k].detach().double().reshape(-1), want[k].detach().double().reshape(-1)
+        scale = float(b.abs().max().clamp_min(1e-30))
+        err = (a - b).abs()
+        bad = int((err > rel * b.abs() + 0.1 * rel * scale).sum())
+        rep[k] = {"max_abs_err_over_scale": float(err.max() / scale), "elements_outside": bad, "elements": a.numel()}
+        ok = ok and bad == 0
+    return ok, rep
+
+
+def batch_parity(arm, views, vec_dev, targets_dev, B, ref_arm):
+    """The batch gradient the TIMED configuration produces (graph replay, `lanes` concurrent views adding into one bucket
+    with fp32 atomics) against (1) the same B views through the eager operator API one at a time, summed in fp64, and
+    (2) the reference arm (its own LBS modules + its CUDA rasteriser) on the same views, summed in fp64."""
+    names = ("xyz", "features", "opacity_logit", "log_scale", "rotation")
+    ml = arm.multi
+    nv = len(views)
+    if ml is not None:
+        ml.zero_grads()
+        for g0 in range(0, B, ml.K):
+            ml.run_group([vec_dev[(g0 + j) % nv] for j in range(min(ml.K, B - g0))])
+        got = {k: ml.flat_views[k].clone() for k in names}
+    else:
+        arm.graphed.zero_grads()
+        for i in range(B):
+            arm.graphed(vec_dev[i % nv], arm.graphed.loss_inputs[0])
+        got = {k: arm.graphed.flat_views[k].clone() for k in names}
+    torch.cuda.synchronize()
+    out = {"views": B, "criterion": "|a-b| <= 1e-4 |b| + 1e-5 max|b| per element"}
+    was = arm.use_graph
+    arm.use_graph = False
+    want = None
+    for i in range(B):
+        _, grads = arm.step(views[i % nv], vec_dev[i % nv], targets_dev)
+        gs = {k: g.detach().double() for k, g in zip(names, grads)}
+        want = gs if want is None else {k: want[k] + gs[k] for k in want}
+    arm.use_graph = was
+    if ml is not None:
+        ml._alias_grads()
+    else:
+        for k, t in arm.leaves.items():
+            t.grad = arm.graphed.flat_views[k]
+    ok, rep = grad_agreement(got, want)
+    out["graph_lanes_vs_eager_sum"] = {"ok": ok, "per_tensor": rep}
+    assert ok, f"batch gradient of the timed configuration differs from the eager per-view sum: {rep}"
+    if ref_arm is not None:
+        for k in names:  # same parameter values on both arms
+            ref_arm.leaves[k].data.copy_(arm.leaves[k].detach())
+        ref_arm.leaves["normals"].data.copy_(arm.leaves["normals"].detach())
+        rwant = None
+        for i in range(B):
+            _, grads = ref_arm.step(views[i % nv], vec_dev[i % nv], targets_dev)
+            gs = {k: g.detach().double() for k, g in zip(names, grads)}
+            rwant = gs if rwant is None else {k: rwant[k] + gs[k] for k in rwant}
+        ok_r, rep_r = grad_agreement(got, rwant)
+        out["graph_lanes_vs_reference_arm"] = {"ok": ok_r, "per_tensor": rep_r, "lbs": ref_arm.lbs_source}
+    return out
+
+
+def measure_large(dev, flush, peak):
+    """The streaming kernels where HBM IS the bound (BASELINE.json config 5): the 3M-Gaussian 1920x1080 forward
+    (SH + scale/rotation path, as baking.py calls the rasteriser) stage by stage, and the onesweep sort of 2^24
+    45-bit depth|tile keys.  GB/s = algorithmic bytes (SURVEY 8d formulas, with the radix passes actually run) / time."""
+    from mygauhuman_b200 import _lib
+    from mygauhuman_b200.diff_gaussian_rasterization import _C
+    out = {}
+    P, W, H = 3_000_000, 1920, 1080
+    g = torch.Generator(device=dev).manual_seed(7)
+    xyz = torch.rand(P, 3, device=dev, generator=g) * 10.0 - 5.0
+    xyz[:, 2] += 6.0
+    scal = torch.exp(math.log(0.02) + 0.3 * torch.randn(P, 3, device=dev, generator=g))
+    rot = torch.nn.functional.normalize(torch.randn(P, 4, device=dev, generator=g))
+    opac = torch.sigmoid(1.5 * torch.randn(P, 1, device=dev, generator=g))
+    sh = torch.cat([torch.rand(P, 1, 3, device=dev, generator=g) * 2 - 1, 0.05 * torch.randn(P, 15, 3, device=dev, generator=g)], 1).contiguous()
+    from mygauhuman_b200 import synthetic as S
+    cam = S.make_camera(W, H, angle=math.pi, radius=6.0, target=(0.0, 0.0, 6.0), elev=0.0, seed=0, focal=1100.0)
+    e = torch.Tensor([])
+    args = (torch.zeros(3, device=dev), xyz, e, opac, scal, rot, 1.0, e, cam["world_view_transform"].to(dev),
+            cam["full_proj_transform"].to(dev), cam["tanfovx"], cam["tanfovy"], H, W, sh, 3, cam["camera_center"].to(dev),
+            False, False)
+    res = _C.rasterize_gaussians(*args)
+    N, V = int(res[0]), int((res[4] > 0).sum())
+    ms = _event_times(lambda: _C.rasterize_gaussians(*args), flush, 10)
+    passes = _lib.state_layout(P, 64, W, H).sort_passes
+    tiles, X = ((W + 15) // 16) * ((H + 15) // 16), W * H
+    _lib.profile_enable(True)
+    _lib.profile_read()
+    for i in range(5):
+        flush.fill_(i)
+        _C.rasterize_gaussians(*args)
+    torch.cuda.synchronize()
+    prof = _lib.profile_read()
+    _lib.profile_enable(False)
+    alg = {"preprocess": 244 * P + 67 * V, "emit_keys": 8 * P + 12 * V + 12 * N, "sort": N * (8 + 24 * passes),
+           "tile_ranges": 8 * N + 8 * tiles, "blend_fwd": 44 * N + 28 * X}
+    stages = {}
+    for name, (t, c) in prof.items():
+        if c and name in alg:
+            us = 1e3 * t / c
+            stages[name] = {"us": round(us, 1), "alg_bytes": int(alg[name]), "GBps": round(alg[name] / us / 1e3, 1),
+                            "frac_of_hbm_peak": round(alg[name] / us / 1e3 / peak, 3)}
+    out["stress_1080p_forward"] = {"P": P, "W": W, "H": H, "N_pairs": N, "V_visible": V, "ms": round(ms, 3),
+                                   "fps": round(1e3 / ms, 1), "radix_passes": passes, "stages": stages}
+    del res, xyz, scal, rot, opac, sh
+    # sort alone: 2^24 keys of 32 depth bits + 13 tile bits (8 160 tiles at 1080p)
+    l = _lib.lib()
+    Nk, bits = 1 << 24, 45
+    tile = torch.randint(0, 8160, (Nk,), device=dev, generator=g, dtype=torch.int64)
+    depth = (torch.rand(Nk, device=dev, generator=g) * 9.8 + 0.2).view(torch.int32).to(torch.int64)
+    keys = (tile << 32) | depth
+    vals = torch.arange(Nk, dtype=torch.int32, device=dev)
+    ka, kb, va, vb = keys.clone(), torch.empty_like(keys), vals.clone(), torch.empty_like(vals)
+    ws = torch.empty(l.ghr_sort_workspace_bytes(Nk), dtype=torch.uint8, device=dev)
+    sel = torch.zeros(1, dtype=torch.int32, device=dev)
+    stream = _lib.raw_stream(dev.index)
+
+    def run():
+        _lib.check(l.ghr_sort_pairs_u64(Nk, bits, ka.data_ptr(), kb.data_ptr(), va.data_ptr(), vb.data_ptr(), ws.data_ptr(),
+                                        ws.numel(), sel.data_ptr(), stream), "ghr_sort_pairs_u64")
+    ts = []
+    for i in range(8):
+        ka.copy_(keys); va.copy_(vals)
+        flush.fill_(i)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); run(); b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    ms = float(np.median(ts[2:]))
+    sorted_keys = kb if int(sel.item()) else ka
+    assert bool((sorted_keys[1:] >= sorted_keys[:-1]).all()), "sort_2p24: output not sorted"
+    npass = (bits + 8) // 9
+    bytes_alg = Nk * (8 + 24 * npass)
+    out["sort_2p24"] = {"keys": Nk, "bits": bits, "radix_passes": npass, "ms": round(ms, 3),
+                        "Gkeys_per_s": round(Nk / ms / 1e6, 2), "alg_bytes": bytes_alg,
+                        "GBps": round(bytes_alg / ms / 1e6, 1), "frac_of_hbm_peak": round(bytes_alg / ms / 1e6 / peak, 3)}
+    return out
+
+
+def load_issue_counts():
+    """Warp-level instructions executed per launch (ncu smsp__inst_executed.sum) of the blend kernels at the zju_512
+    shape, from the committed capture named in the file, or {}."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "issue.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
+# ---------------------------------------------------------------------------
 # main
 # ---------------------------------------------------------------------------
 
@@ -473,36 +855,22 @@ def emit(line):
         os.write(_REAL_STDOUT, data)
 
 
-def main():
-    global _REAL_STDOUT
-    args = parse()
-    # NCCL (version banner), nvidia-smi children and the like write to fd 1 behind Python's back: point fd 1 at stderr for
-    # the whole run and keep the original for the result line
-    sys.stdout.flush()
-    _REAL_STDOUT = os.dup(1)
-    os.dup2(2, 1)
-    world, rank, local = init_dist(args)
-    if args.impl == "reference-cpu":
-        run_reference_cpu(args, world, rank)
-        return
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device. The hot path has no CPU fallback "
-                         "(use --impl reference-cpu for the CPU oracle baseline).")
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    wl = build_workload(args, rank, world)
+def run_workload(args, workload, world, rank, local, dev, K, Wm, headline):
+    """Measure one workload; returns the line (rank 0) or None.  headline=False: a secondary workload carried under an
+    extra key (config 4 in multi-GPU runs): device-timed value + e2e only."""
+    if world > 1:
+        import torch.distributed as dist
+    wargs = argparse.Namespace(**vars(args))
+    wargs.workload = workload
+    wl = build_workload(wargs, rank, world)
     P, W, H = wl["P"], wl["W"], wl["H"]
     X, tiles = W * H, ((W + 15) // 16) * ((H + 15) // 16)
-    if args.impl == "ours":
+    ours = args.impl == "ours"
+    if ours:
         lanes = math.gcd(max(1, args.lanes), max(1, args.batch_views)) if args.mode == "graph" else 1
         arm = OursArm(wl, dev, args.sync_free, graph=(args.mode == "graph"), lanes=lanes)
     else:
-        try:
-            arm = ReferenceArm(wl, dev)
-        except (FileNotFoundError, OSError) as e:
-            if rank == 0:
-                emit({"impl": "reference", "unavailable": f"oracle/_ref not built: {e}"})
-            return
+        arm = ReferenceArm(wl, dev)
     views = wl["views"]
     vec_host = [view_pack(v) for v in views]
     vec_dev = [v.to(dev) for v in vec_host]
@@ -511,34 +879,32 @@ def main():
     vec_stage = torch.empty(PACK_FLOATS, device=dev)
     targets_stage = torch.empty_like(targets_dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    if world > 1:
-        import torch.distributed as dist
     from mygauhuman_b200.multiview import GradientAllReducer
     reducer = GradientAllReducer()
-
-    ar_err = None
-
     B = max(1, args.batch_views)
+    opt, opt_desc, sharded = None, None, False
 
     def graph_on():
-        return args.impl == "ours" and arm.use_graph
+        return ours and arm.use_graph
 
     def begin_batch():
         if graph_on():
-            arm.graphed.zero_grads()  # the graphed step accumulates the batch's gradients in its flat bucket
+            (arm.multi or arm.graphed).zero_grads()  # clears the bucket (and, with lanes, refreshes the nearest-vertex ids)
 
     def end_batch(grads):
-        # view-sharded data parallelism: ONE sum of the Gaussian-parameter gradients over the ranks per batch
+        """End of a multi-view batch: the gradients of the batch are summed over the ranks and the optimiser steps.
+        With ShardedFusedAdam the sum IS the optimiser kernel; otherwise one NCCL all-reduce precedes it."""
         if graph_on():
-            arm.graphed.reduce_grads()
+            if not sharded:
+                arm.graphed.reduce_grads()
         elif world > 1:
             reducer(grads)
+        if opt is not None:
+            opt.step()
 
     def one_view(i, e2e):
         k = i % len(views)
         if graph_on():
-            # the graphed step owns the static input buffers: it copies from pinned host memory itself (e2e), or from
-            # the resident device copies (the target planes already sit in its static buffer)
             if e2e:
                 loss, grads = arm.step(views[k], vec_host[k], targets_host)
             else:
@@ -552,7 +918,7 @@ def main():
         return loss, grads
 
     def one_step(i, e2e, want_grads=False):
-        """A batch of one view (warm-up, verification)."""
+        """A batch of one view (warm-up)."""
         begin_batch()
         loss, grads = one_view(i, e2e)
         end_batch(grads)
@@ -560,13 +926,26 @@ def main():
             return float(loss.item())
         return grads if want_grads else None
 
+    flush_ms = [0.0]
+
+    def finish(starts, ends, t0, n_flushes):
+        """Sum of the event pairs (max over ranks) and the wall clock of the whole loop minus the L2 flushes."""
+        torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3 - n_flushes * flush_ms[0]
+        ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
+        if world > 1:
+            t = torch.tensor([ms, wall], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, wall = float(t[0]), float(t[1])
+        return ms, wall
+
     def timed_lanes(K, e2e):
         """K steps of B views, the views of a batch replayed `lanes` at a time on as many streams (MultiLaneRenderStep).
         One event pair per GROUP of concurrent views on the stream the lanes fork from and join into (L2 flushed before
         every group, outside the pair); the first group's pair of a batch includes the bucket reset, the last one's the
-        fold of the lanes' buckets and the all-reduce.  e2e: every view's inputs come from pinned host memory (the next
-        group's copies are issued right after this group's replays, on the lanes' copy streams) and every view's loss
-        goes back to pinned memory, consumed one group later -- all inside the timed region."""
+        gradient reduction + optimiser step.  e2e: every view's inputs come from pinned host memory (the next group's
+        copies are issued right after this group's replays, on the lanes' copy streams) and every view's loss goes back
+        to pinned memory, consumed one group later -- all inside the timed region."""
         ml = arm.multi
         Kl = ml.K
         groups = K * (B // Kl)
@@ -575,6 +954,7 @@ def main():
         nv = len(views)
         pending, host_losses = [], 0.0
         torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
+        t0 = time.perf_counter()
         if e2e:
             for j in range(Kl):
                 ml.lanes[j].prefetch(vec_host[j % nv], targets_host)
@@ -591,7 +971,7 @@ def main():
             else:
                 ml.run_group([vec_dev[(i + j) % nv] for j in range(Kl)])
             if ((gi + 1) * Kl) % B == 0:
-                ml.reduce_grads()
+                end_batch(None)
             if e2e:
                 new_pending = [ml.lanes[j].loss_to_host() for j in range(Kl)]
                 for slot, ev in pending:  # the previous group's losses: their copies finished long ago
@@ -603,20 +983,15 @@ def main():
         for slot, ev in pending:
             ev.synchronize()
             host_losses += float(slot[0])
-        torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
-        ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
-        if world > 1:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms
+        return finish(starts, ends, t0, groups)
 
     def timed(K, e2e):
         """K steps of B views.  Every view has its own event pair (L2 flushed before it, outside the pair); the first
-        view's pair includes the bucket reset, the last one's the all-reduce.  e2e: inputs from pinned host memory and
-        the view's loss read back.  With the graphed step the e2e loop is pipelined the way a training loop would be:
-        the inputs of view i+1 travel on a copy stream while view i computes, and the loss of view i is copied to
-        pinned memory asynchronously and consumed one view later -- every copy still happens inside the timed region."""
+        view's pair includes the bucket reset, the last one's the gradient reduction + optimiser step.  e2e: inputs
+        from pinned host memory and the view's loss read back.  With the graphed step the e2e loop is pipelined the way
+        a training loop would be: the inputs of view i+1 travel on a copy stream while view i computes, and the loss of
+        view i is copied to pinned memory asynchronously and consumed one view later -- every copy still happens inside
+        the timed region.  Returns (sum of event pairs, wall clock of the loop minus the flushes), max over ranks."""
         if graph_on() and arm.multi is not None:
             return timed_lanes(K, e2e)
         n = K * B
@@ -625,6 +1000,7 @@ def main():
         piped = e2e and graph_on()
         pending, host_losses = None, 0.0
         torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
+        t0 = time.perf_counter()
         if piped:
             arm.graphed.prefetch(vec_host[0], targets_host)
         for i in range(n):
@@ -652,30 +1028,47 @@ def main():
         if pending is not None:
             pending[1].synchronize()
             host_losses += float(pending[0][0])
-        torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
-        ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
-        if world > 1:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms
+        return finish(starts, ends, t0, n)
 
-    K, Wm = args.steps, max(args.warmup, 3)
+    # the L2 flush alone (subtracted from the wall-clock cross-check)
+    fl = []
+    for i in range(6):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); flush.fill_(i); b.record()
+        torch.cuda.synchronize()
+        fl.append(a.elapsed_time(b))
+    flush_ms[0] = float(np.median(fl[2:]))
+
     for i in range(Wm):
         one_step(i, False)
         one_step(i, True)
     torch.cuda.synchronize()
-    graphed = args.impl == "ours" and args.mode == "graph"
+    graphed = ours and args.mode == "graph"
     if graphed:
         # capacity sized from every view this rank cycles through, then one capture; warm the replay path too
         arm.capture(vec_dev, targets_dev)
         arm.use_graph = True
-        for i in range(Wm):
-            one_step(i, False)
-            one_step(i, True)
-        torch.cuda.synchronize()
+    bucket = (arm.multi or arm.graphed).flat if graphed else None
+    sharded_check = None
+    if not args.no_optimizer:
+        opt, opt_desc = make_optimizer(args, arm, world, bucket)
+        sharded = ours and world > 1 and bucket is not None
+        if sharded:
+            def first_batch():
+                begin_batch()
+                if arm.multi is not None:
+                    for g0 in range(0, B, arm.multi.K):
+                        arm.multi.run_group([vec_dev[(g0 + j) % len(views)] for j in range(arm.multi.K)])
+                else:
+                    for i in range(B):
+                        one_view(i, False)
+            sharded_check = verify_sharded_step(arm, opt, world, rank, first_batch)
+    for i in range(Wm):
+        one_step(i, False)
+        one_step(i, True)
+    torch.cuda.synchronize()
 
-    if args.host_profile and rank == 0:
+    if args.host_profile and rank == 0 and headline:
         import cProfile, pstats
         torch.cuda.synchronize()
         t0 = time.perf_counter()
@@ -694,40 +1087,57 @@ def main():
     sampler = ClockSampler(torch.cuda.current_device() if "CUDA_VISIBLE_DEVICES" not in os.environ else local)
     if rank == 0:
         sampler.start()
-    launches0 = arm._lib.launch_count() if args.impl == "ours" else 0
-    ms_dev = timed(K, False)
-    launches = (arm._lib.launch_count() - launches0) if args.impl == "ours" else None
-    ms_e2e = timed(K, True)
+    launches0 = arm._lib.launch_count() if ours else 0
+    ms_dev, wall_dev = timed(K, False)
+    launches = (arm._lib.launch_count() - launches0) if ours else None
+    ms_e2e, wall_e2e = timed(K, True)
     eager = None
     if graphed:
-        launches = K * B * arm.graphed.kernels_per_replay  # libghr kernels inside the K*B replays
+        per_batch = (1 if opt is not None else 0)  # optimiser kernel (graph replays count their own kernels)
+        launches = K * B * arm.graphed.kernels_per_replay + K * per_batch
+        if arm.multi is not None:
+            launches += K * 1  # nearest-vertex search once per batch (zero_grads)
         checker = arm.multi if arm.multi is not None else arm.graphed
         if not checker.check():  # a view overflowed the captured binning capacity: re-captured, measure again
-            ms_dev, ms_e2e = timed(K, False), timed(K, True)
+            (ms_dev, wall_dev), (ms_e2e, wall_e2e) = timed(K, False), timed(K, True)
             assert checker.check()
-        reduced = [g.clone() for g in one_step(0, False, want_grads=True)] if world > 1 else None
+        if sharded:
+            opt.check()
+    clocks = sampler.stop() if rank == 0 else None
+    if graphed and headline:
         arm.use_graph = False  # the same step issued kernel by kernel, for comparison
-        if world > 1:  # the in-graph all-reduce must give what the bucketed NCCL all-reduce of the eager step gives
-            ref = one_step(0, False, want_grads=True)
-            ar_err = max(float((a - b).abs().max() / b.abs().max().clamp_min(1e-30)) for a, b in zip(reduced, ref))
+        was_opt, was_sharded = opt, sharded
+        if sharded:
+            opt, sharded = None, False  # the sharded step needs the flat bucket the graph path fills
         for i in range(3):
             one_step(i, False)
-        eager = (timed(K, False), timed(K, True))
-    clocks = sampler.stop() if rank == 0 else None
+        eager = (timed(K, False)[0], timed(K, True)[0])
+        opt, sharded = was_opt, was_sharded
+        arm.use_graph = True
+        for k, t in arm.leaves.items():
+            t.grad = (arm.multi or arm.graphed).flat_views[k]
 
-    # per-stage device time (ours): a third identical pass with the library's stage events enabled
-    stages, roof = None, None
-    if args.impl == "ours":
+    # per-stage device time (ours): a further eager pass with the library's stage events enabled
+    stages, roof, NV = None, None, None
+    if ours and headline:
+        arm.use_graph = False
+        keep_opt, opt = opt, None
         arm._lib.profile_enable(True)
         arm._lib.profile_read()
         timed(K, False)
         prof = arm._lib.profile_read()
         arm._lib.profile_enable(False)
+        opt = keep_opt
+        arm.use_graph = graphed
+        if graphed:
+            for k, t in arm.leaves.items():
+                t.grad = (arm.multi or arm.graphed).flat_views[k]
         # N, V per view (measured, averaged over the views this rank cycles through)
         nv = [arm.measure_NV(views[i % len(views)], vec_dev[i % len(views)]) for i in range(min(K, len(views)))]
         N = float(np.mean([a for a, _ in nv])); V = float(np.mean([b for _, b in nv]))
+        NV = (N, V)
         from mygauhuman_b200 import _lib
-        passes = _lib.state_layout(P, 1, W, H).sort_passes
+        passes = _lib.state_layout(P, 64, W, H).sort_passes
         peak, peak_src = load_peaks()
         stages = {}
         for name, (ms, cnt) in prof.items():
@@ -739,64 +1149,154 @@ def main():
                             "alg_bytes": None if b is None else int(b),
                             "GBps": None if b is None else round(b / (us * 1e-6) / 1e9, 1)}
         dom = max((s for s in stages if stages[s]["GBps"] is not None), key=lambda s: stages[s]["us"])
-        roof = {"kernel": dom, "bound": "hbm", "achieved": stages[dom]["GBps"], "peak": peak, "unit": "GB/s",
-                "frac": round(stages[dom]["GBps"] / peak, 4), "traffic": load_traffic(dom), "peak_source": peak_src,
-                "note": "blend kernels are fp32-issue/MUFU bound, not HBM bound (DESIGN.md); frac is reported as the contract asks",
-                "N_pairs": N, "V_visible": V}
+        # The dominant kernel is bound by INSTRUCTION ISSUE along the heaviest tiles' lists, not by HBM (its DRAM traffic
+        # is below the algorithmic bytes).  achieved = warp instructions per second: ncu's smsp__inst_executed.sum of
+        # the committed capture (profiles/issue.json) / the kernel's duration measured live here; peak = SMs x 4
+        # schedulers x SM clock (one warp instruction per scheduler per cycle).  The HBM figure stays beside it.
+        issue = load_issue_counts().get(workload, {}).get(dom)
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        mhz = (clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0
+        peak_issue = sms * 4 * mhz * 1e6 / 1e9  # G warp-instructions / s
+        hbm = {"achieved": stages[dom]["GBps"], "peak": peak, "unit": "GB/s", "frac": round(stages[dom]["GBps"] / peak, 4),
+               "alg_bytes": stages[dom]["alg_bytes"], "traffic": load_traffic(dom), "peak_source": peak_src}
+        if issue:
+            ach = issue["inst_executed"] / (stages[dom]["us"] * 1e-6) / 1e9
+            roof = {"kernel": dom, "bound": "issue", "achieved": round(ach, 1), "peak": round(peak_issue, 1),
+                    "unit": "Gwarp-inst/s", "frac": round(ach / peak_issue, 4), "traffic": load_traffic(dom),
+                    "inst_executed_per_launch": issue["inst_executed"], "inst_source": issue.get("source"),
+                    "peak_source": f"{sms} SMs x 4 schedulers x {mhz:.0f} MHz (clock sampled during this run)",
+                    "us": stages[dom]["us"], "hbm": hbm, "N_pairs": N, "V_visible": V}
+        else:
+            roof = dict(hbm, kernel=dom, bound="hbm", N_pairs=N, V_visible=V,
+                        note="no committed instruction count for this kernel (profiles/issue.json): HBM figure only; the "
+                             "blend kernels are issue-bound, not HBM-bound (DESIGN.md 5.4)")
+
+    extras = {}
+    if ours and headline and world == 1 and not args.no_extras:
+        arm.use_graph = graphed
+        extras["u1"] = measure_u1(arm, views[0], vec_dev[0], targets_dev, flush)
+        ref_arm = None
+        try:
+            ref_arm = ReferenceArm(wl, dev)
+        except Exception as ex:  # oracle/_ref absent: the check against the reference arm is skipped, and said so
+            extras["parity_note"] = f"reference arm unavailable: {ex}"
+        if graphed:
+            extras["parity"] = batch_parity(arm, views, vec_dev, targets_dev, B, ref_arm)
+        del ref_arm
+        torch.cuda.empty_cache()
+        extras["stages_large"] = measure_large(dev, flush, load_peaks()[0])
 
     if rank != 0:
-        return
+        return None
     cpu = None
-    if args.impl == "ours" and world == 1 and not args.no_cpu_baseline:
+    if ours and world == 1 and headline and not args.no_cpu_baseline:
         cpu = cpu_baseline(wl, views[0], args.cpu_iters)
 
     views_per_step = world * B  # B views per rank per step
-    n_lanes = arm.multi.K if (args.impl == "ours" and getattr(arm, "multi", None) is not None) else 1
+    n_lanes = arm.multi.K if (ours and getattr(arm, "multi", None) is not None) else 1
     value = views_per_step * K / (ms_dev * 1e-3)
     e2e_val = views_per_step * K / (ms_e2e * 1e-3)
-    h2d = PACK_FLOATS * 4 + 5 * X * 4
+    tb = wl["targets"].element_size()
+    h2d = PACK_FLOATS * 4 + 5 * X * tb
+    if opt is None:
+        comm = None if world == 1 else "one NCCL sum all-reduce of the flat gradient bucket per step (batch)"
+    elif sharded:
+        comm = ("none through NCCL: the gradient sum, Adam and the parameter broadcast are ONE kernel over NVLink peer "
+                "memory (ghr_adam_step_sharded_synced, flag barriers inside the kernel)")
+    else:
+        comm = None if world == 1 else "one NCCL sum all-reduce of the gradients per step (batch), then the optimiser"
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
         "ms_per_step": round(ms_dev / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "impl": args.impl,
-        "config": {"workload": args.workload, "desc": WORKLOADS[args.workload]["desc"], "P": P, "W": W, "H": H,
+        "config": {"workload": workload, "desc": WORKLOADS[workload]["desc"], "P": P, "W": W, "H": H,
                    "sh_degree": 3, "views_cycled": len(views) * world, "parallelism": f"view-sharded dp{world}",
                    "l2": ("flushed before every view (256 MiB fill outside the per-view event pair)" if n_lanes == 1 else
                           f"flushed before every group of {n_lanes} concurrent views (256 MiB fill outside the per-group event pair)"),
                    "lanes": n_lanes,
                    "sync_free": bool(args.sync_free),
-                   "mode": (args.mode if args.impl == "ours" else "eager"),
+                   "mode": (args.mode if ours else "eager"),
                    "batch_views_per_rank": B,
-                   "all_reduce": (None if world == 1 else "one NCCL sum of the flat gradient bucket per step (batch)")},
+                   "step": f"{B} views per rank (LBS + cov + SH -> raster fwd -> loss -> raster bwd -> LBS bwd), gradient sum "
+                           "over the ranks" + ("" if opt is None else ", optimiser step"),
+                   "optimizer": opt_desc, "lr_scale": (None if opt is None else args.lr_scale),
+                   "targets_dtype": str(wl["targets"].dtype).replace("torch.", ""),
+                   "comm": comm, "all_reduce": comm},
         "e2e": {"value": round(e2e_val, 2), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
                 "h2d_bytes_per_step": h2d * B, "d2h_bytes_per_step": 4 * B,
-                "what": "public API step (GraphedRenderStep replay, or in eager mode SMPLDeformer.deform_gaussians -> "
-                        "GaussianRasterizer -> loss -> backward); "
+                "wall_clock_value": round(views_per_step * K / (wall_e2e * 1e-3), 2),
+                "wall_clock_ms_per_step": round(wall_e2e / K, 4),
+                "what": "public API step (GraphedRenderStep / MultiLaneRenderStep replay, or in eager mode "
+                        "SMPLDeformer.deform_gaussians -> GaussianRasterizer -> loss -> backward); "
                         "camera + SMPL pose + 5 target planes copied from pinned host memory and the loss copied back to "
                         "pinned memory for every view inside the timed region (graph mode: input copies of the next view(s) on "
-                        "copy streams during the current one(s), losses consumed one view / group later; with lanes > 1 "
-                        "the views of a batch are replayed `lanes` at a time on as many streams (MultiLaneRenderStep); "
-                        "eager/reference: blocking loss.item()); "
-                        "Gaussian parameters stay resident (model state)"},
+                        "copy streams during the current one(s), losses consumed one view / group later; "
+                        "eager/reference: blocking loss.item()); Gaussian parameters stay resident (model state).  value = sum "
+                        "of the per-group CUDA-event pairs; wall_clock_* = host clock around the whole K-step loop minus the "
+                        f"L2 flushes ({flush_ms[0] * 1e3:.0f} us each), the cross-check that no copy hides between pairs"},
+        "wall_clock_value": round(views_per_step * K / (wall_dev * 1e-3), 2),
         "gpu_launches": launches, "clocks": clocks,
     }
+    if sharded_check is not None:
+        line["sharded_step_check"] = sharded_check
     if eager is not None:
         line["eager"] = {"value": round(views_per_step * K / (eager[0] * 1e-3), 2), "ms_per_step": round(eager[0] / K, 4),
                          "e2e": round(views_per_step * K / (eager[1] * 1e-3), 2),
                          "what": "same step through the eager operator API (one Python call per kernel); host-bound"}
-        if ar_err is not None:
-            line["eager"]["graph_vs_eager_reduced_grad_rel_err"] = ar_err
     if roof is not None:
         line["roofline"] = roof
         line["stages"] = stages
+    line.update(extras)
     if cpu is not None:
         line["cpu_baseline"] = cpu
     if args.impl == "reference":
         line["cpu_baseline"] = {"kind": "reference", "cores": 0, "value": line["value"], "unit": UNIT,
-                                "sample": "the reference's own implementation of this path is CUDA: unmodified "
-                                          "rasteriser sources built for sm_100 (oracle/_ref), timed on the same GPU; "
-                                          "its CPU port is `--impl reference-cpu`"}
-    emit(line)
+                                "sample": "the reference's own implementation of this path is CUDA + PyTorch-on-CUDA, timed on "
+                                          "the same GPU: LBS / covariance / SH = " + arm.lbs_source + "; rasteriser = its "
+                                          "unmodified CUDA sources built for sm_100 (oracle/_ref); its CPU port is "
+                                          "`--impl reference-cpu`"}
+    del arm
+    torch.cuda.empty_cache()
+    return line
+
+
+def main():
+    global _REAL_STDOUT
+    args = parse()
+    # NCCL (version banner), nvidia-smi children and the like write to fd 1 behind Python's back: point fd 1 at stderr for
+    # the whole run and keep the original for the result line
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+    world, rank, local = init_dist(args)
+    if args.impl == "reference-cpu":
+        run_reference_cpu(args, world, rank)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device. The hot path has no CPU fallback "
+                         "(use --impl reference-cpu for the CPU oracle baseline).")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    K, Wm = args.steps, max(args.warmup, 3)
+    try:
+        line = run_workload(args, args.workload, world, rank, local, dev, K, Wm, headline=True)
+    except (FileNotFoundError, OSError) as e:
+        if args.impl != "reference":
+            raise
+        if rank == 0:
+            emit({"impl": "reference", "unavailable": f"oracle/_ref not built: {e}"})
+        return
+    if world > 1 and args.workload == "zju_512" and not args.no_extras:
+        # BASELINE.json config 4 (64 cameras x 300k Gaussians, view-sharded) rides along in multi-GPU runs
+        K4 = max(2, min(K, 10))
+        sub = run_workload(args, "multiview_300k", world, rank, local, dev, K4, 3, headline=False)
+        if rank == 0 and sub is not None:
+            line["multiview_300k"] = {k: sub[k] for k in ("value", "unit", "ms_per_step", "steps", "config", "e2e",
+                                                          "wall_clock_value", "gpu_launches") if k in sub}
+            if "sharded_step_check" in sub:
+                line["multiview_300k"]["sharded_step_check"] = sub["sharded_step_check"]
+    if rank == 0:
+        emit(line)
 
 
 if __name__ == "__main__":

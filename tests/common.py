@@ -116,3 +116,15 @@ def rel_err(a, b):
     """max |a-b| / max(|b|_inf, tiny): the 'relative to the tensor scale' error used for gradients."""
     a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
     return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)) if a.size else 0.0
+
+
+def grad_close(name, a, b, rel=1e-4):
+    """Per-element gradient criterion of the parity tests (north_star: parameter gradients within 1e-4 rel):
+    |a - b| <= rel * |b| + 0.1 * rel * max|b| for EVERY element -- the second term is the floor below which the order
+    of fp32 accumulation (atomics on both sides) decides."""
+    a = np.asarray(a, np.float64).reshape(-1); b = np.asarray(b, np.float64).reshape(-1)
+    assert a.shape == b.shape, name
+    scale = max(np.abs(b).max(), 1e-30) if b.size else 1.0
+    err = np.abs(a - b)
+    bad = err > rel * np.abs(b) + rel * 1e-1 * scale
+    assert not bad.any(), f"{name}: {bad.sum()} of {a.size} elements off, max err {err.max():.3e} (scale {scale:.3e})"

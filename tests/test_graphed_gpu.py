@@ -3,14 +3,15 @@ operator API computes, for every view, and notices when a view needs more binnin
 captured with.
 
 Tolerance: same kernels on both sides; the only difference is the order of the fp32 atomics in the backward
-accumulators, hence 2e-5 of each gradient tensor's scale (images and loss: 1e-6).
+accumulators, hence 3e-5 of each gradient tensor's scale AND, per element, |a-b| <= 1e-4 |b| + 1e-5 max|b|
+(tests.common.grad_close; north_star: gradients within 1e-4 rel); images and loss: 1e-6.
 """
 import numpy as np
 import pytest
 import torch
 
 from mygauhuman_b200 import synthetic as S
-from tests.common import rel_err as _rel_err
+from tests.common import grad_close, rel_err as _rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -19,6 +20,10 @@ P, W, H = 6000, 160, 128
 
 def rel_err(a, b):
     return _rel_err(a.detach().cpu().numpy(), b.detach().cpu().numpy())
+
+
+def _cpu(t):
+    return t.detach().cpu().numpy()
 
 
 def _loss(color, depth, alpha, targets):
@@ -116,7 +121,8 @@ def test_accumulate_mode_sums_the_views_of_a_batch(smpl_model):
         torch.cuda.synchronize()
         for k in want:
             assert leaves[k].grad.data_ptr() == got[k].data_ptr()
-            assert rel_err(got[k], want[k]) < 3e-5, k
+            assert rel_err(got[k], want[k]) < 3e-5, k          # tensor-scale bound: max|a-b| / max|b|
+            grad_close(k, _cpu(got[k]), _cpu(want[k]), rel=1e-4)  # per element: |a-b| <= 1e-4 |b| + 1e-5 max|b|
     assert acc.check()
 
 
@@ -178,7 +184,8 @@ def test_multi_lane_batches_match_the_single_lane_sum(smpl_model):
             assert abs(a - b) <= 1e-5 * max(1.0, abs(b))
         for k in want:
             assert leaves[k].grad.data_ptr() == got[k].data_ptr()
-            assert rel_err(got[k], want[k]) < 3e-5, k
+            assert rel_err(got[k], want[k]) < 3e-5, k          # tensor-scale bound: max|a-b| / max|b|
+            grad_close(k, _cpu(got[k]), _cpu(want[k]), rel=1e-4)  # per element: |a-b| <= 1e-4 |b| + 1e-5 max|b|
     # a ragged last group (2 of 3 lanes) and host inputs through the prefetch pipeline
     host_vecs = [v.cpu().pin_memory() for v in vecs]
     host_targets = targets.cpu().pin_memory()
@@ -201,6 +208,7 @@ def test_multi_lane_batches_match_the_single_lane_sum(smpl_model):
     ml._alias_grads()  # (the eager reference above re-pointed leaves[k].grad)
     for k in part:
         assert rel_err(got[k], part[k]) < 3e-5, k
+        grad_close(k, _cpu(got[k]), _cpu(part[k]), rel=1e-4)
     assert ml.check()
     # overflow on any lane is seen and every lane is re-captured
     for lane in ml.lanes:

@@ -82,7 +82,9 @@ def _compare_forward(tc, fw, ref, rfw, sh_mode):
     return int(vis.sum())
 
 
-def _compare_backward(tc, fw, ref, rfw):
+def _compare_backward(tc, fw, ref, rfw, noise_only=()):
+    """`noise_only`: gradients that are analytically zero for the case (both sides return fp32 cancellation noise):
+    checked to BE noise -- tiny against the matching scale gradient -- instead of element by element."""
     rn, rcolor, rdepth, ralpha, rradii = rfw
     g = Cm.ours_backward(tc, fw)
     rg = ref.backward(tc["bg"], tc["means3D"], rradii, tc["colors"], tc["scales"], tc["rotations"], tc["scale_modifier"],
@@ -92,6 +94,10 @@ def _compare_backward(tc, fw, ref, rfw):
              "dL_drotations"]
     for name, ours in zip(names, g):
         assert tuple(ours.shape) == tuple(rg[name].shape), name
+        if name in noise_only:
+            ref_scale = float(rg["dL_dscales"].abs().max())
+            assert float(ours.abs().max()) <= 1e-4 * ref_scale and float(rg[name].abs().max()) <= 1e-4 * ref_scale, name
+            continue
         _grad_close(name, _np(ours), _np(rg[name]))
 
 
@@ -199,7 +205,8 @@ def test_adversarial_tile_and_block_boundaries(W, H):
     m2 = _np(st["means2D"])[_np(fw[4]) > 0]
     on_block = (np.abs(m2 / 4.0 - np.round(m2 / 4.0)) < 1e-3).all(1).mean()
     assert on_block > 0.9, on_block
-    _compare_backward(tc, fw, ref, rfw)
+    # isotropic scales: the covariance does not depend on the rotation, dL_drotations is analytically zero
+    _compare_backward(tc, fw, ref, rfw, noise_only=("dL_drotations",))
 
 
 def test_fused_lbs_at_50k_against_fp64_oracle(smpl_model):
