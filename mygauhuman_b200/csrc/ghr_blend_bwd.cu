@@ -150,7 +150,15 @@ template <int BATCH, int NSTAGE, int NX>
 __host__ __device__ constexpr size_t blend_bwd_warp_smem()
 {
     return ((sizeof(float4) * 3 + sizeof(uint32_t) + sizeof(float) * attr_row_floats<NX>()) * NSTAGE * BATCH +
-            sizeof(uint32_t) * NSTAGE * (BATCH / 32) + 15) / 16 * 16;
+            (sizeof(uint8_t) * BATCH + sizeof(uint32_t) * 4) * NSTAGE + 15) / 16 * 16;
+}
+
+// see ghr_blend_fwd.cu: one 64-bit load per list entry, consumed only at the next staging step
+__device__ __forceinline__ uint2 ld_entry_b(const uint2* p)
+{
+    uint2 v;
+    asm volatile("ld.global.nc.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
 }
 
 // Persistent kernel: warps pull (tile, 4x4 block) work items from a queue ordered by decreasing tile-list
@@ -165,21 +173,26 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
     const float* __restrict__ xcol, const float* __restrict__ xdpix, float* __restrict__ xaccum)
 {
     constexpr int PER_LANE = BATCH / 32;
+    static_assert(BATCH <= 256, "staged positions are bytes");
     using AL = AttrLayout<(NX ? NX : 2)>;
     constexpr int XS = attr_row_floats<NX>(), XH = AL::XH, CHS = AL::CHS;
-    // per-warp staging ring in dynamic shared memory: records, ids, survivor bits(, attribute rows)
+    // per-warp staging ring in dynamic shared memory; the survivors of a round are staged COMPACTED in walk order
+    // (ghr_blend_fwd.cu): records, ids, per staged record its position inside the round (a byte), per stage the
+    // survivor count(, attribute rows)
     extern __shared__ __align__(16) unsigned char bwd_smem[];
     constexpr size_t kWarpBytes = blend_bwd_warp_smem<BATCH, NSTAGE, NX>();
     static_assert(kWarpBytes % 16 == 0, "per-warp staging area must keep float4 alignment");
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t slot = lane >> 4, pl = lane & 15u;  // which of the pixel's two lanes; pixel inside the 4x4 block
+    const uint32_t lt_mask = (1u << lane) - 1u;
     unsigned char* wbase = bwd_smem + warp * kWarpBytes;
     float4(*s_rec)[BATCH * 3] = reinterpret_cast<float4(*)[BATCH * 3]>(wbase);
     uint32_t(*s_id)[BATCH] = reinterpret_cast<uint32_t(*)[BATCH]>(wbase + sizeof(float4) * NSTAGE * BATCH * 3);
-    uint32_t(*s_keep)[PER_LANE] =
-        reinterpret_cast<uint32_t(*)[PER_LANE]>(wbase + sizeof(float4) * NSTAGE * BATCH * 3 + sizeof(uint32_t) * NSTAGE * BATCH);
-    float* s_x = reinterpret_cast<float*>(wbase + (sizeof(float4) * 3 + sizeof(uint32_t)) * NSTAGE * BATCH +
-                                          (sizeof(uint32_t) * NSTAGE * PER_LANE + 15) / 16 * 16);  // [NSTAGE][BATCH][XS]
+    float* s_x = reinterpret_cast<float*>(wbase + (sizeof(float4) * 3 + sizeof(uint32_t)) * NSTAGE * BATCH);  // [NSTAGE][BATCH][XS]
+    uint8_t(*s_pos)[BATCH] = reinterpret_cast<uint8_t(*)[BATCH]>(
+        wbase + (sizeof(float4) * 3 + sizeof(uint32_t) + sizeof(float) * XS) * NSTAGE * BATCH);
+    uint32_t* s_cnt = reinterpret_cast<uint32_t*>(
+        wbase + (sizeof(float4) * 3 + sizeof(uint32_t) + sizeof(float) * XS + 1) * NSTAGE * BATCH);
     int xidx[2];  // which of the pair's 2*CHS attribute colour gradients this lane holds after half_reduce_n
     xidx[0] = reduce_index<2 * CHS>(lane, 0);
     xidx[1] = reduce_index<2 * CHS>(lane, 1);
@@ -250,94 +263,85 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
         // round r stages list positions walk-1-r*BATCH-slot (back to front).  Entries are fetched one round ahead of
         // the record copies (two dependent L2 round trips otherwise), records two rounds ahead of their use; only the
         // records of Gaussians whose block mask has this block's bit are copied.
-        uint32_t nid[PER_LANE];
-        auto load_ids = [&](int round) {
+        uint2 ent[PER_LANE];
+        auto load_ids = [&](int round) {  // issue only (ld_entry_b)
 #pragma unroll
             for (int u = 0; u < PER_LANE; u++) {
-                const int progress = round * BATCH + (int)lane + u * 32;
-                nid[u] = 0xFFFFFFFFu;
-                if (round < rounds && progress < walk) {
-                    const uint2 e = entries[range.x + (uint32_t)(walk - 1 - progress)];
-                    if ((e.y >> wb) & 1u) nid[u] = e.x;
-                }
+                const int progress = min(round * BATCH + (int)lane + u * 32, walk - 1);
+                ent[u] = ld_entry_b(entries + range.x + (uint32_t)(walk - 1 - progress));
             }
         };
-        auto stage = [&](int buf) {
+        auto stage = [&](int buf, int round) {
+            uint32_t total = 0;
 #pragma unroll
             for (int u = 0; u < PER_LANE; u++) {
                 const int sl = (int)lane + u * 32;
-                const bool keep = nid[u] != 0xFFFFFFFFu;
+                const bool keep = round < rounds && round * BATCH + sl < walk && ((ent[u].y >> wb) & 1u);
                 const uint32_t bits = __ballot_sync(0xffffffffu, keep);
-                if (lane == 0) s_keep[buf][u] = bits;
                 if (keep) {
-                    s_id[buf][sl] = nid[u];
-                    const float4* src = rec + 3 * (size_t)nid[u];
-                    float4* dst = &s_rec[buf][sl * 3];
+                    const uint32_t pos = total + __popc(bits & lt_mask);
+                    s_id[buf][pos] = ent[u].x;
+                    s_pos[buf][pos] = (uint8_t)sl;
+                    const float4* src = rec + 3 * (size_t)ent[u].x;
+                    float4* dst = &s_rec[buf][pos * 3];
                     cp_async16b(dst, src);
                     cp_async16b(dst + 1, src + 1);
                     cp_async16b(dst + 2, src + 2);
                     if constexpr (NX > 0) {
-                        const float* xsrc = xcol + (size_t)nid[u] * XS;
-                        float* xdst = s_x + ((size_t)buf * BATCH + sl) * XS;
+                        const float* xsrc = xcol + (size_t)ent[u].x * XS;
+                        float* xdst = s_x + ((size_t)buf * BATCH + pos) * XS;
 #pragma unroll
                         for (int c = 0; c < XS; c += 4) cp_async16b(xdst + c, xsrc + c);
                     }
                 }
+                total += __popc(bits);
             }
+            if (lane == 0) s_cnt[buf] = total;
             asm volatile("cp.async.commit_group;" ::: "memory");
         };
 
         {
-            uint32_t pre[NSTAGE - 1][PER_LANE];
+            uint2 pre[NSTAGE - 1][PER_LANE];
 #pragma unroll
             for (int q = 0; q < NSTAGE - 1; q++) {
                 load_ids(q);
 #pragma unroll
-                for (int u = 0; u < PER_LANE; u++) pre[q][u] = nid[u];
+                for (int u = 0; u < PER_LANE; u++) pre[q][u] = ent[u];
             }
 #pragma unroll
             for (int q = 0; q < NSTAGE - 1; q++) {
 #pragma unroll
-                for (int u = 0; u < PER_LANE; u++) nid[u] = pre[q][u];
-                stage(q);
+                for (int u = 0; u < PER_LANE; u++) ent[u] = pre[q][u];
+                stage(q, q);
             }
             load_ids(NSTAGE - 1);
         }
-        int toDo = walk;
-        for (int i = 0; i < rounds; i++, toDo -= BATCH) {
+        for (int i = 0; i < rounds; i++) {
             const int buf = i % NSTAGE;
-            stage((i + NSTAGE - 1) % NSTAGE);
-            load_ids(i + NSTAGE);
+            stage((i + NSTAGE - 1) % NSTAGE, i + NSTAGE - 1);
+            if (i + NSTAGE < rounds) load_ids(i + NSTAGE);
             asm volatile("cp.async.wait_group %0;" ::"n"(NSTAGE - 1) : "memory");
             __syncwarp();
-            const int n = min(BATCH, toDo);
             const float4* r = s_rec[buf];
             const float* rf = reinterpret_cast<const float*>(r);
 #ifdef GHR_TRACE
             trace_rounds++;
 #endif
             BTRACE_LAP(c_wait)
-            // entry j of this round sits at list position pos(j) = walk-1-(i*BATCH+j); the reference's
-            // `contributor` for it equals pos(j) (backward.cu:499-501: skip if contributor >= last_contributor)
+            // staged record j of this round came from round entry s_pos[j], i.e. list position
+            // pos0 - s_pos[j]; the reference's `contributor` for it equals that position (backward.cu:499-501: skip if
+            // contributor >= last_contributor)
             const int pos0 = walk - 1 - i * BATCH;
-            // The round's survivors (one bit per staged entry, see stage) are consumed eight at a time ACROSS the 32-entry
-            // words, so a step is full except at the end of the round.
-            (void)n;
-            int g = 0;
-            uint32_t mask = s_keep[buf][0];
-            for (;;) {
-                while (mask == 0 && g + 32 < BATCH) { g += 32; mask = s_keep[buf][g >> 5]; }
-                if (mask == 0) break;
+            const int n = (int)s_cnt[buf];  // survivors of the round, contiguous, in walk order
+            for (int s0 = 0; s0 < n; s0 += 8) {
                 {
                     // eight survivors in walk order; slot 0 owns j[0] j[2] j[4] j[6], slot 1 the others
                     int j[8];
                     bool v_ok[8];
 #pragma unroll
                     for (int u = 0; u < 8; u++) {
-                        while (mask == 0 && g + 32 < BATCH) { g += 32; mask = s_keep[buf][g >> 5]; }
-                        v_ok[u] = mask != 0;
-                        j[u] = v_ok[u] ? g + __ffs(mask) - 1 : j[0];
-                        mask &= mask - 1;
+                        v_ok[u] = s0 + u < n;
+                        j[u] = v_ok[u] ? s0 + u : s0;
                     }
                     // phase 1 (independent: ILP): G / alpha of the four Gaussians this lane owns; alpha 0 = not valid here
                     float G[4], al[4], dx[4], dy[4], depth_own[4];
@@ -354,7 +358,8 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
                         const float power = pair_power(dx[q], dy[q], con[q].x, con[q].y, con[q].z);
                         G[q] = expf(power);
                         const float alpha = fminf(0.99f, __fmul_rn(con[q].w, G[q]));
-                        const bool valid = ok && (pos0 - jm[q] < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                        const bool valid = ok && (pos0 - (int)s_pos[buf][jm[q]] < last_contributor) && !(power > 0.0f) &&
+                                           !(alpha < 1.0f / 255.0f);
                         al[q] = valid ? alpha : 0.0f;
                     }
                     float a[8];
@@ -542,8 +547,13 @@ cudaError_t launch_blend_backward(const ghr_raster_params& p, const char* geom, 
     if (blend_shared_gpu())
         return launch_bwd_config<128, 2, 0>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, nullptr,
                                             nullptr, nullptr, s);
+#ifdef GHR_BWD_BATCH  // tuning builds only
+    return launch_bwd_config<GHR_BWD_BATCH, GHR_BWD_NSTAGE, 0>(GHR_BWD_CTAS, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, nullptr, nullptr,
+                                        nullptr, s);
+#else
     return launch_bwd_config<256, 2, 0>(2, p, geom, binning, img, L, dL_dpix, dL_ddepth, dL_dalpha, accum, nullptr, nullptr,
                                         nullptr, s);
+#endif
 }
 
 // Main image + n_attr (2, 4 or 6) packed attributes in one walk; latency regime only (ghr_api.cu checks).

@@ -51,6 +51,22 @@ __device__ __forceinline__ void cp_async_wait()
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+#ifdef GHR_TRACE  // tuning builds only (tools/build_variant.sh): per-item begin/end timestamps and phase cycle counts
+__device__ unsigned long long g_fwd_trace[1 << 16][8];
+__device__ __forceinline__ unsigned long long gtime()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ uint32_t smid()
+{
+    uint32_t v;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(v));
+    return v;
+}
+#endif
+
 // Staging: 256-entry rounds in a 2-deep per-warp ring, one warp per CTA, 8 CTAs per SM.  Long rounds amortise the
 // per-round cost and few co-resident warps leave the heavy items the issue slots (measured, tools/fwd_trace.py).
 // Frames with millions of pairs take the other kernel family (ghr_blend_fwd_wide.cu), see launch_blend_forward.
@@ -66,7 +82,19 @@ template <int BATCH, int NSTAGE, int NX>
 __host__ __device__ constexpr size_t blend_fwd_warp_smem()
 {
     return ((sizeof(float4) * 3 + sizeof(float) * attr_row_floats<NX>()) * BATCH * NSTAGE +
-            sizeof(uint32_t) * (BATCH / 32) * NSTAGE + 15) / 16 * 16;
+            (sizeof(uint8_t) * BATCH + sizeof(uint32_t) * 4) * NSTAGE + 15) / 16 * 16;
+}
+
+// One 8-byte list entry {Gaussian id, block mask}, read-only path.  Always a single 64-bit load that nothing consumes
+// until the next staging step: the loads of a whole round are in flight together and their latency hides behind the
+// evaluation of the current round.  (Written as `const uint2 e = entries[k]; if ((e.y >> wb) & 1) id = e.x;` the
+// compiler split every entry into two DEPENDENT 32-bit loads behind branches: sixteen exposed L2 round trips per
+// 256-entry round, 41 % of the kernel's warp time in the per-item trace.)
+__device__ __forceinline__ uint2 ld_entry(const uint2* p)
+{
+    uint2 v;
+    asm volatile("ld.global.nc.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
 }
 
 template <int BATCH, int NSTAGE, int WARPS, int NX>
@@ -79,18 +107,24 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
     float* __restrict__ out_x)
 {
     constexpr int PER_LANE = BATCH / 32;
+    static_assert(BATCH <= 256, "staged positions are bytes");
     using AL = AttrLayout<(NX ? NX : 2)>;
     constexpr int XS = attr_row_floats<NX>(), XH = AL::XH, CHS = AL::CHS;
-    // per-warp staging ring in dynamic shared memory: records, (attribute rows,) then one survivor bit per staged entry
+    // per-warp staging ring in dynamic shared memory.  The survivors of a round (entries whose block mask has this
+    // block's bit) are staged COMPACTED, in list order: records (, attribute rows), then per staged record its position
+    // inside the round (a byte) and per stage the survivor count.  The evaluation loop walks 0..count-1 and never looks
+    // at a mask word.
     extern __shared__ __align__(16) unsigned char fwd_smem[];
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t slot = lane >> 4, pl = lane & 15u;  // which of the pixel's two lanes; pixel inside the 4x4 block
+    const uint32_t lt_mask = (1u << lane) - 1u;
     unsigned char* wbase = fwd_smem + warp * blend_fwd_warp_smem<BATCH, NSTAGE, NX>();
     float4(*s_rec)[BATCH * 3] = reinterpret_cast<float4(*)[BATCH * 3]>(wbase);
     float* s_x = reinterpret_cast<float*>(wbase + sizeof(float4) * 3 * BATCH * NSTAGE);  // [NSTAGE][BATCH][XS]
-    uint32_t(*s_keep)[PER_LANE] = reinterpret_cast<uint32_t(*)[PER_LANE]>(
+    uint8_t(*s_pos)[BATCH] = reinterpret_cast<uint8_t(*)[BATCH]>(
         wbase + (sizeof(float4) * 3 + sizeof(float) * XS) * BATCH * NSTAGE);
+    uint32_t* s_cnt = reinterpret_cast<uint32_t*>(wbase + (sizeof(float4) * 3 + sizeof(float) * XS + 1) * BATCH * NSTAGE);
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE;
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
     // {Gaussian id, 4x4-block mask} per list entry, written by tile_ranges_kernel into the key buffer the sort left unused
@@ -122,40 +156,41 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
         const int rounds = (todo_total + BATCH - 1) / BATCH;
 
         // Staging pipeline.  A record gather is two dependent L2 round trips (list entry -> record); the entries of a
-        // round are therefore loaded into registers one round before their records are copied.  Only the records of
-        // Gaussians whose block mask has this block's bit are copied; the round's survivor bits go to s_keep.
-        uint32_t nid[PER_LANE];
+        // round are therefore loaded into registers one round before their records are copied -- issued only, see
+        // ld_entry.  Only the records of Gaussians whose block mask has this block's bit are copied, compacted.
+        uint2 ent[PER_LANE];
         auto load_ids = [&](int round) {
 #pragma unroll
             for (int u = 0; u < PER_LANE; u++) {
                 const uint32_t k = range.x + (uint32_t)round * BATCH + lane + u * 32;
-                nid[u] = 0xFFFFFFFFu;
-                if (round < rounds && k < range.y) {
-                    const uint2 e = entries[k];
-                    if ((e.y >> wb) & 1u) nid[u] = e.x;
-                }
+                ent[u] = ld_entry(entries + min(k, range.y - 1u));  // (range.y > range.x whenever this runs)
             }
         };
-        auto stage = [&](int buf) {  // copies the records of the ids held in nid[]
+        auto stage = [&](int buf, int round) {  // copies the surviving records of the entries held in ent[] (= round's)
+            uint32_t total = 0;
 #pragma unroll
             for (int u = 0; u < PER_LANE; u++) {
-                const bool keep = nid[u] != 0xFFFFFFFFu;
+                const uint32_t k = range.x + (uint32_t)round * BATCH + lane + u * 32;
+                const bool keep = round < rounds && k < range.y && ((ent[u].y >> wb) & 1u);
+                const uint32_t bits = __ballot_sync(0xffffffffu, keep);
                 if (keep) {
-                    const float4* src = rec + 3 * (size_t)nid[u];
-                    float4* dst = &s_rec[buf][(lane + u * 32) * 3];
+                    const uint32_t pos = total + __popc(bits & lt_mask);
+                    const float4* src = rec + 3 * (size_t)ent[u].x;
+                    float4* dst = &s_rec[buf][pos * 3];
                     cp_async16(dst, src);
                     cp_async16(dst + 1, src + 1);
                     cp_async16(dst + 2, src + 2);
                     if constexpr (NX > 0) {
-                        const float* xsrc = xcol + (size_t)nid[u] * XS;
-                        float* xdst = s_x + ((size_t)buf * BATCH + lane + u * 32) * XS;
+                        const float* xsrc = xcol + (size_t)ent[u].x * XS;
+                        float* xdst = s_x + ((size_t)buf * BATCH + pos) * XS;
 #pragma unroll
                         for (int c = 0; c < XS; c += 4) cp_async16(xdst + c, xsrc + c);
                     }
+                    s_pos[buf][pos] = (uint8_t)(lane + u * 32);
                 }
-                const uint32_t bits = __ballot_sync(0xffffffffu, keep);
-                if (lane == 0) s_keep[buf][u] = bits;
+                total += __popc(bits);
             }
+            if (lane == 0) s_cnt[buf] = total;
             cp_async_commit();
         };
 
@@ -170,26 +205,25 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
 
         if (rounds > 0) {
             // prologue: all list entries of the first NSTAGE-1 rounds are requested before the first record copy
-            uint32_t pre[NSTAGE - 1][PER_LANE];
+            uint2 pre[NSTAGE - 1][PER_LANE];
 #pragma unroll
             for (int q = 0; q < NSTAGE - 1; q++) {
                 load_ids(q);
 #pragma unroll
-                for (int u = 0; u < PER_LANE; u++) pre[q][u] = nid[u];
+                for (int u = 0; u < PER_LANE; u++) pre[q][u] = ent[u];
             }
 #pragma unroll
             for (int q = 0; q < NSTAGE - 1; q++) {
 #pragma unroll
-                for (int u = 0; u < PER_LANE; u++) nid[u] = pre[q][u];
-                stage(q);
+                for (int u = 0; u < PER_LANE; u++) ent[u] = pre[q][u];
+                stage(q, q);
             }
             load_ids(NSTAGE - 1);
         }
-        int toDo = todo_total;
-        for (int i = 0; i < rounds; i++, toDo -= BATCH) {
+        for (int i = 0; i < rounds; i++) {
             const int buf = i % NSTAGE;
-            stage((i + NSTAGE - 1) % NSTAGE);  // records of round i+NSTAGE-1 (an empty group past the end keeps the count uniform)
-            load_ids(i + NSTAGE);
+            stage((i + NSTAGE - 1) % NSTAGE, i + NSTAGE - 1);  // records of round i+NSTAGE-1 (an empty group past the end keeps the count uniform)
+            if (i + NSTAGE < rounds) load_ids(i + NSTAGE);
             cp_async_wait<NSTAGE - 1>();       // this lane's copies for rounds <= i have landed
             __syncwarp();             // ... and everybody else's
             if (__all_sync(0xffffffffu, done)) break;  // forward.cu:313-315, per block instead of per tile
@@ -197,39 +231,23 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
             trace_rounds++;
 #endif
             TRACE_LAP(c_wait)
-            const int n = min(BATCH, toDo);
             const float4* r = s_rec[buf];
             const float* rf = reinterpret_cast<const float*>(r);
-            const uint32_t base = (uint32_t)i * BATCH;  // list position of r[0]
-            // (1) The round's survivors (one bit per staged entry: block mask, see stage) are consumed (2) KSTEP at a
-            // time in list order, across the 32-entry words: even ones are evaluated by slot 0, odd ones by slot 1.
-            (void)n;
-            int g = 0;
-            uint32_t mask = s_keep[buf][0];
-            for (;;) {
-                while (mask == 0 && g + 32 < BATCH) { g += 32; mask = s_keep[buf][g >> 5]; }
-                if (mask == 0) break;
-                TRACE_LAP(c_cull)
+            const uint32_t base = (uint32_t)i * BATCH;  // list position of the round's first entry
+            const int n = (int)s_cnt[buf];               // survivors of the round, staged contiguously in list order
+            int last_k = -1;                             // staged index of the last contributor inside this round
+            // Survivors are consumed KSTEP at a time in list order: even ones are evaluated by slot 0, odd ones by slot 1.
+            for (int s0 = 0; s0 < n; s0 += KSTEP) {
 #ifdef GHR_TRACE
                 trace_steps++;
+                trace_surv += min(KSTEP, n - s0);
 #endif
-                int j[KSTEP];
-                bool v[KSTEP];
-#pragma unroll
-                for (int u = 0; u < KSTEP; u++) {
-                    while (mask == 0 && g + 32 < BATCH) { g += 32; mask = s_keep[buf][g >> 5]; }
-                    v[u] = mask != 0;
-#ifdef GHR_TRACE
-                    trace_surv += v[u];
-#endif
-                    j[u] = v[u] ? g + __ffs(mask) - 1 : j[0];
-                    mask &= mask - 1;
-                }
                 float mine[KSTEP / 2];
 #pragma unroll
                 for (int u = 0; u < KSTEP / 2; u++) {
-                    const int jm = slot ? j[2 * u + 1] : j[2 * u];
-                    const bool vm = slot ? v[2 * u + 1] : v[2 * u];
+                    const int jq = s0 + 2 * u + (int)slot;
+                    const bool vm = jq < n;
+                    const int jm = vm ? jq : s0;
                     const float4 r0 = r[3 * jm], r1 = r[3 * jm + 1];
                     const float dx = __fsub_rn(r0.x, pxf), dy = __fsub_rn(r0.y, pyf);
                     const float power = pair_power(dx, dy, r1.x, r1.y, r1.z);
@@ -248,8 +266,9 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
                 float x0[KSTEP], x1[KSTEP], om[KSTEP];
 #pragma unroll
                 for (int u = 0; u < KSTEP; u++) {
-                    const float4 r2 = r[3 * j[u] + 2];
-                    const float depth = rf[12 * j[u] + 2];
+                    const int ju = min(s0 + u, n - 1);
+                    const float4 r2 = r[3 * ju + 2];
+                    const float depth = rf[12 * ju + 2];
                     x0[u] = __fmul_rn(alpha[u], slot ? r2.z : r2.x);
                     x1[u] = __fmul_rn(alpha[u], slot ? depth : r2.y);
                     om[u] = __fsub_rn(1.0f, alpha[u]);
@@ -265,7 +284,8 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
                     A1 = acc ? __fmaf_rn(T, x1[u], A1) : A1;
                     A2 = acc ? __fmaf_rn(T, alpha[u], A2) : A2;
                     if constexpr (NX > 0) {
-                        const float2* cx = reinterpret_cast<const float2*>(s_x + ((size_t)buf * BATCH + j[u]) * XS + slot * XH);
+                        const int ju = min(s0 + u, n - 1);
+                        const float2* cx = reinterpret_cast<const float2*>(s_x + ((size_t)buf * BATCH + ju) * XS + slot * XH);
 #pragma unroll
                         for (int c = 0; c < CHS; c += 2) {
                             const float2 cc = cx[c >> 1];
@@ -273,12 +293,13 @@ __global__ void __launch_bounds__(WARPS * 32) blend_forward_kernel(
                             if (c + 1 < CHS) X[c + 1] = acc ? __fmaf_rn(T, __fmul_rn(alpha[u], cc.y), X[c + 1]) : X[c + 1];
                         }
                     }
-                    last_contributor = acc ? base + (uint32_t)j[u] + 1u : last_contributor;
+                    last_k = acc ? s0 + u : last_k;
                     T = acc ? test_T : T;
                 }
-                if (__all_sync(0xffffffffu, done)) { mask = 0; g = BATCH; }
                 TRACE_LAP(c_eval)
+                if (__all_sync(0xffffffffu, done)) break;
             }
+            if (last_k >= 0) last_contributor = base + (uint32_t)s_pos[buf][last_k] + 1u;
             __syncwarp();  // buffer `buf` is re-filled by the stage() of the next iteration (round i+NSTAGE)
         }
         cp_async_wait<0>();
@@ -366,7 +387,11 @@ cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, c
     if (blend_shared_gpu())  // several views in flight (MultiLaneRenderStep): half the staging per warp, so that the
                              // blend kernels of two views fit an SM together
         return launch_fwd_config<128, 2, 1, 0>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, nullptr, nullptr, s);
+#ifdef GHR_FWD_BATCH  // tuning builds only
+    return launch_fwd_config<GHR_FWD_BATCH, GHR_FWD_NSTAGE, 1, 0>(GHR_FWD_CTAS, p, geom, binning, img, L, out_color, out_depth, out_alpha, nullptr, nullptr, s);
+#else
     return launch_fwd_config<256, 2, 1, 0>(8, p, geom, binning, img, L, out_color, out_depth, out_alpha, nullptr, nullptr, s);
+#endif
 }
 
 // Main image + n_attr (2, 4 or 6) packed attributes in one walk; latency regime only (ghr_api.cu checks).

@@ -5,9 +5,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.ins
 import bench
 from mygauhuman_b200 import _lib
 
-ITEMS_PER_TILE = int(os.environ.get("BWD_ITEMS", "8"))
+ITEMS_PER_TILE = int(os.environ.get("BWD_ITEMS", "16"))
 WARPS = int(os.environ.get("BWD_WARPS_TOTAL", str(148 * 16)))
-class A: workload = "zju_512"; views = 4
+class A: workload = "zju_512"; views = 4; targets = "u8"
 wl = bench.build_workload(A, 0, 1)
 dev = torch.device("cuda")
 arm = bench.OursArm(wl, dev, False)

@@ -6,7 +6,7 @@ import bench
 from mygauhuman_b200 import _lib
 from mygauhuman_b200.diff_gaussian_rasterization import _C
 
-class A: workload = "zju_512"; views = 4
+class A: workload = "zju_512"; views = 4; targets = "u8"
 wl = bench.build_workload(A, 0, 1)
 dev = torch.device("cuda")
 arm = bench.OursArm(wl, dev, False)

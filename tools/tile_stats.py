@@ -5,7 +5,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.ins
 import bench
 from mygauhuman_b200.diff_gaussian_rasterization import _C
 
-class A: workload = sys.argv[1] if len(sys.argv) > 1 else "zju_512"; views = 4
+class A: workload = sys.argv[1] if len(sys.argv) > 1 else "zju_512"; views = 4; targets = "u8"
 wl = bench.build_workload(A, 0, 1)
 dev = torch.device("cuda")
 arm = bench.OursArm(wl, dev, False)
