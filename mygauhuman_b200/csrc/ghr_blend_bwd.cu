@@ -257,6 +257,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
         }
         // per-pixel recurrence state, carried identically by both lanes of the pixel
         float T = T_final;
+        float Bacc = T_final * bg_dot;  // NX == 0: the scalar buffer B of phase 2, seeded with the background term
         float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
         float accum_depth_rec = 0.f, accum_alpha_rec = 0.f, last_alpha = 0.f, last_depth = 0.f;
 
@@ -376,7 +377,65 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
                     if (!__any_sync(0xffffffffu, (a[0] > 0.f) | (a[1] > 0.f) | (a[2] > 0.f) | (a[3] > 0.f) | (a[4] > 0.f) |
                                                      (a[5] > 0.f) | (a[6] > 0.f) | (a[7] > 0.f)))
                         continue;
-                    // phases 2 and 3, one pair of Gaussians (one per slot) at a time
+                    if constexpr (NX == 0) {
+                        // Single-attribute kernel.  Phase 2, the sequential part, carries TWO scalars per pixel instead of
+                        // the reference's six recurrences (backward.cu:508-560): with g = (dL_dpixel, dL_ddepth, dL_dalpha)
+                        // and s_k = <(colour_k, depth_k, 1), g>, the reference's
+                        //     dL_dalpha_k = T_k <(c_k - accum_rec_k), g> - T_final / (1 - alpha_k) <bg, dL_dpixel>
+                        // equals  s_k T_k - B_k / (1 - alpha_k)  where  B_k = T_final <bg, dL_dpixel> + sum_{j behind k} s_j alpha_j T_j
+                        // (accum_rec_k T_k = (sum_{j behind k} c_j alpha_j T_j) / (1 - alpha_k)).  alpha = 0 (skipped here)
+                        // leaves T and B unchanged without any select, so the chain is branch-free: per Gaussian one
+                        // reciprocal, the dot product s, and three multiply-adds.  Phase 3 (gradients of this lane's own
+                        // four Gaussians, 16-lane reductions, atomics) is straight-line code over the four, so the four
+                        // independent butterfly reductions overlap.
+                        float Town[8], Bown[8], sown[8], rown[8];
+#pragma unroll
+                        for (int k = 0; k < 8; k++) {
+                            const float4 c = r[3 * j[k] + 2];
+                            const float dep = rf[12 * j[k] + 2];
+                            sown[k] = fmaf(c.x, dpix0, fmaf(c.y, dpix1, fmaf(c.z, dpix2, fmaf(dep, dL_ddepth, dL_dalpha))));
+                            rown[k] = __fdividef(1.0f, 1.0f - a[k]);
+                            T *= rown[k];
+                            Town[k] = T; Bown[k] = Bacc;
+                            Bacc = fmaf(sown[k], a[k] * T, Bacc);
+                        }
+                        uint32_t live[4];
+                        float total[4];
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            live[q] = __ballot_sync(0xffffffffu, al[q] > 0.0f);
+#ifdef GHR_TRACE
+                            trace_live += ((live[q] & 0xFFFFu) != 0) + ((live[q] >> 16) != 0);
+#endif
+                            const float Tm = slot ? Town[2 * q + 1] : Town[2 * q], Bm = slot ? Bown[2 * q + 1] : Bown[2 * q];
+                            const float sm = slot ? sown[2 * q + 1] : sown[2 * q], rm = slot ? rown[2 * q + 1] : rown[2 * q];
+                            const float aq = al[q];
+                            const float dchannel_dcolor = aq * Tm;
+                            float dL_dopa = fmaf(sm, Tm, -rm * Bm);
+                            dL_dopa = aq > 0.0f ? dL_dopa : 0.0f;
+                            const float dL_dG = con[q].w * dL_dopa;
+                            const float gdx = G[q] * dx[q], gdy = G[q] * dy[q];
+                            const float dG_ddelx = -gdx * con[q].x - gdy * con[q].y;
+                            const float dG_ddely = -gdy * con[q].z - gdx * con[q].y;
+                            float v[9];
+                            v[0] = dchannel_dcolor * dpix0;
+                            v[1] = dchannel_dcolor * dpix1;
+                            v[2] = dchannel_dcolor * dpix2;
+                            v[3] = dL_dG * dG_ddelx * ddelx_dx;
+                            v[4] = dL_dG * dG_ddely * ddely_dy;
+                            v[5] = -0.5f * gdx * dx[q] * dL_dG;
+                            v[6] = -0.5f * gdx * dy[q] * dL_dG;
+                            v[7] = -0.5f * gdy * dy[q] * dL_dG;
+                            v[8] = G[q] * dL_dopa;
+                            total[q] = half_reduce9(v, lane);
+                        }
+#pragma unroll
+                        for (int q = 0; q < 4; q++)
+                            if ((live[q] & half_mask) != 0 && writer)
+                                atomicAdd(accum + 12 * (size_t)s_id[buf][jm[q]] + vslot, total[q]);
+                        BTRACE_LAP(c_p23)
+                    } else {
+                    // (multi-attribute kernels) phases 2 and 3, one pair of Gaussians (one per slot) at a time
 #pragma unroll
                     for (int q = 0; q < 4; q++) {
                         // state after the pair's first Gaussian (S1: what slot 0 differentiates) and after its second (S2)
@@ -478,6 +537,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32) blend_backward_kernel(
                             atomicAdd(accum + 12 * (size_t)s_id[buf][jm[q]] + vslot, total);
                     }
                     BTRACE_LAP(c_p23)
+                    }  // NX > 0
                 }
             }
             __syncwarp();  // buffer `buf` is re-filled by the next iteration's stage()
