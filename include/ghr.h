@@ -107,7 +107,9 @@ typedef struct ghr_geom_header {
     uint32_t scan_ticket;   /* work counter of the fused preprocess+scan kernel   */
     uint32_t blend_fwd_ticket; /* work-queue heads of the two blend kernels        */
     uint32_t blend_bwd_ticket;
-    uint32_t reserved[59];
+    uint32_t depth_hi;      /* max over the visible Gaussians of the depth's fp32 bit pattern (0 if none)          */
+    uint32_t depth_lo_inv;  /* ~min of the same: the sort squeezes the constant high bits of (depth - min) out    */
+    uint32_t reserved[57];
 } ghr_geom_header;
 
 int ghr_version(void);
@@ -418,6 +420,26 @@ size_t ghr_views_workspace_bytes(int32_t P, int32_t n_views, int32_t W, int32_t 
 int ghr_forward_views(const ghr_raster_params* prm, int32_t n_views, const float* cameras, const int32_t* labels,
                       const int32_t* skip_labels, void* workspace, size_t workspace_bytes, int64_t capacity,
                       float* out_color, float* out_depth, float* out_alpha, int32_t* radii, void* stream);
+
+/*
+ * Cube-map -> direction lookup of the occlusion baking (reference baking.py:286-309).
+ *
+ * ghr_cubemap_sample_nearest: what bake_set asks of nvdiffrast (un-vendored third party),
+ *   dr.texture(tex[1,6,res,res,C], uv = dirs[1,H,W,3], filter_mode="nearest", boundary_mode="cube") (:290-297),
+ * for n_maps cube maps at once: out[m][d][c] = tex[m][face(d)][v(d)][u(d)][c].  Cube addressing is the OpenGL one
+ * (major axis -> face +x,-x,+y,-y,+z,-z; in-face coordinates per the OpenGL 4.6 specification, table 8.19), nearest
+ * texel = floor(coordinate * res) clamped to [0, res-1]; a direction without a major axis (NaN, zero) reads 0.
+ * tex [n_maps,6,res,res,channels], dirs [n_dirs,3] (need not be normalised), out [n_maps,n_dirs,channels].
+ *
+ * ghr_bake_occlusion: the rest of bake_set fused with that lookup (:231,305-307) for single-channel alpha cube maps:
+ *   occlusion[p][d] = dot(dirs[d], normals[p]) > 0 ? 1 - cubemaps[cell_of[p]][texel(d)] : 0
+ * cubemaps [n_cells,6,res,res] (the opacity maps ghr_forward_views renders per grid cell), cell_of [P] int64
+ * (pc_grid_indices of pc_to_grid, :104-134), normals [P,3], dirs [n_dirs,3], out [P,n_dirs]  (n_dirs <= 8192).
+ */
+int ghr_cubemap_sample_nearest(int32_t n_maps, int32_t res, int32_t channels, const float* tex, int32_t n_dirs,
+                               const float* dirs, float* out, void* stream);
+int ghr_bake_occlusion(int32_t P, int32_t n_dirs, int32_t n_cells, int32_t res, const float* cubemaps,
+                       const int64_t* cell_of, const float* normals, const float* dirs, float* out, void* stream);
 
 /*
  * Optimiser side of the training iteration (no native counterpart in the reference, which runs

@@ -7,9 +7,11 @@ the alpha map (:283).  ``rasterize_views`` renders any number of views of the sa
 ``ghr_forward_views`` (six kernel launches per batch of views; the per-cell mask is a label compare inside the
 projection kernel), and ``bake_opacity_cubemaps`` is the bake_set loop on top of it.
 
-Not here: the cube-map -> lat-long resampling (``dr.texture(..., boundary_mode="cube")``, baking.py:286-295) is
-nvdiffrast (un-vendored third-party, graphics-stack sampling conventions) and stays with the caller; the
-faces are returned in the order and orientation the reference stacks them in (:284), ready for that call.
+The cube-map -> lat-long resampling (``dr.texture(..., filter_mode="nearest", boundary_mode="cube")``, baking.py
+:286-297) is a plain gather (direction -> face + texel); ``cubemap_sample_nearest`` is that call for any number of cube
+maps, ``texture`` has nvdiffrast's call signature (so the reference's unmodified bake_set runs on it), and
+``bake_occlusion`` is all of bake_set: cube faces, lookup, per-Gaussian ``1 - alpha`` and the normal-hemisphere mask
+(:231,305-307) in three kernels (``ghr_forward_views`` batch, ``ghr_bake_occlusion``).
 
 No CPU fallback: CUDA tensors only.
 """
@@ -190,3 +192,63 @@ def bake_opacity_cubemaps(means3D, opacity, scales, rotations, points=None, grid
                           tanfovx=1.0, tanfovy=1.0, scale_modifier=scale_modifier, labels=cell_of.to(torch.int32),
                           skip_labels=skip)
     return out["alpha"].view(C, 6, res, res, 1), centers, cell_of
+
+
+def envmap_dirs(res=(16, 32), device="cuda"):
+    """baking.py:35-58 get_envmap_dirs: (solid_angles [H,W,1], directions [H,W,3]) of the lat-long grid."""
+    H, W = res
+    gy, gx = torch.meshgrid(torch.linspace(0.0, 1.0, H, device=device), torch.linspace(-1.0, 1.0, W, device=device),
+                            indexing="ij")
+    d_theta, d_phi = math.pi / H, 2 * math.pi / W
+    sintheta, costheta = torch.sin(gy * math.pi), torch.cos(gy * math.pi)
+    sinphi, cosphi = torch.sin(gx * math.pi), torch.cos(gx * math.pi)
+    reflvec = torch.stack((sintheta * sinphi, costheta, -sintheta * cosphi), dim=-1)
+    solid_angles = ((costheta - torch.cos(gy * math.pi + d_theta)) * d_phi)[..., None]
+    return solid_angles, reflvec
+
+
+def cubemap_sample_nearest(tex, dirs):
+    """tex [n,6,res,res,C], dirs [...,3] -> [n, ..., C]: nearest-texel cube-map lookup (OpenGL / nvdiffrast face
+    convention, ghr_cubemap_sample_nearest)."""
+    if not tex.is_cuda:
+        raise RuntimeError("libghr: tensor arguments must live on a CUDA device (there is no CPU fallback)")
+    if tex.dim() != 5 or tex.shape[1] != 6 or tex.shape[2] != tex.shape[3] or dirs.shape[-1] != 3:
+        raise ValueError("tex must be [n,6,res,res,C] and dirs [...,3]")
+    tex = tex.float().contiguous()
+    d = dirs.to(tex.device).float().reshape(-1, 3).contiguous()
+    n, res, C = tex.shape[0], tex.shape[2], tex.shape[4]
+    out = torch.empty(n, d.shape[0], C, device=tex.device)
+    with _lib.on_device(tex.device):
+        _lib.check(_lib.lib().ghr_cubemap_sample_nearest(n, res, C, tex.data_ptr(), d.shape[0], d.data_ptr(), out.data_ptr(),
+                                                         _stream(tex.device)), "ghr_cubemap_sample_nearest")
+    return out.view(n, *dirs.shape[:-1], C)
+
+
+def texture(tex, uv, filter_mode="nearest", boundary_mode="cube"):
+    """nvdiffrast.torch.texture for the one configuration bake_set uses (baking.py:290-297): tex [n,6,res,res,C],
+    uv = directions [n,H,W,3], nearest filter, cube boundary -> [n,H,W,C].  Anything else raises."""
+    if filter_mode != "nearest" or boundary_mode != "cube":
+        raise NotImplementedError("only filter_mode='nearest', boundary_mode='cube' (what bake_set uses)")
+    if uv.shape[0] != tex.shape[0]:
+        raise ValueError("one direction grid per cube map")
+    return torch.cat([cubemap_sample_nearest(tex[i:i + 1], uv[i]) for i in range(tex.shape[0])])
+
+
+def bake_occlusion(means3D, normal, opacity, scales, rotations, H=16, W=32, grid_res=10, res=32, scale_modifier=1.0):
+    """bake_set (baking.py:136-309) end to end: occlusion [P,H,W,1] = (envmap_dirs . normal > 0) * (1 - alpha of the
+    Gaussian's grid cell seen from the cell centre in direction envmap_dirs).  means3D [P,3] world positions, normal
+    [P,3], opacity [P,1], scales [P,3] (activated), rotations [P,4]."""
+    cubes, centers, cell_of = bake_opacity_cubemaps(means3D, opacity, scales, rotations, grid_res=grid_res, res=res,
+                                                    scale_modifier=scale_modifier)
+    _, dirs = envmap_dirs((H, W), means3D.device)
+    d = dirs.reshape(-1, 3).contiguous()
+    P, C = means3D.shape[0], cubes.shape[0]
+    nrm = normal.float().contiguous()
+    cell = cell_of.to(torch.int64).contiguous()
+    cubes = cubes.reshape(C, 6, res, res).contiguous()
+    out = torch.empty(P, H * W, device=means3D.device)
+    with _lib.on_device(means3D.device):
+        _lib.check(_lib.lib().ghr_bake_occlusion(P, H * W, C, res, cubes.data_ptr(), cell.data_ptr(), nrm.data_ptr(),
+                                                 d.data_ptr(), out.data_ptr(), _stream(means3D.device)),
+                   "ghr_bake_occlusion")
+    return out.view(P, H, W, 1)

@@ -80,7 +80,11 @@ inline bool blend_throughput_regime(int64_t capacity)
         return !e ? 0 : (e[0] == 't' ? 2 : 1);
     }();
     if (forced) return forced == 2;
-    return capacity > (int64_t(1) << 19);
+    // Measured on B200 after the compacted-staging rewrite of the 4x4-block kernels (tools/blend_probe.py, forward +
+    // backward incl. the per-entry block masks of tile_ranges_kernel): 2.2 M pairs (300 k Gaussians, 1024^2) 522 us vs
+    // 560 us for the wide family; 12.3 M pairs (3 M Gaussians, 1080p, forward only) 1 305 us vs 593 us -- the masks cost
+    // 16 ellipse tests per list entry, which the wide family does not pay.
+    return capacity > (int64_t(1) << 22);
 }
 
 // Several views share the GPU (views of a batch on several streams): the blend kernels then take half the staging
@@ -119,7 +123,8 @@ cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binni
                              const ghr_layout& L, int64_t capacity, cudaStream_t s);
 // Sort N (device word) pairs held in A; header/status must be zeroed beforehand.
 cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev, int64_t capacity, int bits,
-                        uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, cudaStream_t s);
+                        uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, cudaStream_t s,
+                        const uint32_t* squeeze = nullptr /* device {depth_hi, ~depth_lo} of a depth|tile frame, or NULL */);
 cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, char* binning, char* img,
                                const ghr_layout& L, int64_t capacity, cudaStream_t s);
 cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, const char* binning, char* img,

@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(GHR_BLOCK) preprocess_kernel(const PreArgs a)
     const float* Pm = s_cam + 16;
 
     uint32_t tiles = 0;
+    uint32_t dbits_hi = 0u, dbits_lo_inv = 0u;  // depth bit pattern of a visible Gaussian (hi) and its complement (lo)
     if (idx < a.P) {
         int radius;
         bool near_culled;
@@ -38,6 +39,18 @@ __global__ void __launch_bounds__(GHR_BLOCK) preprocess_kernel(const PreArgs a)
         if (near_culled && a.prefiltered) atomicMax(&a.hdr->error, (uint32_t)(-GHR_ERR_PREFILTER));
         a.radii[idx] = radius;
         a.tiles_touched[idx] = tiles;
+        if (tiles) {
+            dbits_hi = __float_as_uint(a.rec[3 * (size_t)idx].z);  // the depth just written (same thread)
+            dbits_lo_inv = ~dbits_hi;
+        }
+    }
+    // depth range of the visible Gaussians, for the sort (ghr_sort.cu: squeezed digits): depth > 0.2, so the bit
+    // patterns order like the values
+    dbits_hi = __reduce_max_sync(0xffffffffu, dbits_hi);
+    dbits_lo_inv = __reduce_max_sync(0xffffffffu, dbits_lo_inv);
+    if ((tid & 31) == 0 && dbits_hi) {
+        atomicMax(&a.hdr->depth_hi, dbits_hi);
+        atomicMax(&a.hdr->depth_lo_inv, dbits_lo_inv);
     }
 
     // block-wide inclusive scan of `tiles`

@@ -14,7 +14,7 @@
 //                      the device (no host sync)
 //   pass kernel (xK) : one sweep per non-trivial pass: per-warp ranking with
 //                      match-any, per-digit chained scan over tiles
-//                      (decoupled look-back, 4 predecessors per round trip),
+//                      (decoupled look-back, 16 predecessors per round trip),
 //                      then the tile is put in digit order in shared memory
 //                      and written out so that consecutive threads write
 //                      consecutive addresses of a digit's run.
@@ -22,6 +22,7 @@
 // Roofline: HBM stream, algorithmic bytes N*(8 + 24*passes).
 // The pair count N is read from device memory (no D2H sync) when n_dev is
 // given; the grid is sized for `capacity` and surplus tiles exit.
+#include <type_traits>
 #include "ghr_common.cuh"
 #include "ghr_internal.h"
 
@@ -36,6 +37,32 @@ static_assert(kSortThreads == kRadix, "one thread per digit in the scans");
 __device__ __forceinline__ int64_t sort_count(const uint32_t* n_dev, int64_t capacity)
 {
     return n_dev ? min((int64_t)*n_dev, capacity) : capacity;
+}
+
+// Squeezed keys.  A depth|tile key is (tile << 32) | bits(depth) and the depths of one frame span a narrow range (a
+// body 2.4 .. 3.6 m from the camera: sign, exponent and nothing else are constant), so the key's low word minus the
+// frame's smallest depth needs only L = bit-length(max - min) bits, and the digits are taken from
+//     sq(key) = (low32(key) - lo)  |  (high32(key) << L)        (L + tile bits instead of 32 + tile bits)
+// Order is preserved (lo <= every depth), the passes still move the ORIGINAL keys, and the passes left without any
+// varying bit become "all keys share this digit" -- the trivial passes the plan already skips.  A 512^2 .. 1080p body
+// frame goes from 5 radix passes to 4.  `sq` = {depth_hi, ~depth_lo} written by the preprocess kernel, or NULL
+// (generic sort: identity).
+struct Squeeze {
+    uint32_t lo, L;
+};
+__device__ __forceinline__ Squeeze load_squeeze(const uint32_t* sq)
+{
+    Squeeze q;
+    q.lo = 0u; q.L = 32u;
+    if (sq) {
+        const uint32_t hi = sq[0], lo = ~sq[1];
+        if (hi >= lo) { q.lo = lo; q.L = 32u - (uint32_t)__clz(hi - lo); }  // hi < lo: no visible Gaussian, no key
+    }
+    return q;
+}
+__device__ __forceinline__ uint64_t squeezed(uint64_t key, Squeeze q)
+{
+    return (uint64_t)((uint32_t)key - q.lo) | ((key >> 32) << q.L);
 }
 
 // Exclusive scan of one value per thread over the 512-thread block.  s_warp: 17 words; two barriers inside.
@@ -68,13 +95,14 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp
 __global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint64_t* __restrict__ keys,
                                                                       const uint32_t* __restrict__ n_dev,
                                                                       int64_t capacity, int bits, int passes,
-                                                                      SortHeader* hdr)
+                                                                      SortHeader* hdr, const uint32_t* __restrict__ sq)
 {
     __shared__ uint32_t s_hist[kMaxPasses * kRadix];
     __shared__ uint32_t s_warp[2][kSortWarps + 1];
     __shared__ uint32_t s_trivial[kMaxPasses];
     __shared__ uint32_t s_last;
     const int64_t N = sort_count(n_dev, capacity);
+    const Squeeze squeeze = load_squeeze(sq);
     const int t = threadIdx.x;
     for (int i = t; i < passes * kRadix; i += kSortThreads) s_hist[i] = 0;
     __syncthreads();
@@ -89,8 +117,9 @@ __global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             if (i0 + u * stride >= N) break;
+            const uint64_t ks = squeezed(k[u], squeeze);
             for (int p = 0; p < passes; p++) {
-                uint32_t d = (uint32_t)(k[u] >> (p * kRadixBits)) & (uint32_t)(kRadix - 1);
+                uint32_t d = (uint32_t)(ks >> (p * kRadixBits)) & (uint32_t)(kRadix - 1);
                 if (p == passes - 1) d &= lastmask;
                 atomicAdd(&s_hist[p * kRadix + d], 1u);
             }
@@ -133,7 +162,8 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
                                                                         const uint32_t* __restrict__ n_dev,
                                                                         int64_t capacity, int pass, uint32_t digit_mask,
                                                                         SortHeader* hdr,
-                                                                        uint32_t* status /*[tiles][kRadix]*/)
+                                                                        uint32_t* status /*[tiles][kRadix]*/,
+                                                                        const uint32_t* __restrict__ sq)
 {
     constexpr int TILE = kSortThreads * ITEMS;
     // hist: per-warp digit counts, then (after the scans) the tile-local position of each warp's first key of each
@@ -166,6 +196,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
     const int valid = (int)min((int64_t)TILE, N - tile_start);
 
     const int shift = pass * kRadixBits;
+    const Squeeze squeeze = load_squeeze(sq);
     uint64_t key[ITEMS];
     uint32_t val[ITEMS];
     uint32_t pos[ITEMS];  // first: digit << 16 | rank among the warp's keys of that digit; then: tile-local position
@@ -180,7 +211,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const bool ok = (wbase + i * 32) < valid;
-        const uint32_t d = ok ? ((uint32_t)(key[i] >> shift) & digit_mask) : (uint32_t)kRadix;
+        const uint32_t d = ok ? ((uint32_t)(squeezed(key[i], squeeze) >> shift) & digit_mask) : (uint32_t)kRadix;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
@@ -221,20 +252,25 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
     for (int i = 0; i < ITEMS; i++)
         if (pos[i] != 0xFFFFFFFFu) sm.keys[pos[i]] = key[i];
 
-    // decoupled look-back over the predecessors' counts of digit t, four tiles per round trip
+    // decoupled look-back over the predecessors' counts of digit t, sixteen tiles per round trip
     {
         uint32_t excl = 0;
         if (tile != 0) {
             int j = (int)tile - 1;
             bool done = false;
-            while (!done) {
-                uint32_t s[4];
+            // Predecessors per round trip: 4 on the first (at large N the nearest predecessor has usually published its
+            // inclusive prefix already, and every extra word is L2 traffic: 16 words x 512 digits per tile would be
+            // two thirds of the tile's own payload), then 16 -- at small N every tile of a pass is resident at once and
+            // publishes its aggregate at about the same time, so the last tile walks back over ALL of them.
+            auto walk = [&](auto look) {
+                constexpr int kLook = decltype(look)::value;
+                uint32_t s[kLook];
 #pragma unroll
-                for (int u = 0; u < 4; u++)
+                for (int u = 0; u < kLook; u++)
                     s[u] = (j - u) >= 0 ? ld_relaxed_u32(status + (size_t)(j - u) * kRadix + tid) : kStIncl;
                 bool stall = false;
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
+                for (int u = 0; u < kLook; u++) {
                     const uint32_t f = s[u] & ~kStMask;
                     if (!done && !stall) {
                         if (f == 0) stall = true;
@@ -244,7 +280,9 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
                         }
                     }
                 }
-            }
+            };
+            walk(std::integral_constant<int, 4>{});
+            while (!done) walk(std::integral_constant<int, 16>{});
             st_relaxed_u32(my, kStIncl | (excl + sum));
         }
         s_base[tid] = hdr->bin_base[pass][tid] + excl - tile_excl;
@@ -257,7 +295,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
         const int idx = k * kSortThreads + tid;
         if (idx < valid) {
             const uint64_t kk = sm.keys[idx];
-            dst[k] = s_base[(uint32_t)(kk >> shift) & digit_mask] + idx;
+            dst[k] = s_base[(uint32_t)(squeezed(kk, squeeze) >> shift) & digit_mask] + idx;
             kout[dst[k]] = kk;
         }
     }
@@ -276,14 +314,15 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 template <int ITEMS>
 static void launch_pass(int64_t tiles, uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
                         const uint32_t* n_dev, int64_t capacity, int p, uint32_t mask, SortHeader* hdr, uint32_t* st,
-                        cudaStream_t s)
+                        const uint32_t* sq, cudaStream_t s)
 {
     onesweep_pass_kernel<ITEMS><<<(unsigned)tiles, kSortThreads, 0, s>>>(keys_a, keys_b, vals_a, vals_b, n_dev, capacity,
-                                                                         p, mask, hdr, st);
+                                                                         p, mask, hdr, st, sq);
 }
 
 cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev, int64_t capacity, int bits,
-                        uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, cudaStream_t s)
+                        uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, cudaStream_t s,
+                        const uint32_t* squeeze)
 {
     if (capacity <= 0) return cudaSuccess;
     StageTimer timer(GHR_STAGE_SORT, s);
@@ -292,16 +331,16 @@ cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev
     const int64_t tiles = sort_tiles(capacity);
     int64_t hg = (capacity + kSortThreads * 4 - 1) / (kSortThreads * 4);
     const int hgrid = (int)(hg < sm_count() * 4 ? hg : sm_count() * 4);
-    sort_histogram_kernel<<<hgrid, kSortThreads, 0, s>>>(keys_a, n_dev, capacity, bits, passes, hdr);
+    sort_histogram_kernel<<<hgrid, kSortThreads, 0, s>>>(keys_a, n_dev, capacity, bits, passes, hdr, squeeze);
     count_launch(1 + passes);
     for (int p = 0; p < passes; p++) {
         const int rem = bits - p * kRadixBits;
         const uint32_t mask = rem >= kRadixBits ? (uint32_t)(kRadix - 1) : ((1u << rem) - 1u);
         uint32_t* st = status + (size_t)p * tiles * kRadix;
         switch (items) {
-            case 2: launch_pass<2>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, s); break;
-            case 4: launch_pass<4>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, s); break;
-            default: launch_pass<8>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, s); break;
+            case 2: launch_pass<2>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, s); break;
+            case 4: launch_pass<4>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, s); break;
+            default: launch_pass<8>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, s); break;
         }
     }
     return cudaGetLastError();

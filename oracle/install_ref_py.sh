@@ -24,3 +24,7 @@ cp "$REF/transform.py" "$REF/baking.py" "$OUT/"
 # package markers (ours, empty): scene/__init__.py of the reference pulls in the dataset readers and is NOT copied
 for d in scene utils nets smpl smplx; do : > "$OUT/$d/__init__.py"; done
 echo "installed reference python modules into $OUT"
+# the reference's own Python front-end of its rasteriser (autograd function, settings tuple, module); its compiled _C
+# half is provided on the GPU box by oracle/ref_dgr.py on top of oracle/_ref (the unmodified CUDA sources)
+mkdir -p "$OUT/ref_dgr/diff_gaussian_rasterization"
+cp "$REF/submodules/diff-gaussian-rasterization/diff_gaussian_rasterization/__init__.py" "$OUT/ref_dgr/diff_gaussian_rasterization/"

@@ -120,8 +120,9 @@ def load_renderer():
     ns = load()
     if "diff_gaussian_rasterization" not in sys.modules:
         raise ImportError("install a diff_gaussian_rasterization implementation in sys.modules first")
-    ns.baking = importlib.import_module("baking")
+    # gaussian_renderer first: baking imports GaussianModel back from it (the reference's own import order, train.py)
     ns.gaussian_renderer = importlib.import_module("gaussian_renderer")
+    ns.baking = importlib.import_module("baking")
     return ns.gaussian_renderer, ns.baking
 
 
