@@ -50,13 +50,19 @@ __device__ __forceinline__ int64_t sort_count(const uint32_t* n_dev, int64_t cap
 struct Squeeze {
     uint32_t lo, L;
 };
-__device__ __forceinline__ Squeeze load_squeeze(const uint32_t* sq)
+__device__ __forceinline__ Squeeze load_squeeze(const uint32_t* sq, int bits)
 {
     Squeeze q;
     q.lo = 0u; q.L = 32u;
     if (sq) {
         const uint32_t hi = sq[0], lo = ~sq[1];
-        if (hi >= lo) { q.lo = lo; q.L = 32u - (uint32_t)__clz(hi - lo); }  // hi < lo: no visible Gaussian, no key
+        if (hi >= lo) {  // hi < lo: no visible Gaussian, no key
+            const uint32_t L = 32u - (uint32_t)__clz(hi - lo);
+            // only when it saves a pass: otherwise the plain digits are the better balanced ones (3 M Gaussians over
+            // 1 .. 11 m: 38 squeezed bits still take 5 passes, the last over 2 bits -- measured 9 % slower)
+            const int squeezed_bits = bits - 32 + (int)L;
+            if ((squeezed_bits + kRadixBits - 1) / kRadixBits < (bits + kRadixBits - 1) / kRadixBits) { q.lo = lo; q.L = L; }
+        }
     }
     return q;
 }
@@ -102,7 +108,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint
     __shared__ uint32_t s_trivial[kMaxPasses];
     __shared__ uint32_t s_last;
     const int64_t N = sort_count(n_dev, capacity);
-    const Squeeze squeeze = load_squeeze(sq);
+    const Squeeze squeeze = load_squeeze(sq, bits);
     const int t = threadIdx.x;
     for (int i = t; i < passes * kRadix; i += kSortThreads) s_hist[i] = 0;
     __syncthreads();
@@ -163,7 +169,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
                                                                         int64_t capacity, int pass, uint32_t digit_mask,
                                                                         SortHeader* hdr,
                                                                         uint32_t* status /*[tiles][kRadix]*/,
-                                                                        const uint32_t* __restrict__ sq)
+                                                                        const uint32_t* __restrict__ sq, int bits)
 {
     constexpr int TILE = kSortThreads * ITEMS;
     // hist: per-warp digit counts, then (after the scans) the tile-local position of each warp's first key of each
@@ -196,7 +202,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
     const int valid = (int)min((int64_t)TILE, N - tile_start);
 
     const int shift = pass * kRadixBits;
-    const Squeeze squeeze = load_squeeze(sq);
+    const Squeeze squeeze = load_squeeze(sq, bits);
     uint64_t key[ITEMS];
     uint32_t val[ITEMS];
     uint32_t pos[ITEMS];  // first: digit << 16 | rank among the warp's keys of that digit; then: tile-local position
@@ -314,10 +320,10 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 template <int ITEMS>
 static void launch_pass(int64_t tiles, uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
                         const uint32_t* n_dev, int64_t capacity, int p, uint32_t mask, SortHeader* hdr, uint32_t* st,
-                        const uint32_t* sq, cudaStream_t s)
+                        const uint32_t* sq, int bits, cudaStream_t s)
 {
     onesweep_pass_kernel<ITEMS><<<(unsigned)tiles, kSortThreads, 0, s>>>(keys_a, keys_b, vals_a, vals_b, n_dev, capacity,
-                                                                         p, mask, hdr, st, sq);
+                                                                         p, mask, hdr, st, sq, bits);
 }
 
 cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev, int64_t capacity, int bits,
@@ -338,9 +344,9 @@ cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev
         const uint32_t mask = rem >= kRadixBits ? (uint32_t)(kRadix - 1) : ((1u << rem) - 1u);
         uint32_t* st = status + (size_t)p * tiles * kRadix;
         switch (items) {
-            case 2: launch_pass<2>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, s); break;
-            case 4: launch_pass<4>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, s); break;
-            default: launch_pass<8>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, s); break;
+            case 2: launch_pass<2>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, bits, s); break;
+            case 4: launch_pass<4>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, bits, s); break;
+            default: launch_pass<8>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, bits, s); break;
         }
     }
     return cudaGetLastError();

@@ -158,4 +158,8 @@ def make_model(smpl, leaves, device, sh_degree=3, motion_offset=False):
     m._albedo = leaves.get("albedo", torch.zeros_like(leaves["xyz"]))
     m._roughness = leaves.get("roughness", torch.zeros_like(leaves["opacity_logit"]))
     m.optimizer = None
+    if motion_offset:  # __init__ :94-103: the pose-correction and LBS-weight-offset networks, default initialisation
+        torch.manual_seed(0)
+        m.pose_decoder = ns.nets_pose.BodyPoseRefiner(total_bones=24, embedding_size=69, mlp_width=128, mlp_depth=2).to(device)
+        m.lweight_offset_decoder = ns.nets_lbs.LBSOffsetDecoder(total_bones=24).to(device)
     return m

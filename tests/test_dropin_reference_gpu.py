@@ -70,7 +70,12 @@ def _run_render(install, leaves_src, smpl, cam, weights):
     install()
     gr, _ = ref_py.load_renderer()
     leaves = {k: v.detach().clone().requires_grad_(True) for k, v in leaves_src.items()}
-    pc = ref_py.make_model({k: v for k, v in smpl.items()}, leaves, "cuda")
+    # motion_offset_flag=True is the only configuration render() survives (its other branch never binds correct_Rs,
+    # gaussian_renderer/__init__.py:93-96,286): pose-correction and LBS-weight networks are the reference's own modules
+    pc = ref_py.make_model({k: v for k, v in smpl.items()}, leaves, "cuda", motion_offset=True)
+    for net in (pc.pose_decoder, pc.lweight_offset_decoder):
+        for q in net.parameters():
+            q.requires_grad_(False)
     pipe = types.SimpleNamespace(debug=False, compute_cov3D_python=True, convert_SHs_python=True)
     out = gr.render(1, cam, pc, pipe, torch.zeros(3, device="cuda"))
     names = ("render", "render_depth", "render_alpha", "normal", "albedo", "occlusion", "roughness", "world_normal",

@@ -9,8 +9,8 @@ libghr through the drop-in _C / C ABI against the UNMODIFIED reference CUDA buil
   adversarial: projected centres and extents exactly on / one ulp around tile (16 px) and block (4 px) boundaries
   fused LBS + covariance + SH at P = 50 000 against the fp64 oracle
 
-Cases with more than 2^19 (Gaussian, tile) pairs select the wide blend kernel family (ghr_blend_*_wide.cu)
-NATURALLY -- the test asserts that it did.
+Cases with more than 2^22 (Gaussian, tile) pairs select the wide blend kernel family (ghr_blend_*_wide.cu)
+NATURALLY -- the test asserts that it did; the 300 k / 1024^2 case (2.2 M pairs) runs the 4x4-block family at scale.
 
 Bars (north_star): radii / tiles_touched / point_offsets / num_rendered / sorted keys + ids / tile ranges /
 n_contrib bit-exact; colour / depth / alpha <= 1e-5 abs; gradients <= 1e-4 rel (per element, see _grad_close).
@@ -28,7 +28,7 @@ from tests.test_raster_parity_gpu import ABS_IMG, _grad_close, _np, _ref_forward
 
 pytestmark = pytest.mark.gpu
 
-WIDE_PAIRS = 1 << 19  # blend_throughput_regime (ghr_internal.h)
+WIDE_PAIRS = 1 << 22  # blend_throughput_regime (ghr_internal.h): more pairs than this select the wide family
 
 
 def _need_ref():
@@ -132,11 +132,11 @@ def test_stress_3m_1080p_forward_integer_state_exact():
     assert visible >= 1_000_000
 
 
-def test_1080p_300k_backward_selects_the_wide_family_naturally():
+def test_1080p_600k_backward_selects_the_wide_family_naturally():
     """1920x1080 (H not a multiple of 16: the last tile row is partial, reference backward.cu:435,460-464) with enough
     pairs for the wide blend kernels, forward + backward."""
     _need_ref()
-    case = _scene_case(300_000, 1920, 1080, "color_scale_rot", seed=3, scale=0.05)
+    case = _scene_case(600_000, 1920, 1080, "color_scale_rot", seed=3, scale=0.07)
     tc = Cm.to_torch(case, "cuda")
     fw = Cm.ours_forward(tc)
     assert fw[0] > WIDE_PAIRS, fw[0]
