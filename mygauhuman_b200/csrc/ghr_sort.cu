@@ -14,7 +14,7 @@
 //                      the device (no host sync)
 //   pass kernel (xK) : one sweep per non-trivial pass: per-warp ranking with
 //                      match-any, per-digit chained scan over tiles
-//                      (decoupled look-back, 16 predecessors per round trip),
+//                      (decoupled look-back, 4 predecessors per round trip),
 //                      then the tile is put in digit order in shared memory
 //                      and written out so that consecutive threads write
 //                      consecutive addresses of a digit's run.
@@ -258,16 +258,15 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
     for (int i = 0; i < ITEMS; i++)
         if (pos[i] != 0xFFFFFFFFu) sm.keys[pos[i]] = key[i];
 
-    // decoupled look-back over the predecessors' counts of digit t, sixteen tiles per round trip
+    // decoupled look-back over the predecessors' counts of digit t, four tiles per round trip
     {
         uint32_t excl = 0;
         if (tile != 0) {
             int j = (int)tile - 1;
             bool done = false;
-            // Predecessors per round trip: 4 on the first (at large N the nearest predecessor has usually published its
-            // inclusive prefix already, and every extra word is L2 traffic: 16 words x 512 digits per tile would be
-            // two thirds of the tile's own payload), then 16 -- at small N every tile of a pass is resident at once and
-            // publishes its aggregate at about the same time, so the last tile walks back over ALL of them.
+            // Four predecessors per round trip.  (Measured: 16 per trip -- fewer dependent L2 round trips for the last tile
+            // of a small sort, where all tiles of a pass publish their aggregates at once -- is SLOWER at both ends:
+            // 64 vs 58 us at 1.8e5 keys, 764 vs 690 us at 1.2e7 keys; the extra words cost more than the trips save.)
             auto walk = [&](auto look) {
                 constexpr int kLook = decltype(look)::value;
                 uint32_t s[kLook];
@@ -287,8 +286,11 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
                     }
                 }
             };
+#ifndef GHR_SORT_LOOK
+#define GHR_SORT_LOOK 4
+#endif
             walk(std::integral_constant<int, 4>{});
-            while (!done) walk(std::integral_constant<int, 16>{});
+            while (!done) walk(std::integral_constant<int, GHR_SORT_LOOK>{});
             st_relaxed_u32(my, kStIncl | (excl + sum));
         }
         s_base[tid] = hdr->bin_base[pass][tid] + excl - tile_excl;
