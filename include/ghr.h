@@ -243,6 +243,24 @@ int ghr_sort_pairs_u64(int64_t N, int32_t bits, uint64_t* keys_a, uint64_t* keys
                        void* stream);
 
 /*
+ * ghr_sort_pairs_u64 for callers that cannot allocate (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  NO
+ * COUNTERPART IN THE REFERENCE.
+ * Same kernels, arguments and result as ghr_sort_pairs_u64 minus the
+ * workspace: the histogram / look-back scratch is a file-scope static
+ * __device__ array inside libghr.so (ghr_noalloc.cu, ~4.2 MB, held by every
+ * GPU that loads the library until exit).  Limit: N <=
+ * GHR_STATIC_SORT_MAX_KEYS, beyond it GHR_ERR_CAPACITY and a message on
+ * stderr.  Calls no cudaMalloc / cudaFree / allocating routine.  All calls
+ * share the one array (cleared on `stream` at the start of each call): calls
+ * that overlap on the GPU race -- serialise them.
+ */
+#define GHR_STATIC_SORT_MAX_KEYS (1 << 20)
+int64_t ghr_sort_static_max_keys(void);
+int ghr_sort_pairs_u64_static(int64_t N, int32_t bits, uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a,
+                              uint32_t* vals_b, uint32_t* sorted_sel_dev, void* stream);
+
+/*
  * distCUDA2 (submodules/simple-knn/spatial.cu:15-26 -> SimpleKNN::knn,
  * simple_knn.cu:185-221): out[i] = mean of the 3 smallest squared distances
  * from point i to the other points.

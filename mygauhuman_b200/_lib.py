@@ -107,6 +107,8 @@ SIGNATURES = {
     "ghr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ghr_sort_workspace_bytes": (C.c_size_t, [C.c_int64]),
     "ghr_sort_pairs_u64": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_size_t, C.c_void_p, C.c_void_p]),
+    "ghr_sort_static_max_keys": (C.c_int64, []),
+    "ghr_sort_pairs_u64_static": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 6),
     "ghr_knn_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "ghr_dist2_knn3": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "ghr_lbs_prepare": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 6),
