@@ -383,6 +383,40 @@ int ghr_lbs_deform_backward(const ghr_deform_params* prm, const uint8_t* clamped
                             float* dL_dlbs_offsets /*[P,24]*/, float* dL_dscales, float* dL_drotations,
                             float* dL_dshs, float* dL_dA_target, float* dL_dvertex_offsets, void* stream);
 
+/*
+ * The per-Gaussian chain of a view as one kernel each way ("fused LBS + projection + SH"): what render() does between
+ * reading the canonical Gaussians and calling the rasteriser (gaussian_renderer/__init__.py:94-195:
+ * coarse_deform_c2source, get_covariance, eval_sh + clamp, get_opacity) fused with the rasteriser's own per-Gaussian
+ * stage (forward.cu:156-256 preprocessCUDA; backward.cu:144-396).  The deformed mean, world covariance, colour and
+ * opacity stay in registers; results are those of ghr_lbs_deform_forward -> ghr_forward_preprocess (radii, tile rects and
+ * sort keys bit for bit) and of ghr_backward -> ghr_lbs_deform_backward.
+ *
+ *   ghr_forward_deform_preprocess   dp: scales, rotations and shs are required; opacity from dp->opacity_logits
+ *                                   (sigmoid) or view->opacities.  view: P (= dp->P), W, H, tan_fov*, background,
+ *                                   viewmatrix, projmatrix, campos, prefiltered, debug -- its per-Gaussian pointers are
+ *                                   not read.  Writes radii and the geometry state like ghr_forward_preprocess.
+ *                                   world_pts [P,3], world_normals [P,3], cov3D [P,6], colors [P,3] (zero for culled
+ *                                   Gaussians), opacity [P]: optional copies of the intermediate values, NULL = skipped.
+ *   ghr_forward_render_deformed     ghr_forward_render for such a view (no per-Gaussian input pointer is checked).
+ *   ghr_backward_deformed           blend backward + the fused per-Gaussian backward.  Outputs as
+ *                                   ghr_lbs_deform_backward (same accumulate_grads modes, dL_dopacity_logits through
+ *                                   dp), plus dL_dmeans2D [P,3] (screen-space gradient, always stored; NULL = skipped).
+ *                                   Culled Gaussians get zeros (nothing is added in the accumulating modes).
+ */
+int ghr_forward_deform_preprocess(const ghr_deform_params* dp, const ghr_raster_params* view, int32_t* radii, void* geom,
+                                  size_t geom_bytes, float* world_pts, float* world_normals, float* cov3D, float* colors,
+                                  float* opacity, int32_t* num_rendered_host, void* stream);
+int ghr_forward_render_deformed(const ghr_raster_params* view, void* geom, size_t geom_bytes, void* binning,
+                                size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
+                                float* out_depth, float* out_alpha, void* stream);
+int ghr_backward_deformed(const ghr_deform_params* dp, const ghr_raster_params* view, const int32_t* radii,
+                          const void* geom, size_t geom_bytes, const void* binning, size_t binning_bytes, int64_t capacity,
+                          const void* img, size_t img_bytes, const float* dL_dout_color, const float* dL_dout_depth,
+                          const float* dL_dout_alpha, float* accum /* [P,12] zeroed */, float* dL_dmeans2D,
+                          float* dL_dxyz, float* dL_dlbs_offsets /* [P,24]|NULL */, float* dL_dscales,
+                          float* dL_drotations, float* dL_dshs, float* dL_dA_target /* [24*12]|NULL, accumulated */,
+                          float* dL_dvertex_offsets /* [V*3]|NULL, accumulated */, void* stream);
+
 /* Pose-branch backward: dL/dA_target [24,12] and dL/dvertex_offsets [V,3] (or NULL) -> dL/dcorrect_Rs
  * [23,3,3] (the only learnable input of the pose branch, nets/mlp_delta_body_pose.py).
  * dL_dcorrect_Rs must hold 23*9 + 207 floats: the tail is scratch for the pose-feature gradient. */
@@ -586,7 +620,9 @@ enum ghr_stage {
     GHR_STAGE_LBS_BWD = 10,
     GHR_STAGE_MISC = 11,
     GHR_STAGE_OPTIMIZER = 12,   /* fused Adam, densification statistics           */
-    GHR_STAGE_COUNT = 13
+    GHR_STAGE_DEFORM_PROJECT = 13,     /* fused LBS + projection forward (ghr_forward_deform_preprocess) */
+    GHR_STAGE_PROJECT_DEFORM_BWD = 14, /* fused projection + LBS backward (ghr_backward_deformed)        */
+    GHR_STAGE_COUNT = 15
 };
 uint64_t ghr_launch_count(void);
 /* Scheduling hint (process-wide, default 0): 1 = several independent views are in flight on different streams

@@ -120,6 +120,14 @@ SIGNATURES = {
     "ghr_lbs_deform_forward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 10),
     "ghr_lbs_deform_backward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 15),
     "ghr_lbs_pose_backward": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
+    "ghr_forward_deform_preprocess": (C.c_int, [C.POINTER(DeformParams), C.POINTER(RasterParams), C.c_void_p, C.c_void_p,
+                                                C.c_size_t] + [C.c_void_p] * 7),
+    "ghr_forward_render_deformed": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                              C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_void_p]),
+    "ghr_backward_deformed": (C.c_int, [C.POINTER(DeformParams), C.POINTER(RasterParams), C.c_void_p, C.c_void_p,
+                                        C.c_size_t, C.c_void_p, C.c_size_t, C.c_int64, C.c_void_p, C.c_size_t]
+                              + [C.c_void_p] * 13),
     "ghr_smpl_lbs_vertices": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
     "ghr_covariance_forward": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ghr_covariance_backward": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_float] + [C.c_void_p] * 6),
@@ -156,7 +164,7 @@ SIGNATURES = {
 }
 
 STAGES = ("preprocess", "emit_keys", "sort", "tile_ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "knn",
-          "lbs_joints", "lbs_fwd", "lbs_bwd", "misc", "optimizer")
+          "lbs_joints", "lbs_fwd", "lbs_bwd", "misc", "optimizer", "deform_project", "project_deform_bwd")
 
 _lib = None
 

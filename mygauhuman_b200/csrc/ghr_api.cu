@@ -42,6 +42,16 @@ int validate(const ghr_raster_params* p)
     return GHR_OK;
 }
 
+// the camera / image half of ghr_raster_params: what the stages after the projection read
+int validate_view(const ghr_raster_params* p)
+{
+    if (!p) return GHR_ERR_BAD_ARG;
+    if (p->P < 0 || p->W <= 0 || p->H <= 0) return GHR_ERR_BAD_ARG;
+    if (p->P == 0) return GHR_OK;
+    if (!p->viewmatrix || !p->projmatrix || !p->background || !p->campos) return GHR_ERR_BAD_ARG;
+    return GHR_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -141,9 +151,9 @@ static int multi_layout(const ghr_raster_params* prm, int64_t capacity, const vo
 static int forward_render_impl(const ghr_raster_params* prm, void* geom, size_t geom_bytes, void* binning,
                                size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
                                float* out_depth, float* out_alpha, int n_attr, const float* packed, float* out_images,
-                               void* stream)
+                               void* stream, bool deformed = false)
 {
-    int r = validate(prm);
+    int r = deformed ? validate_view(prm) : validate(prm);
     if (r != GHR_OK) return r;
     if (!out_color || !out_depth || !out_alpha) return GHR_ERR_BAD_ARG;
     if (n_attr && (attr_stride(n_attr) == 0 || blend_throughput_regime(capacity) || !packed || !out_images ||
@@ -560,6 +570,79 @@ int ghr_smpl_lbs_vertices(const ghr_lbs_model* model, const float* v_template, c
     if (!v_template || !pose_buf || !offsets || !verts) return GHR_ERR_BAD_ARG;
     return check_cuda(launch_smpl_lbs_vertices(*model, v_template, pose_buf, offsets, verts, T_out, (cudaStream_t)stream),
                       "smpl_lbs_vertices");
+}
+
+// ---- fused LBS + projection chain (include/ghr.h; kernels in ghr_fused.cu) -----------------------------------------
+static int validate_fused(const ghr_deform_params* dp, const ghr_raster_params* view)
+{
+    int r = validate_deform(dp);
+    if (r != GHR_OK) return r;
+    if ((r = validate_view(view)) != GHR_OK) return r;
+    if (view->P != dp->P) return GHR_ERR_BAD_ARG;
+    if (dp->P == 0) return GHR_OK;
+    if (!dp->scales || !dp->rotations || !dp->shs) return GHR_ERR_BAD_ARG;  // the chain needs covariance and colour
+    if (!dp->opacity_logits && !view->opacities) return GHR_ERR_BAD_ARG;
+    if (misaligned(dp->shs, 4)) return GHR_ERR_BAD_ARG;
+    return GHR_OK;
+}
+
+int ghr_forward_deform_preprocess(const ghr_deform_params* dp, const ghr_raster_params* view, int32_t* radii, void* geom,
+                                  size_t geom_bytes, float* world_pts, float* world_normals, float* cov3D, float* colors,
+                                  float* opacity, int32_t* num_rendered_host, void* stream)
+{
+    int r = validate_fused(dp, view);
+    if (r != GHR_OK) return r;
+    cudaStream_t s = (cudaStream_t)stream;
+    ghr_layout L;
+    if (ghr_state_layout(dp->P, 0, view->W, view->H, &L) != GHR_OK) return GHR_ERR_BAD_ARG;
+    if (!geom || geom_bytes < L.geom_bytes || misaligned(geom, 256)) return GHR_ERR_BUFFER;
+    if (dp->P == 0) {
+        r = check_cuda(cudaMemsetAsync(geom, 0, sizeof(ghr_geom_header), s), "deform_preprocess(P=0)");
+        if (num_rendered_host) *num_rendered_host = 0;
+        return r;
+    }
+    if (!radii) return GHR_ERR_BAD_ARG;
+    if (world_normals && !dp->normals) return GHR_ERR_BAD_ARG;
+    return stage_done(view,
+                      launch_deform_project(*dp, *view, radii, (char*)geom, L, world_pts, world_normals, cov3D, colors,
+                                            opacity, num_rendered_host, s),
+                      s, "deform_project");
+}
+
+int ghr_forward_render_deformed(const ghr_raster_params* view, void* geom, size_t geom_bytes, void* binning,
+                                size_t binning_bytes, int64_t capacity, void* img, size_t img_bytes, float* out_color,
+                                float* out_depth, float* out_alpha, void* stream)
+{
+    return forward_render_impl(view, geom, geom_bytes, binning, binning_bytes, capacity, img, img_bytes, out_color,
+                               out_depth, out_alpha, 0, nullptr, nullptr, stream, true);
+}
+
+int ghr_backward_deformed(const ghr_deform_params* dp, const ghr_raster_params* view, const int32_t* radii,
+                          const void* geom, size_t geom_bytes, const void* binning, size_t binning_bytes, int64_t capacity,
+                          const void* img, size_t img_bytes, const float* dL_dout_color, const float* dL_dout_depth,
+                          const float* dL_dout_alpha, float* accum, float* dL_dmeans2D, float* dL_dxyz,
+                          float* dL_dlbs_offsets, float* dL_dscales, float* dL_drotations, float* dL_dshs,
+                          float* dL_dA_target, float* dL_dvertex_offsets, void* stream)
+{
+    int r = validate_fused(dp, view);
+    if (r != GHR_OK) return r;
+    if (dp->P == 0) return GHR_OK;
+    if (!radii || !dL_dout_color || !dL_dout_depth || !dL_dout_alpha || !accum || misaligned(accum, 16) || !dL_dxyz ||
+        !dL_dscales || !dL_drotations || !dL_dshs || misaligned(dL_drotations, 16))
+        return GHR_ERR_BAD_ARG;
+    if (dp->opacity_logits && !dp->dL_dopacity_logits) return GHR_ERR_BAD_ARG;
+    ghr_layout L;
+    if ((r = multi_layout(view, capacity, geom, geom_bytes, binning, binning_bytes, img, img_bytes, &L)) != GHR_OK) return r;
+    cudaStream_t s = (cudaStream_t)stream;
+    r = stage_done(view,
+                   launch_blend_backward(*view, (const char*)geom, (const char*)binning, (const char*)img, L,
+                                         dL_dout_color, dL_dout_depth, dL_dout_alpha, accum, s),
+                   s, "blend_backward");
+    if (r != GHR_OK) return r;
+    DeformGrads g{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, dL_dxyz, nullptr, dL_dlbs_offsets, dL_dscales,
+                  dL_drotations, dL_dshs, dL_dA_target, dL_dvertex_offsets};
+    return stage_done(view, launch_project_deform_backward(*dp, *view, radii, (const char*)geom, L, accum, g, dL_dmeans2D, s),
+                      s, "project_deform_backward");
 }
 
 }  // extern "C"

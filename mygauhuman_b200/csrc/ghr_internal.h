@@ -197,6 +197,13 @@ cudaError_t launch_smpl_lbs_vertices(const ghr_lbs_model& m, const float* vt, co
                                      float* verts, float* T_out, cudaStream_t s);
 cudaError_t launch_lbs_deform_forward(const ghr_deform_params& p, const DeformOut& o, cudaStream_t s);
 cudaError_t launch_lbs_deform_backward(const ghr_deform_params& p, const DeformGrads& g, cudaStream_t s);
+// fused LBS + projection (ghr_fused.cu)
+cudaError_t launch_deform_project(const ghr_deform_params& dp, const ghr_raster_params& p, int32_t* radii, char* geom,
+                                  const ghr_layout& L, float* world_pts, float* world_normals, float* cov3D, float* colors,
+                                  float* opacity, int32_t* n_host, cudaStream_t s);
+cudaError_t launch_project_deform_backward(const ghr_deform_params& dp, const ghr_raster_params& p, const int32_t* radii,
+                                           const char* geom, const ghr_layout& L, const float* accum,
+                                           const DeformGrads& g, float* dL_dmean2D, cudaStream_t s);
 size_t vertex_grid_workspace_bytes(int V);
 cudaError_t launch_vertex_grid_build(int V, const float* verts, char* ws, cudaStream_t s);
 cudaError_t launch_nearest_vertex(int P, const float* query, int V, const char* ws, int32_t* vid, cudaStream_t s);

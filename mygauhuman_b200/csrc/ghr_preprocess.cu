@@ -44,47 +44,7 @@ __global__ void __launch_bounds__(GHR_BLOCK) preprocess_kernel(const PreArgs a)
             dbits_lo_inv = ~dbits_hi;
         }
     }
-    // depth range of the visible Gaussians, for the sort (ghr_sort.cu: squeezed digits): depth > 0.2, so the bit
-    // patterns order like the values
-    dbits_hi = __reduce_max_sync(0xffffffffu, dbits_hi);
-    dbits_lo_inv = __reduce_max_sync(0xffffffffu, dbits_lo_inv);
-    if ((tid & 31) == 0 && dbits_hi) {
-        atomicMax(&a.hdr->depth_hi, dbits_hi);
-        atomicMax(&a.hdr->depth_lo_inv, dbits_lo_inv);
-    }
-
-    // block-wide inclusive scan of `tiles`
-    const uint32_t lane = lane_id(), warp = tid >> 5;
-    uint32_t v = tiles;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
-        if (lane >= (uint32_t)o) v += t;
-    }
-    if (lane == 31) s_warp[warp] = v;
-    __syncthreads();
-    if (warp == 0) {
-        uint32_t w = lane < 8 ? s_warp[lane] : 0;
-#pragma unroll
-        for (int o = 1; o < 8; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
-            if (lane >= (uint32_t)o) w += t;
-        }
-        const uint32_t block_total = __shfl_sync(0xffffffffu, w, 7);
-        // exclusive prefix over warps = inclusive of the previous warp
-        const uint32_t prev = __shfl_up_sync(0xffffffffu, w, 1);
-        if (lane < 8) s_warp[lane] = (lane == 0) ? 0u : prev;
-        const uint32_t excl = lookback_exclusive(a.scan_status, tile, block_total);
-        if (lane == 0) {
-            s_excl = excl;
-            if (tile == a.nblocks - 1) {
-                a.hdr->num_rendered = excl + block_total;
-                if (a.n_host) *a.n_host = (int32_t)(excl + block_total);
-            }
-        }
-    }
-    __syncthreads();
-    if (idx < a.P) a.point_offsets[idx] = s_excl + s_warp[warp] + v;
+    finish_preprocess_block(a, tile, idx, tiles, dbits_hi, dbits_lo_inv, s_warp, s_excl);
 }
 
 __global__ void __launch_bounds__(GHR_BLOCK) mark_visible_kernel(int P, const float* __restrict__ means3D,

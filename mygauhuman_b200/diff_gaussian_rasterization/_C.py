@@ -102,6 +102,38 @@ def _pinned_counter(device):
     return buf
 
 
+def launch_with_capacity(dev, P, W, H, preprocess, render):
+    """The binning-capacity policy of a forward: preprocess(counter_ptr | None) enqueues the projection kernel (which
+    writes num_rendered to the pinned counter when given one), render(capacity) -> binning buffer enqueues the rest.
+    Sync-free mode: fixed capacity, no host read.  Otherwise: optimistic launch (see the comment at _cap_hint).
+    Returns (num_rendered, binning)."""
+    if _capacity is not None:  # explicit sync-free mode
+        preprocess(None)
+        capacity = num_rendered = _round_cap(_capacity)
+        return num_rendered, render(capacity)
+    counter = _pinned_counter(dev)
+    preprocess(counter.data_ptr())
+    key = (dev.index, P, W, H)
+    guess = _cap_hint.get(key)
+    if guess is None:
+        torch.cuda.current_stream().synchronize()  # first call: the reference's blocking read
+        num_rendered = int(counter[0])
+        capacity = _round_cap(num_rendered)
+        binning = render(capacity)
+    else:
+        ev = torch.cuda.Event()
+        ev.record()
+        capacity = guess
+        binning = render(capacity)       # GPU keeps working while the host waits for preprocess only
+        ev.synchronize()
+        num_rendered = int(counter[0])
+        if num_rendered > capacity:      # rare: guess too small -> kernels exited early; redo exactly
+            capacity = _round_cap(num_rendered)
+            binning = render(capacity)
+    _cap_hint[key] = _round_cap(num_rendered + num_rendered // 4 + 1024)
+    return num_rendered, binning
+
+
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
                         prefiltered, debug, _attrs=None):
@@ -149,33 +181,11 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                                        out_alpha.data_ptr(), s), "ghr_forward_render")
             return binning
 
-        if _capacity is not None:  # explicit sync-free mode
-            check(l.ghr_forward_preprocess(C.byref(p), radii.data_ptr(), geom.data_ptr(), geom.numel(), None, s),
+        def preprocess(counter_ptr):
+            check(l.ghr_forward_preprocess(C.byref(p), radii.data_ptr(), geom.data_ptr(), geom.numel(), counter_ptr, s),
                   "ghr_forward_preprocess")
-            capacity = num_rendered = _round_cap(_capacity)
-            binning = render(capacity)
-        else:
-            counter = _pinned_counter(dev)
-            check(l.ghr_forward_preprocess(C.byref(p), radii.data_ptr(), geom.data_ptr(), geom.numel(),
-                                           counter.data_ptr(), s), "ghr_forward_preprocess")
-            key = (dev.index, P, W, H)
-            guess = _cap_hint.get(key)
-            if guess is None:
-                torch.cuda.current_stream().synchronize()  # first call: the reference's blocking read
-                num_rendered = int(counter[0])
-                capacity = _round_cap(num_rendered)
-                binning = render(capacity)
-            else:
-                ev = torch.cuda.Event()
-                ev.record()
-                capacity = guess
-                binning = render(capacity)       # GPU keeps working while the host waits for preprocess only
-                ev.synchronize()
-                num_rendered = int(counter[0])
-                if num_rendered > capacity:      # rare: guess too small -> kernels exited early; redo exactly
-                    capacity = _round_cap(num_rendered)
-                    binning = render(capacity)
-            _cap_hint[key] = _round_cap(num_rendered + num_rendered // 4 + 1024)
+
+        num_rendered, binning = launch_with_capacity(dev, P, W, H, preprocess, render)
         if debug:
             read_status(geom, raise_on_error=True)
     global _last_geom

@@ -53,14 +53,17 @@ class GraphedRenderStep:
 
     def __init__(self, deformer, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx, tanfovy, bg,
                  loss_fn, n_loss_inputs=1, sh_degree=3, scaling_modifier=1.0, capacity_hint=None, use_graph=True,
-                 all_reduce=None, group=None, accumulate=False, shared_flat=None):
+                 all_reduce=None, group=None, accumulate=False, shared_flat=None, fused=True):
         """all_reduce: None (single GPU), "after" (one NCCL sum all-reduce of the flat gradient bucket issued right
         after the replay) or "captured" (the all-reduce is part of the graph: every rank replays in lockstep).
         accumulate=True: multi-view batches.  Every call ADDS its gradients to the flat bucket (leaves[k].grad are
         views of it); zero_grads() starts a batch and reduce_grads() sums the bucket over the ranks once per batch
         (all_reduce must then be None: the collective is per batch, not per view).
         shared_flat (accumulate mode): another step's flat bucket to add into, with atomics -- the lanes of a
-        MultiLaneRenderStep run concurrently on several streams and sum into one bucket."""
+        MultiLaneRenderStep run concurrently on several streams and sum into one bucket.
+        fused=True: the per-Gaussian chain runs as one kernel each way (fused.render_deformed: LBS + covariance + SH +
+        projection, and their backward) instead of SMPLDeformer.deform_gaussians -> GaussianRasterizer."""
+        self.fused = bool(fused)
         self.deformer, self.leaves = deformer, leaves
         self.big, self.t_vertices = big_pose_params, t_vertices
         self.H, self.W, self.tanfovx, self.tanfovy = int(image_height), int(image_width), float(tanfovx), float(tanfovy)
@@ -106,6 +109,8 @@ class GraphedRenderStep:
     def _eager(self, vec, loss_inputs, capacity, reduce=False):
         L = self.leaves
         camd, pose = unpack_view(vec)
+        if self.fused:
+            return self._eager_fused(camd, pose, loss_inputs, capacity, reduce)
         # exp / sigmoid of the raw parameters are fused into the deform kernels (no separate ATen launches)
         self.deformer.vert_ids_override = self.vert_ids
         try:
@@ -150,6 +155,49 @@ class GraphedRenderStep:
             for k in L:
                 L[k].grad = self.flat_views[k]
         return loss, dict(color=color, depth=depth, alpha=alpha, radii=radii, means2D=means2D)
+
+    def _eager_fused(self, camd, pose, loss_inputs, capacity, reduce):
+        from .fused import render_deformed
+        L = self.leaves
+        rs = dgr.GaussianRasterizationSettings(
+            image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=self.bg,
+            scale_modifier=self.mod, viewmatrix=camd["view"], projmatrix=camd["proj"], sh_degree=self.sh_degree,
+            campos=camd["campos"], prefiltered=False, debug=False)
+        means2D = torch.zeros_like(L["xyz"], requires_grad=True)
+        self.deformer.vert_ids_override = self.vert_ids
+        _C.set_sync_free_capacity(capacity)
+        try:
+            color, radii, depth, alpha = render_deformed(
+                self.deformer, L["xyz"], pose, self.big, self.t_vertices, rs, log_scaling=L["log_scale"],
+                rotation=L["rotation"], features=L["features"], opacity_logit=L["opacity_logit"], means2D=means2D)
+        finally:
+            _C.set_sync_free_capacity(None)
+            self.deformer.vert_ids_override = None
+        if capacity is not None:
+            geom = _C._last_geom
+            torch.maximum(self.n_seen, geom[:4].view(torch.int32), out=self.n_seen)
+        loss = self.loss_fn(color, depth, alpha, *loss_inputs)
+        out = dict(color=color, depth=depth, alpha=alpha, radii=radii, means2D=means2D)
+        if self._sink is not None:
+            self.deformer.grad_sink, self.deformer.grad_sink_atomic = self._sink, self._sink_atomic
+            try:
+                loss.backward()
+            finally:
+                self.deformer.grad_sink, self.deformer.grad_sink_atomic = None, False
+            return loss, out
+        for t in L.values():
+            t.grad = None
+        loss.backward()
+        if "normals" in L and L["normals"].grad is None:  # normals do not reach the images on this path
+            L["normals"].grad = torch.zeros_like(L["normals"])
+        if self.flat is not None:
+            with torch.no_grad():
+                torch._foreach_copy_([self.flat_views[k] for k in L], [L[k].grad for k in L])  # one multi-tensor kernel
+                if reduce:
+                    self._reduce()
+            for k in L:
+                L[k].grad = self.flat_views[k]
+        return loss, out
 
     def zero_grads(self):
         """accumulate mode: start a batch of views."""
@@ -296,7 +344,7 @@ class MultiLaneRenderStep:
     """
 
     def __init__(self, deformers, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx, tanfovy, bg,
-                 loss_fn, n_loss_inputs=1, sh_degree=3, scaling_modifier=1.0, use_graph=True, group=None):
+                 loss_fn, n_loss_inputs=1, sh_degree=3, scaling_modifier=1.0, use_graph=True, group=None, fused=True):
         """deformers: one SMPLDeformer per lane (they hold per-call scratch the lanes must not share)."""
         assert len(deformers) >= 1
         self.leaves, self.group = leaves, group
@@ -309,7 +357,7 @@ class MultiLaneRenderStep:
             self.lanes.append(GraphedRenderStep(d, leaves, big_pose_params, t_vertices, image_height, image_width, tanfovx,
                                                 tanfovy, bg, loss_fn, n_loss_inputs=n_loss_inputs, sh_degree=sh_degree,
                                                 scaling_modifier=scaling_modifier, use_graph=use_graph, group=group,
-                                                accumulate=True,
+                                                accumulate=True, fused=fused,
                                                 shared_flat=self.lanes[0].flat if self.lanes else None))
         # The nearest SMPL vertex of a Gaussian depends on the canonical positions only, and those do not change inside a
         # batch: the search runs once per batch (zero_grads) instead of once per view (39 us of a 420 us view).

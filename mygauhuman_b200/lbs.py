@@ -151,6 +151,41 @@ class SMPLDeformer:
                   "ghr_nearest_vertex")
         return vid
 
+    def prepare_pose(self, xyz_c, params, t_params, t_vertices, correct_Rs=None):
+        """Everything the per-Gaussian kernels need besides the Gaussians: (pose buffer of the big pose, pose buffer of the
+        target pose, pose blend-shape vertex offsets [V,3], nearest-vertex ids [P] int32)."""
+        dev = self.device
+        P = xyz_c.shape[0]
+        pose_big = self._big_pose_buffer(t_params)
+        # The nearest-vertex search (depends on xyz only) runs on a side stream next to the pose chain and the pose
+        # blend-shape offsets (depend on the pose only); both are short, latency-bound kernels.  Fork/join through
+        # stream waits, so the overlap is kept when the step is captured into a CUDA graph.  Every buffer the side
+        # stream touches is allocated on the caller's stream beforehand.
+        vid = self.vert_ids_override
+        have_vid = vid is not None
+        if have_vid:
+            assert vid.dtype == torch.int32 and vid.numel() == P and vid.is_contiguous() and vid.device == xyz_c.device
+        else:
+            vid = torch.empty(P, dtype=torch.int32, device=dev)
+        tv = _f32c(t_vertices.detach())
+        cur = torch.cuda.current_stream(dev)
+        side = self._side_stream if not have_vid else None
+        if have_vid:
+            pass
+        elif P and side is not None:
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                self.nearest_vertex(tv, xyz_c, out=vid)
+        pose_tgt = self.pose_buffer(params, correct_Rs)
+        off = self.vertex_offsets(pose_big, pose_tgt, params["shapes"])
+        if have_vid:
+            pass
+        elif P and side is not None:
+            cur.wait_stream(side)
+        elif P:
+            self.nearest_vertex(tv, xyz_c, out=vid)
+        return pose_big, pose_tgt, off, vid
+
     # ---- the operators -----------------------------------------------------
     def deform_gaussians(self, xyz, params, t_params, t_vertices, normals=None, lbs_weights=None, correct_Rs=None,
                          scaling=None, rotation=None, scaling_modifier=1.0, features=None, sh_degree=0, campos=None,
@@ -230,34 +265,7 @@ class _DeformFn(torch.autograd.Function):
         shs = None if features is None else _f32c(features.detach())
         M = 0 if shs is None else shs.shape[1]
         cam = None if campos is None else _f32c(campos.detach().to(dev)).reshape(-1)
-        pose_big = self._big_pose_buffer(t_params)
-        # The nearest-vertex search (depends on xyz only) runs on a side stream next to the pose chain and the pose
-        # blend-shape offsets (depend on the pose only); both are short, latency-bound kernels.  Fork/join through
-        # stream waits, so the overlap is kept when the step is captured into a CUDA graph.  Every buffer the side
-        # stream touches is allocated on the caller's stream beforehand.
-        vid = self.vert_ids_override
-        have_vid = vid is not None
-        if have_vid:
-            assert vid.dtype == torch.int32 and vid.numel() == P and vid.is_contiguous() and vid.device == xyz_c.device
-        else:
-            vid = torch.empty(P, dtype=torch.int32, device=dev)
-        tv = _f32c(t_vertices.detach())
-        cur = torch.cuda.current_stream(dev)
-        side = self._side_stream if not have_vid else None
-        if have_vid:
-            pass
-        elif P and side is not None:
-            side.wait_stream(cur)
-            with torch.cuda.stream(side):
-                self.nearest_vertex(tv, xyz_c, out=vid)
-        pose_tgt = self.pose_buffer(params, correct_Rs)
-        off = self.vertex_offsets(pose_big, pose_tgt, params["shapes"])
-        if have_vid:
-            pass
-        elif P and side is not None:
-            cur.wait_stream(side)
-        elif P:
-            self.nearest_vertex(tv, xyz_c, out=vid)
+        pose_big, pose_tgt, off, vid = self.prepare_pose(xyz_c, params, t_params, t_vertices, correct_Rs)
 
         p = DeformParams()
         p.P, p.V, p.sh_degree, p.M = P, self.V, sh_degree, M
