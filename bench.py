@@ -70,6 +70,9 @@ def parse():
                          "(MultiLaneRenderStep); reduced to a divisor of --batch-views; 1 = one view at a time")
     ap.add_argument("--sync-free", action="store_true",
                     help="ours: size the binning buffer from the previous step instead of a blocking read")
+    ap.add_argument("--eager-chain", default="operators", choices=["operators", "fused"],
+                    help="--mode eager: the reference-shaped two-operator chain (deform_gaussians -> GaussianRasterizer) or "
+                         "the fused per-Gaussian kernels the graph configuration runs (for profiling them one by one)")
     ap.add_argument("--no-optimizer", action="store_true",
                     help="leave the optimiser step out of the measured step (round-1 behaviour: gradient all-reduce only)")
     ap.add_argument("--lr-scale", type=float, default=1e-3,
@@ -904,6 +907,7 @@ def run_workload(args, workload, world, rank, local, dev, K, Wm, headline):
     if ours:
         lanes = math.gcd(max(1, args.lanes), max(1, args.batch_views)) if args.mode == "graph" else 1
         arm = OursArm(wl, dev, args.sync_free, graph=(args.mode == "graph"), lanes=lanes)
+        arm.fused_eager = args.mode == "eager" and args.eager_chain == "fused"
     else:
         arm = ReferenceArm(wl, dev)
     views = wl["views"]
@@ -1157,13 +1161,14 @@ def run_workload(args, workload, world, rank, local, dev, K, Wm, headline):
     if ours and headline:
         arm.use_graph = False
         keep_opt, opt = opt, None
-        arm.fused_eager = graphed  # the graph configuration runs the fused per-Gaussian kernels: profile those
+        keep_chain = arm.fused_eager
+        arm.fused_eager = graphed or keep_chain  # the graph configuration runs the fused per-Gaussian kernels: profile those
         arm._lib.profile_enable(True)
         arm._lib.profile_read()
         timed(K, False)
         prof = arm._lib.profile_read()
         arm._lib.profile_enable(False)
-        arm.fused_eager = False
+        arm.fused_eager = keep_chain
         opt = keep_opt
         arm.use_graph = graphed
         if graphed:

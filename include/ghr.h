@@ -324,6 +324,23 @@ int ghr_lbs_vertex_offsets(const ghr_lbs_model* model, const float* pose_big, co
 /* Nearest SMPL vertex (the reference's knn_cuda KNN(k=1), gaussian_model.py:775).
  * build: bins t_vertices [V,3] into a uniform grid inside `workspace`;
  * query: exact nearest vertex (lowest index on ties) for P points -> vert_ids [P] int32; V as built. */
+/* The pose stage (ghr_lbs_pose + ghr_lbs_vertex_offsets) of the n_views <= GHR_POSE_VIEWS_MAX views of a multi-view
+ * batch in ONE launch: the 17 MB pose basis (posedirs) is read once for the batch instead of once per view.  `views` is a
+ * HOST array; per view the results equal those of the two per-view entry points bit for bit.  Reference: the same lines
+ * as ghr_lbs_pose / ghr_lbs_vertex_offsets (the reference runs them per iteration, batch size 1). */
+#define GHR_POSE_VIEWS_MAX 8
+typedef struct ghr_pose_view {
+    const float* poses;       /* [72]                                    */
+    const float* shapes;      /* [NB]                                    */
+    const float* correct_Rs;  /* [23,3,3] or NULL                        */
+    const float* R;           /* [9]                                     */
+    const float* Th;          /* [3]                                     */
+    float* pose_out;          /* [GHR_POSE_FLOATS] pose buffer           */
+    float* offsets_out;       /* [V,3] vertex offsets against pose_big   */
+} ghr_pose_view;
+int ghr_lbs_pose_views(const ghr_lbs_model* model, int32_t n_views, const ghr_pose_view* views, const float* pose_big,
+                       void* stream);
+
 size_t ghr_vertex_grid_workspace_bytes(int32_t V);
 int ghr_vertex_grid_build(int32_t V, const float* t_vertices, void* workspace, size_t workspace_bytes, void* stream);
 int ghr_nearest_vertex(int32_t P, const float* query, int32_t V, const void* workspace, int32_t* vert_ids,

@@ -47,6 +47,15 @@ class LbsModel(C.Structure):
                 ("joint_template", c_f32p), ("joint_shapedirs", c_f32p), ("parents", C.c_void_p)]
 
 
+class PoseView(C.Structure):
+    """ghr_pose_view (include/ghr.h)."""
+    _fields_ = [("poses", c_f32p), ("shapes", c_f32p), ("correct_Rs", c_f32p), ("R", c_f32p), ("Th", c_f32p),
+                ("pose_out", c_f32p), ("offsets_out", c_f32p)]
+
+
+POSE_VIEWS_MAX = 8
+
+
 class DeformParams(C.Structure):
     """ghr_deform_params (include/ghr.h)."""
     _fields_ = [("P", C.c_int32), ("V", C.c_int32), ("sh_degree", C.c_int32), ("M", C.c_int32),
@@ -114,6 +123,7 @@ SIGNATURES = {
     "ghr_lbs_prepare": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 6),
     "ghr_lbs_pose": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 7),
     "ghr_lbs_vertex_offsets": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 5),
+    "ghr_lbs_pose_views": (C.c_int, [C.POINTER(LbsModel), C.c_int32, C.POINTER(PoseView), C.c_void_p, C.c_void_p]),
     "ghr_vertex_grid_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "ghr_vertex_grid_build": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "ghr_nearest_vertex": (C.c_int, [C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -497,6 +497,20 @@ int ghr_lbs_vertex_offsets(const ghr_lbs_model* model, const float* pose_big, co
                       "lbs_vertex_offsets");
 }
 
+int ghr_lbs_pose_views(const ghr_lbs_model* model, int32_t n_views, const ghr_pose_view* views, const float* pose_big,
+                       void* stream)
+{
+    int r = validate_model(model);
+    if (r != GHR_OK) return r;
+    if (n_views < 0 || n_views > GHR_POSE_VIEWS_MAX || (n_views && !views)) return GHR_ERR_BAD_ARG;
+    if (n_views == 0) return GHR_OK;
+    for (int i = 0; i < n_views; i++) {
+        const ghr_pose_view& v = views[i];
+        if (!v.poses || !v.R || !v.Th || !v.pose_out || !v.offsets_out || (model->NB > 0 && !v.shapes)) return GHR_ERR_BAD_ARG;
+    }
+    return check_cuda(launch_lbs_pose_views(*model, n_views, views, pose_big, (cudaStream_t)stream), "lbs_pose_views");
+}
+
 size_t ghr_vertex_grid_workspace_bytes(int32_t V) { return vertex_grid_workspace_bytes(V); }
 
 int ghr_vertex_grid_build(int32_t V, const float* t_vertices, void* workspace, size_t workspace_bytes, void* stream)

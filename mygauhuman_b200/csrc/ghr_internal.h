@@ -191,6 +191,8 @@ cudaError_t launch_lbs_pose(const ghr_lbs_model& m, const float* poses, const fl
                             const float* R, const float* Th, float* out, cudaStream_t s);
 cudaError_t launch_lbs_vertex_offsets(const ghr_lbs_model& m, const float* pose_big, const float* pose_tgt,
                                       const float* shapes, float* off, cudaStream_t s);
+cudaError_t launch_lbs_pose_views(const ghr_lbs_model& m, int n, const ghr_pose_view* views, const float* pose_big,
+                                  cudaStream_t s);
 cudaError_t launch_lbs_pose_backward(const ghr_lbs_model& m, const float* pose_tgt, const float* dA, const float* doff,
                                      float* dC, float* dpf_scratch, cudaStream_t s);
 cudaError_t launch_smpl_lbs_vertices(const ghr_lbs_model& m, const float* vt, const float* pose, const float* offsets,

@@ -65,28 +65,49 @@ __device__ __forceinline__ void mat3_inverse(const float* m, float* inv)
     inv[6] = c02 * id; inv[7] = (m[1] * m[6] - m[0] * m[7]) * id; inv[8] = (m[0] * m[4] - m[1] * m[3]) * id;
 }
 
-__global__ void __launch_bounds__(32) lbs_pose_kernel(int NB, const float* __restrict__ jt, const float* __restrict__ jsd,
-                                                      const int32_t* __restrict__ parents, const float* __restrict__ poses,
-                                                      const float* __restrict__ shapes, const float* __restrict__ correct_Rs,
-                                                      const float* __restrict__ Rg, const float* __restrict__ Th,
-                                                      float* __restrict__ out)
+// Rodrigues (gaussian_model.py:894-912): angle = |r + 1e-8|, k = r/angle;  K = [0 -kz ky; kz 0 -kx; -ky kx 0];
+// R = I + s K + c1 K K
+__device__ __forceinline__ void rodrigues(float rx, float ry, float rz, float* R)
 {
-    __shared__ float s_rot[kJ][9];
-    __shared__ float s_joint[kJ][3];
-    __shared__ float s_G[kJ][12];
-    const int j = threadIdx.x;
+    const float ax = rx + 1e-8f, ay = ry + 1e-8f, az = rz + 1e-8f;
+    const float angle = sqrtf(ax * ax + ay * ay + az * az);
+    const float kx = rx / angle, ky = ry / angle, kz = rz / angle;
+    const float s = sinf(angle), c1 = 1.0f - cosf(angle);
+    R[0] = 1.0f + c1 * (-kz * kz - ky * ky); R[1] = s * -kz + c1 * (kx * ky); R[2] = s * ky + c1 * (kx * kz);
+    R[3] = s * kz + c1 * (kx * ky); R[4] = 1.0f + c1 * (-kz * kz - kx * kx); R[5] = s * -kx + c1 * (ky * kz);
+    R[6] = s * -ky + c1 * (kx * kz); R[7] = s * kx + c1 * (ky * kz); R[8] = 1.0f + c1 * (-ky * ky - kx * kx);
+}
+
+// rotation of joint j >= 1 as the pose features see it: Rodrigues(poses[j]) (* correct_Rs[j-1])
+__device__ __forceinline__ void joint_rotation(const float* poses, const float* correct_Rs, int j, float* R)
+{
+    rodrigues(poses[3 * j], poses[3 * j + 1], poses[3 * j + 2], R);
+    if (correct_Rs && j > 0) {
+        float C[9], RC[9];
+#pragma unroll
+        for (int k = 0; k < 9; k++) C[k] = correct_Rs[9 * (j - 1) + k];
+        mat3_mul(R, C, RC);
+#pragma unroll
+        for (int k = 0; k < 9; k++) R[k] = RC[k];
+    }
+}
+
+struct PoseScratch {
+    float rot[kJ][9];
+    float joint[kJ][3];
+    float G[kJ][12];
+};
+
+// The pose stage of one view, run by ONE warp (j = lane): rotations, pose features, rest joints, kinematic chain.
+__device__ __forceinline__ void pose_chain(int j, int NB, const float* __restrict__ jt, const float* __restrict__ jsd,
+                                           const int32_t* __restrict__ parents, const float* __restrict__ poses,
+                                           const float* __restrict__ shapes, const float* __restrict__ correct_Rs,
+                                           const float* __restrict__ Rg, const float* __restrict__ Th,
+                                           float* __restrict__ out, PoseScratch& sc)
+{
     if (j < kJ) {
-        // Rodrigues (gaussian_model.py:894-912): angle = |r + 1e-8|, k = r/angle
-        const float rx = poses[3 * j], ry = poses[3 * j + 1], rz = poses[3 * j + 2];
-        const float ax = rx + 1e-8f, ay = ry + 1e-8f, az = rz + 1e-8f;
-        const float angle = sqrtf(ax * ax + ay * ay + az * az);
-        const float kx = rx / angle, ky = ry / angle, kz = rz / angle;
-        const float s = sinf(angle), c1 = 1.0f - cosf(angle);
-        // K = [0 -kz ky; kz 0 -kx; -ky kx 0];  R = I + s K + c1 K K
         float R[9];
-        R[0] = 1.0f + c1 * (-kz * kz - ky * ky); R[1] = s * -kz + c1 * (kx * ky); R[2] = s * ky + c1 * (kx * kz);
-        R[3] = s * kz + c1 * (kx * ky); R[4] = 1.0f + c1 * (-kz * kz - kx * kx); R[5] = s * -kx + c1 * (ky * kz);
-        R[6] = s * -ky + c1 * (kx * kz); R[7] = s * kx + c1 * (ky * kz); R[8] = 1.0f + c1 * (-ky * ky - kx * kx);
+        rodrigues(poses[3 * j], poses[3 * j + 1], poses[3 * j + 2], R);
 #pragma unroll
         for (int k = 0; k < 9; k++) out[GHR_POSE_ROD + 9 * j + k] = R[k];
         if (correct_Rs && j > 0) {
@@ -98,7 +119,7 @@ __global__ void __launch_bounds__(32) lbs_pose_kernel(int NB, const float* __res
             for (int k = 0; k < 9; k++) R[k] = RC[k];
         }
 #pragma unroll
-        for (int k = 0; k < 9; k++) { s_rot[j][k] = R[k]; out[GHR_POSE_ROT + 9 * j + k] = R[k]; }
+        for (int k = 0; k < 9; k++) { sc.rot[j][k] = R[k]; out[GHR_POSE_ROT + 9 * j + k] = R[k]; }
         if (j > 0) {
 #pragma unroll
             for (int k = 0; k < 9; k++) out[GHR_POSE_PF + 9 * (j - 1) + k] = R[k] - ((k == 0 || k == 4 || k == 8) ? 1.0f : 0.0f);
@@ -108,7 +129,7 @@ __global__ void __launch_bounds__(32) lbs_pose_kernel(int NB, const float* __res
         for (int c = 0; c < 3; c++) {
             float v = jt[3 * j + c];
             for (int b = 0; b < NB; b++) v += jsd[(3 * j + c) * NB + b] * shapes[b];
-            s_joint[j][c] = v;
+            sc.joint[j][c] = v;
             out[GHR_POSE_JOINTS + 3 * j + c] = v;
         }
     }
@@ -132,17 +153,17 @@ __global__ void __launch_bounds__(32) lbs_pose_kernel(int NB, const float* __res
         const int p = __shfl_sync(0xffffffffu, my_parent, i);
         if (j < 12) {
             if (i == 0) {
-                gval = c < 3 ? s_rot[0][3 * r + c] : s_joint[0][r];
+                gval = c < 3 ? sc.rot[0][3 * r + c] : sc.joint[0][r];
             } else {
-                const float g0 = s_G[p][4 * r], g1 = s_G[p][4 * r + 1], g2 = s_G[p][4 * r + 2], g3 = s_G[p][4 * r + 3];
+                const float g0 = sc.G[p][4 * r], g1 = sc.G[p][4 * r + 1], g2 = sc.G[p][4 * r + 2], g3 = sc.G[p][4 * r + 3];
                 if (c < 3) {
-                    gval = g0 * s_rot[i][c] + g1 * s_rot[i][3 + c] + g2 * s_rot[i][6 + c];
+                    gval = g0 * sc.rot[i][c] + g1 * sc.rot[i][3 + c] + g2 * sc.rot[i][6 + c];
                 } else {
-                    gval = g0 * (s_joint[i][0] - s_joint[p][0]) + g1 * (s_joint[i][1] - s_joint[p][1]) +
-                           g2 * (s_joint[i][2] - s_joint[p][2]) + g3;
+                    gval = g0 * (sc.joint[i][0] - sc.joint[p][0]) + g1 * (sc.joint[i][1] - sc.joint[p][1]) +
+                           g2 * (sc.joint[i][2] - sc.joint[p][2]) + g3;
                 }
             }
-            s_G[i][j] = gval;
+            sc.G[i][j] = gval;
             out[GHR_POSE_G + 12 * i + j] = gval;
         }
         __syncwarp();
@@ -150,10 +171,20 @@ __global__ void __launch_bounds__(32) lbs_pose_kernel(int NB, const float* __res
             // A_i = G_i with translation - G_i^{3x3} j_i (:939-942)
             float a = gval;
             if (c == 3)
-                a = gval - (s_G[i][4 * r] * s_joint[i][0] + s_G[i][4 * r + 1] * s_joint[i][1] + s_G[i][4 * r + 2] * s_joint[i][2]);
+                a = gval - (sc.G[i][4 * r] * sc.joint[i][0] + sc.G[i][4 * r + 1] * sc.joint[i][1] + sc.G[i][4 * r + 2] * sc.joint[i][2]);
             out[GHR_POSE_A + 12 * i + j] = a;
         }
     }
+}
+
+__global__ void __launch_bounds__(32) lbs_pose_kernel(int NB, const float* __restrict__ jt, const float* __restrict__ jsd,
+                                                      const int32_t* __restrict__ parents, const float* __restrict__ poses,
+                                                      const float* __restrict__ shapes, const float* __restrict__ correct_Rs,
+                                                      const float* __restrict__ Rg, const float* __restrict__ Th,
+                                                      float* __restrict__ out)
+{
+    __shared__ PoseScratch sc;
+    pose_chain(threadIdx.x, NB, jt, jsd, parents, poses, shapes, correct_Rs, Rg, Th, out, sc);
 }
 
 // ---------------------------------------------------------------------------
@@ -179,6 +210,67 @@ __global__ void __launch_bounds__(256) lbs_vertex_offsets_kernel(int rows, int N
 #pragma unroll
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (lane == 0) off[row] = acc;
+}
+
+// ---------------------------------------------------------------------------
+// The pose stage of up to GHR_POSE_VIEWS_MAX views in ONE launch (the views of a multi-view batch): the first n blocks
+// run one view's pose chain each (warp 0), the others are vertex-offset blocks that read every row of the 17 MB pose
+// basis ONCE for all the views (the per-view kernel reads it once per view).  An offset block derives the pose
+// features of its views itself (23 Rodrigues per view, the pose chain's own code), so it does not wait for the pose
+// blocks; per view the arithmetic, and therefore the result, is that of lbs_pose_kernel / lbs_vertex_offsets_kernel.
+// ---------------------------------------------------------------------------
+struct PoseViewsArgs {
+    int n, NB, rows;
+    const float *jt, *jsd, *posedirs, *shapedirs, *pose_big;
+    const int32_t* parents;
+    ghr_pose_view v[GHR_POSE_VIEWS_MAX];
+};
+
+__global__ void __launch_bounds__(256) lbs_pose_views_kernel(const PoseViewsArgs a)
+{
+    __shared__ PoseScratch sc;
+    __shared__ float s_dpf[GHR_POSE_VIEWS_MAX][GHR_LBS_POSE_DIM];
+    if ((int)blockIdx.x < a.n) {
+        if (threadIdx.x < 32) {
+            const ghr_pose_view& v = a.v[blockIdx.x];
+            pose_chain(threadIdx.x, a.NB, a.jt, a.jsd, a.parents, v.poses, v.shapes, v.correct_Rs, v.R, v.Th, v.pose_out, sc);
+        }
+        return;
+    }
+    for (int t = threadIdx.x; t < a.n * (kJ - 1); t += 256) {
+        const int vi = t / (kJ - 1), j = 1 + t % (kJ - 1);
+        float R[9];
+        joint_rotation(a.v[vi].poses, a.v[vi].correct_Rs, j, R);
+#pragma unroll
+        for (int k = 0; k < 9; k++) {
+            const float pf = R[k] - ((k == 0 || k == 4 || k == 8) ? 1.0f : 0.0f);
+            s_dpf[vi][9 * (j - 1) + k] = pf - (a.pose_big ? a.pose_big[GHR_POSE_PF + 9 * (j - 1) + k] : 0.0f);
+        }
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int row = (blockIdx.x - a.n) * 8 + (threadIdx.x >> 5);
+    if (row >= a.rows) return;
+    const float* pr = a.posedirs + (size_t)row * GHR_LBS_POSE_DIM;
+    float acc[GHR_POSE_VIEWS_MAX];
+#pragma unroll
+    for (int vi = 0; vi < GHR_POSE_VIEWS_MAX; vi++) acc[vi] = 0.0f;
+    for (int k = lane; k < GHR_LBS_POSE_DIM; k += 32) {
+        const float pv = pr[k];
+#pragma unroll
+        for (int vi = 0; vi < GHR_POSE_VIEWS_MAX; vi++)
+            if (vi < a.n) acc[vi] = fmaf(pv, s_dpf[vi][k], acc[vi]);
+    }
+    const float sd = (lane < a.NB) ? a.shapedirs[(size_t)row * a.NB + lane] : 0.0f;
+#pragma unroll
+    for (int vi = 0; vi < GHR_POSE_VIEWS_MAX; vi++) {
+        if (vi >= a.n) break;
+        float x = acc[vi];
+        if (a.v[vi].shapes && lane < a.NB) x = fmaf(sd, a.v[vi].shapes[lane], x);
+#pragma unroll
+        for (int o = 16; o; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if (lane == 0) a.v[vi].offsets_out[row] = x;
+    }
 }
 
 // dpf[k] = sum_r posedirs[r][k] * doff[r]  (transposed GEMV; 207 outputs)
@@ -309,6 +401,20 @@ cudaError_t launch_lbs_vertex_offsets(const ghr_lbs_model& m, const float* pose_
     const int rows = m.V * 3;
     lbs_vertex_offsets_kernel<<<(rows + 7) / 8, 256, 0, s>>>(rows, m.NB, m.posedirs, m.shapedirs, pose_big, pose_tgt,
                                                              shapes, off);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lbs_pose_views(const ghr_lbs_model& m, int n, const ghr_pose_view* views, const float* pose_big,
+                                  cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_LBS_JOINTS, s);
+    count_launch();
+    PoseViewsArgs a;
+    a.n = n; a.NB = m.NB; a.rows = m.V * 3;
+    a.jt = m.joint_template; a.jsd = m.joint_shapedirs; a.posedirs = m.posedirs; a.shapedirs = m.shapedirs;
+    a.pose_big = pose_big; a.parents = m.parents;
+    for (int i = 0; i < GHR_POSE_VIEWS_MAX; i++) a.v[i] = views[i < n ? i : 0];
+    lbs_pose_views_kernel<<<n + (a.rows + 7) / 8, 256, 0, s>>>(a);
     return cudaGetLastError();
 }
 

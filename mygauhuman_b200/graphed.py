@@ -91,6 +91,10 @@ class GraphedRenderStep:
                 self.flat_views[k] = self.flat[o:o + t.numel()].view_as(t)
                 o += pad(t.numel())
         self.vert_ids = None  # static int32 [P]: nearest-vertex ids supplied by the owner (MultiLaneRenderStep)
+        # (pose buffer, vertex offsets): static buffers the step reads the target pose from instead of running the pose
+        # stage itself.  A MultiLaneRenderStep fills them for all its lanes with ONE launch per group (pose_views) and sets
+        # _pose_ready; a direct call of this step fills them itself.
+        self.pose_inputs, self._pose_ready = None, False
         self._sink, self._sink_atomic = None, False
         if accumulate:
             # the deform backward kernel adds straight into the bucket: no separate accumulation pass
@@ -106,7 +110,19 @@ class GraphedRenderStep:
         self.out = None
 
     # ---- the eager step (also what gets captured) -------------------------------------------------
-    def _eager(self, vec, loss_inputs, capacity, reduce=False):
+    def _fill_pose(self):
+        """The pose stage of the view in self.vec into the static pose buffers (one launch)."""
+        self.deformer.pose_views(self.big, [_pose_slices(self.vec)], [self.pose_inputs])
+
+    def _eager(self, vec, loss_inputs, capacity, reduce=False, static_pose=False):
+        """static_pose: read the target pose from self.pose_inputs (filled beforehand) instead of computing it from vec."""
+        self.deformer.pose_override = self.pose_inputs if static_pose else None
+        try:
+            return self._eager_impl(vec, loss_inputs, capacity, reduce)
+        finally:
+            self.deformer.pose_override = None
+
+    def _eager_impl(self, vec, loss_inputs, capacity, reduce):
         L = self.leaves
         camd, pose = unpack_view(vec)
         if self.fused:
@@ -241,18 +257,21 @@ class GraphedRenderStep:
         if not self.use_graph:
             return
         in_graph = self.all_reduce == "captured"
+        sp = self.pose_inputs is not None
+        if sp:
+            self._fill_pose()
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             for _ in range(3):  # warm-up on a side stream, as torch.cuda.graph requires
-                self._eager(self.vec, self.loss_inputs, self.capacity, reduce=in_graph)
+                self._eager(self.vec, self.loss_inputs, self.capacity, reduce=in_graph, static_pose=sp)
         torch.cuda.current_stream().wait_stream(s)
         for k, t in self.leaves.items():
             t.grad = None if self._sink is None else self.flat_views[k]
         self.graph = torch.cuda.CUDAGraph()
         n0 = _lib.launch_count()
         with torch.cuda.graph(self.graph):
-            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity, reduce=in_graph)
+            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity, reduce=in_graph, static_pose=sp)
         self.kernels_per_replay = _lib.launch_count() - n0  # libghr kernels inside one replay
         self.n_seen.zero_()
 
@@ -272,8 +291,11 @@ class GraphedRenderStep:
                 dst.copy_(src, non_blocking=True)
 
     def _run(self):
+        if self.pose_inputs is not None and not self._pose_ready:
+            self._fill_pose()
         if self.graph is None:
-            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity, reduce=self.all_reduce is not None)
+            self.loss, self.out = self._eager(self.vec, self.loss_inputs, self.capacity, reduce=self.all_reduce is not None,
+                                              static_pose=self.pose_inputs is not None)
         else:
             self.graph.replay()
             if self.all_reduce == "after":
@@ -362,10 +384,15 @@ class MultiLaneRenderStep:
         # The nearest SMPL vertex of a Gaussian depends on the canonical positions only, and those do not change inside a
         # batch: the search runs once per batch (zero_grads) instead of once per view (39 us of a 420 us view).
         self.vert_ids = torch.zeros(leaves["xyz"].shape[0], dtype=torch.int32, device=deformers[0].device)
+        dev = deformers[0].device
+        # The pose stage (joint chain + pose blend-shape offsets: 17 MB of pose basis per view) of all the views of a
+        # group runs as ONE launch before the lanes fork, into per-lane static buffers the lanes' graphs read.
+        self.batch_pose = len(self.lanes) > 1
         for lane in self.lanes:
             lane._sink_atomic = len(self.lanes) > 1
             lane.vert_ids = self.vert_ids
-        dev = deformers[0].device
+            if self.batch_pose:
+                lane.pose_inputs = (torch.zeros(_lib.POSE_FLOATS, device=dev), torch.zeros(deformers[0].V, 3, device=dev))
         self.streams = [torch.cuda.Stream(device=dev) for _ in self.lanes]
         self._fork = torch.cuda.Event()
         self._joins = [torch.cuda.Event() for _ in self.lanes]
@@ -406,17 +433,35 @@ class MultiLaneRenderStep:
         (only its length is used); next_vecs / next_loss_inputs: what to prefetch per lane right after issuing (the host
         copies of the next group then overlap this group's kernels).  Returns the lanes' loss tensors (static buffers)."""
         cur = torch.cuda.current_stream()
+        if self.batch_pose:
+            srcs = []
+            for j in range(len(vecs)):
+                lane = self.lanes[j]
+                if prefetched:
+                    cur.wait_event(lane._staged_ready)
+                    srcs.append(lane._staged[0])
+                elif vecs[j].is_cuda:
+                    srcs.append(vecs[j])
+                else:
+                    lane.vec.copy_(vecs[j], non_blocking=True)
+                    srcs.append(lane.vec)
+            self.lanes[0].deformer.pose_views(self.lanes[0].big, [_pose_slices(v) for v in srcs],
+                                              [self.lanes[j].pose_inputs for j in range(len(vecs))])
         self._fork.record(cur)
         losses = []
         for j in range(len(vecs)):
             lane, s = self.lanes[j], self.streams[j]
             s.wait_event(self._fork)
             with torch.cuda.stream(s):
-                if prefetched:
-                    losses.append(lane.run_prefetched())
-                else:
-                    li = lane.loss_inputs if loss_inputs is None else loss_inputs[j]
-                    losses.append(lane(vecs[j], *li))
+                lane._pose_ready = self.batch_pose
+                try:
+                    if prefetched:
+                        losses.append(lane.run_prefetched())
+                    else:
+                        li = lane.loss_inputs if loss_inputs is None else loss_inputs[j]
+                        losses.append(lane(vecs[j], *li))
+                finally:
+                    lane._pose_ready = False
                 self._joins[j].record(s)
             if next_vecs is not None and j < len(next_vecs):
                 lane.prefetch(next_vecs[j], *(next_loss_inputs[j] if next_loss_inputs is not None else ()))
@@ -439,6 +484,11 @@ class MultiLaneRenderStep:
             self._alias_grads()
             return False
         return True
+
+
+def _pose_slices(vec):
+    """The SMPL parameters of a packed view vector as contiguous slices (inputs of SMPLDeformer.pose_views)."""
+    return {k: vec[PACK[k][0]:PACK[k][1]] for k in ("poses", "shapes", "R", "Th")}
 
 
 def _C_absent():

@@ -83,6 +83,7 @@ class SMPLDeformer:
         self.grad_sink = None
         self.vert_ids_override = None  # int32 [P]: nearest-vertex ids computed by the caller (once per multi-view batch)
         self.grad_sink_atomic = False  # True: add with atomics (several streams share the sink, MultiLaneRenderStep)
+        self.pose_override = None  # (pose buffer, vertex offsets) of the target pose computed by the caller (pose_views)
 
     # ---- pose stage --------------------------------------------------------
     def pose_buffer(self, params, correct_Rs=None):
@@ -132,6 +133,29 @@ class SMPLDeformer:
                                                off.data_ptr(), _stream()), "ghr_lbs_vertex_offsets")
         return off
 
+    def pose_views(self, t_params, views, outs):
+        """The pose stage of several views in one launch (ghr_lbs_pose_views): views = list of dicts with device tensors
+        poses [72], shapes [>=NB], R [9], Th [3] (fp32, contiguous; slices of a packed view vector are fine) and
+        optionally correct_Rs [23,3,3]; outs = list of (pose buffer [POSE_FLOATS], vertex offsets [V,3]) to fill.  The big
+        pose `t_params` is the one the offsets are taken against."""
+        assert len(views) == len(outs)
+        pose_big = self._big_pose_buffer(t_params)
+        with _lib.on_device(self.device):
+            for s0 in range(0, len(views), _lib.POSE_VIEWS_MAX):
+                chunk = list(zip(views[s0:s0 + _lib.POSE_VIEWS_MAX], outs[s0:s0 + _lib.POSE_VIEWS_MAX]))
+                arr = (_lib.PoseView * len(chunk))()
+                for a, (v, (pose_out, off_out)) in zip(arr, chunk):
+                    for k in ("poses", "shapes", "R", "Th"):
+                        t = v[k]
+                        assert t.is_cuda and t.dtype == torch.float32 and t.is_contiguous(), k
+                        setattr(a, k, t.data_ptr())
+                    cr = v.get("correct_Rs")
+                    a.correct_Rs = None if cr is None else _f32c(cr.detach()).data_ptr()
+                    assert pose_out.numel() >= _lib.POSE_FLOATS and off_out.numel() == self.V * 3
+                    a.pose_out, a.offsets_out = pose_out.data_ptr(), off_out.data_ptr()
+                check(lib().ghr_lbs_pose_views(C.byref(self._model), len(chunk), arr, pose_big.data_ptr(), _stream()),
+                      "ghr_lbs_pose_views")
+
     # ---- nearest vertex ----------------------------------------------------
     def nearest_vertex(self, t_vertices, query, out=None):
         """Exact nearest vertex index [P] int32 (the reference's knn_cuda KNN(k=1), gaussian_model.py:775)."""
@@ -176,8 +200,11 @@ class SMPLDeformer:
             side.wait_stream(cur)
             with torch.cuda.stream(side):
                 self.nearest_vertex(tv, xyz_c, out=vid)
-        pose_tgt = self.pose_buffer(params, correct_Rs)
-        off = self.vertex_offsets(pose_big, pose_tgt, params["shapes"])
+        if self.pose_override is not None:  # computed for the whole batch by pose_views (MultiLaneRenderStep)
+            pose_tgt, off = self.pose_override
+        else:
+            pose_tgt = self.pose_buffer(params, correct_Rs)
+            off = self.vertex_offsets(pose_big, pose_tgt, params["shapes"])
         if have_vid:
             pass
         elif P and side is not None:

@@ -152,3 +152,36 @@ def test_graphed_step_fused_equals_unfused(smpl_model):
     for k in L:
         grad_close(k, res[True][1][k].cpu().numpy(), res[False][1][k].cpu().numpy())
     assert res[True][2] == res[False][2] - 2, res  # two libghr kernels fewer per view
+
+
+@pytest.mark.parametrize("n_views,with_corrections", [(1, False), (3, True), (8, False), (11, True)])
+def test_batched_pose_stage_equals_the_per_view_kernels(smpl_model, n_views, with_corrections):
+    """ghr_lbs_pose_views (one launch for the views of a batch; 11 views = two launches) against ghr_lbs_pose +
+    ghr_lbs_vertex_offsets per view: pose buffers and vertex offsets bit for bit."""
+    from mygauhuman_b200 import _lib
+    from mygauhuman_b200.lbs import SMPLDeformer, batch_rodrigues
+    dev = torch.device("cuda")
+    deformer = SMPLDeformer(smpl_model, dev)
+    big = {k: v.to(dev) for k, v in S.big_pose_params().items()}
+    gen = torch.Generator().manual_seed(n_views)
+    views, want = [], []
+    for i in range(n_views):
+        pose = {k: v.to(dev).float().contiguous() for k, v in S.make_pose_params(20 + i).items()}
+        cr = None
+        if with_corrections and i % 2 == 0:
+            cr = batch_rodrigues((0.05 * torch.randn(23, 3, generator=gen)).to(dev))
+        buf = deformer.pose_buffer(pose, cr)
+        off = deformer.vertex_offsets(deformer._big_pose_buffer(big), buf, pose["shapes"])
+        want.append((buf, off))
+        views.append(dict(poses=pose["poses"].reshape(-1), shapes=pose["shapes"].reshape(-1), R=pose["R"].reshape(-1),
+                          Th=pose["Th"].reshape(-1), correct_Rs=cr))
+    outs = [(torch.full((_lib.POSE_FLOATS,), float("nan"), device=dev), torch.full((deformer.V, 3), float("nan"), device=dev))
+            for _ in range(n_views)]
+    deformer.pose_views(big, views, outs)
+    torch.cuda.synchronize()
+    segments = ((_lib.POSE_A, 288), (_lib.POSE_ROT, 216), (_lib.POSE_PF, 207), (_lib.POSE_JOINTS, 72), (_lib.POSE_RGINV, 9),
+                (_lib.POSE_RG, 9), (_lib.POSE_TH, 3), (_lib.POSE_G, 288), (_lib.POSE_ROD, 216))  # what the kernels write
+    for (gb, go), (wb, wo) in zip(outs, want):
+        for o, n in segments:
+            assert torch.equal(gb[o:o + n], wb[o:o + n]), o
+        assert torch.equal(go, wo)

@@ -98,7 +98,7 @@ def _compare_backward(tc, fw, ref, rfw, noise_only=()):
             ref_scale = float(rg["dL_dscales"].abs().max())
             assert float(ours.abs().max()) <= 1e-4 * ref_scale and float(rg[name].abs().max()) <= 1e-4 * ref_scale, name
             continue
-        _grad_close(name, _np(ours), _np(rg[name]))
+        _grad_close(name, _np(ours), _np(rg[name]), stragglers_per_million=1)
 
 
 # (P, W, H, expects the wide blend family)
