@@ -553,8 +553,8 @@ def make_optimizer(args, arm, world, bucket):
 def verify_sharded_step(arm, opt, world, rank, run_batch):
     """The fused compute+collective kernel against what it replaces, inside the run: one batch of views, then
     ShardedFusedAdam.step() on the live buffers vs NCCL all-reduce of a copy of the bucket + FusedAdam on a copy of the
-    parameters (fresh moments on both sides: this is the optimiser's first step).  Bit-exact at 2 ranks (a + b commutes),
-    1e-6 relative at 4 / 8 (NCCL's summation order differs).  Returns the worst relative difference."""
+    parameters (fresh moments on both sides: this is the optimiser's first step).  Bit-exact at 2 ranks (a + b commutes);
+    at 4 / 8 see the rule below.  Returns the report."""
     import torch.distributed as dist
     from mygauhuman_b200.optim import FusedAdam, flat_layout
     assert opt.steps == 0
@@ -572,24 +572,33 @@ def verify_sharded_step(arm, opt, world, rank, run_batch):
     opt.step()
     torch.cuda.synchronize()
     opt.check()
-    worst, exact = 0.0, True
+    # More than 2 ranks: NCCL's summation order differs from the kernel's fixed rank order, so the summed gradients
+    # differ in the last bits.  This is the optimiser's FIRST step, whose update is lr * g / (|g| + eps) = +-lr whatever
+    # the magnitude of g: an element whose gradient cancels to ~0 over the ranks can land on either sign.  The bound is
+    # therefore per element |dp| <= 2 lr of its group, and such elements must be rare; everything else must agree to
+    # 1e-6 of the step.
+    worst, exact, frac, steps_off = 0.0, True, 0.0, 0.0
     for k, t in arm.leaves.items():
         a, b = t.detach(), ref[k].detach()
         exact = exact and bool(torch.equal(a, b))
         worst = max(worst, float((a - b).abs().max() / b.abs().max().clamp_min(1e-30)))
-    w = torch.tensor([worst, 0.0 if exact else 1.0], device=summed.device, dtype=torch.float64)
+        d = (a - b).abs() / max(lr_of[k], 1e-30)          # difference in units of this group's Adam step
+        steps_off = max(steps_off, float(d.max()))
+        frac = max(frac, float((d > 1e-6).float().mean()))
+    w = torch.tensor([worst, 0.0 if exact else 1.0, frac, steps_off], device=summed.device, dtype=torch.float64)
     dist.all_reduce(w, op=dist.ReduceOp.MAX)
-    worst, exact = float(w[0]), float(w[1]) == 0.0
+    worst, exact, frac, steps_off = float(w[0]), float(w[1]) == 0.0, float(w[2]), float(w[3])
     if world == 2:
         assert exact, f"sharded step differs from all-reduce + FusedAdam at 2 ranks (worst rel {worst:.3e})"
-    assert worst <= 1e-6, f"sharded step differs from all-reduce + FusedAdam: worst rel {worst:.3e}"
+    assert steps_off <= 2.0 * (1 + 1e-5) and frac <= 1e-3, \
+        f"sharded step differs from all-reduce + FusedAdam: {steps_off:.3e} Adam steps on {frac:.3e} of a tensor"
     # replicas stay bit-identical
     mine = arm.flat_params.detach().clone()
     other = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(other, mine)
     assert all(torch.equal(o, other[0]) for o in other), "parameter replicas differ across ranks"
     return {"vs": "NCCL all-reduce + FusedAdam on copies, first optimiser step", "worst_rel": worst, "bit_exact": exact,
-            "replicas_bit_identical": True}
+            "worst_in_adam_steps": steps_off, "fraction_of_elements_over_1e-6_step": frac, "replicas_bit_identical": True}
 
 
 # ---------------------------------------------------------------------------
