@@ -434,6 +434,21 @@ int ghr_backward_deformed(const ghr_deform_params* dp, const ghr_raster_params* 
                           float* dL_drotations, float* dL_dshs, float* dL_dA_target /* [24*12]|NULL, accumulated */,
                           float* dL_dvertex_offsets /* [V*3]|NULL, accumulated */, void* stream);
 
+/*
+ * LBSOffsetDecoder (nets/mlp_delta_weight_lbs.py:5-33; called per view from gaussian_renderer/__init__.py:105): positional
+ * encoding (10 octaves, 63 values) -> Conv1d 63->128, 128->128, 128->128, [63+128]->128 (ReLU each) -> Conv1d 128->24, for
+ * every Gaussian; its output is the `lbs_offsets` input of the deform entry points.  One kernel on the tcgen05 tensor
+ * cores (TF32 operands, fp32 accumulation in TMEM -- the precision of the reference's own Conv1d layers, cuDNN allows
+ * TF32 by default), weights streamed by cp.async.bulk from a prepacked blob.
+ *   ghr_lbs_mlp_pack     weights[5] = the Conv1d weights [out,in(,1)] of bw_linears[0..3] and bw_fc ([128,63] [128,128]
+ *                        [128,128] [128,191] [24,128]), biases[5] likewise -> blob (ghr_lbs_mlp_blob_bytes(), 16-byte
+ *                        aligned).  Repack after every optimiser step that touches the network.
+ *   ghr_lbs_mlp_forward  xyz [P,3] -> logits [P,24] (row-major, 16-byte aligned: `lbs_offsets` with strides 24, 1).
+ */
+size_t ghr_lbs_mlp_blob_bytes(void);
+int ghr_lbs_mlp_pack(const float* const* weights, const float* const* biases, void* blob, void* stream);
+int ghr_lbs_mlp_forward(int32_t P, const float* xyz, const void* blob, float* logits, void* stream);
+
 /* Pose-branch backward: dL/dA_target [24,12] and dL/dvertex_offsets [V,3] (or NULL) -> dL/dcorrect_Rs
  * [23,3,3] (the only learnable input of the pose branch, nets/mlp_delta_body_pose.py).
  * dL_dcorrect_Rs must hold 23*9 + 207 floats: the tail is scratch for the pose-feature gradient. */

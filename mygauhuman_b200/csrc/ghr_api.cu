@@ -659,4 +659,23 @@ int ghr_backward_deformed(const ghr_deform_params* dp, const ghr_raster_params* 
                       s, "project_deform_backward");
 }
 
+// ---- LBS-weight offset network (ghr_mlp.cu) ---------------------------------------------------------------------------
+size_t ghr_lbs_mlp_blob_bytes(void) { return lbs_mlp_blob_bytes(); }
+
+int ghr_lbs_mlp_pack(const float* const* weights, const float* const* biases, void* blob, void* stream)
+{
+    if (!weights || !biases || !blob || misaligned(blob, 16)) return GHR_ERR_BAD_ARG;
+    for (int i = 0; i < 5; i++)
+        if (!weights[i] || !biases[i]) return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_lbs_mlp_pack(weights, biases, blob, (cudaStream_t)stream), "lbs_mlp_pack");
+}
+
+int ghr_lbs_mlp_forward(int32_t P, const float* xyz, const void* blob, float* logits, void* stream)
+{
+    if (P < 0) return GHR_ERR_BAD_ARG;
+    if (P == 0) return GHR_OK;
+    if (!xyz || !blob || !logits || misaligned(blob, 16) || misaligned(logits, 16)) return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_lbs_mlp_forward(P, xyz, blob, logits, (cudaStream_t)stream), "lbs_mlp_forward");
+}
+
 }  // extern "C"

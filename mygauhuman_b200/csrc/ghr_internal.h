@@ -199,6 +199,10 @@ cudaError_t launch_smpl_lbs_vertices(const ghr_lbs_model& m, const float* vt, co
                                      float* verts, float* T_out, cudaStream_t s);
 cudaError_t launch_lbs_deform_forward(const ghr_deform_params& p, const DeformOut& o, cudaStream_t s);
 cudaError_t launch_lbs_deform_backward(const ghr_deform_params& p, const DeformGrads& g, cudaStream_t s);
+// LBS-weight offset network on the tensor cores (ghr_mlp.cu)
+size_t lbs_mlp_blob_bytes();
+cudaError_t launch_lbs_mlp_pack(const float* const* weights, const float* const* biases, void* blob, cudaStream_t s);
+cudaError_t launch_lbs_mlp_forward(int P, const float* xyz, const void* blob, float* logits, cudaStream_t s);
 // fused LBS + projection (ghr_fused.cu)
 cudaError_t launch_deform_project(const ghr_deform_params& dp, const ghr_raster_params& p, int32_t* radii, char* geom,
                                   const ghr_layout& L, float* world_pts, float* world_normals, float* cov3D, float* colors,

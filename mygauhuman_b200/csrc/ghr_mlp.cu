@@ -1,0 +1,333 @@
+// LBS-weight offset network (reference nets/mlp_delta_weight_lbs.py:5-33 LBSOffsetDecoder, called from
+// gaussian_renderer/__init__.py:105): per Gaussian
+//     e = [x, sin(2^f x), cos(2^f x)]_{f=0..9}            63 values   (get_embedder(10), :36-83)
+//     h = relu(W0 e + b0); h = relu(W1 h + b1); h = relu(W2 h + b2); h = relu(W3 [e, h] + b3);  logits = Wf h + bf   (24)
+// as ONE kernel on the 5th-generation tensor cores: a CTA owns 128 Gaussians (the M = 128 rows of every layer),
+// `tcgen05.mma.cta_group::1.kind::tf32` (128 x N x 8 per instruction, issued by one thread) accumulates in TMEM
+// (128 lanes x 128 fp32 columns), the epilogue of a layer reads its accumulator row with `tcgen05.ld` (one thread per
+// Gaussian), adds the bias, applies ReLU and writes the next layer's A operand back to shared memory; weights arrive from
+// a prepacked blob (ghr_lbs_mlp_pack) by `cp.async.bulk` (the TMA engine's 1-D copy, completion on an mbarrier) through a
+// three-slot ring that runs one layer ahead of the tensor core.  Nothing but xyz (12 B) is read and the 24 logits (96 B)
+// written per Gaussian; the reference runs 5 cuDNN convolutions + 8 elementwise kernels with [P,128] activations in HBM.
+//
+// Arithmetic: TF32 operands (activations and weights rounded to nearest, `cvt.rna.tf32.f32`), fp32 accumulation -- what
+// the reference's own Conv1d layers use on Ampere and later (torch.backends.cudnn.allow_tf32 defaults to True).
+//
+// Shared-memory operand layout (no swizzle, K-major, `SmemDescriptor` layout_type 0): 16-byte chunks of 4 consecutive K
+// values; chunk c of row r at ((c * R + r) * 16) bytes.  Rows of an 8-row core matrix are 16 B apart, 8-row groups
+// 128 B apart (SBO), the two chunks of one K = 8 instruction R * 16 B apart (LBO).
+#include <stdio.h>
+#include "ghr_common.cuh"
+#include "ghr_internal.h"
+
+namespace ghr {
+
+namespace {
+
+constexpr int kRows = 128;            // Gaussians per CTA = UMMA M
+constexpr int kHidden = 128;
+constexpr int kEmb = 63;
+constexpr int kOutPad = 32;           // 24 logits padded to a legal UMMA N
+constexpr int kStageBytes = 32768;    // 64 K-columns x 128 rows x 4 B
+// nine weight stages: L0: 1 | L1: 2 | L2: 2 | L3: 3 | fc: 1 (16 KB)
+constexpr int kSlots = 3;
+constexpr int kBiasFloats = 4 * kHidden + kOutPad;
+constexpr size_t kBlobBytes = 8 * (size_t)kStageBytes + 16384 + sizeof(float) * kBiasFloats;
+
+constexpr uint32_t kABytes = 48 * kRows * 16;  // 48 chunks: [0,32) current activation, [32,48) embedding (+1 zero pad)
+constexpr uint32_t kSmemBytes = kABytes + kSlots * kStageBytes + sizeof(float) * kBiasFloats + 64;
+
+__host__ __device__ constexpr int stage_layer(int s) { return s == 0 ? 0 : s <= 2 ? 1 : s <= 4 ? 2 : s <= 7 ? 3 : 4; }
+__host__ __device__ constexpr int stage_first(int layer) { return layer == 0 ? 0 : layer == 1 ? 1 : layer == 2 ? 3 : layer == 3 ? 5 : 8; }
+__host__ __device__ constexpr size_t stage_offset(int s) { return (size_t)s * kStageBytes; }
+__host__ __device__ constexpr uint32_t stage_bytes(int s) { return s == 8 ? 16384u : (uint32_t)kStageBytes; }
+
+__device__ __forceinline__ float to_tf32(float x)
+{
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
+// ---- prepack: the five weight matrices -> stage blobs in the shared-memory chunk layout, TF32-rounded; biases behind ----
+struct MlpWeights {
+    const float *w0, *w1, *w2, *w3, *wf;  // [128,63] [128,128] [128,128] [128,191] [24,128]   (Conv1d weight[out,in,1])
+    const float *b0, *b1, *b2, *b3, *bf;
+};
+
+__global__ void __launch_bounds__(256) lbs_mlp_pack_kernel(const MlpWeights w, float* __restrict__ blob)
+{
+    const int total = (int)((kBlobBytes) / 4);
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+        const int wfloats = (8 * kStageBytes + 16384) / 4;
+        if (i >= wfloats) {  // biases: b0 b1 b2 b3 | bf padded with zeros
+            const int b = i - wfloats;
+            const float* src[4] = {w.b0, w.b1, w.b2, w.b3};
+            blob[i] = b < 4 * kHidden ? src[b / kHidden][b % kHidden] : (b - 4 * kHidden < 24 ? w.bf[b - 4 * kHidden] : 0.0f);
+            continue;
+        }
+        const int s = i < 8 * (kStageBytes / 4) ? i / (kStageBytes / 4) : 8;
+        const int j = i - s * (kStageBytes / 4);
+        const int layer = stage_layer(s);
+        const int R = layer == 4 ? kOutPad : kHidden;
+        const int n = (j / 4) % R;
+        const int k = (j / (4 * R)) * 4 + (j & 3) + (layer == 4 ? 0 : (s - stage_first(layer)) * 64);
+        float v = 0.0f;
+        if (layer == 0) v = k < kEmb ? w.w0[n * kEmb + k] : 0.0f;
+        else if (layer == 1) v = w.w1[n * kHidden + k];
+        else if (layer == 2) v = w.w2[n * kHidden + k];
+        else if (layer == 3) v = k < kHidden ? w.w3[n * 191 + kEmb + k] : (k < kHidden + kEmb ? w.w3[n * 191 + (k - kHidden)] : 0.0f);
+        else v = n < 24 ? w.wf[n * kHidden + k] : 0.0f;
+        blob[i] = to_tf32(v);
+    }
+}
+
+// ---- PTX wrappers ----------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_global, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_global), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+// K-major, no swizzle: LBO = distance of the two 16-byte K chunks of an instruction, SBO = distance of 8-row groups
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes)
+{
+    return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+           (1ull << 46);  // version 1 (Blackwell), base offset 0, layout type 0 = SWIZZLE_NONE
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v)
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// instruction descriptor: D fp32, A/B tf32, both K-major, M = 128, N given
+__host__ __device__ constexpr uint32_t idesc_tf32(int N) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24); }
+
+// ---- the network -----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kRows, 1) lbs_mlp_forward_kernel(int P, const float* __restrict__ xyz,
+                                                                   const unsigned char* __restrict__ blob,
+                                                                   float* __restrict__ logits)
+{
+    extern __shared__ __align__(1024) unsigned char smem[];
+    unsigned char* sA = smem;                                  // [48 chunks][128 rows] x 16 B
+    unsigned char* sB = smem + kABytes;                        // kSlots x 32 KB
+    float* sBias = reinterpret_cast<float*>(sB + kSlots * kStageBytes);
+    uint64_t* full = reinterpret_cast<uint64_t*>(sBias + kBiasFloats);  // [kSlots]
+    uint64_t* acc_bar = full + kSlots;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+
+    const int t = threadIdx.x, warp = t >> 5;
+    const int row0 = blockIdx.x * kRows;
+
+    if (t == 0) {
+        for (int i = 0; i < kSlots; i++) mbar_init(&full[i], 1);
+        mbar_init(acc_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {  // one warp allocates the accumulator: 128 lanes x 128 columns of fp32
+        __syncwarp();
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(128) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    for (int i = t; i < kBiasFloats; i += kRows) sBias[i] = reinterpret_cast<const float*>(blob + 8 * (size_t)kStageBytes + 16384)[i];
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = *tmem_slot;
+
+    // the first three weight stages are on their way while the embedding is computed
+    if (t == 0) {
+        for (int s = 0; s < kSlots; s++) {
+            mbar_expect_tx(&full[s], stage_bytes(s));
+            bulk_load(sB + s * kStageBytes, blob + stage_offset(s), stage_bytes(s), &full[s]);
+        }
+    }
+
+    // positional encoding of this thread's Gaussian -> embedding chunks [32, 48) of row t (zero row beyond P)
+    {
+        float e[64];
+        const int g = row0 + t;
+        const float x = g < P ? xyz[3 * (size_t)g] : 0.0f, y = g < P ? xyz[3 * (size_t)g + 1] : 0.0f,
+                    z = g < P ? xyz[3 * (size_t)g + 2] : 0.0f;
+        e[0] = x; e[1] = y; e[2] = z;
+        float freq = 1.0f;
+#pragma unroll
+        for (int f = 0; f < 10; f++) {
+            float s0, c0, s1, c1, s2, c2;
+            sincosf(x * freq, &s0, &c0); sincosf(y * freq, &s1, &c1); sincosf(z * freq, &s2, &c2);
+            e[3 + 6 * f] = s0; e[4 + 6 * f] = s1; e[5 + 6 * f] = s2;
+            e[6 + 6 * f] = c0; e[7 + 6 * f] = c1; e[8 + 6 * f] = c2;
+            freq *= 2.0f;
+        }
+        e[63] = 0.0f;
+        if (g >= P) {
+#pragma unroll
+            for (int k = 0; k < 64; k++) e[k] = 0.0f;
+        }
+#pragma unroll
+        for (int c = 0; c < 16; c++)
+            *reinterpret_cast<float4*>(sA + ((32 + c) * kRows + t) * 16) =
+                make_float4(to_tf32(e[4 * c]), to_tf32(e[4 * c + 1]), to_tf32(e[4 * c + 2]), to_tf32(e[4 * c + 3]));
+    }
+
+    uint32_t acc_parity = 0;
+#pragma unroll 1
+    for (int layer = 0; layer < 5; layer++) {
+        // the A operand of this layer was written with ordinary stores: make it visible to the tensor core (async proxy)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (t == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int s0 = stage_first(layer);
+            const int n_st = layer == 0 ? 1 : layer == 3 ? 3 : layer == 4 ? 1 : 2;
+            const int Rb = layer == 4 ? kOutPad : kHidden;
+            const uint32_t idesc = idesc_tf32(Rb);
+            const uint32_t a_chunk0 = layer == 0 ? 32u : 0u;
+            uint32_t first = 1;
+            for (int i = 0; i < n_st; i++) {
+                const int s = s0 + i, slot = s % kSlots;
+                mbar_wait(&full[slot], (uint32_t)((s / kSlots) & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const int ksteps = layer == 4 ? 16 : 8;  // K = 8 per instruction; the fc stage holds all of K = 128
+                const uint32_t a_base = smem_u32(sA) + (a_chunk0 + 16u * i) * kRows * 16;
+                const uint32_t b_base = smem_u32(sB) + slot * kStageBytes;
+                for (int k = 0; k < ksteps; k++) {
+                    const uint64_t ad = smem_desc(a_base + k * 2 * kRows * 16, kRows * 16, 128);
+                    const uint64_t bd = smem_desc(b_base + k * 2 * Rb * 16, Rb * 16, 128);
+                    umma_tf32(tmem, ad, bd, idesc, first ? 0u : 1u);
+                    first = 0;
+                }
+            }
+            umma_commit(acc_bar);  // arrives when every MMA above has finished (accumulator complete, smem operands read)
+        }
+        mbar_wait(acc_bar, acc_parity);
+        acc_parity ^= 1;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+        // the slots this layer read are free again: fetch the stages of the layer after next
+        if (t == 0) {
+            const int nxt_lo = layer == 0 ? 3 : layer == 1 ? 4 : layer == 2 ? 6 : layer == 3 ? 8 : 9;
+            const int nxt_hi = layer == 0 ? 4 : layer == 1 ? 6 : layer == 2 ? 8 : layer == 3 ? 9 : 9;
+            for (int s = nxt_lo; s < nxt_hi; s++) {
+                const int slot = s % kSlots;
+                mbar_expect_tx(&full[slot], stage_bytes(s));
+                bulk_load(sB + slot * kStageBytes, blob + stage_offset(s), stage_bytes(s), &full[slot]);
+            }
+        }
+
+        // epilogue: thread t owns accumulator row t (TMEM lane t; a warp may only touch its own 32 lanes)
+        const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+        if (layer < 4) {
+            const float* bias = sBias + layer * kHidden;
+#pragma unroll 1
+            for (int c0 = 0; c0 < kHidden; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(trow + c0, v);
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    float4 o;
+                    o.x = to_tf32(fmaxf(__uint_as_float(v[4 * q]) + bias[c0 + 4 * q], 0.0f));
+                    o.y = to_tf32(fmaxf(__uint_as_float(v[4 * q + 1]) + bias[c0 + 4 * q + 1], 0.0f));
+                    o.z = to_tf32(fmaxf(__uint_as_float(v[4 * q + 2]) + bias[c0 + 4 * q + 2], 0.0f));
+                    o.w = to_tf32(fmaxf(__uint_as_float(v[4 * q + 3]) + bias[c0 + 4 * q + 3], 0.0f));
+                    *reinterpret_cast<float4*>(sA + ((c0 / 4 + q) * kRows + t) * 16) = o;
+                }
+            }
+        } else {
+            uint32_t v[32];
+            tmem_ld32(trow, v);
+            const int g = row0 + t;
+            if (g < P) {
+                const float* bias = sBias + 4 * kHidden;
+                float4* out = reinterpret_cast<float4*>(logits + 24 * (size_t)g);
+#pragma unroll
+                for (int q = 0; q < 6; q++)
+                    out[q] = make_float4(__uint_as_float(v[4 * q]) + bias[4 * q], __uint_as_float(v[4 * q + 1]) + bias[4 * q + 1],
+                                         __uint_as_float(v[4 * q + 2]) + bias[4 * q + 2], __uint_as_float(v[4 * q + 3]) + bias[4 * q + 3]);
+            }
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        __syncwarp();
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(128) : "memory");
+    }
+}
+
+}  // namespace
+
+size_t lbs_mlp_blob_bytes() { return kBlobBytes; }
+
+cudaError_t launch_lbs_mlp_pack(const float* const* weights, const float* const* biases, void* blob, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_MISC, s);
+    count_launch();
+    MlpWeights w{weights[0], weights[1], weights[2], weights[3], weights[4], biases[0], biases[1], biases[2], biases[3], biases[4]};
+    lbs_mlp_pack_kernel<<<64, 256, 0, s>>>(w, reinterpret_cast<float*>(blob));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lbs_mlp_forward(int P, const float* xyz, const void* blob, float* logits, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_MISC, s);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(lbs_mlp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    count_launch();
+    lbs_mlp_forward_kernel<<<(P + kRows - 1) / kRows, kRows, kSmemBytes, s>>>(P, xyz, reinterpret_cast<const unsigned char*>(blob), logits);
+    return cudaGetLastError();
+}
+
+}  // namespace ghr
