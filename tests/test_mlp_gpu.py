@@ -68,7 +68,8 @@ def test_matches_fp64_truth_within_tf32_and_the_reference_default_precision(P):
     print(f"P={P}: ours {err:.3e}, reference default precision {err_ref:.3e}, scale {scale:.3f}")
     assert torch.isfinite(out).all()
     assert err <= REL * scale
-    assert err <= 4.0 * err_ref + 2e-4 * scale
+    if P >= 127:  # (a single point does not take cuDNN's TF32 path: torch computes it in plain fp32, error 2e-7)
+        assert err <= 2.0 * err_ref + 2e-4 * scale
 
 
 def test_repacks_when_the_parameters_change_and_backward_matches_torch():
