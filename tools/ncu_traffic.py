@@ -9,7 +9,8 @@ bench.py divides by the measured stage time for the issue-bound roofline).
 """
 import csv, json, sys
 
-STAGE_OF = {"preprocess_kernel": "preprocess", "emit_keys_kernel": "emit_keys", "sort_histogram_kernel": "sort",
+STAGE_OF = {"blend_forward_wide_kernel": "blend_fwd_wide", "blend_backward_wide_kernel": "blend_bwd_wide",
+            "lbs_mlp_forward_kernel": "lbs_mlp", "preprocess_kernel": "preprocess", "emit_keys_kernel": "emit_keys", "sort_histogram_kernel": "sort",
             "onesweep_pass_kernel": "sort", "tile_ranges_kernel": "tile_ranges", "tile_order_kernel": "tile_ranges",
             "blend_forward_kernel": "blend_fwd", "blend_backward_kernel": "blend_bwd",
             "preprocess_backward_kernel": "preprocess_bwd", "lbs_deform_forward_kernel": "lbs_fwd",
@@ -31,12 +32,17 @@ def main(raw, out_csv, out_json, issue_json=None, workload="zju_512"):
     per_stage, seen, inst = {}, {}, {}
     with open(out_csv, "w", newline="") as f:
         w = csv.writer(f)
-        w.writerow(["kernel", "stage"] + [f"{c} [{units[h.index(c)]}]" for c in cols])
+        stall_cols = [c for c in h if c.startswith("smsp__average_warps_issue_stalled_") and "selected" not in c]
+        w.writerow(["kernel", "stage"] + [f"{c} [{units[h.index(c)]}]" for c in cols] +
+                   ["top stalls (warps stalled per issued instruction)"])
         for r in rows[2:]:
             name = r[kn]
             base = name.split("(")[0].replace("void ", "").split("<")[0].split("::")[-1].strip()
             stage = STAGE_OF.get(base, "")
-            w.writerow([name[:70], stage] + [r[h.index(c)] for c in cols])
+            stalls = sorted(((float(r[h.index(c)].replace(",", "") or 0), c[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")])
+                             for c in stall_cols), reverse=True)[:3]
+            w.writerow([name[:70], stage] + [r[h.index(c)] for c in cols] +
+                       ["; ".join(f"{n} {v:.2f}" for v, n in stalls)])
             if stage:
                 rd = float(r[h.index("dram__bytes_read.sum")].replace(",", "")) * UNIT[units[h.index("dram__bytes_read.sum")]]
                 wr = float(r[h.index("dram__bytes_write.sum")].replace(",", "")) * UNIT[units[h.index("dram__bytes_write.sum")]]
