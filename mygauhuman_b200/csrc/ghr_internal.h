@@ -103,6 +103,17 @@ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 // Streaming multiprocessors of the CURRENT device (148 on B200), queried once per device and cached (ghr_profile.cu):
 // every persistent / grid-capped launch sizes itself as a multiple of this.
 int sm_count();
+// true the first time it is called for `mask` with the current device current: per-DEVICE one-time set-up (function
+// attributes such as the dynamic shared-memory limit belong to the device's context, not to the process)
+inline bool first_use_on_current_device(unsigned long long& mask)
+{
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess) return true;
+    const unsigned long long bit = 1ull << (d & 63);
+    if (mask & bit) return false;
+    mask |= bit;
+    return true;
+}
 
 // rasterizer_impl.cu:35-50 getHigherMsb
 inline uint32_t higher_msb(uint32_t n)

@@ -500,12 +500,11 @@ cudaError_t launch_nearest_vertex(int P, const float* query, int V, const char* 
     const float4* sorted = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(starts) + align_up(sizeof(uint32_t) * ((size_t)kMaxCells + 1)));
     count_launch();
     if (vertex_grid_fits_smem(V)) {
-        static bool attr_set = false;
+        static unsigned long long attr_set = 0ull;
         const size_t smem = vertex_grid_smem_bytes(V);
-        if (!attr_set) {
+        if (first_use_on_current_device(attr_set)) {
             cudaError_t e = cudaFuncSetAttribute(nearest_vertex_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e != cudaSuccess) return e;
-            attr_set = true;
         }
         const int need = (P + 127) / 128;  // 128 eight-lane groups per 1024-thread block
         const int blocks = need < sm_count() ? need : sm_count();

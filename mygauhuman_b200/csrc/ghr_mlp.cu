@@ -319,11 +319,10 @@ cudaError_t launch_lbs_mlp_pack(const float* const* weights, const float* const*
 cudaError_t launch_lbs_mlp_forward(int P, const float* xyz, const void* blob, float* logits, cudaStream_t s)
 {
     StageTimer timer(GHR_STAGE_MISC, s);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0ull;
+    if (first_use_on_current_device(attr_set)) {
         cudaError_t e = cudaFuncSetAttribute(lbs_mlp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     count_launch();
     lbs_mlp_forward_kernel<<<(P + kRows - 1) / kRows, kRows, kSmemBytes, s>>>(P, xyz, reinterpret_cast<const unsigned char*>(blob), logits);
