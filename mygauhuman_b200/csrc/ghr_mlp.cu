@@ -25,6 +25,7 @@ namespace ghr {
 namespace {
 
 constexpr int kRows = 128;            // Gaussians per CTA = UMMA M
+constexpr int kThreads = 256;         // two threads per Gaussian: each takes half of the encoding and half of an accumulator row
 constexpr int kHidden = 128;
 constexpr int kEmb = 63;
 constexpr int kOutPad = 32;           // 24 logits padded to a legal UMMA N
@@ -142,14 +143,33 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v)
           "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
           "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
         : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v)
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // instruction descriptor: D fp32, A/B tf32, both K-major, M = 128, N given
 __host__ __device__ constexpr uint32_t idesc_tf32(int N) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24); }
 
+#ifdef GHR_MLP_TRACE  // tuning builds only (tools/build_variant.sh): phase timestamps of block 0, printed by its thread 0
+#define MLP_T(i) do { if (blockIdx.x == 0 && t == 0) tr[i] = clock64(); } while (0)
+#else
+#define MLP_T(i) do { } while (0)
+#endif
+
 // ---- the network -----------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kRows, 1) lbs_mlp_forward_kernel(int P, const float* __restrict__ xyz,
+// round to TF32 (nearest, ties away: what cvt.rna.tf32.f32 does) with two integer instructions: the conversion
+// instruction runs at a quarter of the ALU rate and a layer's epilogue needs 128 of them per thread
+__device__ __forceinline__ float tf32_rn(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
+
+__global__ void __launch_bounds__(kThreads, 1) lbs_mlp_forward_kernel(int P, int n_tiles, const float* __restrict__ xyz,
                                                                    const unsigned char* __restrict__ blob,
                                                                    float* __restrict__ logits)
 {
@@ -162,7 +182,11 @@ __global__ void __launch_bounds__(kRows, 1) lbs_mlp_forward_kernel(int P, const 
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
 
     const int t = threadIdx.x, warp = t >> 5;
-    const int row0 = blockIdx.x * kRows;
+    const int row = t & (kRows - 1), half = t >> 7;  // warp w may touch TMEM lanes 32 (w % 4) ..: exactly its rows
+#ifdef GHR_MLP_TRACE
+    long long tr[24];
+#endif
+    MLP_T(0);
 
     if (t == 0) {
         for (int i = 0; i < kSlots; i++) mbar_init(&full[i], 1);
@@ -174,124 +198,164 @@ __global__ void __launch_bounds__(kRows, 1) lbs_mlp_forward_kernel(int P, const 
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(128) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    for (int i = t; i < kBiasFloats; i += kRows) sBias[i] = reinterpret_cast<const float*>(blob + 8 * (size_t)kStageBytes + 16384)[i];
+    for (int i = t; i < kBiasFloats; i += kThreads) sBias[i] = reinterpret_cast<const float*>(blob + 8 * (size_t)kStageBytes + 16384)[i];
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
+    MLP_T(1);
 
-    // the first three weight stages are on their way while the embedding is computed
-    if (t == 0) {
-        for (int s = 0; s < kSlots; s++) {
-            mbar_expect_tx(&full[s], stage_bytes(s));
-            bulk_load(sB + s * kStageBytes, blob + stage_offset(s), stage_bytes(s), &full[s]);
-        }
-    }
-
-    // positional encoding of this thread's Gaussian -> embedding chunks [32, 48) of row t (zero row beyond P)
-    {
-        float e[64];
-        const int g = row0 + t;
-        const float x = g < P ? xyz[3 * (size_t)g] : 0.0f, y = g < P ? xyz[3 * (size_t)g + 1] : 0.0f,
-                    z = g < P ? xyz[3 * (size_t)g + 2] : 0.0f;
-        e[0] = x; e[1] = y; e[2] = z;
-        float freq = 1.0f;
-#pragma unroll
-        for (int f = 0; f < 10; f++) {
-            float s0, c0, s1, c1, s2, c2;
-            sincosf(x * freq, &s0, &c0); sincosf(y * freq, &s1, &c1); sincosf(z * freq, &s2, &c2);
-            e[3 + 6 * f] = s0; e[4 + 6 * f] = s1; e[5 + 6 * f] = s2;
-            e[6 + 6 * f] = c0; e[7 + 6 * f] = c1; e[8 + 6 * f] = c2;
-            freq *= 2.0f;
-        }
-        e[63] = 0.0f;
-        if (g >= P) {
-#pragma unroll
-            for (int k = 0; k < 64; k++) e[k] = 0.0f;
-        }
-#pragma unroll
-        for (int c = 0; c < 16; c++)
-            *reinterpret_cast<float4*>(sA + ((32 + c) * kRows + t) * 16) =
-                make_float4(to_tf32(e[4 * c]), to_tf32(e[4 * c + 1]), to_tf32(e[4 * c + 2]), to_tf32(e[4 * c + 3]));
-    }
+    // thread 0 is the weight producer and the MMA issuer.  Stage s of a tile lives in ring slot s % 3; every slot is
+    // filled three times per tile, so the parity a wait needs is the number of fills already consumed from that slot.
+    uint32_t consumed[kSlots] = {0u, 0u, 0u};
+    auto fetch = [&](int s) {
+        const int slot = s % kSlots;
+        mbar_expect_tx(&full[slot], stage_bytes(s));
+        bulk_load(sB + slot * kStageBytes, blob + stage_offset(s), stage_bytes(s), &full[slot]);
+    };
+    if (t == 0)
+        for (int s = 0; s < kSlots; s++) fetch(s);  // on their way while the first encoding is computed
 
     uint32_t acc_parity = 0;
 #pragma unroll 1
-    for (int layer = 0; layer < 5; layer++) {
-        // the A operand of this layer was written with ordinary stores: make it visible to the tensor core (async proxy)
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();
-        if (t == 0) {
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const int s0 = stage_first(layer);
-            const int n_st = layer == 0 ? 1 : layer == 3 ? 3 : layer == 4 ? 1 : 2;
-            const int Rb = layer == 4 ? kOutPad : kHidden;
-            const uint32_t idesc = idesc_tf32(Rb);
-            const uint32_t a_chunk0 = layer == 0 ? 32u : 0u;
-            uint32_t first = 1;
-            for (int i = 0; i < n_st; i++) {
-                const int s = s0 + i, slot = s % kSlots;
-                mbar_wait(&full[slot], (uint32_t)((s / kSlots) & 1));
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const int ksteps = layer == 4 ? 16 : 8;  // K = 8 per instruction; the fc stage holds all of K = 128
-                const uint32_t a_base = smem_u32(sA) + (a_chunk0 + 16u * i) * kRows * 16;
-                const uint32_t b_base = smem_u32(sB) + slot * kStageBytes;
-                for (int k = 0; k < ksteps; k++) {
-                    const uint64_t ad = smem_desc(a_base + k * 2 * kRows * 16, kRows * 16, 128);
-                    const uint64_t bd = smem_desc(b_base + k * 2 * Rb * 16, Rb * 16, 128);
-                    umma_tf32(tmem, ad, bd, idesc, first ? 0u : 1u);
-                    first = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int row0 = tile * kRows;
+        const bool more = tile + (int)gridDim.x < n_tiles;
+
+        // positional encoding of this thread's Gaussian -> chunks [32, 48) of row t (zero row beyond P).  sin / cos of
+        // 2^0 x and 2^5 x are library calls; the four octaves after each follow by angle doubling (sin 2a = 2 sin a cos a,
+        // cos 2a = 1 - 2 sin^2 a): the error grows by <= 2.9x per octave, <= 4e-6 after four -- 1/60 of the TF32 rounding
+        // the value receives next -- for a fifth of the 30 sincosf calls (3 us of a 14 us tile).
+        {
+            const int g = row0 + row;
+            const bool live = g < P;
+            float* erow = reinterpret_cast<float*>(sA + (32 * kRows + row) * 16);  // value k at erow[(k / 4) * kRows * 4 + k % 4]
+            auto put = [&](int k, float v) { erow[(k >> 2) * (kRows * 4) + (k & 3)] = tf32_rn(live ? v : 0.0f); };
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                const float pc = live ? xyz[3 * (size_t)g + c] : 0.0f;
+                if (half == 0) put(c, pc);
+                float sn, cs;
+                sincosf(pc * (half ? 32.0f : 1.0f), &sn, &cs);  // half 0: octaves 0..4, half 1: octaves 5..9
+#pragma unroll
+                for (int f = 0; f < 5; f++) {
+                    const int oct = 5 * half + f;
+                    put(3 + 6 * oct + c, sn);
+                    put(6 + 6 * oct + c, cs);
+                    const float s2 = 2.0f * sn * cs, c2 = fmaf(-2.0f * sn, sn, 1.0f);
+                    sn = s2; cs = c2;
                 }
             }
-            umma_commit(acc_bar);  // arrives when every MMA above has finished (accumulator complete, smem operands read)
+            if (half) put(63, 0.0f);
         }
-        mbar_wait(acc_bar, acc_parity);
-        acc_parity ^= 1;
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        MLP_T(2);
 
-        // the slots this layer read are free again: fetch the stages of the layer after next
-        if (t == 0) {
-            const int nxt_lo = layer == 0 ? 3 : layer == 1 ? 4 : layer == 2 ? 6 : layer == 3 ? 8 : 9;
-            const int nxt_hi = layer == 0 ? 4 : layer == 1 ? 6 : layer == 2 ? 8 : layer == 3 ? 9 : 9;
-            for (int s = nxt_lo; s < nxt_hi; s++) {
-                const int slot = s % kSlots;
-                mbar_expect_tx(&full[slot], stage_bytes(s));
-                bulk_load(sB + slot * kStageBytes, blob + stage_offset(s), stage_bytes(s), &full[slot]);
-            }
-        }
-
-        // epilogue: thread t owns accumulator row t (TMEM lane t; a warp may only touch its own 32 lanes)
-        const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
-        if (layer < 4) {
-            const float* bias = sBias + layer * kHidden;
+#ifdef GHR_MLP_TRACE
+#pragma unroll
+#else
 #pragma unroll 1
-            for (int c0 = 0; c0 < kHidden; c0 += 32) {
-                uint32_t v[32];
-                tmem_ld32(trow + c0, v);
+#endif
+        for (int layer = 0; layer < 5; layer++) {
+            // the A operand of this layer was written with ordinary stores: make it visible to the tensor core (async
+            // proxy); the previous accumulator has been read (tcgen05.wait::ld in the epilogue)
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncthreads();
+            if (t == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const int s0 = stage_first(layer);
+                const int n_st = layer == 0 ? 1 : layer == 3 ? 3 : layer == 4 ? 1 : 2;
+                const int Rb = layer == 4 ? kOutPad : kHidden;
+                const uint32_t idesc = idesc_tf32(Rb);
+                const uint32_t a_chunk0 = layer == 0 ? 32u : 0u;
+                uint32_t first = 1;
+                for (int i = 0; i < n_st; i++) {
+                    const int slot = (s0 + i) % kSlots;
+                    mbar_wait(&full[slot], consumed[slot] & 1u);
+                    consumed[slot]++;
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const int ksteps = layer == 4 ? 16 : 8;  // K = 8 per instruction; the fc stage holds all of K = 128
+                    const uint32_t a_base = smem_u32(sA) + (a_chunk0 + 16u * i) * kRows * 16;
+                    const uint32_t b_base = smem_u32(sB) + slot * kStageBytes;
+                    for (int k = 0; k < ksteps; k++) {
+                        const uint64_t ad = smem_desc(a_base + k * 2 * kRows * 16, kRows * 16, 128);
+                        const uint64_t bd = smem_desc(b_base + k * 2 * Rb * 16, Rb * 16, 128);
+                        umma_tf32(tmem, ad, bd, idesc, first ? 0u : 1u);
+                        first = 0;
+                    }
+                }
+                umma_commit(acc_bar);  // arrives when every MMA above has finished (accumulator complete, operands read)
+            }
+            MLP_T(3 + 3 * layer);
+            mbar_wait(acc_bar, acc_parity);
+            acc_parity ^= 1;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            MLP_T(4 + 3 * layer);
+
+            // the slots this layer read are free again: fetch the stages of the layer after next (after the last two
+            // layers: the first stages of this CTA's next tile)
+            if (t == 0) {
+                if (layer == 0) fetch(3);
+                else if (layer == 1) { fetch(4); fetch(5); }
+                else if (layer == 2) { fetch(6); fetch(7); }
+                else if (layer == 3) { fetch(8); if (more) { fetch(0); fetch(1); } }
+                else if (more) fetch(2);
+            }
+
+            // epilogue: thread t owns accumulator row t (TMEM lane t; a warp may only touch its own 32 lanes)
+            const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+            if (layer < 4) {
+                const float4* bias4 = reinterpret_cast<const float4*>(sBias + layer * kHidden);
+                // this thread's half of the row: both 32-column loads are in flight before the first value is used
+                uint32_t v[64];
+                tmem_ld32(trow + 64 * half, v);
+                tmem_ld32(trow + 64 * half + 32, v + 32);
+                tmem_ld_wait();
 #pragma unroll
-                for (int q = 0; q < 8; q++) {
+                for (int q = 0; q < 16; q++) {
+                    const float4 bq = bias4[16 * half + q];
                     float4 o;
-                    o.x = to_tf32(fmaxf(__uint_as_float(v[4 * q]) + bias[c0 + 4 * q], 0.0f));
-                    o.y = to_tf32(fmaxf(__uint_as_float(v[4 * q + 1]) + bias[c0 + 4 * q + 1], 0.0f));
-                    o.z = to_tf32(fmaxf(__uint_as_float(v[4 * q + 2]) + bias[c0 + 4 * q + 2], 0.0f));
-                    o.w = to_tf32(fmaxf(__uint_as_float(v[4 * q + 3]) + bias[c0 + 4 * q + 3], 0.0f));
-                    *reinterpret_cast<float4*>(sA + ((c0 / 4 + q) * kRows + t) * 16) = o;
+                    o.x = tf32_rn(fmaxf(__uint_as_float(v[4 * q]) + bq.x, 0.0f));
+                    o.y = tf32_rn(fmaxf(__uint_as_float(v[4 * q + 1]) + bq.y, 0.0f));
+                    o.z = tf32_rn(fmaxf(__uint_as_float(v[4 * q + 2]) + bq.z, 0.0f));
+                    o.w = tf32_rn(fmaxf(__uint_as_float(v[4 * q + 3]) + bq.w, 0.0f));
+                    *reinterpret_cast<float4*>(sA + ((16 * half + q) * kRows + row) * 16) = o;
+                }
+                MLP_T(5 + 3 * layer);
+            } else {
+                uint32_t v[16];
+                tmem_ld16(trow + 16 * half, v);  // 24 logits: columns [0,16) here, [16,24) in the other half
+                tmem_ld_wait();
+                const int g = row0 + row;
+                if (g < P) {
+                    const float4* bias4 = reinterpret_cast<const float4*>(sBias + 4 * kHidden) + 4 * half;
+                    float4* out = reinterpret_cast<float4*>(logits + 24 * (size_t)g) + 4 * half;
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        if (4 * half + q >= 6) break;
+                        const float4 bq = bias4[q];
+                        out[q] = make_float4(__uint_as_float(v[4 * q]) + bq.x, __uint_as_float(v[4 * q + 1]) + bq.y,
+                                             __uint_as_float(v[4 * q + 2]) + bq.z, __uint_as_float(v[4 * q + 3]) + bq.w);
+                    }
                 }
             }
-        } else {
-            uint32_t v[32];
-            tmem_ld32(trow, v);
-            const int g = row0 + t;
-            if (g < P) {
-                const float* bias = sBias + 4 * kHidden;
-                float4* out = reinterpret_cast<float4*>(logits + 24 * (size_t)g);
-#pragma unroll
-                for (int q = 0; q < 6; q++)
-                    out[q] = make_float4(__uint_as_float(v[4 * q]) + bias[4 * q], __uint_as_float(v[4 * q + 1]) + bias[4 * q + 1],
-                                         __uint_as_float(v[4 * q + 2]) + bias[4 * q + 2], __uint_as_float(v[4 * q + 3]) + bias[4 * q + 3]);
-            }
         }
+        MLP_T(18);
+#ifdef GHR_MLP_TRACE
+        if (blockIdx.x == 0 && t == 0) {
+            printf("mlp trace (cycles): setup %lld, embed %lld", tr[1] - tr[0], tr[2] - tr[1]);
+            long long prev = tr[2];
+            for (int l = 0; l < 5; l++) {
+                printf(" | L%d issue %lld mma-wait %lld", l, tr[3 + 3 * l] - prev, tr[4 + 3 * l] - tr[3 + 3 * l]);
+                prev = tr[4 + 3 * l];
+                const long long end = l < 4 ? tr[5 + 3 * l] : tr[18];
+                printf(" epi %lld", end - prev);
+                prev = end;
+            }
+            printf(" | total %lld\n", tr[18] - tr[0]);
+            tr[1] = tr[18];
+        }
+#endif
     }
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -325,7 +389,9 @@ cudaError_t launch_lbs_mlp_forward(int P, const float* xyz, const void* blob, fl
         if (e != cudaSuccess) return e;
     }
     count_launch();
-    lbs_mlp_forward_kernel<<<(P + kRows - 1) / kRows, kRows, kSmemBytes, s>>>(P, xyz, reinterpret_cast<const unsigned char*>(blob), logits);
+    const int n_tiles = (P + kRows - 1) / kRows;
+    const int ctas = n_tiles < sm_count() ? n_tiles : sm_count();  // persistent: one CTA per SM walks the tiles
+    lbs_mlp_forward_kernel<<<ctas, kThreads, kSmemBytes, s>>>(P, n_tiles, xyz, reinterpret_cast<const unsigned char*>(blob), logits);
     return cudaGetLastError();
 }
 
