@@ -434,6 +434,16 @@ int ghr_backward_deformed(const ghr_deform_params* dp, const ghr_raster_params* 
                           float* dL_drotations, float* dL_dshs, float* dL_dA_target /* [24*12]|NULL, accumulated */,
                           float* dL_dvertex_offsets /* [V*3]|NULL, accumulated */, void* stream);
 
+/* BodyPoseRefiner (nets/mlp_delta_body_pose.py:5-41 + RodriguesModule :164-193; called per view from
+ * gaussian_renderer/__init__.py:100-102): Linear(69, width) ReLU [Linear(width, width) ReLU]* Linear(width, 69) on the 69
+ * pose values of a view, then Rodrigues with theta = sqrt(1e-5 + |r|^2) -> correct_Rs [23,3,3] (the `correct_Rs` input of
+ * ghr_lbs_pose / ghr_lbs_pose_views).  n_layers = number of Linear layers (2..GHR_REFINER_MAX_LAYERS), weights[i]
+ * row-major [out,in], fp32 throughout.  One launch. */
+#define GHR_REFINER_MAX_LAYERS 6
+#define GHR_REFINER_MAX_WIDTH 256
+int ghr_pose_refiner_forward(int32_t width, int32_t n_layers, const float* const* weights, const float* const* biases,
+                             const float* pose69, float* correct_Rs, void* stream);
+
 /*
  * LBSOffsetDecoder (nets/mlp_delta_weight_lbs.py:5-33; called per view from gaussian_renderer/__init__.py:105): positional
  * encoding (10 octaves, 63 values) -> Conv1d 63->128, 128->128, 128->128, [63+128]->128 (ReLU each) -> Conv1d 128->24, for

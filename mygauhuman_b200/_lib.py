@@ -130,6 +130,8 @@ SIGNATURES = {
     "ghr_lbs_deform_forward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 10),
     "ghr_lbs_deform_backward": (C.c_int, [C.POINTER(DeformParams)] + [C.c_void_p] * 15),
     "ghr_lbs_pose_backward": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
+    "ghr_pose_refiner_forward": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p,
+                                           C.c_void_p, C.c_void_p]),
     "ghr_lbs_mlp_blob_bytes": (C.c_size_t, []),
     "ghr_lbs_mlp_pack": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p]),
     "ghr_lbs_mlp_forward": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

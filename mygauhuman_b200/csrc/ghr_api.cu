@@ -678,4 +678,16 @@ int ghr_lbs_mlp_forward(int32_t P, const float* xyz, const void* blob, float* lo
     return check_cuda(launch_lbs_mlp_forward(P, xyz, blob, logits, (cudaStream_t)stream), "lbs_mlp_forward");
 }
 
+int ghr_pose_refiner_forward(int32_t width, int32_t n_layers, const float* const* weights, const float* const* biases,
+                             const float* pose69, float* correct_Rs, void* stream)
+{
+    if (width < 1 || width > GHR_REFINER_MAX_WIDTH || n_layers < 2 || n_layers > GHR_REFINER_MAX_LAYERS || !weights ||
+        !biases || !pose69 || !correct_Rs)
+        return GHR_ERR_BAD_ARG;
+    for (int i = 0; i < n_layers; i++)
+        if (!weights[i] || !biases[i]) return GHR_ERR_BAD_ARG;
+    return check_cuda(launch_pose_refiner(width, n_layers, weights, biases, pose69, correct_Rs, (cudaStream_t)stream),
+                      "pose_refiner");
+}
+
 }  // extern "C"

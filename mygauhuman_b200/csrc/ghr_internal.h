@@ -210,6 +210,8 @@ cudaError_t launch_smpl_lbs_vertices(const ghr_lbs_model& m, const float* vt, co
                                      float* verts, float* T_out, cudaStream_t s);
 cudaError_t launch_lbs_deform_forward(const ghr_deform_params& p, const DeformOut& o, cudaStream_t s);
 cudaError_t launch_lbs_deform_backward(const ghr_deform_params& p, const DeformGrads& g, cudaStream_t s);
+cudaError_t launch_pose_refiner(int width, int n_layers, const float* const* w, const float* const* b, const float* pose,
+                                float* Rs, cudaStream_t s);
 // LBS-weight offset network on the tensor cores (ghr_mlp.cu)
 size_t lbs_mlp_blob_bytes();
 cudaError_t launch_lbs_mlp_pack(const float* const* weights, const float* const* biases, void* blob, cudaStream_t s);

@@ -445,3 +445,69 @@ cudaError_t launch_smpl_lbs_vertices(const ghr_lbs_model& m, const float* vt, co
 }
 
 }  // namespace ghr
+
+// ---------------------------------------------------------------------------
+// BodyPoseRefiner (reference nets/mlp_delta_body_pose.py:5-41,164-193): Linear(69, W) ReLU [Linear(W, W) ReLU]* Linear(W, 69)
+// on ONE pose vector per view, then the module's own Rodrigues (theta = sqrt(1e-5 + |r|^2)) -> correct_Rs [23,3,3].
+// ~35 kFLOP: the reference spends eight launches on it; here it is one block -- a warp per output row, lanes striding the
+// input (coalesced weight reads), shuffle reduction -- so the whole pose stage of a view stays a couple of launches.
+// ---------------------------------------------------------------------------
+namespace ghr {
+
+struct RefinerArgs {
+    int width, n_layers;              // n_layers linear layers in all (>= 2)
+    const float* w[GHR_REFINER_MAX_LAYERS];
+    const float* b[GHR_REFINER_MAX_LAYERS];
+    const float* pose;                // [69]
+    float* Rs;                        // [23*9]
+};
+
+__global__ void __launch_bounds__(256) pose_refiner_kernel(const RefinerArgs a)
+{
+    __shared__ float s_x[2][GHR_REFINER_MAX_WIDTH];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t < 69) s_x[0][t] = a.pose[t];
+    __syncthreads();
+    int cur = 0, n_in = 69;
+    for (int l = 0; l < a.n_layers; l++) {
+        const int n_out = l == a.n_layers - 1 ? 69 : a.width;
+        const float* W = a.w[l];
+        for (int r = warp; r < n_out; r += 8) {
+            float acc = 0.0f;
+            for (int k = lane; k < n_in; k += 32) acc = fmaf(W[(size_t)r * n_in + k], s_x[cur][k], acc);
+#pragma unroll
+            for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0) {
+                acc += a.b[l][r];
+                s_x[cur ^ 1][r] = l == a.n_layers - 1 ? acc : fmaxf(acc, 0.0f);
+            }
+        }
+        __syncthreads();
+        cur ^= 1;
+        n_in = n_out;
+    }
+    if (t < 23) {
+        const float rx = s_x[cur][3 * t], ry = s_x[cur][3 * t + 1], rz = s_x[cur][3 * t + 2];
+        const float theta = sqrtf(1e-5f + rx * rx + ry * ry + rz * rz);
+        const float x = rx / theta, y = ry / theta, z = rz / theta;
+        const float c = cosf(theta), s = sinf(theta);
+        float* R = a.Rs + 9 * t;
+        R[0] = x * x + (1.f - x * x) * c; R[1] = x * y * (1.f - c) - z * s; R[2] = x * z * (1.f - c) + y * s;
+        R[3] = x * y * (1.f - c) + z * s; R[4] = y * y + (1.f - y * y) * c; R[5] = y * z * (1.f - c) - x * s;
+        R[6] = x * z * (1.f - c) - y * s; R[7] = y * z * (1.f - c) + x * s; R[8] = z * z + (1.f - z * z) * c;
+    }
+}
+
+cudaError_t launch_pose_refiner(int width, int n_layers, const float* const* w, const float* const* b, const float* pose,
+                                float* Rs, cudaStream_t s)
+{
+    StageTimer timer(GHR_STAGE_LBS_JOINTS, s);
+    count_launch();
+    RefinerArgs a;
+    a.width = width; a.n_layers = n_layers; a.pose = pose; a.Rs = Rs;
+    for (int i = 0; i < GHR_REFINER_MAX_LAYERS; i++) { a.w[i] = i < n_layers ? w[i] : nullptr; a.b[i] = i < n_layers ? b[i] : nullptr; }
+    pose_refiner_kernel<<<1, 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace ghr

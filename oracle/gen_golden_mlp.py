@@ -35,5 +35,28 @@ def main():
     print(path, out.shape, float(out.abs().max()), float(out.std()))
 
 
+
+
+def main_refiner():
+    """The same for BodyPoseRefiner (nets/mlp_delta_body_pose.py) in the configuration scene/gaussian_model.py:94-98 builds
+    (width 128, depth 2), last layer scaled up so that the corrections are not ~identity.  Writes tests/golden/pose_refiner.npz."""
+    ns = ref_py.load()
+    torch.manual_seed(21)
+    net = ns.nets_pose.BodyPoseRefiner(total_bones=24, embedding_size=69, mlp_width=128, mlp_depth=2)
+    with torch.no_grad():
+        net.block_mlps[-1].weight.mul_(2e4)
+        net.block_mlps[-1].bias.uniform_(-0.1, 0.1)
+    pose = torch.randn(1, 69, generator=torch.Generator().manual_seed(22)) * 0.4
+    with torch.no_grad():
+        Rs = net(pose)["Rs"]
+    data = {"pose": pose.numpy(), "Rs": Rs.numpy()}
+    for k, v in net.state_dict().items():
+        data["param." + k] = v.numpy()
+    path = os.path.join(ROOT, "tests", "golden", "pose_refiner.npz")
+    np.savez_compressed(path, **data)
+    print(path, Rs.shape, float((Rs - torch.eye(3)).abs().max()))
+
+
 if __name__ == "__main__":
     main()
+    main_refiner()

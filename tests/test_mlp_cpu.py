@@ -32,3 +32,19 @@ def test_forward_refuses_cpu_tensors():
     from mygauhuman_b200.nets import LBSOffsetDecoder
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         LBSOffsetDecoder()(torch.zeros(1, 4, 3))
+
+
+def test_pose_refiner_mirror_matches_the_reference_golden():
+    from mygauhuman_b200.nets import BodyPoseRefiner
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "pose_refiner.npz"))
+    m = BodyPoseRefiner(mlp_width=128, mlp_depth=2)
+    want_keys = {k[6:] for k in g.files if k.startswith("param.")}
+    assert set(m.state_dict().keys()) == want_keys
+    # the reference's initialisation: corrections start at (almost) the identity
+    with torch.no_grad():
+        Rs0 = m.torch_forward(torch.from_numpy(g["pose"]))
+    assert float((Rs0 - torch.eye(3)).abs().max()) < 5e-3
+    m.load_state_dict({k: torch.from_numpy(g["param." + k]) for k in want_keys})
+    with torch.no_grad():
+        Rs = m.torch_forward(torch.from_numpy(g["pose"]))
+    assert float((Rs - torch.from_numpy(g["Rs"])).abs().max()) <= 1e-6

@@ -117,3 +117,37 @@ def test_logits_drive_the_deformation(smpl_model):
     d = float((a["means3D"] - b["means3D"]).abs().max())
     print(f"world points move by {d:.3e} m under the TF32 logits")
     assert d <= 2e-3
+
+
+def test_body_pose_refiner_matches_the_reference_golden_and_feeds_the_pose_stage(smpl_model):
+    """BodyPoseRefiner (nets/mlp_delta_body_pose.py) as one kernel: fp32 throughout, so the bar is fp32 round-off (1e-5 abs
+    on rotation-matrix entries) against the reference module's CPU output; gradients through the torch recompute."""
+    from mygauhuman_b200 import synthetic as S
+    from mygauhuman_b200.lbs import SMPLDeformer
+    from mygauhuman_b200.nets import BodyPoseRefiner
+    dev = torch.device("cuda")
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "pose_refiner.npz"))
+    m = BodyPoseRefiner(mlp_width=128, mlp_depth=2)
+    m.load_state_dict({k[6:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("param.")})
+    m = m.to(dev)
+    pose = torch.from_numpy(g["pose"]).to(dev)
+    Rs = m(pose)["Rs"]
+    want = torch.from_numpy(g["Rs"]).to(dev)
+    assert Rs.shape == want.shape == (1, 23, 3, 3)
+    err = float((Rs - want).abs().max())
+    print(f"pose refiner: max |err| {err:.3e}")
+    assert err <= 1e-5
+    assert float((want - torch.eye(3, device=dev)).abs().max()) > 0.1  # the golden is not the identity
+    w = torch.randn(1, 23, 3, 3, generator=torch.Generator().manual_seed(4)).to(dev)
+    (Rs * w).sum().backward()
+    got = [p.grad.clone() for p in m._params()]
+    for p in m.parameters():
+        p.grad = None
+    (m.torch_forward(pose) * w).sum().backward()
+    for a, p in zip(got, m._params()):
+        assert torch.allclose(a, p.grad, rtol=1e-4, atol=1e-6 * float(p.grad.abs().max()))
+    # its output is the correct_Rs input of the pose stage
+    deformer = SMPLDeformer(smpl_model, dev)
+    params = {k: v.to(dev) for k, v in S.make_pose_params(2).items()}
+    buf = deformer.pose_buffer(params, Rs.detach()[0])
+    assert torch.isfinite(buf[:288]).all()
