@@ -95,6 +95,7 @@ class GraphedRenderStep:
         # stage itself.  A MultiLaneRenderStep fills them for all its lanes with ONE launch per group (pose_views) and sets
         # _pose_ready; a direct call of this step fills them itself.
         self.pose_inputs, self._pose_ready = None, False
+        self._pre_run = None  # owner's hook: makes the current stream wait for a nearest-vertex search still in flight
         self._sink, self._sink_atomic = None, False
         if accumulate:
             # the deform backward kernel adds straight into the bucket: no separate accumulation pass
@@ -291,6 +292,8 @@ class GraphedRenderStep:
                 dst.copy_(src, non_blocking=True)
 
     def _run(self):
+        if self._pre_run is not None:
+            self._pre_run()
         if self.pose_inputs is not None and not self._pose_ready:
             self._fill_pose()
         if self.graph is None:
@@ -391,9 +394,12 @@ class MultiLaneRenderStep:
         for lane in self.lanes:
             lane._sink_atomic = len(self.lanes) > 1
             lane.vert_ids = self.vert_ids
+            lane._pre_run = self._wait_knn
             if self.batch_pose:
                 lane.pose_inputs = (torch.zeros(_lib.POSE_FLOATS, device=dev), torch.zeros(deformers[0].V, 3, device=dev))
         self.streams = [torch.cuda.Stream(device=dev) for _ in self.lanes]
+        self._side = torch.cuda.Stream(device=dev)   # nearest-vertex search of a batch, next to the bucket reset and the pose stage
+        self._knn_done, self._knn_pending = torch.cuda.Event(), False
         self._fork = torch.cuda.Event()
         self._joins = [torch.cuda.Event() for _ in self.lanes]
         self._alias_grads()
@@ -421,11 +427,21 @@ class MultiLaneRenderStep:
         lane = self.lanes[0]
         lane.deformer.nearest_vertex(lane.t_vertices, self.leaves["xyz"], out=self.vert_ids)
 
+    def _wait_knn(self):
+        if self._knn_pending:
+            torch.cuda.current_stream().wait_event(self._knn_done)
+            self._knn_pending = False
+
     def zero_grads(self):
         """Start a batch (on the current stream; the lanes fork from it): clears the gradient bucket and refreshes the
         nearest-vertex ids from the current positions.  Call it after every parameter update."""
+        cur = torch.cuda.current_stream()
+        self._side.wait_stream(cur)  # the positions the optimiser just wrote; the previous batch's lanes have joined `cur`
+        with torch.cuda.stream(self._side):
+            self._nearest_vertices()
+            self._knn_done.record(self._side)
+        self._knn_pending = True
         self.lanes[0].flat.zero_()
-        self._nearest_vertices()
 
     def run_group(self, vecs, loss_inputs=None, prefetched=False, next_vecs=None, next_loss_inputs=None):
         """Replay len(vecs) <= K views concurrently, view j on lane j.  loss_inputs: one tuple per view (None: keep the
@@ -447,6 +463,7 @@ class MultiLaneRenderStep:
                     srcs.append(lane.vec)
             self.lanes[0].deformer.pose_views(self.lanes[0].big, [_pose_slices(v) for v in srcs],
                                               [self.lanes[j].pose_inputs for j in range(len(vecs))])
+        self._wait_knn()
         self._fork.record(cur)
         losses = []
         for j in range(len(vecs)):

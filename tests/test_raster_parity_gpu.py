@@ -291,7 +291,7 @@ def test_autograd_module_matches_raw_calls():
 
 
 def test_throughput_regime_kernels_pass_the_same_parity_tests():
-    """Frames with more than 2^19 (Gaussian, tile) pairs take the other blend kernel family (ghr_blend_*_wide.cu,
+    """Frames with more than 2^22 (Gaussian, tile) pairs take the other blend kernel family (ghr_blend_*_wide.cu,
     8x4-pixel blocks, no block masks).  The regime is chosen once per process, so the forward/backward parity tests of
     this file are re-run in a child process with GHR_BLEND_REGIME=throughput."""
     import os
