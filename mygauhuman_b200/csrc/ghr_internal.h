@@ -216,6 +216,10 @@ cudaError_t launch_pose_refiner(int width, int n_layers, const float* const* w, 
 size_t lbs_mlp_blob_bytes();
 cudaError_t launch_lbs_mlp_pack(const float* const* weights, const float* const* biases, void* blob, cudaStream_t s);
 cudaError_t launch_lbs_mlp_forward(int P, const float* xyz, const void* blob, float* logits, cudaStream_t s);
+size_t lbs_mlp_blob_f16_bytes();
+cudaError_t launch_lbs_mlp_pack_f16(const float* const* weights, void* blob_f16, cudaStream_t s);
+cudaError_t launch_lbs_mlp_forward_f16(int P, const float* xyz, const void* blob_f16, const float* biases, float* logits,
+                                       cudaStream_t s);
 // fused LBS + projection (ghr_fused.cu)
 cudaError_t launch_deform_project(const ghr_deform_params& dp, const ghr_raster_params& p, int32_t* radii, char* geom,
                                   const ghr_layout& L, float* world_pts, float* world_normals, float* cov3D, float* colors,

@@ -19,6 +19,7 @@
 #include <stdio.h>
 #include "ghr_common.cuh"
 #include "ghr_internal.h"
+#include "ghr_umma.cuh"
 
 namespace ghr {
 
@@ -83,80 +84,7 @@ __global__ void __launch_bounds__(256) lbs_mlp_pack_kernel(const MlpWeights w, f
     }
 }
 
-// ---- PTX wrappers ----------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_global, uint32_t bytes, uint64_t* bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
-                 "l"(src_global), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-// K-major, no swizzle: LBO = distance of the two 16-byte K chunks of an instruction, SBO = distance of 8-row groups
-__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes)
-{
-    return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
-           (1ull << 46);  // version 1 (Blackwell), base offset 0, layout type 0 = SWIZZLE_NONE
-}
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
-{
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar)
-{
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v)
-{
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v)
-{
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-        : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// instruction descriptor: D fp32, A/B tf32, both K-major, M = 128, N given
-__host__ __device__ constexpr uint32_t idesc_tf32(int N) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24); }
+using namespace umma;
 
 #ifdef GHR_MLP_TRACE  // tuning builds only (tools/build_variant.sh): phase timestamps of block 0, printed by its thread 0
 #define MLP_T(i) do { if (blockIdx.x == 0 && t == 0) tr[i] = clock64(); } while (0)
@@ -369,7 +297,16 @@ __global__ void __launch_bounds__(kThreads, 1) lbs_mlp_forward_kernel(int P, int
 
 }  // namespace
 
-size_t lbs_mlp_blob_bytes() { return kBlobBytes; }
+// blob = [TF32 stages | biases (fp32)] [FP16 stages]: both kernels' weight formats, packed together
+size_t lbs_mlp_blob_bytes() { return kBlobBytes + lbs_mlp_blob_f16_bytes(); }
+
+// which tensor-core kernel serves ghr_lbs_mlp_forward: "f16" = two tiles in flight per CTA, FP16 operands (ghr_mlp_f16.cu,
+// default), "tf32" = this file's kernel.  Same 11-bit significand either way.
+static bool use_f16_kernel()
+{
+    static const int choice = [] { const char* e = getenv("GHR_MLP_KERNEL"); return e && e[0] == 't' ? 0 : 1; }();
+    return choice == 1;
+}
 
 cudaError_t launch_lbs_mlp_pack(const float* const* weights, const float* const* biases, void* blob, cudaStream_t s)
 {
@@ -377,12 +314,18 @@ cudaError_t launch_lbs_mlp_pack(const float* const* weights, const float* const*
     count_launch();
     MlpWeights w{weights[0], weights[1], weights[2], weights[3], weights[4], biases[0], biases[1], biases[2], biases[3], biases[4]};
     lbs_mlp_pack_kernel<<<64, 256, 0, s>>>(w, reinterpret_cast<float*>(blob));
-    return cudaGetLastError();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    return launch_lbs_mlp_pack_f16(weights, reinterpret_cast<char*>(blob) + kBlobBytes, s);
 }
 
 cudaError_t launch_lbs_mlp_forward(int P, const float* xyz, const void* blob, float* logits, cudaStream_t s)
 {
     StageTimer timer(GHR_STAGE_MISC, s);
+    if (use_f16_kernel())
+        return launch_lbs_mlp_forward_f16(P, xyz, reinterpret_cast<const char*>(blob) + kBlobBytes,
+                                          reinterpret_cast<const float*>(reinterpret_cast<const char*>(blob) + 8 * (size_t)kStageBytes + 16384),
+                                          logits, s);
     static unsigned long long attr_set = 0ull;
     if (first_use_on_current_device(attr_set)) {
         cudaError_t e = cudaFuncSetAttribute(lbs_mlp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);

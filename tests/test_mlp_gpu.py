@@ -5,7 +5,8 @@ ghr_lbs_mlp_forward, csrc/ghr_mlp.cu) against
   * the same layers in fp64 on the GPU (the truth) and in fp32 under torch's DEFAULT settings, which is how the
     reference runs them: cuDNN convolutions with TF32 allowed.
 
-The kernel computes with TF32 operands and fp32 accumulation, so the bar is stated against the truth: max |error| <=
+The kernels compute with 11-bit-significand operands (FP16 by default, TF32 with GHR_MLP_KERNEL=tf32) and fp32
+accumulation, so the bar is stated against the truth: max |error| <=
 3e-3 of the largest logit (TF32 keeps 11 significant bits; five layers of 63..191-term dot products), and not worse than
 the reference's own default-precision error by more than a small factor.  The measured errors are printed.
 """
