@@ -14,7 +14,7 @@ Used by bench.py's reference arm (so that its LBS / covariance / SH half is the 
 restatement) and by the drop-in tests.  Third-party packages the reference imports that are absent from this image
 are replaced by the smallest possible stand-ins, each named here:
 
-    knn_cuda.KNN        (KNN_CUDA 0.2, un-vendored)  -> exact brute-force nearest neighbours (GEMM candidates, exact re-rank)
+    knn_cuda.KNN        (KNN_CUDA 0.2, un-vendored)  -> exact brute-force nearest neighbours (k + 2 GEMM-form candidates, exact re-rank)
     plyfile, trimesh, imageio   (file I/O, unused on the path)  -> empty modules
     nvdiffrast.torch    (un-vendored)  -> `texture` is whatever the caller installs (see set_nvdiffrast_texture)
     gs_ir._C            (the fork's private extension, unused by bake_set)  -> empty module
