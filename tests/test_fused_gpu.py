@@ -185,3 +185,32 @@ def test_batched_pose_stage_equals_the_per_view_kernels(smpl_model, n_views, wit
         for o, n in segments:
             assert torch.equal(gb[o:o + n], wb[o:o + n]), o
         assert torch.equal(go, wo)
+
+
+def test_edge_cases_empty_single_and_fully_culled(smpl_model):
+    """P = 0 (the reference returns its zero-filled outputs, rasterize_points.cu:83), P = 1, and a camera that looks away
+    from the body (every Gaussian culled: background image, zero gradients, nothing added)."""
+    from mygauhuman_b200.fused import render_deformed
+    dev, deformer, L, big, tv, cam, pose = _scene(smpl_model, 300, seed=4)
+    rs = _settings(cam, dev)
+    kw = lambda n: dict(log_scaling=L["log_scale"][:n], rotation=L["rotation"][:n], features=L["features"][:n],
+                        opacity_logit=L["opacity_logit"][:n])
+    c, r, d, a = render_deformed(deformer, L["xyz"][:0], pose, big, tv, rs, **kw(0))
+    assert r.numel() == 0 and float(c.abs().max()) == 0.0 and float(a.abs().max()) == 0.0
+    c1, r1, d1, a1 = render_deformed(deformer, L["xyz"][:1], pose, big, tv, rs, **kw(1))
+    c2, r2, _, _, _, _, _ = _two_operator(deformer, {k: v[:1] for k, v in L.items()}, pose, big, tv, rs)
+    assert torch.equal(r1, r2) and torch.equal(c1, c2)
+    # camera behind the body, looking away: flip the view direction by moving the camera through the body
+    away = S.make_camera(W, H, angle=0.6, radius=-3.0, seed=1, focal=537.0 * W / 512)
+    rs2 = _settings(away, dev)
+    for t in L.values():
+        t.grad = None
+    c3, r3, d3, a3 = render_deformed(deformer, L["xyz"], pose, big, tv, rs2, **kw(300))
+    if int((r3 > 0).sum()) == 0:
+        assert torch.allclose(c3, rs2.bg[:, None, None].expand_as(c3)) and float(a3.abs().max()) == 0.0
+        (c3.sum() + a3.sum()).backward()
+        for k in ("xyz", "log_scale", "rotation", "features", "opacity_logit"):
+            assert float(L[k].grad.abs().max()) == 0.0, k
+    else:  # the synthetic camera still sees part of the body: at least the chains must agree
+        c4, r4, _, _, _, _, _ = _two_operator(deformer, L, pose, big, tv, rs2)
+        assert torch.equal(r3, r4) and torch.equal(c3, c4)
