@@ -23,7 +23,7 @@ if [ $rc -eq 0 ]; then
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file "$OUT/${TAG}_launches.csv" \
     python bench.py --steps 4 --warmup 3 --no-extras --no-cpu-baseline > "$OUT/${TAG}_launches.log" 2>&1
   echo "ncu launch list: exit $?"
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'blend_|onesweep|preprocess|emit_keys|tile_|lbs_|sort_histogram|adam_|nearest_vertex' --launch-skip 60 -c 40 -f \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'blend_|onesweep|emit_keys|tile_|lbs_|sort_histogram|adam_|nearest_vertex|deform_project|project_deform' --launch-skip 60 -c 36 -f \
     -o "$OUT/${TAG}_full" python bench.py --mode eager --eager-chain fused --batch-views 1 --steps 2 --warmup 3 --no-extras --no-cpu-baseline \
     > "$OUT/${TAG}_full.log" 2>&1
   echo "ncu full: exit $?"
