@@ -480,8 +480,11 @@ class MultiLaneRenderStep:
                 finally:
                     lane._pose_ready = False
                 self._joins[j].record(s)
-            if next_vecs is not None and j < len(next_vecs):
-                lane.prefetch(next_vecs[j], *(next_loss_inputs[j] if next_loss_inputs is not None else ()))
+        # the host copies of the NEXT group are issued only after every lane of this group has been launched: issuing them
+        # lane by lane in between delayed the last lane's replay by ~130 us of host calls (9 % of an 8-view group)
+        if next_vecs is not None:
+            for j in range(min(len(vecs), len(next_vecs))):
+                self.lanes[j].prefetch(next_vecs[j], *(next_loss_inputs[j] if next_loss_inputs is not None else ()))
         for j in range(len(vecs)):
             cur.wait_event(self._joins[j])
         return losses
