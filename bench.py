@@ -1145,6 +1145,8 @@ def run_workload(args, workload, world, rank, local, dev, K, Wm, headline):
         launches = K * B * arm.graphed.kernels_per_replay + K * per_batch
         if arm.multi is not None:
             launches += K * 1  # nearest-vertex search once per batch (zero_grads)
+            if arm.multi.batch_pose:
+                launches += K * (B // arm.multi.K)  # the batched pose stage, once per group of concurrent views
         checker = arm.multi if arm.multi is not None else arm.graphed
         if not checker.check():  # a view overflowed the captured binning capacity: re-captured, measure again
             (ms_dev, wall_dev), (ms_e2e, wall_e2e) = timed(K, False), timed(K, True)
