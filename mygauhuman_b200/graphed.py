@@ -443,6 +443,9 @@ class MultiLaneRenderStep:
         self._knn_pending = True
         self.lanes[0].flat.zero_()
 
+    # (Tried: ONE CUDA graph for a whole group -- the pose stage and all K lanes captured across their streams, one host
+    # launch instead of K.  Measured slower on B200, 7 040 vs 7 180 views/s at the ZJU shape: the K per-lane launches cost
+    # ~120 us of host time per group, but the lanes they start staggered overlap better than K branches of one graph.)
     def run_group(self, vecs, loss_inputs=None, prefetched=False, next_vecs=None, next_loss_inputs=None):
         """Replay len(vecs) <= K views concurrently, view j on lane j.  loss_inputs: one tuple per view (None: keep the
         lanes' resident loss inputs).  prefetched=True: run what each lane's last prefetch() staged instead of `vecs`
