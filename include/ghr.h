@@ -419,6 +419,10 @@ int ghr_lbs_deform_backward(const ghr_deform_params* prm, const uint8_t* clamped
  *                                   ghr_lbs_deform_backward (same accumulate_grads modes, dL_dopacity_logits through
  *                                   dp), plus dL_dmeans2D [P,3] (screen-space gradient, always stored; NULL = skipped).
  *                                   Culled Gaussians get zeros (nothing is added in the accumulating modes).
+ *                                   max_radii2D / xyz_gradient_accum / denom: the densification statistics of the
+ *                                   training loop (ghr_densify_stats: train.py:401-404, scene/gaussian_model.py:764-766)
+ *                                   updated in the same kernel for the visible Gaussians, with atomics (views of a batch
+ *                                   may run concurrently); NULL = skipped.
  */
 int ghr_forward_deform_preprocess(const ghr_deform_params* dp, const ghr_raster_params* view, int32_t* radii, void* geom,
                                   size_t geom_bytes, float* world_pts, float* world_normals, float* cov3D, float* colors,
@@ -432,7 +436,9 @@ int ghr_backward_deformed(const ghr_deform_params* dp, const ghr_raster_params* 
                           const float* dL_dout_alpha, float* accum /* [P,12] zeroed */, float* dL_dmeans2D,
                           float* dL_dxyz, float* dL_dlbs_offsets /* [P,24]|NULL */, float* dL_dscales,
                           float* dL_drotations, float* dL_dshs, float* dL_dA_target /* [24*12]|NULL, accumulated */,
-                          float* dL_dvertex_offsets /* [V*3]|NULL, accumulated */, void* stream);
+                          float* dL_dvertex_offsets /* [V*3]|NULL, accumulated */,
+                          float* max_radii2D, float* xyz_gradient_accum, float* denom /* each [P]|NULL, see below */,
+                          void* stream);
 
 /* BodyPoseRefiner (nets/mlp_delta_body_pose.py:5-41 + RodriguesModule :164-193; called per view from
  * gaussian_renderer/__init__.py:100-102): Linear(69, width) ReLU [Linear(width, width) ReLU]* Linear(width, 69) on the 69

@@ -142,7 +142,7 @@ SIGNATURES = {
                                               C.c_void_p]),
     "ghr_backward_deformed": (C.c_int, [C.POINTER(DeformParams), C.POINTER(RasterParams), C.c_void_p, C.c_void_p,
                                         C.c_size_t, C.c_void_p, C.c_size_t, C.c_int64, C.c_void_p, C.c_size_t]
-                              + [C.c_void_p] * 13),
+                              + [C.c_void_p] * 16),
     "ghr_smpl_lbs_vertices": (C.c_int, [C.POINTER(LbsModel)] + [C.c_void_p] * 6),
     "ghr_covariance_forward": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ghr_covariance_backward": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_float] + [C.c_void_p] * 6),

@@ -636,7 +636,8 @@ int ghr_backward_deformed(const ghr_deform_params* dp, const ghr_raster_params* 
                           const void* img, size_t img_bytes, const float* dL_dout_color, const float* dL_dout_depth,
                           const float* dL_dout_alpha, float* accum, float* dL_dmeans2D, float* dL_dxyz,
                           float* dL_dlbs_offsets, float* dL_dscales, float* dL_drotations, float* dL_dshs,
-                          float* dL_dA_target, float* dL_dvertex_offsets, void* stream)
+                          float* dL_dA_target, float* dL_dvertex_offsets, float* max_radii2D, float* xyz_gradient_accum,
+                          float* denom, void* stream)
 {
     int r = validate_fused(dp, view);
     if (r != GHR_OK) return r;
@@ -655,7 +656,8 @@ int ghr_backward_deformed(const ghr_deform_params* dp, const ghr_raster_params* 
     if (r != GHR_OK) return r;
     DeformGrads g{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, dL_dxyz, nullptr, dL_dlbs_offsets, dL_dscales,
                   dL_drotations, dL_dshs, dL_dA_target, dL_dvertex_offsets};
-    return stage_done(view, launch_project_deform_backward(*dp, *view, radii, (const char*)geom, L, accum, g, dL_dmeans2D, s),
+    return stage_done(view, launch_project_deform_backward(*dp, *view, radii, (const char*)geom, L, accum, g, dL_dmeans2D,
+                                                                   max_radii2D, xyz_gradient_accum, denom, s),
                       s, "project_deform_backward");
 }
 

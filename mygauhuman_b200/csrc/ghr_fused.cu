@@ -131,6 +131,8 @@ struct FusedBwdArgs {
     const float* accum;      // [P][12] from the blend backward
     const uint8_t* clamped;  // geom
     float* dL_dmean2D;       // [P,3]
+    // densification statistics of the training loop (train.py:401-404, gaussian_model.py:764-766), fused: NULL = skipped
+    float *max_radii2D, *xyz_gradient_accum, *denom;
 };
 
 __global__ void __launch_bounds__(128) project_deform_backward_kernel(const FusedBwdArgs f)
@@ -186,6 +188,12 @@ __global__ void __launch_bounds__(128) project_deform_backward_kernel(const Fuse
             }
             deform_backward_gaussian(p, s, g, idx, vid, d, xw, up, dAt, bw_keep);
         }
+        if (vis) {  // visibility_filter = radii > 0; atomics: the views of a batch may run concurrently
+            if (f.max_radii2D)  // max of non-negative floats = max of their bit patterns
+                atomicMax(reinterpret_cast<int*>(f.max_radii2D + idx), __float_as_int((float)f.radii[idx]));
+            if (f.xyz_gradient_accum) atomicAdd(f.xyz_gradient_accum + idx, sqrtf(g2x * g2x + g2y * g2y));
+            if (f.denom) atomicAdd(f.denom + idx, 1.0f);
+        }
         if (f.dL_dmean2D) {
             f.dL_dmean2D[3 * (size_t)idx] = g2x; f.dL_dmean2D[3 * (size_t)idx + 1] = g2y; f.dL_dmean2D[3 * (size_t)idx + 2] = 0.0f;
         }
@@ -231,7 +239,8 @@ cudaError_t launch_deform_project(const ghr_deform_params& dp, const ghr_raster_
 
 cudaError_t launch_project_deform_backward(const ghr_deform_params& dp, const ghr_raster_params& p, const int32_t* radii,
                                            const char* geom, const ghr_layout& L, const float* accum,
-                                           const DeformGrads& g, float* dL_dmean2D, cudaStream_t s)
+                                           const DeformGrads& g, float* dL_dmean2D, float* max_radii2D,
+                                           float* xyz_gradient_accum, float* denom, cudaStream_t s)
 {
     StageTimer timer(GHR_STAGE_PROJECT_DEFORM_BWD, s);
     count_launch();
@@ -247,6 +256,7 @@ cudaError_t launch_project_deform_backward(const ghr_deform_params& dp, const gh
     f.accum = accum;
     f.clamped = reinterpret_cast<const uint8_t*>(geom + L.g_clamped);
     f.dL_dmean2D = dL_dmean2D;
+    f.max_radii2D = max_radii2D; f.xyz_gradient_accum = xyz_gradient_accum; f.denom = denom;
     project_deform_backward_kernel<<<(dp.P + 127) / 128, 128, 0, s>>>(f);
     return cudaGetLastError();
 }

@@ -226,7 +226,8 @@ cudaError_t launch_deform_project(const ghr_deform_params& dp, const ghr_raster_
                                   float* opacity, int32_t* n_host, cudaStream_t s);
 cudaError_t launch_project_deform_backward(const ghr_deform_params& dp, const ghr_raster_params& p, const int32_t* radii,
                                            const char* geom, const ghr_layout& L, const float* accum,
-                                           const DeformGrads& g, float* dL_dmean2D, cudaStream_t s);
+                                           const DeformGrads& g, float* dL_dmean2D, float* max_radii2D,
+                                           float* xyz_gradient_accum, float* denom, cudaStream_t s);
 size_t vertex_grid_workspace_bytes(int V);
 cudaError_t launch_vertex_grid_build(int V, const float* verts, char* ws, cudaStream_t s);
 cudaError_t launch_nearest_vertex(int P, const float* query, int V, const char* ws, int32_t* vid, cudaStream_t s);

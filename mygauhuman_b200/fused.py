@@ -39,7 +39,7 @@ def _view_params(keep, P, rs, dev):
 
 class _RenderDeformedFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, deformer, params, t_params, t_vertices, rs, scales_are_log, want_aux, means2D, xyz, normals,
+    def forward(ctx, deformer, params, t_params, t_vertices, rs, scales_are_log, want_aux, densify, means2D, xyz, normals,
                 lbs_weights, correct_Rs, scaling, rotation, features, opacity_logit):
         self = deformer
         dev = self.device
@@ -111,7 +111,7 @@ class _RenderDeformedFn(torch.autograd.Function):
             if rs.debug:
                 _C.read_status(geom, raise_on_error=True)
         _C._last_geom = geom
-        ctx.P, ctx.deformer, ctx.p, ctx.view = P, self, p, view
+        ctx.P, ctx.deformer, ctx.p, ctx.view, ctx.densify = P, self, p, view, densify
         ctx.keep = (keep, xyz_c, nrm, lw, sc, rot, shs, ol, pose_big, pose_tgt, off, vid)
         ctx.state = (radii, geom, binning, img)
         ctx.correct_Rs = correct_Rs
@@ -123,7 +123,7 @@ class _RenderDeformedFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_color, g_radii, g_depth, g_alpha, *g_aux):
-        n_in = 16
+        n_in = 17
         if ctx.P == 0:
             return (None,) * n_in
         self, p, view = ctx.deformer, ctx.p, ctx.view
@@ -137,7 +137,12 @@ class _RenderDeformedFn(torch.autograd.Function):
         g = [zero(*shape) if t is None else _f32c(t)
              for t, shape in ((g_color, (3, H, W)), (g_depth, (1, H, W)), (g_alpha, (1, H, W)))]
         capacity = _C._capacity_of(binning, P, W, H)
-        need = ctx.needs_input_grad  # 7 = means2D, 8.. = xyz, normals, lbs_weights, correct_Rs, scaling, rotation, features, logit
+        need = ctx.needs_input_grad[1:]  # (after dropping `densify`) 7 = means2D, 8.. = xyz, normals, lbs_weights, correct_Rs, ...
+        stats = [None, None, None]
+        if ctx.densify is not None:
+            stats = list(ctx.densify)
+            for t in stats:
+                assert t is None or (t.is_cuda and t.dtype == torch.float32 and t.numel() == P and t.is_contiguous())
         accum = zero(P * 12)
         d_m2d = torch.empty(P, 3, **f)
         sink = self.grad_sink
@@ -162,7 +167,7 @@ class _RenderDeformedFn(torch.autograd.Function):
                 C.byref(p), C.byref(view), radii.data_ptr(), geom.data_ptr(), geom.numel(), binning.data_ptr(),
                 binning.numel(), capacity, img.data_ptr(), img.numel(), g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(),
                 accum.data_ptr(), d_m2d.data_ptr(), d_xyz.data_ptr(), _ptr(d_lw), d_sc.data_ptr(), d_rot.data_ptr(),
-                d_sh.data_ptr(), _ptr(d_A), _ptr(d_off), _stream()), "ghr_backward_deformed")
+                d_sh.data_ptr(), _ptr(d_A), _ptr(d_off), *[_ptr(t) for t in stats], _stream()), "ghr_backward_deformed")
             d_cr = None
             if want_pose:
                 buf = torch.empty(23 * 9 + 207, **f)
@@ -171,15 +176,15 @@ class _RenderDeformedFn(torch.autograd.Function):
                 d_cr = buf[:207].view(23, 3, 3).reshape(ctx.correct_Rs.shape)
         g_m2d = d_m2d if need[7] else None
         if sink is not None:  # the per-Gaussian gradients were added to the sink tensors
-            return (None,) * 7 + (g_m2d, None, None, None, d_cr, None, None, None, None)
+            return (None,) * 8 + (g_m2d, None, None, None, d_cr, None, None, None, None)
         zn = torch.zeros_like(nrm) if has_n and need[9] else None  # normals do not reach the images
-        return (None,) * 7 + (g_m2d, d_xyz, zn, None if d_lw is None else d_lw.view(ctx.lw_shape), d_cr, d_sc, d_rot, d_sh,
+        return (None,) * 8 + (g_m2d, d_xyz, zn, None if d_lw is None else d_lw.view(ctx.lw_shape), d_cr, d_sc, d_rot, d_sh,
                               d_ol.view(ctx.ol_shape))
 
 
 def render_deformed(deformer, xyz, params, t_params, t_vertices, raster_settings, *, rotation, features, opacity_logit,
                     scaling=None, log_scaling=None, normals=None, lbs_weights=None, correct_Rs=None, means2D=None,
-                    return_aux=False):
+                    return_aux=False, densify=None):
     """Deform the canonical Gaussians to the pose `params` and rasterise them with `raster_settings`
     (GaussianRasterizationSettings; its sh_degree is the active SH degree, its campos the SH view point).
 
@@ -187,13 +192,15 @@ def render_deformed(deformer, xyz, params, t_params, t_vertices, raster_settings
     opacity_logit [P,1] raw (sigmoid inside); normals [P,3] optional (only for the `world_normals` aux output);
     lbs_weights [P,24] logit offsets (LBSOffsetDecoder) and correct_Rs [23,3,3] (BodyPoseRefiner) optional;
     means2D [P,3]: optional leaf whose .grad receives the screen-space gradient (densification statistics).
+    densify: optional (max_radii2D, xyz_gradient_accum, denom) fp32 tensors with P entries (any of them None), updated IN
+    the backward kernel for the visible Gaussians as train.py:401-404 / add_densification_stats do after it.
 
     Returns (color[3,H,W], radii[P], depth[1,H,W], alpha[1,H,W]) and, with return_aux=True, a dict of the intermediate
     values (means3D, world_normals, cov3D, colors, opacity) as non-differentiable copies."""
     if (scaling is None) == (log_scaling is None):
         raise ValueError("pass either scaling or log_scaling")
     out = _RenderDeformedFn.apply(deformer, params, t_params, t_vertices, raster_settings, log_scaling is not None,
-                                  bool(return_aux), means2D, xyz, normals, lbs_weights, correct_Rs,
+                                  bool(return_aux), densify, means2D, xyz, normals, lbs_weights, correct_Rs,
                                   log_scaling if scaling is None else scaling, rotation, features, opacity_logit)
     color, radii, depth, alpha = out[:4]
     if not return_aux:

@@ -214,3 +214,31 @@ def test_edge_cases_empty_single_and_fully_culled(smpl_model):
     else:  # the synthetic camera still sees part of the body: at least the chains must agree
         c4, r4, _, _, _, _, _ = _two_operator(deformer, L, pose, big, tv, rs2)
         assert torch.equal(r3, r4) and torch.equal(c3, c4)
+
+
+def test_densification_statistics_fused_into_the_backward(smpl_model):
+    """render_deformed(densify=...) updates max_radii2D / xyz_gradient_accum / denom inside the backward kernel; the
+    reference does it with three indexed statements after backward (train.py:401-404, gaussian_model.py:764-766), which
+    optim.add_densification_stats (ghr_densify_stats, pinned against those statements) restates."""
+    from mygauhuman_b200.fused import render_deformed
+    from mygauhuman_b200.optim import add_densification_stats
+    P = 5000
+    dev, deformer, L, big, tv, cam, pose = _scene(smpl_model, P, seed=6, view_id=2, radius=1.3)
+    rs = _settings(cam, dev)
+    w = torch.randn(3, H, W, generator=torch.Generator().manual_seed(3)).to(dev)
+    got = [torch.zeros(P, device=dev), torch.zeros(P, 1, device=dev), torch.zeros(P, 1, device=dev)]
+    want = [t.clone() for t in got]
+    got[0][::7] = 40.0  # some Gaussians already hold a larger radius than this view gives them
+    want[0][::7] = 40.0
+    for _ in range(2):  # two views accumulate
+        m2d = torch.zeros(P, 3, device=dev, requires_grad=True)
+        color, radii, _, _ = render_deformed(deformer, L["xyz"], pose, big, tv, rs, log_scaling=L["log_scale"],
+                                             rotation=L["rotation"], features=L["features"], opacity_logit=L["opacity_logit"],
+                                             means2D=m2d, densify=tuple(got))
+        (color * w).sum().backward()
+        add_densification_stats(radii, m2d.grad.contiguous(), *want)
+    vis = radii > 0
+    assert 0 < int(vis.sum()) < P
+    assert torch.equal(got[0], want[0]) and torch.equal(got[2], want[2])
+    assert float((got[1] - want[1]).abs().max()) <= 1e-6 * float(want[1].abs().max())
+    assert float(got[2][~vis].abs().max()) == 0.0 and float(got[2][vis].min()) == 2.0
