@@ -1348,6 +1348,18 @@ def main():
                                                           "wall_clock_value", "gpu_launches") if k in sub}
             if "sharded_step_check" in sub:
                 line["multiview_300k"]["sharded_step_check"] = sub["sharded_step_check"]
+    if (world == 1 and args.impl == "ours" and args.mode == "graph" and args.lanes > 1 and args.batch_views > 1
+            and not args.no_extras):
+        # Like for like with the reference arm's execution (ONE view at a time, L2 flushed before every view): the same
+        # step on one lane.  The headline's 8 concurrent lanes are this repo's way of filling the GPU, not part of the
+        # workload; this number takes them out of the comparison.
+        a1 = argparse.Namespace(**vars(args))
+        a1.lanes = 1
+        sub = run_workload(a1, args.workload, world, rank, local, dev, max(10, min(K, 40)), 3, headline=False)
+        if sub is not None:
+            line["one_lane"] = {k: sub[k] for k in ("value", "unit", "ms_per_step", "steps", "e2e", "gpu_launches") if k in sub}
+            line["one_lane"]["what"] = ("--lanes 1: one CUDA-graph replay per view, views of a batch one after the other, L2 "
+                                        "flushed before every view -- the reference arm's execution pattern")
     if rank == 0:
         emit(line)
 
