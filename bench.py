@@ -266,7 +266,7 @@ class OursArm:
             cam = wl["views"][0]["cam"]
             assert all(v["cam"]["tanfovx"] == cam["tanfovx"] and v["cam"]["tanfovy"] == cam["tanfovy"] for v in wl["views"])
             self.multi = None
-            if lanes > 1:
+            if lanes >= 1:  # one lane too: the nearest-vertex search then runs once per batch, not once per view
                 from mygauhuman_b200.graphed import MultiLaneRenderStep
                 deformers = [self.deformer] + [SMPLDeformer(wl["smpl"], dev) for _ in range(lanes - 1)]
                 self.multi = MultiLaneRenderStep(deformers, self.leaves, self.big, self.t_vertices, wl["H"], wl["W"],
