@@ -4,7 +4,9 @@
  * Plain pointers and sizes only: no torch types, no C++ types, never throws.
  * Every entry point returns 0 (GHR_OK) or a negative ghr_status; all work is
  * enqueued on the caller's cudaStream_t (passed as void*), nothing is
- * allocated behind the caller's back, no global state is kept between calls.
+ * allocated behind the caller's back, no global state is kept between calls
+ * (two documented exceptions: the process-wide switches ghr_set_shared_gpu /
+ * ghr_profile_enable, and the static device scratch of ghr_sort_pairs_u64_static).
  *
  * Each entry point names the reference interface it replaces (paths relative
  * to /root/reference/).  `dgr/` = submodules/diff-gaussian-rasterization/.
