@@ -98,6 +98,13 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp
     return s_warp[warp] + inc - v;
 }
 
+// Column of digit d in a warp's row of shared-memory counters.  A digit that straddles the depth exponent and the tile id
+// (bits 27..35 of a 1080p key) takes values t * 32 + c with two or three c only: unswizzled, every such digit of a warp
+// lands in the same two or three banks and the leaders' read-modify-writes serialise (ncu: 2.5x the shared-memory
+// wavefronts of the other passes).  XOR-ing the upper digit bits into the bank bits keeps the map a bijection and keeps
+// "thread t owns digit t" conflict-free (a warp's 32 threads share t >> 5).
+__device__ __forceinline__ uint32_t hist_col(uint32_t d) { return d ^ (d >> 5); }
+
 __global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint64_t* __restrict__ keys,
                                                                       const uint32_t* __restrict__ n_dev,
                                                                       int64_t capacity, int bits, int passes,
@@ -127,14 +134,14 @@ __global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint
             for (int p = 0; p < passes; p++) {
                 uint32_t d = (uint32_t)(ks >> (p * kRadixBits)) & (uint32_t)(kRadix - 1);
                 if (p == passes - 1) d &= lastmask;
-                atomicAdd(&s_hist[p * kRadix + d], 1u);
+                atomicAdd(&s_hist[p * kRadix + hist_col(d)], 1u);
             }
         }
     }
     __syncthreads();
     for (int i = t; i < passes * kRadix; i += kSortThreads) {
         const uint32_t c = s_hist[i];
-        if (c) atomicAdd(&hdr->hist[i / kRadix][i % kRadix], c);
+        if (c) atomicAdd(&hdr->hist[i / kRadix][hist_col(i % kRadix)], c);  // hist_col is its own inverse
     }
     // the last CTA to get here owns the complete histograms and writes the plan
     __threadfence();
@@ -222,8 +229,8 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
         if (ok && lane == leader) {
-            old = sm.hist[warp][d];
-            sm.hist[warp][d] = old + __popc(peers);
+            old = sm.hist[warp][hist_col(d)];
+            sm.hist[warp][hist_col(d)] = old + __popc(peers);
         }
         old = __shfl_sync(0xffffffffu, old, leader);
         pos[i] = (d << 16) | (old + __popc(peers & lt));
@@ -234,7 +241,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
     // thread t owns digit t: tile count, publish, tile-local digit starts
     uint32_t sum = 0;
 #pragma unroll
-    for (int w = 0; w < kSortWarps; w++) sum += sm.hist[w][tid];
+    for (int w = 0; w < kSortWarps; w++) sum += sm.hist[w][hist_col(tid)];
     uint32_t* my = status + (size_t)tile * kRadix + tid;
     st_relaxed_u32(my, (tile == 0 ? kStIncl : kStAgg) | sum);
     const uint32_t tile_excl = block_excl_scan(sum, s_warp);
@@ -242,8 +249,8 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
         uint32_t run = tile_excl;
 #pragma unroll
         for (int w = 0; w < kSortWarps; w++) {
-            const uint32_t c = sm.hist[w][tid];
-            sm.hist[w][tid] = run;
+            const uint32_t c = sm.hist[w][hist_col(tid)];
+            sm.hist[w][hist_col(tid)] = run;
             run += c;
         }
     }
@@ -251,7 +258,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const uint32_t d = pos[i] >> 16;
-        pos[i] = d < (uint32_t)kRadix ? sm.hist[warp][d] + (pos[i] & 0xFFFFu) : 0xFFFFFFFFu;
+        pos[i] = d < (uint32_t)kRadix ? sm.hist[warp][hist_col(d)] + (pos[i] & 0xFFFFu) : 0xFFFFFFFFu;
     }
     __syncthreads();
 #pragma unroll
