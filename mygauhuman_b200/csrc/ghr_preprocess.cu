@@ -10,9 +10,16 @@
 // we additionally write the packed 48-B blend record per visible Gaussian.
 #include "ghr_project.cuh"
 
+// Resident blocks per SM the register allocation aims at (tuning macro).  Measured at 3 M Gaussians / 1080p on B200:
+// 3 (79 registers) 320-334 us, 4 (64 registers, 160 B spilled) 330 us, 5 (48 registers) 378 us -- occupancy is not what
+// holds this kernel at 2.4 TB/s.
+#ifndef GHR_PRE_MIN_BLOCKS
+#define GHR_PRE_MIN_BLOCKS 3
+#endif
+
 namespace ghr {
 
-__global__ void __launch_bounds__(GHR_BLOCK) preprocess_kernel(const PreArgs a)
+__global__ void __launch_bounds__(GHR_BLOCK, GHR_PRE_MIN_BLOCKS) preprocess_kernel(const PreArgs a)
 {
     __shared__ float s_cam[36];  // view[16] proj[16] campos[3]
     __shared__ uint32_t s_ticket;
