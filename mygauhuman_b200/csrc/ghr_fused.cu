@@ -229,6 +229,7 @@ cudaError_t launch_deform_project(const ghr_deform_params& dp, const ghr_raster_
     a.n_host = n_host;
     a.nblocks = (dp.P + GHR_BLOCK - 1) / GHR_BLOCK;
     a.skip_rgb = 0;
+    a.split_scan = 0;
     f.world_pts = world_pts; f.world_normals = world_normals; f.cov3D = cov3D; f.colors = colors; f.opacity = opacity;
     cudaError_t e = cudaMemsetAsync(geom + L.g_header, 0, L.g_rec - L.g_header, s);
     if (e != cudaSuccess) return e;

@@ -19,6 +19,9 @@
 
 namespace ghr {
 
+// Above this many Gaussians the tiles_touched scan is split off the projection kernel (GHR_SPLIT_SCAN_P overrides)
+static const int kSplitScanP = [] { const char* e = getenv("GHR_SPLIT_SCAN_P"); return e ? atoi(e) : (1 << 20); }();
+
 __global__ void __launch_bounds__(GHR_BLOCK, GHR_PRE_MIN_BLOCKS) preprocess_kernel(const PreArgs a)
 {
     __shared__ float s_cam[36];  // view[16] proj[16] campos[3]
@@ -30,7 +33,7 @@ __global__ void __launch_bounds__(GHR_BLOCK, GHR_PRE_MIN_BLOCKS) preprocess_kern
     if (tid < 16) s_cam[tid] = a.view[tid];
     else if (tid < 32) s_cam[tid] = a.proj[tid - 16];
     else if (tid < 35) s_cam[tid] = a.campos[tid - 32];
-    if (tid == 0) s_ticket = atomicAdd(&a.hdr->scan_ticket, 1u);
+    if (tid == 0) s_ticket = a.split_scan ? blockIdx.x : atomicAdd(&a.hdr->scan_ticket, 1u);  // no chain, no ticket
     __syncthreads();
     const int tile = (int)s_ticket;
     const int idx = tile * GHR_BLOCK + tid;
@@ -52,6 +55,56 @@ __global__ void __launch_bounds__(GHR_BLOCK, GHR_PRE_MIN_BLOCKS) preprocess_kern
         }
     }
     finish_preprocess_block(a, tile, idx, tiles, dbits_hi, dbits_lo_inv, s_warp, s_excl);
+}
+
+// Large P (split_scan): exclusive scan of the per-block totals (one CTA; 3 M Gaussians = 11 719 totals), num_rendered, then
+// the block prefixes are added to the block-local inclusive scans.  The fused single-pass look-back is what a small frame
+// wants (one launch); at 3 M Gaussians every block held its SM slot while its warp 0 waited for 32 predecessors.
+__global__ void __launch_bounds__(1024) scan_block_totals_kernel(uint64_t* status, int nblocks, ghr_geom_header* hdr, int32_t* n_host)
+{
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nblocks; base += 1024) {
+        const int i = base + t;
+        const uint32_t x = i < nblocks ? (uint32_t)status[i] : 0u;
+        uint32_t v = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += y;
+        }
+        if (lane == 31) s_warp[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += y;
+            }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        const uint32_t incl = s_carry + (warp ? s_warp[warp - 1] : 0u) + v;
+        if (i < nblocks) status[i] = incl - x;  // exclusive prefix of block i
+        __syncthreads();
+        if (t == 1023) s_carry = incl;
+        __syncthreads();
+    }
+    if (t == 0) {
+        hdr->num_rendered = s_carry;
+        if (n_host) *n_host = (int32_t)s_carry;
+    }
+}
+
+__global__ void __launch_bounds__(GHR_BLOCK) add_block_prefix_kernel(int P, const uint64_t* __restrict__ status,
+                                                                    uint32_t* __restrict__ point_offsets)
+{
+    const int idx = blockIdx.x * GHR_BLOCK + threadIdx.x;
+    if (idx < P && blockIdx.x) point_offsets[idx] += (uint32_t)status[blockIdx.x];
 }
 
 __global__ void __launch_bounds__(GHR_BLOCK) mark_visible_kernel(int P, const float* __restrict__ means3D,
@@ -87,11 +140,17 @@ cudaError_t launch_preprocess(const ghr_raster_params& p, int32_t* radii, char* 
     a.n_host = n_host;
     a.nblocks = (p.P + GHR_BLOCK - 1) / GHR_BLOCK;
     a.skip_rgb = 0;
+    a.split_scan = p.P > kSplitScanP;
     // header + look-back words are contiguous: one memset
     cudaError_t e = cudaMemsetAsync(geom + L.g_header, 0, L.g_rec - L.g_header, s);
     if (e != cudaSuccess) return e;
     preprocess_kernel<<<a.nblocks, GHR_BLOCK, 0, s>>>(a);
     count_launch();
+    if (a.split_scan) {
+        scan_block_totals_kernel<<<1, 1024, 0, s>>>(a.scan_status, a.nblocks, a.hdr, n_host);
+        add_block_prefix_kernel<<<a.nblocks, GHR_BLOCK, 0, s>>>(p.P, a.scan_status, a.point_offsets);
+        count_launch(2);
+    }
     return cudaGetLastError();
 }
 

@@ -25,6 +25,7 @@ struct PreArgs {
     int32_t* n_host;
     int nblocks;
     int skip_rgb;  // view-batched alpha-only rendering: the SH -> RGB evaluation is left out (rgb = 0)
+    int split_scan;  // 1: large P -- blocks only publish their tile count (no look-back); two small kernels finish the scan
 };
 
 constexpr uint64_t kFlagAgg = 1ull << 32;
@@ -101,6 +102,9 @@ __device__ __forceinline__ void finish_preprocess_block(const PreArgs& a, int ti
         // exclusive prefix over warps = inclusive of the previous warp
         const uint32_t prev = __shfl_up_sync(0xffffffffu, w, 1);
         if (lane < 8) s_warp[lane] = (lane == 0) ? 0u : prev;
+        if (a.split_scan) {  // the block's total goes to its status word; scan_block_totals_kernel / add_block_prefix_kernel follow
+            if (lane == 0) { a.scan_status[tile] = block_total; s_excl = 0; }
+        } else {
         const uint32_t excl = lookback_exclusive(a.scan_status, tile, block_total);
         if (lane == 0) {
             s_excl = excl;
@@ -108,6 +112,7 @@ __device__ __forceinline__ void finish_preprocess_block(const PreArgs& a, int ti
                 a.hdr->num_rendered = excl + block_total;
                 if (a.n_host) *a.n_host = (int32_t)(excl + block_total);
             }
+        }
         }
     }
     __syncthreads();

@@ -338,6 +338,7 @@ int ghr_forward_views(const ghr_raster_params* prm, int32_t n_views, const float
     a.hdr = reinterpret_cast<ghr_geom_header*>(w + L.header);
     a.n_host = nullptr;
     a.skip_rgb = want_color ? 0 : 1;
+    a.split_scan = 0;
     va.n_views = n_views; va.cameras = cameras; va.labels = labels; va.skip = skip_labels;
     va.total = (int64_t)prm->P * n_views;
     a.nblocks = (int)((va.total + GHR_BLOCK * kViewsSlots - 1) / (GHR_BLOCK * kViewsSlots));
