@@ -6,11 +6,8 @@
 
 namespace ghr {
 
-// One warp handles 32 Gaussians.  Gaussians touching few tiles are emitted by
-// their own lane; a Gaussian touching >= 32 tiles is emitted cooperatively by
-// the whole warp (lane-contiguous 8-B/4-B stores) so a screen-filling splat
-// does not serialise on one thread.  The emitted order (y-major, then x,
-// starting at point_offsets[idx-1]) is the reference's.
+// One warp handles 32 Gaussians and writes their pairs -- one contiguous range of the list -- cooperatively (see the
+// comment in the kernel).  The emitted order (y-major, then x, starting at point_offsets[idx-1]) is the reference's.
 __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int H,
                                                               const uint32_t* __restrict__ tiles_touched,
                                                               const float4* __restrict__ rec,
@@ -23,37 +20,44 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
     const int idx = blockIdx.x * GHR_BLOCK + threadIdx.x;
     const uint32_t lane = lane_id();
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE, gy = (H + GHR_TILE - 1) / GHR_TILE;
-    uint32_t minx = 0, miny = 0, maxx = 0, maxy = 0, off = 0, dbits = 0;
+    uint32_t minx = 0, miny = 0, maxx = 0, maxy = 0, dbits = 0;
     // tiles_touched > 0  <=>  radii > 0 (preprocess stores both or neither)
     const bool visible = idx < P && tiles_touched[idx] > 0;
     if (visible) {
         const float4 r0 = rec[3 * (size_t)idx];
         get_rect(r0.x, r0.y, __float_as_int(r0.w), gx, gy, minx, miny, maxx, maxy);
-        off = idx == 0 ? 0u : point_offsets[idx - 1];
         dbits = __float_as_uint(r0.z);
     }
+    // where this Gaussian's pairs start: the exclusive scan of tiles_touched (monotone, so defined for culled ones too)
+    const int last = min(idx, P) - 1;
+    const uint32_t off = last < 0 ? 0u : point_offsets[last];
     const uint32_t w = maxx - minx;
     const uint32_t cnt = w * (maxy - miny);
-    uint32_t big = __ballot_sync(0xffffffffu, cnt >= 32u);
-    if (cnt > 0 && cnt < 32u) {
-        for (uint32_t ty = miny; ty < maxy; ty++)
-            for (uint32_t tx = minx; tx < maxx; tx++) {
-                keys[off] = ((uint64_t)(ty * gx + tx) << 32) | dbits;
-                vals[off] = (uint32_t)idx;
-                off++;
-            }
-    }
-    while (big) {
-        const int src = __ffs(big) - 1;
-        big &= big - 1;
-        const uint32_t b_minx = __shfl_sync(0xffffffffu, minx, src), b_miny = __shfl_sync(0xffffffffu, miny, src);
-        const uint32_t b_w = __shfl_sync(0xffffffffu, w, src), b_cnt = __shfl_sync(0xffffffffu, cnt, src);
-        const uint32_t b_off = __shfl_sync(0xffffffffu, off, src), b_d = __shfl_sync(0xffffffffu, dbits, src);
-        const uint32_t b_idx = (uint32_t)(idx - (int)lane + src);
-        for (uint32_t k = lane; k < b_cnt; k += 32) {
-            const uint32_t ty = b_miny + k / b_w, tx = b_minx + k % b_w;
-            keys[b_off + k] = ((uint64_t)(ty * gx + tx) << 32) | b_d;
-            vals[b_off + k] = b_idx;
+    // The 32 Gaussians of a warp own ONE contiguous range of the pair list.  The warp writes it slot by slot -- lane l takes
+    // slots l, l + 32, ... -- so every store instruction covers 32 consecutive pairs (256 + 128 contiguous bytes) whatever
+    // the Gaussians' tile counts are; the owner of a slot is found by a 5-step search over the lanes' start offsets.
+    // (One thread per Gaussian writing its own pairs issued up to 31 scattered store pairs per thread: ncu at 12 M pairs,
+    // lg_throttle 7 + long_scoreboard 16 warps per issued instruction.)  Emitted order: the reference's (y-major, then x).
+    const uint32_t base = __shfl_sync(0xffffffffu, off, 0);
+    const uint32_t rel = off - base;
+    const uint32_t total = __shfl_sync(0xffffffffu, rel + cnt, 31);
+    for (uint32_t j0 = 0; j0 < total; j0 += 32) {
+        const uint32_t j = j0 + lane;
+        uint32_t lo = 0, hi = 31;
+#pragma unroll
+        for (int it = 0; it < 5; it++) {
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            const uint32_t v = __shfl_sync(0xffffffffu, rel, mid);
+            if (v <= j) lo = mid; else hi = mid - 1;
+        }
+        const uint32_t o_rel = __shfl_sync(0xffffffffu, rel, lo), o_w = __shfl_sync(0xffffffffu, w, lo);
+        const uint32_t o_minx = __shfl_sync(0xffffffffu, minx, lo), o_miny = __shfl_sync(0xffffffffu, miny, lo);
+        const uint32_t o_d = __shfl_sync(0xffffffffu, dbits, lo);
+        if (j < total) {
+            const uint32_t k = j - o_rel;
+            const uint32_t ty = o_miny + k / o_w, tx = o_minx + k % o_w;
+            keys[base + j] = ((uint64_t)(ty * gx + tx) << 32) | o_d;
+            vals[base + j] = (uint32_t)(idx - (int)lane) + lo;
         }
     }
 }
