@@ -121,6 +121,45 @@ __global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_kernel(ghr_geom_header*
     }
 }
 
+// Throughput regime (the wide blend kernels cull inside, no block masks): tile boundaries only -- a pure stream over the
+// sorted keys.  Four consecutive keys per thread per step (two 16-byte loads in flight + the predecessor's key): the
+// one-key-per-iteration loop above sat on long_scoreboard (35 warps per issued instruction at 12 M pairs, 1.7 TB/s).
+__global__ void __launch_bounds__(GHR_BLOCK) tile_ranges_only_kernel(ghr_geom_header* hdr, int64_t capacity,
+                                                                     const SortHeader* __restrict__ sh,
+                                                                     const uint64_t* __restrict__ keys_a,
+                                                                     const uint64_t* __restrict__ keys_b, uint2* ranges)
+{
+    const int64_t L = hdr->num_rendered;
+    if (L > capacity) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicMax(&hdr->error, (uint32_t)(-GHR_ERR_CAPACITY));
+        return;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && hdr->error == (uint32_t)(-GHR_ERR_CAPACITY)) hdr->error = 0;
+    const uint64_t* __restrict__ keys = sh->sorted_sel ? keys_b : keys_a;
+    const int64_t stride = (int64_t)gridDim.x * GHR_BLOCK * 4;
+    for (int64_t i0 = ((int64_t)blockIdx.x * GHR_BLOCK + threadIdx.x) * 4; i0 < L; i0 += stride) {
+        uint32_t t[5];  // tile ids of entries i0-1 .. i0+3
+        if (i0 + 4 <= L) {
+            const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(keys + i0);
+            const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(keys + i0 + 2);
+            t[1] = (uint32_t)(a.x >> 32); t[2] = (uint32_t)(a.y >> 32); t[3] = (uint32_t)(b.x >> 32); t[4] = (uint32_t)(b.y >> 32);
+        } else {
+#pragma unroll
+            for (int u = 0; u < 4; u++) t[1 + u] = i0 + u < L ? (uint32_t)(keys[i0 + u] >> 32) : 0u;
+        }
+        t[0] = i0 ? (uint32_t)(keys[i0 - 1] >> 32) : 0u;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int64_t idx = i0 + u;
+            if (idx >= L) break;
+            const uint32_t cur = t[1 + u];
+            if (idx == 0) ranges[cur].x = 0;
+            else if (cur != t[u]) { ranges[t[u]].y = (uint32_t)idx; ranges[cur].x = (uint32_t)idx; }
+            if (idx == L - 1) ranges[cur].y = (uint32_t)L;
+        }
+    }
+}
+
 // Tile ids ordered by decreasing list length (power-of-two buckets): the blend kernels pull (tile, block)
 // work items from a queue in this order, so the few heavy tiles of a human-shaped scene start first and
 // spread over all SMs (longest-processing-time-first) instead of landing wherever blockIdx order puts them.
@@ -237,6 +276,16 @@ cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, cha
     int64_t grid = (capacity + GHR_BLOCK - 1) / GHR_BLOCK;
     if (grid > sm_count() * 16) grid = sm_count() * 16;
     if (grid < 1) grid = 1;
+    if (blend_throughput_regime(capacity)) {
+        int64_t g4 = (capacity / 4 + GHR_BLOCK - 1) / GHR_BLOCK;
+        if (g4 > sm_count() * 16) g4 = sm_count() * 16;
+        if (g4 < 1) g4 = 1;
+        tile_ranges_only_kernel<<<(unsigned)g4, GHR_BLOCK, 0, s>>>(
+            reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header), capacity,
+            reinterpret_cast<const SortHeader*>(binning + L.b_header),
+            reinterpret_cast<const uint64_t*>(binning + L.b_keys_a), reinterpret_cast<const uint64_t*>(binning + L.b_keys_b),
+            reinterpret_cast<uint2*>(img + L.i_ranges));
+    } else
     tile_ranges_kernel<<<(unsigned)grid, GHR_BLOCK, 0, s>>>(
         reinterpret_cast<ghr_geom_header*>(const_cast<char*>(geom) + L.g_header), capacity,
         (p.W + GHR_TILE - 1) / GHR_TILE, reinterpret_cast<const SortHeader*>(binning + L.b_header),
