@@ -212,6 +212,12 @@ int ghr_backward_finish(const ghr_raster_params* prm, const int32_t* radii, cons
  *                              gradients of the attributes (zeroed here)
  *   ghr_unpack_attribute_grads packed_grad -> dL_dcolors[k] ([P,3]; NULL entries are skipped)
  * `colors` / `dL_dcolors` are HOST arrays of n device pointers. */
+/* The sorted list of Gaussian ids in the binning buffer (reference: point_list) is uint32 per pair.  In frames with more
+ * than 2^22 pairs and fewer than 2^24 Gaussians the upper 8 bits of each value carry the mask of the tile's 8x4-pixel
+ * blocks the Gaussian can touch (written by the key emission, read by the blend kernels): AND the values with this
+ * mask to get the ids (0xFFFFFFFF when nothing is packed). */
+uint32_t ghr_point_list_id_mask(int32_t P, int64_t capacity);
+
 int ghr_attribute_stride(int n_attr);
 int ghr_attributes_fused(int64_t capacity);
 int ghr_pack_attributes(int32_t P, int n_attr, const float* const* colors, float* packed, void* stream);

@@ -113,6 +113,7 @@ SIGNATURES = {
     "ghr_backward_multi": (C.c_int, [C.POINTER(RasterParams), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
                                      C.c_int64, C.c_void_p, C.c_size_t] + [C.c_void_p] * 3 + [C.c_int]
                            + [C.c_void_p] * 13),
+    "ghr_point_list_id_mask": (C.c_uint32, [C.c_int32, C.c_int64]),
     "ghr_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ghr_sort_workspace_bytes": (C.c_size_t, [C.c_int64]),
     "ghr_sort_pairs_u64": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_size_t, C.c_void_p, C.c_void_p]),

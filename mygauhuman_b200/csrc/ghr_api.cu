@@ -220,6 +220,8 @@ int ghr_forward_render_multi(const ghr_raster_params* prm, void* geom, size_t ge
                                out_depth, out_alpha, n_attr, packed, out_images, stream);
 }
 
+uint32_t ghr_point_list_id_mask(int32_t P, int64_t capacity) { return wide_masks_packed(P, capacity) ? 0x00FFFFFFu : 0xFFFFFFFFu; }
+
 int ghr_attribute_stride(int n_attr) { return attr_stride(n_attr); }
 int ghr_attributes_fused(int64_t capacity) { return blend_throughput_regime(capacity) ? 0 : 1; }
 

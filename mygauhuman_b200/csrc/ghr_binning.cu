@@ -14,19 +14,22 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
                                                               const uint32_t* __restrict__ point_offsets,
                                                               const ghr_geom_header* __restrict__ hdr,
                                                               int64_t capacity, uint64_t* __restrict__ keys,
-                                                              uint32_t* __restrict__ vals)
+                                                              uint32_t* __restrict__ vals, int pack_masks)
 {
     if ((int64_t)hdr->num_rendered > capacity) return;  // overflow is latched by the ranges kernel
     const int idx = blockIdx.x * GHR_BLOCK + threadIdx.x;
     const uint32_t lane = lane_id();
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE, gy = (H + GHR_TILE - 1) / GHR_TILE;
-    uint32_t minx = 0, miny = 0, maxx = 0, maxy = 0, dbits = 0;
+    uint32_t minx = 0, miny = 0, maxx = 0, maxy = 0, dbits = 0, ext = 0;
+    float cpx = 0.f, cpy = 0.f;
     // tiles_touched > 0  <=>  radii > 0 (preprocess stores both or neither)
     const bool visible = idx < P && tiles_touched[idx] > 0;
     if (visible) {
         const float4 r0 = rec[3 * (size_t)idx];
         get_rect(r0.x, r0.y, __float_as_int(r0.w), gx, gy, minx, miny, maxx, maxy);
         dbits = __float_as_uint(r0.z);
+        cpx = r0.x; cpy = r0.y;
+        if (pack_masks) ext = __float_as_uint(rec[3 * (size_t)idx + 2].w);
     }
     // where this Gaussian's pairs start: the exclusive scan of tiles_touched (monotone, so defined for culled ones too)
     const int last = min(idx, P) - 1;
@@ -53,11 +56,41 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
         const uint32_t o_rel = __shfl_sync(0xffffffffu, rel, lo), o_w = __shfl_sync(0xffffffffu, w, lo);
         const uint32_t o_minx = __shfl_sync(0xffffffffu, minx, lo), o_miny = __shfl_sync(0xffffffffu, miny, lo);
         const uint32_t o_d = __shfl_sync(0xffffffffu, dbits, lo);
+        float o_px = 0.f, o_py = 0.f;
+        uint32_t o_ext = 0;
+        if (pack_masks) {
+            o_px = __shfl_sync(0xffffffffu, cpx, lo); o_py = __shfl_sync(0xffffffffu, cpy, lo);
+            o_ext = __shfl_sync(0xffffffffu, ext, lo);
+        }
         if (j < total) {
             const uint32_t k = j - o_rel;
             const uint32_t ty = o_miny + k / o_w, tx = o_minx + k % o_w;
             keys[base + j] = ((uint64_t)(ty * gx + tx) << 32) | o_d;
-            vals[base + j] = (uint32_t)(idx - (int)lane) + lo;
+            uint32_t v = (uint32_t)(idx - (int)lane) + lo;
+            if (pack_masks) {
+                // bit wb of the mask: the conservative bounding-box cull of block wb (8 wide, 4 high; wb = 2 * row + column)
+                // of this tile -- the very test blend_forward_wide_kernel ran per pair and block warp
+                float ex, ey;
+                unpack_cull_extent(o_ext, ex, ey);
+                uint32_t mx = 0, my = 0;
+#pragma unroll
+                for (uint32_t c = 0; c < 2; c++) {
+                    const float rx0 = (float)(tx * GHR_TILE + c * 8u), rx1 = (float)(tx * GHR_TILE + c * 8u + 7u);
+                    const float ddx = fmaxf(fmaxf(rx0 - o_px, o_px - rx1), 0.0f);
+                    mx |= (ddx > ex ? 0u : 1u) << c;
+                }
+#pragma unroll
+                for (uint32_t r = 0; r < 4; r++) {
+                    const float ry0 = (float)(ty * GHR_TILE + r * 4u), ry1 = (float)(ty * GHR_TILE + r * 4u + 3u);
+                    const float ddy = fmaxf(fmaxf(ry0 - o_py, o_py - ry1), 0.0f);
+                    my |= (ddy > ey ? 0u : 1u) << r;
+                }
+                uint32_t mask = 0;
+#pragma unroll
+                for (uint32_t r = 0; r < 4; r++) mask |= ((my >> r) & 1u) ? (mx << (2u * r)) : 0u;
+                v |= mask << 24;
+            }
+            vals[base + j] = v;
         }
     }
 }
@@ -261,7 +294,8 @@ cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binni
         reinterpret_cast<const float4*>(geom + L.g_rec),
         reinterpret_cast<const uint32_t*>(geom + L.g_point_offsets),
         reinterpret_cast<const ghr_geom_header*>(geom + L.g_header), capacity,
-        reinterpret_cast<uint64_t*>(binning + L.b_keys_a), reinterpret_cast<uint32_t*>(binning + L.b_vals_a));
+        reinterpret_cast<uint64_t*>(binning + L.b_keys_a), reinterpret_cast<uint32_t*>(binning + L.b_vals_a),
+        wide_masks_packed(p.P, capacity) ? 1 : 0);
     return cudaGetLastError();
 }
 

@@ -85,7 +85,8 @@ __global__ void __launch_bounds__(kWideBwdWarps * 32) blend_backward_wide_kernel
     const SortHeader* __restrict__ sh, const uint32_t* __restrict__ vals_a, const uint32_t* __restrict__ vals_b,
     const float4* __restrict__ rec, ghr_geom_header* __restrict__ hdr, int64_t capacity, const float* __restrict__ bg,
     const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
-    const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas, float* __restrict__ accum)
+    const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas, float* __restrict__ accum,
+    uint32_t id_mask /* 0x00FFFFFF when the list values carry block masks (wide_masks_packed) */)
 {
     constexpr int BATCH = kWideBwdBatch, NSTAGE = kWideBwdStages, PER_LANE = BATCH / 32;
     __shared__ __align__(16) float4 s_all[kWideBwdWarps][NSTAGE][BATCH * 3];
@@ -146,7 +147,7 @@ __global__ void __launch_bounds__(kWideBwdWarps * 32) blend_backward_wide_kernel
 #pragma unroll
             for (int u = 0; u < PER_LANE; u++) {
                 const int progress = round * BATCH + (int)lane + u * 32;
-                nid[u] = (round < rounds && progress < walk) ? point_list[range.x + (uint32_t)(walk - 1 - progress)] : 0xFFFFFFFFu;
+                nid[u] = (round < rounds && progress < walk) ? (point_list[range.x + (uint32_t)(walk - 1 - progress)] & id_mask) : 0xFFFFFFFFu;
             }
         };
         auto stage = [&](int buf) {
@@ -291,7 +292,7 @@ cudaError_t launch_blend_backward_wide(const ghr_raster_params& p, const char* g
         reinterpret_cast<const uint32_t*>(binning + L.b_vals_a), reinterpret_cast<const uint32_t*>(binning + L.b_vals_b),
         reinterpret_cast<const float4*>(geom + L.g_rec), hdr, L.capacity, p.background,
         reinterpret_cast<const float*>(img + L.i_final_T), reinterpret_cast<const uint32_t*>(img + L.i_n_contrib), dL_dpix,
-        dL_ddepth, dL_dalpha, accum);
+        dL_ddepth, dL_dalpha, accum, wide_masks_packed(p.P, L.capacity) ? 0x00FFFFFFu : 0xFFFFFFFFu);
     return cudaGetLastError();
 }
 

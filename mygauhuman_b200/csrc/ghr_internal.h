@@ -87,6 +87,11 @@ inline bool blend_throughput_regime(int64_t capacity)
     return capacity > (int64_t(1) << 22);
 }
 
+// Throughput regime: the sorted VALUE of a pair carries, above the 24-bit Gaussian id, the 8-bit mask of the tile's 8x4-pixel
+// blocks whose conservative bounding-box cull the Gaussian passes (computed once per pair by emit_keys instead of once per
+// pair AND block warp inside the blend kernel, and only survivors' records are staged).  Needs ids below 2^24.
+inline bool wide_masks_packed(int P, int64_t capacity) { return blend_throughput_regime(capacity) && P < (1 << 24); }
+
 // Several views share the GPU (views of a batch on several streams): the blend kernels then take half the staging
 // shared memory per warp so that two of them are co-resident on an SM.  Process-wide, set by ghr_set_shared_gpu()
 // (MultiLaneRenderStep), GHR_SHARED_GPU=0|1 overrides (tuning).

@@ -436,7 +436,11 @@ def state_views(P, capacity, W, H, geomBuffer, binningBuffer, imageBuffer):
         va = view(b, L.b_vals_a, capacity, torch.int32, 4)
         vb = view(b, L.b_vals_b, capacity, torch.int32, 4)
         out["point_list_keys"] = (kb if sel else ka)[:n]
-        out["point_list"] = (vb if sel else va)[:n]
+        ids = (vb if sel else va)[:n]
+        id_mask = int(lib().ghr_point_list_id_mask(int(P), int(capacity)))
+        if id_mask != 0xFFFFFFFF:  # large frames: the upper 8 bits of a list value are the pair's block mask
+            ids = ids & id_mask
+        out["point_list"] = ids
         out["sorted_sel"] = sel
         out["pass_trivial"] = view(b, L.b_header + 16, 8, torch.int32, 4)
     return out
