@@ -789,6 +789,17 @@ def measure_large(dev, flush, peak):
     from mygauhuman_b200 import _lib
     from mygauhuman_b200.diff_gaussian_rasterization import _C
     out = {}
+    # One frame owns the GPU here: leave the shared-GPU blend configuration the multi-lane step switched on (half the CTAs
+    # per SM, so that two views' blend kernels fit an SM together) for the duration of this measurement.
+    was_shared = _lib.lib().ghr_shared_gpu()
+    _lib.lib().ghr_set_shared_gpu(0)
+    try:
+        return _measure_large(dev, flush, peak, _lib, _C, out)
+    finally:
+        _lib.lib().ghr_set_shared_gpu(was_shared)
+
+
+def _measure_large(dev, flush, peak, _lib, _C, out):
     P, W, H = 3_000_000, 1920, 1080
     g = torch.Generator(device=dev).manual_seed(7)
     xyz = torch.rand(P, 3, device=dev, generator=g) * 10.0 - 5.0

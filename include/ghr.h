@@ -685,6 +685,7 @@ uint64_t ghr_launch_count(void);
  * (mygauhuman_b200.graphed.MultiLaneRenderStep), so per-view kernels should leave room for each other: the blend
  * kernels then stage half as many entries per warp and two of them fit an SM together.  Results do not change. */
 int ghr_set_shared_gpu(int on);
+int ghr_shared_gpu(void); /* the current setting */
 int ghr_profile_enable(int on);
 int ghr_profile_read(double* ms_out, int64_t* count_out);
 

@@ -175,6 +175,7 @@ SIGNATURES = {
     "ghr_ply_unpack_rows": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p] + [C.c_void_p] * 10),
     "ghr_launch_count": (C.c_uint64, []),
     "ghr_set_shared_gpu": (C.c_int, [C.c_int]),
+    "ghr_shared_gpu": (C.c_int, []),
     "ghr_profile_enable": (C.c_int, [C.c_int]),
     "ghr_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
 }

@@ -81,6 +81,8 @@ int ghr_set_shared_gpu(int on)
     return GHR_OK;
 }
 
+int ghr_shared_gpu(void) { return g_shared_gpu.load(std::memory_order_relaxed); }
+
 uint64_t ghr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 
