@@ -188,7 +188,8 @@ static int forward_render_impl(const ghr_raster_params* prm, void* geom, size_t 
                                    n_dev, capacity, L.sort_bits, reinterpret_cast<uint64_t*>(b + L.b_keys_a),
                                    reinterpret_cast<uint64_t*>(b + L.b_keys_b), reinterpret_cast<uint32_t*>(b + L.b_vals_a),
                                    reinterpret_cast<uint32_t*>(b + L.b_vals_b), s,
-                                   &reinterpret_cast<const ghr_geom_header*>(g + L.g_header)->depth_hi),
+                                   &reinterpret_cast<const ghr_geom_header*>(g + L.g_header)->depth_hi,
+                                   /*histogram_done=*/sort_histogram_in_emit(capacity)),
                        s, "sort");
         if (r != GHR_OK) return r;
     }

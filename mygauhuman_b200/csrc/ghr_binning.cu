@@ -3,6 +3,7 @@
 // HBM-stream kernels: emission 8*P + 12*V + 12*N bytes, ranges 8*N + 8*tiles.
 #include "ghr_common.cuh"
 #include "ghr_internal.h"
+#include "ghr_sort.cuh"
 
 namespace ghr {
 
@@ -14,9 +15,26 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
                                                               const uint32_t* __restrict__ point_offsets,
                                                               const ghr_geom_header* __restrict__ hdr,
                                                               int64_t capacity, uint64_t* __restrict__ keys,
-                                                              uint32_t* __restrict__ vals, int pack_masks)
+                                                              uint32_t* __restrict__ vals, int pack_masks,
+                                                              SortHeader* __restrict__ sort_hdr, int bits, int passes)
 {
+    // sort_hdr != NULL: this kernel also does the work of sort_histogram_kernel (ghr_sort.cu) -- the digit histograms of
+    // all passes over the keys it writes, and, in the last CTA to finish, the plan (bin bases, trivial passes, ping-pong
+    // sources) -- so the frame's sort starts with its first pass (one launch and one read of the keys fewer).
+    __shared__ uint32_t s_hist[kMaxPasses * kRadix];
+    __shared__ uint32_t s_scan[9];
+    __shared__ uint32_t s_trivial[kMaxPasses];
+    __shared__ uint32_t s_last;
     if ((int64_t)hdr->num_rendered > capacity) return;  // overflow is latched by the ranges kernel
+    Squeeze squeeze;
+    squeeze.lo = 0u; squeeze.L = 32u;
+    uint32_t lastmask = 0;
+    if (sort_hdr) {
+        for (int i = threadIdx.x; i < passes * kRadix; i += GHR_BLOCK) s_hist[i] = 0;
+        squeeze = load_squeeze(&hdr->depth_hi, bits);
+        lastmask = (1u << (bits - (passes - 1) * kRadixBits)) - 1u;
+        __syncthreads();
+    }
     const int idx = blockIdx.x * GHR_BLOCK + threadIdx.x;
     const uint32_t lane = lane_id();
     const uint32_t gx = (W + GHR_TILE - 1) / GHR_TILE, gy = (H + GHR_TILE - 1) / GHR_TILE;
@@ -65,7 +83,16 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
         if (j < total) {
             const uint32_t k = j - o_rel;
             const uint32_t ty = o_miny + k / o_w, tx = o_minx + k % o_w;
-            keys[base + j] = ((uint64_t)(ty * gx + tx) << 32) | o_d;
+            const uint64_t key = ((uint64_t)(ty * gx + tx) << 32) | o_d;
+            keys[base + j] = key;
+            if (sort_hdr) {
+                const uint64_t ks = squeezed(key, squeeze);
+                for (int p = 0; p < passes; p++) {
+                    uint32_t d = (uint32_t)(ks >> (p * kRadixBits)) & (uint32_t)(kRadix - 1);
+                    if (p == passes - 1) d &= lastmask;
+                    atomicAdd(&s_hist[p * kRadix + hist_col(d)], 1u);
+                }
+            }
             uint32_t v = (uint32_t)(idx - (int)lane) + lo;
             if (pack_masks) {
                 // bit wb of the mask: the conservative bounding-box cull of block wb (8 wide, 4 high; wb = 2 * row + column)
@@ -92,6 +119,54 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
             }
             vals[base + j] = v;
         }
+    }
+    if (!sort_hdr) return;
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * kRadix; i += GHR_BLOCK) {
+        const uint32_t c = s_hist[i];
+        if (c) atomicAdd(&sort_hdr->hist[i / kRadix][hist_col(i % kRadix)], c);  // hist_col is its own inverse
+    }
+    // the last CTA to get here owns the complete histograms and writes the plan (as sort_histogram_kernel does)
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(&sort_hdr->hist_done, 1u) == gridDim.x - 1u);
+    if (threadIdx.x < kMaxPasses) s_trivial[threadIdx.x] = 0;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const uint32_t N = hdr->num_rendered;
+    const int t = threadIdx.x;  // owns digits 2t and 2t + 1
+    for (int p = 0; p < passes; p++) {
+        const uint32_t c0 = __ldcg(&sort_hdr->hist[p][2 * t]), c1 = __ldcg(&sort_hdr->hist[p][2 * t + 1]);
+        if (c0 == N || c1 == N) s_trivial[p] = 1;  // N == 0 also lands here (every pass trivial)
+        // exclusive scan of c0 + c1 over the 256 threads
+        uint32_t inc = c0 + c1;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+            if ((int)lane >= o) inc += n;
+        }
+        if (lane == 31) s_scan[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t run = 0;
+            for (int w = 0; w < GHR_BLOCK / 32; w++) { const uint32_t x = s_scan[w]; s_scan[w] = run; run += x; }
+        }
+        __syncthreads();
+        const uint32_t excl = s_scan[threadIdx.x >> 5] + inc - (c0 + c1);
+        sort_hdr->bin_base[p][2 * t] = excl;
+        sort_hdr->bin_base[p][2 * t + 1] = excl + c0;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        uint32_t sel = 0;
+        for (int p = 0; p < passes; p++) {
+            sort_hdr->pass_trivial[p] = s_trivial[p];
+            sort_hdr->pass_src[p] = sel;
+            if (!s_trivial[p]) sel ^= 1u;
+        }
+        sort_hdr->sorted_sel = sel;
+        sort_hdr->num_passes = passes;
     }
 }
 
@@ -295,7 +370,9 @@ cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binni
         reinterpret_cast<const uint32_t*>(geom + L.g_point_offsets),
         reinterpret_cast<const ghr_geom_header*>(geom + L.g_header), capacity,
         reinterpret_cast<uint64_t*>(binning + L.b_keys_a), reinterpret_cast<uint32_t*>(binning + L.b_vals_a),
-        wide_masks_packed(p.P, capacity) ? 1 : 0);
+        wide_masks_packed(p.P, capacity) ? 1 : 0,
+        sort_histogram_in_emit(capacity) ? reinterpret_cast<SortHeader*>(binning + L.b_header) : nullptr, L.sort_bits,
+        L.sort_passes);
     return cudaGetLastError();
 }
 

@@ -92,6 +92,11 @@ inline bool blend_throughput_regime(int64_t capacity)
 // pair AND block warp inside the blend kernel, and only survivors' records are staged).  Needs ids below 2^24.
 inline bool wide_masks_packed(int P, int64_t capacity) { return blend_throughput_regime(capacity) && P < (1 << 24); }
 
+// Small frames: emit_keys also accumulates the sort's digit histograms and writes its plan (one launch and one pass over the
+// keys fewer: 58 -> 47 us of sort for 9 -> 16 us of emission at the ZJU shape).  At 12 M pairs its five shared-memory
+// atomics per pair cost more than the separate histogram kernel (emission 82 -> 174 us for 62 us of sort): not there.
+inline bool sort_histogram_in_emit(int64_t capacity) { return !blend_throughput_regime(capacity); }
+
 // Several views share the GPU (views of a batch on several streams): the blend kernels then take half the staging
 // shared memory per warp so that two of them are co-resident on an SM.  Process-wide, set by ghr_set_shared_gpu()
 // (MultiLaneRenderStep), GHR_SHARED_GPU=0|1 overrides (tuning).
@@ -138,9 +143,10 @@ cudaError_t launch_preprocess(const ghr_raster_params& p, int32_t* radii, char* 
 cudaError_t launch_emit_keys(const ghr_raster_params& p, char* geom, char* binning,
                              const ghr_layout& L, int64_t capacity, cudaStream_t s);
 // Sort N (device word) pairs held in A; header/status must be zeroed beforehand.
+// histogram_done: the digit histograms and the plan are already in `hdr` (written by emit_keys): no histogram kernel
 cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev, int64_t capacity, int bits,
                         uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, cudaStream_t s,
-                        const uint32_t* squeeze = nullptr /* device {depth_hi, ~depth_lo} of a depth|tile frame, or NULL */);
+                        const uint32_t* squeeze = nullptr, bool histogram_done = false /* device {depth_hi, ~depth_lo} of a depth|tile frame, or NULL */);
 cudaError_t launch_tile_ranges(const ghr_raster_params& p, const char* geom, char* binning, char* img,
                                const ghr_layout& L, int64_t capacity, cudaStream_t s);
 cudaError_t launch_blend_forward(const ghr_raster_params& p, const char* geom, const char* binning, char* img,

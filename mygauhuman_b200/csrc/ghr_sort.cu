@@ -25,6 +25,7 @@
 #include <type_traits>
 #include "ghr_common.cuh"
 #include "ghr_internal.h"
+#include "ghr_sort.cuh"
 
 namespace ghr {
 
@@ -37,38 +38,6 @@ static_assert(kSortThreads == kRadix, "one thread per digit in the scans");
 __device__ __forceinline__ int64_t sort_count(const uint32_t* n_dev, int64_t capacity)
 {
     return n_dev ? min((int64_t)*n_dev, capacity) : capacity;
-}
-
-// Squeezed keys.  A depth|tile key is (tile << 32) | bits(depth) and the depths of one frame span a narrow range (a
-// body 2.4 .. 3.6 m from the camera: sign, exponent and nothing else are constant), so the key's low word minus the
-// frame's smallest depth needs only L = bit-length(max - min) bits, and the digits are taken from
-//     sq(key) = (low32(key) - lo)  |  (high32(key) << L)        (L + tile bits instead of 32 + tile bits)
-// Order is preserved (lo <= every depth), the passes still move the ORIGINAL keys, and the passes left without any
-// varying bit become "all keys share this digit" -- the trivial passes the plan already skips.  A 512^2 .. 1080p body
-// frame goes from 5 radix passes to 4.  `sq` = {depth_hi, ~depth_lo} written by the preprocess kernel, or NULL
-// (generic sort: identity).
-struct Squeeze {
-    uint32_t lo, L;
-};
-__device__ __forceinline__ Squeeze load_squeeze(const uint32_t* sq, int bits)
-{
-    Squeeze q;
-    q.lo = 0u; q.L = 32u;
-    if (sq) {
-        const uint32_t hi = sq[0], lo = ~sq[1];
-        if (hi >= lo) {  // hi < lo: no visible Gaussian, no key
-            const uint32_t L = 32u - (uint32_t)__clz(hi - lo);
-            // only when it saves a pass: otherwise the plain digits are the better balanced ones (3 M Gaussians over
-            // 1 .. 11 m: 38 squeezed bits still take 5 passes, the last over 2 bits -- measured 9 % slower)
-            const int squeezed_bits = bits - 32 + (int)L;
-            if ((squeezed_bits + kRadixBits - 1) / kRadixBits < (bits + kRadixBits - 1) / kRadixBits) { q.lo = lo; q.L = L; }
-        }
-    }
-    return q;
-}
-__device__ __forceinline__ uint64_t squeezed(uint64_t key, Squeeze q)
-{
-    return (uint64_t)((uint32_t)key - q.lo) | ((key >> 32) << q.L);
 }
 
 // Exclusive scan of one value per thread over the 512-thread block.  s_warp: 17 words; two barriers inside.
@@ -97,13 +66,6 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp
     __syncthreads();
     return s_warp[warp] + inc - v;
 }
-
-// Column of digit d in a warp's row of shared-memory counters.  A digit that straddles the depth exponent and the tile id
-// (bits 27..35 of a 1080p key) takes values t * 32 + c with two or three c only: unswizzled, every such digit of a warp
-// lands in the same two or three banks and the leaders' read-modify-writes serialise (ncu: 2.5x the shared-memory
-// wavefronts of the other passes).  XOR-ing the upper digit bits into the bank bits keeps the map a bijection and keeps
-// "thread t owns digit t" conflict-free (a warp's 32 threads share t >> 5).
-__device__ __forceinline__ uint32_t hist_col(uint32_t d) { return d ^ (d >> 5); }
 
 __global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint64_t* __restrict__ keys,
                                                                       const uint32_t* __restrict__ n_dev,
@@ -337,7 +299,7 @@ static void launch_pass(int64_t tiles, uint64_t* keys_a, uint64_t* keys_b, uint3
 
 cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev, int64_t capacity, int bits,
                         uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, cudaStream_t s,
-                        const uint32_t* squeeze)
+                        const uint32_t* squeeze, bool histogram_done)
 {
     if (capacity <= 0) return cudaSuccess;
     StageTimer timer(GHR_STAGE_SORT, s);
@@ -346,8 +308,8 @@ cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev
     const int64_t tiles = sort_tiles(capacity);
     int64_t hg = (capacity + kSortThreads * 4 - 1) / (kSortThreads * 4);
     const int hgrid = (int)(hg < sm_count() * 4 ? hg : sm_count() * 4);
-    sort_histogram_kernel<<<hgrid, kSortThreads, 0, s>>>(keys_a, n_dev, capacity, bits, passes, hdr, squeeze);
-    count_launch(1 + passes);
+    if (!histogram_done) sort_histogram_kernel<<<hgrid, kSortThreads, 0, s>>>(keys_a, n_dev, capacity, bits, passes, hdr, squeeze);
+    count_launch((histogram_done ? 0 : 1) + passes);
     for (int p = 0; p < passes; p++) {
         const int rem = bits - p * kRadixBits;
         const uint32_t mask = rem >= kRadixBits ? (uint32_t)(kRadix - 1) : ((1u << rem) - 1u);
