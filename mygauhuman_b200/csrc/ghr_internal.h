@@ -95,7 +95,12 @@ inline bool wide_masks_packed(int P, int64_t capacity) { return blend_throughput
 // Small frames: emit_keys also accumulates the sort's digit histograms and writes its plan (one launch and one pass over the
 // keys fewer: 58 -> 47 us of sort for 9 -> 16 us of emission at the ZJU shape).  At 12 M pairs its five shared-memory
 // atomics per pair cost more than the separate histogram kernel (emission 82 -> 174 us for 62 us of sort): not there.
-inline bool sort_histogram_in_emit(int64_t capacity) { return !blend_throughput_regime(capacity); }
+inline bool sort_histogram_in_emit(int64_t capacity)
+{
+    static const int forced = [] { const char* e = getenv("GHR_HIST_IN_EMIT"); return e ? atoi(e) + 1 : 0; }();  // tuning only
+    if (forced) return forced == 2;
+    return !blend_throughput_regime(capacity);
+}
 
 // Several views share the GPU (views of a batch on several streams): the blend kernels then take half the staging
 // shared memory per warp so that two of them are co-resident on an SM.  Process-wide, set by ghr_set_shared_gpu()
