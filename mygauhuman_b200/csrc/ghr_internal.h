@@ -49,6 +49,7 @@ inline int sort_items_per_thread(int64_t capacity)
     static const int forced = [] { const char* e = getenv("GHR_SORT_ITEMS"); return e ? atoi(e) : 0; }();  // tuning only
     if (forced == 2 || forced == 4 || forced == 8) return forced;
     return capacity <= (int64_t(1) << 17) ? 2 : capacity <= (int64_t(3) << 17) ? 4 : 8;  // measured on B200
+    // (16 keys per thread, 64 KB of key staging: 1.128 ms vs 1.091 ms at 2^24 keys, 45 bits -- measured, not kept)
 }
 inline int64_t sort_tiles(int64_t capacity)
 {
