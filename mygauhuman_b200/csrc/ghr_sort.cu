@@ -27,6 +27,13 @@
 #include "ghr_internal.h"
 #include "ghr_sort.cuh"
 
+#ifndef GHR_SORT_RANK
+#define GHR_SORT_RANK 2
+#endif
+#ifndef GHR_SORT_MATCH_RUNS
+#define GHR_SORT_MATCH_RUNS 12  // of 31 neighbour pairs
+#endif
+
 namespace ghr {
 
 constexpr uint32_t kStAgg = 1u << 30;
@@ -162,7 +169,12 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(&hdr->ticket[pass], 1u);
-    for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&sm.hist[0][0])[i] = 0;
+    {
+        static_assert(kSortWarps * kRadix % (4 * kSortThreads) == 0, "counters are cleared four at a time");
+        uint4* z = reinterpret_cast<uint4*>(&sm.hist[0][0]);
+#pragma unroll
+        for (int i = 0; i < kSortWarps * kRadix / (4 * kSortThreads); i++) z[i * kSortThreads + tid] = make_uint4(0u, 0u, 0u, 0u);
+    }
     __syncthreads();
     const uint32_t tile = s_tile;
     const int64_t N = sort_count(n_dev, capacity);
@@ -172,6 +184,9 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 
     const int shift = pass * kRadixBits;
     const Squeeze squeeze = load_squeeze(sq, bits);
+    // The tile's work, specialised for a full tile (all but the last one): no bounds test on any key.
+    auto run = [&](auto full_tile) {
+    constexpr bool FULL = decltype(full_tile)::value;
     uint64_t key[ITEMS];
     uint32_t val[ITEMS];
     uint32_t pos[ITEMS];  // first: digit << 16 | rank among the warp's keys of that digit; then: tile-local position
@@ -179,15 +194,58 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const int idx = wbase + i * 32;
-        if (idx < valid) { key[i] = kin[tile_start + idx]; val[i] = vin[tile_start + idx]; }
+        if (FULL || idx < valid) { key[i] = kin[tile_start + idx]; val[i] = vin[tile_start + idx]; }
         else { key[i] = ~0ull; val[i] = 0; }
     }
     const uint32_t lt = lanemask_lt();
+    // Rank of a key among the warp's keys of the same digit.  MATCH.ANY's latency grows with the number of distinct
+    // values in the warp.  A warp of random 9-bit digits holds ~31 of them, and one ballot per digit bit is faster
+    // (2^24 random keys: 1.10 ms with MATCH.ANY, 0.96 ms with the ballots).  The keys of a frame are the opposite case:
+    // a Gaussian's tiles are emitted together and share their depth, the stable passes keep them together, and a warp
+    // holds a handful of distinct depth digits (3 M Gaussians at 1080p: 671 us with MATCH.ANY, 703 us with the ballots).
+    // So a warp looks at its first 32 keys -- how many equal their left neighbour's digit -- and takes MATCH.ANY when
+    // the digits come in runs.  GHR_SORT_RANK: 0 always MATCH.ANY, 1 always ballots, 2 (default) per warp.
+    // (Also measured, both slower: all eight peer masks before the first counter update, 1.00 ms; that plus one shared
+    // atomicAdd per leader instead of its load + store, 1.02 ms.)
+    auto digit_of = [&](int i, bool ok) {
+        return ok ? ((uint32_t)(squeezed(key[i], squeeze) >> shift) & digit_mask) : (uint32_t)kRadix;
+    };
+    auto ballot_peers = [&](uint32_t d, bool ok) {
+        uint32_t peers = 0xffffffffu;
+        if (!FULL) { peers = __ballot_sync(0xffffffffu, ok); if (!ok) peers = ~peers; }
+#pragma unroll
+        for (int b = 0; b < kRadixBits; b++) {
+            uint32_t v;  // the lanes whose digit agrees with this lane's in bit b
+            asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 t;\n\t"
+                         "and.b32 t, %1, %2;\n\tsetp.ne.u32 p, t, 0;\n\t"
+                         "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t@!p not.b32 %0, %0;\n\t}"
+                         : "=r"(v) : "r"(d), "r"(1u << b));
+            peers &= v;
+        }
+        return peers;
+    };
+#if GHR_SORT_RANK == 2
+    bool runs;
+    {
+        const uint32_t d0 = digit_of(0, FULL || wbase < valid);
+        const uint32_t left = __shfl_up_sync(0xffffffffu, d0, 1);
+        runs = __popc(__ballot_sync(0xffffffffu, lane != 0 && d0 == left)) >= GHR_SORT_MATCH_RUNS;
+    }
+#endif
+    auto peers_of = [&](uint32_t d, bool ok) {
+#if GHR_SORT_RANK == 0
+        return __match_any_sync(0xffffffffu, d);
+#elif GHR_SORT_RANK == 1
+        return ballot_peers(d, ok);
+#else
+        return runs ? __match_any_sync(0xffffffffu, d) : ballot_peers(d, ok);
+#endif
+    };
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
-        const bool ok = (wbase + i * 32) < valid;
-        const uint32_t d = ok ? ((uint32_t)(squeezed(key[i], squeeze) >> shift) & digit_mask) : (uint32_t)kRadix;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const bool ok = FULL || (wbase + i * 32) < valid;
+        const uint32_t d = digit_of(i, ok);
+        const uint32_t peers = peers_of(d, ok);
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
         if (ok && lane == leader) {
@@ -220,12 +278,12 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const uint32_t d = pos[i] >> 16;
-        pos[i] = d < (uint32_t)kRadix ? sm.hist[warp][hist_col(d)] + (pos[i] & 0xFFFFu) : 0xFFFFFFFFu;
+        pos[i] = (FULL || d < (uint32_t)kRadix) ? sm.hist[warp][hist_col(d)] + (pos[i] & 0xFFFFu) : 0xFFFFFFFFu;
     }
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < ITEMS; i++)
-        if (pos[i] != 0xFFFFFFFFu) sm.keys[pos[i]] = key[i];
+        if (FULL || pos[i] != 0xFFFFFFFFu) sm.keys[pos[i]] = key[i];
 
     // decoupled look-back over the predecessors' counts of digit t, four tiles per round trip
     {
@@ -270,7 +328,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
         const int idx = k * kSortThreads + tid;
-        if (idx < valid) {
+        if (FULL || idx < valid) {
             const uint64_t kk = sm.keys[idx];
             dst[k] = s_base[(uint32_t)(squeezed(kk, squeeze) >> shift) & digit_mask] + idx;
             kout[dst[k]] = kk;
@@ -279,13 +337,16 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < ITEMS; i++)
-        if (pos[i] != 0xFFFFFFFFu) sm.vals[pos[i]] = val[i];
+        if (FULL || pos[i] != 0xFFFFFFFFu) sm.vals[pos[i]] = val[i];
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
         const int idx = k * kSortThreads + tid;
-        if (idx < valid) vout[dst[k]] = sm.vals[idx];
+        if (FULL || idx < valid) vout[dst[k]] = sm.vals[idx];
     }
+    };
+    if (valid == TILE) run(std::true_type{});
+    else run(std::false_type{});
 }
 
 template <int ITEMS>
