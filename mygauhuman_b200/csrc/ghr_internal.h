@@ -47,9 +47,11 @@ struct SortHeader {
 inline int sort_items_per_thread(int64_t capacity)
 {
     static const int forced = [] { const char* e = getenv("GHR_SORT_ITEMS"); return e ? atoi(e) : 0; }();  // tuning only
-    if (forced == 2 || forced == 4 || forced == 8) return forced;
-    return capacity <= (int64_t(1) << 17) ? 2 : capacity <= (int64_t(3) << 17) ? 4 : 8;  // measured on B200
-    // (16 keys per thread, 64 KB of key staging: 1.128 ms vs 1.091 ms at 2^24 keys, 45 bits -- measured, not kept)
+    if (forced == 2 || forced == 4 || forced == 8 || forced == 12 || forced == 16) return forced;
+    // Measured on B200 (45-bit keys; us at 8 / 12 / 16 keys per thread): 5.2e5 keys 81 / 85 / 97, 7.9e5 105 / 95 / 105,
+    // 1.6e6 155 / 136 / 146, 3.1e6 222 / 214 / 214, 8.4e6 484 / 433 / 449, 1.7e7 900 / 781 / 823.  A tile's fixed work
+    // (512 digit scans and look-backs) is spread over more keys; 16 spills at 64 registers.
+    return capacity <= (int64_t(1) << 17) ? 2 : capacity <= (int64_t(3) << 17) ? 4 : capacity <= (int64_t(5) << 17) ? 8 : 12;
 }
 inline int64_t sort_tiles(int64_t capacity)
 {
@@ -66,7 +68,7 @@ inline size_t sort_status_bytes(int passes, int64_t capacity)
 inline size_t sort_status_bytes_monotone(int passes, int64_t capacity)
 {
     size_t b = sort_status_bytes(passes, capacity);
-    const int64_t thresholds[2] = {int64_t(1) << 17, int64_t(3) << 17};  // regime ends of sort_items_per_thread
+    const int64_t thresholds[3] = {int64_t(1) << 17, int64_t(3) << 17, int64_t(5) << 17};  // regime ends of sort_items_per_thread
     for (int64_t t : thresholds)
         if (capacity > t) { const size_t at = sort_status_bytes(passes, t); b = b > at ? b : at; }
     return b;

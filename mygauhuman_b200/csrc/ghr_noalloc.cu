@@ -22,8 +22,8 @@ constexpr int64_t kStaticMaxKeys = int64_t(1) << 20;  // == GHR_STATIC_SORT_MAX_
 static_assert(kStaticMaxKeys == GHR_STATIC_SORT_MAX_KEYS, "header and kernel file disagree on the limit");
 
 // The largest workspace ghr_sort_workspace_bytes() asks for at any N <= kStaticMaxKeys.  sort_tiles() is not monotone in
-// N (keys per tile grow 1024 -> 2048 -> 4096 at 2^17 and 3*2^17 keys), so take the maximum over the three regimes:
-// 128, 192 and 256 tiles.
+// N (keys per tile grow 1024 -> 2048 -> 4096 -> 6144 at 2^17, 3*2^17 and 5*2^17 keys), so take a bound on the maximum
+// over the regimes (128, 192, 160 and 171 tiles): 256 tiles.
 constexpr size_t kHeaderBytes = (sizeof(SortHeader) + 255) / 256 * 256;
 constexpr size_t kStatusBytes = sizeof(uint32_t) * (size_t)kMaxPasses * 256 * (size_t)kRadix;
 constexpr size_t kScratchBytes = kHeaderBytes + kStatusBytes + 256;

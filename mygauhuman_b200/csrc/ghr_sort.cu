@@ -30,6 +30,9 @@
 #ifndef GHR_SORT_RANK
 #define GHR_SORT_RANK 2
 #endif
+#ifndef GHR_SORT_CTAS3
+#define GHR_SORT_CTAS3 0
+#endif
 #ifndef GHR_SORT_MATCH_RUNS
 #define GHR_SORT_MATCH_RUNS 12  // of 31 neighbour pairs
 #endif
@@ -139,7 +142,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint
 }
 
 template <int ITEMS>
-__global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t* keys_a, uint64_t* keys_b,
+__global__ void __launch_bounds__(kSortThreads, (GHR_SORT_CTAS3 && ITEMS <= 4) ? 3 : 2) onesweep_pass_kernel(uint64_t* keys_a, uint64_t* keys_b,
                                                                         uint32_t* vals_a, uint32_t* vals_b,
                                                                         const uint32_t* __restrict__ n_dev,
                                                                         int64_t capacity, int pass, uint32_t digit_mask,
@@ -149,26 +152,31 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 {
     constexpr int TILE = kSortThreads * ITEMS;
     // hist: per-warp digit counts, then (after the scans) the tile-local position of each warp's first key of each
-    // digit.  Once every key knows its position the same storage stages the keys, then the values.
+    // digit.  Once every key knows its position the same storage stages the keys; the values have their own, so that
+    // keys and values are staged together before the look-back and written out together after it (five block barriers
+    // per tile instead of seven, and the two global stores of a pair issue back to back).
     union Stage {
         uint32_t hist[kSortWarps][kRadix];
         uint64_t keys[TILE];
-        uint32_t vals[TILE];
     };
-    __shared__ Stage sm;
+    extern __shared__ __align__(16) unsigned char sm_raw[];  // sized in launch_pass
+    Stage& sm = *reinterpret_cast<Stage*>(sm_raw);
+    uint32_t* s_vals = reinterpret_cast<uint32_t*>(sm_raw + sizeof(Stage));
     __shared__ uint32_t s_base[kRadix];  // global offset of the tile's digit run minus its tile-local start
     __shared__ uint32_t s_warp[kSortWarps + 1];
     __shared__ uint32_t s_tile;
 
-    if (hdr->pass_trivial[pass]) return;
-    const uint32_t src = hdr->pass_src[pass];
-    const uint64_t* __restrict__ kin = src ? keys_b : keys_a;
-    const uint32_t* __restrict__ vin = src ? vals_b : vals_a;
-    uint64_t* __restrict__ kout = src ? keys_a : keys_b;
-    uint32_t* __restrict__ vout = src ? vals_a : vals_b;
-
+    // Everything the tile needs from global memory before its keys is asked for at once -- the ticket, the plan's two
+    // words, the key count, the squeeze -- instead of one dependent round trip after the other (a tile is ~8 us long and
+    // two are resident per SM: each round trip saved is throughput).
+    // (Measured and not kept: persistent CTAs, two per SM, that ask for the next tile's ticket while ranking the
+    // current one -- 0.961 vs 0.918 ms at 2^24 keys, 662 vs 642 us on the 3 M-Gaussian frame.)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(&hdr->ticket[pass], 1u);
+    const uint32_t trivial = hdr->pass_trivial[pass];
+    const uint32_t src = hdr->pass_src[pass];
+    const int64_t N = sort_count(n_dev, capacity);
+    const Squeeze squeeze = load_squeeze(sq, bits);
     {
         static_assert(kSortWarps * kRadix % (4 * kSortThreads) == 0, "counters are cleared four at a time");
         uint4* z = reinterpret_cast<uint4*>(&sm.hist[0][0]);
@@ -176,14 +184,16 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
         for (int i = 0; i < kSortWarps * kRadix / (4 * kSortThreads); i++) z[i * kSortThreads + tid] = make_uint4(0u, 0u, 0u, 0u);
     }
     __syncthreads();
+    if (trivial) return;
+    const uint64_t* __restrict__ kin = src ? keys_b : keys_a;
+    const uint32_t* __restrict__ vin = src ? vals_b : vals_a;
+    uint64_t* __restrict__ kout = src ? keys_a : keys_b;
+    uint32_t* __restrict__ vout = src ? vals_a : vals_b;
     const uint32_t tile = s_tile;
-    const int64_t N = sort_count(n_dev, capacity);
     const int64_t tile_start = (int64_t)tile * TILE;
     if (tile_start >= N) return;
     const int valid = (int)min((int64_t)TILE, N - tile_start);
-
     const int shift = pass * kRadixBits;
-    const Squeeze squeeze = load_squeeze(sq, bits);
     // The tile's work, specialised for a full tile (all but the last one): no bounds test on any key.
     auto run = [&](auto full_tile) {
     constexpr bool FULL = decltype(full_tile)::value;
@@ -194,8 +204,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const int idx = wbase + i * 32;
-        if (FULL || idx < valid) { key[i] = kin[tile_start + idx]; val[i] = vin[tile_start + idx]; }
-        else { key[i] = ~0ull; val[i] = 0; }
+        key[i] = (FULL || idx < valid) ? kin[tile_start + idx] : ~0ull;
     }
     const uint32_t lt = lanemask_lt();
     // Rank of a key among the warp's keys of the same digit.  MATCH.ANY's latency grows with the number of distinct
@@ -264,6 +273,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
     for (int w = 0; w < kSortWarps; w++) sum += sm.hist[w][hist_col(tid)];
     uint32_t* my = status + (size_t)tile * kRadix + tid;
     st_relaxed_u32(my, (tile == 0 ? kStIncl : kStAgg) | sum);
+    const uint32_t bin_base = hdr->bin_base[pass][tid];  // asked for here, used after the look-back
     const uint32_t tile_excl = block_excl_scan(sum, s_warp);
     {
         uint32_t run = tile_excl;
@@ -284,6 +294,13 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
 #pragma unroll
     for (int i = 0; i < ITEMS; i++)
         if (FULL || pos[i] != 0xFFFFFFFFu) sm.keys[pos[i]] = key[i];
+    // The values are asked for only now, with the keys' registers free again (more keys per thread fit in 64
+    // registers), and staged after the look-back, which hides their latency.
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const int idx = wbase + i * 32;
+        val[i] = (FULL || idx < valid) ? vin[tile_start + idx] : 0u;
+    }
 
     // decoupled look-back over the predecessors' counts of digit t, four tiles per round trip
     {
@@ -294,12 +311,8 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
             // Four predecessors per round trip.  (Measured: 16 per trip -- fewer dependent L2 round trips for the last tile
             // of a small sort, where all tiles of a pass publish their aggregates at once -- is SLOWER at both ends:
             // 64 vs 58 us at 1.8e5 keys, 764 vs 690 us at 1.2e7 keys; the extra words cost more than the trips save.)
-            auto walk = [&](auto look) {
+            auto consume = [&](auto look, const uint32_t* s) {
                 constexpr int kLook = decltype(look)::value;
-                uint32_t s[kLook];
-#pragma unroll
-                for (int u = 0; u < kLook; u++)
-                    s[u] = (j - u) >= 0 ? ld_relaxed_u32(status + (size_t)(j - u) * kRadix + tid) : kStIncl;
                 bool stall = false;
 #pragma unroll
                 for (int u = 0; u < kLook; u++) {
@@ -313,6 +326,14 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
                     }
                 }
             };
+            auto walk = [&](auto look) {
+                constexpr int kLook = decltype(look)::value;
+                uint32_t s[kLook];
+#pragma unroll
+                for (int u = 0; u < kLook; u++)
+                    s[u] = (j - u) >= 0 ? ld_relaxed_u32(status + (size_t)(j - u) * kRadix + tid) : kStIncl;
+                consume(look, s);
+            };
 #ifndef GHR_SORT_LOOK
 #define GHR_SORT_LOOK 4
 #endif
@@ -320,29 +341,22 @@ __global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t
             while (!done) walk(std::integral_constant<int, GHR_SORT_LOOK>{});
             st_relaxed_u32(my, kStIncl | (excl + sum));
         }
-        s_base[tid] = hdr->bin_base[pass][tid] + excl - tile_excl;
+        s_base[tid] = bin_base + excl - tile_excl;
     }
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++)
+        if (FULL || pos[i] != 0xFFFFFFFFu) s_vals[pos[i]] = val[i];
     __syncthreads();
 
-    uint32_t dst[ITEMS];
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
         const int idx = k * kSortThreads + tid;
         if (FULL || idx < valid) {
             const uint64_t kk = sm.keys[idx];
-            dst[k] = s_base[(uint32_t)(squeezed(kk, squeeze) >> shift) & digit_mask] + idx;
-            kout[dst[k]] = kk;
+            const uint32_t dst = s_base[(uint32_t)(squeezed(kk, squeeze) >> shift) & digit_mask] + idx;
+            kout[dst] = kk;
+            vout[dst] = s_vals[idx];
         }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++)
-        if (FULL || pos[i] != 0xFFFFFFFFu) sm.vals[pos[i]] = val[i];
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < ITEMS; k++) {
-        const int idx = k * kSortThreads + tid;
-        if (FULL || idx < valid) vout[dst[k]] = sm.vals[idx];
     }
     };
     if (valid == TILE) run(std::true_type{});
@@ -354,8 +368,16 @@ static void launch_pass(int64_t tiles, uint64_t* keys_a, uint64_t* keys_b, uint3
                         const uint32_t* n_dev, int64_t capacity, int p, uint32_t mask, SortHeader* hdr, uint32_t* st,
                         const uint32_t* sq, int bits, cudaStream_t s)
 {
-    onesweep_pass_kernel<ITEMS><<<(unsigned)tiles, kSortThreads, 0, s>>>(keys_a, keys_b, vals_a, vals_b, n_dev, capacity,
-                                                                         p, mask, hdr, st, sq, bits);
+    constexpr size_t tile_keys = (size_t)kSortThreads * ITEMS;
+    constexpr size_t hist_bytes = sizeof(uint32_t) * kSortWarps * kRadix;
+    constexpr size_t smem = (tile_keys * 8 > hist_bytes ? tile_keys * 8 : hist_bytes) + tile_keys * 4;
+    if (smem + 4096 > 48 * 1024) {  // with the kernel's static 2.1 KB: beyond what a launch gets without asking
+        static unsigned long long attr_set = 0ull;
+        if (first_use_on_current_device(attr_set))
+            cudaFuncSetAttribute(onesweep_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    }
+    onesweep_pass_kernel<ITEMS><<<(unsigned)tiles, kSortThreads, smem, s>>>(keys_a, keys_b, vals_a, vals_b, n_dev, capacity,
+                                                                            p, mask, hdr, st, sq, bits);
 }
 
 cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev, int64_t capacity, int bits,
@@ -377,6 +399,8 @@ cudaError_t launch_sort(SortHeader* hdr, uint32_t* status, const uint32_t* n_dev
         uint32_t* st = status + (size_t)p * tiles * kRadix;
         switch (items) {
             case 2: launch_pass<2>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, bits, s); break;
+            case 12: launch_pass<12>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, bits, s); break;
+            case 16: launch_pass<16>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, bits, s); break;
             case 4: launch_pass<4>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, bits, s); break;
             default: launch_pass<8>(tiles, keys_a, keys_b, vals_a, vals_b, n_dev, capacity, p, mask, hdr, st, squeeze, bits, s); break;
         }
