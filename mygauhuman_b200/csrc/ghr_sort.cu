@@ -199,7 +199,15 @@ __global__ void __launch_bounds__(kSortThreads, (GHR_SORT_CTAS3 && ITEMS <= 4) ?
     constexpr bool FULL = decltype(full_tile)::value;
     uint64_t key[ITEMS];
     uint32_t val[ITEMS];
-    uint32_t pos[ITEMS];  // first: digit << 16 | rank among the warp's keys of that digit; then: tile-local position
+    // Per key: first its rank among the warp's keys of the same digit, then its tile-local position (0xFFFF: no key).
+    // Both fit 16 bits (a tile holds at most 8192 keys), and two share a register: with the digit recomputed from the
+    // key instead of carried along, 16 keys per thread fit in 64 registers without a spill.
+    uint32_t pos2[(ITEMS + 1) / 2];
+    auto get_pos = [&](int i) { return (i & 1) ? (pos2[i >> 1] >> 16) : (pos2[i >> 1] & 0xFFFFu); };
+    auto set_pos = [&](int i, uint32_t v, bool first) {  // first: nothing of the register is in use yet
+        if (i & 1) pos2[i >> 1] = (pos2[i >> 1] & 0xFFFFu) | (v << 16);
+        else pos2[i >> 1] = first ? v : ((pos2[i >> 1] & 0xFFFF0000u) | v);
+    };
     const int wbase = warp * (32 * ITEMS) + lane;
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
@@ -262,7 +270,7 @@ __global__ void __launch_bounds__(kSortThreads, (GHR_SORT_CTAS3 && ITEMS <= 4) ?
             sm.hist[warp][hist_col(d)] = old + __popc(peers);
         }
         old = __shfl_sync(0xffffffffu, old, leader);
-        pos[i] = (d << 16) | (old + __popc(peers & lt));
+        set_pos(i, old + __popc(peers & lt), true);
         __syncwarp();
     }
     __syncthreads();
@@ -287,13 +295,14 @@ __global__ void __launch_bounds__(kSortThreads, (GHR_SORT_CTAS3 && ITEMS <= 4) ?
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
-        const uint32_t d = pos[i] >> 16;
-        pos[i] = (FULL || d < (uint32_t)kRadix) ? sm.hist[warp][hist_col(d)] + (pos[i] & 0xFFFFu) : 0xFFFFFFFFu;
+        const bool ok = FULL || (wbase + i * 32) < valid;
+        const uint32_t d = digit_of(i, ok);
+        set_pos(i, ok ? sm.hist[warp][hist_col(d)] + get_pos(i) : 0xFFFFu, false);
     }
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < ITEMS; i++)
-        if (FULL || pos[i] != 0xFFFFFFFFu) sm.keys[pos[i]] = key[i];
+        if (FULL || get_pos(i) != 0xFFFFu) sm.keys[get_pos(i)] = key[i];
     // The values are asked for only now, with the keys' registers free again (more keys per thread fit in 64
     // registers), and staged after the look-back, which hides their latency.
 #pragma unroll
@@ -345,7 +354,7 @@ __global__ void __launch_bounds__(kSortThreads, (GHR_SORT_CTAS3 && ITEMS <= 4) ?
     }
 #pragma unroll
     for (int i = 0; i < ITEMS; i++)
-        if (FULL || pos[i] != 0xFFFFFFFFu) s_vals[pos[i]] = val[i];
+        if (FULL || get_pos(i) != 0xFFFFu) s_vals[get_pos(i)] = val[i];
     __syncthreads();
 
 #pragma unroll
