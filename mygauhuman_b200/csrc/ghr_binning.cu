@@ -54,6 +54,10 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
     const uint32_t off = last < 0 ? 0u : point_offsets[last];
     const uint32_t w = maxx - minx;
     const uint32_t cnt = w * (maxy - miny);
+    // k / w for the slots of this Gaussian as one multiply-high: magic = ceil(2^32 / w) is exact for k * w < 2^32
+    // (k < the Gaussian's tile count).  w == 1 would need 33 bits: the loop takes k itself.
+    const uint32_t magic = w >= 2u ? 0xFFFFFFFFu / w + 1u : 0u;
+    const uint32_t minxy = minx | (miny << 16);
     // The 32 Gaussians of a warp own ONE contiguous range of the pair list.  The warp writes it slot by slot -- lane l takes
     // slots l, l + 32, ... -- so every store instruction covers 32 consecutive pairs (256 + 128 contiguous bytes) whatever
     // the Gaussians' tile counts are; the owner of a slot is found by a 5-step search over the lanes' start offsets.
@@ -72,7 +76,7 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
             if (v <= j) lo = mid; else hi = mid - 1;
         }
         const uint32_t o_rel = __shfl_sync(0xffffffffu, rel, lo), o_w = __shfl_sync(0xffffffffu, w, lo);
-        const uint32_t o_minx = __shfl_sync(0xffffffffu, minx, lo), o_miny = __shfl_sync(0xffffffffu, miny, lo);
+        const uint32_t o_magic = __shfl_sync(0xffffffffu, magic, lo), o_minxy = __shfl_sync(0xffffffffu, minxy, lo);
         const uint32_t o_d = __shfl_sync(0xffffffffu, dbits, lo);
         float o_px = 0.f, o_py = 0.f;
         uint32_t o_ext = 0;
@@ -82,7 +86,8 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
         }
         if (j < total) {
             const uint32_t k = j - o_rel;
-            const uint32_t ty = o_miny + k / o_w, tx = o_minx + k % o_w;
+            const uint32_t row = o_w == 1u ? k : __umulhi(k, o_magic);
+            const uint32_t ty = (o_minxy >> 16) + row, tx = (o_minxy & 0xFFFFu) + (k - row * o_w);
             const uint64_t key = ((uint64_t)(ty * gx + tx) << 32) | o_d;
             keys[base + j] = key;
             if (sort_hdr) {
@@ -99,23 +104,22 @@ __global__ void __launch_bounds__(GHR_BLOCK) emit_keys_kernel(int P, int W, int 
                 // of this tile -- the very test blend_forward_wide_kernel ran per pair and block warp
                 float ex, ey;
                 unpack_cull_extent(o_ext, ex, ey);
-                uint32_t mx = 0, my = 0;
+                // The same values in fewer instructions (this kernel is issue-bound at 1.2e7 pairs): the block edges are
+                // the tile origin, converted once, plus small constants (exact in fp32), and
+                // max(a, b, 0) > e  <=>  a > e || b > e  for the non-negative extents.
+                const float fx = (float)(tx * GHR_TILE), fy = (float)(ty * GHR_TILE);
+                uint32_t mx = 0, rows = 0;  // rows: bit 2r set when block row r passes
 #pragma unroll
                 for (uint32_t c = 0; c < 2; c++) {
-                    const float rx0 = (float)(tx * GHR_TILE + c * 8u), rx1 = (float)(tx * GHR_TILE + c * 8u + 7u);
-                    const float ddx = fmaxf(fmaxf(rx0 - o_px, o_px - rx1), 0.0f);
-                    mx |= (ddx > ex ? 0u : 1u) << c;
+                    const float rx0 = fx + (float)(c * 8u), rx1 = fx + (float)(c * 8u + 7u);
+                    mx |= ((rx0 - o_px > ex) || (o_px - rx1 > ex)) ? 0u : (1u << c);
                 }
 #pragma unroll
                 for (uint32_t r = 0; r < 4; r++) {
-                    const float ry0 = (float)(ty * GHR_TILE + r * 4u), ry1 = (float)(ty * GHR_TILE + r * 4u + 3u);
-                    const float ddy = fmaxf(fmaxf(ry0 - o_py, o_py - ry1), 0.0f);
-                    my |= (ddy > ey ? 0u : 1u) << r;
+                    const float ry0 = fy + (float)(r * 4u), ry1 = fy + (float)(r * 4u + 3u);
+                    rows |= ((ry0 - o_py > ey) || (o_py - ry1 > ey)) ? 0u : (1u << (2u * r));
                 }
-                uint32_t mask = 0;
-#pragma unroll
-                for (uint32_t r = 0; r < 4; r++) mask |= ((my >> r) & 1u) ? (mx << (2u * r)) : 0u;
-                v |= mask << 24;
+                v |= (rows * mx) << 24;  // mx in 0..3 lands in every passing row's two bits, no carries
             }
             vals[base + j] = v;
         }

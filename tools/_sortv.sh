@@ -1,10 +1,9 @@
-timeout 300 python -m pytest tests/test_sort_knn_gpu.py tests/test_zz_no_alloc.py -x -q 2>&1 | tail -2 | tee /tmp/t.log
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -2 | tee /tmp/t.log
 grep -q failed /tmp/t.log && exit 1
-for it in 12 16; do GHR_SORT_ITEMS=$it timeout 120 python -m pytest tests/test_sort_knn_gpu.py -x -q 2>&1 | tail -1; GHR_SORT_ITEMS=$it timeout 120 python tools/sort_items_sweep.py 2>&1 | tail -1; done
-for it in "" 16; do
-  echo "== items=${it:-auto}"
-  if [ -n "$it" ]; then export GHR_SORT_ITEMS=$it; else unset GHR_SORT_ITEMS; fi
-  timeout 120 python tools/large_probe.py 1 2>/dev/null | python -c "
+timeout 120 python tools/large_probe.py 1 2>/dev/null | python -c "
 import json,sys
-d=json.loads(sys.stdin.read()); s=d['stress_1080p_forward']; print('stress', s['fps'], s['stages']['sort']['us'], 'sort2p24', d['sort_2p24']['ms'])"
-done
+d=json.loads(sys.stdin.read()); s=d['stress_1080p_forward']; print('stress', s['fps'], {k:v['us'] for k,v in s['stages'].items()}, 'sort2p24', d['sort_2p24']['ms'])"
+timeout 200 python bench.py --no-cpu-baseline --no-extras --steps 60 --warmup 5 2>/dev/null | python -c "
+import json,sys
+b=json.loads([l for l in sys.stdin if l.startswith('{')][-1])
+print('zju', b['value'], b['ms_per_step'], {k:v['us'] for k,v in b['stages'].items() if k in ('sort','emit_keys')})"
