@@ -285,10 +285,42 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(int tiles, const uint2
     __shared__ uint32_t s_hist[33], s_base[33];
     const bool overflow = (int64_t)hdr->num_rendered > capacity;
     if (threadIdx.x < 33) s_hist[threadIdx.x] = 0;
+    // Up to 8192 tiles (1080p has 8160) every thread keeps its tiles' buckets in registers: the ranges are read once,
+    // all loads in flight together, instead of two passes of one dependent load each per 1024 tiles.
+    constexpr int kHeld = 8;
+    const bool held = tiles <= kHeld * 1024;
+    uint32_t bucket[kHeld];
+    if (held) {
+        uint2 r[kHeld];
+#pragma unroll
+        for (int k = 0; k < kHeld; k++) {
+            const int t = k * 1024 + threadIdx.x;
+            r[k] = t < tiles ? ranges[t] : make_uint2(0u, 0u);  // (not waiting for the overflow word)
+        }
+#pragma unroll
+        for (int k = 0; k < kHeld; k++) {
+            const uint32_t n = overflow ? 0u : r[k].y - r[k].x;
+            bucket[k] = n ? 32 - __clz(n) : 0;  // bucket b holds lengths in [2^(b-1), 2^b)
+        }
+    }
     __syncthreads();
-    for (int t = threadIdx.x; t < tiles; t += 1024) {
-        const uint32_t n = overflow ? 0u : ranges[t].y - ranges[t].x;
-        atomicAdd(&s_hist[n ? 32 - __clz(n) : 0], 1u);  // bucket b holds lengths in [2^(b-1), 2^b)
+    // A frame has a dozen distinct buckets: one shared-memory atomic per tile serialises 32-fold on the same word (ncu at
+    // 8160 tiles: 10 us, short_scoreboard).  The lanes of a warp that share a bucket are counted by their leader.
+    const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    if (held) {
+#pragma unroll
+        for (int k = 0; k < kHeld; k++) {
+            if (k * 1024 + (int)(threadIdx.x & ~31u) >= tiles) break;  // whole warp past the end
+            const bool in = k * 1024 + (int)threadIdx.x < tiles;
+            const uint32_t key = in ? bucket[k] : 33u;
+            const uint32_t peers = __match_any_sync(0xffffffffu, key);
+            if (in && (peers & lt) == 0u) atomicAdd(&s_hist[key], (uint32_t)__popc(peers));
+        }
+    } else {
+        for (int t = threadIdx.x; t < tiles; t += 1024) {
+            const uint32_t n = overflow ? 0u : ranges[t].y - ranges[t].x;
+            atomicAdd(&s_hist[n ? 32 - __clz(n) : 0], 1u);
+        }
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -296,9 +328,25 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(int tiles, const uint2
         for (int b = 32; b >= 0; b--) { s_base[b] = acc; acc += s_hist[b]; }
     }
     __syncthreads();
-    for (int t = threadIdx.x; t < tiles; t += 1024) {
-        const uint32_t n = overflow ? 0u : ranges[t].y - ranges[t].x;
-        order[atomicAdd(&s_base[n ? 32 - __clz(n) : 0], 1u)] = (uint32_t)t;
+    if (held) {
+#pragma unroll
+        for (int k = 0; k < kHeld; k++) {
+            if (k * 1024 + (int)(threadIdx.x & ~31u) >= tiles) break;
+            const int t = k * 1024 + threadIdx.x;
+            const bool in = t < tiles;
+            const uint32_t key = in ? bucket[k] : 33u;
+            const uint32_t peers = __match_any_sync(0xffffffffu, key);
+            const int leader = __ffs(peers) - 1;
+            uint32_t base = 0;
+            if (in && (int)lane == leader) base = atomicAdd(&s_base[key], (uint32_t)__popc(peers));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (in) order[base + __popc(peers & lt)] = (uint32_t)t;
+        }
+    } else {
+        for (int t = threadIdx.x; t < tiles; t += 1024) {
+            const uint32_t n = overflow ? 0u : ranges[t].y - ranges[t].x;
+            order[atomicAdd(&s_base[n ? 32 - __clz(n) : 0], 1u)] = (uint32_t)t;
+        }
     }
 }
 

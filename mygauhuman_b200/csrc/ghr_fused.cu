@@ -102,12 +102,13 @@ __global__ void __launch_bounds__(GHR_BLOCK) deform_project_kernel(const FusedFw
         };
         int radius;
         bool near_culled;
-        tiles = project_core(a, (size_t)idx, xw[0], xw[1], xw[2], opac, V, Pm, radius, near_culled, hint, cov3, rgbf);
+        float depth = 0.0f;
+        tiles = project_core(a, (size_t)idx, xw[0], xw[1], xw[2], opac, V, Pm, radius, near_culled, hint, cov3, rgbf, &depth);
         if (near_culled && a.prefiltered) atomicMax(&a.hdr->error, (uint32_t)(-GHR_ERR_PREFILTER));
         a.radii[idx] = radius;
         a.tiles_touched[idx] = tiles;
         if (tiles) {
-            dbits_hi = __float_as_uint(a.rec[3 * (size_t)idx].z);
+            dbits_hi = __float_as_uint(depth);
             dbits_lo_inv = ~dbits_hi;
         }
         if (!coloured && f.colors) {

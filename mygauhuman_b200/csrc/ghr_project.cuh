@@ -128,7 +128,7 @@ __device__ __forceinline__ void finish_preprocess_block(const PreArgs& a, int ti
 template <class HintFn, class Cov3Fn, class RgbFn>
 __device__ __forceinline__ uint32_t project_core(const PreArgs& a, size_t o, float x, float y, float z, float opac_in,
                                                  const float* V, const float* Pm, int& radius, bool& near_culled,
-                                                 HintFn hint, Cov3Fn cov3, RgbFn rgbf)
+                                                 HintFn hint, Cov3Fn cov3, RgbFn rgbf, float* depth_out = nullptr)
 {
     uint32_t tiles = 0;
     radius = 0;
@@ -171,6 +171,7 @@ __device__ __forceinline__ uint32_t project_core(const PreArgs& a, size_t o, flo
                 tiles = cnt;
                 float4* r = a.rec + 3 * o;
                 r[0] = make_float4(px, py, pvz, __int_as_float(ri));
+                if (depth_out) *depth_out = pvz;  // (reading it back from the record is a store -> load round trip to L2)
                 const float opac = opac_in;
                 r[1] = make_float4(con0, con1, con2, opac);
                 r[2] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(pack_cull_extent(con0, con1, con2, opac)));
@@ -183,7 +184,8 @@ __device__ __forceinline__ uint32_t project_core(const PreArgs& a, size_t o, flo
 // project_core over the rasteriser's own input arrays (reference forward.cu:156-256 preprocessCUDA): Gaussian `idx`,
 // record / cov3D / clamp slot `o`.
 __device__ __forceinline__ uint32_t project_gaussian(const PreArgs& a, int idx, size_t o, const float* V, const float* Pm,
-                                                     const float* cam, int& radius, bool& near_culled)
+                                                     const float* cam, int& radius, bool& near_culled,
+                                                     float* depth_out = nullptr)
 {
     const float x = a.means3D[3 * idx], y = a.means3D[3 * idx + 1], z = a.means3D[3 * idx + 2];
     // Every per-Gaussian input that does not depend on the culls is requested here, next to the mean, so that the
@@ -250,7 +252,7 @@ __device__ __forceinline__ uint32_t project_gaussian(const PreArgs& a, int idx, 
             if (a.clamped) a.clamped[o] = (uint8_t)cm;
         }
     };
-    return project_core(a, o, x, y, z, opac_in, V, Pm, radius, near_culled, hint, cov3, rgbf);
+    return project_core(a, o, x, y, z, opac_in, V, Pm, radius, near_culled, hint, cov3, rgbf, depth_out);
 }
 
 }  // namespace ghr

@@ -1,5 +1,7 @@
 """Tuning: onesweep sort time by key count for a forced keys-per-thread (GHR_SORT_ITEMS read once per process).
-    GHR_SORT_ITEMS=12 python tools/sort_items_sweep.py"""
+    GHR_SORT_ITEMS=12 python tools/sort_items_sweep.py [N ...]
+Also the ncu target for the sort alone (6 kernels per sort: histogram + 5 passes at 45 bits):
+    ncu --set full -k regex:'onesweep|sort_histogram' --launch-skip 18 -c 6 ... python tools/sort_items_sweep.py 16777216"""
 import os, sys
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
@@ -9,7 +11,8 @@ l = _lib.lib()
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 bits = 45
 out = []
-for N in [3 << 17, 1 << 19, 3 << 18, 1 << 20, 3 << 19, 1 << 21, 3 << 20, 1 << 22, 1 << 23]:
+SIZES = [int(a) for a in sys.argv[1:]] or [3 << 17, 1 << 19, 3 << 18, 1 << 20, 3 << 19, 1 << 21, 3 << 20, 1 << 22, 1 << 23]
+for N in SIZES:
     g = torch.Generator(device="cpu").manual_seed(N & 0xFFFF)
     tile = torch.randint(0, 8160, (N,), generator=g, dtype=torch.int64)
     depth = (torch.rand(N, generator=g) * 9.8 + 0.2).view(torch.int32).to(torch.int64)
