@@ -12,12 +12,20 @@
 //                      every key as trivial (skipped: such a pass is the
 //                      identity permutation), assigns ping-pong sources on
 //                      the device (no host sync)
-//   pass kernel (xK) : one sweep per non-trivial pass: per-warp ranking with
-//                      match-any, per-digit chained scan over tiles
-//                      (decoupled look-back, 4 predecessors per round trip),
-//                      then the tile is put in digit order in shared memory
-//                      and written out so that consecutive threads write
-//                      consecutive addresses of a digit's run.
+//   pass kernel (xK) : one sweep per non-trivial pass: per-warp ranking --
+//                      MATCH.ANY where the warp's digits come in runs (the
+//                      keys of a frame), one ballot per digit bit where
+//                      they are all different (MATCH.ANY's latency grows
+//                      with the distinct values) --, per-digit chained scan
+//                      over tiles (decoupled look-back, 4 predecessors per
+//                      round trip), then keys and values are put in digit
+//                      order in shared memory and written out so that
+//                      consecutive threads write consecutive addresses of a
+//                      digit's run.  2 .. 12 keys per thread by size
+//                      (sort_items_per_thread): a tile's fixed work -- 512
+//                      digit scans and look-backs -- is what a large sort
+//                      spreads over more keys.  DESIGN.md 5.4b has the
+//                      measurements behind each choice.
 //
 // Roofline: HBM stream, algorithmic bytes N*(8 + 24*passes).
 // The pair count N is read from device memory (no D2H sync) when n_dev is
@@ -29,9 +37,6 @@
 
 #ifndef GHR_SORT_RANK
 #define GHR_SORT_RANK 2
-#endif
-#ifndef GHR_SORT_CTAS3
-#define GHR_SORT_CTAS3 0
 #endif
 #ifndef GHR_SORT_MATCH_RUNS
 #define GHR_SORT_MATCH_RUNS 12  // of 31 neighbour pairs
@@ -147,7 +152,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_histogram_kernel(const uint
 }
 
 template <int ITEMS>
-__global__ void __launch_bounds__(kSortThreads, (GHR_SORT_CTAS3 && ITEMS <= 4) ? 3 : 2) onesweep_pass_kernel(uint64_t* keys_a, uint64_t* keys_b,
+__global__ void __launch_bounds__(kSortThreads, 2) onesweep_pass_kernel(uint64_t* keys_a, uint64_t* keys_b,
                                                                         uint32_t* vals_a, uint32_t* vals_b,
                                                                         const uint32_t* __restrict__ n_dev,
                                                                         int64_t capacity, int pass, uint32_t digit_mask,
