@@ -51,20 +51,21 @@ def test_layout_is_aligned_and_monotone():
 def test_binning_capacity_is_recoverable_from_the_buffer_size():
     """backward must not depend on a side table for the capacity a binning buffer was laid out for.  The
     buffer size is strictly increasing in the capacity (multiples of 64), across the sort's keys-per-tile regime changes
-    at 2^17 and 3*2^17 pairs too, so ghr_binning_capacity inverts it."""
+    at 2^17, 3*2^17 and 5*2^17 pairs too, so ghr_binning_capacity inverts it."""
     l = _lib.lib()
     for (P, W, H) in ((50000, 512, 512), (3_000_000, 1920, 1080), (7, 16, 16)):
         prev = -1
         caps = list(range(0, 64 * 40, 64)) + [(1 << 17) - 64, 1 << 17, (1 << 17) + 64, (3 << 17) - 64, 3 << 17,
-                                              (3 << 17) + 64, 1 << 20, 12_345_664, (1 << 30) - 64]
+                                              (3 << 17) + 64, (5 << 17) - 64, 5 << 17, (5 << 17) + 64, 1 << 20, 12_345_664,
+                                              (1 << 30) - 64]
         for cap in sorted(set(caps)):
             nbytes = _lib.state_layout(P, cap, W, H).binning_bytes
             assert nbytes > prev, (P, W, H, cap)
             prev = nbytes
             assert l.ghr_binning_capacity(P, W, H, nbytes) == cap
             assert l.ghr_binning_capacity(P, W, H, nbytes + 1) == -1
-    # dense sweep over the two regime boundaries
-    for lo in ((1 << 17) - 64 * 300, (3 << 17) - 64 * 300):
+    # dense sweep over the regime boundaries
+    for lo in ((1 << 17) - 64 * 300, (3 << 17) - 64 * 300, (5 << 17) - 64 * 300):
         sizes = [_lib.state_layout(1000, lo + 64 * i, 512, 512).binning_bytes for i in range(600)]
         assert all(b > a for a, b in zip(sizes, sizes[1:]))
 

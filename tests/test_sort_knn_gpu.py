@@ -31,7 +31,10 @@ def make_keys(N, tiles, seed, depth_lo=0.2, depth_hi=10.0):
     return keys.cuda(), torch.arange(N, dtype=torch.int32).cuda()
 
 
-@pytest.mark.parametrize("N", [0, 1, 31, 1000, 1025, 4097, 100003, 1 << 20, (1 << 20) + 7, 5_000_011])
+# every keys-per-thread regime of the pass kernel (2 / 4 / 8 / 12: up to 2^17 / 3*2^17 / 5*2^17 keys / above), full and
+# ragged last tiles
+@pytest.mark.parametrize("N", [0, 1, 31, 1000, 1025, 4097, 100003, 300_001, 3 << 17, 600_011, 1 << 20, (1 << 20) + 7,
+                               5_000_011])
 def test_onesweep_matches_stable_sort(N):
     tiles = 1024
     bits = 32 + 10
@@ -55,6 +58,20 @@ def test_onesweep_skips_constant_digit_passes_and_matches_cub():
         kc, vc, _ = ref_cuda.cub_sort_pairs(keys, vals, 32 + 12)
         torch.cuda.synchronize()
         assert torch.equal(k, kc) and torch.equal(v, vc)
+
+
+@pytest.mark.parametrize("N", [50_000, 1_500_000])
+def test_onesweep_keys_in_runs_and_runs_mixed_with_random_keys(N):
+    """The pass kernel ranks a warp's keys with MATCH.ANY when their digits come in runs (a frame: the tiles of one
+    Gaussian share their depth) and with one ballot per digit bit otherwise; the choice is per warp, so a sort whose
+    first half is runs and second half is random takes both paths in the same launch.  Stability decides inside a run."""
+    base, _ = make_keys(N, 1024, seed=7)
+    runs = base[: N // 2].repeat_interleave(5)[: N // 2]          # runs of five identical keys
+    keys = torch.cat([runs, base[N // 2:]]).contiguous()
+    vals = torch.arange(N, dtype=torch.int32).cuda()
+    k, v = ghr_sort(keys, vals, 32 + 10)
+    ks, order = torch.sort(keys, stable=True)
+    assert torch.equal(k[:N], ks) and torch.equal(v[:N].long(), order)
 
 
 def test_onesweep_full_64bit_and_odd_bits():
